@@ -1,0 +1,334 @@
+// GEMM for every dense projection of the IQ path (see include/b200iq.h: b200iq_gemm).
+//
+// tcgen05 path (default): one 128 x BN output tile per CTA (x split-K slices in grid.z).
+//   warp 0  : TMA producer   (cp.async.bulk.tensor.2d, 128B swizzle, mbarrier complete_tx)
+//   warp 1  : MMA issuer     (one elected lane, tcgen05.mma.cta_group::1.kind::tf32, fp32 accum in TMEM)
+//   warps 2-5: epilogue      (tcgen05.ld 32x32b -> bias / residual / relu / relu-mask -> global)
+// Operands may be K-major ([rows,K] row-major) or MN-major ([K,rows] row-major): the second form is
+// what the backward GEMMs (dX = dY.W, dW = dY^T.X) read, so no tensor is ever transposed in HBM.
+// Out-of-bounds rows/cols/k are zero-filled by TMA, so arbitrary M, N, K are handled without padding.
+#include "common.cuh"
+
+namespace b200iq {
+
+static constexpr int BM = 128;
+static constexpr int BK = 32;          // 32 fp32 = 128 bytes = one swizzle row
+static constexpr int UMMA_K = 8;       // kind::tf32
+static constexpr int GEMM_THREADS = 192;
+
+struct GemmEpi {
+  float* C; const float* bias; const float* residual;
+  int M, N, ldc, ldr, flags; float alpha;
+};
+
+// ------------------------------------------------------------------ PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t addr = smem_u32(bar), done;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done) : "r"(addr), "r"(parity) : "memory");
+  } while (!done);
+}
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* tm, int c0, int c1, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+      ::"r"(smem_u32(dst)), "l"((uint64_t)tm), "r"(c0), "r"(c1), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_c, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_c), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
+      "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr) : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+
+// shared-memory matrix descriptor, 128B swizzle, sm_100 descriptor version 1
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  return (uint64_t)((saddr >> 4) & 0x3FFF) | ((uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16) |
+         ((uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32) | (1ull << 46) | (2ull << 61);
+}
+
+// epilogue math shared by both paths
+__device__ __forceinline__ float epi_value(float acc, const GemmEpi& e, int row, int col, bool add_bias) {
+  float v = acc * e.alpha;
+  if ((e.flags & B200IQ_GEMM_BIAS) && add_bias) v += __ldg(e.bias + col);
+  if (e.flags & B200IQ_GEMM_RESIDUAL) v += __ldg(e.residual + (size_t)row * e.ldr + col);
+  if (e.flags & B200IQ_GEMM_RELU) v = fmaxf(v, 0.f);
+  if (e.flags & B200IQ_GEMM_RELU_MASK) v = (__ldg(e.residual + (size_t)row * e.ldr + col) > 0.f) ? v : 0.f;
+  return v;
+}
+
+template <int BN, bool A_MN, bool B_MN, int STAGES>
+__global__ void __launch_bounds__(GEMM_THREADS)
+gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                 GemmEpi epi, int kblocks_total, int kblocks_per_split) {
+  constexpr int A_BYTES = BM * 128, B_BYTES = BN * 128, STAGE_BYTES = A_BYTES + B_BYTES;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  __shared__ uint64_t full_bar[STAGES], empty_bar[STAGES], tmem_full_bar;
+  __shared__ uint32_t tmem_base_s;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+  const int kb0 = blockIdx.z * kblocks_per_split;
+  const int kb1 = min(kblocks_total, kb0 + kblocks_per_split);
+  const int nkb = kb1 - kb0;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    mbar_init(&tmem_full_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 2) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "n"(BN) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_s;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      for (int it = 0; it < nkb; ++it) {
+        const int s = it % STAGES, ph = (it / STAGES) & 1, k0 = (kb0 + it) * BK;
+        mbar_wait(&empty_bar[s], ph ^ 1);
+        mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+        uint8_t* sa = smem + s * STAGE_BYTES;
+        uint8_t* sb = sa + A_BYTES;
+        if (!A_MN) tma_load_2d(sa, &tmA, k0, m0, &full_bar[s]);
+        else
+          for (int i = 0; i < BM / 32; ++i) tma_load_2d(sa + i * (BK * 128), &tmA, m0 + 32 * i, k0, &full_bar[s]);
+        if (!B_MN) tma_load_2d(sb, &tmB, k0, n0, &full_bar[s]);
+        else
+          for (int i = 0; i < BN / 32; ++i) tma_load_2d(sb + i * (BK * 128), &tmB, n0 + 32 * i, k0, &full_bar[s]);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // instruction descriptor: D=f32, A=B=tf32, majors, N>>3 @17, M>>4 @24
+      const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
+                             ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+      for (int it = 0; it < nkb; ++it) {
+        const int s = it % STAGES, ph = (it / STAGES) & 1;
+        mbar_wait(&full_bar[s], ph);
+        tc_fence_after();
+        const uint32_t sa = smem_u32(smem + s * STAGE_BYTES), sb = sa + A_BYTES;
+#pragma unroll
+        for (int k = 0; k < BK / UMMA_K; ++k) {
+          const uint64_t ad = A_MN ? umma_desc(sa + k * 1024, BK * 128, 1024) : umma_desc(sa + k * 32, 16, 1024);
+          const uint64_t bd = B_MN ? umma_desc(sb + k * 1024, BK * 128, 1024) : umma_desc(sb + k * 32, 16, 1024);
+          umma_tf32(tmem_base, ad, bd, idesc, (it > 0 || k > 0) ? 1u : 0u);
+        }
+        umma_commit(&empty_bar[s]);
+      }
+      umma_commit(&tmem_full_bar);
+    }
+  } else {
+    const int q = warp & 3;  // TMEM lane quadrant this warp may read
+    mbar_wait(&tmem_full_bar, 0);
+    tc_fence_after();
+    const int row = m0 + q * 32 + lane;
+    const bool add_bias = (blockIdx.z == 0);
+    const bool vec_ok = ((epi.ldc & 3) == 0) && ((((uintptr_t)epi.C) & 15) == 0);
+#pragma unroll 1
+    for (int c = 0; c < BN / 32; ++c) {
+      uint32_t r[32];
+      tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + c * 32, r);
+      const int col0 = n0 + c * 32;
+      if (row < epi.M && col0 < epi.N) {
+        float* crow = epi.C + (size_t)row * epi.ldc;
+        if (epi.flags & B200IQ_GEMM_ACCUM) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (col0 + j < epi.N) atomicAdd(crow + col0 + j, epi_value(__uint_as_float(r[j]), epi, row, col0 + j, add_bias));
+        } else if (vec_ok && col0 + 32 <= epi.N) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            float4 v;
+            v.x = epi_value(__uint_as_float(r[j + 0]), epi, row, col0 + j + 0, true);
+            v.y = epi_value(__uint_as_float(r[j + 1]), epi, row, col0 + j + 1, true);
+            v.z = epi_value(__uint_as_float(r[j + 2]), epi, row, col0 + j + 2, true);
+            v.w = epi_value(__uint_as_float(r[j + 3]), epi, row, col0 + j + 3, true);
+            *reinterpret_cast<float4*>(crow + col0 + j) = v;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (col0 + j < epi.N) crow[col0 + j] = epi_value(__uint_as_float(r[j]), epi, row, col0 + j, true);
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(BN) : "memory");
+  }
+}
+
+// ------------------------------------------------------------------ exact-fp32 CUDA-core path
+// 64x64 tile, 256 threads, 4x4 micro-tile; generic strides cover every operand layout.
+__global__ void __launch_bounds__(256)
+gemm_simt_kernel(const float* __restrict__ A, const float* __restrict__ B, GemmEpi epi, int K,
+                 long sam, long sak, long sbn, long sbk, int kchunk) {
+  __shared__ float As[16][64 + 4], Bs[16][64 + 4];
+  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+  const int m0 = blockIdx.y * 64, n0 = blockIdx.x * 64;
+  const int kbeg = blockIdx.z * kchunk, kend = min(K, kbeg + kchunk);
+  float acc[4][4] = {};
+  for (int k0 = kbeg; k0 < kend; k0 += 16) {
+    for (int i = threadIdx.x; i < 64 * 16; i += 256) {
+      int kk, mm;
+      if (sak == 1) { kk = i & 15; mm = i >> 4; } else { mm = i & 63; kk = i >> 6; }
+      int gm = m0 + mm, gk = k0 + kk;
+      As[kk][mm] = (gm < epi.M && gk < kend) ? A[gm * sam + gk * sak] : 0.f;
+      int nn;
+      if (sbk == 1) { kk = i & 15; nn = i >> 4; } else { nn = i & 63; kk = i >> 6; }
+      int gn = n0 + nn; gk = k0 + kk;
+      Bs[kk][nn] = (gn < epi.N && gk < kend) ? B[gn * sbn + gk * sbk] : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < 16; ++kk) {
+      float a[4], b[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) { a[i] = As[kk][ty * 4 + i]; b[i] = Bs[kk][tx * 4 + i]; }
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+  for (int i = 0; i < 4; ++i) {
+    int row = m0 + ty * 4 + i;
+    if (row >= epi.M) continue;
+    for (int j = 0; j < 4; ++j) {
+      int col = n0 + tx * 4 + j;
+      if (col >= epi.N) continue;
+      float v = epi_value(acc[i][j], epi, row, col, blockIdx.z == 0);
+      float* dst = epi.C + (size_t)row * epi.ldc + col;
+      if (epi.flags & B200IQ_GEMM_ACCUM) atomicAdd(dst, v); else *dst = v;
+    }
+  }
+}
+
+// ------------------------------------------------------------------ host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPointByVersion("cuTensorMapEncodeTiled", &p, 12000, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)p;
+  }
+  return fn;
+}
+
+// 2-D fp32 tensor map over a row-major [rows, cols] matrix with leading dimension ld; box = [box_rows, 32 cols]
+static int make_map(CUtensorMap* tm, const float* base, int rows, int cols, int ld, int box_rows) {
+  EncodeTiledFn enc = get_encode();
+  B200IQ_CHECK_ARG(enc, "cuTensorMapEncodeTiled entry point not available");
+  cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t gstr[1] = {(cuuint64_t)ld * 4};
+  cuuint32_t box[2] = {32, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)base, gdim, gstr, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  B200IQ_CHECK_ARG(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed (%d) rows=%d cols=%d ld=%d", (int)r, rows, cols, ld);
+  return 0;
+}
+
+template <int BN, bool A_MN, bool B_MN>
+static int launch_tc(const CUtensorMap& ta, const CUtensorMap& tb, const GemmEpi& e, int K, int split, cudaStream_t st) {
+  constexpr int STAGES = 3;
+  constexpr int SMEM = STAGES * (BM * 128 + BN * 128) + 1024;
+  static bool attr_done = false;
+  auto kern = gemm_tf32_kernel<BN, A_MN, B_MN, STAGES>;
+  if (!attr_done) {
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
+    attr_done = true;
+  }
+  int kblocks = ceil_div(K, BK);
+  if (split > kblocks) split = kblocks;
+  int per = ceil_div(kblocks, split);
+  split = ceil_div(kblocks, per);
+  dim3 grid(ceil_div(e.N, BN), ceil_div(e.M, BM), split);
+  kern<<<grid, GEMM_THREADS, SMEM, st>>>(ta, tb, e, kblocks, per);
+  return launch_status("gemm_tf32_kernel");
+}
+
+}  // namespace b200iq
+
+using namespace b200iq;
+
+extern "C" int b200iq_gemm(const B200iqGemm* p, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  B200IQ_CHECK_ARG(p && p->A && p->B && p->C, "gemm: null pointer");
+  B200IQ_CHECK_ARG(p->M > 0 && p->N > 0 && p->K > 0, "gemm: bad shape M=%d N=%d K=%d", p->M, p->N, p->K);
+  const int f = p->flags;
+  const bool amn = f & B200IQ_GEMM_A_MN, bmn = f & B200IQ_GEMM_B_MN;
+  B200IQ_CHECK_ARG(!(f & B200IQ_GEMM_BIAS) || p->bias, "gemm: BIAS without bias pointer");
+  B200IQ_CHECK_ARG(!(f & (B200IQ_GEMM_RESIDUAL | B200IQ_GEMM_RELU_MASK)) || p->residual, "gemm: residual/gate pointer missing");
+  B200IQ_CHECK_ARG(!((f & B200IQ_GEMM_RESIDUAL) && (f & B200IQ_GEMM_RELU_MASK)), "gemm: RESIDUAL and RELU_MASK are exclusive");
+  int split = p->split_k < 1 ? 1 : p->split_k;
+  B200IQ_CHECK_ARG(split == 1 || ((f & B200IQ_GEMM_ACCUM) && !(f & (B200IQ_GEMM_RELU | B200IQ_GEMM_RELU_MASK | B200IQ_GEMM_RESIDUAL))),
+                   "gemm: split_k>1 needs ACCUM and a linear epilogue");
+  B200IQ_CHECK_ARG(p->lda >= (amn ? p->M : p->K) && p->ldb >= (bmn ? p->N : p->K) && p->ldc >= p->N, "gemm: leading dimension too small");
+  GemmEpi e{p->C, p->bias, p->residual, p->M, p->N, p->ldc, p->ldr, f, p->alpha};
+
+  if (f & B200IQ_GEMM_SIMT) {
+    long sam = amn ? 1 : p->lda, sak = amn ? p->lda : 1, sbn = bmn ? 1 : p->ldb, sbk = bmn ? p->ldb : 1;
+    int kchunk = ceil_div(ceil_div(p->K, split), 16) * 16;
+    dim3 grid(ceil_div(p->N, 64), ceil_div(p->M, 64), ceil_div(p->K, kchunk));
+    gemm_simt_kernel<<<grid, 256, 0, st>>>(p->A, p->B, e, p->K, sam, sak, sbn, sbk, kchunk);
+    return launch_status("gemm_simt_kernel");
+  }
+
+  B200IQ_CHECK_ARG((((uintptr_t)p->A) & 15) == 0 && (((uintptr_t)p->B) & 15) == 0, "gemm: A/B must be 16-byte aligned");
+  B200IQ_CHECK_ARG((p->lda & 3) == 0 && (p->ldb & 3) == 0, "gemm: lda/ldb must be multiples of 4 (lda=%d ldb=%d)", p->lda, p->ldb);
+  CUtensorMap ta, tb;
+  int rc;
+  constexpr int BN = 128;
+  if (!amn) rc = make_map(&ta, p->A, p->M, p->K, p->lda, BM); else rc = make_map(&ta, p->A, p->K, p->M, p->lda, BK);
+  if (rc) return rc;
+  if (!bmn) rc = make_map(&tb, p->B, p->N, p->K, p->ldb, BN); else rc = make_map(&tb, p->B, p->K, p->N, p->ldb, BK);
+  if (rc) return rc;
+  if (!amn && !bmn) return launch_tc<BN, false, false>(ta, tb, e, p->K, split, st);
+  if (!amn && bmn) return launch_tc<BN, false, true>(ta, tb, e, p->K, split, st);
+  if (amn && !bmn) return launch_tc<BN, true, false>(ta, tb, e, p->K, split, st);
+  return launch_tc<BN, true, true>(ta, tb, e, p->K, split, st);
+}
