@@ -69,9 +69,11 @@ __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 
 // shared-memory matrix descriptor, 128B swizzle, sm_100 descriptor version 1
-__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+// layout: 2 = SWIZZLE_128B (16-byte chunks), 1 = SWIZZLE_128B_BASE32B (32-byte chunks; the only
+// swizzle the tensor core accepts for MN-major tf32 operands)
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint64_t layout) {
   return (uint64_t)((saddr >> 4) & 0x3FFF) | ((uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16) |
-         ((uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32) | (1ull << 46) | (2ull << 61);
+         ((uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32) | (1ull << 46) | (layout << 61);
 }
 
 // epilogue math shared by both paths
@@ -142,8 +144,8 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const uint32_t sa = smem_u32(smem + s * STAGE_BYTES), sb = sa + A_BYTES;
 #pragma unroll
         for (int k = 0; k < BK / UMMA_K; ++k) {
-          const uint64_t ad = A_MN ? umma_desc(sa + k * 1024, BK * 128, 1024) : umma_desc(sa + k * 32, 16, 1024);
-          const uint64_t bd = B_MN ? umma_desc(sb + k * 1024, BK * 128, 1024) : umma_desc(sb + k * 32, 16, 1024);
+          const uint64_t ad = A_MN ? umma_desc(sa + k * 1024, BK * 128, 512, 1) : umma_desc(sa + k * 32, 16, 1024, 2);
+          const uint64_t bd = B_MN ? umma_desc(sb + k * 1024, BK * 128, 512, 1) : umma_desc(sb + k * 32, 16, 1024, 2);
           umma_tf32(tmem_base, ad, bd, idesc, (it > 0 || k > 0) ? 1u : 0u);
         }
         umma_commit(&empty_bar[s]);
@@ -258,7 +260,7 @@ static EncodeTiledFn get_encode() {
 }
 
 // 2-D fp32 tensor map over a row-major [rows, cols] matrix with leading dimension ld; box = [box_rows, 32 cols]
-static int make_map(CUtensorMap* tm, const float* base, int rows, int cols, int ld, int box_rows) {
+static int make_map(CUtensorMap* tm, const float* base, int rows, int cols, int ld, int box_rows, bool mn_major) {
   EncodeTiledFn enc = get_encode();
   B200IQ_CHECK_ARG(enc, "cuTensorMapEncodeTiled entry point not available");
   cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
@@ -266,7 +268,8 @@ static int make_map(CUtensorMap* tm, const float* base, int rows, int cols, int 
   cuuint32_t box[2] = {32, (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)base, gdim, gstr, box, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, mn_major ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   B200IQ_CHECK_ARG(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed (%d) rows=%d cols=%d ld=%d", (int)r, rows, cols, ld);
   return 0;
@@ -323,9 +326,9 @@ extern "C" int b200iq_gemm(const B200iqGemm* p, void* stream) {
   CUtensorMap ta, tb;
   int rc;
   constexpr int BN = 128;
-  if (!amn) rc = make_map(&ta, p->A, p->M, p->K, p->lda, BM); else rc = make_map(&ta, p->A, p->K, p->M, p->lda, BK);
+  if (!amn) rc = make_map(&ta, p->A, p->M, p->K, p->lda, BM, false); else rc = make_map(&ta, p->A, p->K, p->M, p->lda, BK, true);
   if (rc) return rc;
-  if (!bmn) rc = make_map(&tb, p->B, p->N, p->K, p->ldb, BN); else rc = make_map(&tb, p->B, p->K, p->N, p->ldb, BK);
+  if (!bmn) rc = make_map(&tb, p->B, p->N, p->K, p->ldb, BN, false); else rc = make_map(&tb, p->B, p->K, p->N, p->ldb, BK, true);
   if (rc) return rc;
   if (!amn && !bmn) return launch_tc<BN, false, false>(ta, tb, e, p->K, split, st);
   if (!amn && bmn) return launch_tc<BN, false, true>(ta, tb, e, p->K, split, st);
