@@ -64,6 +64,90 @@ typedef struct B200iqGemm {
  * leading dimensions that are multiples of 4 floats. */
 int b200iq_gemm(const B200iqGemm* p, void* stream);
 
+/* ---------------------------------------------------------- row / elementwise ops */
+/* out[m,:] = table[ids[m],:]   replaces: nn.Embedding fwd, models/iq.py:71-78 (also decoder_rnn.py:102, encoder_rnn.py:78) */
+int b200iq_embed_gather(const int* ids, const float* table, float* out, int M, int E, int V, void* stream);
+/* dtable[ids[m],:] += dout[m,:] unless ids[m]==pad_id (pad_id<0: no padding row)   replaces: Embedding backward */
+int b200iq_embed_scatter_add(const int* ids, const float* dout, float* dtable, int M, int E, int V, int pad_id, void* stream);
+/* x[b,t,:] += timing[t,:]; token 0 also gets add0[b,:] + add1[b,:] (either may be NULL)
+ * replaces: models/transformer_layers.py:146,214; models/decoder_transformer.py:31-34,46 */
+int b200iq_add_timing(float* x, const float* timing, const float* add0, const float* add1, int B, int n, int H, void* stream);
+/* dst[b,:] (+)= src[b*n,:]  /  dst[b*n,:] += src[b,:]   (gradient plumbing of the token-0 adds; encoder_transformer.py:32) */
+int b200iq_tok0_gather(const float* src, float* dst, int B, int n, int H, int accumulate, void* stream);
+int b200iq_tok0_scatter_add(const float* src, float* dst, int B, int n, int H, void* stream);
+/* torch.nn.LayerNorm(H) forward (saves mean/rstd per row) and backward (dgamma/dbeta accumulate)
+ * replaces: models/transformer_layers.py:134,151,202,220,256-257,320-322 */
+int b200iq_layernorm_fwd(const float* x, const float* gamma, const float* beta, float* y, float* mean, float* rstd,
+                         int M, int H, float eps, void* stream);
+int b200iq_layernorm_bwd(const float* dy, const float* x, const float* gamma, const float* mean, const float* rstd,
+                         float* dx, float* dgamma, float* dbeta, int M, int H, int accumulate_dx, void* stream);
+/* out[c] += sum_m x[m,c]  (bias gradients) */
+int b200iq_colsum_add(const float* x, float* out, int M, int N, int ld, void* stream);
+/* dpre = dy * (y > 0); dbias[c] += colsum(dpre) (dbias may be NULL)   replaces: ReLU backward, transformer_layers.py:405 */
+int b200iq_relu_bwd_colsum(const float* dy, const float* y, float* dpre, float* dbias, int M, int N, void* stream);
+/* inverted dropout in place with a Philox4x32-10 mask keyed (seed, offset); re-applying it to the gradient
+ * with the same key is the backward.   replaces: nn.Dropout at transformer_layers.py:406,520; base_rnn.py:41 */
+int b200iq_dropout(float* x, size_t n, float p, uint64_t seed, uint64_t offset, void* stream);
+/* out ~ N(0,1), Philox4x32-10 + Box-Muller (oracle/philox.py is the bit-level CPU twin)
+ * replaces: torch.randn on the CPU + H2D copy, models/transformer_layers.py:45 */
+int b200iq_randn(float* out, size_t n, uint64_t seed, uint64_t offset, void* stream);
+/* y = a*x + b*y */
+int b200iq_axpby(const float* x, float* y, size_t n, float a, float b, void* stream);
+
+/* ---------------------------------------------------------- fused attention (n <= 128) */
+typedef struct B200iqAttention {
+  const float* q;        /* [B*nq, ldq], head h at columns [h*head_dim, (h+1)*head_dim) */
+  const float* k;        /* [B*nk, ldk] */
+  const float* v;        /* [B*nk, ldv] */
+  float* out;            /* [B*nq, ldo] merged heads (fwd only) */
+  int ldq, ldk, ldv, ldo;
+  const int* key_ids;    /* [B, nk] token ids; keys equal to pad_id are masked; NULL = no padding mask */
+  int pad_id;
+  int causal;            /* 1: key j > query i is masked (transformer_layers.py:207) */
+  int B, num_heads, nq, nk, head_dim;
+  float scale;           /* head_dim^-0.5 (transformer_layers.py:449,499) */
+  float drop_p;          /* attention dropout (transformer_layers.py:520); mask = Philox(seed, offset) */
+  uint64_t seed, offset;
+} B200iqAttention;
+/* replaces: models/transformer_layers.py:494-526; mask fill is the finite -1e18 of :506 */
+int b200iq_attention_fwd(const B200iqAttention* p, void* stream);
+/* recomputes the probabilities from q/k (nothing is stashed by fwd); writes dq/dk/dv (not accumulated) */
+int b200iq_attention_bwd(const B200iqAttention* p, const float* dout, float* dq, float* dk, float* dv,
+                         int lddq, int lddk, int lddv, void* stream);
+
+/* ---------------------------------------------------------- losses */
+/* count[0] = #(targets != pad_id)  (the CE "mean over non-pad" denominator, train_iq.py:82-83) */
+int b200iq_count_nonpad(const int* targets, int n, int pad_id, float* count, void* stream);
+/* Softmax cross-entropy over `rows` logits rows, forward AND gradient in one pass: loss_sum += sum_r (lse_r - logit_r[t_r]) / count;
+ * with write_grad the rows are overwritten by coef * (softmax - onehot) / count (zero rows where t_r == pad_id).  The caller feeds
+ * row CHUNKS of the vocabulary projection, so the (B*T, V) logits tensor never exists.
+ * replaces: models/decoder_transformer.py:40 + train_iq.py:82-83; models/decoder_rnn.py:107 + old_train_iq.py:122-126 */
+int b200iq_ce_rows(float* logits, int ld, const int* targets, int rows, int V, int pad_id, const float* count,
+                   float coef, float* loss_sum, int write_grad, void* stream);
+/* CE(repeat(z_logit, T), targets) without materialising the repeat.   replaces: train_iq.py:92-94 */
+int b200iq_ce_aux(const float* z_logit, float* dz_logit, const int* targets, int B, int T, int V, int pad_id,
+                  const float* count, float coef, float* loss_sum, void* stream);
+/* prior/post are [B,2L] = [mu | logvar]; z = eps*exp(.5*logvar_q)+mu_q (prior when post==NULL); kld_sum += mean_b KL(q||p)
+ * replaces: models/transformer_layers.py:43-58,536-540 */
+int b200iq_latent_fwd(const float* prior, const float* post, const float* eps, float* z, float* kld_sum, int B, int L, void* stream);
+int b200iq_latent_bwd(const float* prior, const float* post, const float* eps, const float* dz, float kld_coef,
+                      float* dprior, float* dpost, int B, int L, void* stream);
+/* nn.BatchNorm1d(H, momentum) on [B,H]; training: batch statistics + running-stat update.   replaces: models/encoder_cnn.py:21,34 */
+int b200iq_bn_fwd(const float* x, const float* gamma, const float* beta, float* y, float* save_mean, float* save_rstd,
+                  float* running_mean, float* running_var, int B, int H, float eps, float momentum, int training, void* stream);
+int b200iq_bn_bwd(const float* dy, const float* x, const float* gamma, const float* save_mean, const float* save_rstd,
+                  float* dx, float* dgamma, float* dbeta, int B, int H, void* stream);
+/* loss_sum += mean((a-b)^2); da += coef*2(a-b)/n; db (+)= -coef*2(a-b)/n (da/db/loss_sum may be NULL)   replaces: train_iq.py:84 */
+int b200iq_mse(const float* a, const float* b, size_t n, float coef, float* loss_sum, float* da, float* db, int accumulate_db, void* stream);
+
+/* ---------------------------------------------------------- optimizer */
+/* out[0] = sum(grad^2) over the flat gradient arena */
+int b200iq_grad_sumsq(const float* grad, size_t n, float* out, void* stream);
+/* clip_grad_norm_(max_norm) + Adam on flat arenas; hyper (device) = {lr, 1-beta1^t, 1-beta2^t, grad_scale}.
+ * replaces: train_iq.py:259-261 (Adam), :372 (gradient_clip_val=5), :252-257 (LR written by the host into hyper[0]) */
+int b200iq_adam_step(float* param, float* grad, float* exp_avg, float* exp_avg_sq, size_t n, const float* hyper,
+                     const float* normsq, float beta1, float beta2, float eps, float max_norm, int zero_grad, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
