@@ -55,21 +55,22 @@ __global__ void add_timing_kernel(float* __restrict__ x, const float* __restrict
 }
 
 // dst[b, :] (+)= src[b*n + 0, :]  — gathers the gradient of token 0 of every sequence
-__global__ void tok0_gather_kernel(const float* __restrict__ src, float* __restrict__ dst, int B, int n, int H, int accumulate) {
+__global__ void tok0_gather_kernel(const float* __restrict__ src, float* __restrict__ dst, int B, int n, int H, int ldd, int accumulate) {
   size_t total = (size_t)B * H;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
     int c = (int)(i % H), b = (int)(i / H);
     float v = src[(size_t)b * n * H + c];
-    dst[i] = accumulate ? dst[i] + v : v;
+    size_t o = (size_t)b * ldd + c;
+    dst[o] = accumulate ? dst[o] + v : v;
   }
 }
 
 // dst[b*n + 0, :] += src[b, :]
-__global__ void tok0_scatter_kernel(const float* __restrict__ src, float* __restrict__ dst, int B, int n, int H) {
+__global__ void tok0_scatter_kernel(const float* __restrict__ src, float* __restrict__ dst, int B, int n, int H, int lds) {
   size_t total = (size_t)B * H;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
     int c = (int)(i % H), b = (int)(i / H);
-    dst[(size_t)b * n * H + c] += src[i];
+    dst[(size_t)b * n * H + c] += src[(size_t)b * lds + c];
   }
 }
 
@@ -205,10 +206,10 @@ __global__ void randn_kernel(float* __restrict__ out, size_t n, uint64_t seed, u
   }
 }
 
-// y = a*x + b*y
-__global__ void axpby_kernel(const float* __restrict__ x, float* __restrict__ y, size_t n, float a, float b) {
+// out = a*x + b*y  (out may alias x or y)
+__global__ void axpby_kernel(const float* x, const float* y, float* out, size_t n, float a, float b) {
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
-    y[i] = a * x[i] + (b == 0.f ? 0.f : b * y[i]);
+    out[i] = a * x[i] + (b == 0.f ? 0.f : b * y[i]);
 }
 
 static inline int grid_for(size_t n, int threads) {
@@ -242,15 +243,15 @@ extern "C" int b200iq_add_timing(float* x, const float* timing, const float* add
   return launch_status("add_timing");
 }
 
-extern "C" int b200iq_tok0_gather(const float* src, float* dst, int B, int n, int H, int accumulate, void* stream) {
-  B200IQ_CHECK_ARG(src && dst && B > 0 && n > 0 && H > 0, "tok0_gather: bad args");
-  tok0_gather_kernel<<<grid_for((size_t)B * H, 256), 256, 0, ST>>>(src, dst, B, n, H, accumulate);
+extern "C" int b200iq_tok0_gather(const float* src, float* dst, int B, int n, int H, int ldd, int accumulate, void* stream) {
+  B200IQ_CHECK_ARG(src && dst && B > 0 && n > 0 && H > 0 && ldd >= H, "tok0_gather: bad args");
+  tok0_gather_kernel<<<grid_for((size_t)B * H, 256), 256, 0, ST>>>(src, dst, B, n, H, ldd, accumulate);
   return launch_status("tok0_gather");
 }
 
-extern "C" int b200iq_tok0_scatter_add(const float* src, float* dst, int B, int n, int H, void* stream) {
-  B200IQ_CHECK_ARG(src && dst && B > 0 && n > 0 && H > 0, "tok0_scatter_add: bad args");
-  tok0_scatter_kernel<<<grid_for((size_t)B * H, 256), 256, 0, ST>>>(src, dst, B, n, H);
+extern "C" int b200iq_tok0_scatter_add(const float* src, float* dst, int B, int n, int H, int lds, void* stream) {
+  B200IQ_CHECK_ARG(src && dst && B > 0 && n > 0 && H > 0 && lds >= H, "tok0_scatter_add: bad args");
+  tok0_scatter_kernel<<<grid_for((size_t)B * H, 256), 256, 0, ST>>>(src, dst, B, n, H, lds);
   return launch_status("tok0_scatter_add");
 }
 
@@ -304,8 +305,8 @@ extern "C" int b200iq_randn(float* out, size_t n, uint64_t seed, uint64_t offset
   return launch_status("randn");
 }
 
-extern "C" int b200iq_axpby(const float* x, float* y, size_t n, float a, float b, void* stream) {
-  B200IQ_CHECK_ARG(x && y && n > 0, "axpby: bad args");
-  axpby_kernel<<<grid_for(n, 256), 256, 0, ST>>>(x, y, n, a, b);
+extern "C" int b200iq_axpby(const float* x, const float* y, float* out, size_t n, float a, float b, void* stream) {
+  B200IQ_CHECK_ARG(x && y && out && n > 0, "axpby: bad args");
+  axpby_kernel<<<grid_for(n, 256), 256, 0, ST>>>(x, y, out, n, a, b);
   return launch_status("axpby");
 }

@@ -1,0 +1,404 @@
+"""`IQ` — drop-in for the reference's models/iq.py:22 `IQ` module (transformer / BLT-VQG variant).
+
+Same constructor, attribute surface and return values as the reference:
+  IQ(latent_transformer, vocab, args, num_att_layers=2)                      models/iq.py:25
+  forward(images, answers, response, target) -> (output, z_logit, kld, (img, recon))   :82-114
+  switch_GVT_train_mode(bool)                                                :51-54
+  decode_greedy(images, answers, max_decode_length=50)                       :117-152   (see decode.py)
+plus the fused entry the reference cannot offer:
+  forward_losses(images, answers, response, target, kliter) -> loss-term vector; runs forward, the fused
+  vocab-projection + cross-entropy (no (B,T,V) logits in HBM) and the complete hand-written backward,
+  leaving gradients in the flat gradient arena.
+All arithmetic runs in libb200iq.so (sm_100a); torch is used for memory, streams and autograd glue only.
+`images` may be pre-pooled trunk features (B, FEAT) (trunk-cut mode) or raw images (B,3,224,224), in which
+case the frozen torchvision trunk of models/encoder_cnn.py:17-19 runs under no_grad first.
+"""
+import math
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+from . import _lib, ops
+from . import transformer as tf
+from .params import Arena, TRANSFORMER_ALIASES, export_state_dict, import_state_dict, transformer_iq_specs
+
+PAD = 0
+TERMS = ("rec", "img", "kld", "aux", "count", "gnorm_sq", "unused0", "unused1")
+
+
+def gen_timing_signal(length, channels, min_timescale=1.0, max_timescale=1.0e4):
+    """models/transformer_layers.py:542-558: [sin | cos] halves, float64 math then cast."""
+    position = np.arange(length)
+    num_timescales = channels // 2
+    inc = math.log(float(max_timescale) / float(min_timescale)) / (float(num_timescales) - 1)
+    inv = min_timescale * np.exp(np.arange(num_timescales).astype(np.float64) * -inc)
+    scaled = position[:, None] * inv[None, :]
+    signal = np.concatenate([np.sin(scaled), np.cos(scaled)], axis=1)
+    signal = np.pad(signal, [[0, 0], [0, channels % 2]], "constant")
+    return torch.from_numpy(signal).float()
+
+
+def _ids(t, device):
+    return t.to(device=device, dtype=torch.int32).contiguous()
+
+
+class _IQFunction(torch.autograd.Function):
+    """autograd glue for the API-exact forward(): one node whose backward is our hand-written schedule"""
+
+    @staticmethod
+    def forward(ctx, flat, model, feats, cids, rids, tids, eps):
+        outs = model._forward_api(feats, cids, rids, tids, eps)
+        ctx.model = model
+        ctx.latent = model.latent_transformer
+        return outs
+
+    @staticmethod
+    def backward(ctx, d_output, d_z_logit, d_kld, d_img, d_recon):
+        g = ctx.model._backward_api(d_output, d_z_logit, d_kld, d_img, d_recon)
+        return g, None, None, None, None, None, None
+
+
+class IQ(nn.Module):
+    def __init__(self, latent_transformer, vocab, args, num_att_layers=2):
+        super().__init__()
+        assert num_att_layers == 2, "image_reconstructor is the 2-layer MLP of models/iq.py:46-48"
+        self.vocab = vocab
+        self.vocab_size = len(vocab.word2idx)
+        self.latent_transformer = latent_transformer
+        self.args = args
+        self.V, self.E, self.H = self.vocab_size, args.emb_dim, args.hidden_dim
+        self.L, self.F, self.NL, self.nh = args.latent_dim, args.pwffn_dim, args.num_layers, args.num_heads
+        self.FEAT = getattr(args, "feat_dim", 512)  # resnet18 fc.in_features (encoder_cnn.py:20)
+        self.sos_id = vocab.word2idx[vocab.SYM_SOQ]
+        assert vocab.word2idx[vocab.SYM_PAD] == PAD
+        assert self.H % self.nh == 0 and self.H % 4 == 0 and self.E % 4 == 0 and self.V % 4 == 0 and self.L % 2 == 0, \
+            "tcgen05/TMA path needs 16-byte aligned rows (H, E, V multiples of 4)"
+        self.attn_dropout, self.relu_dropout = 0.1, 0.1  # transformer_layers.py:96-97,163-164 defaults (N4)
+        self.arena = Arena()
+        transformer_iq_specs(self.arena, self.V, self.E, self.H, self.L, self.F, self.NL, self.FEAT)
+        self.flat = nn.Parameter(self.arena.finalize())
+        self.arena.bind(self.flat.data)
+        self.register_buffer("bn_running_mean", torch.zeros(self.H), persistent=False)
+        self.register_buffer("bn_running_var", torch.ones(self.H), persistent=False)
+        self.register_buffer("bn_num_batches_tracked", torch.zeros((), dtype=torch.long), persistent=False)
+        self.register_buffer("timing_enc", gen_timing_signal(1000, self.H), persistent=False)  # :96,118
+        self.register_buffer("timing_dec", gen_timing_signal(200, self.H), persistent=False)   # :163,184
+        self.trunk = None  # set by attach_trunk(); reference: torchvision resnet18 (encoder_cnn.py:17)
+        self.seed = 1234
+        self.step_idx = 0
+        self._ws = {}
+        self._gflat = None
+        self._terms = None
+        self._ctx = None
+
+    # ------------------------------------------------------------------ module plumbing
+    def _apply(self, fn, *a, **k):
+        super()._apply(fn, *a, **k)
+        self.arena.bind(self.flat.data)
+        self._ws, self._gflat, self._terms = {}, None, None
+        return self
+
+    def _buffers_map(self):
+        return {"encoder_cnn.bn.running_mean": self.bn_running_mean, "encoder_cnn.bn.running_var": self.bn_running_var,
+                "encoder_cnn.bn.num_batches_tracked": self.bn_num_batches_tracked}
+
+    def state_dict(self, *args, destination=None, prefix="", keep_vars=False):
+        """reference key names (models/iq.py attribute tree), duplicates for shared sub-modules included"""
+        sd = export_state_dict(self.arena, self._buffers_map(), TRANSFORMER_ALIASES, prefix)
+        out = destination if destination is not None else type(sd)()
+        for k, v in sd.items():
+            out[k] = v if keep_vars else v.detach()
+        return out
+
+    def load_state_dict(self, state_dict, strict=True):
+        sd = {k: v for k, v in state_dict.items() if not k.startswith("encoder_cnn.cnn.") or k.startswith("encoder_cnn.cnn.fc.")}
+        missing, unexpected = import_state_dict(self.arena, self._buffers_map(), TRANSFORMER_ALIASES, sd, strict)
+        return missing, unexpected
+
+    def switch_GVT_train_mode(self, new_mode):
+        """models/iq.py:51-54"""
+        self.latent_transformer = new_mode
+
+    def attach_trunk(self, trunk):
+        """frozen CNN trunk mapping images -> pooled (B, FEAT) features (reference: resnet18 minus fc)"""
+        self.trunk = trunk
+        for p in trunk.parameters():
+            p.requires_grad = False
+
+    # ------------------------------------------------------------------ internals
+    @property
+    def grad_arena(self):
+        if self._gflat is None:
+            self._gflat = torch.zeros_like(self.flat.data)
+        return self._gflat
+
+    @property
+    def terms(self):
+        if self._terms is None:
+            self._terms = torch.zeros(len(TERMS), device=self.flat.device)
+        return self._terms
+
+    def _workspace(self, key):
+        ws = self._ws.get(key)
+        if ws is None:
+            ws = tf.Workspace(self.flat.device)
+            self._ws[key] = ws
+        return ws
+
+    def _features(self, images):
+        if images.dim() == 2:
+            return images.to(self.flat.device, torch.float32).contiguous()
+        if self.trunk is None:
+            raise _lib.B200iqError("raw images given but no trunk attached (call attach_trunk, or pass pooled features)")
+        with torch.no_grad():
+            return self.trunk(images.to(self.flat.device)).flatten(1).float().contiguous()
+
+    def _make_ctx(self, B, S, R, T, training):
+        _lib.require_device()
+        key = (B, S, R, T, bool(self.latent_transformer), bool(training))
+        ws = self._workspace(key)
+        c = tf.Ctx(self.arena, self.grad_arena, ws, self.H, self.nh, self.F, self.E, self.attn_dropout,
+                   self.relu_dropout, training, self.seed + self.step_idx)
+        return c
+
+    def _run_forward(self, c, feats, cids, rids, tids, eps):
+        """models/iq.py:101-112 down to the decoder's final LayerNorm; everything stays in the workspace"""
+        ws, P, H, L = c.ws, c.P, self.H, self.L
+        B, S, T = feats.shape[0], cids.shape[1], tids.shape[1]
+        latent = self.latent_transformer
+        m = ws.meta
+        # image head: fc + BatchNorm1d (encoder_cnn.py:33-34)
+        img_pre = ws.buf("img_pre", B, H)
+        ops.gemm(feats, P["encoder_cnn.cnn.fc.weight"], img_pre, bias=P["encoder_cnn.cnn.fc.bias"])
+        img = ws.buf("img", B, H)
+        ops.bn_fwd(img_pre, P["encoder_cnn.bn.weight"], P["encoder_cnn.bn.bias"], img, ws.buf("bn.mean", H),
+                   ws.buf("bn.rstd", H), self.bn_running_mean, self.bn_running_var, c.training)
+        # context encoder (encoder_transformer.py:27-32)
+        x = tf.embed_fwd(c, "enc.emb", cids, B, S, self.timing_enc)
+        enc_out = tf.encoder_fwd(c, "enc", "answer_encoder.encoder.", x, cids, B, S, self.NL)
+        ops.add_timing(enc_out, None, img, None, B, S, H)  # enc_out[:,0] += image_features
+        z = None
+        if latent:
+            R = rids.shape[1]
+            xr = tf.embed_fwd(c, "renc.emb", rids, B, R, self.timing_enc)
+            r_out = tf.encoder_fwd(c, "renc", "answer_encoder.r_encoder.", xr, rids, B, R, self.NL)
+            cat = ws.buf("lat.cat", B, 2 * H)  # cat(x_p, x), transformer_layers.py:52
+            ops.tok0_gather(r_out, cat[:, :H], B, R, H)
+            ops.tok0_gather(enc_out, cat[:, H:], B, S, H)
+            pp, pq = "latent_layer.mean_logvar_prior.", "latent_layer.mean_logvar_posterior."
+            p1 = tf.linear_fwd(c, "lat.p1", pp + "0", cat[:, H:], relu=True)
+            p2 = tf.linear_fwd(c, "lat.p2", pp + "3", p1, relu=True)
+            prior = tf.linear_fwd(c, "lat.prior", pp + "6", p2)
+            q1 = tf.linear_fwd(c, "lat.q1", pq + "0", cat, relu=True)
+            q2 = tf.linear_fwd(c, "lat.q2", pq + "3", q1, relu=True)
+            post = tf.linear_fwd(c, "lat.post", pq + "6", q2)
+            e = ws.buf("lat.eps", B, L)
+            if eps is not None:
+                e.copy_(eps)
+            else:
+                ops.randn_(e, c.seed, 7 << 40)
+            zl = ws.buf("lat.z", B, L)
+            ops.latent_fwd(prior, post, e, zl, self.terms[2:3])
+            z = tf.linear_fwd(c, "z", "latent_projection", zl)
+            zimg = ops.axpby(z, img, ws.buf("zimg", B, H))
+            m["z_logit"] = tf.linear_fwd(c, "z_logit", "decoder.z_classifier", zimg)
+        # decoder (decoder_transformer.py:22-38)
+        shifted = ws.buf("dec.ids", B, T, dtype=torch.int32)
+        shifted[:, 0] = self.sos_id
+        shifted[:, 1:] = tids[:, :-1]
+        xd = tf.embed_fwd(c, "dec.emb", shifted, B, T, self.timing_dec, add0=img, add1=z)
+        dec_out = tf.decoder_fwd(c, "dec", "decoder.decoder.", xd, shifted, enc_out, cids, B, T, S, self.NL)
+        # image reconstruction (iq.py:109-112)
+        rin = ws.buf("rin", B, H)
+        ops.tok0_gather(enc_out, rin, B, S, H)
+        if latent:
+            ops.axpby(rin, z, rin)
+        rh = tf.linear_fwd(c, "rec.h", "image_reconstructor.layers.fc0", rin, relu=True)
+        recon = tf.linear_fwd(c, "rec.out", "image_reconstructor.layers.fc1", rh)
+        m.update(img=img, img_pre=img_pre, enc_out=enc_out, z=z, dec_out=dec_out, shifted=shifted, rin=rin, rh=rh,
+                 recon=recon, feats=feats, cids=cids, rids=rids, tids=tids)
+        return dec_out
+
+    def _backward_tail(self, c, d_dec, d_img, d_z, d_recon, kld_coef):
+        """everything below the loss seeds: recon MLP, decoder, latent, both encoders, embedder, image head.
+        d_img / d_z are accumulators already holding the seeds from the losses / z_classifier."""
+        ws, P, G, H, L = c.ws, c.P, c.G, self.H, self.L
+        m = ws.meta
+        latent = self.latent_transformer
+        B, S, T = m["feats"].shape[0], m["cids"].shape[1], m["tids"].shape[1]
+        d_rh = tf.linear_bwd(c, "d_rh", "image_reconstructor.layers.fc1", d_recon, m["rh"], relu_mask=m["rh"])
+        d_rin = tf.linear_bwd(c, "d_rin", "image_reconstructor.layers.fc0", d_rh, m["rin"])
+        if latent:
+            ops.axpby(d_z, d_rin, d_z)
+        d_enc_out = ws.buf("d_enc_out", B * S, H)
+        dxd = tf.decoder_bwd(c, "dec", "decoder.decoder.", d_dec, m["shifted"], m["enc_out"], d_enc_out, m["cids"],
+                             B, T, S, self.NL)
+        ops.tok0_gather(dxd, d_img, B, T, H, accumulate=True)
+        if latent:
+            ops.tok0_gather(dxd, d_z, B, T, H, accumulate=True)
+        tf.embed_bwd(c, "dec.emb", m["shifted"], dxd)
+        ops.tok0_scatter_add(d_rin, d_enc_out, B, S, H)
+        if latent:
+            R = m["rids"].shape[1]
+            pp, pq = "latent_layer.mean_logvar_prior.", "latent_layer.mean_logvar_posterior."
+            d_zl = tf.linear_bwd(c, "d_zl", "latent_projection", d_z, ws["lat.z"])
+            dprior, dpost = ws.buf("d_prior", B, 2 * L), ws.buf("d_post", B, 2 * L)
+            ops.latent_bwd(ws["lat.prior"], ws["lat.post"], ws["lat.eps"], d_zl, kld_coef, dprior, dpost)
+            cat = ws["lat.cat"]
+            d_cat = ws.buf("d_cat", B, 2 * H)
+            d_q2 = tf.linear_bwd(c, "d_q2", pq + "6", dpost, ws["lat.q2"], relu_mask=ws["lat.q2"])
+            d_q1 = tf.linear_bwd(c, "d_q1", pq + "3", d_q2, ws["lat.q1"], relu_mask=ws["lat.q1"])
+            tf.linear_bwd(c, None, pq + "0", d_q1, cat, dx=d_cat)
+            d_p2 = tf.linear_bwd(c, "d_p2", pp + "6", dprior, ws["lat.p2"], relu_mask=ws["lat.p2"])
+            d_p1 = tf.linear_bwd(c, "d_p1", pp + "3", d_p2, ws["lat.p1"], relu_mask=ws["lat.p1"])
+            tf.linear_bwd(c, None, pp + "0", d_p1, cat[:, H:], dx=d_cat[:, H:], accumulate_dx=True)
+            ops.tok0_scatter_add(d_cat[:, H:], d_enc_out, B, S, H)
+            d_r_out = ws.buf("d_r_out", B * R, H)
+            d_r_out.zero_()
+            ops.tok0_scatter_add(d_cat[:, :H], d_r_out, B, R, H)
+            dr_in = tf.encoder_bwd(c, "renc", "answer_encoder.r_encoder.", d_r_out, m["rids"], B, R, self.NL)
+            tf.embed_bwd(c, "renc.emb", m["rids"], dr_in)
+        ops.tok0_gather(d_enc_out, d_img, B, S, H, accumulate=True)  # enc_out[:,0] = LN(..)[:,0] + image_features
+        de_in = tf.encoder_bwd(c, "enc", "answer_encoder.encoder.", d_enc_out, m["cids"], B, S, self.NL)
+        tf.embed_bwd(c, "enc.emb", m["cids"], de_in)
+        d_img_pre = ws.buf("d_img_pre", B, H)
+        ops.bn_bwd(d_img, m["img_pre"], P["encoder_cnn.bn.weight"], ws["bn.mean"], ws["bn.rstd"], d_img_pre,
+                   G["encoder_cnn.bn.weight"], G["encoder_cnn.bn.bias"])
+        tf.grad_w(c, d_img_pre, m["feats"], G["encoder_cnn.cnn.fc.weight"], G["encoder_cnn.cnn.fc.bias"])
+
+    # ------------------------------------------------------------------ fused training path
+    def loss_coefs(self, kliter=0):
+        """train_iq.py:88-101 weights: (rec, img, kld, aux)"""
+        a = self.args
+        if not self.latent_transformer:
+            return 1.0, a.image_recon_lambda, 0.0, 0.0
+        kl_w = min(math.tanh(6 * kliter / a.full_kl_step - 3) + 1, 1)
+        return 1.0, a.image_recon_lambda, a.kl_ceiling * kl_w, a.aux_ceiling
+
+    def _ce_chunk_rows(self, M):
+        rows = (48 << 20) // (4 * self.V)  # keep a logits chunk (fp32) around 48 MB: L2-resident on B200 (126 MB L2)
+        rows = max(128, rows // 128 * 128)
+        return min(M, rows)
+
+    def forward_losses(self, images, answers, response, target, kliter=0, eps=None, backward=True):
+        """Forward + losses (train_iq.py:81-103) + full backward, logits never materialised.
+        Returns the device tensor of loss terms (rec, img, kld, aux, count, ...); gradients are ACCUMULATED into
+        `self.grad_arena`.  total = rec + c_img*img + c_kld*kld + c_aux*aux (see loss_coefs / total_loss)."""
+        dev = self.flat.device
+        feats = self._features(images)
+        cids, tids = _ids(answers, dev), _ids(target, dev)
+        rids = _ids(response, dev) if self.latent_transformer else None
+        B, S, T = feats.shape[0], cids.shape[1], tids.shape[1]
+        R = rids.shape[1] if rids is not None else 0
+        c = self._make_ctx(B, S, R, T, self.training)
+        self._ctx = c
+        ws, P, G, H, V = c.ws, c.P, c.G, self.H, self.V
+        terms = self.terms
+        terms.zero_()
+        dec_out = self._run_forward(c, feats, cids, rids, tids, eps)
+        m = ws.meta
+        c_rec, c_img, c_kld, c_aux = self.loss_coefs(kliter)
+        M = B * T
+        count = terms[4:5]
+        ops.count_nonpad(tids, PAD, count)
+        tflat = tids.view(-1)
+        d_dec = ws.buf("d_dec_out", M, H)
+        chunk = self._ce_chunk_rows(M)
+        logits = ws.buf("logits_chunk", chunk, V)
+        wout, bout = P["decoder.output.weight"], P["decoder.output.bias"]
+        for r0 in range(0, M, chunk):
+            rows = min(chunk, M - r0)
+            lg, xs = logits[:rows], dec_out[r0:r0 + rows]
+            ops.gemm(xs, wout, lg, bias=bout)                      # decoder_transformer.py:40
+            ops.ce_rows(lg, tflat[r0:r0 + rows], PAD, count, c_rec, terms[0:1], write_grad=backward)
+            if backward:
+                ops.gemm(lg, wout, d_dec[r0:r0 + rows], b_t=True)
+                tf.grad_w(c, lg, xs, G["decoder.output.weight"], G["decoder.output.bias"])
+        d_img = ws.buf("d_img", B, H)
+        d_z = None
+        if self.latent_transformer:
+            dzl = ws.buf("d_z_logit", B, V)
+            ops.ce_aux(m["z_logit"], dzl, tids, PAD, count, c_aux, terms[3:4])
+            if backward:
+                d_z = tf.linear_bwd(c, "d_zimg", "decoder.z_classifier", dzl, ws["zimg"])
+                ops.axpby(d_z, d_z, d_img, 1.0, 0.0)
+        elif backward:
+            d_img.zero_()
+        d_recon = ws.buf("d_recon", B, H)
+        ops.mse(m["img"], m["recon"], c_img, terms[1:2], d_img if backward else None, d_recon if backward else None)
+        if backward:
+            self._backward_tail(c, d_dec, d_img, d_z, d_recon, c_kld)
+        return terms
+
+    def total_loss(self, terms, kliter=0):
+        c_rec, c_img, c_kld, c_aux = self.loss_coefs(kliter)
+        return c_rec * terms[0] + c_img * terms[1] + c_kld * terms[2] + c_aux * terms[3]
+
+    # ------------------------------------------------------------------ API-exact path (materialises logits)
+    def forward(self, images, answers, response, target, eps=None):
+        """models/iq.py:82-114. Returns (output (B,T,V), z_logit (B,V)|None, kld|None, (image_features, recon))."""
+        dev = self.flat.device
+        feats = self._features(images)
+        cids, tids = _ids(answers, dev), _ids(target, dev)
+        rids = _ids(response, dev) if self.latent_transformer else None
+        if torch.is_grad_enabled() and self.flat.requires_grad:
+            output, z_logit, kld, img, recon = _IQFunction.apply(self.flat, self, feats, cids, rids, tids, eps)
+        else:
+            output, z_logit, kld, img, recon = self._forward_api(feats, cids, rids, tids, eps)
+        if not self.latent_transformer:
+            z_logit, kld = None, None
+        return output, z_logit, kld, (img, recon)
+
+    def _forward_api(self, feats, cids, rids, tids, eps):
+        B, S, T = feats.shape[0], cids.shape[1], tids.shape[1]
+        R = rids.shape[1] if rids is not None else 0
+        c = self._make_ctx(B, S, R, T, self.training)
+        self._ctx = c
+        self.terms.zero_()
+        dec_out = self._run_forward(c, feats, cids, rids, tids, eps)
+        m = c.ws.meta
+        output = torch.empty(B * T, self.V, device=feats.device)
+        ops.gemm(dec_out, c.P["decoder.output.weight"], output, bias=c.P["decoder.output.bias"])
+        if self.latent_transformer:
+            z_logit, kld = m["z_logit"].clone(), self.terms[2].clone()
+        else:
+            z_logit, kld = torch.zeros(1, device=feats.device), torch.zeros((), device=feats.device)
+        return output.view(B, T, self.V), z_logit, kld, m["img"].clone(), m["recon"].clone()
+
+    def _backward_api(self, d_output, d_z_logit, d_kld, d_img_in, d_recon_in):
+        c = self._ctx
+        ws, m, H = c.ws, c.ws.meta, self.H
+        B, T = m["tids"].shape
+        g = torch.zeros_like(self.flat.data)
+        c.gflat = g
+        c.G = {n: self.arena.view_of(g, n) for n in self.arena.names()}
+        d_dec = ws.buf("d_dec_out", B * T, H)
+        if d_output is not None:
+            dout = d_output.reshape(B * T, self.V).contiguous()
+            ops.gemm(dout, c.P["decoder.output.weight"], d_dec, b_t=True)
+            tf.grad_w(c, dout, m["dec_out"], c.G["decoder.output.weight"], c.G["decoder.output.bias"])
+        else:
+            d_dec.zero_()
+        d_img = ws.buf("d_img", B, H)
+        if d_img_in is not None:
+            d_img.copy_(d_img_in)
+        else:
+            d_img.zero_()
+        d_z = None
+        if self.latent_transformer:
+            d_z = ws.buf("d_zimg", B, H)
+            if d_z_logit is not None:
+                tf.linear_bwd(c, "d_zimg", "decoder.z_classifier", d_z_logit.contiguous(), ws["zimg"], dx=d_z)
+                ops.axpby(d_img, d_z, d_img)
+            else:
+                d_z.zero_()
+        d_recon = ws.buf("d_recon", B, H)
+        if d_recon_in is not None:
+            d_recon.copy_(d_recon_in)
+        else:
+            d_recon.zero_()
+        kld_coef = float(d_kld) if (d_kld is not None and self.latent_transformer) else 0.0
+        self._backward_tail(c, d_dec, d_img, d_z, d_recon, kld_coef)
+        c.gflat, c.G = self.grad_arena, None
+        return g

@@ -62,3 +62,156 @@ def gemm(a, b, out=None, *, a_t=False, b_t=False, bias=None, residual=None, relu
                      flags, split_k, float(alpha))
     L.check(L.lib().b200iq_gemm(C.byref(p), L.stream_ptr()), "b200iq_gemm")
     return out
+
+
+# ------------------------------------------------------------------ helpers
+def _p(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+
+
+def _f(x):
+    return C.c_float(float(x))
+
+
+def _call(name, *args):
+    L.check(getattr(L.lib(), name)(*args, L.stream_ptr()), name)
+
+
+class AttnParams(C.Structure):
+    _fields_ = [
+        ("q", C.c_void_p), ("k", C.c_void_p), ("v", C.c_void_p), ("out", C.c_void_p),
+        ("ldq", C.c_int), ("ldk", C.c_int), ("ldv", C.c_int), ("ldo", C.c_int),
+        ("key_ids", C.c_void_p), ("pad_id", C.c_int), ("causal", C.c_int),
+        ("B", C.c_int), ("num_heads", C.c_int), ("nq", C.c_int), ("nk", C.c_int), ("head_dim", C.c_int),
+        ("scale", C.c_float), ("drop_p", C.c_float), ("seed", C.c_uint64), ("offset", C.c_uint64),
+    ]
+
+
+# ------------------------------------------------------------------ row / elementwise
+def embed_gather(ids, table, out):
+    _call("b200iq_embed_gather", _p(ids), _p(table), _p(out), ids.numel(), table.shape[1], table.shape[0])
+    return out
+
+
+def embed_scatter_add(ids, dout, dtable, pad_id):
+    _call("b200iq_embed_scatter_add", _p(ids), _p(dout), _p(dtable), ids.numel(), dtable.shape[1], dtable.shape[0], int(pad_id))
+
+
+def add_timing(x, timing, add0, add1, B, n, H):
+    _call("b200iq_add_timing", _p(x), _p(timing), _p(add0), _p(add1), B, n, H)
+
+
+def tok0_gather(src, dst, B, n, H, accumulate=False):
+    """dst[b, :H] (+)= src[b*n, :H]; dst may be a column slice of a wider [B, ld] buffer"""
+    _call("b200iq_tok0_gather", _p(src), _p(dst), B, n, H, dst.stride(0), int(accumulate))
+
+
+def tok0_scatter_add(src, dst, B, n, H):
+    """dst[b*n, :H] += src[b, :H]"""
+    _call("b200iq_tok0_scatter_add", _p(src), _p(dst), B, n, H, src.stride(0))
+
+
+def layernorm_fwd(x, g, b, y, mean, rstd, eps=1e-5):
+    M, H = x.shape
+    _call("b200iq_layernorm_fwd", _p(x), _p(g), _p(b), _p(y), _p(mean), _p(rstd), M, H, _f(eps))
+    return y
+
+
+def layernorm_bwd(dy, x, g, mean, rstd, dx, dg, db, accumulate_dx):
+    M, H = x.shape
+    _call("b200iq_layernorm_bwd", _p(dy), _p(x), _p(g), _p(mean), _p(rstd), _p(dx), _p(dg), _p(db), M, H, int(accumulate_dx))
+
+
+def colsum_add(x, out):
+    M, N = x.shape
+    _call("b200iq_colsum_add", _p(x), _p(out), M, N, x.stride(0))
+
+
+def relu_bwd_colsum(dy, y, dpre, dbias):
+    M, N = y.shape
+    _call("b200iq_relu_bwd_colsum", _p(dy), _p(y), _p(dpre), _p(dbias), M, N)
+
+
+def dropout_(x, p, seed, offset):
+    if p > 0:
+        _call("b200iq_dropout", _p(x), C.c_size_t(x.numel()), _f(p), C.c_uint64(seed), C.c_uint64(offset))
+
+
+def randn_(out, seed, offset=0):
+    _call("b200iq_randn", _p(out), C.c_size_t(out.numel()), C.c_uint64(seed), C.c_uint64(offset))
+    return out
+
+
+def axpby(x, y, out, a=1.0, b=1.0):
+    """out = a*x + b*y"""
+    _call("b200iq_axpby", _p(x), _p(y), _p(out), C.c_size_t(x.numel()), _f(a), _f(b))
+    return out
+
+
+# ------------------------------------------------------------------ attention
+def _attn_params(q, k, v, out, key_ids, pad_id, causal, B, nh, nq, nk, d, drop_p, seed, offset):
+    return AttnParams(q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr() if out is not None else 0,
+                      q.stride(0), k.stride(0), v.stride(0), out.stride(0) if out is not None else 0,
+                      key_ids.data_ptr() if key_ids is not None else 0, pad_id, int(causal),
+                      B, nh, nq, nk, d, d ** -0.5, drop_p, seed, offset)
+
+
+def attention_fwd(q, k, v, out, key_ids, pad_id, causal, B, nh, nq, nk, d, drop_p=0.0, seed=0, offset=0):
+    p = _attn_params(q, k, v, out, key_ids, pad_id, causal, B, nh, nq, nk, d, drop_p, seed, offset)
+    _call("b200iq_attention_fwd", C.byref(p))
+    return out
+
+
+def attention_bwd(q, k, v, dout, dq, dk, dv, key_ids, pad_id, causal, B, nh, nq, nk, d, drop_p=0.0, seed=0, offset=0):
+    p = _attn_params(q, k, v, None, key_ids, pad_id, causal, B, nh, nq, nk, d, drop_p, seed, offset)
+    p.ldo = dout.stride(0)
+    _call("b200iq_attention_bwd", C.byref(p), _p(dout), _p(dq), _p(dk), _p(dv), dq.stride(0), dk.stride(0), dv.stride(0))
+
+
+# ------------------------------------------------------------------ losses / heads / optimizer
+def count_nonpad(targets, pad_id, count):
+    _call("b200iq_count_nonpad", _p(targets), targets.numel(), int(pad_id), _p(count))
+
+
+def ce_rows(logits, targets, pad_id, count, coef, loss_sum, write_grad=True):
+    rows, V = logits.shape
+    _call("b200iq_ce_rows", _p(logits), logits.stride(0), _p(targets), rows, V, int(pad_id), _p(count), _f(coef), _p(loss_sum), int(write_grad))
+
+
+def ce_aux(z_logit, dz_logit, targets, pad_id, count, coef, loss_sum):
+    B, V = z_logit.shape
+    _call("b200iq_ce_aux", _p(z_logit), _p(dz_logit), _p(targets), B, targets.numel() // B, V, int(pad_id), _p(count), _f(coef), _p(loss_sum))
+
+
+def latent_fwd(prior, post, eps, z, kld_sum):
+    B, L = eps.shape
+    _call("b200iq_latent_fwd", _p(prior), _p(post), _p(eps), _p(z), _p(kld_sum), B, L)
+
+
+def latent_bwd(prior, post, eps, dz, kld_coef, dprior, dpost):
+    B, L = eps.shape
+    _call("b200iq_latent_bwd", _p(prior), _p(post), _p(eps), _p(dz), _f(kld_coef), _p(dprior), _p(dpost), B, L)
+
+
+def bn_fwd(x, g, b, y, save_mean, save_rstd, run_mean, run_var, training, eps=1e-5, momentum=0.01):
+    B, H = x.shape
+    _call("b200iq_bn_fwd", _p(x), _p(g), _p(b), _p(y), _p(save_mean), _p(save_rstd), _p(run_mean), _p(run_var), B, H,
+          _f(eps), _f(momentum), int(training))
+
+
+def bn_bwd(dy, x, g, save_mean, save_rstd, dx, dg, db):
+    B, H = x.shape
+    _call("b200iq_bn_bwd", _p(dy), _p(x), _p(g), _p(save_mean), _p(save_rstd), _p(dx), _p(dg), _p(db), B, H)
+
+
+def mse(a, b, coef, loss_sum, da, db, accumulate_db=False):
+    _call("b200iq_mse", _p(a), _p(b), C.c_size_t(a.numel()), _f(coef), _p(loss_sum), _p(da), _p(db), int(accumulate_db))
+
+
+def grad_sumsq(grad, out):
+    _call("b200iq_grad_sumsq", _p(grad), C.c_size_t(grad.numel()), _p(out))
+
+
+def adam_step(param, grad, m, v, hyper, normsq, beta1=0.9, beta2=0.999, eps=1e-8, max_norm=5.0, zero_grad=True):
+    _call("b200iq_adam_step", _p(param), _p(grad), _p(m), _p(v), C.c_size_t(param.numel()), _p(hyper), _p(normsq),
+          _f(beta1), _f(beta2), _f(eps), _f(max_norm), int(zero_grad))

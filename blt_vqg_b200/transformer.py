@@ -1,0 +1,297 @@
+"""Host-side forward / hand-written backward schedules of the transformer blocks.
+
+Mirrors models/transformer_layers.py (Encoder :138-152, EncoderLayer :260-282, Decoder :205-221,
+DecoderLayer :326-364, MultiHeadAttention :486-532, PositionwiseFeedForward :400-408) as explicit
+kernel launch sequences over pre-allocated workspace buffers; there is no autograd underneath.
+Every function only enqueues kernels on the current stream (CUDA-graph capturable).
+"""
+import torch
+
+from . import ops
+
+PAD = 0
+
+
+class Workspace:
+    """name -> persistent device buffer (stable addresses, so a captured CUDA graph can be replayed)"""
+
+    def __init__(self, device):
+        self.device = device
+        self.bufs = {}
+        self.meta = {}
+
+    def buf(self, name, *shape, dtype=torch.float32):
+        t = self.bufs.get(name)
+        if t is None or tuple(t.shape) != tuple(shape) or t.dtype != dtype:
+            t = torch.empty(shape, device=self.device, dtype=dtype)
+            self.bufs[name] = t
+        return t
+
+    def __getitem__(self, name):
+        return self.bufs[name]
+
+    def nbytes(self):
+        return sum(t.numel() * t.element_size() for t in self.bufs.values())
+
+
+class Ctx:
+    """everything a block schedule needs: parameter / gradient views, workspace, sizes, dropout keys"""
+
+    def __init__(self, arena, gflat, ws, H, nh, F, E, attn_drop, relu_drop, training, seed):
+        self.arena, self.ws = arena, ws
+        self.P = arena.views
+        self.gflat = gflat
+        self.G = {n: arena.view_of(gflat, n) for n in arena.names()} if gflat is not None else None
+        self.H, self.nh, self.F, self.E, self.d = H, nh, F, E, H // nh
+        self.attn_drop = attn_drop if training else 0.0
+        self.relu_drop = relu_drop if training else 0.0
+        self.training = training
+        self.seed = seed
+        self.site = 0
+        self.sm = 148
+
+    def pspan(self, first, last, cols):
+        o0, o1 = self.arena.span(first, last)
+        return self.arena.flat.detach()[o0:o1].view(-1, cols)
+
+    def gspan(self, first, last, cols):
+        o0, o1 = self.arena.span(first, last)
+        return self.gflat[o0:o1].view(-1, cols)
+
+    def key(self, tag):
+        """(seed, offset) of a dropout site; remembered under `tag` so the backward re-creates the mask"""
+        k = self.ws.meta.get(("key", tag))
+        if k is None or k[0] != self.seed:
+            self.site += 1
+            k = (self.seed, self.site << 40)
+            self.ws.meta[("key", tag)] = k
+        return k
+
+    def split_k(self, n_out, k_in, m_red):
+        tiles = ((n_out + 127) // 128) * ((k_in + 127) // 128)
+        s = max(1, (2 * self.sm) // tiles)
+        return max(1, min(s, (m_red + 127) // 128))
+
+
+def grad_w(c, dy, x, gw, gb=None):
+    """dW[N,K] += dy[M,N]^T @ x[M,K];  db[N] += colsum(dy)"""
+    M = dy.shape[0]
+    ops.gemm(dy, x, gw, a_t=True, b_t=True, accumulate=True, split_k=c.split_k(gw.shape[0], gw.shape[1], M))
+    if gb is not None:
+        ops.colsum_add(dy, gb)
+
+
+def ln_fwd(c, tag, pfx, x):
+    M, H = x.shape
+    y = c.ws.buf(tag + ".y", M, H)
+    mean, rstd = c.ws.buf(tag + ".mean", M), c.ws.buf(tag + ".rstd", M)
+    ops.layernorm_fwd(x, c.P[pfx + ".weight"], c.P[pfx + ".bias"], y, mean, rstd)
+    return y
+
+
+def ln_bwd(c, tag, pfx, dy, x, dx, accumulate):
+    ops.layernorm_bwd(dy, x, c.P[pfx + ".weight"], c.ws[tag + ".mean"], c.ws[tag + ".rstd"], dx,
+                      c.G[pfx + ".weight"], c.G[pfx + ".bias"], accumulate)
+
+
+# ------------------------------------------------------------------ embedder (models/iq.py:57-79)
+def embed_fwd(c, tag, ids, B, n, timing, add0=None, add1=None):
+    M = B * n
+    e = c.ws.buf(tag + ".e", M, c.E)
+    ops.embed_gather(ids, c.P["embedding.0.weight"], e)
+    x = c.ws.buf(tag + ".x0", M, c.H)
+    ops.gemm(e, c.P["embedding.1.weight"], x, bias=c.P["embedding.1.bias"])
+    ops.add_timing(x, timing, add0, add1, B, n, c.H)
+    return x
+
+
+def embed_bwd(c, tag, ids, dx):
+    e = c.ws[tag + ".e"]
+    grad_w(c, dx, e, c.G["embedding.1.weight"], c.G["embedding.1.bias"])
+    de = c.ws.buf("tmp.de.%d" % dx.shape[0], dx.shape[0], c.E)
+    ops.gemm(dx, c.P["embedding.1.weight"], de, b_t=True)
+    ops.embed_scatter_add(ids, de, c.G["embedding.0.weight"], PAD)
+
+
+# ------------------------------------------------------------------ attention blocks
+def self_attn_fwd(c, tag, pfx, xn, x_res, ids, B, n, causal):
+    M, H = xn.shape
+    wqkv = c.pspan(pfx + "query_linear.weight", pfx + "value_linear.weight", H)
+    qkv = c.ws.buf(tag + ".qkv", M, 3 * H)
+    ops.gemm(xn, wqkv, qkv)
+    ctx = c.ws.buf(tag + ".ctx", M, H)
+    seed, off = c.key(tag + ".adrop")
+    ops.attention_fwd(qkv[:, :H], qkv[:, H:2 * H], qkv[:, 2 * H:], ctx, ids, PAD, causal, B, c.nh, n, n, c.d,
+                      c.attn_drop, seed, off)
+    out = c.ws.buf(tag + ".out", M, H)
+    ops.gemm(ctx, c.P[pfx + "output_linear.weight"], out, residual=x_res)
+    return out
+
+
+def self_attn_bwd(c, tag, pfx, dout, xn, ids, B, n, causal):
+    M, H = xn.shape
+    qkv, ctx = c.ws[tag + ".qkv"], c.ws[tag + ".ctx"]
+    grad_w(c, dout, ctx, c.G[pfx + "output_linear.weight"])
+    dctx = c.ws.buf("tmp.dctx.%d" % M, M, H)
+    ops.gemm(dout, c.P[pfx + "output_linear.weight"], dctx, b_t=True)
+    dqkv = c.ws.buf("tmp.dqkv.%d" % M, M, 3 * H)
+    seed, off = c.key(tag + ".adrop")
+    ops.attention_bwd(qkv[:, :H], qkv[:, H:2 * H], qkv[:, 2 * H:], dctx, dqkv[:, :H], dqkv[:, H:2 * H], dqkv[:, 2 * H:],
+                      ids, PAD, causal, B, c.nh, n, n, c.d, c.attn_drop, seed, off)
+    grad_w(c, dqkv, xn, c.gspan(pfx + "query_linear.weight", pfx + "value_linear.weight", H))
+    dxn = c.ws.buf("tmp.dxn.%d" % M, M, H)
+    ops.gemm(dqkv, c.pspan(pfx + "query_linear.weight", pfx + "value_linear.weight", H), dxn, b_t=True)
+    return dxn
+
+
+def cross_attn_fwd(c, tag, pfx, xn, x_res, enc_out, enc_ids, B, nq, nk):
+    M, H = xn.shape
+    q = c.ws.buf(tag + ".q", M, H)
+    ops.gemm(xn, c.P[pfx + "query_linear.weight"], q)
+    kv = c.ws.buf(tag + ".kv", enc_out.shape[0], 2 * H)
+    ops.gemm(enc_out, c.pspan(pfx + "key_linear.weight", pfx + "value_linear.weight", H), kv)
+    ctx = c.ws.buf(tag + ".ctx", M, H)
+    seed, off = c.key(tag + ".adrop")
+    ops.attention_fwd(q, kv[:, :H], kv[:, H:], ctx, enc_ids, PAD, False, B, c.nh, nq, nk, c.d, c.attn_drop, seed, off)
+    out = c.ws.buf(tag + ".out", M, H)
+    ops.gemm(ctx, c.P[pfx + "output_linear.weight"], out, residual=x_res)
+    return out
+
+
+def cross_attn_bwd(c, tag, pfx, dout, xn, enc_out, d_enc_out, first, enc_ids, B, nq, nk):
+    M, H = xn.shape
+    Me = enc_out.shape[0]
+    q, kv, ctx = c.ws[tag + ".q"], c.ws[tag + ".kv"], c.ws[tag + ".ctx"]
+    grad_w(c, dout, ctx, c.G[pfx + "output_linear.weight"])
+    dctx = c.ws.buf("tmp.dctx.%d" % M, M, H)
+    ops.gemm(dout, c.P[pfx + "output_linear.weight"], dctx, b_t=True)
+    dq = c.ws.buf("tmp.dq.%d" % M, M, H)
+    dkv = c.ws.buf("tmp.dkv.%d" % Me, Me, 2 * H)
+    seed, off = c.key(tag + ".adrop")
+    ops.attention_bwd(q, kv[:, :H], kv[:, H:], dctx, dq, dkv[:, :H], dkv[:, H:], enc_ids, PAD, False, B, c.nh, nq, nk,
+                      c.d, c.attn_drop, seed, off)
+    grad_w(c, dq, xn, c.G[pfx + "query_linear.weight"])
+    grad_w(c, dkv, enc_out, c.gspan(pfx + "key_linear.weight", pfx + "value_linear.weight", H))
+    wkv = c.pspan(pfx + "key_linear.weight", pfx + "value_linear.weight", H)
+    ops.gemm(dkv, wkv, d_enc_out, b_t=True, residual=None if first else d_enc_out)
+    dxn = c.ws.buf("tmp.dxn.%d" % M, M, H)
+    ops.gemm(dq, c.P[pfx + "query_linear.weight"], dxn, b_t=True)
+    return dxn
+
+
+# ------------------------------------------------------------------ position-wise FFN (ReLU after BOTH linears, N1)
+def ffn_fwd(c, tag, pfx, xn, x_res):
+    M, H = xn.shape
+    h = c.ws.buf(tag + ".h", M, c.F)
+    ops.gemm(xn, c.P[pfx + "layers.0.weight"], h, bias=c.P[pfx + "layers.0.bias"], relu=True)
+    ops.dropout_(h, c.relu_drop, *c.key(tag + ".d1"))
+    f2 = c.ws.buf(tag + ".f2", M, H)
+    ops.gemm(h, c.P[pfx + "layers.1.weight"], f2, bias=c.P[pfx + "layers.1.bias"], relu=True)
+    ops.dropout_(f2, c.relu_drop, *c.key(tag + ".d2"))
+    out = c.ws.buf(tag + ".out", M, H)
+    ops.axpby(x_res, f2, out)
+    return out
+
+
+def ffn_bwd(c, tag, pfx, dout, xn):
+    """dout: grad wrt (x_res + f2); returns grad wrt xn"""
+    M, H = xn.shape
+    h, f2 = c.ws[tag + ".h"], c.ws[tag + ".f2"]
+    df2 = dout
+    if c.relu_drop > 0:
+        df2 = c.ws.buf("tmp.df2.%d" % M, M, H)
+        ops.axpby(dout, dout, df2, 1.0, 0.0)
+        ops.dropout_(df2, c.relu_drop, *c.key(tag + ".d2"))
+    dpre2 = c.ws.buf("tmp.dpre2.%d" % M, M, H)
+    ops.relu_bwd_colsum(df2, f2, dpre2, c.G[pfx + "layers.1.bias"])
+    grad_w(c, dpre2, h, c.G[pfx + "layers.1.weight"])
+    dh = c.ws.buf("tmp.dh.%d" % M, M, c.F)
+    ops.gemm(dpre2, c.P[pfx + "layers.1.weight"], dh, b_t=True, relu_mask=h)
+    ops.dropout_(dh, c.relu_drop, *c.key(tag + ".d1"))
+    grad_w(c, dh, xn, c.G[pfx + "layers.0.weight"], c.G[pfx + "layers.0.bias"])
+    dxn = c.ws.buf("tmp.dxn.%d" % M, M, H)
+    ops.gemm(dh, c.P[pfx + "layers.0.weight"], dxn, b_t=True)
+    return dxn
+
+
+# ------------------------------------------------------------------ stacks
+def encoder_fwd(c, tag, pfx, x, ids, B, n, NL):
+    """models/transformer_layers.py:138-152 (timing already added by embed_fwd). Returns LN(x_NL)."""
+    c.ws.meta[tag + ".in"] = x
+    for i in range(NL):
+        lt, lp = "%s.%d" % (tag, i), "%senc.%d." % (pfx, i)
+        xn = ln_fwd(c, lt + ".ln1", lp + "layer_norm_mha", x)
+        a = self_attn_fwd(c, lt + ".sa", lp + "multi_head_attention.", xn, x, ids, B, n, False)
+        xn2 = ln_fwd(c, lt + ".ln2", lp + "layer_norm_ffn", a)
+        x = ffn_fwd(c, lt + ".ff", lp + "positionwise_feed_forward.", xn2, a)
+    c.ws.meta[tag + ".last"] = x
+    return ln_fwd(c, tag + ".lnf", pfx + "layer_norm", x)
+
+
+def encoder_bwd(c, tag, pfx, dy, ids, B, n, NL):
+    """dy: grad wrt the final LayerNorm output [M,H]. Returns grad wrt the stack input (in a workspace buffer)."""
+    M, H = dy.shape
+    dx = c.ws.buf(tag + ".dx", M, H)
+    ln_bwd(c, tag + ".lnf", pfx + "layer_norm", dy, c.ws.meta[tag + ".last"], dx, False)
+    for i in reversed(range(NL)):
+        lt, lp = "%s.%d" % (tag, i), "%senc.%d." % (pfx, i)
+        x_in = c.ws.meta[tag + ".in"] if i == 0 else c.ws["%s.%d.ff.out" % (tag, i - 1)]
+        a = c.ws[lt + ".sa.out"]
+        dxn2 = ffn_bwd(c, lt + ".ff", lp + "positionwise_feed_forward.", dx, c.ws[lt + ".ln2.y"])
+        ln_bwd(c, lt + ".ln2", lp + "layer_norm_ffn", dxn2, a, dx, True)
+        dxn = self_attn_bwd(c, lt + ".sa", lp + "multi_head_attention.", dx, c.ws[lt + ".ln1.y"], ids, B, n, False)
+        ln_bwd(c, lt + ".ln1", lp + "layer_norm_mha", dxn, x_in, dx, True)
+    return dx
+
+
+def decoder_fwd(c, tag, pfx, x, ids, enc_out, enc_ids, B, T, S, NL):
+    """models/transformer_layers.py:205-221; causal|pad mask of :207 is built inside the attention kernel."""
+    c.ws.meta[tag + ".in"] = x
+    for i in range(NL):
+        lt, lp = "%s.%d" % (tag, i), "%sdec.%d." % (pfx, i)
+        xn = ln_fwd(c, lt + ".ln1", lp + "layer_norm_mha_dec", x)
+        a = self_attn_fwd(c, lt + ".sa", lp + "multi_head_attention_dec.", xn, x, ids, B, T, True)
+        xn = ln_fwd(c, lt + ".ln2", lp + "layer_norm_mha_enc", a)
+        b = cross_attn_fwd(c, lt + ".ca", lp + "multi_head_attention_enc_dec.", xn, a, enc_out, enc_ids, B, T, S)
+        xn = ln_fwd(c, lt + ".ln3", lp + "layer_norm_ffn", b)
+        x = ffn_fwd(c, lt + ".ff", lp + "positionwise_feed_forward.", xn, b)
+    c.ws.meta[tag + ".last"] = x
+    return ln_fwd(c, tag + ".lnf", pfx + "layer_norm", x)
+
+
+def decoder_bwd(c, tag, pfx, dy, ids, enc_out, d_enc_out, enc_ids, B, T, S, NL):
+    """returns grad wrt decoder input; writes (not accumulates) the sum of cross-attention grads into d_enc_out"""
+    M, H = dy.shape
+    dx = c.ws.buf(tag + ".dx", M, H)
+    ln_bwd(c, tag + ".lnf", pfx + "layer_norm", dy, c.ws.meta[tag + ".last"], dx, False)
+    for i in reversed(range(NL)):
+        lt, lp = "%s.%d" % (tag, i), "%sdec.%d." % (pfx, i)
+        x_in = c.ws.meta[tag + ".in"] if i == 0 else c.ws["%s.%d.ff.out" % (tag, i - 1)]
+        a, b = c.ws[lt + ".sa.out"], c.ws[lt + ".ca.out"]
+        dxn = ffn_bwd(c, lt + ".ff", lp + "positionwise_feed_forward.", dx, c.ws[lt + ".ln3.y"])
+        ln_bwd(c, lt + ".ln3", lp + "layer_norm_ffn", dxn, b, dx, True)
+        dxn = cross_attn_bwd(c, lt + ".ca", lp + "multi_head_attention_enc_dec.", dx, c.ws[lt + ".ln2.y"], enc_out,
+                             d_enc_out, i == NL - 1, enc_ids, B, T, S)
+        ln_bwd(c, lt + ".ln2", lp + "layer_norm_mha_enc", dxn, a, dx, True)
+        dxn = self_attn_bwd(c, lt + ".sa", lp + "multi_head_attention_dec.", dx, c.ws[lt + ".ln1.y"], ids, B, T, True)
+        ln_bwd(c, lt + ".ln1", lp + "layer_norm_mha_dec", dxn, x_in, dx, True)
+    return dx
+
+
+# ------------------------------------------------------------------ small MLPs
+def linear_fwd(c, tag, pfx, x, relu=False, out=None):
+    y = out if out is not None else c.ws.buf(tag, x.shape[0], c.P[pfx + ".weight"].shape[0])
+    ops.gemm(x, c.P[pfx + ".weight"], y, bias=c.P[pfx + ".bias"], relu=relu)
+    return y
+
+
+def linear_bwd(c, tag, pfx, dy, x, relu_mask=None, need_dx=True, dx=None, accumulate_dx=False):
+    """dy is the grad wrt the (pre-activation) output; relu_mask = post-relu INPUT x when x came out of a relu"""
+    grad_w(c, dy, x, c.G[pfx + ".weight"], c.G[pfx + ".bias"])
+    if not need_dx:
+        return None
+    if dx is None:
+        dx = c.ws.buf(tag, dy.shape[0], c.P[pfx + ".weight"].shape[1])
+    assert not (accumulate_dx and relu_mask is not None)
+    ops.gemm(dy, c.P[pfx + ".weight"], dx, b_t=True, relu_mask=relu_mask, residual=dx if accumulate_dx else None)
+    return dx

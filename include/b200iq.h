@@ -72,9 +72,10 @@ int b200iq_embed_scatter_add(const int* ids, const float* dout, float* dtable, i
 /* x[b,t,:] += timing[t,:]; token 0 also gets add0[b,:] + add1[b,:] (either may be NULL)
  * replaces: models/transformer_layers.py:146,214; models/decoder_transformer.py:31-34,46 */
 int b200iq_add_timing(float* x, const float* timing, const float* add0, const float* add1, int B, int n, int H, void* stream);
-/* dst[b,:] (+)= src[b*n,:]  /  dst[b*n,:] += src[b,:]   (gradient plumbing of the token-0 adds; encoder_transformer.py:32) */
-int b200iq_tok0_gather(const float* src, float* dst, int B, int n, int H, int accumulate, void* stream);
-int b200iq_tok0_scatter_add(const float* src, float* dst, int B, int n, int H, void* stream);
+/* dst[b*ldd + c] (+)= src[(b*n)*H + c]  /  dst[(b*n)*H + c] += src[b*lds + c]  for c < H: moves token 0 of every sequence
+ * (x[:,0] reads of models/encoder_transformer.py:32,35, iq.py:110 and the matching gradient plumbing) */
+int b200iq_tok0_gather(const float* src, float* dst, int B, int n, int H, int ldd, int accumulate, void* stream);
+int b200iq_tok0_scatter_add(const float* src, float* dst, int B, int n, int H, int lds, void* stream);
 /* torch.nn.LayerNorm(H) forward (saves mean/rstd per row) and backward (dgamma/dbeta accumulate)
  * replaces: models/transformer_layers.py:134,151,202,220,256-257,320-322 */
 int b200iq_layernorm_fwd(const float* x, const float* gamma, const float* beta, float* y, float* mean, float* rstd,
@@ -91,8 +92,8 @@ int b200iq_dropout(float* x, size_t n, float p, uint64_t seed, uint64_t offset, 
 /* out ~ N(0,1), Philox4x32-10 + Box-Muller (oracle/philox.py is the bit-level CPU twin)
  * replaces: torch.randn on the CPU + H2D copy, models/transformer_layers.py:45 */
 int b200iq_randn(float* out, size_t n, uint64_t seed, uint64_t offset, void* stream);
-/* y = a*x + b*y */
-int b200iq_axpby(const float* x, float* y, size_t n, float a, float b, void* stream);
+/* out = a*x + b*y (out may alias x or y): residual adds that cannot ride a GEMM epilogue */
+int b200iq_axpby(const float* x, const float* y, float* out, size_t n, float a, float b, void* stream);
 
 /* ---------------------------------------------------------- fused attention (n <= 128) */
 typedef struct B200iqAttention {
