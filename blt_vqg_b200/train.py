@@ -1,0 +1,67 @@
+"""One IQ training step on the device: forward + losses + hand-written backward (+ gradient all-reduce) + clip + Adam.
+
+Replaces what Lightning does around `TrainIQ.training_step` (train_iq.py:105-132): `loss.backward()`,
+`gradient_clip_val=5` (train_iq.py:372), `Adam.step()` (train_iq.py:259-261) with the Noam learning rate of
+`custom_optimizer` (train_iq.py:252-257) and the pre-training -> latent switch (train_iq.py:108-111).
+The loss terms stay on the device (one 8-float vector); nothing synchronises with the host inside a step.
+"""
+import math
+
+import torch
+
+from . import ops
+
+
+def noam_lr(step, hidden_dim, warmup=4000):
+    """train_iq.py:252-257 (`lr(0) = 0`, peak at step == warmup)"""
+    return math.sqrt(1.0 / hidden_dim) * min(math.sqrt(1.0 / (step + 1)), step * warmup ** -1.5)
+
+
+class TrainStep:
+    """owns the Adam moments and the per-step schedule for one `IQ` module on one GPU (one DP rank)"""
+
+    def __init__(self, model, max_norm=5.0, betas=(0.9, 0.999), eps=1e-8, lr_fn=None, dp=None):
+        self.model = model
+        self.max_norm, self.betas, self.eps = max_norm, betas, eps
+        flat = model.flat.data
+        self.exp_avg = torch.zeros_like(flat)
+        self.exp_avg_sq = torch.zeros_like(flat)
+        self.hyper = torch.zeros(4, device=flat.device)
+        self._hyper_host = torch.zeros(4).pin_memory() if flat.is_cuda else torch.zeros(4)
+        self.normsq = torch.zeros(1, device=flat.device)
+        self.iter = 0      # TrainIQ.iter (train_iq.py:43)
+        self.kliter = 0    # TrainIQ.kliter (:44), counts steps since the latent switch
+        self.t = 0         # Adam step count (never reset: train_iq.py:111 is a no-op)
+        self.lr_fn = lr_fn or (lambda s: noam_lr(s, model.H))
+        self.dp = dp       # parallel.GradReducer or None
+
+    def set_hyper(self):
+        lr = self.lr_fn(self.iter)
+        t = self.t + 1
+        h = self._hyper_host
+        h[0], h[1], h[2] = lr, 1.0 - self.betas[0] ** t, 1.0 - self.betas[1] ** t
+        h[3] = 1.0 / (self.dp.world_size if self.dp is not None else 1)
+        self.hyper.copy_(h, non_blocking=True)
+
+    def step(self, images, answers, response, target, eps=None):
+        """returns the device tensor of loss terms (rec, img, kld, aux, count, gnorm_sq, ...) of this step"""
+        m = self.model
+        a = m.args
+        if self.iter == getattr(a, "num_pretraining_steps", -1) and not m.latent_transformer:
+            m.switch_GVT_train_mode(True)  # train_iq.py:108-110
+        self.set_hyper()
+        if self.dp is not None:
+            self.dp.begin_step(m)
+        terms = m.forward_losses(images, answers, response, target, kliter=self.kliter, eps=eps, backward=True)
+        g = m.grad_arena
+        if self.dp is not None:
+            self.dp.finish_step(m)
+        ops.grad_sumsq(g, self.normsq)
+        ops.adam_step(m.flat.data, g, self.exp_avg, self.exp_avg_sq, self.hyper, self.normsq, self.betas[0], self.betas[1],
+                      self.eps, self.max_norm, zero_grad=True)
+        self.iter += 1
+        self.t += 1
+        if m.latent_transformer:
+            self.kliter += 1
+        m.step_idx += 1
+        return terms

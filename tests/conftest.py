@@ -1,0 +1,24 @@
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a B200 (sm_100a) device; run with -m gpu on the GPU box")
+
+
+@pytest.fixture(scope="session")
+def built_lib():
+    """libb200iq.so, (re)built in-tree with nvcc when sources changed (cross-compiles without a GPU)"""
+    from blt_vqg_b200 import build
+    return build.build()
+
+
+@pytest.fixture(scope="session")
+def golden_dir():
+    return os.path.join(ROOT, "tests", "golden")
