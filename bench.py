@@ -1,0 +1,338 @@
+#!/usr/bin/env python
+"""bench.py — IQ train samples/sec (BASELINE.json metric) on N B200s of one node, plus the reference arm.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload transformer|lstm] [--impl ours|reference]
+  torchrun --nproc-per-node N bench.py --gpus N ...      (one rank per GPU, NCCL)
+
+A step = the whole hot path on one batch: image head -> encoders -> latent -> decoder -> fused vocab-projection+CE and
+the other loss terms -> full hand-written backward -> (gradient all-reduce) -> global-norm clip + Adam.  The frozen CNN
+trunk is excluded: inputs are pooled (B, FEAT) features.
+Keys: `value` = device-timed throughput with inputs resident in HBM; `e2e` = the same through the public call with
+pinned HOST buffers (H2D of the batch and D2H of the loss terms inside the timed region); `roofline` = the dominant
+kernel (tcgen05 GEMM) timed with CUDA events on the launching stream; `cpu_baseline` = the oracle port of the reference
+step on the host cores (bounded sample); `--impl reference` prints that CPU arm as its own line.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+METRIC = "iq_train_samples_per_sec"
+UNIT = "samples/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=os.environ.get("B200IQ_WORKLOAD", "transformer"), choices=["transformer", "lstm"])
+    ap.add_argument("--batch", type=int, default=0, help="per-GPU batch (default: the workload's)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-roofline", action="store_true")
+    ap.add_argument("--cpu-batch", type=int, default=64, help="bounded CPU sample: batch size of the oracle step")
+    return ap.parse_args()
+
+
+def workload_config(args):
+    from blt_vqg_b200 import synth
+    if args.workload == "transformer":
+        cfg = dict(synth.CONFIGS["cfg3"])   # BASELINE.json configs[2]: 6 layers, d_model 512, 8 heads, T=20, batch 512
+        name = "IQ transformer decoder (BLT-VQG, latent mode), 6 layers, d_model 512, 8 heads, E=300, F=2048, V=15000, T=20, S=5, R=21, FEAT=2048"
+    else:
+        cfg = dict(synth.LSTM_CONFIGS["cfg2"])  # BASELINE.json configs[1]: GloVe-300 LSTM, V=15000, batch 256
+        name = "IQ LSTM decoder full size (GloVe 300-d => H=300), Z=100, V=15000, T=20, FEAT=2048"
+    if args.batch:
+        cfg["B"] = args.batch
+    return cfg, name
+
+
+# ------------------------------------------------------------------ clocks during the timed region
+class ClockSampler(threading.Thread):
+    def __init__(self, index=0, period=0.1):
+        super().__init__(daemon=True)
+        self.index, self.period = index, period
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop_evt = threading.Event()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        names = {
+            getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
+        }
+        while not self._stop_evt.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, nm in names.items():
+                    if r & bit:
+                        self.reasons.add(nm)
+            except Exception:
+                pass
+            time.sleep(self.period)
+
+    def stop(self):
+        self._stop_evt.set()
+        self.join(timeout=2)
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+# ------------------------------------------------------------------ the CPU arm (oracle port of the reference step)
+def cpu_reference_steps(args, cfg, steps, warmup, batch):
+    """the reference training step (fp32, PyTorch CPU, all host threads) via oracle/; returns (samples/s, cores, ms/step)"""
+    from blt_vqg_b200 import synth
+    torch.set_num_threads(os.cpu_count())
+    cores = torch.get_num_threads()
+    if args.workload == "transformer":
+        from oracle import iq_oracle
+        from blt_vqg_b200.iq import IQ
+        torch.manual_seed(0)
+        m0 = IQ(True, synth.SynthVocab(cfg["V"]), synth.args_for(cfg))
+        names = m0.arena.names()
+        P = {k: v.clone() for k, v in m0.state_dict().items()}
+        params = [P[n].requires_grad_(True) for n in names]
+        ocfg = dict(num_layers=cfg["NL"], num_heads=cfg["NH"], latent_dim=cfg["L"], image_recon_lambda=0.1, kl_ceiling=0.5,
+                    aux_ceiling=1.0, full_kl_step=15000)
+        bn = (P["encoder_cnn.bn.running_mean"], P["encoder_cnn.bn.running_var"])
+
+        def loss_fn(b, step):
+            eps = torch.randn(b["feats"].shape[0], cfg["L"])  # CPU generator like transformer_layers.py:45
+            out, zl, kld, img, recon = iq_oracle.iq_forward(P, ocfg, b["feats"], b["answers"], b["posteriors"], b["questions"],
+                                                            eps=eps, latent_mode=True, training=True, drop=(0.1, 0.1), bn_state=bn)
+            return iq_oracle.iq_losses(ocfg, out, zl, kld, img, recon, b["questions"], step, True)[0]
+    else:
+        from oracle import lstm_oracle
+        params, loss_fn = lstm_oracle.make_training_closure(cfg)
+    opt = torch.optim.Adam(params, lr=1e-4)
+    times = []
+    for s in range(warmup + steps):
+        b = synth.make_batch(cfg, seed=1234 + s, B=batch)
+        t0 = time.perf_counter()
+        loss = loss_fn(b, s)
+        opt.zero_grad()
+        loss.backward()
+        torch.nn.utils.clip_grad_norm_(params, 5.0)
+        opt.step()
+        dt = time.perf_counter() - t0
+        if s >= warmup:
+            times.append(dt)
+    total = sum(times)
+    return batch * len(times) / total, cores, 1e3 * total / len(times)
+
+
+# ------------------------------------------------------------------ our arm
+def build_ours(args, cfg, dp):
+    from blt_vqg_b200 import _lib, synth
+    from blt_vqg_b200.train import TrainStep
+    _lib.require_device()
+    torch.manual_seed(0)
+    if args.workload == "transformer":
+        from blt_vqg_b200.iq import IQ
+        model = IQ(True, synth.SynthVocab(cfg["V"]), synth.args_for(cfg)).cuda().train()
+    else:
+        from blt_vqg_b200.lstm_iq import LSTMIQ
+        model = LSTMIQ.from_config(cfg).cuda().train()
+    ts = TrainStep(model, dp=dp)
+    ts.iter = 4000  # Noam LR at its peak (lr(0) would be 0: train_iq.py:252-257)
+    return model, ts
+
+
+def host_batches(cfg, n, rank):
+    """n distinct synthetic batches in pinned host memory, already in the kernels' dtypes (fp32 features, int32 ids)"""
+    from blt_vqg_b200 import synth
+    out = []
+    for i in range(n):
+        b = synth.make_batch(cfg, seed=1234 + 17 * i, rank=rank)
+        out.append({k: (v.float() if v.is_floating_point() else v.int()).contiguous().pin_memory() for k, v in b.items()})
+    return out
+
+
+def step_inputs(workload, b):
+    if workload == "transformer":
+        return b["feats"], b["answers"], b["posteriors"], b["questions"]
+    return b["feats"], b["answers"], b["alengths"], b["questions"]
+
+
+def timed_region(fn, steps, dist_on):
+    import torch.distributed as dist
+    if dist_on:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        fn(i)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    if dist_on:
+        t = torch.tensor([ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t)
+    return ms
+
+
+def gemm_roofline(ts, model, args, dev_batches, peaks):
+    """CUDA events on the launching stream around every GEMM launch of two extra steps (after the timed region)"""
+    from blt_vqg_b200 import ops
+    ops.GEMM_TRACE = []
+    step_t0, step_t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    step_t0.record()
+    for i in range(2):
+        ts.step(*step_inputs(args.workload, dev_batches[i % len(dev_batches)]))
+    step_t1.record()
+    torch.cuda.synchronize()
+    trace, ops.GEMM_TRACE = ops.GEMM_TRACE, None
+    tot_ms = sum(e0.elapsed_time(e1) for e0, e1, *_ in trace)
+    tot_fl = sum(t[2] for t in trace)
+    by_shape = {}
+    for e0, e1, fl, by, tag in trace:
+        d = by_shape.setdefault(tag, [0, 0.0, 0.0, 0.0])
+        d[0] += 1
+        d[1] += e0.elapsed_time(e1)
+        d[2] += fl
+        d[3] += by
+    top = sorted(by_shape.items(), key=lambda kv: -kv[1][1])[:12]
+    detail = [{"M": k[0], "N": k[1], "K": k[2], "flags": k[3], "split_k": k[4], "launches": v[0], "ms": round(v[1], 4),
+               "tflops": round(v[2] / v[1] * 1e-9, 1) if v[1] > 0 else None,
+               "operand_gbs": round(v[3] / v[1] * 1e-6, 1) if v[1] > 0 else None} for k, v in top]
+    peak = peaks.get("bf16_tflops_sustained") or 1400.0
+    ach = tot_fl / tot_ms * 1e-9 if tot_ms > 0 else 0.0
+    roof = {"bound": "tensor", "kernel": "gemm_tf32_kernel (tcgen05.mma kind::tf32, all dense projections)", "achieved": round(ach, 2),
+            "peak": peak, "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if "bf16_tflops_sustained" in peaks else "fallback",
+            "unit": "TFLOP/s", "frac": round(ach / peak, 4), "traffic": None, "launches_per_step": len(trace) // 2,
+            "gemm_ms_per_step": round(tot_ms / 2, 3), "step_ms_instrumented": round(step_t0.elapsed_time(step_t1) / 2, 3),
+            "note": "operands are TF32 (nominal dense peak 1.1 PF = half of bf16); algorithmic flops = 2MNK per launch"}
+    return roof, detail
+
+
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    cfg, wname = workload_config(args)
+    config = {"workload": wname, "per_gpu_batch": cfg["B"], "global_batch": cfg["B"] * world,
+              "parallelism": "dp%d" % world, "trunk": "excluded (pooled features in)",
+              "l2_policy": "per-step working set (347 MB weights + grads + activations) far exceeds the 126 MB L2; 4 rotating input batches"}
+
+    if args.impl == "reference":
+        # the reference's CPU implementation of the path: rank 0 alone, all host threads, bounded sample per step
+        if rank != 0:
+            return 0
+        steps, warm = min(args.steps, 3), min(args.warmup, 1)
+        v, cores, ms = cpu_reference_steps(args, cfg, steps, warm, args.cpu_batch)
+        sample = "fwd+losses+bwd+clip+Adam, fp32 PyTorch CPU oracle port of the reference step, batch %d of the workload's shapes, %d timed steps" % (args.cpu_batch, steps)
+        line = {"impl": "reference", "metric": METRIC, "value": round(v, 2), "unit": UNIT, "n_gpus": args.gpus, "steps": steps, "warmup": warm,
+                "ms_per_step": round(ms, 2), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+                "data": "synthetic", "config": config,
+                "cpu_baseline": {"value": round(v, 2), "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+                "e2e": {"value": round(v, 2), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        print(json.dumps(line), flush=True)
+        return 0
+
+    import torch.distributed as dist
+    dist_on = world > 1
+    torch.cuda.set_device(local_rank)
+    dp = None
+    if dist_on:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        from blt_vqg_b200.parallel import GradReducer
+        dp = GradReducer()
+    from blt_vqg_b200 import ops
+    model, ts = build_ours(args, cfg, dp)
+    hb = host_batches(cfg, 4, rank)
+    db = [{k: v.cuda(non_blocking=True) for k, v in b.items()} for b in hb]
+    torch.cuda.synchronize()
+
+    def dev_step(i):
+        ts.step(*step_inputs(args.workload, db[i % len(db)]))
+
+    sink = torch.zeros(8).pin_memory()
+
+    def e2e_step(i):
+        b = hb[i % len(hb)]
+        terms = ts.step(*step_inputs(args.workload, b))  # H2D of this step's inputs happens inside the call
+        sink.copy_(terms[:8], non_blocking=False)        # D2H of the loss terms (synchronises like the reference's .item())
+
+    for i in range(max(3, args.warmup)):
+        dev_step(i)
+    l0 = ops.LAUNCHES
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    ms = timed_region(dev_step, args.steps, dist_on)
+    launches = ops.LAUNCHES - l0
+    ms_e2e = timed_region(e2e_step, args.steps, dist_on)
+    clocks = sampler.stop()
+    terms = ts.step(*step_inputs(args.workload, db[0])).cpu()
+    finite = bool(torch.isfinite(terms[:4]).all())
+
+    if rank != 0:
+        if dist_on:
+            dist.barrier()
+            dist.destroy_process_group()
+        return 0
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    roof, detail = (None, None)
+    if not args.no_roofline:
+        saved_dp, ts.dp = ts.dp, None  # rank-0-only instrumented pass: no collectives
+        roof, detail = gemm_roofline(ts, model, args, db, peaks)
+        ts.dp = saved_dp
+    cpu = None
+    if not args.no_cpu_baseline and world == 1:
+        v, cores, cms = cpu_reference_steps(args, cfg, 3, 1, args.cpu_batch)
+        cpu = {"value": round(v, 2), "unit": UNIT, "cores": cores, "kind": "port", "ms_per_step": round(cms, 1),
+               "sample": "3 timed steps (after 1 warm-up) of fwd+losses+bwd+clip+Adam at batch %d of the same shapes, fp32 PyTorch CPU oracle port" % args.cpu_batch}
+    B = cfg["B"]
+    h2d = sum(v.numel() * v.element_size() for k, v in hb[0].items() if k in ("feats", "answers", "posteriors", "questions", "alengths"))
+    line = {"metric": METRIC, "value": round(B * world * args.steps / (ms * 1e-3), 1), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(3, args.warmup), "ms_per_step": round(ms / args.steps, 3), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "tf32 (fp32 storage, fp32 accumulate)", "data": "synthetic", "config": config,
+            "e2e": {"value": round(B * world * args.steps / (ms_e2e * 1e-3), 1), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 32,
+                    "ms_per_step": round(ms_e2e / args.steps, 3)},
+            "gpu_launches": launches, "gpu_launches_per_step": launches // max(1, args.steps), "clocks": clocks,
+            "roofline": roof, "cpu_baseline": cpu, "loss_terms_finite": finite,
+            "loss_terms": {"rec": round(float(terms[0]), 4), "img": round(float(terms[1]), 4), "kld": round(float(terms[2]), 4), "aux": round(float(terms[3]), 4)}}
+    print(json.dumps(line), flush=True)
+    if detail:
+        sys.stderr.write("GEMM breakdown (top shapes by time, 2 instrumented steps):\n")
+        for d in detail:
+            sys.stderr.write("  " + json.dumps(d) + "\n")
+    if dist_on:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -40,7 +40,9 @@ def gen_timing_signal(length, channels, min_timescale=1.0, max_timescale=1.0e4):
 
 
 def _ids(t, device):
-    return t.to(device=device, dtype=torch.int32).contiguous()
+    if t.dtype != torch.int32:
+        t = t.to(torch.int32)
+    return t.to(device=device, non_blocking=True).contiguous()
 
 
 class _IQFunction(torch.autograd.Function):
@@ -91,6 +93,7 @@ class IQ(nn.Module):
         self._gflat = None
         self._terms = None
         self._ctx = None
+        self.on_grad_ready = None  # set by parallel.GradReducer.begin_step
 
     # ------------------------------------------------------------------ module plumbing
     def _apply(self, fn, *a, **k):
@@ -148,7 +151,7 @@ class IQ(nn.Module):
 
     def _features(self, images):
         if images.dim() == 2:
-            return images.to(self.flat.device, torch.float32).contiguous()
+            return images.to(self.flat.device, torch.float32, non_blocking=True).contiguous()
         if self.trunk is None:
             raise _lib.B200iqError("raw images given but no trunk attached (call attach_trunk, or pass pooled features)")
         with torch.no_grad():
@@ -160,6 +163,7 @@ class IQ(nn.Module):
         ws = self._workspace(key)
         c = tf.Ctx(self.arena, self.grad_arena, ws, self.H, self.nh, self.F, self.E, self.attn_dropout,
                    self.relu_dropout, training, self.seed + self.step_idx)
+        c.on_ready = self.on_grad_ready
         return c
 
     def _run_forward(self, c, feats, cids, rids, tids, eps):
@@ -229,6 +233,7 @@ class IQ(nn.Module):
         B, S, T = m["feats"].shape[0], m["cids"].shape[1], m["tids"].shape[1]
         d_rh = tf.linear_bwd(c, "d_rh", "image_reconstructor.layers.fc1", d_recon, m["rh"], relu_mask=m["rh"])
         d_rin = tf.linear_bwd(c, "d_rin", "image_reconstructor.layers.fc0", d_rh, m["rin"])
+        c.ready("decoder.z_classifier.weight")  # vocab projections + reconstructor: final, largest bucket goes first
         if latent:
             ops.axpby(d_z, d_rin, d_z)
         d_enc_out = ws.buf("d_enc_out", B * S, H)
@@ -254,6 +259,7 @@ class IQ(nn.Module):
             d_p1 = tf.linear_bwd(c, "d_p1", pp + "3", d_p2, ws["lat.p1"], relu_mask=ws["lat.p1"])
             tf.linear_bwd(c, None, pp + "0", d_p1, cat[:, H:], dx=d_cat[:, H:], accumulate_dx=True)
             ops.tok0_scatter_add(d_cat[:, H:], d_enc_out, B, S, H)
+            c.ready("latent_layer.mean_logvar_prior.0.weight")
             d_r_out = ws.buf("d_r_out", B * R, H)
             d_r_out.zero_()
             ops.tok0_scatter_add(d_cat[:, :H], d_r_out, B, R, H)

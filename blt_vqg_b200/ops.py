@@ -12,6 +12,11 @@ from . import _lib as L
 
 # global switch: exact-fp32 CUDA-core GEMMs instead of tcgen05 TF32 (parity debugging, greedy decode)
 _FORCE_SIMT = os.environ.get("B200IQ_GEMM", "") == "simt"
+# number of kernel launches issued through the C ABI (bench.py reports it as gpu_launches)
+LAUNCHES = 0
+# when a list: gemm() brackets every launch with CUDA events on the launching stream and appends
+# (start_event, end_event, flops, hbm_bytes, tag) — bench.py's per-kernel roofline pass
+GEMM_TRACE = None
 
 
 class gemm_mode:
@@ -60,6 +65,15 @@ def gemm(a, b, out=None, *, a_t=False, b_t=False, bias=None, residual=None, relu
     p = L.GemmParams(L.fptr(a), L.fptr(b), L.fptr(out), L.fptr(bias), L.fptr(residual), M, N, K,
                      _ld(a), _ld(b), _ld(out), _ld(residual) if residual is not None else 0,
                      flags, split_k, float(alpha))
+    global LAUNCHES
+    LAUNCHES += 1
+    if GEMM_TRACE is not None:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        L.check(L.lib().b200iq_gemm(C.byref(p), L.stream_ptr()), "b200iq_gemm")
+        e1.record()
+        GEMM_TRACE.append((e0, e1, 2.0 * M * N * K, 4.0 * (M * K + N * K + M * N), (M, N, K, flags, split_k)))
+        return out
     L.check(L.lib().b200iq_gemm(C.byref(p), L.stream_ptr()), "b200iq_gemm")
     return out
 
@@ -74,6 +88,8 @@ def _f(x):
 
 
 def _call(name, *args):
+    global LAUNCHES
+    LAUNCHES += 1
     L.check(getattr(L.lib(), name)(*args, L.stream_ptr()), name)
 
 

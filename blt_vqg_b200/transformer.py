@@ -49,6 +49,11 @@ class Ctx:
         self.seed = seed
         self.site = 0
         self.sm = 148
+        self.on_ready = None  # callable(flat_offset): gradients at and after this arena offset are final (parallel.py)
+
+    def ready(self, name):
+        if self.on_ready is not None:
+            self.on_ready(self.arena.offsets.get(name + "#pack", self.arena.offsets.get(name)))
 
     def pspan(self, first, last, cols):
         o0, o1 = self.arena.span(first, last)
@@ -241,6 +246,7 @@ def encoder_bwd(c, tag, pfx, dy, ids, B, n, NL):
         ln_bwd(c, lt + ".ln2", lp + "layer_norm_ffn", dxn2, a, dx, True)
         dxn = self_attn_bwd(c, lt + ".sa", lp + "multi_head_attention.", dx, c.ws[lt + ".ln1.y"], ids, B, n, False)
         ln_bwd(c, lt + ".ln1", lp + "layer_norm_mha", dxn, x_in, dx, True)
+        c.ready(lp + "layer_norm_mha.weight")
     return dx
 
 
@@ -275,6 +281,7 @@ def decoder_bwd(c, tag, pfx, dy, ids, enc_out, d_enc_out, enc_ids, B, T, S, NL):
         ln_bwd(c, lt + ".ln2", lp + "layer_norm_mha_enc", dxn, a, dx, True)
         dxn = self_attn_bwd(c, lt + ".sa", lp + "multi_head_attention_dec.", dx, c.ws[lt + ".ln1.y"], ids, B, T, True)
         ln_bwd(c, lt + ".ln1", lp + "layer_norm_mha_dec", dxn, x_in, dx, True)
+        c.ready(lp + "layer_norm_mha_dec.weight")
     return dx
 
 

@@ -1,0 +1,128 @@
+"""GPU: every C-ABI kernel against a plain torch fp32/fp64 statement of the same op (called through ctypes)."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ops(built_lib):
+    from blt_vqg_b200 import _lib, ops as o
+    _lib.require_device()
+    torch.manual_seed(0)
+    return o
+
+
+def rel(a, b):
+    return float((a.double() - b.double()).norm() / (b.double().norm() + 1e-30))
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 128, 32), (256, 384, 300), (1000, 200, 1024), (37, 52, 20), (640, 15000, 512)])
+@pytest.mark.parametrize("a_t,b_t", [(False, False), (False, True), (True, False), (True, True)])
+def test_gemm_all_layouts(ops, M, N, K, a_t, b_t):
+    if (a_t and M % 4) or (b_t and N % 4) or (not a_t and K % 4) or (not b_t and K % 4):
+        pytest.skip("TMA needs 16-byte row pitch")
+    dev = "cuda"
+    A, B = torch.randn(M, K, device=dev), torch.randn(N, K, device=dev)
+    Aa = A.t().contiguous() if a_t else A
+    Bb = B.t().contiguous() if b_t else B
+    bias, res = torch.randn(N, device=dev), torch.randn(M, N, device=dev)
+    ref = A.double() @ B.double().t()
+    for simt, tol in ((True, 1e-5), (False, 2e-3)):  # exact fp32 CUDA cores / tcgen05 TF32 (10-bit mantissa)
+        assert rel(ops.gemm(Aa, Bb, a_t=a_t, b_t=b_t, simt=simt), ref) < tol
+        out = ops.gemm(Aa, Bb, a_t=a_t, b_t=b_t, bias=bias, residual=res, relu=True, alpha=0.5, simt=simt)
+        assert rel(out, torch.relu(0.5 * ref + bias.double() + res.double())) < tol
+        acc = torch.ones(M, N, device=dev)
+        ops.gemm(Aa, Bb, acc, a_t=a_t, b_t=b_t, accumulate=True, split_k=4, simt=simt)
+        assert rel(acc, ref + 1.0) < tol
+        gate = torch.randn(M, N, device=dev)
+        out = ops.gemm(Aa, Bb, a_t=a_t, b_t=b_t, relu_mask=gate, simt=simt)
+        assert rel(out, ref * (gate > 0)) < tol
+
+
+def test_gemm_rejects_bad_arguments(ops):
+    from blt_vqg_b200._lib import B200iqError
+    a, b = torch.randn(8, 6, device="cuda"), torch.randn(8, 6, device="cuda")
+    with pytest.raises(B200iqError):
+        ops.gemm(a, b)  # K=6: leading dimension not a multiple of 4 floats
+    with pytest.raises(B200iqError):
+        ops.gemm(torch.randn(8, 8, device="cuda"), torch.randn(8, 8, device="cuda"), torch.zeros(8, 8, device="cuda"), split_k=2)
+
+
+def test_embedding_gather_scatter(ops):
+    V, E, M = 300, 52, 1000
+    table = torch.randn(V, E, device="cuda")
+    ids = torch.randint(0, V, (M,), device="cuda", dtype=torch.int32)
+    ids[::7] = 0
+    out = torch.empty(M, E, device="cuda")
+    ops.embed_gather(ids, table, out)
+    assert torch.equal(out, table[ids.long()])
+    dout = torch.randn(M, E, device="cuda")
+    dt = torch.zeros(V, E, device="cuda")
+    ops.embed_scatter_add(ids, dout, dt, 0)
+    ref = torch.zeros(V, E, device="cuda", dtype=torch.float64).index_add_(0, ids.long(), dout.double())
+    ref[0] = 0  # padding_idx row gets no gradient
+    assert rel(dt, ref) < 1e-6
+
+
+def test_layernorm_fwd_bwd(ops):
+    for M, H in ((333, 64), (1000, 512), (77, 300)):
+        x = torch.randn(M, H, device="cuda", requires_grad=True)
+        g, b = torch.randn(H, device="cuda", requires_grad=True), torch.randn(H, device="cuda", requires_grad=True)
+        y = torch.empty(M, H, device="cuda")
+        mean, rstd = torch.empty(M, device="cuda"), torch.empty(M, device="cuda")
+        ops.layernorm_fwd(x.detach(), g.detach(), b.detach(), y, mean, rstd)
+        yr = torch.nn.functional.layer_norm(x, (H,), g, b, 1e-5)
+        assert rel(y, yr) < 1e-5
+        dy = torch.randn(M, H, device="cuda")
+        yr.backward(dy)
+        dx = torch.ones(M, H, device="cuda")
+        dg, db = torch.zeros(H, device="cuda"), torch.zeros(H, device="cuda")
+        ops.layernorm_bwd(dy, x.detach(), g.detach(), mean, rstd, dx, dg, db, True)
+        assert rel(dx - 1.0, x.grad) < 1e-4
+        assert rel(dg, g.grad) < 1e-4 and rel(db, b.grad) < 1e-4
+
+
+def test_small_elementwise(ops):
+    B, n, H = 9, 5, 64
+    x = torch.randn(B * n, H, device="cuda")
+    timing, a0, a1 = torch.randn(n, H, device="cuda"), torch.randn(B, H, device="cuda"), torch.randn(B, H, device="cuda")
+    ref = x.view(B, n, H) + timing[None]
+    ref[:, 0] += a0 + a1
+    ops.add_timing(x, timing, a0, a1, B, n, H)
+    assert rel(x.view(B, n, H), ref) < 1e-6
+    wide = torch.zeros(B, 2 * H, device="cuda")
+    ops.tok0_gather(x, wide[:, H:], B, n, H)
+    assert torch.equal(wide[:, H:], x.view(B, n, H)[:, 0]) and float(wide[:, :H].abs().max()) == 0
+    dst = torch.zeros(B * n, H, device="cuda")
+    ops.tok0_scatter_add(wide[:, H:], dst, B, n, H)
+    assert torch.equal(dst.view(B, n, H)[:, 0], wide[:, H:]) and float(dst.view(B, n, H)[:, 1:].abs().max()) == 0
+    y = torch.randn(500, 96, device="cuda")
+    cs = torch.ones(96, device="cuda")
+    ops.colsum_add(y, cs)
+    assert rel(cs, 1 + y.double().sum(0)) < 1e-5
+    dy = torch.randn(500, 96, device="cuda")
+    dpre, dbias = torch.empty_like(dy), torch.zeros(96, device="cuda")
+    ops.relu_bwd_colsum(dy, y, dpre, dbias)
+    assert torch.equal(dpre, dy * (y > 0)) and rel(dbias, (dy * (y > 0)).double().sum(0)) < 1e-5
+    out = torch.empty_like(y)
+    ops.axpby(y, dy, out, 0.5, -2.0)
+    assert rel(out, 0.5 * y - 2.0 * dy) < 1e-6
+
+
+def test_philox_randn_and_dropout(ops):
+    n = 1 << 20
+    a, b = torch.empty(n, device="cuda"), torch.empty(n, device="cuda")
+    ops.randn_(a, 1234, 0)
+    ops.randn_(b, 1234, 0)
+    assert torch.equal(a, b)  # counter-based: same key, same numbers
+    ops.randn_(b, 1235, 0)
+    assert not torch.equal(a, b)
+    assert abs(float(a.mean())) < 5e-3 and abs(float(a.std()) - 1) < 5e-3
+    x = torch.ones(n, device="cuda")
+    ops.dropout_(x, 0.1, 7, 1 << 40)
+    keep = float((x > 0).float().mean())
+    assert abs(keep - 0.9) < 3e-3 and float(x.max()) == pytest.approx(1 / 0.9)
+    g = torch.ones(n, device="cuda")
+    ops.dropout_(g, 0.1, 7, 1 << 40)
+    assert torch.equal(g, x)  # backward re-creates the same mask
