@@ -71,4 +71,4 @@ class GemmParams(C.Structure):
 
 
 GEMM_A_MN, GEMM_B_MN, GEMM_BIAS, GEMM_RELU = 1, 2, 4, 8
-GEMM_RESIDUAL, GEMM_ACCUM, GEMM_SIMT, GEMM_RELU_MASK = 16, 32, 64, 128
+GEMM_RESIDUAL, GEMM_ACCUM, GEMM_SIMT, GEMM_RELU_MASK, GEMM_FP32_OUT = 16, 32, 64, 128, 256

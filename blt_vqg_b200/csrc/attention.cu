@@ -19,6 +19,7 @@ struct AttnArgs {
   int B, nh, nq, nk, d;
   float scale, drop_p;
   uint64_t seed, offset;
+  int rn;  // round outputs to TF32
 };
 
 __device__ __forceinline__ float keep_scale(const AttnArgs& a, size_t elem) {
@@ -99,7 +100,7 @@ attention_fwd_kernel(AttnArgs a, float* __restrict__ out, int ldo) {
     for (int c = lane; c < a.d; c += 32) {
       float o = 0.f;
       for (int j = 0; j < a.nk; ++j) o = fmaf(Pw[j], Vs[j * dp + c], o);
-      orow[c] = o;
+      orow[c] = rnd(o, a.rn);
     }
     __syncwarp();
   }
@@ -153,7 +154,7 @@ attention_bwd_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, float*
     int i = idx / a.d, c = idx - i * a.d;
     float s = 0.f;
     for (int j = 0; j < a.nk; ++j) s = fmaf(dSs[i * np + j], Ks[j * dp + c], s);
-    dq[((size_t)b * a.nq + i) * lddq + h * a.d + c] = s;
+    dq[((size_t)b * a.nq + i) * lddq + h * a.d + c] = rnd(s, a.rn);
   }
   for (int idx = threadIdx.x; idx < a.nk * a.d; idx += blockDim.x) {
     int j = idx / a.d, c = idx - j * a.d;
@@ -162,8 +163,8 @@ attention_bwd_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, float*
       sk = fmaf(dSs[i * np + j], Qs[i * dp + c], sk);
       sv = fmaf(Ws[i * np + j], dOs[i * dp + c], sv);
     }
-    dk[((size_t)b * a.nk + j) * lddk + h * a.d + c] = sk;
-    dv[((size_t)b * a.nk + j) * lddv + h * a.d + c] = sv;
+    dk[((size_t)b * a.nk + j) * lddk + h * a.d + c] = rnd(sk, a.rn);
+    dv[((size_t)b * a.nk + j) * lddv + h * a.d + c] = rnd(sv, a.rn);
   }
 }
 
@@ -180,6 +181,7 @@ static AttnArgs to_args(const B200iqAttention* p) {
   a.key_ids = p->key_ids; a.pad_id = p->pad_id; a.causal = p->causal;
   a.B = p->B; a.nh = p->num_heads; a.nq = p->nq; a.nk = p->nk; a.d = p->head_dim;
   a.scale = p->scale; a.drop_p = p->drop_p; a.seed = p->seed; a.offset = p->offset;
+  a.rn = round_mode();
   return a;
 }
 

@@ -32,6 +32,8 @@ static inline int launch_status(const char* what) {
 
 static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 int sm_count();
+// 1: every activation / gradient tensor a kernel writes is rounded to the nearest TF32 value (b200iq_set_tf32_rounding)
+int round_mode();
 
 // ---------------------------------------------------------------- device utils
 __device__ __forceinline__ float warp_sum(float v) {
@@ -44,6 +46,16 @@ __device__ __forceinline__ float warp_max(float v) {
   for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
   return v;
 }
+
+// Round-to-nearest (ties away) fp32 -> tf32, kept in an fp32 container.  tcgen05.mma kind::tf32 TRUNCATES its fp32
+// operands; truncation shrinks every product towards zero (a systematic ~7e-4 relative bias per GEMM), so every
+// tensor that can become a GEMM operand is rounded once, by the kernel that produces it.
+__device__ __forceinline__ float tf32_rn(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+}
+__device__ __forceinline__ float rnd(float x, int on) { return on ? tf32_rn(x) : x; }
 
 // block-wide sum; `red` must hold >= 32 floats of shared memory. All threads get the result.
 __device__ __forceinline__ float block_sum(float v, float* red) {

@@ -12,6 +12,9 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 
+static int g_round = 1;
+int round_mode() { return g_round; }
+
 int sm_count() {
   static int n = 0;
   if (!n) {
@@ -25,6 +28,12 @@ int sm_count() {
 }  // namespace b200iq
 
 extern "C" int b200iq_abi_version(void) { return B200IQ_ABI_VERSION; }
+
+extern "C" int b200iq_set_tf32_rounding(int on) {
+  int prev = b200iq::g_round;
+  b200iq::g_round = on ? 1 : 0;
+  return prev;
+}
 
 extern "C" const char* b200iq_last_error(void) { return b200iq::g_err; }
 

@@ -8,7 +8,7 @@ namespace b200iq {
 // ---------------------------------------------------------------- embedding gather
 // out[m, :] = table[ids[m], :]            replaces: nn.Embedding forward, models/iq.py:71-78
 __global__ void embed_gather_kernel(const int* __restrict__ ids, const float* __restrict__ table,
-                                    float* __restrict__ out, int M, int E, int V) {
+                                    float* __restrict__ out, int M, int E, int V, int rn) {
   int m = blockIdx.x * blockDim.y + threadIdx.y;
   if (m >= M) return;
   int id = ids[m];
@@ -16,10 +16,13 @@ __global__ void embed_gather_kernel(const int* __restrict__ ids, const float* __
   const float* src = table + (size_t)id * E;
   float* dst = out + (size_t)m * E;
   if ((E & 3) == 0) {
-    for (int c = threadIdx.x * 4; c < E; c += blockDim.x * 4)
-      *reinterpret_cast<float4*>(dst + c) = __ldg(reinterpret_cast<const float4*>(src + c));
+    for (int c = threadIdx.x * 4; c < E; c += blockDim.x * 4) {
+      float4 v = __ldg(reinterpret_cast<const float4*>(src + c));
+      v.x = rnd(v.x, rn); v.y = rnd(v.y, rn); v.z = rnd(v.z, rn); v.w = rnd(v.w, rn);
+      *reinterpret_cast<float4*>(dst + c) = v;
+    }
   } else {
-    for (int c = threadIdx.x; c < E; c += blockDim.x) dst[c] = __ldg(src + c);
+    for (int c = threadIdx.x; c < E; c += blockDim.x) dst[c] = rnd(__ldg(src + c), rn);
   }
 }
 
@@ -39,7 +42,7 @@ __global__ void embed_scatter_kernel(const int* __restrict__ ids, const float* _
 // replaces: transformer_layers.py:146,214 and encoder/decoder_transformer.py token-0 adds
 __global__ void add_timing_kernel(float* __restrict__ x, const float* __restrict__ timing,
                                   const float* __restrict__ add0, const float* __restrict__ add1,
-                                  int B, int n, int H) {
+                                  int B, int n, int H, int rn) {
   size_t total = (size_t)B * n * H;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
     int c = (int)(i % H);
@@ -50,18 +53,18 @@ __global__ void add_timing_kernel(float* __restrict__ x, const float* __restrict
       if (add0) v += add0[(size_t)b * H + c];
       if (add1) v += add1[(size_t)b * H + c];
     }
-    x[i] = v;
+    x[i] = rnd(v, rn);
   }
 }
 
 // dst[b, :] (+)= src[b*n + 0, :]  — gathers the gradient of token 0 of every sequence
-__global__ void tok0_gather_kernel(const float* __restrict__ src, float* __restrict__ dst, int B, int n, int H, int ldd, int accumulate) {
+__global__ void tok0_gather_kernel(const float* __restrict__ src, float* __restrict__ dst, int B, int n, int H, int ldd, int accumulate, int rn) {
   size_t total = (size_t)B * H;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
     int c = (int)(i % H), b = (int)(i / H);
     float v = src[(size_t)b * n * H + c];
     size_t o = (size_t)b * ldd + c;
-    dst[o] = accumulate ? dst[o] + v : v;
+    dst[o] = rnd(accumulate ? dst[o] + v : v, rn);
   }
 }
 
@@ -78,7 +81,7 @@ __global__ void tok0_scatter_kernel(const float* __restrict__ src, float* __rest
 // replaces: torch.nn.LayerNorm at transformer_layers.py:134,151,202,220,256-257,320-322
 __global__ void layernorm_fwd_kernel(const float* __restrict__ x, const float* __restrict__ g, const float* __restrict__ b,
                                      float* __restrict__ y, float* __restrict__ mean, float* __restrict__ rstd,
-                                     int M, int H, float eps) {
+                                     int M, int H, float eps, int rn) {
   int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
   if (row >= M) return;
   const float* xr = x + (size_t)row * H;
@@ -89,7 +92,7 @@ __global__ void layernorm_fwd_kernel(const float* __restrict__ x, const float* _
   for (int c = lane; c < H; c += 32) { float d = xr[c] - mu; v += d * d; }
   float rs = rsqrtf(warp_sum(v) / H + eps);
   float* yr = y + (size_t)row * H;
-  for (int c = lane; c < H; c += 32) yr[c] = (xr[c] - mu) * rs * g[c] + b[c];
+  for (int c = lane; c < H; c += 32) yr[c] = rnd((xr[c] - mu) * rs * g[c] + b[c], rn);
   if (lane == 0) { if (mean) mean[row] = mu; if (rstd) rstd[row] = rs; }
 }
 
@@ -99,7 +102,7 @@ template <int MAXC>
 __global__ void layernorm_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ g,
                                      const float* __restrict__ mean, const float* __restrict__ rstd,
                                      float* __restrict__ dx, float* __restrict__ dg, float* __restrict__ db,
-                                     int M, int H, int rows_per_cta, int accumulate) {
+                                     int M, int H, int rows_per_cta, int accumulate, int rn) {
   __shared__ float red[32];
   int r0 = blockIdx.x * rows_per_cta, r1 = min(M, r0 + rows_per_cta);
   float pg[MAXC], pb[MAXC];
@@ -128,7 +131,7 @@ __global__ void layernorm_bwd_kernel(const float* __restrict__ dy, const float* 
       if (c < H) {
         float xh = (xr[c] - mu) * rs;
         float v = rs * (dyr[c] * g[c] - s1 - xh * s2);
-        dxr[c] = accumulate ? dxr[c] + v : v;
+        dxr[c] = rnd(accumulate ? dxr[c] + v : v, rn);
       }
     }
   }
@@ -169,7 +172,7 @@ __global__ void relu_bwd_colsum_kernel(const float* dy, const float* __restrict_
 // ---------------------------------------------------------------- Philox dropout / randn / axpy
 // x *= mask / (1-p), mask from Philox(seed; counter = offset + i/4).  Calling it again with the same
 // (seed, offset) on the gradient reproduces the mask, so no mask tensor is stored.
-__global__ void dropout_kernel(float* __restrict__ x, size_t n, float p, uint64_t seed, uint64_t offset) {
+__global__ void dropout_kernel(float* __restrict__ x, size_t n, float p, uint64_t seed, uint64_t offset, int rn) {
   Philox ph(seed);
   float scale = 1.f / (1.f - p);
   size_t n4 = (n + 3) / 4;
@@ -180,7 +183,7 @@ __global__ void dropout_kernel(float* __restrict__ x, size_t n, float p, uint64_
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       size_t i = q * 4 + j;
-      if (i < n) x[i] = (u32_to_unit(r[j]) > p) ? x[i] * scale : 0.f;
+      if (i < n) x[i] = (u32_to_unit(r[j]) > p) ? rnd(x[i] * scale, rn) : 0.f;
     }
   }
 }
@@ -207,9 +210,23 @@ __global__ void randn_kernel(float* __restrict__ out, size_t n, uint64_t seed, u
 }
 
 // out = a*x + b*y  (out may alias x or y)
-__global__ void axpby_kernel(const float* x, const float* y, float* out, size_t n, float a, float b) {
+__global__ void axpby_kernel(const float* x, const float* y, float* out, size_t n, float a, float b, int rn) {
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
-    out[i] = a * x[i] + (b == 0.f ? 0.f : b * y[i]);
+    out[i] = rnd(a * x[i] + (b == 0.f ? 0.f : b * y[i]), rn);
+}
+
+// dst = rn_tf32(src), float4-vectorised (n and both pointers 16-byte aligned) with a scalar tail
+__global__ void round_tf32_kernel(const float* __restrict__ src, float* __restrict__ dst, size_t n) {
+  size_t n4 = n >> 2;
+  const float4* s4 = reinterpret_cast<const float4*>(src);
+  float4* d4 = reinterpret_cast<float4*>(dst);
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+    float4 v = s4[i];
+    v.x = tf32_rn(v.x); v.y = tf32_rn(v.y); v.z = tf32_rn(v.z); v.w = tf32_rn(v.w);
+    d4[i] = v;
+  }
+  for (size_t i = (n4 << 2) + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    dst[i] = tf32_rn(src[i]);
 }
 
 static inline int grid_for(size_t n, int threads) {
@@ -226,7 +243,7 @@ using namespace b200iq;
 extern "C" int b200iq_embed_gather(const int* ids, const float* table, float* out, int M, int E, int V, void* stream) {
   B200IQ_CHECK_ARG(ids && table && out && M > 0 && E > 0 && V > 0, "embed_gather: bad args");
   dim3 blk(32, 8);
-  embed_gather_kernel<<<ceil_div(M, 8), blk, 0, ST>>>(ids, table, out, M, E, V);
+  embed_gather_kernel<<<ceil_div(M, 8), blk, 0, ST>>>(ids, table, out, M, E, V, round_mode());
   return launch_status("embed_gather");
 }
 
@@ -239,13 +256,13 @@ extern "C" int b200iq_embed_scatter_add(const int* ids, const float* dout, float
 
 extern "C" int b200iq_add_timing(float* x, const float* timing, const float* add0, const float* add1, int B, int n, int H, void* stream) {
   B200IQ_CHECK_ARG(x && B > 0 && n > 0 && H > 0, "add_timing: bad args");
-  add_timing_kernel<<<grid_for((size_t)B * n * H, 256), 256, 0, ST>>>(x, timing, add0, add1, B, n, H);
+  add_timing_kernel<<<grid_for((size_t)B * n * H, 256), 256, 0, ST>>>(x, timing, add0, add1, B, n, H, round_mode());
   return launch_status("add_timing");
 }
 
 extern "C" int b200iq_tok0_gather(const float* src, float* dst, int B, int n, int H, int ldd, int accumulate, void* stream) {
   B200IQ_CHECK_ARG(src && dst && B > 0 && n > 0 && H > 0 && ldd >= H, "tok0_gather: bad args");
-  tok0_gather_kernel<<<grid_for((size_t)B * H, 256), 256, 0, ST>>>(src, dst, B, n, H, ldd, accumulate);
+  tok0_gather_kernel<<<grid_for((size_t)B * H, 256), 256, 0, ST>>>(src, dst, B, n, H, ldd, accumulate, round_mode());
   return launch_status("tok0_gather");
 }
 
@@ -258,7 +275,7 @@ extern "C" int b200iq_tok0_scatter_add(const float* src, float* dst, int B, int 
 extern "C" int b200iq_layernorm_fwd(const float* x, const float* gamma, const float* beta, float* y, float* mean, float* rstd,
                                     int M, int H, float eps, void* stream) {
   B200IQ_CHECK_ARG(x && gamma && beta && y && M > 0 && H > 0, "layernorm_fwd: bad args");
-  layernorm_fwd_kernel<<<ceil_div(M, 8), 256, 0, ST>>>(x, gamma, beta, y, mean, rstd, M, H, eps);
+  layernorm_fwd_kernel<<<ceil_div(M, 8), 256, 0, ST>>>(x, gamma, beta, y, mean, rstd, M, H, eps, round_mode());
   return launch_status("layernorm_fwd");
 }
 
@@ -269,10 +286,10 @@ extern "C" int b200iq_layernorm_bwd(const float* dy, const float* x, const float
   int ctas = min(M, sm_count() * 4);
   int rows = ceil_div(M, ctas);
   ctas = ceil_div(M, rows);
-  if (H <= 256) layernorm_bwd_kernel<1><<<ctas, 256, 0, ST>>>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, M, H, rows, accumulate_dx);
-  else if (H <= 512) layernorm_bwd_kernel<2><<<ctas, 256, 0, ST>>>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, M, H, rows, accumulate_dx);
-  else if (H <= 1024) layernorm_bwd_kernel<4><<<ctas, 256, 0, ST>>>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, M, H, rows, accumulate_dx);
-  else layernorm_bwd_kernel<8><<<ctas, 256, 0, ST>>>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, M, H, rows, accumulate_dx);
+  if (H <= 256) layernorm_bwd_kernel<1><<<ctas, 256, 0, ST>>>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, M, H, rows, accumulate_dx, round_mode());
+  else if (H <= 512) layernorm_bwd_kernel<2><<<ctas, 256, 0, ST>>>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, M, H, rows, accumulate_dx, round_mode());
+  else if (H <= 1024) layernorm_bwd_kernel<4><<<ctas, 256, 0, ST>>>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, M, H, rows, accumulate_dx, round_mode());
+  else layernorm_bwd_kernel<8><<<ctas, 256, 0, ST>>>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, M, H, rows, accumulate_dx, round_mode());
   return launch_status("layernorm_bwd");
 }
 
@@ -295,7 +312,7 @@ extern "C" int b200iq_relu_bwd_colsum(const float* dy, const float* y, float* dp
 extern "C" int b200iq_dropout(float* x, size_t n, float p, uint64_t seed, uint64_t offset, void* stream) {
   B200IQ_CHECK_ARG(x && n > 0 && p >= 0.f && p < 1.f, "dropout: bad args");
   if (p == 0.f) return 0;
-  dropout_kernel<<<grid_for((n + 3) / 4, 256), 256, 0, ST>>>(x, n, p, seed, offset);
+  dropout_kernel<<<grid_for((n + 3) / 4, 256), 256, 0, ST>>>(x, n, p, seed, offset, round_mode());
   return launch_status("dropout");
 }
 
@@ -307,6 +324,13 @@ extern "C" int b200iq_randn(float* out, size_t n, uint64_t seed, uint64_t offset
 
 extern "C" int b200iq_axpby(const float* x, const float* y, float* out, size_t n, float a, float b, void* stream) {
   B200IQ_CHECK_ARG(x && y && out && n > 0, "axpby: bad args");
-  axpby_kernel<<<grid_for(n, 256), 256, 0, ST>>>(x, y, out, n, a, b);
+  axpby_kernel<<<grid_for(n, 256), 256, 0, ST>>>(x, y, out, n, a, b, round_mode());
   return launch_status("axpby");
+}
+
+extern "C" int b200iq_round_tf32(const float* src, float* dst, size_t n, void* stream) {
+  B200IQ_CHECK_ARG(src && dst && n > 0, "round_tf32: bad args");
+  B200IQ_CHECK_ARG(((((uintptr_t)src) | ((uintptr_t)dst)) & 15) == 0, "round_tf32: pointers must be 16-byte aligned");
+  round_tf32_kernel<<<grid_for((n + 3) / 4, 256), 256, 0, ST>>>(src, dst, n);
+  return launch_status("round_tf32");
 }

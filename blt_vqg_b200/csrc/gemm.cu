@@ -19,6 +19,7 @@ static constexpr int GEMM_THREADS = 192;
 struct GemmEpi {
   float* C; const float* bias; const float* residual;
   int M, N, ldc, ldr, flags; float alpha;
+  int round;  // round C to TF32 (activations / activation gradients); never with ACCUM or FP32_OUT
 };
 
 // ------------------------------------------------------------------ PTX wrappers
@@ -83,7 +84,7 @@ __device__ __forceinline__ float epi_value(float acc, const GemmEpi& e, int row,
   if (e.flags & B200IQ_GEMM_RESIDUAL) v += __ldg(e.residual + (size_t)row * e.ldr + col);
   if (e.flags & B200IQ_GEMM_RELU) v = fmaxf(v, 0.f);
   if (e.flags & B200IQ_GEMM_RELU_MASK) v = (__ldg(e.residual + (size_t)row * e.ldr + col) > 0.f) ? v : 0.f;
-  return v;
+  return rnd(v, e.round);
 }
 
 template <int BN, bool A_MN, bool B_MN, int STAGES>
@@ -311,7 +312,8 @@ extern "C" int b200iq_gemm(const B200iqGemm* p, void* stream) {
   B200IQ_CHECK_ARG(split == 1 || ((f & B200IQ_GEMM_ACCUM) && !(f & (B200IQ_GEMM_RELU | B200IQ_GEMM_RELU_MASK | B200IQ_GEMM_RESIDUAL))),
                    "gemm: split_k>1 needs ACCUM and a linear epilogue");
   B200IQ_CHECK_ARG(p->lda >= (amn ? p->M : p->K) && p->ldb >= (bmn ? p->N : p->K) && p->ldc >= p->N, "gemm: leading dimension too small");
-  GemmEpi e{p->C, p->bias, p->residual, p->M, p->N, p->ldc, p->ldr, f, p->alpha};
+  const int round = (round_mode() && !(f & (B200IQ_GEMM_ACCUM | B200IQ_GEMM_FP32_OUT | B200IQ_GEMM_SIMT))) ? 1 : 0;
+  GemmEpi e{p->C, p->bias, p->residual, p->M, p->N, p->ldc, p->ldr, f, p->alpha, round};
 
   if (f & B200IQ_GEMM_SIMT) {
     long sam = amn ? 1 : p->lda, sak = amn ? p->lda : 1, sbn = bmn ? 1 : p->ldb, sbk = bmn ? p->ldb : 1;

@@ -18,7 +18,7 @@ __global__ void count_nonpad_kernel(const int* __restrict__ t, int n, int pad, f
 // loss_sum += (lse - logit[target]) / count.      replaces: train_iq.py:82-83 (F.cross_entropy, ignore_index=PAD)
 __global__ void __launch_bounds__(256)
 ce_rows_kernel(float* __restrict__ logits, int ld, const int* __restrict__ targets, int V, int pad,
-               const float* __restrict__ count, float coef, float* __restrict__ loss_sum, int cache_row, int write_grad) {
+               const float* __restrict__ count, float coef, float* __restrict__ loss_sum, int cache_row, int write_grad, int rn) {
   extern __shared__ float row_s[];
   __shared__ float red[32];
   const int r = blockIdx.x;
@@ -45,7 +45,7 @@ ce_rows_kernel(float* __restrict__ logits, int ld, const int* __restrict__ targe
     const float k = coef * inv_cnt, inv_s = 1.f / s;
     for (int c = threadIdx.x; c < V; c += blockDim.x) {
       float p = __expf(src[c] - mx) * inv_s;
-      row[c] = k * (p - (c == tgt ? 1.f : 0.f));
+      row[c] = rnd(k * (p - (c == tgt ? 1.f : 0.f)), rn);
     }
   }
 }
@@ -55,7 +55,7 @@ ce_rows_kernel(float* __restrict__ logits, int ld, const int* __restrict__ targe
 // replaces: train_iq.py:92-94
 __global__ void __launch_bounds__(256)
 ce_aux_kernel(const float* __restrict__ zl, float* __restrict__ dz, const int* __restrict__ targets, int T, int V, int pad,
-              const float* __restrict__ count, float coef, float* __restrict__ loss_sum) {
+              const float* __restrict__ count, float coef, float* __restrict__ loss_sum, int rn) {
   __shared__ float red[32];
   const int b = blockIdx.x;
   const float* row = zl + (size_t)b * V;
@@ -82,12 +82,16 @@ ce_aux_kernel(const float* __restrict__ zl, float* __restrict__ dz, const int* _
     int tg = targets[b * T + t];
     if (tg != pad) atomicAdd(drow + tg, -k);
   }
+  if (rn) {
+    __syncthreads();
+    for (int c = threadIdx.x; c < V; c += blockDim.x) drow[c] = tf32_rn(drow[c]);
+  }
 }
 
 // ---------------------------------------------------------------- latent tail
 // replaces: models/transformer_layers.py:43-58 + gaussian_kld :536-540 (mean over batch at :55)
 __global__ void latent_fwd_kernel(const float* __restrict__ prior, const float* __restrict__ post, const float* __restrict__ eps,
-                                  float* __restrict__ z, float* __restrict__ kld_sum, int B, int L) {
+                                  float* __restrict__ z, float* __restrict__ kld_sum, int B, int L, int rn) {
   __shared__ float red[32];
   float acc = 0.f;
   int n = B * L;
@@ -96,11 +100,11 @@ __global__ void latent_fwd_kernel(const float* __restrict__ prior, const float* 
     float mp = prior[b * 2 * L + c], lp = prior[b * 2 * L + L + c];
     if (post) {
       float mq = post[b * 2 * L + c], lq = post[b * 2 * L + L + c];
-      z[i] = eps[i] * expf(0.5f * lq) + mq;
+      z[i] = rnd(eps[i] * expf(0.5f * lq) + mq, rn);
       float dm = mp - mq;
       acc += -0.5f * (1.f + (lq - lp) - dm * dm / expf(lp) - expf(lq) / expf(lp));
     } else {
-      z[i] = eps[i] * expf(0.5f * lp) + mp;
+      z[i] = rnd(eps[i] * expf(0.5f * lp) + mp, rn);
     }
   }
   if (post && kld_sum) {
@@ -111,7 +115,7 @@ __global__ void latent_fwd_kernel(const float* __restrict__ prior, const float* 
 
 __global__ void latent_bwd_kernel(const float* __restrict__ prior, const float* __restrict__ post, const float* __restrict__ eps,
                                   const float* __restrict__ dz, float kld_coef, float* __restrict__ dprior, float* __restrict__ dpost,
-                                  int B, int L) {
+                                  int B, int L, int rn) {
   int n = B * L;
   float kc = kld_coef / B;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
@@ -120,10 +124,10 @@ __global__ void latent_bwd_kernel(const float* __restrict__ prior, const float* 
     float mq = post[b * 2 * L + c], lq = post[b * 2 * L + L + c];
     float g = dz ? dz[i] : 0.f;
     float ivp = expf(-lp), dm = mp - mq, r = expf(lq - lp);
-    dpost[b * 2 * L + c] = g - kc * dm * ivp;
-    dpost[b * 2 * L + L + c] = g * eps[i] * 0.5f * expf(0.5f * lq) - 0.5f * kc * (1.f - r);
-    dprior[b * 2 * L + c] = kc * dm * ivp;
-    dprior[b * 2 * L + L + c] = -0.5f * kc * (-1.f + dm * dm * ivp + r);
+    dpost[b * 2 * L + c] = rnd(g - kc * dm * ivp, rn);
+    dpost[b * 2 * L + L + c] = rnd(g * eps[i] * 0.5f * expf(0.5f * lq) - 0.5f * kc * (1.f - r), rn);
+    dprior[b * 2 * L + c] = rnd(kc * dm * ivp, rn);
+    dprior[b * 2 * L + L + c] = rnd(-0.5f * kc * (-1.f + dm * dm * ivp + r), rn);
   }
 }
 
@@ -170,7 +174,7 @@ bn_fwd_kernel(const float* __restrict__ x, const float* __restrict__ g, const fl
 
 __global__ void __launch_bounds__(1024)
 bn_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ g, const float* __restrict__ save_mean,
-              const float* __restrict__ save_rstd, float* __restrict__ dx, float* __restrict__ dg, float* __restrict__ db, int B, int H) {
+              const float* __restrict__ save_rstd, float* __restrict__ dx, float* __restrict__ dg, float* __restrict__ db, int B, int H, int rn) {
   __shared__ float red1[32][33], red2[32][33];
   int c = blockIdx.x * 32 + threadIdx.x, ty = threadIdx.y;
   float mu = c < H ? save_mean[c] : 0.f, rs = c < H ? save_rstd[c] : 0.f;
@@ -188,7 +192,7 @@ bn_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ x, const f
     float gg = g[c] * rs, m1 = s1 / B, m2 = s2 / B;
     for (int r = ty; r < B; r += 32) {
       float xh = (x[(size_t)r * H + c] - mu) * rs;
-      dx[(size_t)r * H + c] = gg * (dy[(size_t)r * H + c] - m1 - xh * m2);
+      dx[(size_t)r * H + c] = rnd(gg * (dy[(size_t)r * H + c] - m1 - xh * m2), rn);
     }
   }
 }
@@ -196,14 +200,14 @@ bn_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ x, const f
 // ---------------------------------------------------------------- MSE (loss + both gradients)
 // loss_sum += mean((a-b)^2);  da += coef*2(a-b)/n;  db (+)= -coef*2(a-b)/n      replaces: train_iq.py:84 (nn.MSELoss)
 __global__ void mse_kernel(const float* __restrict__ a, const float* __restrict__ b, size_t n, float coef, float* __restrict__ loss_sum,
-                           float* __restrict__ da, float* __restrict__ db, int accumulate_db) {
+                           float* __restrict__ da, float* __restrict__ db, int accumulate_db, int rn) {
   __shared__ float red[32];
   float acc = 0.f, k = 2.f * coef / (float)n;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
     float d = a[i] - b[i];
     acc += d * d;
     if (da) da[i] += k * d;
-    if (db) db[i] = (accumulate_db ? db[i] : 0.f) - k * d;
+    if (db) db[i] = rnd((accumulate_db ? db[i] : 0.f) - k * d, rn);
   }
   acc = block_sum(acc, red);
   if (threadIdx.x == 0 && loss_sum) atomicAdd(loss_sum, acc / (float)n);
@@ -231,27 +235,27 @@ extern "C" int b200iq_ce_rows(float* logits, int ld, const int* targets, int row
     cudaFuncSetAttribute(ce_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     attr = 200 * 1024;
   }
-  ce_rows_kernel<<<rows, 256, smem, ST>>>(logits, ld, targets, V, pad_id, count, coef, loss_sum, cache, write_grad);
+  ce_rows_kernel<<<rows, 256, smem, ST>>>(logits, ld, targets, V, pad_id, count, coef, loss_sum, cache, write_grad, round_mode());
   return launch_status("ce_rows");
 }
 
 extern "C" int b200iq_ce_aux(const float* z_logit, float* dz_logit, const int* targets, int B, int T, int V, int pad_id,
                              const float* count, float coef, float* loss_sum, void* stream) {
   B200IQ_CHECK_ARG(z_logit && dz_logit && targets && count && loss_sum && B > 0 && T > 0 && V > 0, "ce_aux: bad args");
-  ce_aux_kernel<<<B, 256, 0, ST>>>(z_logit, dz_logit, targets, T, V, pad_id, count, coef, loss_sum);
+  ce_aux_kernel<<<B, 256, 0, ST>>>(z_logit, dz_logit, targets, T, V, pad_id, count, coef, loss_sum, round_mode());
   return launch_status("ce_aux");
 }
 
 extern "C" int b200iq_latent_fwd(const float* prior, const float* post, const float* eps, float* z, float* kld_sum, int B, int L, void* stream) {
   B200IQ_CHECK_ARG(prior && eps && z && B > 0 && L > 0, "latent_fwd: bad args");
-  latent_fwd_kernel<<<min(ceil_div(B * L, 256), 148), 256, 0, ST>>>(prior, post, eps, z, kld_sum, B, L);
+  latent_fwd_kernel<<<min(ceil_div(B * L, 256), 148), 256, 0, ST>>>(prior, post, eps, z, kld_sum, B, L, round_mode());
   return launch_status("latent_fwd");
 }
 
 extern "C" int b200iq_latent_bwd(const float* prior, const float* post, const float* eps, const float* dz, float kld_coef,
                                  float* dprior, float* dpost, int B, int L, void* stream) {
   B200IQ_CHECK_ARG(prior && post && eps && dprior && dpost && B > 0 && L > 0, "latent_bwd: bad args");
-  latent_bwd_kernel<<<min(ceil_div(B * L, 256), 148), 256, 0, ST>>>(prior, post, eps, dz, kld_coef, dprior, dpost, B, L);
+  latent_bwd_kernel<<<min(ceil_div(B * L, 256), 148), 256, 0, ST>>>(prior, post, eps, dz, kld_coef, dprior, dpost, B, L, round_mode());
   return launch_status("latent_bwd");
 }
 
@@ -266,13 +270,13 @@ extern "C" int b200iq_bn_fwd(const float* x, const float* gamma, const float* be
 extern "C" int b200iq_bn_bwd(const float* dy, const float* x, const float* gamma, const float* save_mean, const float* save_rstd,
                              float* dx, float* dgamma, float* dbeta, int B, int H, void* stream) {
   B200IQ_CHECK_ARG(dy && x && gamma && save_mean && save_rstd && dx && dgamma && dbeta && B > 0 && H > 0, "bn_bwd: bad args");
-  bn_bwd_kernel<<<ceil_div(H, 32), dim3(32, 32), 0, ST>>>(dy, x, gamma, save_mean, save_rstd, dx, dgamma, dbeta, B, H);
+  bn_bwd_kernel<<<ceil_div(H, 32), dim3(32, 32), 0, ST>>>(dy, x, gamma, save_mean, save_rstd, dx, dgamma, dbeta, B, H, round_mode());
   return launch_status("bn_bwd");
 }
 
 extern "C" int b200iq_mse(const float* a, const float* b, size_t n, float coef, float* loss_sum, float* da, float* db,
                           int accumulate_db, void* stream) {
   B200IQ_CHECK_ARG(a && b && n > 0, "mse: bad args");
-  mse_kernel<<<(int)min((n + 255) / 256, (size_t)296), 256, 0, ST>>>(a, b, n, coef, loss_sum, da, db, accumulate_db);
+  mse_kernel<<<(int)min((n + 255) / 256, (size_t)296), 256, 0, ST>>>(a, b, n, coef, loss_sum, da, db, accumulate_db, round_mode());
   return launch_status("mse");
 }

@@ -92,6 +92,7 @@ class IQ(nn.Module):
         self._ws = {}
         self._gflat = None
         self._terms = None
+        self._wflat = None  # TF32-rounded copy of the arena: the GEMM weight operands
         self._ctx = None
         self.on_grad_ready = None  # set by parallel.GradReducer.begin_step
 
@@ -99,7 +100,7 @@ class IQ(nn.Module):
     def _apply(self, fn, *a, **k):
         super()._apply(fn, *a, **k)
         self.arena.bind(self.flat.data)
-        self._ws, self._gflat, self._terms = {}, None, None
+        self._ws, self._gflat, self._terms, self._wflat = {}, None, None, None
         return self
 
     def _buffers_map(self):
@@ -151,18 +152,28 @@ class IQ(nn.Module):
 
     def _features(self, images):
         if images.dim() == 2:
-            return images.to(self.flat.device, torch.float32, non_blocking=True).contiguous()
+            f = images.to(self.flat.device, torch.float32, non_blocking=True).contiguous()
+            if ops.exact_mode():
+                return f
+            return ops.round_tf32(f, self._workspace("feats").buf("feats", *f.shape))
         if self.trunk is None:
             raise _lib.B200iqError("raw images given but no trunk attached (call attach_trunk, or pass pooled features)")
         with torch.no_grad():
-            return self.trunk(images.to(self.flat.device)).flatten(1).float().contiguous()
+            f = self.trunk(images.to(self.flat.device)).flatten(1).float().contiguous()
+        return f if ops.exact_mode() else ops.round_tf32(f, f)
 
     def _make_ctx(self, B, S, R, T, training):
         _lib.require_device()
         key = (B, S, R, T, bool(self.latent_transformer), bool(training))
         ws = self._workspace(key)
+        wflat = None
+        if not ops.exact_mode():
+            # tcgen05 kind::tf32 truncates its operands: feed it round-to-nearest copies of the master weights
+            if self._wflat is None:
+                self._wflat = torch.empty_like(self.flat.data)
+            wflat = ops.round_tf32(self.flat.data, self._wflat)
         c = tf.Ctx(self.arena, self.grad_arena, ws, self.H, self.nh, self.F, self.E, self.attn_dropout,
-                   self.relu_dropout, training, self.seed + self.step_idx)
+                   self.relu_dropout, training, self.seed + self.step_idx, wflat=wflat)
         c.on_ready = self.on_grad_ready
         return c
 
@@ -174,7 +185,7 @@ class IQ(nn.Module):
         m = ws.meta
         # image head: fc + BatchNorm1d (encoder_cnn.py:33-34)
         img_pre = ws.buf("img_pre", B, H)
-        ops.gemm(feats, P["encoder_cnn.cnn.fc.weight"], img_pre, bias=P["encoder_cnn.cnn.fc.bias"])
+        ops.gemm(feats, c.W["encoder_cnn.cnn.fc.weight"], img_pre, bias=P["encoder_cnn.cnn.fc.bias"], fp32_out=True)
         img = ws.buf("img", B, H)
         ops.bn_fwd(img_pre, P["encoder_cnn.bn.weight"], P["encoder_cnn.bn.bias"], img, ws.buf("bn.mean", H),
                    ws.buf("bn.rstd", H), self.bn_running_mean, self.bn_running_var, c.training)
@@ -206,7 +217,7 @@ class IQ(nn.Module):
             ops.latent_fwd(prior, post, e, zl, self.terms[2:3])
             z = tf.linear_fwd(c, "z", "latent_projection", zl)
             zimg = ops.axpby(z, img, ws.buf("zimg", B, H))
-            m["z_logit"] = tf.linear_fwd(c, "z_logit", "decoder.z_classifier", zimg)
+            m["z_logit"] = tf.linear_fwd(c, "z_logit", "decoder.z_classifier", zimg, fp32_out=True)
         # decoder (decoder_transformer.py:22-38)
         shifted = ws.buf("dec.ids", B, T, dtype=torch.int32)
         shifted[:, 0] = self.sos_id
@@ -219,7 +230,7 @@ class IQ(nn.Module):
         if latent:
             ops.axpby(rin, z, rin)
         rh = tf.linear_fwd(c, "rec.h", "image_reconstructor.layers.fc0", rin, relu=True)
-        recon = tf.linear_fwd(c, "rec.out", "image_reconstructor.layers.fc1", rh)
+        recon = tf.linear_fwd(c, "rec.out", "image_reconstructor.layers.fc1", rh, fp32_out=True)
         m.update(img=img, img_pre=img_pre, enc_out=enc_out, z=z, dec_out=dec_out, shifted=shifted, rin=rin, rh=rh,
                  recon=recon, feats=feats, cids=cids, rids=rids, tids=tids)
         return dec_out
@@ -312,11 +323,11 @@ class IQ(nn.Module):
         d_dec = ws.buf("d_dec_out", M, H)
         chunk = self._ce_chunk_rows(M)
         logits = ws.buf("logits_chunk", chunk, V)
-        wout, bout = P["decoder.output.weight"], P["decoder.output.bias"]
+        wout, bout = c.W["decoder.output.weight"], P["decoder.output.bias"]
         for r0 in range(0, M, chunk):
             rows = min(chunk, M - r0)
             lg, xs = logits[:rows], dec_out[r0:r0 + rows]
-            ops.gemm(xs, wout, lg, bias=bout)                      # decoder_transformer.py:40
+            ops.gemm(xs, wout, lg, bias=bout, fp32_out=True)       # decoder_transformer.py:40
             ops.ce_rows(lg, tflat[r0:r0 + rows], PAD, count, c_rec, terms[0:1], write_grad=backward)
             if backward:
                 ops.gemm(lg, wout, d_dec[r0:r0 + rows], b_t=True)
@@ -365,7 +376,7 @@ class IQ(nn.Module):
         dec_out = self._run_forward(c, feats, cids, rids, tids, eps)
         m = c.ws.meta
         output = torch.empty(B * T, self.V, device=feats.device)
-        ops.gemm(dec_out, c.P["decoder.output.weight"], output, bias=c.P["decoder.output.bias"])
+        ops.gemm(dec_out, c.W["decoder.output.weight"], output, bias=c.P["decoder.output.bias"], fp32_out=True)
         if self.latent_transformer:
             z_logit, kld = m["z_logit"].clone(), self.terms[2].clone()
         else:
@@ -382,7 +393,9 @@ class IQ(nn.Module):
         d_dec = ws.buf("d_dec_out", B * T, H)
         if d_output is not None:
             dout = d_output.reshape(B * T, self.V).contiguous()
-            ops.gemm(dout, c.P["decoder.output.weight"], d_dec, b_t=True)
+            if not ops.exact_mode():
+                dout = ops.round_tf32(dout, torch.empty_like(dout))
+            ops.gemm(dout, c.W["decoder.output.weight"], d_dec, b_t=True)
             tf.grad_w(c, dout, m["dec_out"], c.G["decoder.output.weight"], c.G["decoder.output.bias"])
         else:
             d_dec.zero_()
@@ -395,13 +408,18 @@ class IQ(nn.Module):
         if self.latent_transformer:
             d_z = ws.buf("d_zimg", B, H)
             if d_z_logit is not None:
-                tf.linear_bwd(c, "d_zimg", "decoder.z_classifier", d_z_logit.contiguous(), ws["zimg"], dx=d_z)
+                dzl = d_z_logit.contiguous()
+                if not ops.exact_mode():
+                    dzl = ops.round_tf32(dzl, torch.empty_like(dzl))
+                tf.linear_bwd(c, "d_zimg", "decoder.z_classifier", dzl, ws["zimg"], dx=d_z)
                 ops.axpby(d_img, d_z, d_img)
             else:
                 d_z.zero_()
         d_recon = ws.buf("d_recon", B, H)
         if d_recon_in is not None:
             d_recon.copy_(d_recon_in)
+            if not ops.exact_mode():
+                ops.round_tf32(d_recon, d_recon)
         else:
             d_recon.zero_()
         kld_coef = float(d_kld) if (d_kld is not None and self.latent_transformer) else 0.0

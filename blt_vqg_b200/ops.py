@@ -19,8 +19,14 @@ LAUNCHES = 0
 GEMM_TRACE = None
 
 
+def exact_mode():
+    """True when the library is in exact-fp32 mode (CUDA-core GEMMs, no TF32 rounding)"""
+    return _FORCE_SIMT
+
+
 class gemm_mode:
-    """context manager: `with gemm_mode(simt=True): ...` forces the exact-fp32 GEMM path"""
+    """context manager: `with gemm_mode(simt=True): ...` runs everything in exact fp32 — CUDA-core GEMMs and no TF32
+    rounding of activations (b200iq_set_tf32_rounding(0)); simt=False is the tensor-core path"""
 
     def __init__(self, simt):
         self.simt = simt
@@ -29,10 +35,12 @@ class gemm_mode:
         global _FORCE_SIMT
         self.prev = _FORCE_SIMT
         _FORCE_SIMT = self.simt
+        L.lib().b200iq_set_tf32_rounding(0 if self.simt else 1)
 
     def __exit__(self, *a):
         global _FORCE_SIMT
         _FORCE_SIMT = self.prev
+        L.lib().b200iq_set_tf32_rounding(0 if self.prev else 1)
 
 
 def _ld(t):
@@ -41,7 +49,7 @@ def _ld(t):
 
 
 def gemm(a, b, out=None, *, a_t=False, b_t=False, bias=None, residual=None, relu=False, relu_mask=None,
-         accumulate=False, split_k=1, alpha=1.0, simt=None):
+         accumulate=False, split_k=1, alpha=1.0, simt=None, fp32_out=False):
     """out[M,N] = epi(alpha * A @ B^T); a is [M,K] ([K,M] if a_t), b is [N,K] ([K,N] if b_t).
     mirrors torch.nn.functional.linear(a, b, bias) (+ fused relu / residual / relu-backward mask)."""
     M, K = (a.shape[1], a.shape[0]) if a_t else a.shape
@@ -61,6 +69,7 @@ def gemm(a, b, out=None, *, a_t=False, b_t=False, bias=None, residual=None, relu
         flags |= L.GEMM_RELU_MASK
         residual = relu_mask
     if accumulate: flags |= L.GEMM_ACCUM
+    if fp32_out: flags |= L.GEMM_FP32_OUT
     if simt if simt is not None else _FORCE_SIMT: flags |= L.GEMM_SIMT
     p = L.GemmParams(L.fptr(a), L.fptr(b), L.fptr(out), L.fptr(bias), L.fptr(residual), M, N, K,
                      _ld(a), _ld(b), _ld(out), _ld(residual) if residual is not None else 0,
@@ -156,6 +165,12 @@ def dropout_(x, p, seed, offset):
 def randn_(out, seed, offset=0):
     _call("b200iq_randn", _p(out), C.c_size_t(out.numel()), C.c_uint64(seed), C.c_uint64(offset))
     return out
+
+
+def round_tf32(src, dst):
+    """dst = nearest-TF32(src) (no-op copy in exact mode is NOT done here: callers skip it)"""
+    _call("b200iq_round_tf32", _p(src), _p(dst), C.c_size_t(src.numel()))
+    return dst
 
 
 def axpby(x, y, out, a=1.0, b=1.0):

@@ -37,9 +37,12 @@ class Workspace:
 class Ctx:
     """everything a block schedule needs: parameter / gradient views, workspace, sizes, dropout keys"""
 
-    def __init__(self, arena, gflat, ws, H, nh, F, E, attn_drop, relu_drop, training, seed):
+    def __init__(self, arena, gflat, ws, H, nh, F, E, attn_drop, relu_drop, training, seed, wflat=None):
         self.arena, self.ws = arena, ws
-        self.P = arena.views
+        self.P = arena.views      # fp32 masters: biases, LayerNorm / BatchNorm affine, embedding table
+        # GEMM weight operands: the TF32-rounded copy of the arena (the masters themselves in exact mode)
+        self.wflat = wflat if wflat is not None else arena.flat.detach()
+        self.W = {n: arena.view_of(self.wflat, n) for n in arena.names()} if wflat is not None else arena.views
         self.gflat = gflat
         self.G = {n: arena.view_of(gflat, n) for n in arena.names()} if gflat is not None else None
         self.H, self.nh, self.F, self.E, self.d = H, nh, F, E, H // nh
@@ -57,7 +60,7 @@ class Ctx:
 
     def pspan(self, first, last, cols):
         o0, o1 = self.arena.span(first, last)
-        return self.arena.flat.detach()[o0:o1].view(-1, cols)
+        return self.wflat[o0:o1].view(-1, cols)
 
     def gspan(self, first, last, cols):
         o0, o1 = self.arena.span(first, last)
@@ -105,7 +108,7 @@ def embed_fwd(c, tag, ids, B, n, timing, add0=None, add1=None):
     e = c.ws.buf(tag + ".e", M, c.E)
     ops.embed_gather(ids, c.P["embedding.0.weight"], e)
     x = c.ws.buf(tag + ".x0", M, c.H)
-    ops.gemm(e, c.P["embedding.1.weight"], x, bias=c.P["embedding.1.bias"])
+    ops.gemm(e, c.W["embedding.1.weight"], x, bias=c.P["embedding.1.bias"])
     ops.add_timing(x, timing, add0, add1, B, n, c.H)
     return x
 
@@ -114,7 +117,7 @@ def embed_bwd(c, tag, ids, dx):
     e = c.ws[tag + ".e"]
     grad_w(c, dx, e, c.G["embedding.1.weight"], c.G["embedding.1.bias"])
     de = c.ws.buf("tmp.de.%d" % dx.shape[0], dx.shape[0], c.E)
-    ops.gemm(dx, c.P["embedding.1.weight"], de, b_t=True)
+    ops.gemm(dx, c.W["embedding.1.weight"], de, b_t=True)
     ops.embed_scatter_add(ids, de, c.G["embedding.0.weight"], PAD)
 
 
@@ -129,7 +132,7 @@ def self_attn_fwd(c, tag, pfx, xn, x_res, ids, B, n, causal):
     ops.attention_fwd(qkv[:, :H], qkv[:, H:2 * H], qkv[:, 2 * H:], ctx, ids, PAD, causal, B, c.nh, n, n, c.d,
                       c.attn_drop, seed, off)
     out = c.ws.buf(tag + ".out", M, H)
-    ops.gemm(ctx, c.P[pfx + "output_linear.weight"], out, residual=x_res)
+    ops.gemm(ctx, c.W[pfx + "output_linear.weight"], out, residual=x_res)
     return out
 
 
@@ -138,7 +141,7 @@ def self_attn_bwd(c, tag, pfx, dout, xn, ids, B, n, causal):
     qkv, ctx = c.ws[tag + ".qkv"], c.ws[tag + ".ctx"]
     grad_w(c, dout, ctx, c.G[pfx + "output_linear.weight"])
     dctx = c.ws.buf("tmp.dctx.%d" % M, M, H)
-    ops.gemm(dout, c.P[pfx + "output_linear.weight"], dctx, b_t=True)
+    ops.gemm(dout, c.W[pfx + "output_linear.weight"], dctx, b_t=True)
     dqkv = c.ws.buf("tmp.dqkv.%d" % M, M, 3 * H)
     seed, off = c.key(tag + ".adrop")
     ops.attention_bwd(qkv[:, :H], qkv[:, H:2 * H], qkv[:, 2 * H:], dctx, dqkv[:, :H], dqkv[:, H:2 * H], dqkv[:, 2 * H:],
@@ -152,14 +155,14 @@ def self_attn_bwd(c, tag, pfx, dout, xn, ids, B, n, causal):
 def cross_attn_fwd(c, tag, pfx, xn, x_res, enc_out, enc_ids, B, nq, nk):
     M, H = xn.shape
     q = c.ws.buf(tag + ".q", M, H)
-    ops.gemm(xn, c.P[pfx + "query_linear.weight"], q)
+    ops.gemm(xn, c.W[pfx + "query_linear.weight"], q)
     kv = c.ws.buf(tag + ".kv", enc_out.shape[0], 2 * H)
     ops.gemm(enc_out, c.pspan(pfx + "key_linear.weight", pfx + "value_linear.weight", H), kv)
     ctx = c.ws.buf(tag + ".ctx", M, H)
     seed, off = c.key(tag + ".adrop")
     ops.attention_fwd(q, kv[:, :H], kv[:, H:], ctx, enc_ids, PAD, False, B, c.nh, nq, nk, c.d, c.attn_drop, seed, off)
     out = c.ws.buf(tag + ".out", M, H)
-    ops.gemm(ctx, c.P[pfx + "output_linear.weight"], out, residual=x_res)
+    ops.gemm(ctx, c.W[pfx + "output_linear.weight"], out, residual=x_res)
     return out
 
 
@@ -169,7 +172,7 @@ def cross_attn_bwd(c, tag, pfx, dout, xn, enc_out, d_enc_out, first, enc_ids, B,
     q, kv, ctx = c.ws[tag + ".q"], c.ws[tag + ".kv"], c.ws[tag + ".ctx"]
     grad_w(c, dout, ctx, c.G[pfx + "output_linear.weight"])
     dctx = c.ws.buf("tmp.dctx.%d" % M, M, H)
-    ops.gemm(dout, c.P[pfx + "output_linear.weight"], dctx, b_t=True)
+    ops.gemm(dout, c.W[pfx + "output_linear.weight"], dctx, b_t=True)
     dq = c.ws.buf("tmp.dq.%d" % M, M, H)
     dkv = c.ws.buf("tmp.dkv.%d" % Me, Me, 2 * H)
     seed, off = c.key(tag + ".adrop")
@@ -180,7 +183,7 @@ def cross_attn_bwd(c, tag, pfx, dout, xn, enc_out, d_enc_out, first, enc_ids, B,
     wkv = c.pspan(pfx + "key_linear.weight", pfx + "value_linear.weight", H)
     ops.gemm(dkv, wkv, d_enc_out, b_t=True, residual=None if first else d_enc_out)
     dxn = c.ws.buf("tmp.dxn.%d" % M, M, H)
-    ops.gemm(dq, c.P[pfx + "query_linear.weight"], dxn, b_t=True)
+    ops.gemm(dq, c.W[pfx + "query_linear.weight"], dxn, b_t=True)
     return dxn
 
 
@@ -188,10 +191,10 @@ def cross_attn_bwd(c, tag, pfx, dout, xn, enc_out, d_enc_out, first, enc_ids, B,
 def ffn_fwd(c, tag, pfx, xn, x_res):
     M, H = xn.shape
     h = c.ws.buf(tag + ".h", M, c.F)
-    ops.gemm(xn, c.P[pfx + "layers.0.weight"], h, bias=c.P[pfx + "layers.0.bias"], relu=True)
+    ops.gemm(xn, c.W[pfx + "layers.0.weight"], h, bias=c.P[pfx + "layers.0.bias"], relu=True)
     ops.dropout_(h, c.relu_drop, *c.key(tag + ".d1"))
     f2 = c.ws.buf(tag + ".f2", M, H)
-    ops.gemm(h, c.P[pfx + "layers.1.weight"], f2, bias=c.P[pfx + "layers.1.bias"], relu=True)
+    ops.gemm(h, c.W[pfx + "layers.1.weight"], f2, bias=c.P[pfx + "layers.1.bias"], relu=True)
     ops.dropout_(f2, c.relu_drop, *c.key(tag + ".d2"))
     out = c.ws.buf(tag + ".out", M, H)
     ops.axpby(x_res, f2, out)
@@ -211,11 +214,11 @@ def ffn_bwd(c, tag, pfx, dout, xn):
     ops.relu_bwd_colsum(df2, f2, dpre2, c.G[pfx + "layers.1.bias"])
     grad_w(c, dpre2, h, c.G[pfx + "layers.1.weight"])
     dh = c.ws.buf("tmp.dh.%d" % M, M, c.F)
-    ops.gemm(dpre2, c.P[pfx + "layers.1.weight"], dh, b_t=True, relu_mask=h)
+    ops.gemm(dpre2, c.W[pfx + "layers.1.weight"], dh, b_t=True, relu_mask=h)
     ops.dropout_(dh, c.relu_drop, *c.key(tag + ".d1"))
     grad_w(c, dh, xn, c.G[pfx + "layers.0.weight"], c.G[pfx + "layers.0.bias"])
     dxn = c.ws.buf("tmp.dxn.%d" % M, M, H)
-    ops.gemm(dh, c.P[pfx + "layers.0.weight"], dxn, b_t=True)
+    ops.gemm(dh, c.W[pfx + "layers.0.weight"], dxn, b_t=True)
     return dxn
 
 
@@ -286,9 +289,9 @@ def decoder_bwd(c, tag, pfx, dy, ids, enc_out, d_enc_out, enc_ids, B, T, S, NL):
 
 
 # ------------------------------------------------------------------ small MLPs
-def linear_fwd(c, tag, pfx, x, relu=False, out=None):
-    y = out if out is not None else c.ws.buf(tag, x.shape[0], c.P[pfx + ".weight"].shape[0])
-    ops.gemm(x, c.P[pfx + ".weight"], y, bias=c.P[pfx + ".bias"], relu=relu)
+def linear_fwd(c, tag, pfx, x, relu=False, out=None, fp32_out=False):
+    y = out if out is not None else c.ws.buf(tag, x.shape[0], c.W[pfx + ".weight"].shape[0])
+    ops.gemm(x, c.W[pfx + ".weight"], y, bias=c.P[pfx + ".bias"], relu=relu, fp32_out=fp32_out)
     return y
 
 
@@ -298,7 +301,7 @@ def linear_bwd(c, tag, pfx, dy, x, relu_mask=None, need_dx=True, dx=None, accumu
     if not need_dx:
         return None
     if dx is None:
-        dx = c.ws.buf(tag, dy.shape[0], c.P[pfx + ".weight"].shape[1])
+        dx = c.ws.buf(tag, dy.shape[0], c.W[pfx + ".weight"].shape[1])
     assert not (accumulate_dx and relu_mask is not None)
-    ops.gemm(dy, c.P[pfx + ".weight"], dx, b_t=True, relu_mask=relu_mask, residual=dx if accumulate_dx else None)
+    ops.gemm(dy, c.W[pfx + ".weight"], dx, b_t=True, relu_mask=relu_mask, residual=dx if accumulate_dx else None)
     return dx

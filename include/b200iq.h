@@ -28,6 +28,11 @@ int b200iq_abi_version(void);
 /* 1 when the current device is compute capability 10.0, else 0 */
 int b200iq_device_supported(void);
 const char* b200iq_last_error(void);
+/* Numerics mode of the whole library (default 1).  1: the tensor-core path — every activation / gradient tensor a
+ * kernel writes is rounded to the nearest TF32 value, because tcgen05.mma kind::tf32 truncates its fp32 operands and
+ * truncation biases every dot product towards zero.  0: nothing is rounded (use with B200IQ_GEMM_SIMT for an exact
+ * fp32 run, e.g. the bit-exact greedy decode).  Returns the previous mode. */
+int b200iq_set_tf32_rounding(int on);
 
 /* ------------------------------------------------------------------ GEMM */
 /* flags for B200iqGemm.flags */
@@ -39,6 +44,7 @@ const char* b200iq_last_error(void);
 #define B200IQ_GEMM_ACCUM     32  /* C += result (atomic; required when split_k > 1) */
 #define B200IQ_GEMM_SIMT      64  /* exact-fp32 CUDA-core path instead of tcgen05 TF32 */
 #define B200IQ_GEMM_RELU_MASK 128 /* multiply result by (gate[M,N] > 0): relu backward fused */
+#define B200IQ_GEMM_FP32_OUT  256 /* keep the full fp32 result (logits, returned tensors): no TF32 rounding of C */
 
 typedef struct B200iqGemm {
   const float* A;        /* [M,K] ld=lda, or [K,M] when A_MN */
@@ -94,6 +100,8 @@ int b200iq_dropout(float* x, size_t n, float p, uint64_t seed, uint64_t offset, 
 int b200iq_randn(float* out, size_t n, uint64_t seed, uint64_t offset, void* stream);
 /* out = a*x + b*y (out may alias x or y): residual adds that cannot ride a GEMM epilogue */
 int b200iq_axpby(const float* x, const float* y, float* out, size_t n, float a, float b, void* stream);
+/* dst = round_to_nearest_tf32(src): the GEMM-operand copy of the fp32 master weights / of user inputs */
+int b200iq_round_tf32(const float* src, float* dst, size_t n, void* stream);
 
 /* ---------------------------------------------------------- fused attention (n <= 128) */
 typedef struct B200iqAttention {

@@ -6,9 +6,11 @@ pytestmark = pytest.mark.gpu
 
 
 @pytest.fixture(scope="module")
-def ops(built_lib):
+def ops(built_lib, request):
     from blt_vqg_b200 import _lib, ops as o
     _lib.require_device()
+    prev = _lib.lib().b200iq_set_tf32_rounding(0)  # kernels are checked in exact mode; rounding has its own test
+    request.addfinalizer(lambda: _lib.lib().b200iq_set_tf32_rounding(prev))
     torch.manual_seed(0)
     return o
 
@@ -126,3 +128,34 @@ def test_philox_randn_and_dropout(ops):
     g = torch.ones(n, device="cuda")
     ops.dropout_(g, 0.1, 7, 1 << 40)
     assert torch.equal(g, x)  # backward re-creates the same mask
+
+
+def test_tf32_rounding_mode(ops):
+    """b200iq_set_tf32_rounding(1): producers write round-to-nearest TF32 values, so the tensor core's operand truncation
+    is a no-op and GEMM results are unbiased; with truncation alone every dot product shrinks by ~7e-4."""
+    from blt_vqg_b200 import _lib
+    x = torch.rand(1 << 16, device="cuda") + 0.5
+    r = ops.round_tf32(x, torch.empty_like(x))
+    assert float((r.view(torch.int32) & 0x1FFF).abs().max()) == 0           # low 13 mantissa bits cleared
+    assert float(((r - x) / x).abs().max()) <= 2.0 ** -11 + 1e-9            # nearest, not truncated
+    assert abs(float(((r - x) / x).mean())) < 2e-5                          # unbiased
+    A, B = torch.rand(512, 1024, device="cuda") + 0.5, torch.rand(256, 1024, device="cuda") + 0.5
+    ref = A.double() @ B.double().t()
+    trunc = ops.gemm(A, B, simt=False)
+    bias_trunc = float(((trunc.double() - ref) / ref).mean())
+    Ar, Br = ops.round_tf32(A, torch.empty_like(A)), ops.round_tf32(B, torch.empty_like(B))
+    rn = ops.gemm(Ar, Br, simt=False)
+    bias_rn = float(((rn.double() - ref) / ref).mean())
+    assert bias_trunc < -3e-4 and abs(bias_rn) < 3e-5, (bias_trunc, bias_rn)
+    _lib.lib().b200iq_set_tf32_rounding(1)
+    try:
+        y = torch.empty(64, 96, device="cuda")
+        xin = torch.randn(64, 96, device="cuda")
+        ops.layernorm_fwd(xin, torch.ones(96, device="cuda"), torch.zeros(96, device="cuda"), y, torch.empty(64, device="cuda"), torch.empty(64, device="cuda"))
+        assert float((y.view(torch.int32) & 0x1FFF).abs().max()) == 0
+        out = ops.gemm(Ar, Br, simt=False)
+        assert float((out.view(torch.int32) & 0x1FFF).abs().max()) == 0
+        out = ops.gemm(Ar, Br, simt=False, fp32_out=True)
+        assert float((out.view(torch.int32) & 0x1FFF).abs().max()) != 0
+    finally:
+        _lib.lib().b200iq_set_tf32_rounding(0)
