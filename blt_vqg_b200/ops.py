@@ -246,3 +246,20 @@ def grad_sumsq(grad, out):
 def adam_step(param, grad, m, v, hyper, normsq, beta1=0.9, beta2=0.999, eps=1e-8, max_norm=5.0, zero_grad=True):
     _call("b200iq_adam_step", _p(param), _p(grad), _p(m), _p(v), C.c_size_t(param.numel()), _p(hyper), _p(normsq),
           _f(beta1), _f(beta2), _f(eps), _f(max_norm), int(zero_grad))
+
+
+# ------------------------------------------------------------------ LSTM recurrence
+def lstm_cell_fwd(gates, c_prev, h_prev, c_next, h_next, lengths, t):
+    B, H = c_prev.shape
+    _call("b200iq_lstm_cell_fwd", _p(gates), _p(c_prev), _p(h_prev), _p(c_next), _p(h_next), _p(lengths), int(t), B, H)
+
+
+def lstm_cell_bwd(gates, c_prev, c_t, dh_run, dh_out, dc, dgates, lengths, t):
+    B, H = c_prev.shape
+    _call("b200iq_lstm_cell_bwd", _p(gates), _p(c_prev), _p(c_t), _p(dh_run), _p(dh_out), _p(dc), _p(dgates), _p(lengths), int(t), B, H)
+
+
+def transpose_ids(ids, out, col0, T_out):
+    B, T_in = ids.shape
+    _call("b200iq_transpose_ids", _p(ids), _p(out), B, T_in, int(T_out), int(col0))
+    return out

@@ -53,6 +53,16 @@ CONFIGS = {
 }
 
 
+# LSTM variant (upstream IQ lineage; SURVEY.md §8d config mapping): H hidden, Z latent, A = att_ff width of the MLPs
+LSTM_CONFIGS = {
+    "tiny": dict(B=6, V=120, H=32, Z=12, A=40, T=8, S=5, FEAT=48),
+    "small": dict(B=24, V=1000, H=128, Z=32, A=96, T=12, S=5, FEAT=256),
+    "cfg1": dict(B=32, V=5000, H=512, Z=100, A=512, T=20, S=5, FEAT=2048),     # BASELINE.json configs[0]
+    "cfg2": dict(B=256, V=15000, H=300, Z=100, A=512, T=20, S=5, FEAT=2048),   # configs[1]: GloVe-300 => H=300
+    "cfg4": dict(B=512, V=15000, H=512, Z=100, A=512, T=20, S=5, FEAT=2048),   # configs[3] per-GPU shard
+}
+
+
 def args_for(cfg, **kw):
     return make_args(emb_dim=cfg["E"], hidden_dim=cfg["H"], latent_dim=cfg["L"], pwffn_dim=cfg["F"],
                      num_layers=cfg["NL"], num_heads=cfg["NH"], feat_dim=cfg["FEAT"], **kw)
@@ -94,4 +104,5 @@ def make_batch(cfg, seed=1234, rank=0, B=None):
         "feats": torch.from_numpy(feats), "questions": torch.from_numpy(questions),
         "posteriors": torch.from_numpy(posteriors), "answers": torch.from_numpy(answers),
         "answer_types_for_input": torch.from_numpy(atypes), "qlen": torch.from_numpy(qlen),
+        "alengths": torch.from_numpy((answers != PAD).sum(1)),  # utils/train_utils.py:127-141 process_lengths
     }

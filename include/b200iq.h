@@ -149,6 +149,21 @@ int b200iq_bn_bwd(const float* dy, const float* x, const float* gamma, const flo
 /* loss_sum += mean((a-b)^2); da += coef*2(a-b)/n; db (+)= -coef*2(a-b)/n (da/db/loss_sum may be NULL)   replaces: train_iq.py:84 */
 int b200iq_mse(const float* a, const float* b, size_t n, float coef, float* loss_sum, float* da, float* db, int accumulate_db, void* stream);
 
+/* ---------------------------------------------------------- LSTM recurrence (time-major, gate order i|f|g|o) */
+/* One step of nn.LSTM: `gates` [B,4H] holds the pre-activations h_{t-1}.W_hh^T + x_t.W_ih^T + b (written by b200iq_gemm with
+ * the residual epilogue) and is overwritten with the activated gates (kept for the backward pass); c_next = f*c_prev + i*g,
+ * h_next = o*tanh(c_next).  lengths (or NULL): rows with t >= lengths[b] copy their state (packed-sequence semantics).
+ * replaces: models/decoder_rnn.py:105 / models/encoder_rnn.py:80-86 (cuDNN LSTM forward) */
+int b200iq_lstm_cell_fwd(float* gates, const float* c_prev, const float* h_prev, float* c_next, float* h_next,
+                         const int* lengths, int t, int B, int H, void* stream);
+/* Backward of one step: dgates [B,4H] = pre-activation gradients; dc updated in place to d/dc_{t-1}; dh_run (d/dh_t from the
+ * future) is left holding only the pass-through of masked rows so that  dh_run = dgates.W_hh + dh_run  (b200iq_gemm) is
+ * d/dh_{t-1}.  dh_out: gradient from the consumers of h_t, or NULL. */
+int b200iq_lstm_cell_bwd(const float* gates, const float* c_prev, const float* c_t, float* dh_run, const float* dh_out,
+                         float* dc, float* dgates, const int* lengths, int t, int B, int H, void* stream);
+/* out[t*B+b] = in[b*T_in + col0 + t], t < T_out: batch-major token ids -> time-major (inputs[:, :-1] of decoder_rnn.py:141) */
+int b200iq_transpose_ids(const int* in, int* out, int B, int T_in, int T_out, int col0, void* stream);
+
 /* ---------------------------------------------------------- optimizer */
 /* out[0] = sum(grad^2) over the flat gradient arena */
 int b200iq_grad_sumsq(const float* grad, size_t n, float* out, void* stream);
