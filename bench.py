@@ -158,8 +158,9 @@ def build_ours(args, cfg, dp):
     else:
         from blt_vqg_b200.lstm_iq import LSTMIQ
         model = LSTMIQ.from_config(cfg).cuda().train()
-    ts = TrainStep(model, dp=dp)
-    ts.iter = 4000  # Noam LR at its peak (lr(0) would be 0: train_iq.py:252-257)
+    # transformer: Noam schedule (train_iq.py:252-257) at its peak; LSTM: constant Adam lr (old_train_iq.py:358-359)
+    ts = TrainStep(model, dp=dp, lr_fn=None if args.workload == "transformer" else (lambda s: 1e-4))
+    ts.iter = 4000
     return model, ts
 
 

@@ -213,9 +213,85 @@ __global__ void mse_kernel(const float* __restrict__ a, const float* __restrict_
   if (threadIdx.x == 0 && loss_sum) atomicAdd(loss_sum, acc / (float)n);
 }
 
+// ---------------------------------------------------------------- decode-time helpers
+// rows of logits -> log-probabilities in place.   replaces: F.log_softmax at models/decoder_rnn.py:107
+__global__ void __launch_bounds__(256) log_softmax_rows_kernel(float* __restrict__ x, int ld, int V) {
+  __shared__ float red[32];
+  float* row = x + (size_t)blockIdx.x * ld;
+  float mx = -3.0e38f;
+  for (int c = threadIdx.x; c < V; c += blockDim.x) mx = fmaxf(mx, row[c]);
+  mx = block_max(mx, red);
+  float s = 0.f;
+  for (int c = threadIdx.x; c < V; c += blockDim.x) s += expf(row[c] - mx);
+  s = block_sum(s, red);
+  const float lse = mx + logf(s);
+  for (int c = threadIdx.x; c < V; c += blockDim.x) row[c] -= lse;
+}
+
+// per row: the K largest logits (ties -> lowest index, like torch.max / torch.topk on distinct values) and their softmax
+// probabilities.   replaces: torch.max + torch.topk(softmax(...), 6) at models/iq.py:136-137 and topk(1) at decoder_rnn.py:124
+template <int K>
+__global__ void __launch_bounds__(256) topk_softmax_rows_kernel(const float* __restrict__ x, int ld, int V, int* __restrict__ idx_out,
+                                                                float* __restrict__ val_out) {
+  __shared__ float red[32];
+  __shared__ float sv[8];
+  __shared__ int si[8];
+  __shared__ float bv[32];
+  __shared__ int bi[32];
+  const float* row = x + (size_t)blockIdx.x * ld;
+  float mx = -3.0e38f;
+  for (int c = threadIdx.x; c < V; c += blockDim.x) mx = fmaxf(mx, row[c]);
+  mx = block_max(mx, red);
+  float s = 0.f;
+  for (int c = threadIdx.x; c < V; c += blockDim.x) s += expf(row[c] - mx);
+  s = block_sum(s, red);
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  for (int k = 0; k < K; ++k) {
+    float best = -3.0e38f;
+    int besti = 0x7fffffff;
+    for (int c = threadIdx.x; c < V; c += blockDim.x) {
+      float v = row[c];
+      bool taken = false;
+      for (int j = 0; j < k; ++j) taken |= (si[j] == c);
+      if (!taken && (v > best || (v == best && c < besti))) { best = v; besti = c; }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      float ov = __shfl_xor_sync(0xffffffffu, best, o);
+      int oi = __shfl_xor_sync(0xffffffffu, besti, o);
+      if (ov > best || (ov == best && oi < besti)) { best = ov; besti = oi; }
+    }
+    if (lane == 0) { bv[w] = best; bi[w] = besti; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      for (int j = 1; j < nw; ++j)
+        if (bv[j] > bv[0] || (bv[j] == bv[0] && bi[j] < bi[0])) { bv[0] = bv[j]; bi[0] = bi[j]; }
+      sv[k] = bv[0]; si[k] = bi[0];
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x < K) {
+    idx_out[(size_t)blockIdx.x * K + threadIdx.x] = si[threadIdx.x];
+    if (val_out) val_out[(size_t)blockIdx.x * K + threadIdx.x] = expf(sv[threadIdx.x] - mx) / s;
+  }
+}
+
 }  // namespace b200iq
 using namespace b200iq;
 #define ST ((cudaStream_t)stream)
+
+extern "C" int b200iq_log_softmax_rows(float* x, int ld, int rows, int V, void* stream) {
+  B200IQ_CHECK_ARG(x && rows > 0 && V > 0 && ld >= V, "log_softmax_rows: bad args");
+  log_softmax_rows_kernel<<<rows, 256, 0, ST>>>(x, ld, V);
+  return launch_status("log_softmax_rows");
+}
+
+extern "C" int b200iq_topk_softmax_rows(const float* x, int ld, int rows, int V, int k, int* idx_out, float* val_out, void* stream) {
+  B200IQ_CHECK_ARG(x && idx_out && rows > 0 && V > 0 && ld >= V && (k == 1 || k == 6) && V >= k, "topk_softmax_rows: bad args (k must be 1 or 6)");
+  if (k == 1) topk_softmax_rows_kernel<1><<<rows, 256, 0, ST>>>(x, ld, V, idx_out, val_out);
+  else topk_softmax_rows_kernel<6><<<rows, 256, 0, ST>>>(x, ld, V, idx_out, val_out);
+  return launch_status("topk_softmax_rows");
+}
 
 extern "C" int b200iq_count_nonpad(const int* targets, int n, int pad_id, float* count, void* stream) {
   B200IQ_CHECK_ARG(targets && count && n > 0, "count_nonpad: bad args");

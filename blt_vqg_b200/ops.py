@@ -263,3 +263,15 @@ def transpose_ids(ids, out, col0, T_out):
     B, T_in = ids.shape
     _call("b200iq_transpose_ids", _p(ids), _p(out), B, T_in, int(T_out), int(col0))
     return out
+
+
+# ------------------------------------------------------------------ decode-time helpers
+def log_softmax_rows_(x):
+    rows, V = x.shape
+    _call("b200iq_log_softmax_rows", _p(x), x.stride(0), rows, V)
+    return x
+
+
+def topk_softmax_rows(x, k, idx_out, val_out=None):
+    rows, V = x.shape
+    _call("b200iq_topk_softmax_rows", _p(x), x.stride(0), rows, V, int(k), _p(idx_out), _p(val_out))

@@ -149,6 +149,13 @@ int b200iq_bn_bwd(const float* dy, const float* x, const float* gamma, const flo
 /* loss_sum += mean((a-b)^2); da += coef*2(a-b)/n; db (+)= -coef*2(a-b)/n (da/db/loss_sum may be NULL)   replaces: train_iq.py:84 */
 int b200iq_mse(const float* a, const float* b, size_t n, float coef, float* loss_sum, float* da, float* db, int accumulate_db, void* stream);
 
+/* ---------------------------------------------------------- decode-time helpers */
+/* x[r,:] -= logsumexp(x[r,:])   replaces: F.log_softmax at models/decoder_rnn.py:107 */
+int b200iq_log_softmax_rows(float* x, int ld, int rows, int V, void* stream);
+/* per row the k (1 or 6) largest logits, ties to the lowest index; val_out (or NULL) = their softmax probabilities
+ * replaces: torch.max + torch.topk(softmax, 6) at models/iq.py:136-137; topk(1) at models/decoder_rnn.py:124 */
+int b200iq_topk_softmax_rows(const float* x, int ld, int rows, int V, int k, int* idx_out, float* val_out, void* stream);
+
 /* ---------------------------------------------------------- LSTM recurrence (time-major, gate order i|f|g|o) */
 /* One step of nn.LSTM: `gates` [B,4H] holds the pre-activations h_{t-1}.W_hh^T + x_t.W_ih^T + b (written by b200iq_gemm with
  * the residual epilogue) and is overwritten with the activated gates (kept for the backward pass); c_next = f*c_prev + i*g,

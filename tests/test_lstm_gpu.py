@@ -1,0 +1,128 @@
+"""GPU parity of the LSTM variant (through the C ABI): training step vs the golden fixture built from the reference's own
+DecoderRNN / EncoderRNN / MLP classes and vs the oracle on a larger ragged batch; staged API; bit-exact greedy ids.
+Tolerances as in test_iq_gpu.py: exact path 1e-4 / 2e-4; tensor-core (TF32) path losses 1e-3, gradients global 2e-2."""
+import os
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def rel(a, b):
+    return float((a.double().cpu() - b.double().cpu()).norm() / (b.double().cpu().norm() + 1e-30))
+
+
+@pytest.fixture(scope="module")
+def env(built_lib):
+    from blt_vqg_b200 import _lib
+    _lib.require_device()
+    return True
+
+
+def _build(cfg, sd):
+    from blt_vqg_b200.lstm_iq import LSTMIQ
+    m = LSTMIQ.from_config(cfg).cuda().train()
+    m.load_state_dict(sd)
+    return m
+
+
+def _check(m, terms, want, grads, simt):
+    ltol, ttol, gtol = (1e-4, 2e-4, 2e-4) if simt else (1e-3, 8e-2, 2e-2)
+    t = terms.cpu()
+    for i, k in enumerate(("gen", "kl", "rec_i", "rec_a")):
+        assert float(t[i]) == pytest.approx(float(want[k]), rel=ltol), k
+    assert float(m.total_loss(t)) == pytest.approx(float(want["loss"]), rel=ltol)
+    num = den = 0.0
+    for k, gref in grads.items():
+        g = m.arena.view_of(m.grad_arena, k)
+        if k == "encoder_cnn.cnn.fc.bias":  # exactly-zero gradient (bias in front of BatchNorm)
+            assert float(g.abs().max()) < 1e-3
+            continue
+        d = float((g.double().cpu() - gref.double()).norm())
+        num += d * d
+        den += float(gref.double().norm()) ** 2
+        assert d / (float(gref.double().norm()) + 1e-30) < ttol or float((g.cpu() - gref).abs().max()) < 1e-6, (k, d)
+    assert (num / den) ** 0.5 < gtol
+
+
+@pytest.mark.parametrize("simt", [True, False])
+def test_lstm_training_step_matches_reference_blocks_golden(env, golden_dir, simt):
+    from blt_vqg_b200 import ops
+    gold = torch.load(os.path.join(golden_dir, "iq_lstm_tiny.pt"), weights_only=False)
+    b = gold["batch"]
+    m = _build(gold["cfg"], gold["state_dict"])
+    with ops.gemm_mode(simt=simt):
+        terms = m.forward_losses(b["feats"], b["answers"], b["alengths"], b["questions"], eps=gold["eps"].cuda(), eps2=gold["eps2"].cuda())
+    _check(m, terms, gold["losses"], gold["grads"], simt)
+    assert float(terms[4]) == float((b["questions"][:, 1:] != 0).sum())
+    assert rel(m.bn_running_mean, gold["bn_running_mean_after"]) < 1e-3
+
+
+@pytest.mark.parametrize("simt", [True, False])
+def test_lstm_training_step_matches_oracle_small(env, simt):
+    from blt_vqg_b200 import ops, synth
+    from oracle import lstm_oracle
+    cfg = synth.LSTM_CONFIGS["small"]
+    b = synth.make_batch(cfg)  # unsorted, ragged answer lengths: length masking instead of packing
+    sd = lstm_oracle.init_state_dict(cfg, seed=4)
+    g = torch.Generator().manual_seed(5)
+    eps, eps2 = torch.randn(cfg["B"], cfg["Z"], generator=g), torch.randn(cfg["B"], cfg["Z"], generator=g)
+    P = {k: v.clone().requires_grad_("running" not in k) for k, v in sd.items()}
+    bn = (P["encoder_cnn.bn.running_mean"].clone(), P["encoder_cnn.bn.running_var"].clone())
+    loss, want = lstm_oracle.lstm_iq_losses(P, b["feats"], b["answers"], b["alengths"], b["questions"], eps, eps2, bn_state=bn)
+    loss.backward()
+    m = _build(cfg, sd)
+    with ops.gemm_mode(simt=simt):
+        terms = m.forward_losses(b["feats"], b["answers"], b["alengths"], b["questions"], eps=eps.cuda(), eps2=eps2.cuda())
+    _check(m, terms, {k: v.detach() for k, v in want.items()}, {k: v.grad for k, v in P.items() if v.requires_grad}, simt)
+
+
+def test_staged_api_and_bit_exact_greedy_ids(env, golden_dir):
+    """old_train_iq.py:100-106 call sequence in eval mode; ids of the free-running decoder equal the fp32 reference's"""
+    from blt_vqg_b200 import ops, synth
+    from oracle import lstm_oracle
+    gold = torch.load(os.path.join(golden_dir, "iq_lstm_tiny.pt"), weights_only=False)
+    b, cfg = gold["batch"], gold["cfg"]
+    sd = dict(gold["state_dict"])
+    sd["encoder_cnn.bn.running_mean"], sd["encoder_cnn.bn.running_var"] = gold["bn_running_mean_after"], gold["bn_running_var_after"]
+    m = _build(cfg, sd).eval()
+    with ops.gemm_mode(simt=True):
+        img = m.encode_images(b["feats"])
+        ans = m.encode_answers(b["answers"], b["alengths"])
+        mus, logvars = m.encode_into_z(img, ans)
+        zs = m.reparameterize(mus, logvars)           # eval: zs = mus
+        outputs, hidden, ret = m.decode_questions(img, zs, questions=None, teacher_forcing_ratio=0)
+        tf_out, _, tf_ret = m.decode_questions(img, zs, questions=b["questions"], teacher_forcing_ratio=1.0)
+        ri, ra = m.reconstruct_inputs(img, ans)
+    P = {k: v for k, v in sd.items()}
+    with torch.no_grad():
+        img_r = lstm_oracle.encode_images(P, b["feats"], training=False)
+        ans_r = lstm_oracle.encode_answers(P, b["answers"], b["alengths"])
+        mu_r, lv_r = lstm_oracle.encode_into_z(P, img_r, ans_r)
+        logp_r = lstm_oracle.decode_questions(P, img_r, mu_r, b["questions"])
+    assert rel(img, img_r) < 1e-5 and rel(ans, ans_r) < 1e-5 and rel(mus, mu_r) < 1e-5 and rel(logvars, lv_r) < 1e-5
+    ids = torch.cat(ret[m.KEY_SEQUENCE], dim=1).cpu()
+    assert ids.shape == (cfg["B"], cfg["T"]) and torch.equal(ids, gold["greedy_ids"])
+    assert len(outputs) == cfg["T"] and outputs[0].shape == (cfg["B"], cfg["V"])
+    assert len(tf_out) == cfg["T"] - 1
+    assert rel(torch.stack(tf_out, 1), logp_r) < 1e-5
+    assert hidden[0].shape == (1, cfg["B"], cfg["H"]) and len(ret[m.KEY_LENGTH]) == cfg["B"]
+    assert ri.shape == ra.shape == (cfg["B"], cfg["H"])
+
+
+def test_lstm_train_step_runs_with_dropout_and_adam(env):
+    from blt_vqg_b200 import synth
+    from blt_vqg_b200.lstm_iq import LSTMIQ
+    from blt_vqg_b200.train import TrainStep
+    cfg = synth.LSTM_CONFIGS["small"]
+    torch.manual_seed(0)
+    m = LSTMIQ.from_config(cfg, input_dropout_p=0.3).cuda().train()
+    ts = TrainStep(m, lr_fn=lambda s: 1e-3)
+    first = None
+    for i in range(8):
+        b = synth.make_batch(cfg, seed=7)
+        t = ts.step(b["feats"], b["answers"], b["alengths"], b["questions"]).cpu()
+        assert torch.isfinite(t).all()
+        first = float(t[0]) if first is None else first
+    assert float(t[0]) < first  # the generation loss goes down on a repeated batch

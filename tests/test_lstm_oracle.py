@@ -1,0 +1,64 @@
+"""CPU: the LSTM-variant oracle (oracle/lstm_oracle.py) against the golden fixture produced from the reference's own
+DecoderRNN / EncoderRNN / MLP classes (oracle/gen_golden_lstm.py)."""
+import os
+
+import pytest
+import torch
+
+from blt_vqg_b200 import synth
+from oracle import lstm_oracle, refload
+
+
+def test_lstm_oracle_matches_reference_blocks(golden_dir):
+    gold = torch.load(os.path.join(golden_dir, "iq_lstm_tiny.pt"), weights_only=False)
+    b = gold["batch"]
+    P = {k: v.clone().requires_grad_("running" not in k) for k, v in gold["state_dict"].items()}
+    bn = (P["encoder_cnn.bn.running_mean"].clone(), P["encoder_cnn.bn.running_var"].clone())
+    loss, terms = lstm_oracle.lstm_iq_losses(P, b["feats"], b["answers"], b["alengths"], b["questions"], gold["eps"], gold["eps2"], bn_state=bn)
+    loss.backward()
+    for k in ("loss", "gen", "kl", "rec_i", "rec_a"):
+        assert float(terms[k].detach()) == pytest.approx(gold["losses"][k], rel=2e-5), k
+    assert torch.allclose(bn[0], gold["bn_running_mean_after"], atol=1e-6)
+    n = 0
+    for k, gref in gold["grads"].items():
+        g = P[k].grad
+        assert float((g - gref).norm() / (gref.norm() + 1e-12)) < 1e-4 or float((g - gref).abs().max()) < 1e-7, k
+        n += 1
+    assert n >= 30
+
+
+def test_lstm_oracle_greedy_ids_bit_exact(golden_dir):
+    gold = torch.load(os.path.join(golden_dir, "iq_lstm_tiny.pt"), weights_only=False)
+    b = gold["batch"]
+    P = {k: v for k, v in gold["state_dict"].items()}
+    P["encoder_cnn.bn.running_mean"], P["encoder_cnn.bn.running_var"] = gold["bn_running_mean_after"], gold["bn_running_var_after"]
+    with torch.no_grad():
+        img = lstm_oracle.encode_images(P, b["feats"], training=False)
+        ans = lstm_oracle.encode_answers(P, b["answers"], b["alengths"])
+        mu, _ = lstm_oracle.encode_into_z(P, img, ans)
+        ids = lstm_oracle.greedy_decode(P, img, mu, synth.SOQ, gold["cfg"]["T"])
+    assert torch.equal(ids, gold["greedy_ids"])
+
+
+def test_packed_sequence_semantics_of_lstm_seq():
+    """length masking == nn.LSTM on a packed sequence (encoder_rnn.py:80-86)"""
+    torch.manual_seed(0)
+    B, T, H = 5, 4, 8
+    rnn = torch.nn.LSTM(H, H, 1, batch_first=True)
+    x = torch.randn(B, T, H)
+    lengths = torch.tensor([4, 3, 3, 2, 1])
+    packed = torch.nn.utils.rnn.pack_padded_sequence(x, lengths, batch_first=True)
+    _, (h, c) = rnn(packed)
+    z = torch.zeros(B, H)
+    _, h2, c2 = lstm_oracle.lstm_seq(x, z, z, rnn.weight_ih_l0, rnn.weight_hh_l0, rnn.bias_ih_l0, rnn.bias_hh_l0, lengths=lengths)
+    assert torch.allclose(h[0], h2, atol=1e-6) and torch.allclose(c[0], c2, atol=1e-6)
+
+
+@pytest.mark.skipif(not refload.available(), reason="reference tree only exists in the build container")
+def test_lstm_golden_regenerates_from_reference(golden_dir):
+    from oracle import gen_golden_lstm
+    gold = torch.load(os.path.join(golden_dir, "iq_lstm_tiny.pt"), weights_only=False)
+    fresh = gen_golden_lstm.run_reference("tiny")
+    for k in ("loss", "gen", "kl", "rec_i", "rec_a"):
+        assert fresh["losses"][k] == pytest.approx(gold["losses"][k], rel=1e-6)
+    assert torch.equal(fresh["greedy_ids"], gold["greedy_ids"])
