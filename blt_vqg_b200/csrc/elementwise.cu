@@ -48,11 +48,13 @@ __global__ void add_timing_kernel(float* __restrict__ x, const float* __restrict
     int c = (int)(i % H);
     size_t row = i / H;
     int t = (int)(row % n), b = (int)(row / n);
-    float v = x[i] + (timing ? timing[(size_t)t * H + c] : 0.f);
+    // same association order as the reference: (emb + add0 + add1) first (decoder_transformer.py:31-34,46), timing after (:214)
+    float v = x[i];
     if (t == 0) {
       if (add0) v += add0[(size_t)b * H + c];
       if (add1) v += add1[(size_t)b * H + c];
     }
+    if (timing) v += timing[(size_t)t * H + c];
     x[i] = rnd(v, rn);
   }
 }

@@ -426,3 +426,82 @@ class IQ(nn.Module):
         self._backward_tail(c, d_dec, d_img, d_z, d_recon, kld_coef)
         c.gflat, c.G = self.grad_arena, None
         return g
+
+    # ------------------------------------------------------------------ greedy decoding (models/iq.py:117-152)
+    @torch.no_grad()
+    def decode_greedy(self, images, answers, max_decode_length=50, eps=None, exact=True):
+        """models/iq.py:117-152: encoder once, prior-only latent (a fresh eps: Philox here, or injected), then
+        max_decode_length+1 decoder passes over the growing prefix that starts with PAD (so key 0 is pad-masked and the first
+        query row is fully masked -> uniform attention), argmax + top-6 softmax per step.
+        Runs in EXACT fp32 (CUDA-core GEMMs, no TF32 rounding) so the token ids are bit-identical to an fp32 run.
+        Returns (sentences, top_args (B, L+1, 6) float32, top_vals (B, L+1, 6) float32) like the reference."""
+        with ops.gemm_mode(simt=exact):
+            return self._decode_greedy(images, answers, max_decode_length, eps)
+
+    def _decode_greedy(self, images, answers, max_decode_length, eps):
+        dev = self.flat.device
+        was_training = self.training
+        self.eval()
+        try:
+            feats = self._features(images)
+            cids = _ids(answers, dev)
+            B, S, H, L, V = feats.shape[0], cids.shape[1], self.H, self.L, self.V
+            steps = max_decode_length + 1
+            c = self._make_ctx(B, S, 0, steps, False)
+            ws, P = c.ws, c.P
+            img_pre = ws.buf("img_pre", B, H)
+            ops.gemm(feats, c.W["encoder_cnn.cnn.fc.weight"], img_pre, bias=P["encoder_cnn.cnn.fc.bias"], fp32_out=True)
+            img = ws.buf("img", B, H)
+            ops.bn_fwd(img_pre, P["encoder_cnn.bn.weight"], P["encoder_cnn.bn.bias"], img, ws.buf("bn.mean", H), ws.buf("bn.rstd", H),
+                       self.bn_running_mean, self.bn_running_var, False)
+            x = tf.embed_fwd(c, "enc.emb", cids, B, S, self.timing_enc)
+            enc_out = tf.encoder_fwd(c, "enc", "answer_encoder.encoder.", x, cids, B, S, self.NL)
+            ops.add_timing(enc_out, None, img, None, B, S, H)
+            z = None
+            if self.latent_transformer:
+                x0 = ws.buf("g.x0", B, H)
+                ops.tok0_gather(enc_out, x0, B, S, H)
+                pp = "latent_layer.mean_logvar_prior."
+                p1 = tf.linear_fwd(c, "lat.p1", pp + "0", x0, relu=True)
+                p2 = tf.linear_fwd(c, "lat.p2", pp + "3", p1, relu=True)
+                prior = tf.linear_fwd(c, "lat.prior", pp + "6", p2, fp32_out=True)
+                e = ws.buf("lat.eps", B, L)
+                if eps is not None:
+                    e.copy_(eps)
+                else:
+                    ops.randn_(e, self.seed + self.step_idx, 11 << 40)
+                zl = ws.buf("lat.z", B, L)
+                ops.latent_fwd(prior, None, e, zl, None)                     # Latent(x, None): sample from the prior (iq.py:126)
+                z = tf.linear_fwd(c, "z", "latent_projection", zl)
+            ys = torch.full((B, steps + 1), PAD, dtype=torch.int32, device=dev)  # prefix: ys[:, 0] = PAD (iq.py:129)
+            top_i = torch.zeros(B, steps, 6, dtype=torch.int32, device=dev)
+            top_v = torch.zeros(B, steps, 6, device=dev)
+            last = ws.buf("g.last", B, H)
+            logit = ws.buf("g.logit", B, V)
+            ti, tv = ws.buf("g.ti", B, 6, dtype=torch.int32), ws.buf("g.tv", B, 6)
+            for i in range(steps):
+                n = i + 1
+                prefix = ys[:, :n].contiguous()
+                xd = tf.embed_fwd(c, "g.emb", prefix, B, n, self.timing_dec, add0=z, add1=img)   # decoder_transformer.py:46
+                dec = tf.decoder_fwd(c, "g", "decoder.decoder.", xd, prefix, enc_out, cids, B, n, S, self.NL)
+                ops.tok0_gather(dec[n - 1:], last, B, n, H)                    # logits[:, -1]
+                ops.gemm(last, c.W["decoder.output.weight"], logit, bias=P["decoder.output.bias"], fp32_out=True)
+                ops.topk_softmax_rows(logit, 6, ti, tv)                       # iq.py:136-137
+                ys[:, n] = ti[:, 0]
+                top_i[:, i] = ti
+                top_v[:, i] = tv
+            ids = ys[:, 1:].cpu()
+        finally:
+            self.train(was_training)
+            self._ws.pop((B, S, 0, steps, bool(self.latent_transformer), False), None)  # decode buffers are not kept
+        eos = self.vocab.word2idx[self.vocab.SYM_EOS]
+        sentences = []
+        for row in ids.tolist():                                              # iq.py:144-151
+            st = ""
+            for t in row:
+                if t == eos:
+                    break
+                st += self.vocab.idx2word[t] + " "
+            sentences.append(st)
+        self.last_greedy_ids = ids.long()
+        return sentences, top_i.float(), top_v

@@ -251,3 +251,22 @@ def test_dropout_training_mode_runs_and_is_reproducible(env):
     m.grad_arena.zero_()
     t3 = m.forward_losses(b["feats"], b["answers"], b["posteriors"], b["questions"])
     assert not torch.allclose(t1[:4], t3[:4], rtol=1e-7)
+
+
+@pytest.mark.parametrize("mode", ["latent", "pretrain"])
+def test_greedy_decode_ids_bit_exact_vs_reference(env, golden_dir, mode):
+    """models/iq.py:117-152: token ids (and the top-6 alternatives) of decode_greedy equal the REAL reference's fp32 run"""
+    gold = torch.load(os.path.join(golden_dir, "iq_transformer_tiny_%s.pt" % mode), weights_only=False)
+    cfg, b = gold["cfg"], gold["batch"]
+    sd = dict(gold["state_dict"])
+    sd["encoder_cnn.bn.running_mean"], sd["encoder_cnn.bn.running_var"] = gold["bn_running_mean_after"], gold["bn_running_var_after"]
+    m = _build(cfg, gold["latent_mode"], sd)
+    sentences, top_args, top_vals = m.decode_greedy(b["feats"], b["answers"], max_decode_length=gold["greedy_len"],
+                                                    eps=gold["eps_greedy"].cuda())
+    n = gold["greedy_len"] + 1
+    assert top_args.shape == (cfg["B"], n, 6) and top_args.dtype == torch.float32 and top_vals.shape == (cfg["B"], n, 6)
+    assert torch.equal(m.last_greedy_ids, gold["greedy_ids"])
+    assert torch.equal(top_args.long().cpu(), gold["greedy_top6_ids"])
+    assert torch.allclose(top_vals.cpu(), gold["greedy_top6_vals"], atol=1e-6)
+    assert len(sentences) == cfg["B"] and all(isinstance(s, str) for s in sentences)
+    assert m.training  # mode restored
