@@ -293,6 +293,13 @@ def main():
     clocks = sampler.stop()
     terms = ts.step(*step_inputs(args.workload, db[0])).cpu()
     finite = bool(torch.isfinite(terms[:4]).all())
+    in_sync = None
+    if dist_on:  # data-parallel replicas must hold bit-identical weights after the same number of reduced steps
+        chk = model.flat.data.double().sum().view(1)
+        lo, hi = chk.clone(), chk.clone()
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        in_sync = bool((hi - lo).abs().item() == 0.0)
 
     if rank != 0:
         if dist_on:
@@ -322,7 +329,8 @@ def main():
             "e2e": {"value": round(B * world * args.steps / (ms_e2e * 1e-3), 1), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 32,
                     "ms_per_step": round(ms_e2e / args.steps, 3)},
             "gpu_launches": launches, "gpu_launches_per_step": launches // max(1, args.steps), "clocks": clocks,
-            "roofline": roof, "cpu_baseline": cpu, "loss_terms_finite": finite,
+            "roofline": roof, "cpu_baseline": cpu, "loss_terms_finite": finite, "replicas_in_sync": in_sync,
+            "allreduce_buckets_per_step": (dp.collectives // max(1, ts.t)) if dp is not None else 0,
             "loss_terms": {"rec": round(float(terms[0]), 4), "img": round(float(terms[1]), 4), "kld": round(float(terms[2]), 4), "aux": round(float(terms[3]), 4)}}
     print(json.dumps(line), flush=True)
     if detail:

@@ -1,0 +1,66 @@
+"""CPU (gloo, world_size 2): the bucketed gradient reducer that the backward schedule drives (parallel.GradReducer)."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+class _FakeModel:
+    def __init__(self, n, rank):
+        g = torch.Generator().manual_seed(100 + rank)
+        self.grad_arena = torch.randn(n, generator=g)
+        self.on_grad_ready = None
+
+
+def _worker(rank, world, port, n, bucket_bytes, marks, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from blt_vqg_b200.parallel import GradReducer, shard_batch
+        m = _FakeModel(n, rank)
+        local = m.grad_arena.clone()
+        red = GradReducer(bucket_bytes=bucket_bytes)
+        red.begin_step(m)
+        assert m.on_grad_ready is not None
+        sent_before_finish = []
+        for off in marks:                      # the backward schedule reports ready suffixes in decreasing offset order
+            m.on_grad_ready(off)
+            sent_before_finish.append(red.collectives)
+        red.finish_step(m)
+        assert m.on_grad_ready is None
+        gathered = [torch.empty(n) for _ in range(world)]
+        dist.all_gather(gathered, local)
+        want = sum(gathered)
+        ok = torch.allclose(m.grad_arena, want, atol=1e-6)
+        b = shard_batch({"x": torch.arange(8).view(8, 1), "y": torch.arange(16).view(8, 2)}, rank, world)
+        shard_ok = b["x"].shape[0] == 4 and int(b["x"][0]) == 4 * rank
+        if rank == 0:
+            torch.save({"ok": ok, "shard_ok": shard_ok, "collectives": red.collectives, "sent": sent_before_finish}, out)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("n,bucket_bytes,marks", [
+    (10000, 4 * 3000, [9000, 6500, 3000, 100]),   # several buckets, some flushed before finish (overlap with "backward")
+    (1000, 1 << 20, [500]),                        # everything fits one bucket: a single collective at finish
+])
+def test_grad_reducer_sums_over_ranks_in_buckets(tmp_path, n, bucket_bytes, marks):
+    out = str(tmp_path / "res.pt")
+    port = _free_port()
+    mp.spawn(_worker, args=(2, port, n, bucket_bytes, marks, out), nprocs=2, join=True)
+    res = torch.load(out)
+    assert res["ok"] and res["shard_ok"]
+    elems = bucket_bytes // 4
+    assert res["collectives"] == -(-n // elems)          # ceil(n / bucket): every element reduced exactly once
+    if n > elems:
+        assert res["sent"][-1] >= 1                      # buckets were launched before the end of "backward"
+        assert res["sent"] == sorted(res["sent"])
