@@ -263,6 +263,8 @@ def main():
     torch.cuda.set_device(local_rank)
     dp = None
     if dist_on:
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"   # keep stdout to the one JSON line (NCCL prints its version banner there)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
         from blt_vqg_b200.parallel import GradReducer
         dp = GradReducer()
