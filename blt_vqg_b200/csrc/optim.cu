@@ -5,8 +5,12 @@
 
 namespace b200iq {
 
-__global__ void __launch_bounds__(256) sumsq_kernel(const float* __restrict__ g, size_t n, float* __restrict__ out) {
+// Deterministic: every block writes its partial to scratch[blockIdx.x]; the LAST block to finish (ticket in scratch[gridDim.x])
+// adds the partials in index order.  A float atomicAdd tree would make the clip factor differ in the last bit from run to run
+// and from rank to rank, and data-parallel replicas would drift apart.
+__global__ void __launch_bounds__(256) sumsq_kernel(const float* __restrict__ g, size_t n, float* __restrict__ out, float* __restrict__ scratch) {
   __shared__ float red[32];
+  __shared__ bool is_last;
   float acc = 0.f;
   size_t n4 = n >> 2;
   const float4* g4 = reinterpret_cast<const float4*>(g);
@@ -16,7 +20,21 @@ __global__ void __launch_bounds__(256) sumsq_kernel(const float* __restrict__ g,
   }
   for (size_t i = (n4 << 2) + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) acc += g[i] * g[i];
   acc = block_sum(acc, red);
-  if (threadIdx.x == 0) atomicAdd(out, acc);
+  unsigned int* ticket = reinterpret_cast<unsigned int*>(scratch + gridDim.x);
+  if (threadIdx.x == 0) {
+    scratch[blockIdx.x] = acc;
+    __threadfence();
+    is_last = (atomicAdd(ticket, 1u) == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (is_last) {
+    __threadfence();
+    float s = 0.f;
+    for (unsigned int i = threadIdx.x; i < gridDim.x; i += blockDim.x) s += ((volatile float*)scratch)[i];
+    // fixed-shape tree: thread t owns partials t, t+256, ...; block_sum's shuffle order is fixed
+    s = block_sum(s, red);
+    if (threadIdx.x == 0) { out[0] = s; *ticket = 0u; }
+  }
 }
 
 // hyper (device): [0]=lr  [1]=1-beta1^t  [2]=1-beta2^t  [3]=grad_scale (1/world_size)
@@ -54,14 +72,26 @@ adam_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m,
     if (zero_grad) g[i] = 0.f;
   }
 }
+// hyper[0..3] = {lr, 1-beta1^t, 1-beta2^t, grad_scale}: host scalars travel as kernel arguments, so there is no pinned
+// staging buffer the host could overwrite while an earlier step's copy is still queued
+__global__ void set_hyper_kernel(float* hyper, float lr, float bc1, float bc2, float gs) {
+  hyper[0] = lr; hyper[1] = bc1; hyper[2] = bc2; hyper[3] = gs;
+}
 }  // namespace b200iq
 using namespace b200iq;
 
-extern "C" int b200iq_grad_sumsq(const float* grad, size_t n, float* out, void* stream) {
-  B200IQ_CHECK_ARG(grad && out && n > 0 && (((uintptr_t)grad) & 15) == 0, "grad_sumsq: bad args");
-  cudaMemsetAsync(out, 0, sizeof(float), (cudaStream_t)stream);
+extern "C" int b200iq_set_hyper(float* hyper, float lr, float bias_corr1, float bias_corr2, float grad_scale, void* stream) {
+  B200IQ_CHECK_ARG(hyper, "set_hyper: null pointer");
+  set_hyper_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(hyper, lr, bias_corr1, bias_corr2, grad_scale);
+  return launch_status("set_hyper");
+}
+
+extern "C" int b200iq_grad_sumsq(const float* grad, size_t n, float* out, float* scratch, int scratch_floats, void* stream) {
+  B200IQ_CHECK_ARG(grad && out && scratch && n > 0 && (((uintptr_t)grad) & 15) == 0, "grad_sumsq: bad args");
   int grid = (int)min((size_t)sm_count() * 8, (n / 4 + 255) / 256 + 1);
-  sumsq_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(grad, n, out);
+  if (grid > scratch_floats - 1) grid = scratch_floats - 1;
+  B200IQ_CHECK_ARG(grid >= 1, "grad_sumsq: scratch too small");
+  sumsq_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(grad, n, out, scratch);
   return launch_status("grad_sumsq");
 }
 

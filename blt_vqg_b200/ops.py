@@ -239,8 +239,19 @@ def mse(a, b, coef, loss_sum, da, db, accumulate_db=False):
     _call("b200iq_mse", _p(a), _p(b), C.c_size_t(a.numel()), _f(coef), _p(loss_sum), _p(da), _p(db), int(accumulate_db))
 
 
+def set_hyper(hyper, lr, bc1, bc2, grad_scale):
+    _call("b200iq_set_hyper", _p(hyper), _f(lr), _f(bc1), _f(bc2), _f(grad_scale))
+
+
+_SUMSQ_SCRATCH = {}
+
+
 def grad_sumsq(grad, out):
-    _call("b200iq_grad_sumsq", _p(grad), C.c_size_t(grad.numel()), _p(out))
+    key = (grad.device, torch.cuda.current_stream().cuda_stream)
+    scratch = _SUMSQ_SCRATCH.get(key)
+    if scratch is None:
+        scratch = _SUMSQ_SCRATCH[key] = torch.zeros(2048, device=grad.device)
+    _call("b200iq_grad_sumsq", _p(grad), C.c_size_t(grad.numel()), _p(out), _p(scratch), scratch.numel())
 
 
 def adam_step(param, grad, m, v, hyper, normsq, beta1=0.9, beta2=0.999, eps=1e-8, max_norm=5.0, zero_grad=True):

@@ -27,7 +27,6 @@ class TrainStep:
         self.exp_avg = torch.zeros_like(flat)
         self.exp_avg_sq = torch.zeros_like(flat)
         self.hyper = torch.zeros(4, device=flat.device)
-        self._hyper_host = torch.zeros(4).pin_memory() if flat.is_cuda else torch.zeros(4)
         self.normsq = torch.zeros(1, device=flat.device)
         self.iter = 0      # TrainIQ.iter (train_iq.py:43)
         self.kliter = 0    # TrainIQ.kliter (:44), counts steps since the latent switch
@@ -38,10 +37,8 @@ class TrainStep:
     def set_hyper(self):
         lr = self.lr_fn(self.iter)
         t = self.t + 1
-        h = self._hyper_host
-        h[0], h[1], h[2] = lr, 1.0 - self.betas[0] ** t, 1.0 - self.betas[1] ** t
-        h[3] = 1.0 / (self.dp.world_size if self.dp is not None else 1)
-        self.hyper.copy_(h, non_blocking=True)
+        ops.set_hyper(self.hyper, lr, 1.0 - self.betas[0] ** t, 1.0 - self.betas[1] ** t,
+                      1.0 / (self.dp.world_size if self.dp is not None else 1))
 
     def step(self, images, answers, response, target, eps=None):
         """returns the device tensor of loss terms (rec, img, kld, aux, count, gnorm_sq, ...) of this step"""

@@ -172,8 +172,13 @@ int b200iq_lstm_cell_bwd(const float* gates, const float* c_prev, const float* c
 int b200iq_transpose_ids(const int* in, int* out, int B, int T_in, int T_out, int col0, void* stream);
 
 /* ---------------------------------------------------------- optimizer */
-/* out[0] = sum(grad^2) over the flat gradient arena */
-int b200iq_grad_sumsq(const float* grad, size_t n, float* out, void* stream);
+/* hyper[0..3] = {lr, 1-beta1^t, 1-beta2^t, grad_scale}, written by a kernel whose ARGUMENTS carry the host scalars (no pinned
+ * staging buffer to race with).   replaces: the param_groups[0]["lr"] write of train_iq.py:257 */
+int b200iq_set_hyper(float* hyper, float lr, float bias_corr1, float bias_corr2, float grad_scale, void* stream);
+/* out[0] = sum(grad^2) over the flat gradient arena, bit-reproducible (fixed reduction order; no float atomics), so the clip
+ * factor is identical on every data-parallel rank.  scratch: >= 1186 floats of caller-owned device memory, ZERO-initialised once by the caller and then
+ * reused across calls (the kernel leaves its ticket word at 0) */
+int b200iq_grad_sumsq(const float* grad, size_t n, float* out, float* scratch, int scratch_floats, void* stream);
 /* clip_grad_norm_(max_norm) + Adam on flat arenas; hyper (device) = {lr, 1-beta1^t, 1-beta2^t, grad_scale}.
  * replaces: train_iq.py:259-261 (Adam), :372 (gradient_clip_val=5), :252-257 (LR written by the host into hyper[0]) */
 int b200iq_adam_step(float* param, float* grad, float* exp_avg, float* exp_avg_sq, size_t n, const float* hyper,
