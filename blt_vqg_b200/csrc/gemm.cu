@@ -1,9 +1,9 @@
 // GEMM for every dense projection of the IQ path (see include/b200iq.h: b200iq_gemm).
 //
-// tcgen05 path (default): one 128 x BN output tile per CTA (x split-K slices in grid.z).
+// tcgen05 path (default): PERSISTENT kernel, one CTA per SM looping over (split-K slice, 128 x BN tile) work items.
 //   warp 0  : TMA producer   (cp.async.bulk.tensor.2d, 128B swizzle, mbarrier complete_tx)
-//   warp 1  : MMA issuer     (one elected lane, tcgen05.mma.cta_group::1.kind::tf32, fp32 accum in TMEM)
-//   warps 2-5: epilogue      (tcgen05.ld 32x32b -> bias / residual / relu / relu-mask -> global)
+//   warp 1  : MMA issuer     (one elected lane, tcgen05.mma.cta_group::1.kind::tf32, fp32 accum in 2 TMEM buffers)
+//   warps 2-5: epilogue      (tcgen05.ld 32x32b -> bias / residual / relu / relu-mask -> swizzled smem -> TMA store / reduce-add)
 // Operands may be K-major ([rows,K] row-major) or MN-major ([K,rows] row-major): the second form is
 // what the backward GEMMs (dX = dY.W, dW = dY^T.X) read, so no tensor is ever transposed in HBM.
 // Out-of-bounds rows/cols/k are zero-filled by TMA, so arbitrary M, N, K are handled without padding.
@@ -14,7 +14,8 @@ namespace b200iq {
 static constexpr int BM = 128;
 static constexpr int BK = 32;          // 32 fp32 = 128 bytes = one swizzle row
 static constexpr int UMMA_K = 8;       // kind::tf32
-static constexpr int GEMM_THREADS = 192;
+static constexpr int GEMM_THREADS = 320;   // producer warp + MMA warp + 8 epilogue warps
+static constexpr int EPI_WARPS = 8;
 
 struct GemmEpi {
   float* C; const float* bias; const float* residual;
@@ -87,29 +88,52 @@ __device__ __forceinline__ float epi_value(float acc, const GemmEpi& e, int row,
   return rnd(v, e.round);
 }
 
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* tm, const void* src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+               ::"l"((uint64_t)tm), "r"(smem_u32(src)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* tm, const void* src, int c0, int c1) {
+  asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];"
+               ::"l"((uint64_t)tm), "r"(smem_u32(src)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+// Persistent GEMM: grid = min(#work items, #SMs); a work item = (split-K slice, 128 x BN output tile).
+//   warp 0   : TMA producer — one continuous smem pipeline (STAGES deep) across all work items of the CTA
+//   warp 1   : MMA issuer   — tcgen05.mma kind::tf32 into one of TWO TMEM accumulators (2 x BN columns)
+//   warps 2-5: epilogue     — tcgen05.ld 32 columns at a time -> epilogue math -> 128B-swizzled smem staging tile ->
+//                             TMA store (or TMA reduce-add for split-K) ; overlaps the next item's main loop
+// The epilogue of the first version wrote one row per thread (32 sectors per store request, ncu profiles/r01_gemm_*); staging
+// through shared memory + TMA makes every global write a full 128-byte line and clips M/N edges in hardware.
 template <int BN, bool A_MN, bool B_MN, int STAGES>
-__global__ void __launch_bounds__(GEMM_THREADS)
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                 GemmEpi epi, int kblocks_total, int kblocks_per_split) {
+                 const __grid_constant__ CUtensorMap tmC, GemmEpi epi, int m_tiles, int n_tiles, int splits,
+                 int kblocks_total, int kblocks_per_split, int use_tma_c) {
   constexpr int A_BYTES = BM * 128, B_BYTES = BN * 128, STAGE_BYTES = A_BYTES + B_BYTES;
+  constexpr int STG_BYTES = 32 * 128;  // one 32 x 32 fp32 staging tile
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-  __shared__ uint64_t full_bar[STAGES], empty_bar[STAGES], tmem_full_bar;
+  uint8_t* stg_base = smem + STAGES * STAGE_BYTES;  // [8 epilogue warps][2 buffers][4096 B], 1024-aligned
+  __shared__ uint64_t full_bar[STAGES], empty_bar[STAGES], tfull_bar[2], tempty_bar[2];
   __shared__ uint32_t tmem_base_s;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
-  const int kb0 = blockIdx.z * kblocks_per_split;
-  const int kb1 = min(kblocks_total, kb0 + kblocks_per_split);
-  const int nkb = kb1 - kb0;
+  const int tiles = m_tiles * n_tiles, total = tiles * splits;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-    mbar_init(&tmem_full_bar, 1);
+    for (int a = 0; a < 2; ++a) { mbar_init(&tfull_bar[a], 1); mbar_init(&tempty_bar[a], EPI_WARPS); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 2) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "n"(BN) : "memory");
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "n"(2 * BN) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
   tc_fence_before();
@@ -119,18 +143,24 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
   if (warp == 0) {
     if (lane == 0) {
-      for (int it = 0; it < nkb; ++it) {
-        const int s = it % STAGES, ph = (it / STAGES) & 1, k0 = (kb0 + it) * BK;
-        mbar_wait(&empty_bar[s], ph ^ 1);
-        mbar_expect_tx(&full_bar[s], STAGE_BYTES);
-        uint8_t* sa = smem + s * STAGE_BYTES;
-        uint8_t* sb = sa + A_BYTES;
-        if (!A_MN) tma_load_2d(sa, &tmA, k0, m0, &full_bar[s]);
-        else
-          for (int i = 0; i < BM / 32; ++i) tma_load_2d(sa + i * (BK * 128), &tmA, m0 + 32 * i, k0, &full_bar[s]);
-        if (!B_MN) tma_load_2d(sb, &tmB, k0, n0, &full_bar[s]);
-        else
-          for (int i = 0; i < BN / 32; ++i) tma_load_2d(sb + i * (BK * 128), &tmB, n0 + 32 * i, k0, &full_bar[s]);
+      uint32_t it = 0;
+      for (int w = blockIdx.x; w < total; w += gridDim.x) {
+        const int z = w / tiles, r = w - z * tiles, mt = r / n_tiles, nt = r - mt * n_tiles;
+        const int m0 = mt * BM, n0 = nt * BN;
+        const int kb0 = z * kblocks_per_split, kb1 = min(kblocks_total, kb0 + kblocks_per_split);
+        for (int kb = kb0; kb < kb1; ++kb, ++it) {
+          const int s = it % STAGES, ph = (it / STAGES) & 1, k0 = kb * BK;
+          mbar_wait(&empty_bar[s], ph ^ 1);
+          mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+          uint8_t* sa = smem + s * STAGE_BYTES;
+          uint8_t* sb = sa + A_BYTES;
+          if (!A_MN) tma_load_2d(sa, &tmA, k0, m0, &full_bar[s]);
+          else
+            for (int i = 0; i < BM / 32; ++i) tma_load_2d(sa + i * (BK * 128), &tmA, m0 + 32 * i, k0, &full_bar[s]);
+          if (!B_MN) tma_load_2d(sb, &tmB, k0, n0, &full_bar[s]);
+          else
+            for (int i = 0; i < BN / 32; ++i) tma_load_2d(sb + i * (BK * 128), &tmB, n0 + 32 * i, k0, &full_bar[s]);
+        }
       }
     }
   } else if (warp == 1) {
@@ -138,62 +168,132 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       // instruction descriptor: D=f32, A=B=tf32, majors, N>>3 @17, M>>4 @24
       const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
                              ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
-      for (int it = 0; it < nkb; ++it) {
-        const int s = it % STAGES, ph = (it / STAGES) & 1;
-        mbar_wait(&full_bar[s], ph);
+      uint32_t it = 0, ti = 0;
+      for (int w = blockIdx.x; w < total; w += gridDim.x, ++ti) {
+        const int z = w / tiles;
+        const int kb0 = z * kblocks_per_split, kb1 = min(kblocks_total, kb0 + kblocks_per_split);
+        const uint32_t acc = ti & 1, aph = (ti >> 1) & 1;
+        mbar_wait(&tempty_bar[acc], aph ^ 1);  // epilogue has drained this accumulator (passes at first use)
         tc_fence_after();
-        const uint32_t sa = smem_u32(smem + s * STAGE_BYTES), sb = sa + A_BYTES;
+        const uint32_t tacc = tmem_base + acc * BN;
+        for (int kb = kb0; kb < kb1; ++kb, ++it) {
+          const int s = it % STAGES, ph = (it / STAGES) & 1;
+          mbar_wait(&full_bar[s], ph);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + s * STAGE_BYTES), sb = sa + A_BYTES;
 #pragma unroll
-        for (int k = 0; k < BK / UMMA_K; ++k) {
-          const uint64_t ad = A_MN ? umma_desc(sa + k * 1024, BK * 128, 512, 1) : umma_desc(sa + k * 32, 16, 1024, 2);
-          const uint64_t bd = B_MN ? umma_desc(sb + k * 1024, BK * 128, 512, 1) : umma_desc(sb + k * 32, 16, 1024, 2);
-          umma_tf32(tmem_base, ad, bd, idesc, (it > 0 || k > 0) ? 1u : 0u);
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            const uint64_t ad = A_MN ? umma_desc(sa + k * 1024, BK * 128, 512, 1) : umma_desc(sa + k * 32, 16, 1024, 2);
+            const uint64_t bd = B_MN ? umma_desc(sb + k * 1024, BK * 128, 512, 1) : umma_desc(sb + k * 32, 16, 1024, 2);
+            umma_tf32(tacc, ad, bd, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[s]);
         }
-        umma_commit(&empty_bar[s]);
+        umma_commit(&tfull_bar[acc]);
       }
-      umma_commit(&tmem_full_bar);
     }
   } else {
-    const int q = warp & 3;  // TMEM lane quadrant this warp may read
-    mbar_wait(&tmem_full_bar, 0);
-    tc_fence_after();
-    const int row = m0 + q * 32 + lane;
-    const bool add_bias = (blockIdx.z == 0);
-    const bool vec_ok = ((epi.ldc & 3) == 0) && ((((uintptr_t)epi.C) & 15) == 0);
+    // warp w may read TMEM lanes 32*(w%4)..+31; two warps share a quadrant and split the BN columns between them
+    const int q = warp & 3, chalf = (warp - 2) >> 2;
+    constexpr int CHUNKS = BN / 32 / 2;
+    uint8_t* stg = stg_base + (warp - 2) * 2 * STG_BYTES;
+    const bool accum = epi.flags & B200IQ_GEMM_ACCUM;
+    uint32_t ti = 0, chunk = 0;
+    for (int w = blockIdx.x; w < total; w += gridDim.x, ++ti) {
+      const int z = w / tiles, r = w - z * tiles, mt = r / n_tiles, nt = r - mt * n_tiles;
+      const int m0 = mt * BM, n0 = nt * BN;
+      const uint32_t acc = ti & 1, aph = (ti >> 1) & 1;
+      mbar_wait(&tfull_bar[acc], aph);
+      tc_fence_after();
+      const int row0 = m0 + q * 32, row = row0 + lane;
+      const bool add_bias = (z == 0);
 #pragma unroll 1
-    for (int c = 0; c < BN / 32; ++c) {
-      uint32_t r[32];
-      tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + c * 32, r);
-      const int col0 = n0 + c * 32;
-      if (row < epi.M && col0 < epi.N) {
-        float* crow = epi.C + (size_t)row * epi.ldc;
-        if (epi.flags & B200IQ_GEMM_ACCUM) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (col0 + j < epi.N) atomicAdd(crow + col0 + j, epi_value(__uint_as_float(r[j]), epi, row, col0 + j, add_bias));
-        } else if (vec_ok && col0 + 32 <= epi.N) {
+      for (int c = chalf * CHUNKS; c < (chalf + 1) * CHUNKS; ++c) {
+        const int col0 = n0 + c * 32;
+        if (col0 >= epi.N) break;  // warp-uniform
+        uint32_t rr[32];
+        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN + c * 32, rr);
+        if (row0 >= epi.M) continue;  // warp-uniform: nothing of this quadrant is inside the matrix
+        const bool row_ok = row < epi.M;
+        if (use_tma_c && (epi.flags & (B200IQ_GEMM_RESIDUAL | B200IQ_GEMM_RELU_MASK)) == 0 && col0 + 32 <= epi.N) {
+          // fast path (no per-element operand): bias read as 8 x float4, no bounds checks
+          uint8_t* buf = stg + (chunk & 1) * STG_BYTES;
+          if (lane == 0) bulk_wait_read<1>();
+          __syncwarp();
+          const bool bias_on = (epi.flags & B200IQ_GEMM_BIAS) && add_bias, relu = epi.flags & B200IQ_GEMM_RELU;
+          const float4* b4 = reinterpret_cast<const float4*>(epi.bias + col0);
+          const bool bvec = bias_on && ((((uintptr_t)(epi.bias + col0)) & 15) == 0);
 #pragma unroll
           for (int j = 0; j < 32; j += 4) {
+            float4 bb = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (bvec) bb = __ldg(b4 + (j >> 2));
+            else if (bias_on) { bb.x = __ldg(epi.bias + col0 + j); bb.y = __ldg(epi.bias + col0 + j + 1); bb.z = __ldg(epi.bias + col0 + j + 2); bb.w = __ldg(epi.bias + col0 + j + 3); }
             float4 v;
-            v.x = epi_value(__uint_as_float(r[j + 0]), epi, row, col0 + j + 0, true);
-            v.y = epi_value(__uint_as_float(r[j + 1]), epi, row, col0 + j + 1, true);
-            v.z = epi_value(__uint_as_float(r[j + 2]), epi, row, col0 + j + 2, true);
-            v.w = epi_value(__uint_as_float(r[j + 3]), epi, row, col0 + j + 3, true);
-            *reinterpret_cast<float4*>(crow + col0 + j) = v;
+            v.x = __uint_as_float(rr[j + 0]) * epi.alpha + bb.x;
+            v.y = __uint_as_float(rr[j + 1]) * epi.alpha + bb.y;
+            v.z = __uint_as_float(rr[j + 2]) * epi.alpha + bb.z;
+            v.w = __uint_as_float(rr[j + 3]) * epi.alpha + bb.w;
+            if (relu) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
+            v.x = rnd(v.x, epi.round); v.y = rnd(v.y, epi.round); v.z = rnd(v.z, epi.round); v.w = rnd(v.w, epi.round);
+            *reinterpret_cast<float4*>(buf + lane * 128 + (((j >> 2) ^ (lane & 7)) << 4)) = v;
           }
-        } else {
+          fence_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            if (accum) tma_reduce_add_2d(&tmC, buf, col0, row0); else tma_store_2d(&tmC, buf, col0, row0);
+            bulk_commit();
+          }
+          ++chunk;
+        } else if (use_tma_c) {
+          uint8_t* buf = stg + (chunk & 1) * STG_BYTES;
+          if (lane == 0) bulk_wait_read<1>();  // the store that last read this buffer has finished reading
+          __syncwarp();
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (row_ok) {
+              if (col0 + j + 3 < epi.N) {
+                v.x = epi_value(__uint_as_float(rr[j + 0]), epi, row, col0 + j + 0, add_bias);
+                v.y = epi_value(__uint_as_float(rr[j + 1]), epi, row, col0 + j + 1, add_bias);
+                v.z = epi_value(__uint_as_float(rr[j + 2]), epi, row, col0 + j + 2, add_bias);
+                v.w = epi_value(__uint_as_float(rr[j + 3]), epi, row, col0 + j + 3, add_bias);
+              } else {
+                float* vv = &v.x;
+                for (int t = 0; t < 4; ++t)
+                  if (col0 + j + t < epi.N) vv[t] = epi_value(__uint_as_float(rr[j + t]), epi, row, col0 + j + t, add_bias);
+              }
+            }
+            // 128B swizzle: 16-byte chunk index XOR (row & 7), the layout the C tensor map expects
+            *reinterpret_cast<float4*>(buf + lane * 128 + (((j >> 2) ^ (lane & 7)) << 4)) = v;
+          }
+          fence_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            if (accum) tma_reduce_add_2d(&tmC, buf, col0, row0); else tma_store_2d(&tmC, buf, col0, row0);
+            bulk_commit();
+          }
+          ++chunk;
+        } else if (row_ok) {
+          float* crow = epi.C + (size_t)row * epi.ldc;
 #pragma unroll
           for (int j = 0; j < 32; ++j)
-            if (col0 + j < epi.N) crow[col0 + j] = epi_value(__uint_as_float(r[j]), epi, row, col0 + j, true);
+            if (col0 + j < epi.N) {
+              const float v = epi_value(__uint_as_float(rr[j]), epi, row, col0 + j, add_bias);
+              if (accum) atomicAdd(crow + col0 + j, v); else crow[col0 + j] = v;
+            }
         }
       }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty_bar[acc]);
     }
+    if (lane == 0) bulk_wait_all();  // every queued TMA store has landed before the CTA exits
   }
   tc_fence_before();
   __syncthreads();
   if (warp == 2) {
     tc_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(BN) : "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(2 * BN) : "memory");
   }
 }
 
@@ -277,9 +377,10 @@ static int make_map(CUtensorMap* tm, const float* base, int rows, int cols, int 
 }
 
 template <int BN, bool A_MN, bool B_MN>
-static int launch_tc(const CUtensorMap& ta, const CUtensorMap& tb, const GemmEpi& e, int K, int split, cudaStream_t st) {
-  constexpr int STAGES = 3;
-  constexpr int SMEM = STAGES * (BM * 128 + BN * 128) + 1024;
+static int launch_tc(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, int use_tma_c, const GemmEpi& e, int K,
+                     int split, cudaStream_t st) {
+  constexpr int STAGES = (BN == 256) ? 3 : 4;
+  constexpr int SMEM = STAGES * (BM * 128 + BN * 128) + EPI_WARPS * 2 * 32 * 128 + 1024;
   static bool attr_done = false;
   auto kern = gemm_tf32_kernel<BN, A_MN, B_MN, STAGES>;
   if (!attr_done) {
@@ -290,9 +391,20 @@ static int launch_tc(const CUtensorMap& ta, const CUtensorMap& tb, const GemmEpi
   if (split > kblocks) split = kblocks;
   int per = ceil_div(kblocks, split);
   split = ceil_div(kblocks, per);
-  dim3 grid(ceil_div(e.N, BN), ceil_div(e.M, BM), split);
-  kern<<<grid, GEMM_THREADS, SMEM, st>>>(ta, tb, e, kblocks, per);
+  const int m_tiles = ceil_div(e.M, BM), n_tiles = ceil_div(e.N, BN);
+  const int total = m_tiles * n_tiles * split;
+  const int grid = total < sm_count() ? total : sm_count();
+  kern<<<grid, GEMM_THREADS, SMEM, st>>>(ta, tb, tc, e, m_tiles, n_tiles, split, kblocks, per, use_tma_c);
   return launch_status("gemm_tf32_kernel");
+}
+
+// 128 x 256 tiles halve the B-operand traffic per flop but quantise worse: pick by rounds over the SMs x relative tile cost
+static int pick_bn(int M, int N, int split) {
+  if (N <= 128) return 128;
+  const int sms = sm_count();
+  const long t128 = (long)ceil_div(M, BM) * ceil_div(N, 128) * split, t256 = (long)ceil_div(M, BM) * ceil_div(N, 256) * split;
+  const double c128 = (double)((t128 + sms - 1) / sms) * 1.15, c256 = (double)((t256 + sms - 1) / sms) * 2.0;
+  return c256 < c128 ? 256 : 128;
 }
 
 }  // namespace b200iq
@@ -325,15 +437,25 @@ extern "C" int b200iq_gemm(const B200iqGemm* p, void* stream) {
 
   B200IQ_CHECK_ARG((((uintptr_t)p->A) & 15) == 0 && (((uintptr_t)p->B) & 15) == 0, "gemm: A/B must be 16-byte aligned");
   B200IQ_CHECK_ARG((p->lda & 3) == 0 && (p->ldb & 3) == 0, "gemm: lda/ldb must be multiples of 4 (lda=%d ldb=%d)", p->lda, p->ldb);
-  CUtensorMap ta, tb;
+  CUtensorMap ta, tb, tc;
   int rc;
-  constexpr int BN = 128;
+  const int BN = pick_bn(p->M, p->N, split);
   if (!amn) rc = make_map(&ta, p->A, p->M, p->K, p->lda, BM, false); else rc = make_map(&ta, p->A, p->K, p->M, p->lda, BK, true);
   if (rc) return rc;
   if (!bmn) rc = make_map(&tb, p->B, p->N, p->K, p->ldb, BN, false); else rc = make_map(&tb, p->B, p->K, p->N, p->ldb, BK, true);
   if (rc) return rc;
-  if (!amn && !bmn) return launch_tc<BN, false, false>(ta, tb, e, p->K, split, st);
-  if (!amn && bmn) return launch_tc<BN, false, true>(ta, tb, e, p->K, split, st);
-  if (amn && !bmn) return launch_tc<BN, true, false>(ta, tb, e, p->K, split, st);
-  return launch_tc<BN, true, true>(ta, tb, e, p->K, split, st);
+  // C goes out through TMA (32 x 32 boxes, 128B swizzle) when its pitch / base allow it; else per-thread stores
+  const int use_tma_c = ((p->ldc & 3) == 0 && (((uintptr_t)p->C) & 15) == 0) ? 1 : 0;
+  if (use_tma_c) rc = make_map(&tc, p->C, p->M, p->N, p->ldc, 32, false); else memset(&tc, 0, sizeof(tc));
+  if (rc) return rc;
+#define B200IQ_LAUNCH(BN_) \
+  do { \
+    if (!amn && !bmn) return launch_tc<BN_, false, false>(ta, tb, tc, use_tma_c, e, p->K, split, st); \
+    if (!amn && bmn) return launch_tc<BN_, false, true>(ta, tb, tc, use_tma_c, e, p->K, split, st); \
+    if (amn && !bmn) return launch_tc<BN_, true, false>(ta, tb, tc, use_tma_c, e, p->K, split, st); \
+    return launch_tc<BN_, true, true>(ta, tb, tc, use_tma_c, e, p->K, split, st); \
+  } while (0)
+  if (BN == 256) B200IQ_LAUNCH(256);
+  B200IQ_LAUNCH(128);
+#undef B200IQ_LAUNCH
 }
