@@ -5,8 +5,8 @@
 
 namespace b200iq {
 
-// Deterministic: every block writes its partial to scratch[blockIdx.x]; the LAST block to finish (ticket in scratch[gridDim.x])
-// adds the partials in index order.  A float atomicAdd tree would make the clip factor differ in the last bit from run to run
+// Deterministic: every block writes its partial to scratch[1 + blockIdx.x]; the LAST block to finish (ticket in scratch[0],
+// a fixed slot so that calls with different grids can share one scratch buffer) adds the partials in index order.  A float atomicAdd tree would make the clip factor differ in the last bit from run to run
 // and from rank to rank, and data-parallel replicas would drift apart.
 __global__ void __launch_bounds__(256) sumsq_kernel(const float* __restrict__ g, size_t n, float* __restrict__ out, float* __restrict__ scratch) {
   __shared__ float red[32];
@@ -20,7 +20,8 @@ __global__ void __launch_bounds__(256) sumsq_kernel(const float* __restrict__ g,
   }
   for (size_t i = (n4 << 2) + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) acc += g[i] * g[i];
   acc = block_sum(acc, red);
-  unsigned int* ticket = reinterpret_cast<unsigned int*>(scratch + gridDim.x);
+  unsigned int* ticket = reinterpret_cast<unsigned int*>(scratch);
+  scratch += 1;
   if (threadIdx.x == 0) {
     scratch[blockIdx.x] = acc;
     __threadfence();
