@@ -168,6 +168,280 @@ attention_bwd_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, float*
   }
 }
 
+// ------------------------------------------------------------------ tensor-core path (head_dim 64, nq,nk <= 32)
+// The SIMT kernels above are issue-bound (ncu profiles/r01c_attention_*: 69 % issue-active at 7 % of HBM peak: one LDS
+// pair per FMA).  Here ONE WARP owns one (sample, head) and keeps everything in registers: QK^T and PV are
+// mma.sync.m16n8k8 TF32 with operands loaded straight from global memory as float4 — the reduction index of an MMA may
+// be permuted freely as long as A and B agree, and so may the n index as long as the store agrees, which is what makes
+// 16-byte loads and 32-byte-per-lane stores line up with the fragment layouts.  No shared memory in the forward.
+//   A frag: a0 (g, t) a1 (g+8, t) a2 (g, t+4) a3 (g+8, t+4);  B frag: b0 (k=t, n=g) b1 (k=t+4, n=g);
+//   C frag: c0 (g, 2t) c1 (g, 2t+1) c2 (g+8, 2t) c3 (g+8, 2t+1)          with g = lane>>2, t = lane&3
+__device__ __forceinline__ void mma_tf32(float (&c)[4], float a0, float a1, float a2, float a3, float b0, float b1) {
+  asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+               : "r"(__float_as_uint(a0)), "r"(__float_as_uint(a1)), "r"(__float_as_uint(a2)), "r"(__float_as_uint(a3)),
+                 "r"(__float_as_uint(b0)), "r"(__float_as_uint(b1)));
+}
+__device__ __forceinline__ float4 ld4(const float* base, int row, int nrows, int ld, int col) {
+  if (row < nrows) return __ldg(reinterpret_cast<const float4*>(base + (size_t)row * ld + col));
+  return make_float4(0.f, 0.f, 0.f, 0.f);
+}
+
+// acc[mt][nt] += X[16mt.., :64] . Y[8nt.., :64]^T   (both K-major in global memory; rows beyond nx / ny read as zero)
+template <int MT, int NT>
+__device__ __forceinline__ void mma_xyT(float (&acc)[MT][NT][4], const float* X, int nx, int ldx, const float* Y, int ny, int ldy,
+                                        int g, int t) {
+#pragma unroll
+  for (int kk = 0; kk < 4; ++kk) {
+    float4 xa[MT], xb[MT], yf[NT];
+#pragma unroll
+    for (int mt = 0; mt < MT; ++mt) { xa[mt] = ld4(X, 16 * mt + g, nx, ldx, 16 * kk + 4 * t); xb[mt] = ld4(X, 16 * mt + g + 8, nx, ldx, 16 * kk + 4 * t); }
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) yf[nt] = ld4(Y, 8 * nt + g, ny, ldy, 16 * kk + 4 * t);
+#pragma unroll
+    for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt) {
+        mma_tf32(acc[mt][nt], xa[mt].x, xb[mt].x, xa[mt].y, xb[mt].y, yf[nt].x, yf[nt].y);
+        mma_tf32(acc[mt][nt], xa[mt].z, xb[mt].z, xa[mt].w, xb[mt].w, yf[nt].z, yf[nt].w);
+      }
+  }
+}
+
+// out[16mt.., :64] = P . Y with P[mt][nt] in C-fragment layout (rows i, cols j) and Y[j, :64] in global memory (rows >= ny zero).
+// Lane (g,t) ends up with 8 contiguous output floats per row and 32-column block: cols 32cq + 8t .. +7.
+template <int MT, int NT>
+__device__ __forceinline__ void mma_pY_store(const float (&P)[MT][NT][4], const float* Y, int ny, int ldy, float* out, int nrows,
+                                             int ldo, int g, int t, int rn) {
+#pragma unroll
+  for (int cq = 0; cq < 2; ++cq) {
+    float acc[MT][4][4];
+#pragma unroll
+    for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) acc[mt][u][e] = 0.f;
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) {
+      const float4 y0 = ld4(Y, 8 * nt + 2 * t, ny, ldy, 32 * cq + 4 * g), y1 = ld4(Y, 8 * nt + 2 * t + 1, ny, ldy, 32 * cq + 4 * g);
+      const float* y0a = &y0.x; const float* y1a = &y1.x;
+#pragma unroll
+      for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+        for (int u = 0; u < 4; ++u) mma_tf32(acc[mt][u], P[mt][nt][0], P[mt][nt][2], P[mt][nt][1], P[mt][nt][3], y0a[u], y1a[u]);
+    }
+#pragma unroll
+    for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+      for (int hh = 0; hh < 2; ++hh) {
+        const int row = 16 * mt + g + 8 * hh;
+        if (row < nrows) {
+          float4* dst = reinterpret_cast<float4*>(out + (size_t)row * ldo + 32 * cq + 8 * t);
+          dst[0] = make_float4(rnd(acc[mt][0][2 * hh], rn), rnd(acc[mt][1][2 * hh], rn), rnd(acc[mt][2][2 * hh], rn), rnd(acc[mt][3][2 * hh], rn));
+          dst[1] = make_float4(rnd(acc[mt][0][2 * hh + 1], rn), rnd(acc[mt][1][2 * hh + 1], rn), rnd(acc[mt][2][2 * hh + 1], rn), rnd(acc[mt][3][2 * hh + 1], rn));
+        }
+      }
+  }
+}
+
+// softmax over j of the masked, scaled scores in C-fragment layout; S becomes P (pre-dropout). msk bit (nt*4+e) per mt.
+template <int MT, int NT>
+__device__ __forceinline__ void softmax_frag(const AttnArgs& a, float (&S)[MT][NT][4], uint32_t (&msk)[MT], int b, int g, int t) {
+  bool padj[NT][2];
+#pragma unroll
+  for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+      const int j = 8 * nt + 2 * t + e;
+      padj[nt][e] = (a.key_ids != nullptr) && j < a.nk && __ldg(a.key_ids + b * a.nk + j) == a.pad_id;
+    }
+#pragma unroll
+  for (int mt = 0; mt < MT; ++mt) {
+    msk[mt] = 0;
+#pragma unroll
+    for (int hh = 0; hh < 2; ++hh) {
+      const int i = 16 * mt + g + 8 * hh;
+      float mx = -3.0e38f;
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const int j = 8 * nt + 2 * t + e;
+          const bool m = (a.causal && j > i) || padj[nt][e];
+          if (m) msk[mt] |= 1u << (nt * 4 + 2 * hh + e);
+          float s = m ? -1e18f : S[mt][nt][2 * hh + e] * a.scale;
+          if (j >= a.nk) s = -3.0e38f;
+          S[mt][nt][2 * hh + e] = s;
+          mx = fmaxf(mx, s);
+        }
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+      float sum = 0.f;
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const int j = 8 * nt + 2 * t + e;
+          const float p = (j < a.nk) ? __expf(S[mt][nt][2 * hh + e] - mx) : 0.f;
+          S[mt][nt][2 * hh + e] = p;
+          sum += p;
+        }
+      sum += __shfl_xor_sync(0xffffffffu, sum, 1);
+      sum += __shfl_xor_sync(0xffffffffu, sum, 2);
+      const float inv = 1.f / sum;
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+        for (int e = 0; e < 2; ++e) S[mt][nt][2 * hh + e] *= inv;
+    }
+  }
+}
+
+static constexpr int ATT_TC_WARPS = 4;
+
+template <int MT, int NT>
+__global__ void __launch_bounds__(ATT_TC_WARPS * 32)
+attention_fwd_tc_kernel(AttnArgs a, float* __restrict__ out, int ldo) {
+  const int bh = blockIdx.x * ATT_TC_WARPS + (threadIdx.x >> 5);
+  if (bh >= a.B * a.nh) return;
+  const int b = bh / a.nh, h = bh - b * a.nh, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  const float* Q = a.q + (size_t)b * a.nq * a.ldq + h * 64;
+  const float* K = a.k + (size_t)b * a.nk * a.ldk + h * 64;
+  const float* V = a.v + (size_t)b * a.nk * a.ldv + h * 64;
+  float S[MT][NT][4];
+#pragma unroll
+  for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) S[mt][nt][e] = 0.f;
+  mma_xyT<MT, NT>(S, Q, a.nq, a.ldq, K, a.nk, a.ldk, g, t);
+  uint32_t msk[MT];
+  softmax_frag<MT, NT>(a, S, msk, b, g, t);
+#pragma unroll
+  for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int i = 16 * mt + g + 8 * (e >> 1), j = 8 * nt + 2 * t + (e & 1);
+        float w = S[mt][nt][e];
+        if (a.drop_p > 0.f && i < a.nq && j < a.nk) w *= keep_scale(a, ((size_t)bh * a.nq + i) * a.nk + j);
+        S[mt][nt][e] = tf32_rn(w);
+      }
+  mma_pY_store<MT, NT>(S, V, a.nk, a.ldv, out + (size_t)b * a.nq * ldo + h * 64, a.nq, ldo, g, t, a.rn);
+}
+
+// out[j, :64] = sum_i T[i][j] * X[i, :64] for j < nj, with T ([32][33] floats, rows i, written by this warp in C layout)
+// used as the TRANSPOSED A operand.  Reduction slot t of k-step s is i = 4*MT*t + 2s (slot t+4: i+1), which makes the
+// shared-memory reads of a fragment hit 32 distinct banks for MT = 2.
+template <int MT, int NT>
+__device__ __forceinline__ void mma_TtX_store(const float* T, const float* X, int nx, int ldx, float* out, int nj, int ldo,
+                                              int g, int t, int rn) {
+  constexpr int MTJ = (NT + 1) / 2;
+#pragma unroll
+  for (int cq = 0; cq < 2; ++cq) {
+    float acc[MTJ][4][4];
+#pragma unroll
+    for (int mj = 0; mj < MTJ; ++mj)
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) acc[mj][u][e] = 0.f;
+#pragma unroll
+    for (int s = 0; s < 2 * MT; ++s) {
+      const int i = 4 * MT * t + 2 * s;
+      const float4 x0 = ld4(X, i, nx, ldx, 32 * cq + 4 * g), x1 = ld4(X, i + 1, nx, ldx, 32 * cq + 4 * g);
+      const float* x0a = &x0.x; const float* x1a = &x1.x;
+#pragma unroll
+      for (int mj = 0; mj < MTJ; ++mj) {
+        const int j0 = 16 * mj + g, j1 = j0 + 8;
+        const float a0 = T[i * 33 + j0], a2 = T[(i + 1) * 33 + j0];
+        const float a1 = (j1 < 8 * NT) ? T[i * 33 + j1] : 0.f, a3 = (j1 < 8 * NT) ? T[(i + 1) * 33 + j1] : 0.f;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) mma_tf32(acc[mj][u], a0, a1, a2, a3, x0a[u], x1a[u]);
+      }
+    }
+#pragma unroll
+    for (int mj = 0; mj < MTJ; ++mj)
+#pragma unroll
+      for (int hh = 0; hh < 2; ++hh) {
+        const int row = 16 * mj + g + 8 * hh;
+        if (row < nj) {
+          float4* dst = reinterpret_cast<float4*>(out + (size_t)row * ldo + 32 * cq + 8 * t);
+          dst[0] = make_float4(rnd(acc[mj][0][2 * hh], rn), rnd(acc[mj][1][2 * hh], rn), rnd(acc[mj][2][2 * hh], rn), rnd(acc[mj][3][2 * hh], rn));
+          dst[1] = make_float4(rnd(acc[mj][0][2 * hh + 1], rn), rnd(acc[mj][1][2 * hh + 1], rn), rnd(acc[mj][2][2 * hh + 1], rn), rnd(acc[mj][3][2 * hh + 1], rn));
+        }
+      }
+  }
+}
+
+template <int MT, int NT>
+__global__ void __launch_bounds__(ATT_TC_WARPS * 32)
+attention_bwd_tc_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, float* __restrict__ dq, float* __restrict__ dk,
+                        float* __restrict__ dv, int lddq, int lddk, int lddv) {
+  __shared__ float tsm[ATT_TC_WARPS][2][32 * 33];
+  const int wid = threadIdx.x >> 5;
+  const int bh = blockIdx.x * ATT_TC_WARPS + wid;
+  if (bh >= a.B * a.nh) return;
+  const int b = bh / a.nh, h = bh - b * a.nh, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  const float* Q = a.q + (size_t)b * a.nq * a.ldq + h * 64;
+  const float* K = a.k + (size_t)b * a.nk * a.ldk + h * 64;
+  const float* V = a.v + (size_t)b * a.nk * a.ldv + h * 64;
+  const float* dO = dout + (size_t)b * a.nq * ldo + h * 64;
+  float S[MT][NT][4], dW[MT][NT][4];
+#pragma unroll
+  for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) { S[mt][nt][e] = 0.f; dW[mt][nt][e] = 0.f; }
+  mma_xyT<MT, NT>(S, Q, a.nq, a.ldq, K, a.nk, a.ldk, g, t);      // scores
+  mma_xyT<MT, NT>(dW, dO, a.nq, ldo, V, a.nk, a.ldv, g, t);      // d(post-dropout weights) = dO . V^T
+  uint32_t msk[MT];
+  softmax_frag<MT, NT>(a, S, msk, b, g, t);
+  float* Ws = tsm[wid][0];
+  float* Ds = tsm[wid][1];
+  // S: P -> dS (tf32) ; dW -> W (tf32); both also go to shared memory as the transposed operands of dK / dV
+#pragma unroll
+  for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+    for (int hh = 0; hh < 2; ++hh) {
+      const int i = 16 * mt + g + 8 * hh;
+      float ks[NT][2], dot = 0.f;
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const int j = 8 * nt + 2 * t + e;
+          ks[nt][e] = (a.drop_p > 0.f && i < a.nq && j < a.nk) ? keep_scale(a, ((size_t)bh * a.nq + i) * a.nk + j) : 1.f;
+          const float dP = dW[mt][nt][2 * hh + e] * ks[nt][e];
+          dW[mt][nt][2 * hh + e] = dP;
+          dot += dP * S[mt][nt][2 * hh + e];
+        }
+      dot += __shfl_xor_sync(0xffffffffu, dot, 1);
+      dot += __shfl_xor_sync(0xffffffffu, dot, 2);
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const int j = 8 * nt + 2 * t + e, idx = 2 * hh + e;
+          const float p = S[mt][nt][idx];
+          const bool m = (msk[mt] >> (nt * 4 + idx)) & 1u;
+          const float ds = (m || i >= a.nq) ? 0.f : tf32_rn(p * (dW[mt][nt][idx] - dot) * a.scale);
+          const float w = (i >= a.nq) ? 0.f : tf32_rn(p * ks[nt][e]);
+          S[mt][nt][idx] = ds;
+          Ws[i * 33 + j] = w;
+          Ds[i * 33 + j] = ds;
+        }
+    }
+  __syncwarp();
+  mma_pY_store<MT, NT>(S, K, a.nk, a.ldk, dq + (size_t)b * a.nq * lddq + h * 64, a.nq, lddq, g, t, a.rn);   // dQ = dS . K
+  mma_TtX_store<MT, NT>(Ds, Q, a.nq, a.ldq, dk + (size_t)b * a.nk * lddk + h * 64, a.nk, lddk, g, t, a.rn);  // dK = dS^T . Q
+  mma_TtX_store<MT, NT>(Ws, dO, a.nq, ldo, dv + (size_t)b * a.nk * lddv + h * 64, a.nk, lddv, g, t, a.rn);   // dV = W^T . dO
+}
+
 static int check_attn(const B200iqAttention* p) {
   B200IQ_CHECK_ARG(p && p->q && p->k && p->v, "attention: null pointer");
   B200IQ_CHECK_ARG(p->B > 0 && p->num_heads > 0 && p->nq > 0 && p->nk > 0 && p->head_dim > 0, "attention: bad shape");
@@ -185,6 +459,17 @@ static AttnArgs to_args(const B200iqAttention* p) {
   return a;
 }
 
+static bool tc_ok(const B200iqAttention* p, const void* const* ptrs, int nptr, const int* lds, int nld) {
+  if (!round_mode() || p->head_dim != 64 || p->nq > 32 || p->nk > 32) return false;
+  for (int i = 0; i < nptr; ++i) if (((uintptr_t)ptrs[i]) & 15) return false;
+  for (int i = 0; i < nld; ++i) if (lds[i] & 3) return false;
+  return true;
+}
+#define B200IQ_ATT_DISPATCH(MT_, NT_, CALL) \
+  do { \
+    if (MT_ == 1) { if (NT_ == 1) { CALL(1, 1); } else if (NT_ == 2) { CALL(1, 2); } else if (NT_ == 3) { CALL(1, 3); } else { CALL(1, 4); } } \
+    else          { if (NT_ == 1) { CALL(2, 1); } else if (NT_ == 2) { CALL(2, 2); } else if (NT_ == 3) { CALL(2, 3); } else { CALL(2, 4); } } \
+  } while (0)
 }  // namespace b200iq
 using namespace b200iq;
 
@@ -192,6 +477,17 @@ extern "C" int b200iq_attention_fwd(const B200iqAttention* p, void* stream) {
   if (int rc = check_attn(p)) return rc;
   B200IQ_CHECK_ARG(p->out, "attention_fwd: null out");
   AttnArgs a = to_args(p);
+  {
+    const void* ptrs[] = {p->q, p->k, p->v, p->out};
+    const int lds[] = {p->ldq, p->ldk, p->ldv, p->ldo};
+    if (tc_ok(p, ptrs, 4, lds, 4)) {
+      const int mt = a.nq > 16 ? 2 : 1, nt = (a.nk + 7) / 8, grid = (a.B * a.nh + ATT_TC_WARPS - 1) / ATT_TC_WARPS;
+#define CALL(M_, N_) attention_fwd_tc_kernel<M_, N_><<<grid, ATT_TC_WARPS * 32, 0, (cudaStream_t)stream>>>(a, p->out, p->ldo)
+      B200IQ_ATT_DISPATCH(mt, nt, CALL);
+#undef CALL
+      return launch_status("attention_fwd_tc");
+    }
+  }
   size_t smem = sizeof(float) * ((size_t)(a.nq + 2 * a.nk) * (a.d + 1) + (ATT_THREADS / 32) * a.nk);
   B200IQ_CHECK_ARG(smem <= 227 * 1024, "attention_fwd: tile does not fit shared memory (%zu B)", smem);
   if (smem > 48 * 1024) cudaFuncSetAttribute(attention_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -204,6 +500,17 @@ extern "C" int b200iq_attention_bwd(const B200iqAttention* p, const float* dout,
   if (int rc = check_attn(p)) return rc;
   B200IQ_CHECK_ARG(dout && dq && dk && dv, "attention_bwd: null pointer");
   AttnArgs a = to_args(p);
+  {
+    const void* ptrs[] = {p->q, p->k, p->v, dout, dq, dk, dv};
+    const int lds[] = {p->ldq, p->ldk, p->ldv, p->ldo, lddq, lddk, lddv};
+    if (tc_ok(p, ptrs, 7, lds, 7)) {
+      const int mt = a.nq > 16 ? 2 : 1, nt = (a.nk + 7) / 8, grid = (a.B * a.nh + ATT_TC_WARPS - 1) / ATT_TC_WARPS;
+#define CALL(M_, N_) attention_bwd_tc_kernel<M_, N_><<<grid, ATT_TC_WARPS * 32, 0, (cudaStream_t)stream>>>(a, dout, p->ldo, dq, dk, dv, lddq, lddk, lddv)
+      B200IQ_ATT_DISPATCH(mt, nt, CALL);
+#undef CALL
+      return launch_status("attention_bwd_tc");
+    }
+  }
   size_t smem = sizeof(float) * ((size_t)(2 * a.nq + 2 * a.nk) * (a.d + 1) + 2 * (size_t)a.nq * (a.nk + 1));
   B200IQ_CHECK_ARG(smem <= 227 * 1024, "attention_bwd: tile does not fit shared memory (%zu B)", smem);
   if (smem > 48 * 1024) cudaFuncSetAttribute(attention_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

@@ -198,15 +198,26 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     constexpr int CHUNKS = BN / 32 / 2;
     uint8_t* stg = stg_base + (warp - 2) * 2 * STG_BYTES;
     const bool accum = epi.flags & B200IQ_GEMM_ACCUM;
+    const bool has_r = epi.flags & (B200IQ_GEMM_RESIDUAL | B200IQ_GEMM_RELU_MASK);
+    const bool gate = epi.flags & B200IQ_GEMM_RELU_MASK, relu = epi.flags & B200IQ_GEMM_RELU;
     uint32_t ti = 0, chunk = 0;
+    float g[32];  // residual / relu-gate tile of the NEXT chunk: row r of the tile, column `lane` (coalesced 128-byte rows)
+    auto fetch_g = [&](int row0, int col0) {
+      const int cc = col0 + lane;
+      const float* src = epi.residual + (size_t)row0 * epi.ldr + cc;
+#pragma unroll
+      for (int r = 0; r < 32; ++r) g[r] = (row0 + r < epi.M && cc < epi.N) ? __ldg(src + (size_t)r * epi.ldr) : 0.f;
+    };
     for (int w = blockIdx.x; w < total; w += gridDim.x, ++ti) {
       const int z = w / tiles, r = w - z * tiles, mt = r / n_tiles, nt = r - mt * n_tiles;
       const int m0 = mt * BM, n0 = nt * BN;
       const uint32_t acc = ti & 1, aph = (ti >> 1) & 1;
-      mbar_wait(&tfull_bar[acc], aph);
-      tc_fence_after();
       const int row0 = m0 + q * 32, row = row0 + lane;
       const bool add_bias = (z == 0);
+      // the first chunk's residual tile travels while the MMAs of this tile are still running
+      if (has_r && use_tma_c) fetch_g(row0, n0 + chalf * CHUNKS * 32);
+      mbar_wait(&tfull_bar[acc], aph);
+      tc_fence_after();
 #pragma unroll 1
       for (int c = chalf * CHUNKS; c < (chalf + 1) * CHUNKS; ++c) {
         const int col0 = n0 + c * 32;
@@ -214,57 +225,44 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         uint32_t rr[32];
         tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN + c * 32, rr);
         if (row0 >= epi.M) continue;  // warp-uniform: nothing of this quadrant is inside the matrix
-        const bool row_ok = row < epi.M;
-        if (use_tma_c && (epi.flags & (B200IQ_GEMM_RESIDUAL | B200IQ_GEMM_RELU_MASK)) == 0 && col0 + 32 <= epi.N) {
-          // fast path (no per-element operand): bias read as 8 x float4, no bounds checks
-          uint8_t* buf = stg + (chunk & 1) * STG_BYTES;
-          if (lane == 0) bulk_wait_read<1>();
-          __syncwarp();
-          const bool bias_on = (epi.flags & B200IQ_GEMM_BIAS) && add_bias, relu = epi.flags & B200IQ_GEMM_RELU;
-          const float4* b4 = reinterpret_cast<const float4*>(epi.bias + col0);
-          const bool bvec = bias_on && ((((uintptr_t)(epi.bias + col0)) & 15) == 0);
-#pragma unroll
-          for (int j = 0; j < 32; j += 4) {
-            float4 bb = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (bvec) bb = __ldg(b4 + (j >> 2));
-            else if (bias_on) { bb.x = __ldg(epi.bias + col0 + j); bb.y = __ldg(epi.bias + col0 + j + 1); bb.z = __ldg(epi.bias + col0 + j + 2); bb.w = __ldg(epi.bias + col0 + j + 3); }
-            float4 v;
-            v.x = __uint_as_float(rr[j + 0]) * epi.alpha + bb.x;
-            v.y = __uint_as_float(rr[j + 1]) * epi.alpha + bb.y;
-            v.z = __uint_as_float(rr[j + 2]) * epi.alpha + bb.z;
-            v.w = __uint_as_float(rr[j + 3]) * epi.alpha + bb.w;
-            if (relu) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
-            v.x = rnd(v.x, epi.round); v.y = rnd(v.y, epi.round); v.z = rnd(v.z, epi.round); v.w = rnd(v.w, epi.round);
-            *reinterpret_cast<float4*>(buf + lane * 128 + (((j >> 2) ^ (lane & 7)) << 4)) = v;
-          }
-          fence_async_smem();
-          __syncwarp();
-          if (lane == 0) {
-            if (accum) tma_reduce_add_2d(&tmC, buf, col0, row0); else tma_store_2d(&tmC, buf, col0, row0);
-            bulk_commit();
-          }
-          ++chunk;
-        } else if (use_tma_c) {
+        if (use_tma_c) {
           uint8_t* buf = stg + (chunk & 1) * STG_BYTES;
           if (lane == 0) bulk_wait_read<1>();  // the store that last read this buffer has finished reading
           __syncwarp();
+          if (has_r) {
+            // transpose through the staging buffer (same 128B swizzle as the output tile): lane r later re-reads row r
+#pragma unroll
+            for (int r2 = 0; r2 < 32; ++r2)
+              *reinterpret_cast<float*>(buf + r2 * 128 + ((((lane >> 2) ^ (r2 & 7)) << 4) | ((lane & 3) << 2))) = g[r2];
+            __syncwarp();
+            if (c + 1 < (chalf + 1) * CHUNKS && col0 + 32 < epi.N) fetch_g(row0, col0 + 32);  // in flight during the math below
+          }
+          const bool bias_on = (epi.flags & B200IQ_GEMM_BIAS) && add_bias;
+          const bool full = col0 + 32 <= epi.N;
+          const bool bvec = bias_on && full && ((((uintptr_t)(epi.bias + col0)) & 15) == 0);
+          const float4* b4 = reinterpret_cast<const float4*>(epi.bias + col0);
 #pragma unroll
           for (int j = 0; j < 32; j += 4) {
-            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (row_ok) {
-              if (col0 + j + 3 < epi.N) {
-                v.x = epi_value(__uint_as_float(rr[j + 0]), epi, row, col0 + j + 0, add_bias);
-                v.y = epi_value(__uint_as_float(rr[j + 1]), epi, row, col0 + j + 1, add_bias);
-                v.z = epi_value(__uint_as_float(rr[j + 2]), epi, row, col0 + j + 2, add_bias);
-                v.w = epi_value(__uint_as_float(rr[j + 3]), epi, row, col0 + j + 3, add_bias);
-              } else {
-                float* vv = &v.x;
-                for (int t = 0; t < 4; ++t)
-                  if (col0 + j + t < epi.N) vv[t] = epi_value(__uint_as_float(rr[j + t]), epi, row, col0 + j + t, add_bias);
-              }
+            float4* slot = reinterpret_cast<float4*>(buf + lane * 128 + (((j >> 2) ^ (lane & 7)) << 4));
+            float4 bb = make_float4(0.f, 0.f, 0.f, 0.f), gg = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (bvec) bb = __ldg(b4 + (j >> 2));
+            else if (bias_on) {
+              float* b1 = &bb.x;
+#pragma unroll
+              for (int t = 0; t < 4; ++t) if (col0 + j + t < epi.N) b1[t] = __ldg(epi.bias + col0 + j + t);
             }
-            // 128B swizzle: 16-byte chunk index XOR (row & 7), the layout the C tensor map expects
-            *reinterpret_cast<float4*>(buf + lane * 128 + (((j >> 2) ^ (lane & 7)) << 4)) = v;
+            if (has_r) gg = *slot;
+            float v[4];
+            const float* ga = &gg.x; const float* ba = &bb.x;
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+              float x = __uint_as_float(rr[j + t]) * epi.alpha + ba[t];
+              if (gate) x = ga[t] > 0.f ? x : 0.f; else x += ga[t];
+              if (relu) x = fmaxf(x, 0.f);
+              v[t] = rnd(x, epi.round);
+            }
+            // 128B swizzle: 16-byte chunk index XOR (row & 7), the layout the C tensor map expects; TMA clips M/N edges
+            *slot = make_float4(v[0], v[1], v[2], v[3]);
           }
           fence_async_smem();
           __syncwarp();
@@ -273,7 +271,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             bulk_commit();
           }
           ++chunk;
-        } else if (row_ok) {
+        } else if (row < epi.M) {
           float* crow = epi.C + (size_t)row * epi.ldc;
 #pragma unroll
           for (int j = 0; j < 32; ++j)

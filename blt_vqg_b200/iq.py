@@ -330,7 +330,7 @@ class IQ(nn.Module):
             ops.gemm(xs, wout, lg, bias=bout, fp32_out=True)       # decoder_transformer.py:40
             ops.ce_rows(lg, tflat[r0:r0 + rows], PAD, count, c_rec, terms[0:1], write_grad=backward)
             if backward:
-                ops.gemm(lg, wout, d_dec[r0:r0 + rows], b_t=True)
+                ops.gemm(lg, wout, d_dec[r0:r0 + rows], b_t=True, auto_split=True)
                 tf.grad_w(c, lg, xs, G["decoder.output.weight"], G["decoder.output.bias"])
         d_img = ws.buf("d_img", B, H)
         d_z = None

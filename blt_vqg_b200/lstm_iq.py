@@ -318,7 +318,7 @@ class LSTMIQ(nn.Module):
             ops.gemm(xs, wout, lg, bias=bout, fp32_out=True)                          # decoder_rnn.py:107
             ops.ce_rows(lg, tgt[r0:r0 + n], PAD, count, lam["lambda_gen"], terms[0:1], write_grad=backward)
             if backward:
-                ops.gemm(lg, wout, d_out[r0:r0 + n], b_t=True)
+                ops.gemm(lg, wout, d_out[r0:r0 + n], b_t=True, auto_split=True)
                 tf.grad_w(c, lg, xs, G["decoder.out.weight"], G["decoder.out.bias"])
         # ---- reconstructions from the detached features through a second reparameterisation (old_train_iq.py:145-155)
         z2 = ws.buf("z2", B, Z)

@@ -49,7 +49,7 @@ def _ld(t):
 
 
 def gemm(a, b, out=None, *, a_t=False, b_t=False, bias=None, residual=None, relu=False, relu_mask=None,
-         accumulate=False, split_k=1, alpha=1.0, simt=None, fp32_out=False):
+         accumulate=False, split_k=1, alpha=1.0, simt=None, fp32_out=False, auto_split=False):
     """out[M,N] = epi(alpha * A @ B^T); a is [M,K] ([K,M] if a_t), b is [N,K] ([K,N] if b_t).
     mirrors torch.nn.functional.linear(a, b, bias) (+ fused relu / residual / relu-backward mask)."""
     M, K = (a.shape[1], a.shape[0]) if a_t else a.shape
@@ -59,6 +59,14 @@ def gemm(a, b, out=None, *, a_t=False, b_t=False, bias=None, residual=None, relu
         assert not accumulate
         out = torch.empty(M, N, device=a.device, dtype=torch.float32)
     assert out.shape == (M, N)
+    if auto_split and not _FORCE_SIMT and not simt and not accumulate and residual is None and relu_mask is None and not relu:
+        # skinny output, long reduction (dX of the vocabulary projection: 768 x 512 x 15000 = 24 tiles on 148 SMs):
+        # zero C and let split-K slices TMA-reduce-add into it
+        tiles = ((M + 127) // 128) * ((N + 127) // 128)
+        sk = min(148 // tiles, K // 512) if tiles <= 74 else 1
+        if sk > 1:
+            out.zero_()
+            accumulate, split_k = True, sk
     flags = 0
     if a_t: flags |= L.GEMM_A_MN
     if b_t: flags |= L.GEMM_B_MN

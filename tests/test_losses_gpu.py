@@ -85,6 +85,48 @@ def test_attention_dropout_is_consistent_between_fwd_and_bwd(ops):
             assert fd == pytest.approx(float(g[idx]), rel=2e-2, abs=2e-3)
 
 
+@pytest.mark.parametrize("nq,nk,causal", [(5, 5, False), (21, 21, False), (20, 20, True), (20, 5, False), (32, 32, True), (1, 1, True), (17, 9, False)])
+@pytest.mark.parametrize("drop", [0.0, 0.3])
+def test_attention_tensor_core_path(ops, nq, nk, causal, drop):
+    """head_dim 64 with TF32 rounding on -> the warp-per-head mma.sync kernels; checked against torch autograd (drop=0) and
+    against the exact SIMT kernels under the same Philox key (drop>0: same mask by construction)"""
+    from blt_vqg_b200 import _lib
+    B, nh, d = 9, 3, 64
+    H = nh * d
+    rt = lambda x: ops.round_tf32(x, torch.empty_like(x))
+    q = rt(torch.randn(B * nq, H, device="cuda"))
+    kv = rt(torch.randn(B * nk, 2 * H, device="cuda"))
+    k, v = kv[:, :H], kv[:, H:]  # column slices of a packed buffer (ld = 2H), like the workspace
+    do = rt(torch.randn(B * nq, H, device="cuda"))
+    ids = torch.randint(1, 50, (B, nk), device="cuda", dtype=torch.int32)
+    for b in range(B):
+        ids[b, max(1, nk - b):] = 0
+    if nk > 1:
+        ids[0, 0] = 0
+    key = (drop, 1234, 9 << 40)
+
+    def run():
+        out = torch.empty(B * nq, H, device="cuda")
+        dq, dkv = torch.empty_like(q), torch.empty_like(kv)
+        ops.attention_fwd(q, k, v, out, ids, 0, causal, B, nh, nq, nk, d, *key)
+        ops.attention_bwd(q, k, v, do, dq, dkv[:, :H], dkv[:, H:], ids, 0, causal, B, nh, nq, nk, d, *key)
+        return out, dq, dkv[:, :H].clone(), dkv[:, H:].clone()
+    exact = run()                                   # rounding off: SIMT kernels
+    prev = _lib.lib().b200iq_set_tf32_rounding(1)
+    try:
+        tc = run()                                  # rounding on + d=64 + n<=32: tensor-core kernels
+    finally:
+        _lib.lib().b200iq_set_tf32_rounding(prev)
+    for a, b in zip(tc, exact):
+        assert torch.isfinite(a).all()
+        assert rel(a, b) < 2e-3                     # P / dS are rounded to TF32 (2^-11 relative) before the second MMA
+    if drop == 0.0:
+        qr, kr, vr = (t.clone().requires_grad_(True) for t in (q, k.contiguous(), v.contiguous()))
+        ref = _ref_attention(qr, kr, vr, ids, causal, B, nh, nq, nk, d)
+        ref.backward(do)
+        assert rel(tc[0], ref) < 2e-3 and rel(tc[1], qr.grad) < 2e-3 and rel(tc[2], kr.grad) < 2e-3 and rel(tc[3], vr.grad) < 2e-3
+
+
 def test_ce_rows_and_aux(ops):
     rows, V, T = 300, 1000, 10
     logits = torch.randn(rows, V, device="cuda") * 3
