@@ -67,8 +67,9 @@ class GemmParams(C.Structure):
         ("M", C.c_int), ("N", C.c_int), ("K", C.c_int),
         ("lda", C.c_int), ("ldb", C.c_int), ("ldc", C.c_int), ("ldr", C.c_int),
         ("flags", C.c_int), ("split_k", C.c_int), ("alpha", C.c_float),
+        ("drop_p", C.c_float), ("drop_seed", C.c_uint64), ("drop_offset", C.c_uint64),
     ]
 
 
 GEMM_A_MN, GEMM_B_MN, GEMM_BIAS, GEMM_RELU = 1, 2, 4, 8
-GEMM_RESIDUAL, GEMM_ACCUM, GEMM_SIMT, GEMM_RELU_MASK, GEMM_FP32_OUT = 16, 32, 64, 128, 256
+GEMM_RESIDUAL, GEMM_ACCUM, GEMM_SIMT, GEMM_RELU_MASK, GEMM_FP32_OUT, GEMM_DROPOUT = 16, 32, 64, 128, 256, 512

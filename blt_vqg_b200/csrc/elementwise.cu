@@ -155,16 +155,17 @@ __global__ void colsum_kernel(const float* __restrict__ x, float* __restrict__ o
   atomicAdd(out + c, s);
 }
 
-// dpre = dy * (y > 0), in place on dy allowed; db[c] += colsum(dpre)
+// dpre = scale * dy * (y > 0), in place on dy allowed; db[c] += colsum(dpre).  scale = 1/(1-p) folds the backward of the
+// dropout that follows the relu: a dropped element has y == 0 and is masked by the same test.
 __global__ void relu_bwd_colsum_kernel(const float* dy, const float* __restrict__ y, float* dpre,
-                                       float* __restrict__ db, int M, int N, int rows_per_cta) {
+                                       float* __restrict__ db, int M, int N, int rows_per_cta, float scale, int rn) {
   int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= N) return;
   int r0 = blockIdx.y * rows_per_cta, r1 = min(M, r0 + rows_per_cta);
   float s = 0.f;
   for (int r = r0; r < r1; ++r) {
     size_t i = (size_t)r * N + c;
-    float v = y[i] > 0.f ? dy[i] : 0.f;
+    float v = y[i] > 0.f ? rnd(dy[i] * scale, rn && scale != 1.f) : 0.f;
     dpre[i] = v;
     s += v;
   }
@@ -303,11 +304,11 @@ extern "C" int b200iq_colsum_add(const float* x, float* out, int M, int N, int l
   return launch_status("colsum_add");
 }
 
-extern "C" int b200iq_relu_bwd_colsum(const float* dy, const float* y, float* dpre, float* dbias, int M, int N, void* stream) {
+extern "C" int b200iq_relu_bwd_colsum(const float* dy, const float* y, float* dpre, float* dbias, int M, int N, float scale, void* stream) {
   B200IQ_CHECK_ARG(dy && y && dpre && M > 0 && N > 0, "relu_bwd_colsum: bad args");
   int rows = max(8, ceil_div(M, max(1, sm_count() * 4 / ceil_div(N, 128))));
   dim3 grid(ceil_div(N, 128), ceil_div(M, rows));
-  relu_bwd_colsum_kernel<<<grid, 128, 0, ST>>>(dy, y, dpre, dbias, M, N, rows);
+  relu_bwd_colsum_kernel<<<grid, 128, 0, ST>>>(dy, y, dpre, dbias, M, N, rows, scale, round_mode());
   return launch_status("relu_bwd_colsum");
 }
 

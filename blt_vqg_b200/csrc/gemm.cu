@@ -21,6 +21,7 @@ struct GemmEpi {
   float* C; const float* bias; const float* residual;
   int M, N, ldc, ldr, flags; float alpha;
   int round;  // round C to TF32 (activations / activation gradients); never with ACCUM or FP32_OUT
+  float drop_p, drop_scale; uint64_t drop_seed, drop_offset;  // DROPOUT: keep-mask from Philox(seed; offset + (row*N+col)/4)
 };
 
 // ------------------------------------------------------------------ PTX wrappers
@@ -85,6 +86,13 @@ __device__ __forceinline__ float epi_value(float acc, const GemmEpi& e, int row,
   if (e.flags & B200IQ_GEMM_RESIDUAL) v += __ldg(e.residual + (size_t)row * e.ldr + col);
   if (e.flags & B200IQ_GEMM_RELU) v = fmaxf(v, 0.f);
   if (e.flags & B200IQ_GEMM_RELU_MASK) v = (__ldg(e.residual + (size_t)row * e.ldr + col) > 0.f) ? v : 0.f;
+  if (e.flags & B200IQ_GEMM_DROPOUT) {
+    const size_t i = (size_t)row * e.N + col;
+    const uint64_t ctr = e.drop_offset + (i >> 2);
+    uint32_t r[4];
+    Philox(e.drop_seed)((uint32_t)ctr, (uint32_t)(ctr >> 32), 0u, 0u, r);
+    v = (u32_to_unit(r[i & 3]) > e.drop_p) ? v * e.drop_scale : 0.f;
+  }
   return rnd(v, e.round);
 }
 
@@ -111,7 +119,7 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
 //                             TMA store (or TMA reduce-add for split-K) ; overlaps the next item's main loop
 // The epilogue of the first version wrote one row per thread (32 sectors per store request, ncu profiles/r01_gemm_*); staging
 // through shared memory + TMA makes every global write a full 128-byte line and clips M/N edges in hardware.
-template <int BN, bool A_MN, bool B_MN, int STAGES>
+template <int BN, bool A_MN, bool B_MN, int STAGES, bool FULL_EPI>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const __grid_constant__ CUtensorMap tmC, GemmEpi epi, int m_tiles, int n_tiles, int splits,
@@ -198,8 +206,11 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     constexpr int CHUNKS = BN / 32 / 2;
     uint8_t* stg = stg_base + (warp - 2) * 2 * STG_BYTES;
     const bool accum = epi.flags & B200IQ_GEMM_ACCUM;
-    const bool has_r = epi.flags & (B200IQ_GEMM_RESIDUAL | B200IQ_GEMM_RELU_MASK);
-    const bool gate = epi.flags & B200IQ_GEMM_RELU_MASK, relu = epi.flags & B200IQ_GEMM_RELU;
+    // FULL_EPI = false is the lean instantiation (bias / relu / alpha / rounding only): the residual-gate staging and the
+    // Philox dropout cost registers and issue slots even when their flags are off
+    const bool has_r = FULL_EPI && (epi.flags & (B200IQ_GEMM_RESIDUAL | B200IQ_GEMM_RELU_MASK));
+    const bool gate = FULL_EPI && (epi.flags & B200IQ_GEMM_RELU_MASK), relu = epi.flags & B200IQ_GEMM_RELU;
+    const bool drop = FULL_EPI && (epi.flags & B200IQ_GEMM_DROPOUT);
     uint32_t ti = 0, chunk = 0;
     float g[32];  // residual / relu-gate tile of the NEXT chunk: row r of the tile, column `lane` (coalesced 128-byte rows)
     auto fetch_g = [&](int row0, int col0) {
@@ -252,6 +263,11 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               for (int t = 0; t < 4; ++t) if (col0 + j + t < epi.N) b1[t] = __ldg(epi.bias + col0 + j + t);
             }
             if (has_r) gg = *slot;
+            uint32_t keep[4] = {0u, 0u, 0u, 0u};
+            if (drop) {  // one Philox call covers the 4 consecutive elements of this float4 (N % 4 == 0, ldc == N)
+              const uint64_t ctr = epi.drop_offset + (((size_t)row * epi.N + col0 + j) >> 2);
+              Philox(epi.drop_seed)((uint32_t)ctr, (uint32_t)(ctr >> 32), 0u, 0u, keep);
+            }
             float v[4];
             const float* ga = &gg.x; const float* ba = &bb.x;
 #pragma unroll
@@ -259,6 +275,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               float x = __uint_as_float(rr[j + t]) * epi.alpha + ba[t];
               if (gate) x = ga[t] > 0.f ? x : 0.f; else x += ga[t];
               if (relu) x = fmaxf(x, 0.f);
+              if (drop) x = (u32_to_unit(keep[t]) > epi.drop_p) ? x * epi.drop_scale : 0.f;
               v[t] = rnd(x, epi.round);
             }
             // 128B swizzle: 16-byte chunk index XOR (row & 7), the layout the C tensor map expects; TMA clips M/N edges
@@ -374,13 +391,13 @@ static int make_map(CUtensorMap* tm, const float* base, int rows, int cols, int 
   return 0;
 }
 
-template <int BN, bool A_MN, bool B_MN>
+template <int BN, bool A_MN, bool B_MN, bool FULL_EPI>
 static int launch_tc(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, int use_tma_c, const GemmEpi& e, int K,
                      int split, cudaStream_t st) {
   constexpr int STAGES = (BN == 256) ? 3 : 4;
   constexpr int SMEM = STAGES * (BM * 128 + BN * 128) + EPI_WARPS * 2 * 32 * 128 + 1024;
   static bool attr_done = false;
-  auto kern = gemm_tf32_kernel<BN, A_MN, B_MN, STAGES>;
+  auto kern = gemm_tf32_kernel<BN, A_MN, B_MN, STAGES, FULL_EPI>;
   if (!attr_done) {
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
     attr_done = true;
@@ -423,7 +440,13 @@ extern "C" int b200iq_gemm(const B200iqGemm* p, void* stream) {
                    "gemm: split_k>1 needs ACCUM and a linear epilogue");
   B200IQ_CHECK_ARG(p->lda >= (amn ? p->M : p->K) && p->ldb >= (bmn ? p->N : p->K) && p->ldc >= p->N, "gemm: leading dimension too small");
   const int round = (round_mode() && !(f & (B200IQ_GEMM_ACCUM | B200IQ_GEMM_FP32_OUT | B200IQ_GEMM_SIMT))) ? 1 : 0;
-  GemmEpi e{p->C, p->bias, p->residual, p->M, p->N, p->ldc, p->ldr, f, p->alpha, round};
+  GemmEpi e{p->C, p->bias, p->residual, p->M, p->N, p->ldc, p->ldr, f, p->alpha, round, 0.f, 1.f, 0ull, 0ull};
+  if (f & B200IQ_GEMM_DROPOUT) {
+    B200IQ_CHECK_ARG(p->drop_p > 0.f && p->drop_p < 1.f, "gemm: DROPOUT needs 0 < drop_p < 1");
+    B200IQ_CHECK_ARG(p->ldc == p->N && (p->N & 3) == 0 && split == 1 && !(f & B200IQ_GEMM_ACCUM) && (((uintptr_t)p->C) & 15) == 0,
+                     "gemm: DROPOUT needs a contiguous, 16-byte aligned C with N %% 4 == 0, no split-K / ACCUM");
+    e.drop_p = p->drop_p; e.drop_scale = 1.f / (1.f - p->drop_p); e.drop_seed = p->drop_seed; e.drop_offset = p->drop_offset;
+  }
 
   if (f & B200IQ_GEMM_SIMT) {
     long sam = amn ? 1 : p->lda, sak = amn ? p->lda : 1, sbn = bmn ? 1 : p->ldb, sbk = bmn ? p->ldb : 1;
@@ -446,14 +469,19 @@ extern "C" int b200iq_gemm(const B200iqGemm* p, void* stream) {
   const int use_tma_c = ((p->ldc & 3) == 0 && (((uintptr_t)p->C) & 15) == 0) ? 1 : 0;
   if (use_tma_c) rc = make_map(&tc, p->C, p->M, p->N, p->ldc, 32, false); else memset(&tc, 0, sizeof(tc));
   if (rc) return rc;
-#define B200IQ_LAUNCH(BN_) \
+#define B200IQ_LAUNCH2(BN_, FE_) \
   do { \
-    if (!amn && !bmn) return launch_tc<BN_, false, false>(ta, tb, tc, use_tma_c, e, p->K, split, st); \
-    if (!amn && bmn) return launch_tc<BN_, false, true>(ta, tb, tc, use_tma_c, e, p->K, split, st); \
-    if (amn && !bmn) return launch_tc<BN_, true, false>(ta, tb, tc, use_tma_c, e, p->K, split, st); \
-    return launch_tc<BN_, true, true>(ta, tb, tc, use_tma_c, e, p->K, split, st); \
+    if (!amn && !bmn) return launch_tc<BN_, false, false, FE_>(ta, tb, tc, use_tma_c, e, p->K, split, st); \
+    if (!amn && bmn) return launch_tc<BN_, false, true, FE_>(ta, tb, tc, use_tma_c, e, p->K, split, st); \
+    if (amn && !bmn) return launch_tc<BN_, true, false, FE_>(ta, tb, tc, use_tma_c, e, p->K, split, st); \
+    return launch_tc<BN_, true, true, FE_>(ta, tb, tc, use_tma_c, e, p->K, split, st); \
   } while (0)
+#define B200IQ_LAUNCH(BN_) \
+  do { if (full_epi) B200IQ_LAUNCH2(BN_, true); else B200IQ_LAUNCH2(BN_, false); } while (0)
+  // without a TMA-storable C the per-thread fallback path handles every flag itself (epi_value)
+  const bool full_epi = (f & (B200IQ_GEMM_RESIDUAL | B200IQ_GEMM_RELU_MASK | B200IQ_GEMM_DROPOUT)) != 0;
   if (BN == 256) B200IQ_LAUNCH(256);
   B200IQ_LAUNCH(128);
+#undef B200IQ_LAUNCH2
 #undef B200IQ_LAUNCH
 }

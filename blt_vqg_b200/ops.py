@@ -49,7 +49,7 @@ def _ld(t):
 
 
 def gemm(a, b, out=None, *, a_t=False, b_t=False, bias=None, residual=None, relu=False, relu_mask=None,
-         accumulate=False, split_k=1, alpha=1.0, simt=None, fp32_out=False, auto_split=False):
+         accumulate=False, split_k=1, alpha=1.0, simt=None, fp32_out=False, auto_split=False, dropout=None):
     """out[M,N] = epi(alpha * A @ B^T); a is [M,K] ([K,M] if a_t), b is [N,K] ([K,N] if b_t).
     mirrors torch.nn.functional.linear(a, b, bias) (+ fused relu / residual / relu-backward mask)."""
     M, K = (a.shape[1], a.shape[0]) if a_t else a.shape
@@ -78,10 +78,12 @@ def gemm(a, b, out=None, *, a_t=False, b_t=False, bias=None, residual=None, relu
         residual = relu_mask
     if accumulate: flags |= L.GEMM_ACCUM
     if fp32_out: flags |= L.GEMM_FP32_OUT
+    dp, dseed, doff = dropout if dropout is not None and dropout[0] > 0 else (0.0, 0, 0)
+    if dp > 0: flags |= L.GEMM_DROPOUT
     if simt if simt is not None else _FORCE_SIMT: flags |= L.GEMM_SIMT
     p = L.GemmParams(L.fptr(a), L.fptr(b), L.fptr(out), L.fptr(bias), L.fptr(residual), M, N, K,
                      _ld(a), _ld(b), _ld(out), _ld(residual) if residual is not None else 0,
-                     flags, split_k, float(alpha))
+                     flags, split_k, float(alpha), float(dp), dseed, doff)
     global LAUNCHES
     LAUNCHES += 1
     if GEMM_TRACE is not None:
@@ -160,9 +162,10 @@ def colsum_add(x, out):
     _call("b200iq_colsum_add", _p(x), _p(out), M, N, x.stride(0))
 
 
-def relu_bwd_colsum(dy, y, dpre, dbias):
+def relu_bwd_colsum(dy, y, dpre, dbias, scale=1.0):
+    """dpre = scale * dy * (y > 0); dbias += colsum(dpre)"""
     M, N = y.shape
-    _call("b200iq_relu_bwd_colsum", _p(dy), _p(y), _p(dpre), _p(dbias), M, N)
+    _call("b200iq_relu_bwd_colsum", _p(dy), _p(y), _p(dpre), _p(dbias), M, N, _f(scale))
 
 
 def dropout_(x, p, seed, offset):

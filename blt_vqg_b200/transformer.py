@@ -5,11 +5,15 @@ DecoderLayer :326-364, MultiHeadAttention :486-532, PositionwiseFeedForward :400
 kernel launch sequences over pre-allocated workspace buffers; there is no autograd underneath.
 Every function only enqueues kernels on the current stream (CUDA-graph capturable).
 """
+import os
+
 import torch
 
 from . import ops
 
 PAD = 0
+# forward FFN dropout inside the GEMM epilogue (1) or as the standalone HBM-bound kernel (0); same mask either way
+FUSE_DROPOUT = os.environ.get("B200IQ_FUSE_DROPOUT", "1") == "1"
 
 
 class Workspace:
@@ -189,33 +193,36 @@ def cross_attn_bwd(c, tag, pfx, dout, xn, enc_out, d_enc_out, first, enc_ids, B,
 
 # ------------------------------------------------------------------ position-wise FFN (ReLU after BOTH linears, N1)
 def ffn_fwd(c, tag, pfx, xn, x_res):
+    """relu + dropout after BOTH linears (N1) ride in the GEMM epilogues: h and f2 are written once, post-dropout"""
     M, H = xn.shape
     h = c.ws.buf(tag + ".h", M, c.F)
-    ops.gemm(xn, c.W[pfx + "layers.0.weight"], h, bias=c.P[pfx + "layers.0.bias"], relu=True)
-    ops.dropout_(h, c.relu_drop, *c.key(tag + ".d1"))
     f2 = c.ws.buf(tag + ".f2", M, H)
-    ops.gemm(h, c.W[pfx + "layers.1.weight"], f2, bias=c.P[pfx + "layers.1.bias"], relu=True)
-    ops.dropout_(f2, c.relu_drop, *c.key(tag + ".d2"))
+    if FUSE_DROPOUT:
+        ops.gemm(xn, c.W[pfx + "layers.0.weight"], h, bias=c.P[pfx + "layers.0.bias"], relu=True,
+                 dropout=(c.relu_drop, *c.key(tag + ".d1")))
+        ops.gemm(h, c.W[pfx + "layers.1.weight"], f2, bias=c.P[pfx + "layers.1.bias"], relu=True,
+                 dropout=(c.relu_drop, *c.key(tag + ".d2")))
+    else:
+        ops.gemm(xn, c.W[pfx + "layers.0.weight"], h, bias=c.P[pfx + "layers.0.bias"], relu=True)
+        ops.dropout_(h, c.relu_drop, *c.key(tag + ".d1"))
+        ops.gemm(h, c.W[pfx + "layers.1.weight"], f2, bias=c.P[pfx + "layers.1.bias"], relu=True)
+        ops.dropout_(f2, c.relu_drop, *c.key(tag + ".d2"))
     out = c.ws.buf(tag + ".out", M, H)
     ops.axpby(x_res, f2, out)
     return out
 
 
 def ffn_bwd(c, tag, pfx, dout, xn):
-    """dout: grad wrt (x_res + f2); returns grad wrt xn"""
+    """dout: grad wrt (x_res + f2); returns grad wrt xn.  h and f2 are post-dropout, so (y > 0) is the relu mask AND the
+    keep mask; the dropout backward is just the 1/(1-p) factor (no Philox in the backward)"""
     M, H = xn.shape
     h, f2 = c.ws[tag + ".h"], c.ws[tag + ".f2"]
-    df2 = dout
-    if c.relu_drop > 0:
-        df2 = c.ws.buf("tmp.df2.%d" % M, M, H)
-        ops.axpby(dout, dout, df2, 1.0, 0.0)
-        ops.dropout_(df2, c.relu_drop, *c.key(tag + ".d2"))
+    inv_keep = 1.0 / (1.0 - c.relu_drop)
     dpre2 = c.ws.buf("tmp.dpre2.%d" % M, M, H)
-    ops.relu_bwd_colsum(df2, f2, dpre2, c.G[pfx + "layers.1.bias"])
+    ops.relu_bwd_colsum(dout, f2, dpre2, c.G[pfx + "layers.1.bias"], scale=inv_keep)
     grad_w(c, dpre2, h, c.G[pfx + "layers.1.weight"])
     dh = c.ws.buf("tmp.dh.%d" % M, M, c.F)
-    ops.gemm(dpre2, c.W[pfx + "layers.1.weight"], dh, b_t=True, relu_mask=h)
-    ops.dropout_(dh, c.relu_drop, *c.key(tag + ".d1"))
+    ops.gemm(dpre2, c.W[pfx + "layers.1.weight"], dh, b_t=True, relu_mask=h, alpha=inv_keep)
     grad_w(c, dh, xn, c.G[pfx + "layers.0.weight"], c.G[pfx + "layers.0.bias"])
     dxn = c.ws.buf("tmp.dxn.%d" % M, M, H)
     ops.gemm(dh, c.W[pfx + "layers.0.weight"], dxn, b_t=True)

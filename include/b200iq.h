@@ -45,6 +45,9 @@ int b200iq_set_tf32_rounding(int on);
 #define B200IQ_GEMM_SIMT      64  /* exact-fp32 CUDA-core path instead of tcgen05 TF32 */
 #define B200IQ_GEMM_RELU_MASK 128 /* multiply result by (gate[M,N] > 0): relu backward fused */
 #define B200IQ_GEMM_FP32_OUT  256 /* keep the full fp32 result (logits, returned tensors): no TF32 rounding of C */
+#define B200IQ_GEMM_DROPOUT   512 /* after relu: C *= keep/(1-p), keep from Philox(seed; counter = offset + (row*N+col)/4) — the
+                                     mask b200iq_dropout makes on the contiguous [M,N] tensor (needs ldc == N, N % 4 == 0);
+                                     replaces the nn.Dropout after each FFN linear, transformer_layers.py:405-406 */
 
 typedef struct B200iqGemm {
   const float* A;        /* [M,K] ld=lda, or [K,M] when A_MN */
@@ -57,6 +60,8 @@ typedef struct B200iqGemm {
   int flags;
   int split_k;           /* >=1; >1 needs ACCUM and forbids RELU */
   float alpha;           /* scales A·B before the epilogue */
+  float drop_p;          /* DROPOUT: drop probability in [0,1) */
+  unsigned long long drop_seed, drop_offset; /* DROPOUT: Philox key / counter base */
 } B200iqGemm;
 
 /* C = epilogue(alpha * op(A) · op(B)^T).
@@ -91,7 +96,7 @@ int b200iq_layernorm_bwd(const float* dy, const float* x, const float* gamma, co
 /* out[c] += sum_m x[m,c]  (bias gradients) */
 int b200iq_colsum_add(const float* x, float* out, int M, int N, int ld, void* stream);
 /* dpre = dy * (y > 0); dbias[c] += colsum(dpre) (dbias may be NULL)   replaces: ReLU backward, transformer_layers.py:405 */
-int b200iq_relu_bwd_colsum(const float* dy, const float* y, float* dpre, float* dbias, int M, int N, void* stream);
+int b200iq_relu_bwd_colsum(const float* dy, const float* y, float* dpre, float* dbias, int M, int N, float scale, void* stream);
 /* inverted dropout in place with a Philox4x32-10 mask keyed (seed, offset); re-applying it to the gradient
  * with the same key is the backward.   replaces: nn.Dropout at transformer_layers.py:406,520; base_rnn.py:41 */
 int b200iq_dropout(float* x, size_t n, float p, uint64_t seed, uint64_t offset, void* stream);

@@ -130,6 +130,29 @@ def test_philox_randn_and_dropout(ops):
     assert torch.equal(g, x)  # backward re-creates the same mask
 
 
+@pytest.mark.parametrize("simt", [False, True])
+@pytest.mark.parametrize("M,N,K", [(300, 256, 96), (1000, 2048, 64), (77, 36, 40)])
+def test_gemm_fused_relu_dropout_matches_the_standalone_mask(ops, M, N, K, simt):
+    """GEMM epilogue dropout == the b200iq_dropout mask of the same (seed, offset) on the contiguous output; and the
+    backward needs no Philox: (y > 0) of the post-dropout tensor masks relu and dropout at once, times 1/(1-p)."""
+    a, w, b = torch.randn(M, K, device="cuda"), torch.randn(N, K, device="cuda"), torch.randn(N, device="cuda")
+    key = (0.25, 4321, 3 << 40)
+    y0 = ops.gemm(a, w, bias=b, relu=True, simt=simt)
+    ops.dropout_(y0, *key)
+    y1 = ops.gemm(a, w, bias=b, relu=True, simt=simt, dropout=key)
+    assert torch.equal(y1 > 0, y0 > 0)
+    assert rel(y1, y0) < 1e-6
+    keep = float((y1 > 0).sum()) / float((ops.gemm(a, w, bias=b, relu=True, simt=simt) > 0).sum())
+    assert abs(keep - 0.75) < 0.03
+    dy = torch.randn(M, N, device="cuda")
+    dpre, db = torch.empty_like(dy), torch.zeros(N, device="cuda")
+    ops.relu_bwd_colsum(dy, y1, dpre, db, scale=1 / 0.75)
+    want = dy.clone()
+    ops.dropout_(want, *key)          # dropout backward with the regenerated mask ...
+    want = want * (y0 > 0)            # ... then relu backward
+    assert rel(dpre, want) < 1e-6 and rel(db, want.double().sum(0)) < 1e-5
+
+
 def test_tf32_rounding_mode(ops):
     """b200iq_set_tf32_rounding(1): producers write round-to-nearest TF32 values, so the tensor core's operand truncation
     is a no-op and GEMM results are unbiased; with truncation alone every dot product shrinks by ~7e-4."""
