@@ -2,6 +2,7 @@
 // token-0 adds, LayerNorm fwd/bwd, column sums (bias grads), relu backward, Philox dropout / randn.
 // All are coalesced along the feature dimension and use float4 accesses where the width allows.
 #include "common.cuh"
+#include "rowops.cuh"
 
 namespace b200iq {
 
@@ -278,6 +279,14 @@ extern "C" int b200iq_tok0_scatter_add(const float* src, float* dst, int B, int 
 extern "C" int b200iq_layernorm_fwd(const float* x, const float* gamma, const float* beta, float* y, float* mean, float* rstd,
                                     int M, int H, float eps, void* stream) {
   B200IQ_CHECK_ARG(x && gamma && beta && y && M > 0 && H > 0, "layernorm_fwd: bad args");
+  if ((H == 128 || H == 256 || H == 512 || H == 1024) && (((uintptr_t)x | (uintptr_t)y | (uintptr_t)gamma | (uintptr_t)beta) & 15) == 0) {
+    const int grid = min(ceil_div(M, 8), sm_count() * 8), rn = round_mode();
+    if (H == 128) ln_fwd_warp_kernel<1><<<grid, 256, 0, ST>>>(x, gamma, beta, y, mean, rstd, M, eps, rn);
+    else if (H == 256) ln_fwd_warp_kernel<2><<<grid, 256, 0, ST>>>(x, gamma, beta, y, mean, rstd, M, eps, rn);
+    else if (H == 512) ln_fwd_warp_kernel<4><<<grid, 256, 0, ST>>>(x, gamma, beta, y, mean, rstd, M, eps, rn);
+    else ln_fwd_warp_kernel<8><<<grid, 256, 0, ST>>>(x, gamma, beta, y, mean, rstd, M, eps, rn);
+    return launch_status("layernorm_fwd");
+  }
   layernorm_fwd_kernel<<<ceil_div(M, 8), 256, 0, ST>>>(x, gamma, beta, y, mean, rstd, M, H, eps, round_mode());
   return launch_status("layernorm_fwd");
 }
@@ -286,6 +295,14 @@ extern "C" int b200iq_layernorm_bwd(const float* dy, const float* x, const float
                                     float* dx, float* dgamma, float* dbeta, int M, int H, int accumulate_dx, void* stream) {
   B200IQ_CHECK_ARG(dy && x && gamma && mean && rstd && dx && dgamma && dbeta && M > 0 && H > 0, "layernorm_bwd: bad args");
   B200IQ_CHECK_ARG(H <= 2048, "layernorm_bwd: H=%d > 2048 unsupported", H);
+  if ((H == 128 || H == 256 || H == 512 || H == 1024) && (((uintptr_t)x | (uintptr_t)dy | (uintptr_t)dx | (uintptr_t)gamma) & 15) == 0) {
+    const int grid = min(ceil_div(M, 8), sm_count() * 2), rn = round_mode();
+    if (H == 128) ln_bwd_warp_kernel<1><<<grid, 256, 0, ST>>>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, M, accumulate_dx, rn);
+    else if (H == 256) ln_bwd_warp_kernel<2><<<grid, 256, 0, ST>>>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, M, accumulate_dx, rn);
+    else if (H == 512) ln_bwd_warp_kernel<4><<<grid, 256, 0, ST>>>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, M, accumulate_dx, rn);
+    else ln_bwd_warp_kernel<8><<<grid, 256, 0, ST>>>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, M, accumulate_dx, rn);
+    return launch_status("layernorm_bwd");
+  }
   int ctas = min(M, sm_count() * 4);
   int rows = ceil_div(M, ctas);
   ctas = ceil_div(M, rows);
@@ -298,6 +315,11 @@ extern "C" int b200iq_layernorm_bwd(const float* dy, const float* x, const float
 
 extern "C" int b200iq_colsum_add(const float* x, float* out, int M, int N, int ld, void* stream) {
   B200IQ_CHECK_ARG(x && out && M > 0 && N > 0 && ld >= N, "colsum_add: bad args");
+  if ((N & 3) == 0 && (ld & 3) == 0 && (((uintptr_t)x) & 15) == 0) {
+    const int cx = ceil_div(N, 128), rpc = max(32, ceil_div(M, max(1, sm_count() * 4 / cx)));
+    colsum4_kernel<false><<<dim3(cx, ceil_div(M, rpc)), dim3(32, 8), 0, ST>>>(x, nullptr, nullptr, out, M, N, ld, rpc, 1.f, 0);
+    return launch_status("colsum_add");
+  }
   int rows = max(8, ceil_div(M, max(1, sm_count() * 4 / ceil_div(N, 128))));
   dim3 grid(ceil_div(N, 128), ceil_div(M, rows));
   colsum_kernel<<<grid, 128, 0, ST>>>(x, out, M, N, ld, rows);
@@ -306,6 +328,11 @@ extern "C" int b200iq_colsum_add(const float* x, float* out, int M, int N, int l
 
 extern "C" int b200iq_relu_bwd_colsum(const float* dy, const float* y, float* dpre, float* dbias, int M, int N, float scale, void* stream) {
   B200IQ_CHECK_ARG(dy && y && dpre && M > 0 && N > 0, "relu_bwd_colsum: bad args");
+  if ((N & 3) == 0 && (((uintptr_t)dy | (uintptr_t)y | (uintptr_t)dpre) & 15) == 0) {
+    const int cx = ceil_div(N, 128), rpc = max(32, ceil_div(M, max(1, sm_count() * 4 / cx)));
+    colsum4_kernel<true><<<dim3(cx, ceil_div(M, rpc)), dim3(32, 8), 0, ST>>>(dy, y, dpre, dbias, M, N, N, rpc, scale, round_mode());
+    return launch_status("relu_bwd_colsum");
+  }
   int rows = max(8, ceil_div(M, max(1, sm_count() * 4 / ceil_div(N, 128))));
   dim3 grid(ceil_div(N, 128), ceil_div(M, rows));
   relu_bwd_colsum_kernel<<<grid, 128, 0, ST>>>(dy, y, dpre, dbias, M, N, rows, scale, round_mode());

@@ -68,7 +68,7 @@ def test_embedding_gather_scatter(ops):
 
 
 def test_layernorm_fwd_bwd(ops):
-    for M, H in ((333, 64), (1000, 512), (77, 300)):
+    for M, H in ((333, 64), (1000, 512), (77, 300), (10240, 512), (5, 128), (3001, 1024), (100, 256)):
         x = torch.randn(M, H, device="cuda", requires_grad=True)
         g, b = torch.randn(H, device="cuda", requires_grad=True), torch.randn(H, device="cuda", requires_grad=True)
         y = torch.empty(M, H, device="cuda")
@@ -107,6 +107,14 @@ def test_small_elementwise(ops):
     dpre, dbias = torch.empty_like(dy), torch.zeros(96, device="cuda")
     ops.relu_bwd_colsum(dy, y, dpre, dbias)
     assert torch.equal(dpre, dy * (y > 0)) and rel(dbias, (dy * (y > 0)).double().sum(0)) < 1e-5
+    for M, N in ((10240, 2048), (37, 512), (5000, 100)):   # float4 path incl. ragged row blocks
+        yy, dd = torch.randn(M, N, device="cuda"), torch.randn(M, N, device="cuda")
+        cs = torch.zeros(N, device="cuda")
+        ops.colsum_add(yy, cs)
+        assert rel(cs, yy.double().sum(0)) < 1e-5
+        dp, dbb = torch.empty_like(dd), torch.zeros(N, device="cuda")
+        ops.relu_bwd_colsum(dd, yy, dp, dbb)
+        assert torch.equal(dp, dd * (yy > 0)) and rel(dbb, (dd * (yy > 0)).double().sum(0)) < 1e-5
     out = torch.empty_like(y)
     ops.axpby(y, dy, out, 0.5, -2.0)
     assert rel(out, 0.5 * y - 2.0 * dy) < 1e-6
