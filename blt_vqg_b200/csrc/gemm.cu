@@ -8,6 +8,7 @@
 // what the backward GEMMs (dX = dY.W, dW = dY^T.X) read, so no tensor is ever transposed in HBM.
 // Out-of-bounds rows/cols/k are zero-filled by TMA, so arbitrary M, N, K are handled without padding.
 #include "common.cuh"
+#include <stdlib.h>
 
 namespace b200iq {
 
@@ -71,6 +72,33 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 
+// ---- CTA-pair (cta_group::2) variants: one MMA spans two SMs (M = 256), each CTA feeds its 128 rows of A and HALF of B
+static constexpr uint32_t PEER_MASK = 0xFEFFFFFFu;  // clears the CTA-rank bit of a shared::cluster address -> the pair's leader
+__device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// both CTAs of the pair signal the LEADER's full barrier (the only one the MMA thread waits on)
+__device__ __forceinline__ void tma_load_2d_pair(void* dst, const CUtensorMap* tm, int c0, int c1, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+      ::"r"(smem_u32(dst)), "l"((uint64_t)tm), "r"(c0), "r"(c1), "r"(smem_u32(bar) & PEER_MASK) : "memory");
+}
+__device__ __forceinline__ void umma_tf32_pair(uint32_t tmem_c, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_c), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum) : "memory");
+}
+// completion of all prior MMAs of the pair arrives on the barrier at this offset in BOTH CTAs
+__device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+               ::"r"(smem_u32(bar)), "h"((uint16_t)3) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_leader(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(smem_u32(bar) & PEER_MASK) : "memory");
+}
+
 // shared-memory matrix descriptor, 128B swizzle, sm_100 descriptor version 1
 // layout: 2 = SWIZZLE_128B (16-byte chunks), 1 = SWIZZLE_128B_BASE32B (32-byte chunks; the only
 // swizzle the tensor core accepts for MN-major tf32 operands)
@@ -119,12 +147,13 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
 //                             TMA store (or TMA reduce-add for split-K) ; overlaps the next item's main loop
 // The epilogue of the first version wrote one row per thread (32 sectors per store request, ncu profiles/r01_gemm_*); staging
 // through shared memory + TMA makes every global write a full 128-byte line and clips M/N edges in hardware.
-template <int BN, bool A_MN, bool B_MN, int STAGES, bool FULL_EPI>
+template <int BN, bool A_MN, bool B_MN, int STAGES, bool FULL_EPI, int CTAS>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const __grid_constant__ CUtensorMap tmC, GemmEpi epi, int m_tiles, int n_tiles, int splits,
                  int kblocks_total, int kblocks_per_split, int use_tma_c) {
-  constexpr int A_BYTES = BM * 128, B_BYTES = BN * 128, STAGE_BYTES = A_BYTES + B_BYTES;
+  constexpr int BNL = BN / CTAS;  // rows of B this CTA stages (the pair's MMA reads N/2 from each CTA)
+  constexpr int A_BYTES = BM * 128, B_BYTES = BNL * 128, STAGE_BYTES = A_BYTES + B_BYTES;
   constexpr int STG_BYTES = 32 * 128;  // one 32 x 32 fp32 staging tile
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -134,50 +163,61 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int tiles = m_tiles * n_tiles, total = tiles * splits;
+  const int rank = (CTAS == 2) ? (int)cluster_ctarank() : 0;
+  const int w_first = blockIdx.x / CTAS, w_step = gridDim.x / CTAS;  // work items are dealt to CTAs (or CTA pairs)
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(&tfull_bar[a], 1); mbar_init(&tempty_bar[a], EPI_WARPS); }
+    for (int a = 0; a < 2; ++a) { mbar_init(&tfull_bar[a], 1); mbar_init(&tempty_bar[a], EPI_WARPS * CTAS); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 2) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "n"(2 * BN) : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    if (CTAS == 2) {
+      asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "n"(2 * BN) : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    } else {
+      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "n"(2 * BN) : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
   }
   tc_fence_before();
   __syncthreads();
+  if (CTAS == 2) cluster_sync_all();  // the peer's barriers are initialised before any remote arrive / TMA signal
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_s;
 
   if (warp == 0) {
     if (lane == 0) {
       uint32_t it = 0;
-      for (int w = blockIdx.x; w < total; w += gridDim.x) {
+      auto load = [&](void* dst, const CUtensorMap* tm, int c0, int c1, uint64_t* bar) {
+        if (CTAS == 2) tma_load_2d_pair(dst, tm, c0, c1, bar); else tma_load_2d(dst, tm, c0, c1, bar);
+      };
+      for (int w = w_first; w < total; w += w_step) {
         const int z = w / tiles, r = w - z * tiles, mt = r / n_tiles, nt = r - mt * n_tiles;
-        const int m0 = mt * BM, n0 = nt * BN;
+        const int m0 = (mt * CTAS + rank) * BM, n0 = nt * BN + rank * BNL;
         const int kb0 = z * kblocks_per_split, kb1 = min(kblocks_total, kb0 + kblocks_per_split);
         for (int kb = kb0; kb < kb1; ++kb, ++it) {
           const int s = it % STAGES, ph = (it / STAGES) & 1, k0 = kb * BK;
           mbar_wait(&empty_bar[s], ph ^ 1);
-          mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+          if (rank == 0) mbar_expect_tx(&full_bar[s], STAGE_BYTES * CTAS);  // the leader's barrier counts both CTAs' bytes
           uint8_t* sa = smem + s * STAGE_BYTES;
           uint8_t* sb = sa + A_BYTES;
-          if (!A_MN) tma_load_2d(sa, &tmA, k0, m0, &full_bar[s]);
+          if (!A_MN) load(sa, &tmA, k0, m0, &full_bar[s]);
           else
-            for (int i = 0; i < BM / 32; ++i) tma_load_2d(sa + i * (BK * 128), &tmA, m0 + 32 * i, k0, &full_bar[s]);
-          if (!B_MN) tma_load_2d(sb, &tmB, k0, n0, &full_bar[s]);
+            for (int i = 0; i < BM / 32; ++i) load(sa + i * (BK * 128), &tmA, m0 + 32 * i, k0, &full_bar[s]);
+          if (!B_MN) load(sb, &tmB, k0, n0, &full_bar[s]);
           else
-            for (int i = 0; i < BN / 32; ++i) tma_load_2d(sb + i * (BK * 128), &tmB, n0 + 32 * i, k0, &full_bar[s]);
+            for (int i = 0; i < BNL / 32; ++i) load(sb + i * (BK * 128), &tmB, n0 + 32 * i, k0, &full_bar[s]);
         }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    if (lane == 0 && rank == 0) {
       // instruction descriptor: D=f32, A=B=tf32, majors, N>>3 @17, M>>4 @24
       const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
-                             ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+                             ((uint32_t)(BN >> 3) << 17) | ((uint32_t)((BM * CTAS) >> 4) << 24);
       uint32_t it = 0, ti = 0;
-      for (int w = blockIdx.x; w < total; w += gridDim.x, ++ti) {
+      for (int w = w_first; w < total; w += w_step, ++ti) {
         const int z = w / tiles;
         const int kb0 = z * kblocks_per_split, kb1 = min(kblocks_total, kb0 + kblocks_per_split);
         const uint32_t acc = ti & 1, aph = (ti >> 1) & 1;
@@ -193,11 +233,12 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           for (int k = 0; k < BK / UMMA_K; ++k) {
             const uint64_t ad = A_MN ? umma_desc(sa + k * 1024, BK * 128, 512, 1) : umma_desc(sa + k * 32, 16, 1024, 2);
             const uint64_t bd = B_MN ? umma_desc(sb + k * 1024, BK * 128, 512, 1) : umma_desc(sb + k * 32, 16, 1024, 2);
-            umma_tf32(tacc, ad, bd, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            if (CTAS == 2) umma_tf32_pair(tacc, ad, bd, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            else umma_tf32(tacc, ad, bd, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
           }
-          umma_commit(&empty_bar[s]);
+          if (CTAS == 2) umma_commit_pair(&empty_bar[s]); else umma_commit(&empty_bar[s]);
         }
-        umma_commit(&tfull_bar[acc]);
+        if (CTAS == 2) umma_commit_pair(&tfull_bar[acc]); else umma_commit(&tfull_bar[acc]);
       }
     }
   } else {
@@ -219,9 +260,9 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #pragma unroll
       for (int r = 0; r < 32; ++r) g[r] = (row0 + r < epi.M && cc < epi.N) ? __ldg(src + (size_t)r * epi.ldr) : 0.f;
     };
-    for (int w = blockIdx.x; w < total; w += gridDim.x, ++ti) {
+    for (int w = w_first; w < total; w += w_step, ++ti) {
       const int z = w / tiles, r = w - z * tiles, mt = r / n_tiles, nt = r - mt * n_tiles;
-      const int m0 = mt * BM, n0 = nt * BN;
+      const int m0 = (mt * CTAS + rank) * BM, n0 = nt * BN;
       const uint32_t acc = ti & 1, aph = (ti >> 1) & 1;
       const int row0 = m0 + q * 32, row = row0 + lane;
       const bool add_bias = (z == 0);
@@ -300,15 +341,17 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+      if (lane == 0) { if (CTAS == 2) mbar_arrive_leader(&tempty_bar[acc]); else mbar_arrive(&tempty_bar[acc]); }
     }
     if (lane == 0) bulk_wait_all();  // every queued TMA store has landed before the CTA exits
   }
   tc_fence_before();
   __syncthreads();
+  if (CTAS == 2) cluster_sync_all();  // no CTA of the pair leaves (or frees TMEM) while the other may still touch it
   if (warp == 2) {
     tc_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(2 * BN) : "memory");
+    if (CTAS == 2) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(2 * BN) : "memory");
+    else asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(2 * BN) : "memory");
   }
 }
 
@@ -391,13 +434,13 @@ static int make_map(CUtensorMap* tm, const float* base, int rows, int cols, int 
   return 0;
 }
 
-template <int BN, bool A_MN, bool B_MN, bool FULL_EPI>
+template <int BN, bool A_MN, bool B_MN, bool FULL_EPI, int CTAS>
 static int launch_tc(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, int use_tma_c, const GemmEpi& e, int K,
                      int split, cudaStream_t st) {
-  constexpr int STAGES = (BN == 256) ? 3 : 4;
-  constexpr int SMEM = STAGES * (BM * 128 + BN * 128) + EPI_WARPS * 2 * 32 * 128 + 1024;
+  constexpr int STAGES = (CTAS == 2) ? 5 : (BN == 256) ? 3 : 4;
+  constexpr int SMEM = STAGES * (BM * 128 + (BN / CTAS) * 128) + EPI_WARPS * 2 * 32 * 128 + 1024;
   static bool attr_done = false;
-  auto kern = gemm_tf32_kernel<BN, A_MN, B_MN, STAGES, FULL_EPI>;
+  auto kern = gemm_tf32_kernel<BN, A_MN, B_MN, STAGES, FULL_EPI, CTAS>;
   if (!attr_done) {
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
     attr_done = true;
@@ -406,25 +449,57 @@ static int launch_tc(const CUtensorMap& ta, const CUtensorMap& tb, const CUtenso
   if (split > kblocks) split = kblocks;
   int per = ceil_div(kblocks, split);
   split = ceil_div(kblocks, per);
-  const int m_tiles = ceil_div(e.M, BM), n_tiles = ceil_div(e.N, BN);
+  const int m_tiles = ceil_div(e.M, BM * CTAS), n_tiles = ceil_div(e.N, BN);
   const int total = m_tiles * n_tiles * split;
-  const int grid = total < sm_count() ? total : sm_count();
-  kern<<<grid, GEMM_THREADS, SMEM, st>>>(ta, tb, tc, e, m_tiles, n_tiles, split, kblocks, per, use_tma_c);
+  const int slots = sm_count() / CTAS;
+  const int grid = (total < slots ? total : slots) * CTAS;
+  if (CTAS == 1) {
+    kern<<<grid, GEMM_THREADS, SMEM, st>>>(ta, tb, tc, e, m_tiles, n_tiles, split, kblocks, per, use_tma_c);
+  } else {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(GEMM_THREADS); cfg.dynamicSmemBytes = SMEM; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    cudaError_t err = cudaLaunchKernelEx(&cfg, kern, ta, tb, tc, e, m_tiles, n_tiles, split, kblocks, per, use_tma_c);
+    if (err != cudaSuccess) { set_error("gemm_tf32_kernel<pair>: %s", cudaGetErrorString(err)); return (int)err; }
+  }
   return launch_status("gemm_tf32_kernel");
 }
 
 // 128 x 256 tiles halve the B-operand traffic per flop but quantise worse: pick by rounds over the SMs x relative tile cost
-static int pick_bn(int M, int N, int split) {
+// returns 128 / 256 (one CTA per tile) or 512 = CTA pair (cta_group::2, 256 x 256 per pair): per k-block a CTA pulls
+// 32 KB from L2 for a 128x128 tile, 48 KB for 128x256, and 32 KB for its 128x256 half of a pair's tile.
+static int g_force_tile = 0;  // B200IQ_GEMM_TILE=128|256|512 (tuning / tests)
+static int pick_bn(int M, int N, int K, int split, bool heavy_epi) {
+  static bool env_done = false;
+  if (!env_done) { const char* v = getenv("B200IQ_GEMM_TILE"); g_force_tile = v ? atoi(v) : 0; env_done = true; }
+  const bool pair_ok = N > 128 && M > 128;
+  if (g_force_tile == 512) return pair_ok ? 512 : 128;
+  if (g_force_tile == 128 || g_force_tile == 256) return N <= 128 ? 128 : g_force_tile;
   if (N <= 128) return 128;
   const int sms = sm_count();
   const long t128 = (long)ceil_div(M, BM) * ceil_div(N, 128) * split, t256 = (long)ceil_div(M, BM) * ceil_div(N, 256) * split;
+  const long t2 = (long)ceil_div(M, 2 * BM) * ceil_div(N, 256) * split;
   const double c128 = (double)((t128 + sms - 1) / sms) * 1.15, c256 = (double)((t256 + sms - 1) / sms) * 2.0;
+  const double c2 = (double)((t2 + sms / 2 - 1) / (sms / 2)) * 1.6;
+  // measured (cfg3 shapes): pairs win 20 % when the reduction is long; at K = 512 the epilogue dominates and a residual /
+  // gate epilogue on a 128 x 256 half-tile loses to 128 x 128 tiles
+  if (pair_ok && K / split >= 1024 && !heavy_epi && c2 <= c128 && c2 <= c256) return 512;
   return c256 < c128 ? 256 : 128;
 }
 
 }  // namespace b200iq
 
 using namespace b200iq;
+
+extern "C" int b200iq_set_gemm_tile(int tile) {
+  pick_bn(256, 256, 256, 1, false);  // make sure the environment default has been read before it is overridden
+  const int prev = g_force_tile;
+  g_force_tile = tile;
+  return prev;
+}
 
 extern "C" int b200iq_gemm(const B200iqGemm* p, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
@@ -460,28 +535,30 @@ extern "C" int b200iq_gemm(const B200iqGemm* p, void* stream) {
   B200IQ_CHECK_ARG((p->lda & 3) == 0 && (p->ldb & 3) == 0, "gemm: lda/ldb must be multiples of 4 (lda=%d ldb=%d)", p->lda, p->ldb);
   CUtensorMap ta, tb, tc;
   int rc;
-  const int BN = pick_bn(p->M, p->N, split);
+  const int tile = pick_bn(p->M, p->N, p->K, split, (f & (B200IQ_GEMM_RESIDUAL | B200IQ_GEMM_RELU_MASK)) != 0);
+  const int BN = tile == 512 ? 256 : tile, BNL = tile == 512 ? 128 : tile;
   if (!amn) rc = make_map(&ta, p->A, p->M, p->K, p->lda, BM, false); else rc = make_map(&ta, p->A, p->K, p->M, p->lda, BK, true);
   if (rc) return rc;
-  if (!bmn) rc = make_map(&tb, p->B, p->N, p->K, p->ldb, BN, false); else rc = make_map(&tb, p->B, p->K, p->N, p->ldb, BK, true);
+  if (!bmn) rc = make_map(&tb, p->B, p->N, p->K, p->ldb, BNL, false); else rc = make_map(&tb, p->B, p->K, p->N, p->ldb, BK, true);
   if (rc) return rc;
   // C goes out through TMA (32 x 32 boxes, 128B swizzle) when its pitch / base allow it; else per-thread stores
   const int use_tma_c = ((p->ldc & 3) == 0 && (((uintptr_t)p->C) & 15) == 0) ? 1 : 0;
   if (use_tma_c) rc = make_map(&tc, p->C, p->M, p->N, p->ldc, 32, false); else memset(&tc, 0, sizeof(tc));
   if (rc) return rc;
-#define B200IQ_LAUNCH2(BN_, FE_) \
+#define B200IQ_LAUNCH2(BN_, FE_, CT_) \
   do { \
-    if (!amn && !bmn) return launch_tc<BN_, false, false, FE_>(ta, tb, tc, use_tma_c, e, p->K, split, st); \
-    if (!amn && bmn) return launch_tc<BN_, false, true, FE_>(ta, tb, tc, use_tma_c, e, p->K, split, st); \
-    if (amn && !bmn) return launch_tc<BN_, true, false, FE_>(ta, tb, tc, use_tma_c, e, p->K, split, st); \
-    return launch_tc<BN_, true, true, FE_>(ta, tb, tc, use_tma_c, e, p->K, split, st); \
+    if (!amn && !bmn) return launch_tc<BN_, false, false, FE_, CT_>(ta, tb, tc, use_tma_c, e, p->K, split, st); \
+    if (!amn && bmn) return launch_tc<BN_, false, true, FE_, CT_>(ta, tb, tc, use_tma_c, e, p->K, split, st); \
+    if (amn && !bmn) return launch_tc<BN_, true, false, FE_, CT_>(ta, tb, tc, use_tma_c, e, p->K, split, st); \
+    return launch_tc<BN_, true, true, FE_, CT_>(ta, tb, tc, use_tma_c, e, p->K, split, st); \
   } while (0)
-#define B200IQ_LAUNCH(BN_) \
-  do { if (full_epi) B200IQ_LAUNCH2(BN_, true); else B200IQ_LAUNCH2(BN_, false); } while (0)
+#define B200IQ_LAUNCH(BN_, CT_) \
+  do { if (full_epi) B200IQ_LAUNCH2(BN_, true, CT_); else B200IQ_LAUNCH2(BN_, false, CT_); } while (0)
   // without a TMA-storable C the per-thread fallback path handles every flag itself (epi_value)
   const bool full_epi = (f & (B200IQ_GEMM_RESIDUAL | B200IQ_GEMM_RELU_MASK | B200IQ_GEMM_DROPOUT)) != 0;
-  if (BN == 256) B200IQ_LAUNCH(256);
-  B200IQ_LAUNCH(128);
+  if (tile == 512) B200IQ_LAUNCH(256, 2);
+  if (BN == 256) B200IQ_LAUNCH(256, 1);
+  B200IQ_LAUNCH(128, 1);
 #undef B200IQ_LAUNCH2
 #undef B200IQ_LAUNCH
 }

@@ -74,6 +74,10 @@ typedef struct B200iqGemm {
  * TMEM accumulator -> tcgen05.ld epilogue.  Needs 16-byte aligned bases and
  * leading dimensions that are multiples of 4 floats. */
 int b200iq_gemm(const B200iqGemm* p, void* stream);
+/* tile policy of the tcgen05 path: 0 = automatic (default), 128 / 256 = one CTA per 128 x tile output tile,
+ * 512 = CTA pairs (tcgen05.mma.cta_group::2, 256 x 256 per pair) wherever M, N > 128.  Returns the previous setting.
+ * Environment default: B200IQ_GEMM_TILE. */
+int b200iq_set_gemm_tile(int tile);
 
 /* ---------------------------------------------------------- row / elementwise ops */
 /* out[m,:] = table[ids[m],:]   replaces: nn.Embedding fwd, models/iq.py:71-78 (also decoder_rnn.py:102, encoder_rnn.py:78) */

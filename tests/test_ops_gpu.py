@@ -21,7 +21,12 @@ def rel(a, b):
 
 @pytest.mark.parametrize("M,N,K", [(128, 128, 32), (256, 384, 300), (1000, 200, 1024), (37, 52, 20), (640, 15000, 512)])
 @pytest.mark.parametrize("a_t,b_t", [(False, False), (False, True), (True, False), (True, True)])
-def test_gemm_all_layouts(ops, M, N, K, a_t, b_t):
+@pytest.mark.parametrize("tile", [0, 512])
+def test_gemm_all_layouts(ops, M, N, K, a_t, b_t, tile, request):
+    """tile=512 forces the CTA-pair kernel (tcgen05.mma.cta_group::2, 256 x 256 per pair) wherever M, N > 128"""
+    from blt_vqg_b200 import _lib
+    prev = _lib.lib().b200iq_set_gemm_tile(tile)
+    request.addfinalizer(lambda: _lib.lib().b200iq_set_gemm_tile(prev))
     if (a_t and M % 4) or (b_t and N % 4) or (not a_t and K % 4) or (not b_t and K % 4):
         pytest.skip("TMA needs 16-byte row pitch")
     dev = "cuda"
@@ -40,6 +45,28 @@ def test_gemm_all_layouts(ops, M, N, K, a_t, b_t):
         gate = torch.randn(M, N, device=dev)
         out = ops.gemm(Aa, Bb, a_t=a_t, b_t=b_t, relu_mask=gate, simt=simt)
         assert rel(out, ref * (gate > 0)) < tol
+
+
+@pytest.mark.parametrize("tile", [128, 256, 512])
+def test_gemm_tile_policies_agree_on_multi_wave_shapes(ops, tile, request):
+    """every tile policy on shapes with several persistent waves, ragged edges and split-K (the cfg3 GEMM shapes, scaled)"""
+    from blt_vqg_b200 import _lib
+    prev = _lib.lib().b200iq_set_gemm_tile(tile)
+    request.addfinalizer(lambda: _lib.lib().b200iq_set_gemm_tile(prev))
+    for M, N, K, a_t, b_t, sk in ((10240, 2048, 512, False, False, 1), (10240, 512, 2048, False, True, 1), (5000, 1000, 512, False, False, 1),
+                                  (512, 2048, 10240, True, True, 4), (768, 15000, 512, False, False, 1), (300, 260, 96, False, True, 1)):
+        A, B = torch.randn(M, K, device="cuda"), torch.randn(N, K, device="cuda")
+        Aa = A.t().contiguous() if a_t else A
+        Bb = B.t().contiguous() if b_t else B
+        ref = A.double() @ B.double().t()
+        if sk > 1:
+            acc = torch.ones(M, N, device="cuda")
+            ops.gemm(Aa, Bb, acc, a_t=a_t, b_t=b_t, accumulate=True, split_k=sk)
+            assert rel(acc, ref + 1.0) < 2e-3
+        else:
+            bias, gate = torch.randn(N, device="cuda"), torch.randn(M, N, device="cuda")
+            assert rel(ops.gemm(Aa, Bb, a_t=a_t, b_t=b_t, bias=bias, relu=True), torch.relu(ref + bias.double())) < 2e-3
+            assert rel(ops.gemm(Aa, Bb, a_t=a_t, b_t=b_t, relu_mask=gate), ref * (gate > 0)) < 2e-3
 
 
 def test_gemm_rejects_bad_arguments(ops):
