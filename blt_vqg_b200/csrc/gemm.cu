@@ -147,7 +147,7 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
 //                             TMA store (or TMA reduce-add for split-K) ; overlaps the next item's main loop
 // The epilogue of the first version wrote one row per thread (32 sectors per store request, ncu profiles/r01_gemm_*); staging
 // through shared memory + TMA makes every global write a full 128-byte line and clips M/N edges in hardware.
-template <int BN, bool A_MN, bool B_MN, int STAGES, bool FULL_EPI, int CTAS>
+template <int BN, bool A_MN, bool B_MN, int STAGES, int EPI, int CTAS>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const __grid_constant__ CUtensorMap tmC, GemmEpi epi, int m_tiles, int n_tiles, int splits,
@@ -247,11 +247,12 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     constexpr int CHUNKS = BN / 32 / 2;
     uint8_t* stg = stg_base + (warp - 2) * 2 * STG_BYTES;
     const bool accum = epi.flags & B200IQ_GEMM_ACCUM;
-    // FULL_EPI = false is the lean instantiation (bias / relu / alpha / rounding only): the residual-gate staging and the
-    // Philox dropout cost registers and issue slots even when their flags are off
-    const bool has_r = FULL_EPI && (epi.flags & (B200IQ_GEMM_RESIDUAL | B200IQ_GEMM_RELU_MASK));
-    const bool gate = FULL_EPI && (epi.flags & B200IQ_GEMM_RELU_MASK), relu = epi.flags & B200IQ_GEMM_RELU;
-    const bool drop = FULL_EPI && (epi.flags & B200IQ_GEMM_DROPOUT);
+    // EPI: 0 = lean (bias / relu / alpha / rounding), 1 = + residual or relu-gate tile, 2 = + Philox dropout.  Separate
+    // instantiations keep each unrolled epilogue body inside the instruction cache: with everything in one body the dropout
+    // kernel was 8.7k SASS instructions and its epilogue warps stalled on instruction fetch (ncu: stall_no_inst dominant).
+    const bool has_r = EPI == 1 && (epi.flags & (B200IQ_GEMM_RESIDUAL | B200IQ_GEMM_RELU_MASK));
+    const bool gate = EPI == 1 && (epi.flags & B200IQ_GEMM_RELU_MASK), relu = epi.flags & B200IQ_GEMM_RELU;
+    const bool drop = EPI == 2;
     uint32_t ti = 0, chunk = 0;
     float g[32];  // residual / relu-gate tile of the NEXT chunk: row r of the tile, column `lane` (coalesced 128-byte rows)
     auto fetch_g = [&](int row0, int col0) {
@@ -329,14 +330,22 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             bulk_commit();
           }
           ++chunk;
-        } else if (row < epi.M) {
-          float* crow = epi.C + (size_t)row * epi.ldc;
+        } else {
+          // C cannot go through TMA (pitch / base not 16-byte aligned): rare, so compact code matters more than speed —
+          // park the row in the staging buffer and run a rolled loop over it
+          float* mine = reinterpret_cast<float*>(stg + lane * 128);
 #pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (col0 + j < epi.N) {
-              const float v = epi_value(__uint_as_float(rr[j]), epi, row, col0 + j, add_bias);
-              if (accum) atomicAdd(crow + col0 + j, v); else crow[col0 + j] = v;
-            }
+          for (int j = 0; j < 32; j += 4)
+            *reinterpret_cast<uint4*>(mine + j) = make_uint4(rr[j], rr[j + 1], rr[j + 2], rr[j + 3]);
+          if (row < epi.M) {
+            float* crow = epi.C + (size_t)row * epi.ldc;
+#pragma unroll 1
+            for (int j = 0; j < 32; ++j)
+              if (col0 + j < epi.N) {
+                const float v = epi_value(mine[j], epi, row, col0 + j, add_bias);
+                if (accum) atomicAdd(crow + col0 + j, v); else crow[col0 + j] = v;
+              }
+          }
         }
       }
       tc_fence_before();
@@ -434,13 +443,13 @@ static int make_map(CUtensorMap* tm, const float* base, int rows, int cols, int 
   return 0;
 }
 
-template <int BN, bool A_MN, bool B_MN, bool FULL_EPI, int CTAS>
+template <int BN, bool A_MN, bool B_MN, int EPI, int CTAS>
 static int launch_tc(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, int use_tma_c, const GemmEpi& e, int K,
                      int split, cudaStream_t st) {
   constexpr int STAGES = (CTAS == 2) ? 5 : (BN == 256) ? 3 : 4;
   constexpr int SMEM = STAGES * (BM * 128 + (BN / CTAS) * 128) + EPI_WARPS * 2 * 32 * 128 + 1024;
   static bool attr_done = false;
-  auto kern = gemm_tf32_kernel<BN, A_MN, B_MN, STAGES, FULL_EPI, CTAS>;
+  auto kern = gemm_tf32_kernel<BN, A_MN, B_MN, STAGES, EPI, CTAS>;
   if (!attr_done) {
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
     attr_done = true;
@@ -553,9 +562,14 @@ extern "C" int b200iq_gemm(const B200iqGemm* p, void* stream) {
     return launch_tc<BN_, true, true, FE_, CT_>(ta, tb, tc, use_tma_c, e, p->K, split, st); \
   } while (0)
 #define B200IQ_LAUNCH(BN_, CT_) \
-  do { if (full_epi) B200IQ_LAUNCH2(BN_, true, CT_); else B200IQ_LAUNCH2(BN_, false, CT_); } while (0)
+  do { \
+    if (epi_mode == 2) return launch_tc<BN_, false, false, 2, CT_>(ta, tb, tc, use_tma_c, e, p->K, split, st); \
+    if (epi_mode == 1) B200IQ_LAUNCH2(BN_, 1, CT_); else B200IQ_LAUNCH2(BN_, 0, CT_); \
+  } while (0)
   // without a TMA-storable C the per-thread fallback path handles every flag itself (epi_value)
-  const bool full_epi = (f & (B200IQ_GEMM_RESIDUAL | B200IQ_GEMM_RELU_MASK | B200IQ_GEMM_DROPOUT)) != 0;
+  const int epi_mode = (f & B200IQ_GEMM_DROPOUT) ? 2 : (f & (B200IQ_GEMM_RESIDUAL | B200IQ_GEMM_RELU_MASK)) ? 1 : 0;
+  B200IQ_CHECK_ARG(epi_mode != 2 || (!amn && !bmn && !(f & (B200IQ_GEMM_RESIDUAL | B200IQ_GEMM_RELU_MASK))),
+                   "gemm: the tcgen05 DROPOUT epilogue takes K-major A and B and no residual / gate");
   if (tile == 512) B200IQ_LAUNCH(256, 2);
   if (BN == 256) B200IQ_LAUNCH(256, 1);
   B200IQ_LAUNCH(128, 1);
