@@ -481,21 +481,23 @@ static int launch_tc(const CUtensorMap& ta, const CUtensorMap& tb, const CUtenso
 // returns 128 / 256 (one CTA per tile) or 512 = CTA pair (cta_group::2, 256 x 256 per pair): per k-block a CTA pulls
 // 32 KB from L2 for a 128x128 tile, 48 KB for 128x256, and 32 KB for its 128x256 half of a pair's tile.
 static int g_force_tile = 0;  // B200IQ_GEMM_TILE=128|256|512 (tuning / tests)
-static int pick_bn(int M, int N, int K, int split, bool heavy_epi) {
+static int pick_bn(int M, int N, int K, int split, bool heavy_epi, bool dropout_epi = false) {
   static bool env_done = false;
   if (!env_done) { const char* v = getenv("B200IQ_GEMM_TILE"); g_force_tile = v ? atoi(v) : 0; env_done = true; }
   const bool pair_ok = N > 128 && M > 128;
   if (g_force_tile == 512) return pair_ok ? 512 : 128;
   if (g_force_tile == 128 || g_force_tile == 256) return N <= 128 ? 128 : g_force_tile;
   if (N <= 128) return 128;
+  // measured on the cfg3 shapes (scripts/gpu_gemm_sweep.py, profiles/r01g_gemm_sweep.txt):
+  //  * residual / relu-gate epilogues are epilogue-bound: 128 x 128 tiles (2 chunks per epilogue warp and tile) win everywhere
+  //  * dropout epilogues: pairs once the reduction is long enough to hide them (K >= 1024), else 256 / 128 by tile count
+  //  * everything else: CTA pairs (20-35 % faster than 128 x 256 at K >= 1536, 5-10 % at K = 512)
+  if (heavy_epi) return 128;
+  if (dropout_epi) return (pair_ok && K / split >= 1024) ? 512 : ((long)M * N >= (8192L * 2048) ? 256 : 128);
+  if (pair_ok) return 512;
   const int sms = sm_count();
   const long t128 = (long)ceil_div(M, BM) * ceil_div(N, 128) * split, t256 = (long)ceil_div(M, BM) * ceil_div(N, 256) * split;
-  const long t2 = (long)ceil_div(M, 2 * BM) * ceil_div(N, 256) * split;
   const double c128 = (double)((t128 + sms - 1) / sms) * 1.15, c256 = (double)((t256 + sms - 1) / sms) * 2.0;
-  const double c2 = (double)((t2 + sms / 2 - 1) / (sms / 2)) * 1.6;
-  // measured (cfg3 shapes): pairs win 20 % when the reduction is long; at K = 512 the epilogue dominates and a residual /
-  // gate epilogue on a 128 x 256 half-tile loses to 128 x 128 tiles
-  if (pair_ok && K / split >= 1024 && !heavy_epi && c2 <= c128 && c2 <= c256) return 512;
   return c256 < c128 ? 256 : 128;
 }
 
@@ -544,7 +546,7 @@ extern "C" int b200iq_gemm(const B200iqGemm* p, void* stream) {
   B200IQ_CHECK_ARG((p->lda & 3) == 0 && (p->ldb & 3) == 0, "gemm: lda/ldb must be multiples of 4 (lda=%d ldb=%d)", p->lda, p->ldb);
   CUtensorMap ta, tb, tc;
   int rc;
-  const int tile = pick_bn(p->M, p->N, p->K, split, (f & (B200IQ_GEMM_RESIDUAL | B200IQ_GEMM_RELU_MASK)) != 0);
+  const int tile = pick_bn(p->M, p->N, p->K, split, (f & (B200IQ_GEMM_RESIDUAL | B200IQ_GEMM_RELU_MASK)) != 0, (f & B200IQ_GEMM_DROPOUT) != 0);
   const int BN = tile == 512 ? 256 : tile, BNL = tile == 512 ? 128 : tile;
   if (!amn) rc = make_map(&ta, p->A, p->M, p->K, p->lda, BM, false); else rc = make_map(&ta, p->A, p->K, p->M, p->lda, BK, true);
   if (rc) return rc;
