@@ -38,6 +38,7 @@ def parse():
     ap.add_argument("--batch", type=int, default=0, help="per-GPU batch (default: the workload's)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
+    ap.add_argument("--no-secondary", action="store_true", help="skip the LSTM (configs[1]) measurement beside the transformer headline")
     ap.add_argument("--cpu-batch", type=int, default=64, help="bounded CPU sample: batch size of the oracle step")
     return ap.parse_args()
 
@@ -233,6 +234,93 @@ def gemm_roofline(ts, model, args, dev_batches, peaks):
     return roof, detail
 
 
+def measure(args, cfg, config, dp, rank, world, local_rank, roofline=True, cpu_arm=True):
+    """one workload on this rank: device-timed value, end-to-end value, roofline of the dominant kernel, CPU arm"""
+    import torch.distributed as dist
+    dist_on = world > 1
+    from blt_vqg_b200 import ops
+    model, ts = build_ours(args, cfg, dp)
+    hb = host_batches(cfg, 4, rank)
+    db = [{k: v.cuda(non_blocking=True) for k, v in b.items()} for b in hb]
+    torch.cuda.synchronize()
+
+    def dev_step(i):
+        ts.step(*step_inputs(args.workload, db[i % len(db)]))
+
+    sinks = [torch.zeros(8).pin_memory() for _ in range(2)]
+    sink_ev = [torch.cuda.Event() for _ in range(2)]
+    seen = []
+
+    def e2e_step(i):
+        # every step: H2D of this step's inputs from pinned host memory (inside the call) and a D2H read of its loss terms.
+        # The read is double-buffered: step i's terms are consumed on the host after step i+1 has been queued, so the host
+        # keeps launching while the device works (an async logger; the reference's .item() blocks instead).
+        b = hb[i % len(hb)]
+        terms = ts.step(*step_inputs(args.workload, b))
+        k = i & 1
+        if i >= 2:
+            sink_ev[k].synchronize()
+            seen.append(float(sinks[k][0]))
+        sinks[k].copy_(terms[:8], non_blocking=True)
+        sink_ev[k].record()
+
+    def e2e_blocking_step(i):
+        b = hb[i % len(hb)]
+        terms = ts.step(*step_inputs(args.workload, b))
+        sinks[0].copy_(terms[:8], non_blocking=False)    # synchronises like the reference's .item()
+
+    for i in range(max(3, args.warmup)):
+        dev_step(i)
+    l0 = ops.LAUNCHES
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    ms = timed_region(dev_step, args.steps, dist_on)
+    launches = ops.LAUNCHES - l0
+    ms_e2e = timed_region(e2e_step, args.steps, dist_on)
+    ms_e2e_blk = timed_region(e2e_blocking_step, args.steps, dist_on)
+    clocks = sampler.stop()
+    terms = ts.step(*step_inputs(args.workload, db[0])).cpu()
+    finite = bool(torch.isfinite(terms[:4]).all())
+    in_sync = None
+    if dist_on:  # data-parallel replicas must hold bit-identical weights after the same number of reduced steps
+        chk = model.flat.data.double().sum().view(1)
+        lo, hi = chk.clone(), chk.clone()
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        in_sync = bool((hi - lo).abs().item() == 0.0)
+
+    if rank != 0:
+        return None, None
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    roof, detail = (None, None)
+    if roofline:
+        saved_dp, ts.dp = ts.dp, None  # rank-0-only instrumented pass: no collectives
+        roof, detail = gemm_roofline(ts, model, args, db, peaks)
+        ts.dp = saved_dp
+    cpu = None
+    if cpu_arm and world == 1:
+        v, cores, cms = cpu_reference_steps(args, cfg, 3, 1, args.cpu_batch)
+        cpu = {"value": round(v, 2), "unit": UNIT, "cores": cores, "kind": "port", "ms_per_step": round(cms, 1),
+               "sample": "3 timed steps (after 1 warm-up) of fwd+losses+bwd+clip+Adam at batch %d of the same shapes, fp32 PyTorch CPU oracle port" % args.cpu_batch}
+    B = cfg["B"]
+    h2d = sum(v.numel() * v.element_size() for k, v in hb[0].items() if k in ("feats", "answers", "posteriors", "questions", "alengths"))
+    line = {"metric": METRIC, "value": round(B * world * args.steps / (ms * 1e-3), 1), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(3, args.warmup), "ms_per_step": round(ms / args.steps, 3), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "tf32 (fp32 storage, fp32 accumulate)", "data": "synthetic", "config": config,
+            "e2e": {"value": round(B * world * args.steps / (ms_e2e * 1e-3), 1), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 32,
+                    "ms_per_step": round(ms_e2e / args.steps, 3), "loss_read": "every step, double-buffered pinned sink, consumed one step later",
+                    "blocking_read_value": round(B * world * args.steps / (ms_e2e_blk * 1e-3), 1)},
+            "gpu_launches": launches, "gpu_launches_per_step": launches // max(1, args.steps), "clocks": clocks,
+            "roofline": roof, "cpu_baseline": cpu, "loss_terms_finite": finite, "replicas_in_sync": in_sync,
+            "allreduce_buckets_per_step": (dp.collectives // max(1, ts.t)) if dp is not None else 0,
+            "loss_terms": {"rec": round(float(terms[0]), 4), "img": round(float(terms[1]), 4), "kld": round(float(terms[2]), 4), "aux": round(float(terms[3]), 4)}}
+    return line, detail
+
+
 def main():
     args = parse()
     rank = int(os.environ.get("RANK", "0"))
@@ -241,7 +329,7 @@ def main():
     cfg, wname = workload_config(args)
     config = {"workload": wname, "per_gpu_batch": cfg["B"], "global_batch": cfg["B"] * world,
               "parallelism": "dp%d" % world, "trunk": "excluded (pooled features in)",
-              "l2_policy": "per-step working set (347 MB weights + grads + activations) far exceeds the 126 MB L2; 4 rotating input batches"}
+              "l2_policy": "inputs larger than L2: the per-step working set (weights, gradients, Adam moments, activations: > 2 GB) far exceeds the 126 MB L2; 4 rotating input batches"}
 
     if args.impl == "reference":
         # the reference's CPU implementation of the path: rank 0 alone, all host threads, bounded sample per step
@@ -268,72 +356,23 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
         from blt_vqg_b200.parallel import GradReducer
         dp = GradReducer()
-    from blt_vqg_b200 import ops
-    model, ts = build_ours(args, cfg, dp)
-    hb = host_batches(cfg, 4, rank)
-    db = [{k: v.cuda(non_blocking=True) for k, v in b.items()} for b in hb]
-    torch.cuda.synchronize()
-
-    def dev_step(i):
-        ts.step(*step_inputs(args.workload, db[i % len(db)]))
-
-    sink = torch.zeros(8).pin_memory()
-
-    def e2e_step(i):
-        b = hb[i % len(hb)]
-        terms = ts.step(*step_inputs(args.workload, b))  # H2D of this step's inputs happens inside the call
-        sink.copy_(terms[:8], non_blocking=False)        # D2H of the loss terms (synchronises like the reference's .item())
-
-    for i in range(max(3, args.warmup)):
-        dev_step(i)
-    l0 = ops.LAUNCHES
-    sampler = ClockSampler(local_rank)
-    sampler.start()
-    ms = timed_region(dev_step, args.steps, dist_on)
-    launches = ops.LAUNCHES - l0
-    ms_e2e = timed_region(e2e_step, args.steps, dist_on)
-    clocks = sampler.stop()
-    terms = ts.step(*step_inputs(args.workload, db[0])).cpu()
-    finite = bool(torch.isfinite(terms[:4]).all())
-    in_sync = None
-    if dist_on:  # data-parallel replicas must hold bit-identical weights after the same number of reduced steps
-        chk = model.flat.data.double().sum().view(1)
-        lo, hi = chk.clone(), chk.clone()
-        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
-        dist.all_reduce(hi, op=dist.ReduceOp.MAX)
-        in_sync = bool((hi - lo).abs().item() == 0.0)
-
+    line, detail = measure(args, cfg, config, dp, rank, world, local_rank, roofline=not args.no_roofline,
+                           cpu_arm=not args.no_cpu_baseline)
+    if rank == 0 and args.workload == "transformer" and not args.no_secondary:
+        # BASELINE.json configs[1] (LSTM decoder, full size) measured the same way, reported beside the headline workload
+        import copy
+        a2 = copy.copy(args)
+        a2.workload, a2.batch = "lstm", 0
+        cfg2, name2 = workload_config(a2)
+        if world == 1:
+            l2, _ = measure(a2, cfg2, {"workload": name2}, None, rank, world, local_rank, roofline=False, cpu_arm=False)
+            line["other_workloads"] = {"lstm_cfg2": {k: l2[k] for k in ("value", "unit", "ms_per_step", "e2e", "gpu_launches_per_step", "loss_terms")}}
+            line["other_workloads"]["lstm_cfg2"]["workload"] = name2
     if rank != 0:
         if dist_on:
             dist.barrier()
             dist.destroy_process_group()
         return 0
-    peaks = {}
-    try:
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-    except Exception:
-        pass
-    roof, detail = (None, None)
-    if not args.no_roofline:
-        saved_dp, ts.dp = ts.dp, None  # rank-0-only instrumented pass: no collectives
-        roof, detail = gemm_roofline(ts, model, args, db, peaks)
-        ts.dp = saved_dp
-    cpu = None
-    if not args.no_cpu_baseline and world == 1:
-        v, cores, cms = cpu_reference_steps(args, cfg, 3, 1, args.cpu_batch)
-        cpu = {"value": round(v, 2), "unit": UNIT, "cores": cores, "kind": "port", "ms_per_step": round(cms, 1),
-               "sample": "3 timed steps (after 1 warm-up) of fwd+losses+bwd+clip+Adam at batch %d of the same shapes, fp32 PyTorch CPU oracle port" % args.cpu_batch}
-    B = cfg["B"]
-    h2d = sum(v.numel() * v.element_size() for k, v in hb[0].items() if k in ("feats", "answers", "posteriors", "questions", "alengths"))
-    line = {"metric": METRIC, "value": round(B * world * args.steps / (ms * 1e-3), 1), "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": max(3, args.warmup), "ms_per_step": round(ms / args.steps, 3), "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "tf32 (fp32 storage, fp32 accumulate)", "data": "synthetic", "config": config,
-            "e2e": {"value": round(B * world * args.steps / (ms_e2e * 1e-3), 1), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 32,
-                    "ms_per_step": round(ms_e2e / args.steps, 3)},
-            "gpu_launches": launches, "gpu_launches_per_step": launches // max(1, args.steps), "clocks": clocks,
-            "roofline": roof, "cpu_baseline": cpu, "loss_terms_finite": finite, "replicas_in_sync": in_sync,
-            "allreduce_buckets_per_step": (dp.collectives // max(1, ts.t)) if dp is not None else 0,
-            "loss_terms": {"rec": round(float(terms[0]), 4), "img": round(float(terms[1]), 4), "kld": round(float(terms[2]), 4), "aux": round(float(terms[3]), 4)}}
     print(json.dumps(line), flush=True)
     if detail:
         sys.stderr.write("GEMM breakdown (top shapes by time, 2 instrumented steps):\n")

@@ -42,8 +42,27 @@ def require_device():
         raise B200iqError("libb200iq only contains sm_100a code (B200, compute capability 10.0)")
 
 
+_STREAM = None  # cached c_void_p of the launching stream while a `pinned_stream()` block is active
+
+
 def stream_ptr():
+    if _STREAM is not None:
+        return _STREAM
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+class pinned_stream:
+    """`with pinned_stream():` looks torch's current stream up once for the whole block (a training step issues
+    ~650 launches; the per-launch lookup was a measurable share of the host time).  Do not switch streams inside."""
+
+    def __enter__(self):
+        global _STREAM
+        self.prev = _STREAM
+        _STREAM = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+    def __exit__(self, *a):
+        global _STREAM
+        _STREAM = self.prev
 
 
 def ptr(t):
@@ -62,8 +81,7 @@ def fptr(t):
 
 class GemmParams(C.Structure):
     _fields_ = [
-        ("A", C.POINTER(C.c_float)), ("B", C.POINTER(C.c_float)), ("C", C.POINTER(C.c_float)),
-        ("bias", C.POINTER(C.c_float)), ("residual", C.POINTER(C.c_float)),
+        ("A", C.c_void_p), ("B", C.c_void_p), ("C", C.c_void_p), ("bias", C.c_void_p), ("residual", C.c_void_p),
         ("M", C.c_int), ("N", C.c_int), ("K", C.c_int),
         ("lda", C.c_int), ("ldb", C.c_int), ("ldc", C.c_int), ("ldr", C.c_int),
         ("flags", C.c_int), ("split_k", C.c_int), ("alpha", C.c_float),

@@ -81,7 +81,8 @@ def gemm(a, b, out=None, *, a_t=False, b_t=False, bias=None, residual=None, relu
     dp, dseed, doff = dropout if dropout is not None and dropout[0] > 0 else (0.0, 0, 0)
     if dp > 0: flags |= L.GEMM_DROPOUT
     if simt if simt is not None else _FORCE_SIMT: flags |= L.GEMM_SIMT
-    p = L.GemmParams(L.fptr(a), L.fptr(b), L.fptr(out), L.fptr(bias), L.fptr(residual), M, N, K,
+    p = L.GemmParams(a.data_ptr(), b.data_ptr(), out.data_ptr(), bias.data_ptr() if bias is not None else None,
+                     residual.data_ptr() if residual is not None else None, M, N, K,
                      _ld(a), _ld(b), _ld(out), _ld(residual) if residual is not None else 0,
                      flags, split_k, float(alpha), float(dp), dseed, doff)
     global LAUNCHES
@@ -258,7 +259,7 @@ _SUMSQ_SCRATCH = {}
 
 
 def grad_sumsq(grad, out):
-    key = (grad.device, torch.cuda.current_stream().cuda_stream)
+    key = (grad.device, L.stream_ptr().value)
     scratch = _SUMSQ_SCRATCH.get(key)
     if scratch is None:
         scratch = _SUMSQ_SCRATCH[key] = torch.zeros(2048, device=grad.device)

@@ -9,7 +9,7 @@ import math
 
 import torch
 
-from . import ops
+from . import _lib, ops
 
 
 def noam_lr(step, hidden_dim, warmup=4000):
@@ -42,6 +42,10 @@ class TrainStep:
 
     def step(self, images, answers, response, target, eps=None):
         """returns the device tensor of loss terms (rec, img, kld, aux, count, gnorm_sq, ...) of this step"""
+        with _lib.pinned_stream():
+            return self._step(images, answers, response, target, eps)
+
+    def _step(self, images, answers, response, target, eps):
         m = self.model
         a = m.args
         if self.iter == getattr(a, "num_pretraining_steps", -1) and not m.latent_transformer:
