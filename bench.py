@@ -225,10 +225,18 @@ def gemm_roofline(ts, model, args, dev_batches, peaks):
                "tflops": round(v[2] / v[1] * 1e-9, 1) if v[1] > 0 else None,
                "operand_gbs": round(v[3] / v[1] * 1e-6, 1) if v[1] > 0 else None} for k, v in top]
     peak = peaks.get("bf16_tflops_sustained") or 1400.0
+    traffic, traffic_src = None, None
+    try:  # dram bytes per launch of the same kernel from the committed ncu capture (one cfg3 step, all 353 GEMM launches)
+        tj = json.load(open(os.path.join(ROOT, "profiles", "r01d_gemm_traffic.json")))
+        if args.workload == "transformer":
+            traffic, traffic_src = round(tj["dram_bytes_per_launch"]), tj["source"]
+    except Exception:
+        pass
     ach = tot_fl / tot_ms * 1e-9 if tot_ms > 0 else 0.0
     roof = {"bound": "tensor", "kernel": "gemm_tf32_kernel (tcgen05.mma kind::tf32, all dense projections)", "achieved": round(ach, 2),
             "peak": peak, "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if "bf16_tflops_sustained" in peaks else "fallback",
-            "unit": "TFLOP/s", "frac": round(ach / peak, 4), "traffic": None, "launches_per_step": len(trace) // 2,
+            "unit": "TFLOP/s", "frac": round(ach / peak, 4), "traffic": traffic, "traffic_unit": "DRAM bytes per launch (ncu)", "traffic_source": traffic_src,
+            "algorithmic_bytes_per_launch": round(sum(t[3] for t in trace) / max(1, len(trace))), "launches_per_step": len(trace) // 2,
             "gemm_ms_per_step": round(tot_ms / 2, 3), "step_ms_instrumented": round(step_t0.elapsed_time(step_t1) / 2, 3),
             "note": "operands are TF32 (nominal dense peak 1.1 PF = half of bf16); algorithmic flops = 2MNK per launch"}
     return roof, detail
