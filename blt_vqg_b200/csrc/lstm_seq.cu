@@ -1,0 +1,182 @@
+// Persistent LSTM recurrence: the whole time loop of nn.LSTM(H, H, 1) in ONE launch (forward) / ONE launch (BPTT).
+// replaces: the per-timestep cuDNN recurrence of torch.nn.LSTM at models/decoder_rnn.py:73,105 and models/encoder_rnn.py:51,83
+//           (and, here, the 2 launches per timestep of the first version: one tcgen05 GEMM + one cell kernel).
+//
+// Decomposition: a thread-block CLUSTER of 8 CTAs owns 16 batch rows; CTA c of the cluster owns hidden units
+// [c*U, (c+1)*U), U = ceil(H/8) rounded up to even, and keeps the 4U rows of W_hh that produce ITS gates (i,f,g,o of its
+// units) resident in shared memory for all T steps (H = 300: 152 x 308 floats = 187 KB).  Per step a CTA
+//   1. pulls h_{t-1} of its 16 rows (all H units) from the h sequence in global memory (L2 hits: 19 KB, float4),
+//   2. computes gates[16, 4U] = h . W_slice^T with mma.sync.m16n8k8 TF32 (operands from shared memory, bank-conflict-free
+//      pitch = 20 mod 32); the slice's rows are stored unit-major / gate-minor so the four gates of one (row, unit) land
+//      in two ADJACENT lanes of a C fragment and meet through one shuffle,
+//   3. adds the precomputed input projection, applies the cell, keeps c in REGISTERS across time, writes activated gates /
+//      c_t / h_t (the backward pass and the vocabulary GEMM read them) and
+//   4. meets its 7 peers at a hardware cluster barrier (release / acquire), after which h_t is visible to them.
+// The algorithmic HBM traffic per token is what SURVEY 8(d) counts: read x-projection 16H B, write gates 16H + h,c 8H B.
+#include "common.cuh"
+
+namespace b200iq {
+
+static constexpr int LS_CL = 8;        // CTAs per cluster
+static constexpr int LS_ROWS = 16;     // batch rows per cluster (one MMA m-tile)
+static constexpr int LS_THREADS = 256; // 8 warps
+static constexpr int LS_MAXT = 3;      // n-tiles per warp in the forward: 8 warps x 3 x 8 columns >= 4U  (U <= 48)
+
+__device__ __forceinline__ void ls_mma(float (&c)[4], float a0, float a1, float a2, float a3, float b0, float b1) {
+  asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+               : "r"(__float_as_uint(a0)), "r"(__float_as_uint(a1)), "r"(__float_as_uint(a2)), "r"(__float_as_uint(a3)),
+                 "r"(__float_as_uint(b0)), "r"(__float_as_uint(b1)));
+}
+__device__ __forceinline__ uint32_t ls_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ uint32_t ls_clusterid() { uint32_t r; asm volatile("mov.u32 %0, %%clusterid.x;" : "=r"(r)); return r; }
+__device__ __forceinline__ void ls_cluster_sync() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ float ls_sigmoid(float x) { return 1.f / (1.f + __expf(-x)); }
+
+struct LstmSeqDims { int T, B, H, U, Hp, LD; };  // U units per CTA, Hp = H rounded up to 8, LD = shared-memory pitch
+
+// W_slice[4*ul + gate][k] = W_hh[gate*H + (rank*U + ul)][k]   (zero for units / k beyond H)
+__device__ __forceinline__ void ls_load_wslice(float* Ws, const float* __restrict__ whh, const LstmSeqDims& d, int rank) {
+  const int rows = 4 * d.U;
+  for (int idx = threadIdx.x; idx < rows * d.LD; idx += LS_THREADS) {
+    const int n = idx / d.LD, k = idx - n * d.LD;
+    const int ul = n >> 2, gate = n & 3, u = rank * d.U + ul;
+    Ws[idx] = (u < d.H && k < d.H) ? __ldg(whh + (size_t)(gate * d.H + u) * d.H + k) : 0.f;
+  }
+}
+
+__global__ void __cluster_dims__(LS_CL, 1, 1) __launch_bounds__(LS_THREADS, 1)
+lstm_seq_fwd_kernel(float* gates, const float* __restrict__ whh, float* hbuf, float* cbuf,
+                    const int* __restrict__ lengths, LstmSeqDims d, int rn) {
+  extern __shared__ float ls_smem[];
+  float* Ws = ls_smem;                    // [4U][LD]
+  float* hs = Ws + 4 * d.U * d.LD;        // [16][LD]
+  const int rank = ls_ctarank(), b0 = ls_clusterid() * LS_ROWS;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t4 = lane & 3;
+  const int NT = d.U / 2, KS = d.Hp / 8;
+  const size_t BH = (size_t)d.B * d.H, B4H = 4 * BH;
+  ls_load_wslice(Ws, whh, d, rank);
+  // zero the k-padding of the h tile once (columns H..LD-1 are never written again)
+  for (int idx = threadIdx.x; idx < LS_ROWS * d.LD; idx += LS_THREADS) hs[idx] = 0.f;
+  // each lane owns ONE (row, unit) pair per n-tile of its warp: even t4 -> row g, odd t4 -> row g+8; unit = 2*nt + (t4>>1)
+  const int my_row = g + 8 * (t4 & 1), b = b0 + my_row;
+  const bool row_ok = b < d.B;
+  const int len = (lengths && row_ok) ? __ldg(lengths + b) : 0x7fffffff;
+  float creg[LS_MAXT], xg[LS_MAXT][4];
+  int unit[LS_MAXT];
+#pragma unroll
+  for (int i = 0; i < LS_MAXT; ++i) {
+    const int nt = warp + 8 * i;
+    unit[i] = (nt < NT) ? rank * d.U + 2 * nt + (t4 >> 1) : d.H;  // >= H: nothing to do
+    creg[i] = (row_ok && unit[i] < d.H) ? cbuf[(size_t)b * d.H + unit[i]] : 0.f;
+  }
+  auto fetch_x = [&](int t) {
+#pragma unroll
+    for (int i = 0; i < LS_MAXT; ++i)
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+        xg[i][q] = (row_ok && unit[i] < d.H && t < len) ? __ldcg(gates + (size_t)t * B4H + (size_t)b * 4 * d.H + q * d.H + unit[i]) : 0.f;
+  };
+  fetch_x(0);
+  __syncthreads();
+  for (int t = 0; t < d.T; ++t) {
+    // 1. h_{t-1} of the cluster's 16 rows -> shared memory (float4 when H allows it)
+    const float* hprev = hbuf + (size_t)t * BH;
+    if ((d.H & 3) == 0) {
+      const int h4 = d.H >> 2;
+      for (int idx = threadIdx.x; idx < LS_ROWS * h4; idx += LS_THREADS) {
+        const int r = idx / h4, c4 = idx - r * h4;
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (b0 + r < d.B) v = __ldcg(reinterpret_cast<const float4*>(hprev + (size_t)(b0 + r) * d.H + 4 * c4));  // L2: written by peer SMs
+        *reinterpret_cast<float4*>(hs + r * d.LD + 4 * c4) = v;
+      }
+    } else {
+      for (int idx = threadIdx.x; idx < LS_ROWS * d.H; idx += LS_THREADS) {
+        const int r = idx / d.H, c = idx - r * d.H;
+        hs[r * d.LD + c] = (b0 + r < d.B) ? __ldcg(hprev + (size_t)(b0 + r) * d.H + c) : 0.f;
+      }
+    }
+    __syncthreads();
+    // 2. gates[16, 4U] = h . W_slice^T
+    float acc[LS_MAXT][4];
+#pragma unroll
+    for (int i = 0; i < LS_MAXT; ++i)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) acc[i][e] = 0.f;
+    for (int ks = 0; ks < KS; ++ks) {
+      const float* hp = hs + 8 * ks + t4;
+      const float a0 = hp[g * d.LD], a1 = hp[(g + 8) * d.LD], a2 = hp[g * d.LD + 4], a3 = hp[(g + 8) * d.LD + 4];
+#pragma unroll
+      for (int i = 0; i < LS_MAXT; ++i) {
+        const int nt = warp + 8 * i;
+        if (nt < NT) {
+          const float* wp = Ws + (8 * nt + g) * d.LD + 8 * ks + t4;
+          ls_mma(acc[i], a0, a1, a2, a3, wp[0], wp[4]);
+        }
+      }
+    }
+    // 3. the four gates of (my_row, unit) meet: even lanes keep row g and take (g,o) from the odd neighbour, odd lanes keep
+    //    row g+8 and take (i,f) from the even neighbour
+    float hnew[LS_MAXT];
+#pragma unroll
+    for (int i = 0; i < LS_MAXT; ++i) {
+      const bool odd = t4 & 1;
+      const float s0 = odd ? acc[i][0] : acc[i][2], s1 = odd ? acc[i][1] : acc[i][3];
+      const float r0 = __shfl_xor_sync(0xffffffffu, s0, 1), r1 = __shfl_xor_sync(0xffffffffu, s1, 1);
+      float gi = odd ? r0 : acc[i][0], gf = odd ? r1 : acc[i][1], gg = odd ? acc[i][2] : r0, go = odd ? acc[i][3] : r1;
+      hnew[i] = 0.f;
+      if (row_ok && unit[i] < d.H) {
+        const size_t o = (size_t)b * d.H + unit[i];
+        if (t < len) {
+          gi = ls_sigmoid(gi + xg[i][0]); gf = ls_sigmoid(gf + xg[i][1]); gg = tanhf(gg + xg[i][2]); go = ls_sigmoid(go + xg[i][3]);
+          creg[i] = gf * creg[i] + gi * gg;
+          hnew[i] = rnd(go * tanhf(creg[i]), rn);
+          float* gout = gates + (size_t)t * B4H + (size_t)b * 4 * d.H + unit[i];
+          gout[0] = gi; gout[d.H] = gf; gout[2 * d.H] = gg; gout[3 * d.H] = go;
+        } else {
+          hnew[i] = hs[my_row * d.LD + unit[i]];  // packed-sequence semantics: the state stops at the row's length
+        }
+        cbuf[(size_t)(t + 1) * BH + o] = creg[i];
+        hbuf[(size_t)(t + 1) * BH + o] = hnew[i];
+      }
+    }
+    if (t + 1 < d.T) fetch_x(t + 1);  // in flight across the barrier
+    // 4. h_t of all 8 unit slices becomes visible to the cluster (also orders this step's reads of `hs` before the refill)
+    ls_cluster_sync();
+  }
+}
+
+}  // namespace b200iq
+using namespace b200iq;
+
+static int ls_dims(int T, int B, int H, LstmSeqDims* d, size_t* smem_fwd) {
+  d->T = T; d->B = B; d->H = H;
+  d->U = ((H + LS_CL - 1) / LS_CL + 1) & ~1;
+  d->Hp = (H + 7) & ~7;
+  d->LD = d->Hp + ((20 - d->Hp % 32) + 32) % 32;  // pitch = 20 (mod 32): the 8 x 4 fragment loads hit 32 distinct banks
+  *smem_fwd = sizeof(float) * ((size_t)4 * d->U * d->LD + (size_t)LS_ROWS * d->LD);
+  return 0;
+}
+
+// 1 when the persistent kernels can take this width (W_hh slice + h tile fit the 227 KB of one SM), else 0
+extern "C" int b200iq_lstm_seq_supported(int H) {
+  LstmSeqDims d; size_t smem;
+  ls_dims(1, 1, H, &d, &smem);
+  return (H >= 8 && d.U / 2 <= 8 * LS_MAXT && smem + 1024 <= 227 * 1024) ? 1 : 0;
+}
+
+extern "C" int b200iq_lstm_seq_fwd(float* gates, const float* whh, float* hbuf, float* cbuf, const int* lengths,
+                                   int T, int B, int H, void* stream) {
+  B200IQ_CHECK_ARG(gates && whh && hbuf && cbuf && T > 0 && B > 0 && H > 0, "lstm_seq_fwd: bad args");
+  B200IQ_CHECK_ARG(b200iq_lstm_seq_supported(H), "lstm_seq_fwd: H=%d does not fit the shared-memory resident slice", H);
+  B200IQ_CHECK_ARG((((uintptr_t)hbuf) & 15) == 0, "lstm_seq_fwd: hbuf must be 16-byte aligned");
+  LstmSeqDims d; size_t smem;
+  ls_dims(T, B, H, &d, &smem);
+  static bool attr_done = false;
+  if (!attr_done) { cudaFuncSetAttribute(lstm_seq_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); attr_done = true; }
+  const int clusters = (B + LS_ROWS - 1) / LS_ROWS;
+  lstm_seq_fwd_kernel<<<clusters * LS_CL, LS_THREADS, smem, (cudaStream_t)stream>>>(gates, whh, hbuf, cbuf, lengths, d, round_mode());
+  return launch_status("lstm_seq_fwd");
+}

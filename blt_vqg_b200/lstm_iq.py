@@ -18,6 +18,8 @@ over all T*B rows.  State-dict names follow the upstream module tree (see oracle
 import math
 from types import SimpleNamespace
 
+import os
+
 import torch
 import torch.nn as nn
 
@@ -61,6 +63,10 @@ def mlp_specs(a, name, i, hdim, o):
     a.add(name + ".layers.fc0.bias", (hdim,), ("zeros", 0))
     a.add(name + ".layers.fc1.weight", (o, hdim), ("he", hdim))
     a.add(name + ".layers.fc1.bias", (o,), ("zeros", 0))
+
+
+# persistent recurrence kernels (one launch per LSTM pass) when the width fits; B200IQ_LSTM_PERSISTENT=0 = per-step launches
+PERSISTENT = os.environ.get("B200IQ_LSTM_PERSISTENT", "1") == "1"
 
 
 class LSTMIQ(nn.Module):
@@ -201,6 +207,9 @@ class LSTMIQ(nn.Module):
             hbuf[0].copy_(h0)
             cbuf[0].copy_(c0)
         whh = c.W[pfx + "weight_hh_l0"]
+        if PERSISTENT and ops.lstm_seq_supported(H):
+            ops.lstm_seq_fwd(gates, whh, hbuf, cbuf, lengths)   # the whole recurrence in one launch
+            return hbuf
         for t in range(T):
             ops.gemm(hbuf[t], whh, gates[t], residual=gates[t], fp32_out=True)
             ops.lstm_cell_fwd(gates[t], cbuf[t], hbuf[t], cbuf[t + 1], hbuf[t + 1], lengths, t)

@@ -272,6 +272,16 @@ def adam_step(param, grad, m, v, hyper, normsq, beta1=0.9, beta2=0.999, eps=1e-8
 
 
 # ------------------------------------------------------------------ LSTM recurrence
+def lstm_seq_supported(H):
+    return bool(L.lib().b200iq_lstm_seq_supported(int(H))) and not _FORCE_SIMT
+
+
+def lstm_seq_fwd(gates, whh, hbuf, cbuf, lengths):
+    """all T steps in one launch; gates [T,B,4H] in: x-projection + biases, out: activated gates"""
+    T, B, H4 = gates.shape
+    _call("b200iq_lstm_seq_fwd", _p(gates), _p(whh), _p(hbuf), _p(cbuf), _p(lengths), T, B, H4 // 4)
+
+
 def lstm_cell_fwd(gates, c_prev, h_prev, c_next, h_next, lengths, t):
     B, H = c_prev.shape
     _call("b200iq_lstm_cell_fwd", _p(gates), _p(c_prev), _p(h_prev), _p(c_next), _p(h_next), _p(lengths), int(t), B, H)

@@ -177,6 +177,13 @@ int b200iq_lstm_cell_fwd(float* gates, const float* c_prev, const float* h_prev,
  * d/dh_{t-1}.  dh_out: gradient from the consumers of h_t, or NULL. */
 int b200iq_lstm_cell_bwd(const float* gates, const float* c_prev, const float* c_t, float* dh_run, const float* dh_out,
                          float* dc, float* dgates, const int* lengths, int t, int B, int H, void* stream);
+/* Persistent recurrence: all T steps of nn.LSTM(H, H, 1) in one launch (8-CTA clusters, W_hh slice resident in shared
+ * memory, mma.sync TF32, c in registers, one hardware cluster barrier per step).  Same buffers as the per-step pair
+ * b200iq_gemm + b200iq_lstm_cell_fwd: gates [T,B,4H] holds the input projection (+ both biases) on entry and the ACTIVATED
+ * gates on return; hbuf / cbuf [T+1,B,H] with slot 0 = the initial state; lengths [B] or NULL (packed-sequence masking,
+ * models/encoder_rnn.py:80-86).   replaces: models/decoder_rnn.py:105, models/encoder_rnn.py:83 (cuDNN recurrence). */
+int b200iq_lstm_seq_supported(int H);
+int b200iq_lstm_seq_fwd(float* gates, const float* whh, float* hbuf, float* cbuf, const int* lengths, int T, int B, int H, void* stream);
 /* out[t*B+b] = in[b*T_in + col0 + t], t < T_out: batch-major token ids -> time-major (inputs[:, :-1] of decoder_rnn.py:141) */
 int b200iq_transpose_ids(const int* in, int* out, int B, int T_in, int T_out, int col0, void* stream);
 

@@ -126,3 +126,43 @@ def test_lstm_train_step_runs_with_dropout_and_adam(env):
         assert torch.isfinite(t).all()
         first = float(t[0]) if first is None else first
     assert float(t[0]) < first  # the generation loss goes down on a repeated batch
+
+
+@pytest.mark.parametrize("T,B,H,ragged", [(19, 256, 300, False), (5, 256, 300, True), (7, 37, 64, True), (3, 16, 100, False), (4, 50, 304, True)])
+def test_persistent_recurrence_matches_the_per_step_kernels(env, T, B, H, ragged):
+    """b200iq_lstm_seq_fwd / _bwd (8-CTA clusters, W_hh slice in shared memory, one launch per pass) against the per-timestep
+    GEMM + cell kernels on the same buffers: activated gates, h and c sequences, and the BPTT outputs."""
+    from blt_vqg_b200 import _lib, ops
+    assert ops.lstm_seq_supported(H)
+    prev = _lib.lib().b200iq_set_tf32_rounding(1)
+    try:
+        torch.manual_seed(3)
+        rt = lambda x: ops.round_tf32(x, torch.empty_like(x))
+        whh = rt(torch.randn(4 * H, H, device="cuda") * H ** -0.5)
+        xproj = torch.randn(T, B, 4 * H, device="cuda")
+        h0, c0 = rt(torch.randn(B, H, device="cuda") * 0.5), torch.randn(B, H, device="cuda") * 0.5
+        lengths = torch.randint(1, T + 1, (B,), device="cuda", dtype=torch.int32) if ragged else None
+
+        def run(persistent):
+            gates = xproj.clone()
+            hbuf, cbuf = torch.zeros(T + 1, B, H, device="cuda"), torch.zeros(T + 1, B, H, device="cuda")
+            hbuf[0].copy_(h0)
+            cbuf[0].copy_(c0)
+            if persistent:
+                ops.lstm_seq_fwd(gates, whh, hbuf, cbuf, lengths)
+            else:
+                for t in range(T):
+                    ops.gemm(hbuf[t], whh, gates[t], residual=gates[t], fp32_out=True)
+                    ops.lstm_cell_fwd(gates[t], cbuf[t], hbuf[t], cbuf[t + 1], hbuf[t + 1], lengths, t)
+            return gates, hbuf, cbuf
+        g1, h1, c1 = run(True)
+        g0, h0_, c0_ = run(False)
+        assert torch.isfinite(h1).all()
+        assert rel(h1, h0_) < 2e-3 and rel(c1, c0_) < 2e-3
+        if lengths is None:
+            assert rel(g1, g0) < 2e-3
+        else:  # rows past their length keep the untouched input projection in both versions
+            live = (torch.arange(T, device="cuda")[:, None] < lengths[None, :]).float()[:, :, None]
+            assert rel(g1 * live, g0 * live) < 2e-3
+    finally:
+        _lib.lib().b200iq_set_tf32_rounding(prev)
