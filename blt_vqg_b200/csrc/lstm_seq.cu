@@ -148,6 +148,132 @@ lstm_seq_fwd_kernel(float* gates, const float* __restrict__ whh, float* hbuf, fl
   }
 }
 
+
+// ---------------------------------------------------------------- BPTT, same decomposition
+// Per step (t = T-1 .. 0) a CTA turns d h_t, d c_t of ITS units into the four pre-activation gate gradients (registers ->
+// dgates[t] in global memory for the weight-gradient GEMMs, and a [16, 4U] shared-memory tile), multiplies that tile with
+// its resident W_hh slice — a K-slice of  d h_{t-1} = dgates . W_hh  — and publishes the [16, Hp] partial product; after
+// the cluster barrier every CTA sums the 8 partials of its own units (fixed order: deterministic).  Two partial buffers
+// alternate so that a fast CTA's next write never races a slow CTA's read.
+static constexpr int LS_MAXTB = 5;  // n-tiles per warp in the backward: 8 warps x 5 x 8 columns >= Hp  (Hp <= 320)
+
+__global__ void __cluster_dims__(LS_CL, 1, 1) __launch_bounds__(LS_THREADS, 1)
+lstm_seq_bwd_kernel(const float* __restrict__ gates, const float* __restrict__ cbuf, const float* __restrict__ whh,
+                    const float* __restrict__ dh_last, const float* __restrict__ d_out, float* __restrict__ dgates,
+                    float* __restrict__ dh0, float* __restrict__ dc0, float* part, const int* __restrict__ lengths,
+                    LstmSeqDims d, int LDG, int rn) {
+  extern __shared__ float ls_smem[];
+  float* Ws = ls_smem;                    // [4U][LD]
+  float* dgs = Ws + 4 * d.U * d.LD;       // [16][LDG]  (unit-major / gate-minor columns, like the rows of Ws)
+  const int rank = ls_ctarank(), cl = ls_clusterid(), b0 = cl * LS_ROWS;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t4 = lane & 3;
+  const int NT = d.U / 2, NTB = d.Hp / 8, KS = d.U / 2;
+  const size_t BH = (size_t)d.B * d.H, B4H = 4 * BH;
+  ls_load_wslice(Ws, whh, d, rank);
+  for (int idx = threadIdx.x; idx < LS_ROWS * LDG; idx += LS_THREADS) dgs[idx] = 0.f;
+  const int my_row = g + 8 * (t4 & 1), b = b0 + my_row;
+  const bool row_ok = b < d.B;
+  const int len = (lengths && row_ok) ? __ldg(lengths + b) : 0x7fffffff;
+  int unit[LS_MAXT], ul[LS_MAXT];
+  float dh_run[LS_MAXT], dc[LS_MAXT], gt[LS_MAXT][4], cprev[LS_MAXT], ct[LS_MAXT], dout[LS_MAXT];
+#pragma unroll
+  for (int i = 0; i < LS_MAXT; ++i) {
+    const int nt = warp + 8 * i;
+    ul[i] = 2 * nt + (t4 >> 1);
+    unit[i] = (nt < NT) ? rank * d.U + ul[i] : d.H;
+    const bool ok = row_ok && unit[i] < d.H;
+    dh_run[i] = (ok && dh_last) ? __ldg(dh_last + (size_t)b * d.H + unit[i]) : 0.f;
+    dc[i] = 0.f;
+    ct[i] = ok ? __ldg(cbuf + (size_t)d.T * BH + (size_t)b * d.H + unit[i]) : 0.f;
+  }
+  auto fetch = [&](int t) {
+#pragma unroll
+    for (int i = 0; i < LS_MAXT; ++i) {
+      const bool ok = row_ok && unit[i] < d.H;
+      const size_t o = (size_t)b * d.H + unit[i];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) gt[i][q] = (ok && t < len) ? __ldg(gates + (size_t)t * B4H + (size_t)b * 4 * d.H + q * d.H + unit[i]) : 0.f;
+      cprev[i] = ok ? __ldg(cbuf + (size_t)t * BH + o) : 0.f;
+      dout[i] = (ok && d_out) ? __ldg(d_out + (size_t)t * BH + o) : 0.f;
+    }
+  };
+  fetch(d.T - 1);
+  __syncthreads();
+  const size_t part_cl = (size_t)LS_CL * LS_ROWS * d.Hp;  // floats per cluster and parity
+  for (int t = d.T - 1; t >= 0; --t) {
+    // a-c. cell backward for my (row, unit) pairs
+#pragma unroll
+    for (int i = 0; i < LS_MAXT; ++i) {
+      if (row_ok && unit[i] < d.H) {
+        const float dh = dh_run[i] + dout[i];
+        float dg4[4] = {0.f, 0.f, 0.f, 0.f};
+        if (t < len) {
+          const float gi = gt[i][0], gf = gt[i][1], gg = gt[i][2], go = gt[i][3];
+          const float tc = tanhf(ct[i]);
+          const float dct = dc[i] + dh * go * (1.f - tc * tc);
+          dg4[0] = rnd(dct * gg * gi * (1.f - gi), rn);
+          dg4[1] = rnd(dct * cprev[i] * gf * (1.f - gf), rn);
+          dg4[2] = rnd(dct * gi * (1.f - gg * gg), rn);
+          dg4[3] = rnd(dh * tc * go * (1.f - go), rn);
+          dc[i] = dct * gf;
+          dh_run[i] = 0.f;
+        } else {
+          dh_run[i] = dh;  // the state was copied at this step: the gradient passes straight through, dc unchanged
+        }
+        float* gout = dgates + (size_t)t * B4H + (size_t)b * 4 * d.H + unit[i];
+        gout[0] = dg4[0]; gout[d.H] = dg4[1]; gout[2 * d.H] = dg4[2]; gout[3 * d.H] = dg4[3];
+        *reinterpret_cast<float4*>(dgs + my_row * LDG + 4 * ul[i]) = make_float4(dg4[0], dg4[1], dg4[2], dg4[3]);
+        ct[i] = cprev[i];  // c_{t-1} is the next step's c_t
+      }
+    }
+    __syncthreads();
+    // e. partial d h_{t-1}[16, Hp] = dgates_slice[16, 4U] . W_slice[4U, Hp]
+    float acc[LS_MAXTB][4];
+#pragma unroll
+    for (int i = 0; i < LS_MAXTB; ++i)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) acc[i][e] = 0.f;
+    for (int ks = 0; ks < KS; ++ks) {
+      const float* ap = dgs + 8 * ks + t4;
+      const float a0 = ap[g * LDG], a1 = ap[(g + 8) * LDG], a2 = ap[g * LDG + 4], a3 = ap[(g + 8) * LDG + 4];
+      const float* wp = Ws + (8 * ks + t4) * d.LD + g;
+#pragma unroll
+      for (int i = 0; i < LS_MAXTB; ++i) {
+        const int nb = warp + 8 * i;
+        if (nb < NTB) ls_mma(acc[i], a0, a1, a2, a3, wp[8 * nb], wp[4 * d.LD + 8 * nb]);
+      }
+    }
+    // f. publish the partial product
+    float* pp = part + ((size_t)(t & 1) * gridDim.x / LS_CL + cl) * part_cl + (size_t)rank * LS_ROWS * d.Hp;
+#pragma unroll
+    for (int i = 0; i < LS_MAXTB; ++i) {
+      const int nb = warp + 8 * i;
+      if (nb < NTB) {
+        *reinterpret_cast<float2*>(pp + (size_t)g * d.Hp + 8 * nb + 2 * t4) = make_float2(acc[i][0], acc[i][1]);
+        *reinterpret_cast<float2*>(pp + (size_t)(g + 8) * d.Hp + 8 * nb + 2 * t4) = make_float2(acc[i][2], acc[i][3]);
+      }
+    }
+    if (t > 0) fetch(t - 1);  // in flight across the barrier
+    ls_cluster_sync();
+    // h. d h_{t-1} of my (row, unit) pairs = pass-through + the 8 K-slices, summed in rank order
+    const float* pc = part + ((size_t)(t & 1) * gridDim.x / LS_CL + cl) * part_cl + (size_t)my_row * d.Hp;
+#pragma unroll
+    for (int i = 0; i < LS_MAXT; ++i)
+      if (row_ok && unit[i] < d.H) {
+        float s = 0.f;
+#pragma unroll
+        for (int src = 0; src < LS_CL; ++src) s += __ldcg(pc + (size_t)src * LS_ROWS * d.Hp + unit[i]);
+        dh_run[i] += rnd(s, rn);
+      }
+  }
+#pragma unroll
+  for (int i = 0; i < LS_MAXT; ++i)
+    if (row_ok && unit[i] < d.H) {
+      dh0[(size_t)b * d.H + unit[i]] = dh_run[i];
+      dc0[(size_t)b * d.H + unit[i]] = dc[i];
+    }
+}
+
 }  // namespace b200iq
 using namespace b200iq;
 
@@ -164,7 +290,7 @@ static int ls_dims(int T, int B, int H, LstmSeqDims* d, size_t* smem_fwd) {
 extern "C" int b200iq_lstm_seq_supported(int H) {
   LstmSeqDims d; size_t smem;
   ls_dims(1, 1, H, &d, &smem);
-  return (H >= 8 && d.U / 2 <= 8 * LS_MAXT && smem + 1024 <= 227 * 1024) ? 1 : 0;
+  return (H >= 8 && d.U / 2 <= 8 * LS_MAXT && d.Hp <= 320 && smem + 1024 <= 227 * 1024) ? 1 : 0;
 }
 
 extern "C" int b200iq_lstm_seq_fwd(float* gates, const float* whh, float* hbuf, float* cbuf, const int* lengths,
@@ -179,4 +305,32 @@ extern "C" int b200iq_lstm_seq_fwd(float* gates, const float* whh, float* hbuf, 
   const int clusters = (B + LS_ROWS - 1) / LS_ROWS;
   lstm_seq_fwd_kernel<<<clusters * LS_CL, LS_THREADS, smem, (cudaStream_t)stream>>>(gates, whh, hbuf, cbuf, lengths, d, round_mode());
   return launch_status("lstm_seq_fwd");
+}
+
+static int ls_ldg(const LstmSeqDims& d) { const int w = 4 * d.U; return w + ((4 - w % 32) + 32) % 32; }  // pitch = 4 (mod 32)
+
+extern "C" size_t b200iq_lstm_seq_bwd_workspace_bytes(int B, int H) {
+  LstmSeqDims d; size_t smem;
+  ls_dims(1, B, H, &d, &smem);
+  const size_t clusters = (B + LS_ROWS - 1) / LS_ROWS;
+  return sizeof(float) * 2 * clusters * LS_CL * LS_ROWS * d.Hp;
+}
+
+extern "C" int b200iq_lstm_seq_bwd(const float* gates, const float* cbuf, const float* whh, const float* dh_last, const float* d_out,
+                                   float* dgates, float* dh0, float* dc0, float* workspace, const int* lengths,
+                                   int T, int B, int H, void* stream) {
+  B200IQ_CHECK_ARG(gates && cbuf && whh && dgates && dh0 && dc0 && workspace && T > 0 && B > 0 && H > 0, "lstm_seq_bwd: bad args");
+  LstmSeqDims d; size_t smem;
+  ls_dims(T, B, H, &d, &smem);
+  const int LDG = ls_ldg(d);
+  smem = sizeof(float) * ((size_t)4 * d.U * d.LD + (size_t)LS_ROWS * LDG);
+  B200IQ_CHECK_ARG(b200iq_lstm_seq_supported(H) && d.Hp / 8 <= 8 * LS_MAXTB && smem + 1024 <= 227 * 1024,
+                   "lstm_seq_bwd: H=%d does not fit the shared-memory resident slice", H);
+  B200IQ_CHECK_ARG((((uintptr_t)workspace) & 15) == 0, "lstm_seq_bwd: workspace must be 16-byte aligned");
+  static bool attr_done = false;
+  if (!attr_done) { cudaFuncSetAttribute(lstm_seq_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); attr_done = true; }
+  const int clusters = (B + LS_ROWS - 1) / LS_ROWS;
+  lstm_seq_bwd_kernel<<<clusters * LS_CL, LS_THREADS, smem, (cudaStream_t)stream>>>(gates, cbuf, whh, dh_last, d_out, dgates, dh0, dc0,
+                                                                                    workspace, lengths, d, LDG, round_mode());
+  return launch_status("lstm_seq_bwd");
 }

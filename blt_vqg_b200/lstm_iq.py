@@ -229,9 +229,12 @@ class LSTMIQ(nn.Module):
         dc.zero_()
         whh = c.W[pfx + "weight_hh_l0"]
         dov = d_out.view(T, B, H) if d_out is not None else None
-        for t in reversed(range(T)):
-            ops.lstm_cell_bwd(gates[t], cbuf[t], cbuf[t + 1], dh_run, dov[t] if dov is not None else None, dc, dgates[t], lengths, t)
-            ops.gemm(dgates[t], whh, dh_run, b_t=True, residual=dh_run)
+        if PERSISTENT and ops.lstm_seq_supported(H):
+            ops.lstm_seq_bwd(gates, cbuf, whh, dh_run, dov, dgates, dh_run, dc, lengths)   # BPTT in one launch
+        else:
+            for t in reversed(range(T)):
+                ops.lstm_cell_bwd(gates[t], cbuf[t], cbuf[t + 1], dh_run, dov[t] if dov is not None else None, dc, dgates[t], lengths, t)
+                ops.gemm(dgates[t], whh, dh_run, b_t=True, residual=dh_run)
         dg = dgates.view(T * B, 4 * H)
         tf.grad_w(c, dg, hbuf[:T].view(T * B, H), G[pfx + "weight_hh_l0"], G[pfx + "bias_hh_l0"])
         tf.grad_w(c, dg, e, G[pfx + "weight_ih_l0"], G[pfx + "bias_ih_l0"])

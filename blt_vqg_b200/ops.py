@@ -282,6 +282,22 @@ def lstm_seq_fwd(gates, whh, hbuf, cbuf, lengths):
     _call("b200iq_lstm_seq_fwd", _p(gates), _p(whh), _p(hbuf), _p(cbuf), _p(lengths), T, B, H4 // 4)
 
 
+_LSTM_WS = {}
+
+
+def lstm_seq_bwd(gates, cbuf, whh, dh_last, d_out, dgates, dh0, dc0, lengths):
+    """BPTT of lstm_seq_fwd in one launch; dh_last / d_out may be None"""
+    T, B, H4 = gates.shape
+    H = H4 // 4
+    key = (gates.device, B, H)
+    ws = _LSTM_WS.get(key)
+    if ws is None:
+        L.lib().b200iq_lstm_seq_bwd_workspace_bytes.restype = C.c_size_t
+        ws = _LSTM_WS[key] = torch.empty(L.lib().b200iq_lstm_seq_bwd_workspace_bytes(B, H) // 4, device=gates.device)
+    _call("b200iq_lstm_seq_bwd", _p(gates), _p(cbuf), _p(whh), _p(dh_last), _p(d_out), _p(dgates), _p(dh0), _p(dc0), _p(ws),
+          _p(lengths), T, B, H)
+
+
 def lstm_cell_fwd(gates, c_prev, h_prev, c_next, h_next, lengths, t):
     B, H = c_prev.shape
     _call("b200iq_lstm_cell_fwd", _p(gates), _p(c_prev), _p(h_prev), _p(c_next), _p(h_next), _p(lengths), int(t), B, H)

@@ -184,6 +184,13 @@ int b200iq_lstm_cell_bwd(const float* gates, const float* c_prev, const float* c
  * models/encoder_rnn.py:80-86).   replaces: models/decoder_rnn.py:105, models/encoder_rnn.py:83 (cuDNN recurrence). */
 int b200iq_lstm_seq_supported(int H);
 int b200iq_lstm_seq_fwd(float* gates, const float* whh, float* hbuf, float* cbuf, const int* lengths, int T, int B, int H, void* stream);
+/* BPTT of the same recurrence in one launch: gates (activated, from the forward) and cbuf in; dh_last [B,H] (gradient of the
+ * final hidden state) and d_out [T,B,H] (gradient of every output) may each be NULL; writes dgates [T,B,4H] (pre-activation
+ * gate gradients: the operand of the dW_hh / dW_ih / dx GEMMs), dh0 and dc0 [B,H].  workspace: caller-owned scratch of
+ * b200iq_lstm_seq_bwd_workspace_bytes(B, H) bytes (partial products exchanged between the CTAs of a cluster). */
+size_t b200iq_lstm_seq_bwd_workspace_bytes(int B, int H);
+int b200iq_lstm_seq_bwd(const float* gates, const float* cbuf, const float* whh, const float* dh_last, const float* d_out,
+                        float* dgates, float* dh0, float* dc0, float* workspace, const int* lengths, int T, int B, int H, void* stream);
 /* out[t*B+b] = in[b*T_in + col0 + t], t < T_out: batch-major token ids -> time-major (inputs[:, :-1] of decoder_rnn.py:141) */
 int b200iq_transpose_ids(const int* in, int* out, int B, int T_in, int T_out, int col0, void* stream);
 

@@ -164,5 +164,18 @@ def test_persistent_recurrence_matches_the_per_step_kernels(env, T, B, H, ragged
         else:  # rows past their length keep the untouched input projection in both versions
             live = (torch.arange(T, device="cuda")[:, None] < lengths[None, :]).float()[:, :, None]
             assert rel(g1 * live, g0 * live) < 2e-3
+        # BPTT: same activated gates / c sequence into both versions
+        dh_last, d_out = rt(torch.randn(B, H, device="cuda")), rt(torch.randn(T, B, H, device="cuda"))
+        for use_last, use_out in ((True, True), (True, False), (False, True)):
+            dgp, dh0p, dc0p = torch.empty(T, B, 4 * H, device="cuda"), torch.empty(B, H, device="cuda"), torch.empty(B, H, device="cuda")
+            ops.lstm_seq_bwd(g0, c0_, whh, dh_last if use_last else None, d_out if use_out else None, dgp, dh0p, dc0p, lengths)
+            dgs, dh_run, dc = torch.empty(T, B, 4 * H, device="cuda"), torch.zeros(B, H, device="cuda"), torch.zeros(B, H, device="cuda")
+            if use_last:
+                dh_run.copy_(dh_last)
+            for t in reversed(range(T)):
+                ops.lstm_cell_bwd(g0[t], c0_[t], c0_[t + 1], dh_run, d_out[t] if use_out else None, dc, dgs[t], lengths, t)
+                ops.gemm(dgs[t], whh, dh_run, b_t=True, residual=dh_run)
+            assert torch.isfinite(dgp).all()
+            assert rel(dgp, dgs) < 3e-3 and rel(dh0p, dh_run) < 3e-3 and rel(dc0p, dc) < 3e-3
     finally:
         _lib.lib().b200iq_set_tf32_rounding(prev)
