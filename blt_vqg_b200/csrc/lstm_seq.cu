@@ -30,6 +30,8 @@ __device__ __forceinline__ void ls_mma(float (&c)[4], float a0, float a1, float 
 }
 __device__ __forceinline__ uint32_t ls_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
 __device__ __forceinline__ uint32_t ls_clusterid() { uint32_t r; asm volatile("mov.u32 %0, %%clusterid.x;" : "=r"(r)); return r; }
+__device__ __forceinline__ void ls_cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+__device__ __forceinline__ void ls_cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
 __device__ __forceinline__ void ls_cluster_sync() {
   asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
@@ -39,11 +41,13 @@ struct LstmSeqDims { int T, B, H, U, Hp, LD; };  // U units per CTA, Hp = H roun
 
 // W_slice[4*ul + gate][k] = W_hh[gate*H + (rank*U + ul)][k]   (zero for units / k beyond H)
 __device__ __forceinline__ void ls_load_wslice(float* Ws, const float* __restrict__ whh, const LstmSeqDims& d, int rank) {
-  const int rows = 4 * d.U;
-  for (int idx = threadIdx.x; idx < rows * d.LD; idx += LS_THREADS) {
-    const int n = idx / d.LD, k = idx - n * d.LD;
+  // one warp per slice row, lanes along k: coalesced 128-byte reads, 8 rows in flight per warp
+  const int rows = 4 * d.U, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int n = warp; n < rows; n += LS_THREADS / 32) {
     const int ul = n >> 2, gate = n & 3, u = rank * d.U + ul;
-    Ws[idx] = (u < d.H && k < d.H) ? __ldg(whh + (size_t)(gate * d.H + u) * d.H + k) : 0.f;
+    const float* src = whh + (size_t)(gate * d.H + u) * d.H;
+#pragma unroll 4
+    for (int k = lane; k < d.LD; k += 32) Ws[n * d.LD + k] = (u < d.H && k < d.H) ? __ldg(src + k) : 0.f;
   }
 }
 
@@ -105,6 +109,7 @@ lstm_seq_fwd_kernel(float* gates, const float* __restrict__ whh, float* hbuf, fl
     for (int i = 0; i < LS_MAXT; ++i)
 #pragma unroll
       for (int e = 0; e < 4; ++e) acc[i][e] = 0.f;
+#pragma unroll 2
     for (int ks = 0; ks < KS; ++ks) {
       const float* hp = hs + 8 * ks + t4;
       const float a0 = hp[g * d.LD], a1 = hp[(g + 8) * d.LD], a2 = hp[g * d.LD + 4], a3 = hp[(g + 8) * d.LD + 4];
@@ -119,7 +124,7 @@ lstm_seq_fwd_kernel(float* gates, const float* __restrict__ whh, float* hbuf, fl
     }
     // 3. the four gates of (my_row, unit) meet: even lanes keep row g and take (g,o) from the odd neighbour, odd lanes keep
     //    row g+8 and take (i,f) from the even neighbour
-    float hnew[LS_MAXT];
+    float hnew[LS_MAXT], ga[LS_MAXT][4];
 #pragma unroll
     for (int i = 0; i < LS_MAXT; ++i) {
       const bool odd = t4 & 1;
@@ -128,23 +133,31 @@ lstm_seq_fwd_kernel(float* gates, const float* __restrict__ whh, float* hbuf, fl
       float gi = odd ? r0 : acc[i][0], gf = odd ? r1 : acc[i][1], gg = odd ? acc[i][2] : r0, go = odd ? acc[i][3] : r1;
       hnew[i] = 0.f;
       if (row_ok && unit[i] < d.H) {
-        const size_t o = (size_t)b * d.H + unit[i];
         if (t < len) {
           gi = ls_sigmoid(gi + xg[i][0]); gf = ls_sigmoid(gf + xg[i][1]); gg = tanhf(gg + xg[i][2]); go = ls_sigmoid(go + xg[i][3]);
           creg[i] = gf * creg[i] + gi * gg;
           hnew[i] = rnd(go * tanhf(creg[i]), rn);
-          float* gout = gates + (size_t)t * B4H + (size_t)b * 4 * d.H + unit[i];
-          gout[0] = gi; gout[d.H] = gf; gout[2 * d.H] = gg; gout[3 * d.H] = go;
         } else {
           hnew[i] = hs[my_row * d.LD + unit[i]];  // packed-sequence semantics: the state stops at the row's length
         }
-        cbuf[(size_t)(t + 1) * BH + o] = creg[i];
-        hbuf[(size_t)(t + 1) * BH + o] = hnew[i];
+        hbuf[(size_t)(t + 1) * BH + (size_t)b * d.H + unit[i]] = hnew[i];
       }
+      ga[i][0] = gi; ga[i][1] = gf; ga[i][2] = gg; ga[i][3] = go;
     }
-    if (t + 1 < d.T) fetch_x(t + 1);  // in flight across the barrier
-    // 4. h_t of all 8 unit slices becomes visible to the cluster (also orders this step's reads of `hs` before the refill)
-    ls_cluster_sync();
+    // 4. h_t first, then ARRIVE (release: only the h stores are outstanding), and let everything the peers do not need —
+    //    activated gates, c_t, the next step's input projection — overlap the barrier latency before the WAIT
+    ls_cluster_arrive();
+#pragma unroll
+    for (int i = 0; i < LS_MAXT; ++i)
+      if (row_ok && unit[i] < d.H) {
+        if (t < len) {
+          float* gout = gates + (size_t)t * B4H + (size_t)b * 4 * d.H + unit[i];
+          gout[0] = ga[i][0]; gout[d.H] = ga[i][1]; gout[2 * d.H] = ga[i][2]; gout[3 * d.H] = ga[i][3];
+        }
+        cbuf[(size_t)(t + 1) * BH + (size_t)b * d.H + unit[i]] = creg[i];
+      }
+    if (t + 1 < d.T) fetch_x(t + 1);
+    ls_cluster_wait();  // h_t of all 8 unit slices is visible; also orders this step's reads of `hs` before the refill
   }
 }
 
@@ -202,11 +215,13 @@ lstm_seq_bwd_kernel(const float* __restrict__ gates, const float* __restrict__ c
   const size_t part_cl = (size_t)LS_CL * LS_ROWS * d.Hp;  // floats per cluster and parity
   for (int t = d.T - 1; t >= 0; --t) {
     // a-c. cell backward for my (row, unit) pairs
+    float dgk[LS_MAXT][4];
 #pragma unroll
     for (int i = 0; i < LS_MAXT; ++i) {
+      float (&dg4)[4] = dgk[i];
+      dg4[0] = dg4[1] = dg4[2] = dg4[3] = 0.f;
       if (row_ok && unit[i] < d.H) {
         const float dh = dh_run[i] + dout[i];
-        float dg4[4] = {0.f, 0.f, 0.f, 0.f};
         if (t < len) {
           const float gi = gt[i][0], gf = gt[i][1], gg = gt[i][2], go = gt[i][3];
           const float tc = tanhf(ct[i]);
@@ -220,8 +235,6 @@ lstm_seq_bwd_kernel(const float* __restrict__ gates, const float* __restrict__ c
         } else {
           dh_run[i] = dh;  // the state was copied at this step: the gradient passes straight through, dc unchanged
         }
-        float* gout = dgates + (size_t)t * B4H + (size_t)b * 4 * d.H + unit[i];
-        gout[0] = dg4[0]; gout[d.H] = dg4[1]; gout[2 * d.H] = dg4[2]; gout[3 * d.H] = dg4[3];
         *reinterpret_cast<float4*>(dgs + my_row * LDG + 4 * ul[i]) = make_float4(dg4[0], dg4[1], dg4[2], dg4[3]);
         ct[i] = cprev[i];  // c_{t-1} is the next step's c_t
       }
@@ -233,6 +246,7 @@ lstm_seq_bwd_kernel(const float* __restrict__ gates, const float* __restrict__ c
     for (int i = 0; i < LS_MAXTB; ++i)
 #pragma unroll
       for (int e = 0; e < 4; ++e) acc[i][e] = 0.f;
+#pragma unroll 2
     for (int ks = 0; ks < KS; ++ks) {
       const float* ap = dgs + 8 * ks + t4;
       const float a0 = ap[g * LDG], a1 = ap[(g + 8) * LDG], a2 = ap[g * LDG + 4], a3 = ap[(g + 8) * LDG + 4];
@@ -253,8 +267,15 @@ lstm_seq_bwd_kernel(const float* __restrict__ gates, const float* __restrict__ c
         *reinterpret_cast<float2*>(pp + (size_t)(g + 8) * d.Hp + 8 * nb + 2 * t4) = make_float2(acc[i][2], acc[i][3]);
       }
     }
+    ls_cluster_arrive();  // release covers the partial product only; dgates (not needed by the peers) goes out behind it
+#pragma unroll
+    for (int i = 0; i < LS_MAXT; ++i)
+      if (row_ok && unit[i] < d.H) {
+        float* gout = dgates + (size_t)t * B4H + (size_t)b * 4 * d.H + unit[i];
+        gout[0] = dgk[i][0]; gout[d.H] = dgk[i][1]; gout[2 * d.H] = dgk[i][2]; gout[3 * d.H] = dgk[i][3];
+      }
     if (t > 0) fetch(t - 1);  // in flight across the barrier
-    ls_cluster_sync();
+    ls_cluster_wait();
     // h. d h_{t-1} of my (row, unit) pairs = pass-through + the 8 K-slices, summed in rank order
     const float* pc = part + ((size_t)(t & 1) * gridDim.x / LS_CL + cl) * part_cl + (size_t)my_row * d.Hp;
 #pragma unroll
