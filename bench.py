@@ -36,6 +36,7 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=os.environ.get("B200IQ_WORKLOAD", "transformer"), choices=["transformer", "lstm"])
     ap.add_argument("--batch", type=int, default=0, help="per-GPU batch (default: the workload's)")
+    ap.add_argument("--config", default="", help="other BASELINE.json configs as parity / sizing runs: transformer cfg1|cfg3|cfg5, lstm cfg1|cfg2|cfg4")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
     ap.add_argument("--no-secondary", action="store_true", help="skip the LSTM (configs[1]) measurement beside the transformer headline")
@@ -46,11 +47,12 @@ def parse():
 def workload_config(args):
     from blt_vqg_b200 import synth
     if args.workload == "transformer":
-        cfg = dict(synth.CONFIGS["cfg3"])   # BASELINE.json configs[2]: 6 layers, d_model 512, 8 heads, T=20, batch 512
-        name = "IQ transformer decoder (BLT-VQG, latent mode), 6 layers, d_model 512, 8 heads, E=300, F=2048, V=15000, T=20, S=5, R=21, FEAT=2048"
+        cfg = dict(synth.CONFIGS[args.config or "cfg3"])   # BASELINE.json configs[2]: 6 layers, d_model 512, 8 heads, T=20, batch 512
+        name = "IQ transformer decoder (BLT-VQG, latent mode), %d layers, d_model %d, %d heads, E=%d, F=%d, V=%d, T=%d, S=%d, R=%d, FEAT=%d" % (
+            cfg["NL"], cfg["H"], cfg["NH"], cfg["E"], cfg["F"], cfg["V"], cfg["T"], cfg["S"], cfg["T"] + 1, cfg["FEAT"])
     else:
-        cfg = dict(synth.LSTM_CONFIGS["cfg2"])  # BASELINE.json configs[1]: GloVe-300 LSTM, V=15000, batch 256
-        name = "IQ LSTM decoder full size (GloVe 300-d => H=300), Z=100, V=15000, T=20, FEAT=2048"
+        cfg = dict(synth.LSTM_CONFIGS[args.config or "cfg2"])  # BASELINE.json configs[1]: GloVe-300 LSTM, V=15000, batch 256
+        name = "IQ LSTM decoder%s, H=%d, Z=%d, V=%d, T=%d, FEAT=%d" % (" full size (GloVe 300-d => H=300)" if cfg["H"] == 300 else "", cfg["H"], cfg["Z"], cfg["V"], cfg["T"], cfg["FEAT"])
     if args.batch:
         cfg["B"] = args.batch
     return cfg, name
@@ -366,11 +368,11 @@ def main():
         dp = GradReducer()
     line, detail = measure(args, cfg, config, dp, rank, world, local_rank, roofline=not args.no_roofline,
                            cpu_arm=not args.no_cpu_baseline)
-    if rank == 0 and args.workload == "transformer" and not args.no_secondary:
+    if rank == 0 and args.workload == "transformer" and not args.no_secondary and not args.config:
         # BASELINE.json configs[1] (LSTM decoder, full size) measured the same way, reported beside the headline workload
         import copy
         a2 = copy.copy(args)
-        a2.workload, a2.batch = "lstm", 0
+        a2.workload, a2.batch, a2.config = "lstm", 0, ""
         cfg2, name2 = workload_config(a2)
         if world == 1:
             l2, _ = measure(a2, cfg2, {"workload": name2}, None, rank, world, local_rank, roofline=False, cpu_arm=False)

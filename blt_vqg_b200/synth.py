@@ -45,6 +45,9 @@ CONFIGS = {
     # tiny: checked-in golden fixtures
     "tiny": dict(B=4, V=200, E=32, H=64, L=16, F=128, NL=2, NH=4, T=8, S=5, FEAT=48),
     "small": dict(B=16, V=1000, E=60, H=128, L=32, F=256, NL=2, NH=4, T=12, S=5, FEAT=256),
+    # cfg3's widths (head_dim 64, H=512, F=2048, V=15000, T=20) at 2 layers and a small batch: the production kernel variants
+    # (CTA-pair GEMM, tensor-core attention, warp-per-row LayerNorm, chunked vocabulary CE) against the host oracle in seconds
+    "wide": dict(B=24, V=15000, E=300, H=512, L=100, F=2048, NL=2, NH=8, T=20, S=5, FEAT=2048),
     # BASELINE.json configs[0] sizes on the transformer variant
     "cfg1": dict(B=32, V=5000, E=300, H=512, L=100, F=2048, NL=6, NH=8, T=20, S=5, FEAT=2048),
     # BASELINE.json configs[2]: the single-GPU transformer workload the metric is quoted on

@@ -106,12 +106,13 @@ def test_training_step_matches_reference_golden(env, golden_dir, mode, simt):
     assert rel(m.bn_running_var, gold["bn_running_var_after"]) < 1e-3
 
 
-@pytest.mark.parametrize("latent", [True, False])
-def test_training_step_matches_oracle_small(env, latent):
-    """seeded synthetic batch at a mid size (ragged lengths, 12 tokens): oracle computed here on the host"""
+@pytest.mark.parametrize("latent,size", [(True, "small"), (False, "small"), (True, "wide")])
+def test_training_step_matches_oracle_small(env, latent, size):
+    """seeded synthetic batch at a mid size (ragged lengths, 12 tokens) and at cfg3's full widths (2 layers, 20 tokens):
+    oracle computed here on the host"""
     from blt_vqg_b200 import synth
     from oracle import iq_oracle
-    cfg = synth.CONFIGS["small"]
+    cfg = synth.CONFIGS[size]
     batch = synth.make_batch(cfg)
     from blt_vqg_b200.iq import IQ
     torch.manual_seed(3)
