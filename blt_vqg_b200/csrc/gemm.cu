@@ -280,8 +280,11 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         if (row0 >= epi.M) continue;  // warp-uniform: nothing of this quadrant is inside the matrix
         if (use_tma_c) {
           uint8_t* buf = stg + (chunk & 1) * STG_BYTES;
-          if (lane == 0) bulk_wait_read<1>();  // the store that last read this buffer has finished reading
-          __syncwarp();
+          const bool by_tma = accum || use_tma_c == 1;
+          if (by_tma) {
+            if (lane == 0) bulk_wait_read<1>();  // the store that last read this buffer has finished reading
+            __syncwarp();
+          }
           if (has_r) {
             // transpose through the staging buffer (same 128B swizzle as the output tile): lane r later re-reads row r
 #pragma unroll
@@ -323,13 +326,33 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             // 128B swizzle: 16-byte chunk index XOR (row & 7), the layout the C tensor map expects; TMA clips M/N edges
             *slot = make_float4(v[0], v[1], v[2], v[3]);
           }
-          fence_async_smem();
-          __syncwarp();
-          if (lane == 0) {
-            if (accum) tma_reduce_add_2d(&tmC, buf, col0, row0); else tma_store_2d(&tmC, buf, col0, row0);
-            bulk_commit();
+          if (by_tma) {
+            fence_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+              if (accum) tma_reduce_add_2d(&tmC, buf, col0, row0); else tma_store_2d(&tmC, buf, col0, row0);
+              bulk_commit();
+            }
+            ++chunk;
+          } else {
+            // use_tma_c == 2: plain stores, re-read from the staging tile so that 8 lanes write one full 128-byte line
+            __syncwarp();
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const int tr = i * 4 + (lane >> 3), ch = lane & 7;
+              const float4 v4 = *reinterpret_cast<const float4*>(buf + tr * 128 + ((ch ^ (tr & 7)) << 4));
+              const int grow = row0 + tr, gcol = col0 + ch * 4;
+              if (grow < epi.M) {
+                float* dst = epi.C + (size_t)grow * epi.ldc + gcol;
+                if (gcol + 3 < epi.N) *reinterpret_cast<float4*>(dst) = v4;
+                else {
+                  const float* va = &v4.x;
+                  for (int t = 0; t < 4; ++t) if (gcol + t < epi.N) dst[t] = va[t];
+                }
+              }
+            }
+            __syncwarp();
           }
-          ++chunk;
         } else {
           // C cannot go through TMA (pitch / base not 16-byte aligned): rare, so compact code matters more than speed —
           // park the row in the staging buffer and run a rolled loop over it
@@ -553,7 +576,9 @@ extern "C" int b200iq_gemm(const B200iqGemm* p, void* stream) {
   if (!bmn) rc = make_map(&tb, p->B, p->N, p->K, p->ldb, BNL, false); else rc = make_map(&tb, p->B, p->K, p->N, p->ldb, BK, true);
   if (rc) return rc;
   // C goes out through TMA (32 x 32 boxes, 128B swizzle) when its pitch / base allow it; else per-thread stores
-  const int use_tma_c = ((p->ldc & 3) == 0 && (((uintptr_t)p->C) & 15) == 0) ? 1 : 0;
+  static int store_mode = -1;  // B200IQ_GEMM_STORE=2: staged st.global instead of TMA stores (tuning)
+  if (store_mode < 0) { const char* v = getenv("B200IQ_GEMM_STORE"); store_mode = v ? atoi(v) : 1; }
+  const int use_tma_c = ((p->ldc & 3) == 0 && (((uintptr_t)p->C) & 15) == 0) ? store_mode : 0;
   if (use_tma_c) rc = make_map(&tc, p->C, p->M, p->N, p->ldc, 32, false); else memset(&tc, 0, sizeof(tc));
   if (rc) return rc;
 #define B200IQ_LAUNCH2(BN_, FE_, CT_) \

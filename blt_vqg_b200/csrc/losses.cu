@@ -50,6 +50,54 @@ ce_rows_kernel(float* __restrict__ logits, int ld, const int* __restrict__ targe
   }
 }
 
+// Register-resident variant: the row lives in up to 16 float4 per thread (V <= 16 * 4 * THREADS), so the logits chunk is read
+// once and written once with 16-byte accesses and exp() runs once per element.  Same math / same outputs as ce_rows_kernel.
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS)
+ce_rows_reg_kernel(float* __restrict__ logits, int ld, const int* __restrict__ targets, int V, int pad,
+                   const float* __restrict__ count, float coef, float* __restrict__ loss_sum, int write_grad, int rn) {
+  __shared__ float red[32];
+  const int r = blockIdx.x, V4 = V >> 2;
+  float4* row = reinterpret_cast<float4*>(logits + (size_t)r * ld);
+  const int tgt = __ldg(targets + r);
+  if (tgt == pad) {
+    if (write_grad) for (int c = threadIdx.x; c < V4; c += THREADS) row[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+    return;
+  }
+  float4 v[16];
+  float mx = -3.0e38f;
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    const int c = threadIdx.x + i * THREADS;
+    v[i] = make_float4(-3.0e38f, -3.0e38f, -3.0e38f, -3.0e38f);
+    if (c < V4) v[i] = row[c];
+    mx = fmaxf(fmaxf(mx, fmaxf(v[i].x, v[i].y)), fmaxf(v[i].z, v[i].w));
+  }
+  mx = block_max(mx, red);
+  const float xt = logits[(size_t)r * ld + tgt];
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    v[i].x = __expf(v[i].x - mx); v[i].y = __expf(v[i].y - mx); v[i].z = __expf(v[i].z - mx); v[i].w = __expf(v[i].w - mx);
+    s += (v[i].x + v[i].y) + (v[i].z + v[i].w);   // padding slots hold exp(-huge) = 0
+  }
+  s = block_sum(s, red);
+  const float inv_cnt = 1.f / __ldg(count);
+  if (threadIdx.x == 0) atomicAdd(loss_sum, (mx + logf(s) - xt) * inv_cnt);
+  if (write_grad) {
+    const float k = coef * inv_cnt, ks = k / s;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      const int c = threadIdx.x + i * THREADS;
+      if (c < V4) {
+        float4 o = make_float4(ks * v[i].x, ks * v[i].y, ks * v[i].z, ks * v[i].w);
+        if ((tgt >> 2) == c) { float* oa = &o.x; oa[tgt & 3] -= k; }
+        row[c] = make_float4(rnd(o.x, rn), rnd(o.y, rn), rnd(o.z, rn), rnd(o.w, rn));
+      }
+    }
+  }
+}
+
 // Auxiliary loss: CE(repeat(z_logit, T), target) without the repeat.  One CTA per sample b.
 // loss_sum += (cnt_b * lse_b - sum_t z_logit[b, tgt_bt]) / count;  dz[b,:] = coef * (cnt_b * softmax - hist(tgt_b)) / count
 // replaces: train_iq.py:92-94
@@ -304,6 +352,11 @@ extern "C" int b200iq_ce_rows(float* logits, int ld, const int* targets, int row
                               float coef, float* loss_sum, int write_grad, void* stream) {
   B200IQ_CHECK_ARG(logits && targets && count && loss_sum && rows > 0 && V > 0 && ld >= V, "ce_rows: bad args");
   size_t smem = (size_t)V * sizeof(float);
+  if ((V & 3) == 0 && (ld & 3) == 0 && (((uintptr_t)logits) & 15) == 0 && V <= 16 * 4 * 512) {
+    if (V <= 16 * 4 * 256) ce_rows_reg_kernel<256><<<rows, 256, 0, ST>>>(logits, ld, targets, V, pad_id, count, coef, loss_sum, write_grad, round_mode());
+    else ce_rows_reg_kernel<512><<<rows, 512, 0, ST>>>(logits, ld, targets, V, pad_id, count, coef, loss_sum, write_grad, round_mode());
+    return launch_status("ce_rows");
+  }
   int cache = smem <= 200 * 1024;
   if (!cache) smem = 0;
   static size_t attr = 0;
