@@ -275,6 +275,27 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       for (int c = chalf * CHUNKS; c < (chalf + 1) * CHUNKS; ++c) {
         const int col0 = n0 + c * 32;
         if (col0 >= epi.N) break;  // warp-uniform
+        // the chunk's 32 bias values travel while tcgen05.ld is in flight (loaded inside the j-loop below they cost one
+        // L1/L2 round trip per float4: ncu showed the epilogue FFMAs waiting on exactly these loads)
+        const bool bias_on = (epi.flags & B200IQ_GEMM_BIAS) && add_bias;
+        float4 bias4[8];
+        if (bias_on) {
+          if (col0 + 32 <= epi.N && ((((uintptr_t)(epi.bias + col0)) & 15) == 0)) {
+            const float4* b4 = reinterpret_cast<const float4*>(epi.bias + col0);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) bias4[j] = __ldg(b4 + j);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              float* b1 = &bias4[j].x;
+#pragma unroll
+              for (int t = 0; t < 4; ++t) b1[t] = (col0 + 4 * j + t < epi.N) ? __ldg(epi.bias + col0 + 4 * j + t) : 0.f;
+            }
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) bias4[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
         uint32_t rr[32];
         tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN + c * 32, rr);
         if (row0 >= epi.M) continue;  // warp-uniform: nothing of this quadrant is inside the matrix
@@ -293,20 +314,10 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             __syncwarp();
             if (c + 1 < (chalf + 1) * CHUNKS && col0 + 32 < epi.N) fetch_g(row0, col0 + 32);  // in flight during the math below
           }
-          const bool bias_on = (epi.flags & B200IQ_GEMM_BIAS) && add_bias;
-          const bool full = col0 + 32 <= epi.N;
-          const bool bvec = bias_on && full && ((((uintptr_t)(epi.bias + col0)) & 15) == 0);
-          const float4* b4 = reinterpret_cast<const float4*>(epi.bias + col0);
 #pragma unroll
           for (int j = 0; j < 32; j += 4) {
             float4* slot = reinterpret_cast<float4*>(buf + lane * 128 + (((j >> 2) ^ (lane & 7)) << 4));
-            float4 bb = make_float4(0.f, 0.f, 0.f, 0.f), gg = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (bvec) bb = __ldg(b4 + (j >> 2));
-            else if (bias_on) {
-              float* b1 = &bb.x;
-#pragma unroll
-              for (int t = 0; t < 4; ++t) if (col0 + j + t < epi.N) b1[t] = __ldg(epi.bias + col0 + j + t);
-            }
+            float4 bb = bias4[j >> 2], gg = make_float4(0.f, 0.f, 0.f, 0.f);
             if (has_r) gg = *slot;
             uint32_t keep[4] = {0u, 0u, 0u, 0u};
             if (drop) {  // one Philox call covers the 4 consecutive elements of this float4 (N % 4 == 0, ldc == N)

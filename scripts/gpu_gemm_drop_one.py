@@ -7,7 +7,7 @@ _lib.require_device()
 tile = int(sys.argv[1]) if len(sys.argv) > 1 else 0
 kind = sys.argv[2] if len(sys.argv) > 2 else "drop"
 _lib.lib().b200iq_set_gemm_tile(tile)
-M, N, K = 10240, 2048, 512
+M, N, K = 10240, int(sys.argv[3]) if len(sys.argv) > 3 else 2048, 512
 A, B, C = torch.randn(M, K, device="cuda"), torch.randn(N, K, device="cuda"), torch.empty(M, N, device="cuda")
 bias, R = torch.randn(N, device="cuda"), torch.randn(M, N, device="cuda")
 for _ in range(5):
