@@ -96,7 +96,7 @@ __device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {
                ::"r"(smem_u32(bar)), "h"((uint16_t)3) : "memory");
 }
 __device__ __forceinline__ void mbar_arrive_leader(uint64_t* bar) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(smem_u32(bar) & PEER_MASK) : "memory");
+  asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(smem_u32(bar) & PEER_MASK) : "memory");
 }
 
 // shared-memory matrix descriptor, 128B swizzle, sm_100 descriptor version 1
@@ -137,7 +137,9 @@ template <int N> __device__ __forceinline__ void bulk_wait_read() { asm volatile
 __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+  // relaxed: the arrive only says "this warp's tcgen05.ld of the accumulator has completed" (tcgen05.wait::ld + the tcgen05
+  // fence order that); the default .release compiled to MEMBAR.ALL.CTA + ERRBAR behind the epilogue's stores (7 % of its samples)
+  asm volatile("mbarrier.arrive.relaxed.cta.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
 // Persistent GEMM: grid = min(#work items, #SMs); a work item = (split-K slice, 128 x BN output tile).
@@ -150,7 +152,7 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
 template <int BN, bool A_MN, bool B_MN, int STAGES, int EPI, int CTAS>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                 const __grid_constant__ CUtensorMap tmC, GemmEpi epi, int m_tiles, int n_tiles, int splits,
+                 const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmR, GemmEpi epi, int m_tiles, int n_tiles, int splits,
                  int kblocks_total, int kblocks_per_split, int use_tma_c) {
   constexpr int BNL = BN / CTAS;  // rows of B this CTA stages (the pair's MMA reads N/2 from each CTA)
   constexpr int A_BYTES = BM * 128, B_BYTES = BNL * 128, STAGE_BYTES = A_BYTES + B_BYTES;
@@ -159,6 +161,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   uint8_t* stg_base = smem + STAGES * STAGE_BYTES;  // [8 epilogue warps][2 buffers][4096 B], 1024-aligned
   __shared__ uint64_t full_bar[STAGES], empty_bar[STAGES], tfull_bar[2], tempty_bar[2];
+  __shared__ uint64_t gbar[EPI == 1 ? EPI_WARPS : 1][2];  // residual / gate tiles arriving by TMA, per epilogue warp and staging buffer
   __shared__ uint32_t tmem_base_s;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -169,6 +172,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   if (threadIdx.x == 0) {
     for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
     for (int a = 0; a < 2; ++a) { mbar_init(&tfull_bar[a], 1); mbar_init(&tempty_bar[a], EPI_WARPS * CTAS); }
+    if (EPI == 1) for (int a = 0; a < EPI_WARPS; ++a) { mbar_init(&gbar[a][0], 1); mbar_init(&gbar[a][1], 1); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 2) {
@@ -254,12 +258,16 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const bool gate = EPI == 1 && (epi.flags & B200IQ_GEMM_RELU_MASK), relu = epi.flags & B200IQ_GEMM_RELU;
     const bool drop = EPI == 2;
     uint32_t ti = 0, chunk = 0;
-    float g[32];  // residual / relu-gate tile of the NEXT chunk: row r of the tile, column `lane` (coalesced 128-byte rows)
-    auto fetch_g = [&](int row0, int col0) {
-      const int cc = col0 + lane;
-      const float* src = epi.residual + (size_t)row0 * epi.ldr + cc;
-#pragma unroll
-      for (int r = 0; r < 32; ++r) g[r] = (row0 + r < epi.M && cc < epi.N) ? __ldg(src + (size_t)r * epi.ldr) : 0.f;
+    // EPI 1: the 32 x 32 residual / relu-gate tile of a chunk is pulled by TMA straight into the chunk's staging buffer (same
+    // 128B swizzle as the output tile, so lane r finds row r where it will write row r), one chunk ahead of the math.
+    // `ch` = the chunk counter value the tile belongs to; its buffer was last read by the store of chunk ch - 2.
+    auto fetch_r = [&](int row0, int col0, uint32_t ch) {
+      if (lane == 0) {
+        bulk_wait_read<1>();
+        uint64_t* gb = &gbar[EPI == 1 ? warp - 2 : 0][ch & 1];
+        mbar_expect_tx(gb, STG_BYTES);
+        tma_load_2d(stg + (ch & 1) * STG_BYTES, &tmR, col0, row0, gb);
+      }
     };
     for (int w = w_first; w < total; w += w_step, ++ti) {
       const int z = w / tiles, r = w - z * tiles, mt = r / n_tiles, nt = r - mt * n_tiles;
@@ -268,7 +276,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const int row0 = m0 + q * 32, row = row0 + lane;
       const bool add_bias = (z == 0);
       // the first chunk's residual tile travels while the MMAs of this tile are still running
-      if (has_r && use_tma_c) fetch_g(row0, n0 + chalf * CHUNKS * 32);
+      if (has_r && use_tma_c && row0 < epi.M && n0 + chalf * CHUNKS * 32 < epi.N) fetch_r(row0, n0 + chalf * CHUNKS * 32, chunk);
       mbar_wait(&tfull_bar[acc], aph);
       tc_fence_after();
 #pragma unroll 1
@@ -301,18 +309,11 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         if (row0 >= epi.M) continue;  // warp-uniform: nothing of this quadrant is inside the matrix
         if (use_tma_c) {
           uint8_t* buf = stg + (chunk & 1) * STG_BYTES;
-          const bool by_tma = accum || use_tma_c == 1;
-          if (by_tma) {
+          if (has_r) {
+            mbar_wait(&gbar[EPI == 1 ? warp - 2 : 0][chunk & 1], (chunk >> 1) & 1);  // the tile has landed
+          } else {
             if (lane == 0) bulk_wait_read<1>();  // the store that last read this buffer has finished reading
             __syncwarp();
-          }
-          if (has_r) {
-            // transpose through the staging buffer (same 128B swizzle as the output tile): lane r later re-reads row r
-#pragma unroll
-            for (int r2 = 0; r2 < 32; ++r2)
-              *reinterpret_cast<float*>(buf + r2 * 128 + ((((lane >> 2) ^ (r2 & 7)) << 4) | ((lane & 3) << 2))) = g[r2];
-            __syncwarp();
-            if (c + 1 < (chalf + 1) * CHUNKS && col0 + 32 < epi.N) fetch_g(row0, col0 + 32);  // in flight during the math below
           }
 #pragma unroll
           for (int j = 0; j < 32; j += 4) {
@@ -337,33 +338,14 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             // 128B swizzle: 16-byte chunk index XOR (row & 7), the layout the C tensor map expects; TMA clips M/N edges
             *slot = make_float4(v[0], v[1], v[2], v[3]);
           }
-          if (by_tma) {
-            fence_async_smem();
-            __syncwarp();
-            if (lane == 0) {
-              if (accum) tma_reduce_add_2d(&tmC, buf, col0, row0); else tma_store_2d(&tmC, buf, col0, row0);
-              bulk_commit();
-            }
-            ++chunk;
-          } else {
-            // use_tma_c == 2: plain stores, re-read from the staging tile so that 8 lanes write one full 128-byte line
-            __syncwarp();
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              const int tr = i * 4 + (lane >> 3), ch = lane & 7;
-              const float4 v4 = *reinterpret_cast<const float4*>(buf + tr * 128 + ((ch ^ (tr & 7)) << 4));
-              const int grow = row0 + tr, gcol = col0 + ch * 4;
-              if (grow < epi.M) {
-                float* dst = epi.C + (size_t)grow * epi.ldc + gcol;
-                if (gcol + 3 < epi.N) *reinterpret_cast<float4*>(dst) = v4;
-                else {
-                  const float* va = &v4.x;
-                  for (int t = 0; t < 4; ++t) if (gcol + t < epi.N) dst[t] = va[t];
-                }
-              }
-            }
-            __syncwarp();
+          fence_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            if (accum) tma_reduce_add_2d(&tmC, buf, col0, row0); else tma_store_2d(&tmC, buf, col0, row0);
+            bulk_commit();
           }
+          ++chunk;
+          if (has_r && c + 1 < (chalf + 1) * CHUNKS && col0 + 32 < epi.N) fetch_r(row0, col0 + 32, chunk);  // next chunk's tile
         } else {
           // C cannot go through TMA (pitch / base not 16-byte aligned): rare, so compact code matters more than speed —
           // park the row in the staging buffer and run a rolled loop over it
@@ -478,7 +460,7 @@ static int make_map(CUtensorMap* tm, const float* base, int rows, int cols, int 
 }
 
 template <int BN, bool A_MN, bool B_MN, int EPI, int CTAS>
-static int launch_tc(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, int use_tma_c, const GemmEpi& e, int K,
+static int launch_tc(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const CUtensorMap& tr, int use_tma_c, const GemmEpi& e, int K,
                      int split, cudaStream_t st) {
   constexpr int STAGES = (CTAS == 2) ? 5 : (BN == 256) ? 3 : 4;
   constexpr int SMEM = STAGES * (BM * 128 + (BN / CTAS) * 128) + EPI_WARPS * 2 * 32 * 128 + 1024;
@@ -497,7 +479,7 @@ static int launch_tc(const CUtensorMap& ta, const CUtensorMap& tb, const CUtenso
   const int slots = sm_count() / CTAS;
   const int grid = (total < slots ? total : slots) * CTAS;
   if (CTAS == 1) {
-    kern<<<grid, GEMM_THREADS, SMEM, st>>>(ta, tb, tc, e, m_tiles, n_tiles, split, kblocks, per, use_tma_c);
+    kern<<<grid, GEMM_THREADS, SMEM, st>>>(ta, tb, tc, tr, e, m_tiles, n_tiles, split, kblocks, per, use_tma_c);
   } else {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(grid); cfg.blockDim = dim3(GEMM_THREADS); cfg.dynamicSmemBytes = SMEM; cfg.stream = st;
@@ -505,7 +487,7 @@ static int launch_tc(const CUtensorMap& ta, const CUtensorMap& tb, const CUtenso
     at[0].id = cudaLaunchAttributeClusterDimension;
     at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     cfg.attrs = at; cfg.numAttrs = 1;
-    cudaError_t err = cudaLaunchKernelEx(&cfg, kern, ta, tb, tc, e, m_tiles, n_tiles, split, kblocks, per, use_tma_c);
+    cudaError_t err = cudaLaunchKernelEx(&cfg, kern, ta, tb, tc, tr, e, m_tiles, n_tiles, split, kblocks, per, use_tma_c);
     if (err != cudaSuccess) { set_error("gemm_tf32_kernel<pair>: %s", cudaGetErrorString(err)); return (int)err; }
   }
   return launch_status("gemm_tf32_kernel");
@@ -523,11 +505,11 @@ static int pick_bn(int M, int N, int K, int split, bool heavy_epi, bool dropout_
   if (g_force_tile == 128 || g_force_tile == 256) return N <= 128 ? 128 : g_force_tile;
   if (N <= 128) return 128;
   // measured on the cfg3 shapes (scripts/gpu_gemm_sweep.py, profiles/r01g_gemm_sweep.txt):
-  //  * residual / relu-gate epilogues are epilogue-bound: 128 x 128 tiles (2 chunks per epilogue warp and tile) win everywhere
-  //  * dropout epilogues: pairs once the reduction is long enough to hide them (K >= 1024), else 256 / 128 by tile count
+  //  * residual / relu-gate epilogues (tile pulled in by TMA): pairs for wide outputs, 128 x 128 tiles for N = 512
+  //  * dropout epilogues: pairs for long reductions or big outputs, else 128 x 128
   //  * everything else: CTA pairs (20-35 % faster than 128 x 256 at K >= 1536, 5-10 % at K = 512)
-  if (heavy_epi) return 128;
-  if (dropout_epi) return (pair_ok && K / split >= 1024) ? 512 : ((long)M * N >= (8192L * 2048) ? 256 : 128);
+  if (heavy_epi) return (pair_ok && N >= 1024) ? 512 : 128;
+  if (dropout_epi) return (pair_ok && (K / split >= 1024 || (long)M * N >= (8192L * 2048))) ? 512 : 128;
   if (pair_ok) return 512;
   const int sms = sm_count();
   const long t128 = (long)ceil_div(M, BM) * ceil_div(N, 128) * split, t256 = (long)ceil_div(M, BM) * ceil_div(N, 256) * split;
@@ -587,21 +569,26 @@ extern "C" int b200iq_gemm(const B200iqGemm* p, void* stream) {
   if (!bmn) rc = make_map(&tb, p->B, p->N, p->K, p->ldb, BNL, false); else rc = make_map(&tb, p->B, p->K, p->N, p->ldb, BK, true);
   if (rc) return rc;
   // C goes out through TMA (32 x 32 boxes, 128B swizzle) when its pitch / base allow it; else per-thread stores
-  static int store_mode = -1;  // B200IQ_GEMM_STORE=2: staged st.global instead of TMA stores (tuning)
-  if (store_mode < 0) { const char* v = getenv("B200IQ_GEMM_STORE"); store_mode = v ? atoi(v) : 1; }
-  const int use_tma_c = ((p->ldc & 3) == 0 && (((uintptr_t)p->C) & 15) == 0) ? store_mode : 0;
+  // C goes out through TMA (32 x 32 boxes, 128B swizzle) when its pitch / base allow it — and so does the residual / gate
+  // tile coming in; otherwise the per-thread fallback path
+  const bool has_res = (f & (B200IQ_GEMM_RESIDUAL | B200IQ_GEMM_RELU_MASK)) != 0;
+  const int use_tma_c = ((p->ldc & 3) == 0 && (((uintptr_t)p->C) & 15) == 0 &&
+                         (!has_res || ((p->ldr & 3) == 0 && (((uintptr_t)p->residual) & 15) == 0))) ? 1 : 0;
+  CUtensorMap tr;
+  memset(&tr, 0, sizeof(tr));
+  if (use_tma_c && has_res) { rc = make_map(&tr, p->residual, p->M, p->N, p->ldr, 32, false); if (rc) return rc; }
   if (use_tma_c) rc = make_map(&tc, p->C, p->M, p->N, p->ldc, 32, false); else memset(&tc, 0, sizeof(tc));
   if (rc) return rc;
 #define B200IQ_LAUNCH2(BN_, FE_, CT_) \
   do { \
-    if (!amn && !bmn) return launch_tc<BN_, false, false, FE_, CT_>(ta, tb, tc, use_tma_c, e, p->K, split, st); \
-    if (!amn && bmn) return launch_tc<BN_, false, true, FE_, CT_>(ta, tb, tc, use_tma_c, e, p->K, split, st); \
-    if (amn && !bmn) return launch_tc<BN_, true, false, FE_, CT_>(ta, tb, tc, use_tma_c, e, p->K, split, st); \
-    return launch_tc<BN_, true, true, FE_, CT_>(ta, tb, tc, use_tma_c, e, p->K, split, st); \
+    if (!amn && !bmn) return launch_tc<BN_, false, false, FE_, CT_>(ta, tb, tc, tr, use_tma_c, e, p->K, split, st); \
+    if (!amn && bmn) return launch_tc<BN_, false, true, FE_, CT_>(ta, tb, tc, tr, use_tma_c, e, p->K, split, st); \
+    if (amn && !bmn) return launch_tc<BN_, true, false, FE_, CT_>(ta, tb, tc, tr, use_tma_c, e, p->K, split, st); \
+    return launch_tc<BN_, true, true, FE_, CT_>(ta, tb, tc, tr, use_tma_c, e, p->K, split, st); \
   } while (0)
 #define B200IQ_LAUNCH(BN_, CT_) \
   do { \
-    if (epi_mode == 2) return launch_tc<BN_, false, false, 2, CT_>(ta, tb, tc, use_tma_c, e, p->K, split, st); \
+    if (epi_mode == 2) return launch_tc<BN_, false, false, 2, CT_>(ta, tb, tc, tr, use_tma_c, e, p->K, split, st); \
     if (epi_mode == 1) B200IQ_LAUNCH2(BN_, 1, CT_); else B200IQ_LAUNCH2(BN_, 0, CT_); \
   } while (0)
   // without a TMA-storable C the per-thread fallback path handles every flag itself (epi_value)
