@@ -20,6 +20,7 @@ struct AttnArgs {
   float scale, drop_p;
   uint64_t seed, offset;
   int rn;  // round outputs to TF32
+  size_t bsk, bsv;  // elements between consecutive samples' K / V blocks (nk*ldk, nk*ldv unless reading a KV cache)
 };
 
 __device__ __forceinline__ float keep_scale(const AttnArgs& a, size_t elem) {
@@ -82,8 +83,8 @@ attention_fwd_kernel(AttnArgs a, float* __restrict__ out, int ldo) {
   float* Vs = Ks + a.nk * dp;
   float* Ps = Vs + a.nk * dp;  // [4 warps][nk]
   load_tile(Qs, a.q + (size_t)b * a.nq * a.ldq + h * a.d, a.nq, a.d, dp, a.ldq);
-  load_tile(Ks, a.k + (size_t)b * a.nk * a.ldk + h * a.d, a.nk, a.d, dp, a.ldk);
-  load_tile(Vs, a.v + (size_t)b * a.nk * a.ldv + h * a.d, a.nk, a.d, dp, a.ldv);
+  load_tile(Ks, a.k + (size_t)b * a.bsk + h * a.d, a.nk, a.d, dp, a.ldk);
+  load_tile(Vs, a.v + (size_t)b * a.bsv + h * a.d, a.nk, a.d, dp, a.ldv);
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   float* Pw = Ps + warp * a.nk;
@@ -118,8 +119,8 @@ attention_bwd_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, float*
   float* Ws = dOs + a.nq * dp;   // post-dropout weights [nq][np]
   float* dSs = Ws + a.nq * np;   // d(logits) * scale     [nq][np]
   load_tile(Qs, a.q + (size_t)b * a.nq * a.ldq + h * a.d, a.nq, a.d, dp, a.ldq);
-  load_tile(Ks, a.k + (size_t)b * a.nk * a.ldk + h * a.d, a.nk, a.d, dp, a.ldk);
-  load_tile(Vs, a.v + (size_t)b * a.nk * a.ldv + h * a.d, a.nk, a.d, dp, a.ldv);
+  load_tile(Ks, a.k + (size_t)b * a.bsk + h * a.d, a.nk, a.d, dp, a.ldk);
+  load_tile(Vs, a.v + (size_t)b * a.bsv + h * a.d, a.nk, a.d, dp, a.ldv);
   load_tile(dOs, dout + (size_t)b * a.nq * ldo + h * a.d, a.nq, a.d, dp, ldo);
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -307,8 +308,8 @@ attention_fwd_tc_kernel(AttnArgs a, float* __restrict__ out, int ldo) {
   if (bh >= a.B * a.nh) return;
   const int b = bh / a.nh, h = bh - b * a.nh, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
   const float* Q = a.q + (size_t)b * a.nq * a.ldq + h * 64;
-  const float* K = a.k + (size_t)b * a.nk * a.ldk + h * 64;
-  const float* V = a.v + (size_t)b * a.nk * a.ldv + h * 64;
+  const float* K = a.k + (size_t)b * a.bsk + h * 64;
+  const float* V = a.v + (size_t)b * a.bsv + h * 64;
   float S[MT][NT][4];
 #pragma unroll
   for (int mt = 0; mt < MT; ++mt)
@@ -387,8 +388,8 @@ attention_bwd_tc_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, flo
   if (bh >= a.B * a.nh) return;
   const int b = bh / a.nh, h = bh - b * a.nh, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
   const float* Q = a.q + (size_t)b * a.nq * a.ldq + h * 64;
-  const float* K = a.k + (size_t)b * a.nk * a.ldk + h * 64;
-  const float* V = a.v + (size_t)b * a.nk * a.ldv + h * 64;
+  const float* K = a.k + (size_t)b * a.bsk + h * 64;
+  const float* V = a.v + (size_t)b * a.bsv + h * 64;
   const float* dO = dout + (size_t)b * a.nq * ldo + h * 64;
   float S[MT][NT][4], dW[MT][NT][4];
 #pragma unroll
@@ -456,6 +457,8 @@ static AttnArgs to_args(const B200iqAttention* p) {
   a.B = p->B; a.nh = p->num_heads; a.nq = p->nq; a.nk = p->nk; a.d = p->head_dim;
   a.scale = p->scale; a.drop_p = p->drop_p; a.seed = p->seed; a.offset = p->offset;
   a.rn = round_mode();
+  a.bsk = p->kv_batch_stride > 0 ? (size_t)p->kv_batch_stride : (size_t)p->nk * p->ldk;
+  a.bsv = p->kv_batch_stride > 0 ? (size_t)p->kv_batch_stride : (size_t)p->nk * p->ldv;
   return a;
 }
 
@@ -499,6 +502,7 @@ extern "C" int b200iq_attention_bwd(const B200iqAttention* p, const float* dout,
                                     int lddq, int lddk, int lddv, void* stream) {
   if (int rc = check_attn(p)) return rc;
   B200IQ_CHECK_ARG(dout && dq && dk && dv, "attention_bwd: null pointer");
+  B200IQ_CHECK_ARG(p->kv_batch_stride == 0, "attention_bwd: kv_batch_stride is a forward-only (KV cache) option");
   AttnArgs a = to_args(p);
   {
     const void* ptrs[] = {p->q, p->k, p->v, dout, dq, dk, dv};

@@ -429,16 +429,71 @@ class IQ(nn.Module):
 
     # ------------------------------------------------------------------ greedy decoding (models/iq.py:117-152)
     @torch.no_grad()
-    def decode_greedy(self, images, answers, max_decode_length=50, eps=None, exact=True):
+    def decode_greedy(self, images, answers, max_decode_length=50, eps=None, exact=True, kv_cache=True):
         """models/iq.py:117-152: encoder once, prior-only latent (a fresh eps: Philox here, or injected), then
         max_decode_length+1 decoder passes over the growing prefix that starts with PAD (so key 0 is pad-masked and the first
         query row is fully masked -> uniform attention), argmax + top-6 softmax per step.
         Runs in EXACT fp32 (CUDA-core GEMMs, no TF32 rounding) so the token ids are bit-identical to an fp32 run.
+        kv_cache=True (default) feeds only the newest token through the decoder and keeps every layer's self-attention K/V
+        (and the cross-attention K/V of the 5-token context) in a cache: the decoder is causal and pre-LN, so earlier rows
+        never change and the last row comes out bit-identical to the reference's O(T^2) recomputation (kv_cache=False).
         Returns (sentences, top_args (B, L+1, 6) float32, top_vals (B, L+1, 6) float32) like the reference."""
         with ops.gemm_mode(simt=exact):
-            return self._decode_greedy(images, answers, max_decode_length, eps)
+            return self._decode_greedy(images, answers, max_decode_length, eps, kv_cache)
 
-    def _decode_greedy(self, images, answers, max_decode_length, eps):
+    def _decode_steps_cached(self, c, ys, top_i, top_v, enc_out, cids, img, z, B, S, steps):
+        """inference_forward (decoder_transformer.py:43-48) for the newest token only, with per-layer K/V caches"""
+        ws, P, W, H, V, NL, nh, d = c.ws, c.P, c.W, self.H, self.V, self.NL, self.nh, self.H // self.nh
+        pfx = "decoder.decoder."
+        kc = [ws.buf("kv.k%d" % i, B, steps, H) for i in range(NL)]
+        vc = [ws.buf("kv.v%d" % i, B, steps, H) for i in range(NL)]
+        ckv = []
+        for i in range(NL):   # cross-attention K | V of the context: once per layer instead of once per step
+            lp = "%sdec.%d.multi_head_attention_enc_dec." % (pfx, i)
+            ckv.append(ops.gemm(enc_out, c.pspan(lp + "key_linear.weight", lp + "value_linear.weight", H), ws.buf("kv.c%d" % i, B * S, 2 * H)))
+        e1, x = ws.buf("kv.e", B, self.E), ws.buf("kv.x", B, H)
+        xn, qkv, ctx = ws.buf("kv.xn", B, H), ws.buf("kv.qkv", B, 3 * H), ws.buf("kv.ctx", B, H)
+        a, q, b_, h, f2 = ws.buf("kv.a", B, H), ws.buf("kv.q", B, H), ws.buf("kv.b", B, H), ws.buf("kv.h", B, self.F), ws.buf("kv.f2", B, H)
+        logit = ws.buf("g.logit", B, V)
+        ti, tv = ws.buf("g.ti", B, 6, dtype=torch.int32), ws.buf("g.tv", B, 6)
+
+        def ln(name, src, dst):
+            ops.layernorm_fwd(src, P[name + ".weight"], P[name + ".bias"], dst, None, None)
+        for p in range(steps):
+            n = p + 1
+            tok = ys[:, p].contiguous()
+            prefix = ys[:, :n].contiguous()
+            ops.embed_gather(tok, P["embedding.0.weight"], e1)
+            ops.gemm(e1, W["embedding.1.weight"], x, bias=P["embedding.1.bias"])
+            # timing signal of position p; token 0 also gets z + image_features (decoder_transformer.py:46)
+            ops.add_timing(x, self.timing_dec[p:p + 1], z if p == 0 else None, img if p == 0 else None, B, 1, H)
+            for i in range(NL):
+                lp = "%sdec.%d." % (pfx, i)
+                sa, ca, ff = lp + "multi_head_attention_dec.", lp + "multi_head_attention_enc_dec.", lp + "positionwise_feed_forward."
+                ln(lp + "layer_norm_mha_dec", x, xn)
+                ops.gemm(xn, c.pspan(sa + "query_linear.weight", sa + "value_linear.weight", H), qkv)
+                kc[i][:, p].copy_(qkv[:, H:2 * H])
+                vc[i][:, p].copy_(qkv[:, 2 * H:])
+                # every cached key is at or before the query's position: the causal part of the mask is implied
+                ops.attention_fwd(qkv[:, :H], kc[i].view(B * steps, H), vc[i].view(B * steps, H), ctx, prefix, PAD, False, B, nh, 1, n, d,
+                                  kv_batch_stride=steps * H)
+                ops.gemm(ctx, W[sa + "output_linear.weight"], a, residual=x)
+                ln(lp + "layer_norm_mha_enc", a, xn)
+                ops.gemm(xn, W[ca + "query_linear.weight"], q)
+                ops.attention_fwd(q, ckv[i][:, :H], ckv[i][:, H:], ctx, cids, PAD, False, B, nh, 1, S, d)
+                ops.gemm(ctx, W[ca + "output_linear.weight"], b_, residual=a)
+                ln(lp + "layer_norm_ffn", b_, xn)
+                ops.gemm(xn, W[ff + "layers.0.weight"], h, bias=P[ff + "layers.0.bias"], relu=True)
+                ops.gemm(h, W[ff + "layers.1.weight"], f2, bias=P[ff + "layers.1.bias"], relu=True)
+                ops.axpby(b_, f2, x)
+            ln(pfx + "layer_norm", x, xn)
+            ops.gemm(xn, W["decoder.output.weight"], logit, bias=P["decoder.output.bias"], fp32_out=True)
+            ops.topk_softmax_rows(logit, 6, ti, tv)                           # iq.py:136-137
+            ys[:, n] = ti[:, 0]
+            top_i[:, p] = ti
+            top_v[:, p] = tv
+
+    def _decode_greedy(self, images, answers, max_decode_length, eps, kv_cache=True):
         dev = self.flat.device
         was_training = self.training
         self.eval()
@@ -479,17 +534,20 @@ class IQ(nn.Module):
             last = ws.buf("g.last", B, H)
             logit = ws.buf("g.logit", B, V)
             ti, tv = ws.buf("g.ti", B, 6, dtype=torch.int32), ws.buf("g.tv", B, 6)
-            for i in range(steps):
-                n = i + 1
-                prefix = ys[:, :n].contiguous()
-                xd = tf.embed_fwd(c, "g.emb", prefix, B, n, self.timing_dec, add0=z, add1=img)   # decoder_transformer.py:46
-                dec = tf.decoder_fwd(c, "g", "decoder.decoder.", xd, prefix, enc_out, cids, B, n, S, self.NL)
-                ops.tok0_gather(dec[n - 1:], last, B, n, H)                    # logits[:, -1]
-                ops.gemm(last, c.W["decoder.output.weight"], logit, bias=P["decoder.output.bias"], fp32_out=True)
-                ops.topk_softmax_rows(logit, 6, ti, tv)                       # iq.py:136-137
-                ys[:, n] = ti[:, 0]
-                top_i[:, i] = ti
-                top_v[:, i] = tv
+            if kv_cache:
+                self._decode_steps_cached(c, ys, top_i, top_v, enc_out, cids, img, z, B, S, steps)
+            else:
+                for i in range(steps):
+                    n = i + 1
+                    prefix = ys[:, :n].contiguous()
+                    xd = tf.embed_fwd(c, "g.emb", prefix, B, n, self.timing_dec, add0=z, add1=img)   # decoder_transformer.py:46
+                    dec = tf.decoder_fwd(c, "g", "decoder.decoder.", xd, prefix, enc_out, cids, B, n, S, self.NL)
+                    ops.tok0_gather(dec[n - 1:], last, B, n, H)                    # logits[:, -1]
+                    ops.gemm(last, c.W["decoder.output.weight"], logit, bias=P["decoder.output.bias"], fp32_out=True)
+                    ops.topk_softmax_rows(logit, 6, ti, tv)                       # iq.py:136-137
+                    ys[:, n] = ti[:, 0]
+                    top_i[:, i] = ti
+                    top_v[:, i] = tv
             ids = ys[:, 1:].cpu()
         finally:
             self.train(was_training)

@@ -120,6 +120,7 @@ class AttnParams(C.Structure):
         ("key_ids", C.c_void_p), ("pad_id", C.c_int), ("causal", C.c_int),
         ("B", C.c_int), ("num_heads", C.c_int), ("nq", C.c_int), ("nk", C.c_int), ("head_dim", C.c_int),
         ("scale", C.c_float), ("drop_p", C.c_float), ("seed", C.c_uint64), ("offset", C.c_uint64),
+        ("kv_batch_stride", C.c_longlong),
     ]
 
 
@@ -192,15 +193,16 @@ def axpby(x, y, out, a=1.0, b=1.0):
 
 
 # ------------------------------------------------------------------ attention
-def _attn_params(q, k, v, out, key_ids, pad_id, causal, B, nh, nq, nk, d, drop_p, seed, offset):
+def _attn_params(q, k, v, out, key_ids, pad_id, causal, B, nh, nq, nk, d, drop_p, seed, offset, kv_batch_stride=0):
     return AttnParams(q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr() if out is not None else 0,
                       q.stride(0), k.stride(0), v.stride(0), out.stride(0) if out is not None else 0,
                       key_ids.data_ptr() if key_ids is not None else 0, pad_id, int(causal),
-                      B, nh, nq, nk, d, d ** -0.5, drop_p, seed, offset)
+                      B, nh, nq, nk, d, d ** -0.5, drop_p, seed, offset, kv_batch_stride)
 
 
-def attention_fwd(q, k, v, out, key_ids, pad_id, causal, B, nh, nq, nk, d, drop_p=0.0, seed=0, offset=0):
-    p = _attn_params(q, k, v, out, key_ids, pad_id, causal, B, nh, nq, nk, d, drop_p, seed, offset)
+def attention_fwd(q, k, v, out, key_ids, pad_id, causal, B, nh, nq, nk, d, drop_p=0.0, seed=0, offset=0, kv_batch_stride=0):
+    """kv_batch_stride (elements) lets k / v be the first nk positions of a [B, max_len, H] KV cache"""
+    p = _attn_params(q, k, v, out, key_ids, pad_id, causal, B, nh, nq, nk, d, drop_p, seed, offset, kv_batch_stride)
     _call("b200iq_attention_fwd", C.byref(p))
     return out
 

@@ -126,6 +126,8 @@ typedef struct B200iqAttention {
   float scale;           /* head_dim^-0.5 (transformer_layers.py:449,499) */
   float drop_p;          /* attention dropout (transformer_layers.py:520); mask = Philox(seed, offset) */
   uint64_t seed, offset;
+  long long kv_batch_stride; /* elements between consecutive samples' K (and V) blocks; 0 = nk*ldk / nk*ldv (dense [B*nk, ld]).
+                                A KV cache [B, max_len, H] read at length nk passes max_len*H here (forward only). */
 } B200iqAttention;
 /* replaces: models/transformer_layers.py:494-526; mask fill is the finite -1e18 of :506 */
 int b200iq_attention_fwd(const B200iqAttention* p, void* stream);
