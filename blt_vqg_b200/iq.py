@@ -14,6 +14,7 @@ All arithmetic runs in libb200iq.so (sm_100a); torch is used for memory, streams
 case the frozen torchvision trunk of models/encoder_cnn.py:17-19 runs under no_grad first.
 """
 import math
+import os
 
 import numpy as np
 import torch
@@ -24,6 +25,7 @@ from . import transformer as tf
 from .params import Arena, TRANSFORMER_ALIASES, export_state_dict, import_state_dict, transformer_iq_specs
 
 PAD = 0
+CE_CHUNK_MB = int(os.environ.get("B200IQ_CE_CHUNK_MB", "80"))  # size of one logits chunk of the fused vocabulary projection + CE
 TERMS = ("rec", "img", "kld", "aux", "count", "gnorm_sq", "unused0", "unused1")
 
 
@@ -294,7 +296,7 @@ class IQ(nn.Module):
         return 1.0, a.image_recon_lambda, a.kl_ceiling * kl_w, a.aux_ceiling
 
     def _ce_chunk_rows(self, M):
-        rows = (48 << 20) // (4 * self.V)  # keep a logits chunk (fp32) around 48 MB: L2-resident on B200 (126 MB L2)
+        rows = (CE_CHUNK_MB << 20) // (4 * self.V)  # keep a logits chunk (fp32) L2-resident on B200 (126 MB L2)
         rows = max(128, rows // 128 * 128)
         return min(M, rows)
 
