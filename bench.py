@@ -331,8 +331,26 @@ def measure(args, cfg, config, dp, rank, world, local_rank, roofline=True, cpu_a
     return line, detail
 
 
+_REAL_STDOUT = None
+
+
+def emit(line):
+    """the ONE JSON line goes to the process's original stdout; everything else (NCCL's version banner, library chatter) was
+    re-routed to stderr by main()"""
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def main():
+    global _REAL_STDOUT
     args = parse()
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)   # fd 1 -> stderr for the rest of the run (native libraries print banners with printf)
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -353,7 +371,7 @@ def main():
                 "data": "synthetic", "config": config,
                 "cpu_baseline": {"value": round(v, 2), "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
                 "e2e": {"value": round(v, 2), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-        print(json.dumps(line), flush=True)
+        emit(line)
         return 0
 
     import torch.distributed as dist
@@ -361,8 +379,6 @@ def main():
     torch.cuda.set_device(local_rank)
     dp = None
     if dist_on:
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-            os.environ["NCCL_DEBUG"] = "WARN"   # keep stdout to the one JSON line (NCCL prints its version banner there)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
         from blt_vqg_b200.parallel import GradReducer
         dp = GradReducer()
@@ -383,7 +399,7 @@ def main():
             dist.barrier()
             dist.destroy_process_group()
         return 0
-    print(json.dumps(line), flush=True)
+    emit(line)
     if detail:
         sys.stderr.write("GEMM breakdown (top shapes by time, 2 instrumented steps):\n")
         for d in detail:
