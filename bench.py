@@ -229,7 +229,7 @@ def gemm_roofline(ts, model, args, dev_batches, peaks):
     peak = peaks.get("bf16_tflops_sustained") or 1400.0
     traffic, traffic_src = None, None
     try:  # dram bytes per launch of the same kernel from the committed ncu capture (one cfg3 step, all 353 GEMM launches)
-        tj = json.load(open(os.path.join(ROOT, "profiles", "r01d_gemm_traffic.json")))
+        tj = json.load(open(os.path.join(ROOT, "profiles", "r01i_gemm_traffic.json")))
         if args.workload == "transformer":
             traffic, traffic_src = round(tj["dram_bytes_per_launch"]), tj["source"]
     except Exception:

@@ -25,6 +25,9 @@ from . import transformer as tf
 from .params import Arena, TRANSFORMER_ALIASES, export_state_dict, import_state_dict, transformer_iq_specs
 
 PAD = 0
+# run the 5-token context encoder on a side stream next to the 21-token response encoder (forward and backward): its GEMMs
+# have 2560 rows = 20-40 tiles for 148 SMs, so on its own it leaves three quarters of the GPU idle
+CONCURRENT_ENCODERS = os.environ.get("B200IQ_CONCURRENT", "1") == "1"
 CE_CHUNK_MB = int(os.environ.get("B200IQ_CE_CHUNK_MB", "80"))  # size of one logits chunk of the fused vocabulary projection + CE
 TERMS = ("rec", "img", "kld", "aux", "count", "gnorm_sq", "unused0", "unused1")
 
@@ -164,6 +167,19 @@ class IQ(nn.Module):
             f = self.trunk(images.to(self.flat.device)).flatten(1).float().contiguous()
         return f if ops.exact_mode() else ops.round_tf32(f, f)
 
+    def _fork(self, enable):
+        """side stream that starts where the current stream is now (None when disabled)"""
+        if not enable:
+            return None
+        if getattr(self, "_side", None) is None:
+            self._side = torch.cuda.Stream(device=self.flat.device)
+        self._side.wait_stream(torch.cuda.current_stream())
+        return self._side
+
+    def _join(self, side):
+        if side is not None:
+            torch.cuda.current_stream().wait_stream(side)
+
     def _make_ctx(self, B, S, R, T, training):
         _lib.require_device()
         key = (B, S, R, T, bool(self.latent_transformer), bool(training))
@@ -192,14 +208,24 @@ class IQ(nn.Module):
         ops.bn_fwd(img_pre, P["encoder_cnn.bn.weight"], P["encoder_cnn.bn.bias"], img, ws.buf("bn.mean", H),
                    ws.buf("bn.rstd", H), self.bn_running_mean, self.bn_running_var, c.training)
         # context encoder (encoder_transformer.py:27-32)
-        x = tf.embed_fwd(c, "enc.emb", cids, B, S, self.timing_enc)
-        enc_out = tf.encoder_fwd(c, "enc", "answer_encoder.encoder.", x, cids, B, S, self.NL)
-        ops.add_timing(enc_out, None, img, None, B, S, H)  # enc_out[:,0] += image_features
+        def context_encoder():
+            x = tf.embed_fwd(c, "enc.emb", cids, B, S, self.timing_enc)
+            eo = tf.encoder_fwd(c, "enc", "answer_encoder.encoder.", x, cids, B, S, self.NL)
+            ops.add_timing(eo, None, img, None, B, S, H)  # enc_out[:,0] += image_features
+            return eo
         z = None
+        # (the two stacks share per-row-count scratch buffers in the backward, so they must differ in length)
+        side = self._fork(latent and CONCURRENT_ENCODERS and rids.shape[1] != S)
+        if side is None:
+            enc_out = context_encoder()
+        else:
+            with torch.cuda.stream(side), _lib.pinned_stream():
+                enc_out = context_encoder()
         if latent:
             R = rids.shape[1]
             xr = tf.embed_fwd(c, "renc.emb", rids, B, R, self.timing_enc)
             r_out = tf.encoder_fwd(c, "renc", "answer_encoder.r_encoder.", xr, rids, B, R, self.NL)
+            self._join(side)
             cat = ws.buf("lat.cat", B, 2 * H)  # cat(x_p, x), transformer_layers.py:52
             ops.tok0_gather(r_out, cat[:, :H], B, R, H)
             ops.tok0_gather(enc_out, cat[:, H:], B, S, H)
@@ -273,14 +299,30 @@ class IQ(nn.Module):
             tf.linear_bwd(c, None, pp + "0", d_p1, cat[:, H:], dx=d_cat[:, H:], accumulate_dx=True)
             ops.tok0_scatter_add(d_cat[:, H:], d_enc_out, B, S, H)
             c.ready("latent_layer.mean_logvar_prior.0.weight")
+
+        def context_encoder_bwd():
+            ops.tok0_gather(d_enc_out, d_img, B, S, H, accumulate=True)  # enc_out[:,0] = LN(..)[:,0] + image_features
+            de_in = tf.encoder_bwd(c, "enc", "answer_encoder.encoder.", d_enc_out, m["cids"], B, S, self.NL)
+            tf.embed_bwd(c, "enc.emb", m["cids"], de_in)
+        side = self._fork(latent and CONCURRENT_ENCODERS and m["rids"].shape[1] != S)
+        if side is not None:
+            # both encoder backward passes at once; gradient-bucket marks wait for the join (the two stacks finish in no fixed
+            # order, and a mark promises that everything above an arena offset is final)
+            saved, c.on_ready = c.on_ready, None
+            with torch.cuda.stream(side), _lib.pinned_stream():
+                context_encoder_bwd()
+        if latent:
             d_r_out = ws.buf("d_r_out", B * R, H)
             d_r_out.zero_()
             ops.tok0_scatter_add(d_cat[:, :H], d_r_out, B, R, H)
             dr_in = tf.encoder_bwd(c, "renc", "answer_encoder.r_encoder.", d_r_out, m["rids"], B, R, self.NL)
             tf.embed_bwd(c, "renc.emb", m["rids"], dr_in)
-        ops.tok0_gather(d_enc_out, d_img, B, S, H, accumulate=True)  # enc_out[:,0] = LN(..)[:,0] + image_features
-        de_in = tf.encoder_bwd(c, "enc", "answer_encoder.encoder.", d_enc_out, m["cids"], B, S, self.NL)
-        tf.embed_bwd(c, "enc.emb", m["cids"], de_in)
+        if side is not None:
+            self._join(side)
+            c.on_ready = saved
+            c.ready("answer_encoder.encoder.enc.0.layer_norm_mha.weight")
+        else:
+            context_encoder_bwd()
         d_img_pre = ws.buf("d_img_pre", B, H)
         ops.bn_bwd(d_img, m["img_pre"], P["encoder_cnn.bn.weight"], ws["bn.mean"], ws["bn.rstd"], d_img_pre,
                    G["encoder_cnn.bn.weight"], G["encoder_cnn.bn.bias"])

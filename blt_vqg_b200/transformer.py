@@ -310,5 +310,6 @@ def linear_bwd(c, tag, pfx, dy, x, relu_mask=None, need_dx=True, dx=None, accumu
     if dx is None:
         dx = c.ws.buf(tag, dy.shape[0], c.W[pfx + ".weight"].shape[1])
     assert not (accumulate_dx and relu_mask is not None)
-    ops.gemm(dy, c.W[pfx + ".weight"], dx, b_t=True, relu_mask=relu_mask, residual=dx if accumulate_dx else None)
+    ops.gemm(dy, c.W[pfx + ".weight"], dx, b_t=True, relu_mask=relu_mask, residual=dx if accumulate_dx else None,
+             auto_split=True)   # e.g. z_classifier: 512 x 512 output over K = 15000 -> 4 tiles without split-K
     return dx
