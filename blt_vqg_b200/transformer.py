@@ -9,11 +9,13 @@ import os
 
 import torch
 
-from . import ops
+from . import _lib, ops
 
 PAD = 0
 # forward FFN dropout inside the GEMM epilogue (1) or as the standalone HBM-bound kernel (0); same mask either way
 FUSE_DROPOUT = os.environ.get("B200IQ_FUSE_DROPOUT", "1") == "1"
+# small context-side GEMMs of the decoder (cross-attention K|V projections, their gradients) on a side stream
+CONCURRENT = os.environ.get("B200IQ_CONCURRENT", "1") == "1"
 
 
 class Workspace:
@@ -57,6 +59,13 @@ class Ctx:
         self.site = 0
         self.sm = 148
         self.on_ready = None  # callable(flat_offset): gradients at and after this arena offset are final (parallel.py)
+
+    def side_stream(self):
+        """one side stream per workspace for the small context-side GEMMs that are off the critical path"""
+        st = self.ws.meta.get("side_stream")
+        if st is None:
+            st = self.ws.meta["side_stream"] = torch.cuda.Stream(device=self.ws.device)
+        return st
 
     def ready(self, name):
         if self.on_ready is not None:
@@ -156,12 +165,19 @@ def self_attn_bwd(c, tag, pfx, dout, xn, ids, B, n, causal):
     return dxn
 
 
-def cross_attn_fwd(c, tag, pfx, xn, x_res, enc_out, enc_ids, B, nq, nk):
+def cross_kv_fwd(c, tag, pfx, enc_out):
+    """K | V of the context for one decoder layer: depends only on enc_out, so decoder_fwd computes all layers' up front"""
+    kv = c.ws.buf(tag + ".kv", enc_out.shape[0], 2 * c.H)
+    ops.gemm(enc_out, c.pspan(pfx + "key_linear.weight", pfx + "value_linear.weight", c.H), kv)
+    return kv
+
+
+def cross_attn_fwd(c, tag, pfx, xn, x_res, enc_out, enc_ids, B, nq, nk, kv=None):
     M, H = xn.shape
     q = c.ws.buf(tag + ".q", M, H)
     ops.gemm(xn, c.W[pfx + "query_linear.weight"], q)
-    kv = c.ws.buf(tag + ".kv", enc_out.shape[0], 2 * H)
-    ops.gemm(enc_out, c.pspan(pfx + "key_linear.weight", pfx + "value_linear.weight", H), kv)
+    if kv is None:
+        kv = cross_kv_fwd(c, tag, pfx, enc_out)
     ctx = c.ws.buf(tag + ".ctx", M, H)
     seed, off = c.key(tag + ".adrop")
     ops.attention_fwd(q, kv[:, :H], kv[:, H:], ctx, enc_ids, PAD, False, B, c.nh, nq, nk, c.d, c.attn_drop, seed, off)
@@ -170,7 +186,7 @@ def cross_attn_fwd(c, tag, pfx, xn, x_res, enc_out, enc_ids, B, nq, nk):
     return out
 
 
-def cross_attn_bwd(c, tag, pfx, dout, xn, enc_out, d_enc_out, first, enc_ids, B, nq, nk):
+def cross_attn_bwd(c, tag, pfx, dout, xn, enc_out, d_enc_out, first, enc_ids, B, nq, nk, side=None):
     M, H = xn.shape
     Me = enc_out.shape[0]
     q, kv, ctx = c.ws[tag + ".q"], c.ws[tag + ".kv"], c.ws[tag + ".ctx"]
@@ -178,14 +194,23 @@ def cross_attn_bwd(c, tag, pfx, dout, xn, enc_out, d_enc_out, first, enc_ids, B,
     dctx = c.ws.buf("tmp.dctx.%d" % M, M, H)
     ops.gemm(dout, c.W[pfx + "output_linear.weight"], dctx, b_t=True)
     dq = c.ws.buf("tmp.dq.%d" % M, M, H)
-    dkv = c.ws.buf("tmp.dkv.%d" % Me, Me, 2 * H)
+    # with a side stream the context-side GEMMs below read dkv while the main stream moves on: one buffer per layer
+    dkv = c.ws.buf((tag + ".dkv") if side is not None else ("tmp.dkv.%d" % Me), Me, 2 * H)
     seed, off = c.key(tag + ".adrop")
     ops.attention_bwd(q, kv[:, :H], kv[:, H:], dctx, dq, dkv[:, :H], dkv[:, H:], enc_ids, PAD, False, B, c.nh, nq, nk,
                       c.d, c.attn_drop, seed, off)
+    def context_side():
+        # 2560-row GEMMs (20-40 tiles): off the decoder's critical path, so they go to the side stream when there is one
+        grad_w(c, dkv, enc_out, c.gspan(pfx + "key_linear.weight", pfx + "value_linear.weight", H))
+        wkv = c.pspan(pfx + "key_linear.weight", pfx + "value_linear.weight", H)
+        ops.gemm(dkv, wkv, d_enc_out, b_t=True, residual=None if first else d_enc_out)
+    if side is not None:
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side), _lib.pinned_stream():
+            context_side()
+    else:
+        context_side()
     grad_w(c, dq, xn, c.G[pfx + "query_linear.weight"])
-    grad_w(c, dkv, enc_out, c.gspan(pfx + "key_linear.weight", pfx + "value_linear.weight", H))
-    wkv = c.pspan(pfx + "key_linear.weight", pfx + "value_linear.weight", H)
-    ops.gemm(dkv, wkv, d_enc_out, b_t=True, residual=None if first else d_enc_out)
     dxn = c.ws.buf("tmp.dxn.%d" % M, M, H)
     ops.gemm(dq, c.W[pfx + "query_linear.weight"], dxn, b_t=True)
     return dxn
@@ -263,12 +288,23 @@ def encoder_bwd(c, tag, pfx, dy, ids, B, n, NL):
 def decoder_fwd(c, tag, pfx, x, ids, enc_out, enc_ids, B, T, S, NL):
     """models/transformer_layers.py:205-221; causal|pad mask of :207 is built inside the attention kernel."""
     c.ws.meta[tag + ".in"] = x
+    # every layer's cross-attention K | V depends only on enc_out: six 2560-row GEMMs on the side stream, under layer 0's
+    # self-attention block
+    kvs = [None] * NL
+    side = c.side_stream() if CONCURRENT else None
+    if side is not None:
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side), _lib.pinned_stream():
+            for i in range(NL):
+                kvs[i] = cross_kv_fwd(c, "%s.%d.ca" % (tag, i), "%sdec.%d.multi_head_attention_enc_dec." % (pfx, i), enc_out)
     for i in range(NL):
         lt, lp = "%s.%d" % (tag, i), "%sdec.%d." % (pfx, i)
         xn = ln_fwd(c, lt + ".ln1", lp + "layer_norm_mha_dec", x)
         a = self_attn_fwd(c, lt + ".sa", lp + "multi_head_attention_dec.", xn, x, ids, B, T, True)
         xn = ln_fwd(c, lt + ".ln2", lp + "layer_norm_mha_enc", a)
-        b = cross_attn_fwd(c, lt + ".ca", lp + "multi_head_attention_enc_dec.", xn, a, enc_out, enc_ids, B, T, S)
+        if side is not None and i == 0:
+            torch.cuda.current_stream().wait_stream(side)
+        b = cross_attn_fwd(c, lt + ".ca", lp + "multi_head_attention_enc_dec.", xn, a, enc_out, enc_ids, B, T, S, kv=kvs[i])
         xn = ln_fwd(c, lt + ".ln3", lp + "layer_norm_ffn", b)
         x = ffn_fwd(c, lt + ".ff", lp + "positionwise_feed_forward.", xn, b)
     c.ws.meta[tag + ".last"] = x
@@ -280,6 +316,7 @@ def decoder_bwd(c, tag, pfx, dy, ids, enc_out, d_enc_out, enc_ids, B, T, S, NL):
     M, H = dy.shape
     dx = c.ws.buf(tag + ".dx", M, H)
     ln_bwd(c, tag + ".lnf", pfx + "layer_norm", dy, c.ws.meta[tag + ".last"], dx, False)
+    side = c.side_stream() if CONCURRENT else None
     for i in reversed(range(NL)):
         lt, lp = "%s.%d" % (tag, i), "%sdec.%d." % (pfx, i)
         x_in = c.ws.meta[tag + ".in"] if i == 0 else c.ws["%s.%d.ff.out" % (tag, i - 1)]
@@ -287,10 +324,12 @@ def decoder_bwd(c, tag, pfx, dy, ids, enc_out, d_enc_out, enc_ids, B, T, S, NL):
         dxn = ffn_bwd(c, lt + ".ff", lp + "positionwise_feed_forward.", dx, c.ws[lt + ".ln3.y"])
         ln_bwd(c, lt + ".ln3", lp + "layer_norm_ffn", dxn, b, dx, True)
         dxn = cross_attn_bwd(c, lt + ".ca", lp + "multi_head_attention_enc_dec.", dx, c.ws[lt + ".ln2.y"], enc_out,
-                             d_enc_out, i == NL - 1, enc_ids, B, T, S)
+                             d_enc_out, i == NL - 1, enc_ids, B, T, S, side=side)
         ln_bwd(c, lt + ".ln2", lp + "layer_norm_mha_enc", dxn, a, dx, True)
         dxn = self_attn_bwd(c, lt + ".sa", lp + "multi_head_attention_dec.", dx, c.ws[lt + ".ln1.y"], ids, B, T, True)
         ln_bwd(c, lt + ".ln1", lp + "layer_norm_mha_dec", dxn, x_in, dx, True)
+        if side is not None:
+            torch.cuda.current_stream().wait_stream(side)   # this layer's K|V weight gradients are final before the mark
         c.ready(lp + "layer_norm_mha_dec.weight")
     return dx
 
