@@ -433,7 +433,7 @@ class IQ(nn.Module):
         B, T = m["tids"].shape
         g = torch.zeros_like(self.flat.data)
         c.gflat = g
-        c.G = {n: self.arena.view_of(g, n) for n in self.arena.names()}
+        c.G = self.arena.views_over(g, cache=False)
         d_dec = ws.buf("d_dec_out", B * T, H)
         if d_output is not None:
             dout = d_output.reshape(B * T, self.V).contiguous()

@@ -102,6 +102,26 @@ class Arena:
                 return other_flat[o:o + n].view(shape)
         raise KeyError(name)
 
+    def views_over(self, other_flat, cache=True):
+        """all named slices of another flat buffer laid out like the arena (TF32 operand copy, gradients), built once
+        per buffer: a training step asks for them every step"""
+        store = self.__dict__.setdefault("_views_over", {})
+        key = (other_flat.data_ptr(), other_flat.numel(), other_flat.dtype, str(other_flat.device))
+        v = store.get(key) if cache else None
+        if v is None:
+            v = {}
+            for nm, shape, _ in self.specs:
+                n = 1
+                for s in shape:
+                    n *= s
+                o = self.offsets[nm]
+                v[nm.replace("#pack", "")] = other_flat[o:o + n].view(shape)
+            if cache:   # only long-lived buffers (the cached views keep the storage alive)
+                if len(store) > 8:
+                    store.clear()
+                store[key] = v
+        return v
+
     def span(self, first, last):
         """flat range covering consecutive packed tensors first..last as one [rows, cols] matrix"""
         o0 = self.offsets.get(first + "#pack", self.offsets.get(first))

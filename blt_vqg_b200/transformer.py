@@ -48,9 +48,9 @@ class Ctx:
         self.P = arena.views      # fp32 masters: biases, LayerNorm / BatchNorm affine, embedding table
         # GEMM weight operands: the TF32-rounded copy of the arena (the masters themselves in exact mode)
         self.wflat = wflat if wflat is not None else arena.flat.detach()
-        self.W = {n: arena.view_of(self.wflat, n) for n in arena.names()} if wflat is not None else arena.views
+        self.W = arena.views_over(wflat) if wflat is not None else arena.views
         self.gflat = gflat
-        self.G = {n: arena.view_of(gflat, n) for n in arena.names()} if gflat is not None else None
+        self.G = arena.views_over(gflat) if gflat is not None else None
         self.H, self.nh, self.F, self.E, self.d = H, nh, F, E, H // nh
         self.attn_drop = attn_drop if training else 0.0
         self.relu_drop = relu_drop if training else 0.0
