@@ -6,10 +6,13 @@ Replaces what Lightning does around `TrainIQ.training_step` (train_iq.py:105-132
 The loss terms stay on the device (one 8-float vector); nothing synchronises with the host inside a step.
 """
 import math
+import os
 
 import torch
 
 from . import _lib, ops
+
+HIGH_PRIORITY_STEP = os.environ.get("B200IQ_HP_STREAM", "1") == "1"
 
 
 def noam_lr(step, hidden_dim, warmup=4000):
@@ -28,6 +31,7 @@ class TrainStep:
         self.exp_avg_sq = torch.zeros_like(flat)
         self.hyper = torch.zeros(4, device=flat.device)
         self.normsq = torch.zeros(1, device=flat.device)
+        self._hp = None
         self.iter = 0      # TrainIQ.iter (train_iq.py:43)
         self.kliter = 0    # TrainIQ.kliter (:44), counts steps since the latent switch
         self.t = 0         # Adam step count (never reset: train_iq.py:111 is a no-op)
@@ -42,8 +46,20 @@ class TrainStep:
 
     def step(self, images, answers, response, target, eps=None):
         """returns the device tensor of loss terms (rec, img, kld, aux, count, gnorm_sq, ...) of this step"""
-        with _lib.pinned_stream():
-            return self._step(images, answers, response, target, eps)
+        if not HIGH_PRIORITY_STEP:
+            with _lib.pinned_stream():
+                return self._step(images, answers, response, target, eps)
+        # the step's critical path runs on a high-priority stream, so that when one of its GEMMs and an off-path kernel on a
+        # (default-priority) side stream are both pending, the block scheduler hands the SMs to the critical path first
+        # and the side kernel fills the last wave.  Ordered against the caller's stream on both sides.
+        cur = torch.cuda.current_stream()
+        if self._hp is None:
+            self._hp = torch.cuda.Stream(priority=-1)
+        self._hp.wait_stream(cur)
+        with torch.cuda.stream(self._hp), _lib.pinned_stream():
+            terms = self._step(images, answers, response, target, eps)
+        cur.wait_stream(self._hp)
+        return terms
 
     def _step(self, images, answers, response, target, eps):
         m = self.model

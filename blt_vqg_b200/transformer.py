@@ -16,6 +16,9 @@ PAD = 0
 FUSE_DROPOUT = os.environ.get("B200IQ_FUSE_DROPOUT", "1") == "1"
 # small context-side GEMMs of the decoder (cross-attention K|V projections, their gradients) on a side stream
 CONCURRENT = os.environ.get("B200IQ_CONCURRENT", "1") == "1"
+# weight-gradient GEMMs of a block on the side stream, under the block's dX chain: the persistent GEMM grids leave SMs idle in
+# their last wave (80 pair tiles on 74 SM pairs for every M=10240, N=512 product) and the side kernels' CTAs fill them
+CONCURRENT_DW = CONCURRENT and os.environ.get("B200IQ_CONCURRENT_DW", "1") == "1"
 
 
 class Workspace:
@@ -61,11 +64,59 @@ class Ctx:
         self.on_ready = None  # callable(flat_offset): gradients at and after this arena offset are final (parallel.py)
 
     def side_stream(self):
-        """one side stream per workspace for the small context-side GEMMs that are off the critical path"""
-        st = self.ws.meta.get("side_stream")
+        """the side stream paired with the CURRENT stream (the two encoders run on different streams, each gets its own)
+        for work that is off the critical path: weight-gradient GEMMs, the decoder's context-side projections"""
+        key = ("side_stream", torch.cuda.current_stream().cuda_stream)
+        st = self.ws.meta.get(key)
         if st is None:
-            st = self.ws.meta["side_stream"] = torch.cuda.Stream(device=self.ws.device)
+            st = self.ws.meta[key] = torch.cuda.Stream(device=self.ws.device)
         return st
+
+    def mark(self):
+        """an event at this point of the current stream: `on_side(fn, after=mark)` lets the caller issue its own
+        critical-path kernel BEFORE the side work, so that kernel gets the SMs first and the side kernel fills its tail"""
+        if not CONCURRENT_DW:
+            return None
+        key = ("side_event", torch.cuda.current_stream().cuda_stream)
+        ev = self.ws.meta.get(key)
+        if ev is None:
+            ev = self.ws.meta[key] = torch.cuda.Event()
+        ev.record()
+        return ev
+
+    def on_side(self, fn, after=None):
+        """issue fn's launches on the side stream, ordered after `after` (a mark()) or after everything issued so far on
+        the current stream.  The caller must join_side() before it overwrites anything fn reads and before it marks
+        fn's gradients ready."""
+        if not CONCURRENT_DW:
+            return fn()
+        side = self.side_stream()
+        if after is not None:
+            side.wait_event(after)
+        else:
+            side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side), _lib.pinned_stream():
+            fn()
+
+    def join_side(self):
+        if CONCURRENT_DW:
+            torch.cuda.current_stream().wait_stream(self.side_stream())
+
+    def side_mark(self):
+        """an event after the side work issued so far: the current stream waits on it (wait_side_mark) before it overwrites
+        what that work reads, without waiting for side work issued later"""
+        if not CONCURRENT_DW:
+            return None
+        key = ("side_done_event", torch.cuda.current_stream().cuda_stream)
+        ev = self.ws.meta.get(key)
+        if ev is None:
+            ev = self.ws.meta[key] = torch.cuda.Event()
+        ev.record(self.side_stream())
+        return ev
+
+    def wait_side_mark(self, ev):
+        if ev is not None:
+            torch.cuda.current_stream().wait_event(ev)
 
     def ready(self, name):
         if self.on_ready is not None:
@@ -128,10 +179,12 @@ def embed_fwd(c, tag, ids, B, n, timing, add0=None, add1=None):
 
 def embed_bwd(c, tag, ids, dx):
     e = c.ws[tag + ".e"]
-    grad_w(c, dx, e, c.G["embedding.1.weight"], c.G["embedding.1.bias"])
+    ev = c.mark()
     de = c.ws.buf("tmp.de.%d" % dx.shape[0], dx.shape[0], c.E)
     ops.gemm(dx, c.W["embedding.1.weight"], de, b_t=True)
+    c.on_side(lambda: grad_w(c, dx, e, c.G["embedding.1.weight"], c.G["embedding.1.bias"]), ev)
     ops.embed_scatter_add(ids, de, c.G["embedding.0.weight"], PAD)
+    c.join_side()
 
 
 # ------------------------------------------------------------------ attention blocks
@@ -152,17 +205,21 @@ def self_attn_fwd(c, tag, pfx, xn, x_res, ids, B, n, causal):
 def self_attn_bwd(c, tag, pfx, dout, xn, ids, B, n, causal):
     M, H = xn.shape
     qkv, ctx = c.ws[tag + ".qkv"], c.ws[tag + ".ctx"]
-    grad_w(c, dout, ctx, c.G[pfx + "output_linear.weight"])
+    ev = c.mark()
     dctx = c.ws.buf("tmp.dctx.%d" % M, M, H)
     ops.gemm(dout, c.W[pfx + "output_linear.weight"], dctx, b_t=True)
+    c.on_side(lambda: grad_w(c, dout, ctx, c.G[pfx + "output_linear.weight"]), ev)
+    dout_read = c.side_mark()
     dqkv = c.ws.buf("tmp.dqkv.%d" % M, M, 3 * H)
     seed, off = c.key(tag + ".adrop")
     ops.attention_bwd(qkv[:, :H], qkv[:, H:2 * H], qkv[:, 2 * H:], dctx, dqkv[:, :H], dqkv[:, H:2 * H], dqkv[:, 2 * H:],
                       ids, PAD, causal, B, c.nh, n, n, c.d, c.attn_drop, seed, off)
-    grad_w(c, dqkv, xn, c.gspan(pfx + "query_linear.weight", pfx + "value_linear.weight", H))
+    ev = c.mark()
     dxn = c.ws.buf("tmp.dxn.%d" % M, M, H)
     ops.gemm(dqkv, c.pspan(pfx + "query_linear.weight", pfx + "value_linear.weight", H), dxn, b_t=True)
-    return dxn
+    c.on_side(lambda: grad_w(c, dqkv, xn, c.gspan(pfx + "query_linear.weight", pfx + "value_linear.weight", H)), ev)
+    c.wait_side_mark(dout_read)   # the caller's LayerNorm backward accumulates into dout's buffer next; the stack joins
+    return dxn                    # the rest of the side work at the end of the layer
 
 
 def cross_kv_fwd(c, tag, pfx, enc_out):
@@ -186,33 +243,31 @@ def cross_attn_fwd(c, tag, pfx, xn, x_res, enc_out, enc_ids, B, nq, nk, kv=None)
     return out
 
 
-def cross_attn_bwd(c, tag, pfx, dout, xn, enc_out, d_enc_out, first, enc_ids, B, nq, nk, side=None):
+def cross_attn_bwd(c, tag, pfx, dout, xn, enc_out, d_enc_out, first, enc_ids, B, nq, nk):
     M, H = xn.shape
     Me = enc_out.shape[0]
     q, kv, ctx = c.ws[tag + ".q"], c.ws[tag + ".kv"], c.ws[tag + ".ctx"]
-    grad_w(c, dout, ctx, c.G[pfx + "output_linear.weight"])
+    ev = c.mark()
     dctx = c.ws.buf("tmp.dctx.%d" % M, M, H)
     ops.gemm(dout, c.W[pfx + "output_linear.weight"], dctx, b_t=True)
+    c.on_side(lambda: grad_w(c, dout, ctx, c.G[pfx + "output_linear.weight"]), ev)
+    dout_read = c.side_mark()
     dq = c.ws.buf("tmp.dq.%d" % M, M, H)
-    # with a side stream the context-side GEMMs below read dkv while the main stream moves on: one buffer per layer
-    dkv = c.ws.buf((tag + ".dkv") if side is not None else ("tmp.dkv.%d" % Me), Me, 2 * H)
+    dkv = c.ws.buf("tmp.dkv.%d" % Me, Me, 2 * H)
     seed, off = c.key(tag + ".adrop")
     ops.attention_bwd(q, kv[:, :H], kv[:, H:], dctx, dq, dkv[:, :H], dkv[:, H:], enc_ids, PAD, False, B, c.nh, nq, nk,
                       c.d, c.attn_drop, seed, off)
-    def context_side():
-        # 2560-row GEMMs (20-40 tiles): off the decoder's critical path, so they go to the side stream when there is one
+    def off_path():
+        # the context-side 2560-row GEMMs (20-40 tiles) and the query weight gradient: none feeds the decoder's dX chain
         grad_w(c, dkv, enc_out, c.gspan(pfx + "key_linear.weight", pfx + "value_linear.weight", H))
         wkv = c.pspan(pfx + "key_linear.weight", pfx + "value_linear.weight", H)
         ops.gemm(dkv, wkv, d_enc_out, b_t=True, residual=None if first else d_enc_out)
-    if side is not None:
-        side.wait_stream(torch.cuda.current_stream())
-        with torch.cuda.stream(side), _lib.pinned_stream():
-            context_side()
-    else:
-        context_side()
-    grad_w(c, dq, xn, c.G[pfx + "query_linear.weight"])
+        grad_w(c, dq, xn, c.G[pfx + "query_linear.weight"])
+    ev = c.mark()
     dxn = c.ws.buf("tmp.dxn.%d" % M, M, H)
     ops.gemm(dq, c.W[pfx + "query_linear.weight"], dxn, b_t=True)
+    c.on_side(off_path, ev)
+    c.wait_side_mark(dout_read)
     return dxn
 
 
@@ -245,13 +300,15 @@ def ffn_bwd(c, tag, pfx, dout, xn):
     inv_keep = 1.0 / (1.0 - c.relu_drop)
     dpre2 = c.ws.buf("tmp.dpre2.%d" % M, M, H)
     ops.relu_bwd_colsum(dout, f2, dpre2, c.G[pfx + "layers.1.bias"], scale=inv_keep)
-    grad_w(c, dpre2, h, c.G[pfx + "layers.1.weight"])
+    ev = c.mark()
     dh = c.ws.buf("tmp.dh.%d" % M, M, c.F)
     ops.gemm(dpre2, c.W[pfx + "layers.1.weight"], dh, b_t=True, relu_mask=h, alpha=inv_keep)
-    grad_w(c, dh, xn, c.G[pfx + "layers.0.weight"], c.G[pfx + "layers.0.bias"])
+    c.on_side(lambda: grad_w(c, dpre2, h, c.G[pfx + "layers.1.weight"]), ev)
+    ev = c.mark()
     dxn = c.ws.buf("tmp.dxn.%d" % M, M, H)
     ops.gemm(dh, c.W[pfx + "layers.0.weight"], dxn, b_t=True)
-    return dxn
+    c.on_side(lambda: grad_w(c, dh, xn, c.G[pfx + "layers.0.weight"], c.G[pfx + "layers.0.bias"]), ev)
+    return dxn   # side work reads dpre2 / dh / saved activations only: joined by the stack at the end of the layer
 
 
 # ------------------------------------------------------------------ stacks
@@ -281,6 +338,7 @@ def encoder_bwd(c, tag, pfx, dy, ids, B, n, NL):
         ln_bwd(c, lt + ".ln2", lp + "layer_norm_ffn", dxn2, a, dx, True)
         dxn = self_attn_bwd(c, lt + ".sa", lp + "multi_head_attention.", dx, c.ws[lt + ".ln1.y"], ids, B, n, False)
         ln_bwd(c, lt + ".ln1", lp + "layer_norm_mha", dxn, x_in, dx, True)
+        c.join_side()   # the layer's weight gradients are final, and the tmp.* buffers the side work read are free again
         c.ready(lp + "layer_norm_mha.weight")
     return dx
 
@@ -316,7 +374,6 @@ def decoder_bwd(c, tag, pfx, dy, ids, enc_out, d_enc_out, enc_ids, B, T, S, NL):
     M, H = dy.shape
     dx = c.ws.buf(tag + ".dx", M, H)
     ln_bwd(c, tag + ".lnf", pfx + "layer_norm", dy, c.ws.meta[tag + ".last"], dx, False)
-    side = c.side_stream() if CONCURRENT else None
     for i in reversed(range(NL)):
         lt, lp = "%s.%d" % (tag, i), "%sdec.%d." % (pfx, i)
         x_in = c.ws.meta[tag + ".in"] if i == 0 else c.ws["%s.%d.ff.out" % (tag, i - 1)]
@@ -324,12 +381,11 @@ def decoder_bwd(c, tag, pfx, dy, ids, enc_out, d_enc_out, enc_ids, B, T, S, NL):
         dxn = ffn_bwd(c, lt + ".ff", lp + "positionwise_feed_forward.", dx, c.ws[lt + ".ln3.y"])
         ln_bwd(c, lt + ".ln3", lp + "layer_norm_ffn", dxn, b, dx, True)
         dxn = cross_attn_bwd(c, lt + ".ca", lp + "multi_head_attention_enc_dec.", dx, c.ws[lt + ".ln2.y"], enc_out,
-                             d_enc_out, i == NL - 1, enc_ids, B, T, S, side=side)
+                             d_enc_out, i == NL - 1, enc_ids, B, T, S)
         ln_bwd(c, lt + ".ln2", lp + "layer_norm_mha_enc", dxn, a, dx, True)
         dxn = self_attn_bwd(c, lt + ".sa", lp + "multi_head_attention_dec.", dx, c.ws[lt + ".ln1.y"], ids, B, T, True)
         ln_bwd(c, lt + ".ln1", lp + "layer_norm_mha_dec", dxn, x_in, dx, True)
-        if side is not None:
-            torch.cuda.current_stream().wait_stream(side)   # this layer's K|V weight gradients are final before the mark
+        c.join_side()
         c.ready(lp + "layer_norm_mha_dec.weight")
     return dx
 

@@ -20,6 +20,11 @@ t0 = time.perf_counter()
 for _ in range(N): ts.step(*args)
 t1 = time.perf_counter(); torch.cuda.synchronize(); t2 = time.perf_counter()
 print("%s step: host issue %.3f ms, with final sync %.3f ms" % (name, 1e3 * (t1 - t0) / N, 1e3 * (t2 - t0) / N))
+iso = []
+for _ in range(10):   # one step issued into an idle queue: never blocks on queue depth, so this is the true host cost
+    torch.cuda.synchronize(); t0 = time.perf_counter(); ts.step(*args); iso.append(time.perf_counter() - t0)
+torch.cuda.synchronize()
+print("isolated host issue per step: min %.3f ms, median %.3f ms" % (1e3 * min(iso), 1e3 * sorted(iso)[5]))
 if len(sys.argv) > 2:
     pr = cProfile.Profile(); pr.enable()
     for _ in range(10): ts.step(*args)
