@@ -304,6 +304,8 @@ static constexpr int ATT_TC_WARPS = 4;
 template <int MT, int NT>
 __global__ void __launch_bounds__(ATT_TC_WARPS * 32)
 attention_fwd_tc_kernel(AttnArgs a, float* __restrict__ out, int ldo) {
+  pdl_trigger();
+  pdl_wait();
   const int bh = blockIdx.x * ATT_TC_WARPS + (threadIdx.x >> 5);
   if (bh >= a.B * a.nh) return;
   const int b = bh / a.nh, h = bh - b * a.nh, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
@@ -383,6 +385,8 @@ __global__ void __launch_bounds__(ATT_TC_WARPS * 32)
 attention_bwd_tc_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, float* __restrict__ dq, float* __restrict__ dk,
                         float* __restrict__ dv, int lddq, int lddk, int lddv) {
   __shared__ float tsm[ATT_TC_WARPS][2][32 * 33];
+  pdl_trigger();
+  pdl_wait();
   const int wid = threadIdx.x >> 5;
   const int bh = blockIdx.x * ATT_TC_WARPS + wid;
   if (bh >= a.B * a.nh) return;
@@ -485,7 +489,7 @@ extern "C" int b200iq_attention_fwd(const B200iqAttention* p, void* stream) {
     const int lds[] = {p->ldq, p->ldk, p->ldv, p->ldo};
     if (tc_ok(p, ptrs, 4, lds, 4)) {
       const int mt = a.nq > 16 ? 2 : 1, nt = (a.nk + 7) / 8, grid = (a.B * a.nh + ATT_TC_WARPS - 1) / ATT_TC_WARPS;
-#define CALL(M_, N_) attention_fwd_tc_kernel<M_, N_><<<grid, ATT_TC_WARPS * 32, 0, (cudaStream_t)stream>>>(a, p->out, p->ldo)
+#define CALL(M_, N_) launch_dep(attention_fwd_tc_kernel<M_, N_>, dim3(grid), dim3(ATT_TC_WARPS * 32), 0, (cudaStream_t)stream, a, p->out, p->ldo)
       B200IQ_ATT_DISPATCH(mt, nt, CALL);
 #undef CALL
       return launch_status("attention_fwd_tc");
@@ -509,7 +513,7 @@ extern "C" int b200iq_attention_bwd(const B200iqAttention* p, const float* dout,
     const int lds[] = {p->ldq, p->ldk, p->ldv, p->ldo, lddq, lddk, lddv};
     if (tc_ok(p, ptrs, 7, lds, 7)) {
       const int mt = a.nq > 16 ? 2 : 1, nt = (a.nk + 7) / 8, grid = (a.B * a.nh + ATT_TC_WARPS - 1) / ATT_TC_WARPS;
-#define CALL(M_, N_) attention_bwd_tc_kernel<M_, N_><<<grid, ATT_TC_WARPS * 32, 0, (cudaStream_t)stream>>>(a, dout, p->ldo, dq, dk, dv, lddq, lddk, lddv)
+#define CALL(M_, N_) launch_dep(attention_bwd_tc_kernel<M_, N_>, dim3(grid), dim3(ATT_TC_WARPS * 32), 0, (cudaStream_t)stream, a, dout, p->ldo, dq, dk, dv, lddq, lddk, lddv)
       B200IQ_ATT_DISPATCH(mt, nt, CALL);
 #undef CALL
       return launch_status("attention_bwd_tc");

@@ -35,6 +35,24 @@ int sm_count();
 // 1: every activation / gradient tensor a kernel writes is rounded to the nearest TF32 value (b200iq_set_tf32_rounding)
 int round_mode();
 
+// Programmatic dependent launch (b200iq_set_pdl): a kernel launched through launch_dep() may become resident while the
+// previous kernel of its stream is still draining, runs its prologue, and blocks in pdl_wait() until that kernel has
+// completed and its writes are visible.  Every kernel launched this way calls pdl_wait() before its first global access
+// (reads AND writes) and pdl_trigger() at its top; both are no-ops for a plain launch.
+int pdl_mode();
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+template <class... KA, class... A>
+static inline cudaError_t launch_dep(void (*kernel)(KA...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, A... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = pdl_mode() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, KA(args)...);
+}
+
 // ---------------------------------------------------------------- device utils
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll

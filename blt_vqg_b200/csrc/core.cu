@@ -14,6 +14,8 @@ void set_error(const char* fmt, ...) {
 
 static int g_round = 1;
 int round_mode() { return g_round; }
+static int g_pdl = 0;
+int pdl_mode() { return g_pdl; }
 
 int sm_count() {
   static int n = 0;
@@ -32,6 +34,12 @@ extern "C" int b200iq_abi_version(void) { return B200IQ_ABI_VERSION; }
 extern "C" int b200iq_set_tf32_rounding(int on) {
   int prev = b200iq::g_round;
   b200iq::g_round = on ? 1 : 0;
+  return prev;
+}
+
+extern "C" int b200iq_set_pdl(int on) {
+  int prev = b200iq::g_pdl;
+  b200iq::g_pdl = on ? 1 : 0;
   return prev;
 }
 

@@ -215,6 +215,8 @@ __global__ void randn_kernel(float* __restrict__ out, size_t n, uint64_t seed, u
 
 // out = a*x + b*y  (out may alias x or y)
 __global__ void axpby_kernel(const float* x, const float* y, float* out, size_t n, float a, float b, int rn) {
+  pdl_trigger();
+  pdl_wait();
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
     out[i] = rnd(a * x[i] + (b == 0.f ? 0.f : b * y[i]), rn);
 }
@@ -281,10 +283,10 @@ extern "C" int b200iq_layernorm_fwd(const float* x, const float* gamma, const fl
   B200IQ_CHECK_ARG(x && gamma && beta && y && M > 0 && H > 0, "layernorm_fwd: bad args");
   if ((H == 128 || H == 256 || H == 512 || H == 1024) && (((uintptr_t)x | (uintptr_t)y | (uintptr_t)gamma | (uintptr_t)beta) & 15) == 0) {
     const int grid = min(ceil_div(M, 8), sm_count() * 8), rn = round_mode();
-    if (H == 128) ln_fwd_warp_kernel<1><<<grid, 256, 0, ST>>>(x, gamma, beta, y, mean, rstd, M, eps, rn);
-    else if (H == 256) ln_fwd_warp_kernel<2><<<grid, 256, 0, ST>>>(x, gamma, beta, y, mean, rstd, M, eps, rn);
-    else if (H == 512) ln_fwd_warp_kernel<4><<<grid, 256, 0, ST>>>(x, gamma, beta, y, mean, rstd, M, eps, rn);
-    else ln_fwd_warp_kernel<8><<<grid, 256, 0, ST>>>(x, gamma, beta, y, mean, rstd, M, eps, rn);
+    if (H == 128) launch_dep(ln_fwd_warp_kernel<1>, dim3(grid), dim3(256), 0, ST, x, gamma, beta, y, mean, rstd, M, eps, rn);
+    else if (H == 256) launch_dep(ln_fwd_warp_kernel<2>, dim3(grid), dim3(256), 0, ST, x, gamma, beta, y, mean, rstd, M, eps, rn);
+    else if (H == 512) launch_dep(ln_fwd_warp_kernel<4>, dim3(grid), dim3(256), 0, ST, x, gamma, beta, y, mean, rstd, M, eps, rn);
+    else launch_dep(ln_fwd_warp_kernel<8>, dim3(grid), dim3(256), 0, ST, x, gamma, beta, y, mean, rstd, M, eps, rn);
     return launch_status("layernorm_fwd");
   }
   layernorm_fwd_kernel<<<ceil_div(M, 8), 256, 0, ST>>>(x, gamma, beta, y, mean, rstd, M, H, eps, round_mode());
@@ -297,10 +299,10 @@ extern "C" int b200iq_layernorm_bwd(const float* dy, const float* x, const float
   B200IQ_CHECK_ARG(H <= 2048, "layernorm_bwd: H=%d > 2048 unsupported", H);
   if ((H == 128 || H == 256 || H == 512 || H == 1024) && (((uintptr_t)x | (uintptr_t)dy | (uintptr_t)dx | (uintptr_t)gamma) & 15) == 0) {
     const int grid = min(ceil_div(M, 8), sm_count() * 2), rn = round_mode();
-    if (H == 128) ln_bwd_warp_kernel<1><<<grid, 256, 0, ST>>>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, M, accumulate_dx, rn);
-    else if (H == 256) ln_bwd_warp_kernel<2><<<grid, 256, 0, ST>>>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, M, accumulate_dx, rn);
-    else if (H == 512) ln_bwd_warp_kernel<4><<<grid, 256, 0, ST>>>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, M, accumulate_dx, rn);
-    else ln_bwd_warp_kernel<8><<<grid, 256, 0, ST>>>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, M, accumulate_dx, rn);
+    if (H == 128) launch_dep(ln_bwd_warp_kernel<1>, dim3(grid), dim3(256), 0, ST, dy, x, gamma, mean, rstd, dx, dgamma, dbeta, M, accumulate_dx, rn);
+    else if (H == 256) launch_dep(ln_bwd_warp_kernel<2>, dim3(grid), dim3(256), 0, ST, dy, x, gamma, mean, rstd, dx, dgamma, dbeta, M, accumulate_dx, rn);
+    else if (H == 512) launch_dep(ln_bwd_warp_kernel<4>, dim3(grid), dim3(256), 0, ST, dy, x, gamma, mean, rstd, dx, dgamma, dbeta, M, accumulate_dx, rn);
+    else launch_dep(ln_bwd_warp_kernel<8>, dim3(grid), dim3(256), 0, ST, dy, x, gamma, mean, rstd, dx, dgamma, dbeta, M, accumulate_dx, rn);
     return launch_status("layernorm_bwd");
   }
   int ctas = min(M, sm_count() * 4);
@@ -317,7 +319,7 @@ extern "C" int b200iq_colsum_add(const float* x, float* out, int M, int N, int l
   B200IQ_CHECK_ARG(x && out && M > 0 && N > 0 && ld >= N, "colsum_add: bad args");
   if ((N & 3) == 0 && (ld & 3) == 0 && (((uintptr_t)x) & 15) == 0) {
     const int cx = ceil_div(N, 128), rpc = max(32, ceil_div(M, max(1, sm_count() * 4 / cx)));
-    colsum4_kernel<false><<<dim3(cx, ceil_div(M, rpc)), dim3(32, 8), 0, ST>>>(x, nullptr, nullptr, out, M, N, ld, rpc, 1.f, 0);
+    launch_dep(colsum4_kernel<false>, dim3(cx, ceil_div(M, rpc)), dim3(32, 8), 0, ST, x, nullptr, nullptr, out, M, N, ld, rpc, 1.f, 0);
     return launch_status("colsum_add");
   }
   int rows = max(8, ceil_div(M, max(1, sm_count() * 4 / ceil_div(N, 128))));
@@ -330,7 +332,7 @@ extern "C" int b200iq_relu_bwd_colsum(const float* dy, const float* y, float* dp
   B200IQ_CHECK_ARG(dy && y && dpre && M > 0 && N > 0, "relu_bwd_colsum: bad args");
   if ((N & 3) == 0 && (((uintptr_t)dy | (uintptr_t)y | (uintptr_t)dpre) & 15) == 0) {
     const int cx = ceil_div(N, 128), rpc = max(32, ceil_div(M, max(1, sm_count() * 4 / cx)));
-    colsum4_kernel<true><<<dim3(cx, ceil_div(M, rpc)), dim3(32, 8), 0, ST>>>(dy, y, dpre, dbias, M, N, N, rpc, scale, round_mode());
+    launch_dep(colsum4_kernel<true>, dim3(cx, ceil_div(M, rpc)), dim3(32, 8), 0, ST, dy, y, dpre, dbias, M, N, N, rpc, scale, round_mode());
     return launch_status("relu_bwd_colsum");
   }
   int rows = max(8, ceil_div(M, max(1, sm_count() * 4 / ceil_div(N, 128))));
@@ -354,7 +356,7 @@ extern "C" int b200iq_randn(float* out, size_t n, uint64_t seed, uint64_t offset
 
 extern "C" int b200iq_axpby(const float* x, const float* y, float* out, size_t n, float a, float b, void* stream) {
   B200IQ_CHECK_ARG(x && y && out && n > 0, "axpby: bad args");
-  axpby_kernel<<<grid_for(n, 256), 256, 0, ST>>>(x, y, out, n, a, b, round_mode());
+  launch_dep(axpby_kernel, dim3(grid_for(n, 256)), dim3(256), 0, ST, x, y, out, n, a, b, round_mode());
   return launch_status("axpby");
 }
 

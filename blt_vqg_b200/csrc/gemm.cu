@@ -158,6 +158,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   constexpr int A_BYTES = BM * 128, B_BYTES = BNL * 128, STAGE_BYTES = A_BYTES + B_BYTES;
   constexpr int STG_BYTES = 32 * 128;  // one 32 x 32 fp32 staging tile
   extern __shared__ uint8_t smem_raw[];
+  pdl_trigger();  // the next kernel of the stream may take SMs as this grid's CTAs retire (it blocks in its own pdl_wait)
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   uint8_t* stg_base = smem + STAGES * STAGE_BYTES;  // [8 epilogue warps][2 buffers][4096 B], 1024-aligned
   __shared__ uint64_t full_bar[STAGES], empty_bar[STAGES], tfull_bar[2], tempty_bar[2];
@@ -189,6 +190,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   if (CTAS == 2) cluster_sync_all();  // the peer's barriers are initialised before any remote arrive / TMA signal
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_s;
+  pdl_wait();  // barriers, TMEM and the cluster handshake are set up under the previous kernel's tail; operands are read after it
 
   if (warp == 0) {
     if (lane == 0) {
@@ -478,17 +480,24 @@ static int launch_tc(const CUtensorMap& ta, const CUtensorMap& tb, const CUtenso
   const int total = m_tiles * n_tiles * split;
   const int slots = sm_count() / CTAS;
   const int grid = (total < slots ? total : slots) * CTAS;
-  if (CTAS == 1) {
-    kern<<<grid, GEMM_THREADS, SMEM, st>>>(ta, tb, tc, tr, e, m_tiles, n_tiles, split, kblocks, per, use_tma_c);
-  } else {
+  {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(grid); cfg.blockDim = dim3(GEMM_THREADS); cfg.dynamicSmemBytes = SMEM; cfg.stream = st;
-    cudaLaunchAttribute at[1];
-    at[0].id = cudaLaunchAttributeClusterDimension;
-    at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
-    cfg.attrs = at; cfg.numAttrs = 1;
+    cudaLaunchAttribute at[2];
+    int na = 0;
+    if (CTAS == 2) {
+      at[na].id = cudaLaunchAttributeClusterDimension;
+      at[na].val.clusterDim.x = 2; at[na].val.clusterDim.y = 1; at[na].val.clusterDim.z = 1;
+      ++na;
+    }
+    if (pdl_mode()) {
+      at[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+      at[na].val.programmaticStreamSerializationAllowed = 1;
+      ++na;
+    }
+    cfg.attrs = at; cfg.numAttrs = na;
     cudaError_t err = cudaLaunchKernelEx(&cfg, kern, ta, tb, tc, tr, e, m_tiles, n_tiles, split, kblocks, per, use_tma_c);
-    if (err != cudaSuccess) { set_error("gemm_tf32_kernel<pair>: %s", cudaGetErrorString(err)); return (int)err; }
+    if (err != cudaSuccess) { set_error("gemm_tf32_kernel: %s", cudaGetErrorString(err)); return (int)err; }
   }
   return launch_status("gemm_tf32_kernel");
 }

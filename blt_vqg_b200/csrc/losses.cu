@@ -57,6 +57,8 @@ __global__ void __launch_bounds__(THREADS)
 ce_rows_reg_kernel(float* __restrict__ logits, int ld, const int* __restrict__ targets, int V, int pad,
                    const float* __restrict__ count, float coef, float* __restrict__ loss_sum, int write_grad, int rn) {
   __shared__ float red[32];
+  pdl_trigger();
+  pdl_wait();
   const int r = blockIdx.x, V4 = V >> 2;
   float4* row = reinterpret_cast<float4*>(logits + (size_t)r * ld);
   const int tgt = __ldg(targets + r);
@@ -353,8 +355,8 @@ extern "C" int b200iq_ce_rows(float* logits, int ld, const int* targets, int row
   B200IQ_CHECK_ARG(logits && targets && count && loss_sum && rows > 0 && V > 0 && ld >= V, "ce_rows: bad args");
   size_t smem = (size_t)V * sizeof(float);
   if ((V & 3) == 0 && (ld & 3) == 0 && (((uintptr_t)logits) & 15) == 0 && V <= 16 * 4 * 512) {
-    if (V <= 16 * 4 * 256) ce_rows_reg_kernel<256><<<rows, 256, 0, ST>>>(logits, ld, targets, V, pad_id, count, coef, loss_sum, write_grad, round_mode());
-    else ce_rows_reg_kernel<512><<<rows, 512, 0, ST>>>(logits, ld, targets, V, pad_id, count, coef, loss_sum, write_grad, round_mode());
+    if (V <= 16 * 4 * 256) launch_dep(ce_rows_reg_kernel<256>, dim3(rows), dim3(256), 0, ST, logits, ld, targets, V, pad_id, count, coef, loss_sum, write_grad, round_mode());
+    else launch_dep(ce_rows_reg_kernel<512>, dim3(rows), dim3(512), 0, ST, logits, ld, targets, V, pad_id, count, coef, loss_sum, write_grad, round_mode());
     return launch_status("ce_rows");
   }
   int cache = smem <= 200 * 1024;

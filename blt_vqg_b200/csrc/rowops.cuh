@@ -18,6 +18,8 @@ ln_fwd_warp_kernel(const float* __restrict__ x, const float* __restrict__ g, con
                    float* __restrict__ mean, float* __restrict__ rstd, int M, float eps, int rn) {
   constexpr int H = 128 * NV;
   const int lane = threadIdx.x & 31, nw = gridDim.x * (blockDim.x >> 5);
+  pdl_trigger();
+  pdl_wait();
   float4 gv[NV], bv[NV];
 #pragma unroll
   for (int i = 0; i < NV; ++i) { gv[i] = ldg4(g + (i * 32 + lane) * 4); bv[i] = ldg4(b + (i * 32 + lane) * 4); }
@@ -59,6 +61,8 @@ ln_bwd_warp_kernel(const float* __restrict__ dy, const float* __restrict__ x, co
   constexpr int H = 128 * NV;
   __shared__ float red[8][H];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = gridDim.x * 8;
+  pdl_trigger();
+  pdl_wait();
   float4 gv[NV], pg[NV], pb[NV];
 #pragma unroll
   for (int i = 0; i < NV; ++i) {
@@ -121,6 +125,8 @@ colsum4_kernel(const float* dy, const float* __restrict__ y, float* dpre, float*
   __shared__ float4 red[8][32];
   const int tx = threadIdx.x, ty = threadIdx.y, c = (blockIdx.x * 32 + tx) * 4;
   const int r0 = blockIdx.y * rows_per_cta, r1 = min(M, r0 + rows_per_cta);
+  pdl_trigger();
+  pdl_wait();
   float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
   if (c < N) {
 #pragma unroll 4

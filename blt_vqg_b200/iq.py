@@ -27,6 +27,10 @@ from .params import Arena, TRANSFORMER_ALIASES, export_state_dict, import_state_
 PAD = 0
 # run the 5-token context encoder on a side stream next to the 21-token response encoder (forward and backward): its GEMMs
 # have 2560 rows = 20-40 tiles for 148 SMs, so on its own it leaves three quarters of the GPU idle
+# B200IQ_PDL=2: programmatic dependent launch for the forward chain and the vocabulary loop only (=1: the whole step, see
+# train.py).  Off by default: measured on cfg3 it costs 0.5 ms (=2) / 1.2 ms (=1) per step, because a dependent kernel's
+# CTAs hold their SMs while they wait, and those are the SMs the side-stream kernels would otherwise fill.
+PDL_FORWARD = os.environ.get("B200IQ_PDL", "0") == "2"
 CONCURRENT_ENCODERS = os.environ.get("B200IQ_CONCURRENT", "1") == "1"
 CE_CHUNK_MB = int(os.environ.get("B200IQ_CE_CHUNK_MB", "80"))  # size of one logits chunk of the fused vocabulary projection + CE
 TERMS = ("rec", "img", "kld", "aux", "count", "gnorm_sq", "unused0", "unused1")
@@ -357,6 +361,7 @@ class IQ(nn.Module):
         ws, P, G, H, V = c.ws, c.P, c.G, self.H, self.V
         terms = self.terms
         terms.zero_()
+        pdl_prev = ops.set_pdl(True) if PDL_FORWARD else None
         dec_out = self._run_forward(c, feats, cids, rids, tids, eps)
         m = ws.meta
         c_rec, c_img, c_kld, c_aux = self.loss_coefs(kliter)
@@ -376,6 +381,8 @@ class IQ(nn.Module):
             if backward:
                 ops.gemm(lg, wout, d_dec[r0:r0 + rows], b_t=True, auto_split=True)
                 tf.grad_w(c, lg, xs, G["decoder.output.weight"], G["decoder.output.bias"])
+        if pdl_prev is not None:
+            ops.set_pdl(pdl_prev)
         d_img = ws.buf("d_img", B, H)
         d_z = None
         if self.latent_transformer:

@@ -24,6 +24,11 @@ def exact_mode():
     return _FORCE_SIMT
 
 
+def set_pdl(on):
+    """programmatic dependent launch for the hot kernels (b200iq_set_pdl); returns the previous setting"""
+    return bool(L.lib().b200iq_set_pdl(1 if on else 0))
+
+
 class gemm_mode:
     """context manager: `with gemm_mode(simt=True): ...` runs everything in exact fp32 — CUDA-core GEMMs and no TF32
     rounding of activations (b200iq_set_tf32_rounding(0)); simt=False is the tensor-core path"""

@@ -13,6 +13,9 @@ import torch
 from . import _lib, ops
 
 HIGH_PRIORITY_STEP = os.environ.get("B200IQ_HP_STREAM", "1") == "1"
+# B200IQ_PDL=1: programmatic dependent launch for the whole step (the next kernel's prologue runs under the previous
+# kernel's tail).  Off by default: with the side streams filling the tails it is a net loss (see iq.py PDL_FORWARD).
+PDL = os.environ.get("B200IQ_PDL", "0") == "1"
 
 
 def noam_lr(step, hidden_dim, warmup=4000):
@@ -62,6 +65,13 @@ class TrainStep:
         return terms
 
     def _step(self, images, answers, response, target, eps):
+        prev = ops.set_pdl(PDL)
+        try:
+            return self._step_body(images, answers, response, target, eps)
+        finally:
+            ops.set_pdl(prev)
+
+    def _step_body(self, images, answers, response, target, eps):
         m = self.model
         a = m.args
         if self.iter == getattr(a, "num_pretraining_steps", -1) and not m.latent_transformer:

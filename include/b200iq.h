@@ -33,6 +33,10 @@ const char* b200iq_last_error(void);
  * truncation biases every dot product towards zero.  0: nothing is rounded (use with B200IQ_GEMM_SIMT for an exact
  * fp32 run, e.g. the bit-exact greedy decode).  Returns the previous mode. */
 int b200iq_set_tf32_rounding(int on);
+/* Programmatic dependent launch for the hot kernels (GEMM, LayerNorm, column sums, attention, cross entropy, axpby):
+ * 1 lets each of them become resident under the tail of the previous kernel of its stream and block until that kernel
+ * has completed (griddepcontrol.wait) — same results, no launch gap.  Default 0.  Returns the previous setting. */
+int b200iq_set_pdl(int on);
 
 /* ------------------------------------------------------------------ GEMM */
 /* flags for B200iqGemm.flags */

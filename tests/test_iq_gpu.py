@@ -341,3 +341,32 @@ def test_full_size_fused_path_equals_api_path_and_trains(env):
         losses.append(float(m.total_loss(t.cpu(), 7000)))
     assert all(math.isfinite(x) for x in losses) and losses[-1] < losses[0] - 0.5, losses
     assert torch.isfinite(m.flat.data).all()
+
+
+def test_programmatic_dependent_launch_changes_nothing(env):
+    """b200iq_set_pdl(1): every hot kernel may start under the previous kernel's tail and blocks in griddepcontrol.wait until
+    that kernel is complete — losses and gradients must be the ones of plain stream-ordered launches (full size, so the GEMM,
+    LayerNorm, attention, column-sum, axpby and cross-entropy kernels all take their production paths)."""
+    from blt_vqg_b200 import ops, synth
+    from blt_vqg_b200.iq import IQ
+    cfg = synth.CONFIGS["cfg3"]
+    torch.manual_seed(0)
+    m = IQ(True, synth.SynthVocab(cfg["V"]), synth.args_for(cfg)).cuda().train()
+    b = {k: v.cuda() for k, v in synth.make_batch(cfg, seed=9).items()}
+    eps = torch.randn(cfg["B"], cfg["L"], device="cuda")
+    out = {}
+    for on in (False, True, False):
+        prev = ops.set_pdl(on)
+        try:
+            m.grad_arena.zero_()
+            t = m.forward_losses(b["feats"], b["answers"], b["posteriors"], b["questions"], kliter=7000, eps=eps).clone()
+            torch.cuda.synchronize()
+        finally:
+            ops.set_pdl(prev)
+        assert prev is False
+        out.setdefault(on, []).append((t, m.grad_arena.clone()))
+    (t0, g0), (t2, g2) = out[False]
+    t1, g1 = out[True][0]
+    noise = max(rel(g2, g0), 1e-7)          # split-K atomics reorder between two identical plain runs
+    assert torch.allclose(t1[:4], t0[:4], rtol=1e-5, atol=1e-6), (t1, t0)
+    assert rel(g1, g0) <= 4 * noise + 1e-6, (rel(g1, g0), noise)
