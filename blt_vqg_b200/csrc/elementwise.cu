@@ -226,13 +226,24 @@ __global__ void round_tf32_kernel(const float* __restrict__ src, float* __restri
   size_t n4 = n >> 2;
   const float4* s4 = reinterpret_cast<const float4*>(src);
   float4* d4 = reinterpret_cast<float4*>(dst);
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  for (; i + 3 * stride < n4; i += 4 * stride) {  // four loads in flight per thread: the weight arena streams from HBM
+    float4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) v[u] = s4[i + u * stride];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      v[u].x = tf32_rn(v[u].x); v[u].y = tf32_rn(v[u].y); v[u].z = tf32_rn(v[u].z); v[u].w = tf32_rn(v[u].w);
+      d4[i + u * stride] = v[u];
+    }
+  }
+  for (; i < n4; i += stride) {
     float4 v = s4[i];
     v.x = tf32_rn(v.x); v.y = tf32_rn(v.y); v.z = tf32_rn(v.z); v.w = tf32_rn(v.w);
     d4[i] = v;
   }
-  for (size_t i = (n4 << 2) + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
-    dst[i] = tf32_rn(src[i]);
+  for (size_t j = (n4 << 2) + (size_t)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += stride) dst[j] = tf32_rn(src[j]);
 }
 
 static inline int grid_for(size_t n, int threads) {
@@ -363,6 +374,9 @@ extern "C" int b200iq_axpby(const float* x, const float* y, float* out, size_t n
 extern "C" int b200iq_round_tf32(const float* src, float* dst, size_t n, void* stream) {
   B200IQ_CHECK_ARG(src && dst && n > 0, "round_tf32: bad args");
   B200IQ_CHECK_ARG(((((uintptr_t)src) | ((uintptr_t)dst)) & 15) == 0, "round_tf32: pointers must be 16-byte aligned");
-  round_tf32_kernel<<<grid_for((n + 3) / 4, 256), 256, 0, ST>>>(src, dst, n);
+  static int per_sm = 0;  // one resident wave (see b200iq_adam_step)
+  if (!per_sm) { cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, round_tf32_kernel, 256, 0); if (per_sm < 1) per_sm = 1; }
+  const size_t want = ((n + 3) / 4 + 255) / 256, cap = (size_t)sm_count() * per_sm;
+  round_tf32_kernel<<<(int)(want < cap ? (want < 1 ? 1 : want) : cap), 256, 0, ST>>>(src, dst, n);
   return launch_status("round_tf32");
 }

@@ -14,7 +14,15 @@ __global__ void __launch_bounds__(256) sumsq_kernel(const float* __restrict__ g,
   float acc = 0.f;
   size_t n4 = n >> 2;
   const float4* g4 = reinterpret_cast<const float4*>(g);
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+  // four independent 16-byte loads in flight per thread (one was 2 TB/s: 32 KB in flight per SM does not cover HBM latency)
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  for (; i + 3 * stride < n4; i += 4 * stride) {
+    const float4 a = g4[i], b = g4[i + stride], c = g4[i + 2 * stride], d = g4[i + 3 * stride];
+    acc += (a.x * a.x + a.y * a.y + a.z * a.z + a.w * a.w) + (b.x * b.x + b.y * b.y + b.z * b.z + b.w * b.w);
+    acc += (c.x * c.x + c.y * c.y + c.z * c.z + c.w * c.w) + (d.x * d.x + d.y * d.y + d.z * d.z + d.w * d.w);
+  }
+  for (; i < n4; i += stride) {
     float4 v = g4[i];
     acc += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
   }
@@ -89,7 +97,9 @@ extern "C" int b200iq_set_hyper(float* hyper, float lr, float bias_corr1, float 
 
 extern "C" int b200iq_grad_sumsq(const float* grad, size_t n, float* out, float* scratch, int scratch_floats, void* stream) {
   B200IQ_CHECK_ARG(grad && out && scratch && n > 0 && (((uintptr_t)grad) & 15) == 0, "grad_sumsq: bad args");
-  int grid = (int)min((size_t)sm_count() * 8, (n / 4 + 255) / 256 + 1);
+  static int per_sm = 0;  // one resident wave (see b200iq_adam_step)
+  if (!per_sm) { cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sumsq_kernel, 256, 0); if (per_sm < 1) per_sm = 1; }
+  int grid = (int)min((size_t)sm_count() * per_sm, (n / 4 + 255) / 256 + 1);
   if (grid > scratch_floats - 1) grid = scratch_floats - 1;
   B200IQ_CHECK_ARG(grid >= 1, "grad_sumsq: scratch too small");
   sumsq_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(grad, n, out, scratch);
@@ -101,7 +111,11 @@ extern "C" int b200iq_adam_step(float* param, float* grad, float* exp_avg, float
   B200IQ_CHECK_ARG(param && grad && exp_avg && exp_avg_sq && hyper && n > 0, "adam_step: bad args");
   B200IQ_CHECK_ARG(max_norm <= 0.f || normsq, "adam_step: clipping needs normsq");
   B200IQ_CHECK_ARG(((((uintptr_t)param) | ((uintptr_t)grad) | ((uintptr_t)exp_avg) | ((uintptr_t)exp_avg_sq)) & 15) == 0, "adam_step: arenas must be 16-byte aligned");
-  int grid = (int)min((size_t)sm_count() * 8, (n / 4 + 255) / 256 + 1);
+  // one resident wave: the grid-stride loop deals every CTA of the grid an equal share, so CTAs beyond what fits on the SMs
+  // (48 registers -> 5 per SM, not 8) ran as a second, mostly idle wave (433 us for 1.04 GB)
+  static int per_sm = 0;
+  if (!per_sm) { cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, adam_kernel, 256, 0); if (per_sm < 1) per_sm = 1; }
+  int grid = (int)min((size_t)sm_count() * per_sm, (n / 4 + 255) / 256 + 1);
   adam_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(param, grad, exp_avg, exp_avg_sq, n, hyper, normsq, beta1, beta2, eps, max_norm, zero_grad);
   return launch_status("adam_step");
 }

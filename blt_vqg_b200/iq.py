@@ -379,8 +379,12 @@ class IQ(nn.Module):
             ops.gemm(xs, wout, lg, bias=bout, fp32_out=True)       # decoder_transformer.py:40
             ops.ce_rows(lg, tflat[r0:r0 + rows], PAD, count, c_rec, terms[0:1], write_grad=backward)
             if backward:
+                # dX on the critical path, the vocabulary weight gradient (+ bias column sum) on the side stream under it;
+                # joined before the next chunk's logits overwrite lg
+                ev = c.mark()
                 ops.gemm(lg, wout, d_dec[r0:r0 + rows], b_t=True, auto_split=True)
-                tf.grad_w(c, lg, xs, G["decoder.output.weight"], G["decoder.output.bias"])
+                c.on_side(lambda: tf.grad_w(c, lg, xs, G["decoder.output.weight"], G["decoder.output.bias"]), ev)
+                c.join_side()
         if pdl_prev is not None:
             ops.set_pdl(pdl_prev)
         d_img = ws.buf("d_img", B, H)
