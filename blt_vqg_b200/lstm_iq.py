@@ -236,12 +236,16 @@ class LSTMIQ(nn.Module):
                 ops.lstm_cell_bwd(gates[t], cbuf[t], cbuf[t + 1], dh_run, dov[t] if dov is not None else None, dc, dgates[t], lengths, t)
                 ops.gemm(dgates[t], whh, dh_run, b_t=True, residual=dh_run)
         dg = dgates.view(T * B, 4 * H)
-        tf.grad_w(c, dg, hbuf[:T].view(T * B, H), G[pfx + "weight_hh_l0"], G[pfx + "bias_hh_l0"])
-        tf.grad_w(c, dg, e, G[pfx + "weight_ih_l0"], G[pfx + "bias_ih_l0"])
+        def weight_grads():   # off the dX chain: side stream, under the input-gradient GEMM and the embedding scatter
+            tf.grad_w(c, dg, hbuf[:T].view(T * B, H), G[pfx + "weight_hh_l0"], G[pfx + "bias_hh_l0"])
+            tf.grad_w(c, dg, e, G[pfx + "weight_ih_l0"], G[pfx + "bias_ih_l0"])
+        ev = c.mark()
         de = ws.buf(tag + ".de", T * B, H)
         ops.gemm(dg, c.W[pfx + "weight_ih_l0"], de, b_t=True)
+        c.on_side(weight_grads, ev)
         ops.dropout_(de, c.in_drop, *c.key(tag + ".indrop"))
         ops.embed_scatter_add(ids_tm, de, G[emb_name], -1)
+        c.join_side()
         return dh_run, dc
 
     def _mlp_fwd(self, c, tag, name, x, fp32_out=False):
@@ -330,8 +334,10 @@ class LSTMIQ(nn.Module):
             ops.gemm(xs, wout, lg, bias=bout, fp32_out=True)                          # decoder_rnn.py:107
             ops.ce_rows(lg, tgt[r0:r0 + n], PAD, count, lam["lambda_gen"], terms[0:1], write_grad=backward)
             if backward:
+                ev = c.mark()
                 ops.gemm(lg, wout, d_out[r0:r0 + n], b_t=True, auto_split=True)
-                tf.grad_w(c, lg, xs, G["decoder.out.weight"], G["decoder.out.bias"])
+                c.on_side(lambda: tf.grad_w(c, lg, xs, G["decoder.out.weight"], G["decoder.out.bias"]), ev)
+                c.join_side()   # before the next chunk's logits overwrite lg
         # ---- reconstructions from the detached features through a second reparameterisation (old_train_iq.py:145-155)
         z2 = ws.buf("z2", B, Z)
         ops.latent_fwd(zeros2z, mulv, e2, z2, None)
