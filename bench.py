@@ -204,14 +204,21 @@ def timed_region(fn, steps, dist_on):
 
 def gemm_roofline(ts, model, args, dev_batches, peaks):
     """CUDA events on the launching stream around every GEMM launch of two extra steps (after the timed region)"""
-    from blt_vqg_b200 import ops
+    from blt_vqg_b200 import iq as iq_mod, ops, transformer as tf_mod
+    # one kernel at a time for these two steps: with the side streams on, an event pair around a GEMM would also count the
+    # time its CTAs wait for SMs another stream's kernel holds
+    saved = (tf_mod.CONCURRENT, tf_mod.CONCURRENT_DW, iq_mod.CONCURRENT_ENCODERS)
+    tf_mod.CONCURRENT = tf_mod.CONCURRENT_DW = iq_mod.CONCURRENT_ENCODERS = False
     ops.GEMM_TRACE = []
     step_t0, step_t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    step_t0.record()
-    for i in range(2):
-        ts.step(*step_inputs(args.workload, dev_batches[i % len(dev_batches)]))
-    step_t1.record()
-    torch.cuda.synchronize()
+    try:
+        step_t0.record()
+        for i in range(2):
+            ts.step(*step_inputs(args.workload, dev_batches[i % len(dev_batches)]))
+        step_t1.record()
+        torch.cuda.synchronize()
+    finally:
+        tf_mod.CONCURRENT, tf_mod.CONCURRENT_DW, iq_mod.CONCURRENT_ENCODERS = saved
     trace, ops.GEMM_TRACE = ops.GEMM_TRACE, None
     tot_ms = sum(e0.elapsed_time(e1) for e0, e1, *_ in trace)
     tot_fl = sum(t[2] for t in trace)
@@ -240,7 +247,8 @@ def gemm_roofline(ts, model, args, dev_batches, peaks):
             "unit": "TFLOP/s", "frac": round(ach / peak, 4), "traffic": traffic, "traffic_unit": "DRAM bytes per launch (ncu)", "traffic_source": traffic_src,
             "algorithmic_bytes_per_launch": round(sum(t[3] for t in trace) / max(1, len(trace))), "launches_per_step": len(trace) // 2,
             "gemm_ms_per_step": round(tot_ms / 2, 3), "step_ms_instrumented": round(step_t0.elapsed_time(step_t1) / 2, 3),
-            "note": "operands are TF32 (nominal dense peak 1.1 PF = half of bf16); algorithmic flops = 2MNK per launch"}
+            "note": "operands are TF32 (nominal dense peak 1.1 PF = half of bf16); algorithmic flops = 2MNK per launch; launch durations "
+                    "from two extra steps run with the side streams off (one kernel at a time), events on the launching stream"}
     return roof, detail
 
 

@@ -104,6 +104,7 @@ class IQ(nn.Module):
         self._wflat = None  # TF32-rounded copy of the arena: the GEMM weight operands
         self._ctx = None
         self.on_grad_ready = None  # set by parallel.GradReducer.begin_step
+        self.on_grad_range = None  # (lo, hi) pieces that become final out of arena order (the side-stream encoder)
 
     # ------------------------------------------------------------------ module plumbing
     def _apply(self, fn, *a, **k):
@@ -170,6 +171,19 @@ class IQ(nn.Module):
         with torch.no_grad():
             f = self.trunk(images.to(self.flat.device)).flatten(1).float().contiguous()
         return f if ops.exact_mode() else ops.round_tf32(f, f)
+
+    def _range_marks(self, prefix):
+        """Ctx.on_ready callback for a stack that runs beside the main backward: turns its top-down layer marks into
+        (lo, hi) pieces of the stack's own arena region"""
+        offs = self.arena.offsets
+        ends = [offs[n] + self.arena.views[n.replace("#pack", "")].numel() for n in offs if n.startswith(prefix)]
+        state = {"hi": max(ends)}
+
+        def mark(lo):
+            if lo < state["hi"]:
+                self.on_grad_range(lo, state["hi"])
+                state["hi"] = lo
+        return mark
 
     def _fork(self, enable):
         """side stream that starts where the current stream is now (None when disabled)"""
@@ -312,9 +326,14 @@ class IQ(nn.Module):
         if side is not None:
             # both encoder backward passes at once; gradient-bucket marks wait for the join (the two stacks finish in no fixed
             # order, and a mark promises that everything above an arena offset is final)
-            saved, c.on_ready = c.on_ready, None
+            # order: the main stream keeps its suffix marks (the response encoder lies ABOVE the context encoder in the arena,
+            # so "everything above this offset is final" stays true for it); the context encoder reports its layers as
+            # ranges from the side stream
+            saved = c.on_ready
+            c.on_ready = self._range_marks("answer_encoder.encoder.") if (saved is not None and self.on_grad_range is not None) else None
             with torch.cuda.stream(side), _lib.pinned_stream():
                 context_encoder_bwd()
+            c.on_ready = saved
         if latent:
             d_r_out = ws.buf("d_r_out", B * R, H)
             d_r_out.zero_()
@@ -323,7 +342,6 @@ class IQ(nn.Module):
             tf.embed_bwd(c, "renc.emb", m["rids"], dr_in)
         if side is not None:
             self._join(side)
-            c.on_ready = saved
             c.ready("answer_encoder.encoder.enc.0.layer_norm_mha.weight")
         else:
             context_encoder_bwd()

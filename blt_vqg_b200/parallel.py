@@ -8,12 +8,14 @@ ready range (bucketed to `bucket_bytes`) on a dedicated communication stream, or
 an event.  The 1/world_size factor is folded into the clip+Adam kernel (hyper[3]); the global grad norm is computed on
 the already-reduced arena, so clipping needs no extra collective.
 """
+import os
+
 import torch
 import torch.distributed as dist
 
 
 class GradReducer:
-    def __init__(self, group=None, bucket_bytes=48 << 20):
+    def __init__(self, group=None, bucket_bytes=int(os.environ.get("B200IQ_BUCKET_MB", "48")) << 20):
         assert dist.is_initialized()
         self.group = group
         self.world_size = dist.get_world_size(group)
@@ -24,17 +26,22 @@ class GradReducer:
         self.pending_lo = None   # lowest offset reported ready and not yet sent
         self.collectives = 0
         self._grad = None
+        self.sent = []           # [lo, hi) pieces reduced out of order through mark_range (disjoint)
+        self.range_pending = None
 
     def _stream(self, device):
         if self.comm_stream is None and device.type == "cuda":
-            self.comm_stream = torch.cuda.Stream(device=device)
+            # default priority (the step runs on a high-priority stream, train.py); -1 measured the same at N=2
+            self.comm_stream = torch.cuda.Stream(device=device, priority=int(os.environ.get("B200IQ_COMM_PRIORITY", "0")))
         return self.comm_stream
 
     def begin_step(self, model):
         self._grad = model.grad_arena
         self.hi = self._grad.numel()
         self.pending_lo = self.hi
+        self.sent, self.range_pending = [], None
         model.on_grad_ready = self.mark_ready
+        model.on_grad_range = self.mark_range
 
     def _send(self, lo, hi):
         if hi <= lo:
@@ -52,6 +59,37 @@ class GradReducer:
             dist.all_reduce(g[lo:hi], group=self.group)
         self.collectives += 1
 
+    def _send_unsent(self, lo, hi):
+        """[lo, hi) minus the pieces mark_range already reduced"""
+        for a, b in sorted(self.sent):
+            if b <= lo or a >= hi:
+                continue
+            self._send(lo, min(a, hi))
+            lo = max(lo, b)
+        self._send(lo, hi)
+
+    def _flush_range(self):
+        if self.range_pending is not None:
+            lo, hi = self.range_pending
+            self._send(lo, hi)
+            self.sent.append((lo, hi))
+            self.range_pending = None
+
+    def mark_range(self, lo, hi):
+        """grad[lo:hi] is final although parts of grad[hi:] may not be: a stack that runs on a side stream next to the main
+        backward (the context encoder beside the response encoder) reports its layers this way, from ITS stream, and the
+        suffix sweep of mark_ready later skips them.  Adjacent pieces (layers, top down) are merged up to one bucket."""
+        lo, hi = max(0, lo), min(hi, self._grad.numel())
+        if hi <= lo:
+            return
+        if self.range_pending is not None and self.range_pending[0] == hi:
+            self.range_pending = (lo, self.range_pending[1])
+        else:
+            self._flush_range()
+            self.range_pending = (lo, hi)
+        if self.range_pending[1] - self.range_pending[0] >= self.bucket_elems:
+            self._flush_range()
+
     def mark_ready(self, lo, force=False):
         """the backward schedule guarantees grad[lo:] will not be written again in this step"""
         lo = max(0, min(lo, self.hi))
@@ -59,13 +97,16 @@ class GradReducer:
             self.pending_lo = lo
         while self.hi - self.pending_lo >= self.bucket_elems or (force and self.hi > self.pending_lo):
             lo_b = max(self.pending_lo, self.hi - self.bucket_elems)
-            self._send(lo_b, self.hi)
+            if self.range_pending is not None and self.range_pending[1] > lo_b:
+                self._flush_range()   # the sweep has reached an out-of-order piece that is still waiting for neighbours
+            self._send_unsent(lo_b, self.hi)
             self.hi = lo_b
 
     def finish_step(self, model):
         """flush what is left and make the compute stream wait for the communication stream"""
         self.mark_ready(0, force=True)
         model.on_grad_ready = None
+        model.on_grad_range = None
         st = self._stream(self._grad.device)
         if st is not None:
             ev = torch.cuda.Event()

@@ -33,7 +33,10 @@ def _worker(rank, world, port, n, bucket_bytes, marks, out):
         assert m.on_grad_ready is not None
         sent_before_finish = []
         for off in marks:                      # the backward schedule reports ready suffixes in decreasing offset order
-            m.on_grad_ready(off)
+            if isinstance(off, tuple):         # ... and (lo, hi) pieces of a stack that runs beside it, out of arena order
+                m.on_grad_range(*off)
+            else:
+                m.on_grad_ready(off)
             sent_before_finish.append(red.collectives)
         red.finish_step(m)
         assert m.on_grad_ready is None
@@ -64,3 +67,19 @@ def test_grad_reducer_sums_over_ranks_in_buckets(tmp_path, n, bucket_bytes, mark
     if n > elems:
         assert res["sent"][-1] >= 1                      # buckets were launched before the end of "backward"
         assert res["sent"] == sorted(res["sent"])
+
+
+@pytest.mark.parametrize("marks", [
+    # suffix marks down to 7000; a side stack owns [2500, 5000) and reports it top-down as ranges while the main backward
+    # goes on with suffix marks over [5000, 7000); then the join mark at 2500 and the rest at finish
+    [9000, 7000, (4000, 5000), (3000, 4000), 6000, (2500, 3000), 5000, 2500],
+    # ranges larger than a bucket, ranges that are not adjacent, a suffix sweep that runs into a piece still pending
+    [(1000, 6000), (500, 800), 9500, 300],
+])
+def test_grad_reducer_out_of_order_ranges_are_reduced_exactly_once(tmp_path, marks):
+    out = str(tmp_path / "res.pt")
+    port = _free_port()
+    mp.spawn(_worker, args=(2, port, 10000, 4 * 3000, marks, out), nprocs=2, join=True)
+    res = torch.load(out)
+    assert res["ok"]                                    # a piece sent twice would be summed twice: caught by the sum check
+    assert res["sent"][-1] >= 2
