@@ -39,6 +39,7 @@ def parse():
     ap.add_argument("--config", default="", help="other BASELINE.json configs as parity / sizing runs: transformer cfg1|cfg3|cfg5, lstm cfg1|cfg2|cfg4")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
+    ap.add_argument("--no-eager-baseline", action="store_true", help="skip the stock-PyTorch-eager-on-B200 timing of the oracle port")
     ap.add_argument("--no-secondary", action="store_true", help="skip the LSTM (configs[1]) measurement beside the transformer headline")
     ap.add_argument("--cpu-batch", type=int, default=64, help="bounded CPU sample: batch size of the oracle step")
     return ap.parse_args()
@@ -107,25 +108,31 @@ class ClockSampler(threading.Thread):
 
 
 # ------------------------------------------------------------------ the CPU arm (oracle port of the reference step)
-def cpu_reference_steps(args, cfg, steps, warmup, batch):
-    """the reference training step (fp32, PyTorch CPU, all host threads) via oracle/; returns (samples/s, cores, ms/step)"""
+def cpu_reference_steps(args, cfg, steps, warmup, batch, device="cpu", mode="fp32"):
+    """the reference training step (fp32, PyTorch CPU, all host threads) via oracle/; returns (samples/s, cores, ms/step).
+    device="cuda" runs the same port as stock PyTorch eager on the B200 (the reference ships no kernels of
+    its own, so eager PyTorch is its Blackwell path): mode "fp32" (TF32 off) | "tf32" | "bf16" (autocast).  Transformer only."""
     from blt_vqg_b200 import synth
     torch.set_num_threads(os.cpu_count())
     cores = torch.get_num_threads()
+    on_gpu = device != "cpu"
+    if on_gpu:
+        torch.backends.cuda.matmul.allow_tf32 = mode != "fp32"
+        torch.backends.cudnn.allow_tf32 = mode != "fp32"
     if args.workload == "transformer":
         from oracle import iq_oracle
         from blt_vqg_b200.iq import IQ
         torch.manual_seed(0)
         m0 = IQ(True, synth.SynthVocab(cfg["V"]), synth.args_for(cfg))
         names = m0.arena.names()
-        P = {k: v.clone() for k, v in m0.state_dict().items()}
+        P = {k: v.clone().to(device) for k, v in m0.state_dict().items()}
         params = [P[n].requires_grad_(True) for n in names]
         ocfg = dict(num_layers=cfg["NL"], num_heads=cfg["NH"], latent_dim=cfg["L"], image_recon_lambda=0.1, kl_ceiling=0.5,
                     aux_ceiling=1.0, full_kl_step=15000)
         bn = (P["encoder_cnn.bn.running_mean"], P["encoder_cnn.bn.running_var"])
 
         def loss_fn(b, step):
-            eps = torch.randn(b["feats"].shape[0], cfg["L"])  # CPU generator like transformer_layers.py:45
+            eps = torch.randn(b["feats"].shape[0], cfg["L"]).to(device)  # CPU generator like transformer_layers.py:45
             out, zl, kld, img, recon = iq_oracle.iq_forward(P, ocfg, b["feats"], b["answers"], b["posteriors"], b["questions"],
                                                             eps=eps, latent_mode=True, training=True, drop=(0.1, 0.1), bn_state=bn)
             return iq_oracle.iq_losses(ocfg, out, zl, kld, img, recon, b["questions"], step, True)[0]
@@ -136,12 +143,21 @@ def cpu_reference_steps(args, cfg, steps, warmup, batch):
     times = []
     for s in range(warmup + steps):
         b = synth.make_batch(cfg, seed=1234 + s, B=batch)
+        if on_gpu:
+            b = {k: v.to(device) for k, v in b.items()}
+            torch.cuda.synchronize()
         t0 = time.perf_counter()
-        loss = loss_fn(b, s)
+        if mode == "bf16":
+            with torch.autocast(device_type="cuda", dtype=torch.bfloat16):
+                loss = loss_fn(b, s)
+        else:
+            loss = loss_fn(b, s)
         opt.zero_grad()
         loss.backward()
         torch.nn.utils.clip_grad_norm_(params, 5.0)
         opt.step()
+        if on_gpu:
+            torch.cuda.synchronize()
         dt = time.perf_counter() - t0
         if s >= warmup:
             times.append(dt)
@@ -324,6 +340,20 @@ def measure(args, cfg, config, dp, rank, world, local_rank, roofline=True, cpu_a
         v, cores, cms = cpu_reference_steps(args, cfg, 3, 1, args.cpu_batch)
         cpu = {"value": round(v, 2), "unit": UNIT, "cores": cores, "kind": "port", "ms_per_step": round(cms, 1),
                "sample": "3 timed steps (after 1 warm-up) of fwd+losses+bwd+clip+Adam at batch %d of the same shapes, fp32 PyTorch CPU oracle port" % args.cpu_batch}
+        if args.workload == "transformer" and not args.no_eager_baseline:
+            # the same port as stock PyTorch eager on this B200 at the FULL batch (device-resident inputs)
+            eager = {}
+            for mode in ("fp32", "tf32", "bf16"):
+                try:
+                    ev, _, ems = cpu_reference_steps(args, cfg, 5, 3, cfg["B"], device="cuda", mode=mode)
+                    eager[mode] = {"value": round(ev, 1), "ms_per_step": round(ems, 2)}
+                except Exception as e:  # informational leg: never fail the bench line over it
+                    eager[mode] = {"error": "%s: %s" % (type(e).__name__, str(e)[:120])}
+                torch.cuda.empty_cache()
+            torch.backends.cuda.matmul.allow_tf32 = False
+            torch.backends.cudnn.allow_tf32 = False
+            cpu["eager_b200"] = dict(eager, unit=UNIT, sample="oracle port of the reference step run by stock PyTorch eager on cuda:0, batch %d, "
+                                     "5 timed steps after 3 warm-up; fp32 = TF32 off, tf32 = allow_tf32, bf16 = autocast" % cfg["B"])
     B = cfg["B"]
     h2d = sum(v.numel() * v.element_size() for k, v in hb[0].items() if k in ("feats", "answers", "posteriors", "questions", "alengths"))
     line = {"metric": METRIC, "value": round(B * world * args.steps / (ms * 1e-3), 1), "unit": UNIT, "n_gpus": world, "steps": args.steps,
