@@ -109,9 +109,13 @@ struct Philox {
   // counter = (c0,c1,c2,c3) -> 4 random words
   __host__ __device__ inline void operator()(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
                                              uint32_t out[4]) const {
+    rounds<10>(c0, c1, c2, c3, out);
+  }
+  template <int ROUNDS>
+  __host__ __device__ inline void rounds(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t out[4]) const {
     uint32_t a = k0, b = k1;
 #pragma unroll
-    for (int r = 0; r < 10; ++r) {
+    for (int r = 0; r < ROUNDS; ++r) {
       uint32_t h0, l0, h1, l1;
       mulhilo(0xD2511F53u, c0, h0, l0);
       mulhilo(0xCD9E8D57u, c2, h1, l1);
@@ -124,6 +128,20 @@ struct Philox {
 };
 __host__ __device__ inline float u32_to_unit(uint32_t x) {  // (0,1]
   return ((float)(x >> 8) + 1.0f) * (1.0f / 16777216.0f);
+}
+
+// The feed-forward dropout mask (b200iq_dropout and the GEMM epilogue make the SAME one): element i of the contiguous tensor
+// takes 16 bits of Philox4x32-7(seed; counter = offset + i/8) — word i & 3, upper half when (i >> 2) & 1 — and is kept when
+// they are >= round(p * 65536).  One call covers 8 elements and 7 rounds is the depth Salmon et al. report as passing
+// BigCrush: 2.9x less integer work per element than a 10-round word per element, which the GEMM epilogue could not hide
+// (profiles/r01f_gemm_dropout_epilogue_icache.txt).
+__host__ __device__ inline uint32_t dropout_threshold(float p) { return (uint32_t)(p * 65536.0f + 0.5f); }
+__device__ __forceinline__ void dropout_words(uint64_t seed, uint64_t offset, size_t i, uint32_t w[4]) {
+  const uint64_t ctr = offset + (i >> 3);
+  Philox(seed).rounds<7>((uint32_t)ctr, (uint32_t)(ctr >> 32), 0u, 0u, w);
+}
+__device__ __forceinline__ bool dropout_keep(const uint32_t w[4], size_t i, uint32_t thr) {
+  return ((w[i & 3] >> (((i >> 2) & 1) << 4)) & 0xFFFFu) >= thr;
 }
 
 }  // namespace b200iq

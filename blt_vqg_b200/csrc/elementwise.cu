@@ -174,20 +174,19 @@ __global__ void relu_bwd_colsum_kernel(const float* dy, const float* __restrict_
 }
 
 // ---------------------------------------------------------------- Philox dropout / randn / axpy
-// x *= mask / (1-p), mask from Philox(seed; counter = offset + i/4).  Calling it again with the same
-// (seed, offset) on the gradient reproduces the mask, so no mask tensor is stored.
+// x *= mask / (1-p), mask = dropout_keep (common.cuh: 16 bits of Philox4x32-7(seed; offset + i/8) per element).  Calling
+// it again with the same (seed, offset) on the gradient reproduces the mask, so no mask tensor is stored.
 __global__ void dropout_kernel(float* __restrict__ x, size_t n, float p, uint64_t seed, uint64_t offset, int rn) {
-  Philox ph(seed);
-  float scale = 1.f / (1.f - p);
-  size_t n4 = (n + 3) / 4;
-  for (size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x; q < n4; q += (size_t)gridDim.x * blockDim.x) {
-    uint32_t r[4];
-    uint64_t ctr = offset + q;
-    ph((uint32_t)ctr, (uint32_t)(ctr >> 32), 0u, 0u, r);
+  const float scale = 1.f / (1.f - p);
+  const uint32_t thr = dropout_threshold(p);
+  size_t n8 = (n + 7) / 8;
+  for (size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x; q < n8; q += (size_t)gridDim.x * blockDim.x) {
+    uint32_t w[4];
+    dropout_words(seed, offset, q * 8, w);
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      size_t i = q * 4 + j;
-      if (i < n) x[i] = (u32_to_unit(r[j]) > p) ? rnd(x[i] * scale, rn) : 0.f;
+    for (int j = 0; j < 8; ++j) {
+      size_t i = q * 8 + j;
+      if (i < n) x[i] = dropout_keep(w, i, thr) ? rnd(x[i] * scale, rn) : 0.f;
     }
   }
 }
@@ -355,7 +354,7 @@ extern "C" int b200iq_relu_bwd_colsum(const float* dy, const float* y, float* dp
 extern "C" int b200iq_dropout(float* x, size_t n, float p, uint64_t seed, uint64_t offset, void* stream) {
   B200IQ_CHECK_ARG(x && n > 0 && p >= 0.f && p < 1.f, "dropout: bad args");
   if (p == 0.f) return 0;
-  dropout_kernel<<<grid_for((n + 3) / 4, 256), 256, 0, ST>>>(x, n, p, seed, offset, round_mode());
+  dropout_kernel<<<grid_for((n + 7) / 8, 256), 256, 0, ST>>>(x, n, p, seed, offset, round_mode());
   return launch_status("dropout");
 }
 

@@ -116,10 +116,9 @@ __device__ __forceinline__ float epi_value(float acc, const GemmEpi& e, int row,
   if (e.flags & B200IQ_GEMM_RELU_MASK) v = (__ldg(e.residual + (size_t)row * e.ldr + col) > 0.f) ? v : 0.f;
   if (e.flags & B200IQ_GEMM_DROPOUT) {
     const size_t i = (size_t)row * e.N + col;
-    const uint64_t ctr = e.drop_offset + (i >> 2);
-    uint32_t r[4];
-    Philox(e.drop_seed)((uint32_t)ctr, (uint32_t)(ctr >> 32), 0u, 0u, r);
-    v = (u32_to_unit(r[i & 3]) > e.drop_p) ? v * e.drop_scale : 0.f;
+    uint32_t w[4];
+    dropout_words(e.drop_seed, e.drop_offset, i, w);
+    v = dropout_keep(w, i, dropout_threshold(e.drop_p)) ? v * e.drop_scale : 0.f;
   }
   return rnd(v, e.round);
 }
@@ -259,6 +258,8 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const bool has_r = EPI == 1 && (epi.flags & (B200IQ_GEMM_RESIDUAL | B200IQ_GEMM_RELU_MASK));
     const bool gate = EPI == 1 && (epi.flags & B200IQ_GEMM_RELU_MASK), relu = epi.flags & B200IQ_GEMM_RELU;
     const bool drop = EPI == 2;
+    const bool drop_pairs = (epi.N & 7) == 0;
+    const uint32_t drop_thr = dropout_threshold(epi.drop_p);
     uint32_t ti = 0, chunk = 0;
     // EPI 1: the 32 x 32 residual / relu-gate tile of a chunk is pulled by TMA straight into the chunk's staging buffer (same
     // 128B swizzle as the output tile, so lane r finds row r where it will write row r), one chunk ahead of the math.
@@ -317,16 +318,16 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             if (lane == 0) bulk_wait_read<1>();  // the store that last read this buffer has finished reading
             __syncwarp();
           }
+          uint32_t keep[4] = {0u, 0u, 0u, 0u};
 #pragma unroll
           for (int j = 0; j < 32; j += 4) {
             float4* slot = reinterpret_cast<float4*>(buf + lane * 128 + (((j >> 2) ^ (lane & 7)) << 4));
             float4 bb = bias4[j >> 2], gg = make_float4(0.f, 0.f, 0.f, 0.f);
             if (has_r) gg = *slot;
-            uint32_t keep[4] = {0u, 0u, 0u, 0u};
-            if (drop) {  // one Philox call covers the 4 consecutive elements of this float4 (N % 4 == 0, ldc == N)
-              const uint64_t ctr = epi.drop_offset + (((size_t)row * epi.N + col0 + j) >> 2);
-              Philox(epi.drop_seed)((uint32_t)ctr, (uint32_t)(ctr >> 32), 0u, 0u, keep);
-            }
+            // one Philox call covers 8 consecutive elements = this float4 and its neighbour (N % 4 == 0, ldc == N); when
+            // N % 8 == 0 every row starts a group of 8, so the odd float4s reuse the words of the even ones
+            const size_t ei = (size_t)row * epi.N + col0 + j;
+            if (drop && (!drop_pairs || !(j & 4))) dropout_words(epi.drop_seed, epi.drop_offset, ei, keep);
             float v[4];
             const float* ga = &gg.x; const float* ba = &bb.x;
 #pragma unroll
@@ -334,7 +335,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               float x = __uint_as_float(rr[j + t]) * epi.alpha + ba[t];
               if (gate) x = ga[t] > 0.f ? x : 0.f; else x += ga[t];
               if (relu) x = fmaxf(x, 0.f);
-              if (drop) x = (u32_to_unit(keep[t]) > epi.drop_p) ? x * epi.drop_scale : 0.f;
+              if (drop) x = dropout_keep(keep, ei + t, drop_thr) ? x * epi.drop_scale : 0.f;
               v[t] = rnd(x, epi.round);
             }
             // 128B swizzle: 16-byte chunk index XOR (row & 7), the layout the C tensor map expects; TMA clips M/N edges

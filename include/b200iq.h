@@ -49,8 +49,9 @@ int b200iq_set_pdl(int on);
 #define B200IQ_GEMM_SIMT      64  /* exact-fp32 CUDA-core path instead of tcgen05 TF32 */
 #define B200IQ_GEMM_RELU_MASK 128 /* multiply result by (gate[M,N] > 0): relu backward fused */
 #define B200IQ_GEMM_FP32_OUT  256 /* keep the full fp32 result (logits, returned tensors): no TF32 rounding of C */
-#define B200IQ_GEMM_DROPOUT   512 /* after relu: C *= keep/(1-p), keep from Philox(seed; counter = offset + (row*N+col)/4) — the
-                                     mask b200iq_dropout makes on the contiguous [M,N] tensor (needs ldc == N, N % 4 == 0);
+#define B200IQ_GEMM_DROPOUT   512 /* after relu: C *= keep/(1-p), keep = 16 bits of Philox4x32-7(seed; counter = offset +
+                                     (row*N+col)/8) >= round(65536 p) — the mask b200iq_dropout makes on the contiguous [M,N]
+                                     tensor (needs ldc == N, N % 4 == 0);
                                      replaces the nn.Dropout after each FFN linear, transformer_layers.py:405-406 */
 
 typedef struct B200iqGemm {
@@ -105,10 +106,10 @@ int b200iq_layernorm_bwd(const float* dy, const float* x, const float* gamma, co
 int b200iq_colsum_add(const float* x, float* out, int M, int N, int ld, void* stream);
 /* dpre = dy * (y > 0); dbias[c] += colsum(dpre) (dbias may be NULL)   replaces: ReLU backward, transformer_layers.py:405 */
 int b200iq_relu_bwd_colsum(const float* dy, const float* y, float* dpre, float* dbias, int M, int N, float scale, void* stream);
-/* inverted dropout in place with a Philox4x32-10 mask keyed (seed, offset); re-applying it to the gradient
- * with the same key is the backward.   replaces: nn.Dropout at transformer_layers.py:406,520; base_rnn.py:41 */
+/* inverted dropout in place; element i is kept when 16 bits of Philox4x32-7(seed; counter = offset + i/8) — word i & 3,
+ * upper half when (i >> 2) & 1 — are >= round(65536 p).  Re-applying it to the gradient with the same key is the backward.   replaces: nn.Dropout at transformer_layers.py:406,520; base_rnn.py:41 */
 int b200iq_dropout(float* x, size_t n, float p, uint64_t seed, uint64_t offset, void* stream);
-/* out ~ N(0,1), Philox4x32-10 + Box-Muller (oracle/philox.py is the bit-level CPU twin)
+/* out ~ N(0,1), Philox4x32-10(seed; counter = offset + i/4) + Box-Muller (moments checked in tests/test_ops_gpu.py)
  * replaces: torch.randn on the CPU + H2D copy, models/transformer_layers.py:45 */
 int b200iq_randn(float* out, size_t n, uint64_t seed, uint64_t offset, void* stream);
 /* out = a*x + b*y (out may alias x or y): residual adds that cannot ride a GEMM epilogue */
