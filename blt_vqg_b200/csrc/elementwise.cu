@@ -293,14 +293,28 @@ extern "C" int b200iq_layernorm_fwd(const float* x, const float* gamma, const fl
   B200IQ_CHECK_ARG(x && gamma && beta && y && M > 0 && H > 0, "layernorm_fwd: bad args");
   if ((H == 128 || H == 256 || H == 512 || H == 1024) && (((uintptr_t)x | (uintptr_t)y | (uintptr_t)gamma | (uintptr_t)beta) & 15) == 0) {
     const int grid = min(ceil_div(M, 8), sm_count() * 8), rn = round_mode();
-    if (H == 128) launch_dep(ln_fwd_warp_kernel<1>, dim3(grid), dim3(256), 0, ST, x, gamma, beta, y, mean, rstd, M, eps, rn);
-    else if (H == 256) launch_dep(ln_fwd_warp_kernel<2>, dim3(grid), dim3(256), 0, ST, x, gamma, beta, y, mean, rstd, M, eps, rn);
-    else if (H == 512) launch_dep(ln_fwd_warp_kernel<4>, dim3(grid), dim3(256), 0, ST, x, gamma, beta, y, mean, rstd, M, eps, rn);
-    else launch_dep(ln_fwd_warp_kernel<8>, dim3(grid), dim3(256), 0, ST, x, gamma, beta, y, mean, rstd, M, eps, rn);
+    if (H == 128) launch_dep(ln_fwd_warp_kernel<1, false>, dim3(grid), dim3(256), 0, ST, x, nullptr, nullptr, gamma, beta, y, mean, rstd, M, eps, rn);
+    else if (H == 256) launch_dep(ln_fwd_warp_kernel<2, false>, dim3(grid), dim3(256), 0, ST, x, nullptr, nullptr, gamma, beta, y, mean, rstd, M, eps, rn);
+    else if (H == 512) launch_dep(ln_fwd_warp_kernel<4, false>, dim3(grid), dim3(256), 0, ST, x, nullptr, nullptr, gamma, beta, y, mean, rstd, M, eps, rn);
+    else launch_dep(ln_fwd_warp_kernel<8, false>, dim3(grid), dim3(256), 0, ST, x, nullptr, nullptr, gamma, beta, y, mean, rstd, M, eps, rn);
     return launch_status("layernorm_fwd");
   }
   layernorm_fwd_kernel<<<ceil_div(M, 8), 256, 0, ST>>>(x, gamma, beta, y, mean, rstd, M, H, eps, round_mode());
   return launch_status("layernorm_fwd");
+}
+
+extern "C" int b200iq_add_layernorm_fwd(const float* x, const float* add, float* sum, const float* gamma, const float* beta, float* y,
+                                        float* mean, float* rstd, int M, int H, float eps, void* stream) {
+  B200IQ_CHECK_ARG(x && add && sum && gamma && beta && y && M > 0 && H > 0, "add_layernorm_fwd: bad args");
+  B200IQ_CHECK_ARG(H == 128 || H == 256 || H == 512 || H == 1024, "add_layernorm_fwd: H=%d unsupported (128, 256, 512, 1024)", H);
+  B200IQ_CHECK_ARG((((uintptr_t)x | (uintptr_t)add | (uintptr_t)sum | (uintptr_t)y | (uintptr_t)gamma | (uintptr_t)beta) & 15) == 0,
+                   "add_layernorm_fwd: pointers must be 16-byte aligned");
+  const int grid = min(ceil_div(M, 8), sm_count() * 8), rn = round_mode();
+  if (H == 128) launch_dep(ln_fwd_warp_kernel<1, true>, dim3(grid), dim3(256), 0, ST, x, add, sum, gamma, beta, y, mean, rstd, M, eps, rn);
+  else if (H == 256) launch_dep(ln_fwd_warp_kernel<2, true>, dim3(grid), dim3(256), 0, ST, x, add, sum, gamma, beta, y, mean, rstd, M, eps, rn);
+  else if (H == 512) launch_dep(ln_fwd_warp_kernel<4, true>, dim3(grid), dim3(256), 0, ST, x, add, sum, gamma, beta, y, mean, rstd, M, eps, rn);
+  else launch_dep(ln_fwd_warp_kernel<8, true>, dim3(grid), dim3(256), 0, ST, x, add, sum, gamma, beta, y, mean, rstd, M, eps, rn);
+  return launch_status("add_layernorm_fwd");
 }
 
 extern "C" int b200iq_layernorm_bwd(const float* dy, const float* x, const float* gamma, const float* mean, const float* rstd,

@@ -12,10 +12,14 @@ __device__ __forceinline__ float4 ldg4(const float* p) { return __ldg(reinterpre
 __device__ __forceinline__ void st4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
 
 // ---------------------------------------------------------------- LayerNorm forward: one warp per row, one HBM read
-template <int NV>  // float4s per lane; H = 128 * NV
+// ADD: the residual add in front of the LayerNorm rides along — s = rnd(x + add) is written to `sum` (the next block's
+// residual input and the LayerNorm backward's x) and normalised in the same pass: one launch and one read of s less than
+// axpby + LayerNorm, bit-identical to them.
+template <int NV, bool ADD>  // float4s per lane; H = 128 * NV
 __global__ void __launch_bounds__(256)
-ln_fwd_warp_kernel(const float* __restrict__ x, const float* __restrict__ g, const float* __restrict__ b, float* __restrict__ y,
-                   float* __restrict__ mean, float* __restrict__ rstd, int M, float eps, int rn) {
+ln_fwd_warp_kernel(const float* __restrict__ x, const float* __restrict__ add, float* __restrict__ sum, const float* __restrict__ g,
+                   const float* __restrict__ b, float* __restrict__ y, float* __restrict__ mean, float* __restrict__ rstd, int M,
+                   float eps, int rn) {
   constexpr int H = 128 * NV;
   const int lane = threadIdx.x & 31, nw = gridDim.x * (blockDim.x >> 5);
   pdl_trigger();
@@ -27,7 +31,15 @@ ln_fwd_warp_kernel(const float* __restrict__ x, const float* __restrict__ g, con
     float4 xv[NV];
     float s = 0.f;
 #pragma unroll
-    for (int i = 0; i < NV; ++i) { xv[i] = ldg4(x + (size_t)row * H + (i * 32 + lane) * 4); s += (xv[i].x + xv[i].y) + (xv[i].z + xv[i].w); }
+    for (int i = 0; i < NV; ++i) {
+      xv[i] = ldg4(x + (size_t)row * H + (i * 32 + lane) * 4);
+      if (ADD) {
+        const float4 av = ldg4(add + (size_t)row * H + (i * 32 + lane) * 4);
+        xv[i] = make_float4(rnd(xv[i].x + av.x, rn), rnd(xv[i].y + av.y, rn), rnd(xv[i].z + av.z, rn), rnd(xv[i].w + av.w, rn));
+        st4(sum + (size_t)row * H + (i * 32 + lane) * 4, xv[i]);
+      }
+      s += (xv[i].x + xv[i].y) + (xv[i].z + xv[i].w);
+    }
     const float mu = warp_sum(s) * (1.f / H);
     float v = 0.f;
 #pragma unroll

@@ -159,6 +159,17 @@ def layernorm_fwd(x, g, b, y, mean, rstd, eps=1e-5):
     return y
 
 
+def add_layernorm_supported(x):
+    return x.shape[1] in (128, 256, 512, 1024)
+
+
+def add_layernorm_fwd(x, add, out, g, b, y, mean, rstd, eps=1e-5):
+    """out = x + add (rounded like axpby), y = LayerNorm(out) in one pass"""
+    M, H = x.shape
+    _call("b200iq_add_layernorm_fwd", _p(x), _p(add), _p(out), _p(g), _p(b), _p(y), _p(mean), _p(rstd), M, H, _f(eps))
+    return y
+
+
 def layernorm_bwd(dy, x, g, mean, rstd, dx, dg, db, accumulate_dx):
     M, H = x.shape
     _call("b200iq_layernorm_bwd", _p(dy), _p(x), _p(g), _p(mean), _p(rstd), _p(dx), _p(dg), _p(db), M, H, int(accumulate_dx))

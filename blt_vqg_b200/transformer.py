@@ -272,8 +272,10 @@ def cross_attn_bwd(c, tag, pfx, dout, xn, enc_out, d_enc_out, first, enc_ids, B,
 
 
 # ------------------------------------------------------------------ position-wise FFN (ReLU after BOTH linears, N1)
-def ffn_fwd(c, tag, pfx, xn, x_res):
-    """relu + dropout after BOTH linears (N1) ride in the GEMM epilogues: h and f2 are written once, post-dropout"""
+def ffn_fwd(c, tag, pfx, xn, x_res, next_ln=None):
+    """relu + dropout after BOTH linears (N1) ride in the GEMM epilogues: h and f2 are written once, post-dropout.
+    next_ln = (tag, prefix) of the LayerNorm that reads this block's output (the next layer's first one, or the stack's final
+    one): the residual add and that LayerNorm then run as one kernel and (out, LN(out)) is returned instead of out."""
     M, H = xn.shape
     h = c.ws.buf(tag + ".h", M, c.F)
     f2 = c.ws.buf(tag + ".f2", M, H)
@@ -288,8 +290,18 @@ def ffn_fwd(c, tag, pfx, xn, x_res):
         ops.gemm(h, c.W[pfx + "layers.1.weight"], f2, bias=c.P[pfx + "layers.1.bias"], relu=True)
         ops.dropout_(f2, c.relu_drop, *c.key(tag + ".d2"))
     out = c.ws.buf(tag + ".out", M, H)
-    ops.axpby(x_res, f2, out)
-    return out
+    if next_ln is None:
+        ops.axpby(x_res, f2, out)
+        return out
+    ln_tag, ln_pfx = next_ln
+    y = c.ws.buf(ln_tag + ".y", M, H)
+    mean, rstd = c.ws.buf(ln_tag + ".mean", M), c.ws.buf(ln_tag + ".rstd", M)
+    if ops.add_layernorm_supported(out):
+        ops.add_layernorm_fwd(x_res, f2, out, c.P[ln_pfx + ".weight"], c.P[ln_pfx + ".bias"], y, mean, rstd)
+    else:
+        ops.axpby(x_res, f2, out)
+        ops.layernorm_fwd(out, c.P[ln_pfx + ".weight"], c.P[ln_pfx + ".bias"], y, mean, rstd)
+    return out, y
 
 
 def ffn_bwd(c, tag, pfx, dout, xn):
@@ -315,14 +327,16 @@ def ffn_bwd(c, tag, pfx, dout, xn):
 def encoder_fwd(c, tag, pfx, x, ids, B, n, NL):
     """models/transformer_layers.py:138-152 (timing already added by embed_fwd). Returns LN(x_NL)."""
     c.ws.meta[tag + ".in"] = x
+    xn = ln_fwd(c, tag + ".0.ln1", pfx + "enc.0.layer_norm_mha", x)
     for i in range(NL):
         lt, lp = "%s.%d" % (tag, i), "%senc.%d." % (pfx, i)
-        xn = ln_fwd(c, lt + ".ln1", lp + "layer_norm_mha", x)
         a = self_attn_fwd(c, lt + ".sa", lp + "multi_head_attention.", xn, x, ids, B, n, False)
         xn2 = ln_fwd(c, lt + ".ln2", lp + "layer_norm_ffn", a)
-        x = ffn_fwd(c, lt + ".ff", lp + "positionwise_feed_forward.", xn2, a)
+        # the block's residual add and the LayerNorm that reads it (next layer's first, or the final one) are one kernel
+        nxt = ("%s.%d.ln1" % (tag, i + 1), "%senc.%d.layer_norm_mha" % (pfx, i + 1)) if i + 1 < NL else (tag + ".lnf", pfx + "layer_norm")
+        x, xn = ffn_fwd(c, lt + ".ff", lp + "positionwise_feed_forward.", xn2, a, next_ln=nxt)
     c.ws.meta[tag + ".last"] = x
-    return ln_fwd(c, tag + ".lnf", pfx + "layer_norm", x)
+    return xn
 
 
 def encoder_bwd(c, tag, pfx, dy, ids, B, n, NL):
@@ -355,18 +369,20 @@ def decoder_fwd(c, tag, pfx, x, ids, enc_out, enc_ids, B, T, S, NL):
         with torch.cuda.stream(side), _lib.pinned_stream():
             for i in range(NL):
                 kvs[i] = cross_kv_fwd(c, "%s.%d.ca" % (tag, i), "%sdec.%d.multi_head_attention_enc_dec." % (pfx, i), enc_out)
+    xn1 = ln_fwd(c, tag + ".0.ln1", pfx + "dec.0.layer_norm_mha_dec", x)
     for i in range(NL):
         lt, lp = "%s.%d" % (tag, i), "%sdec.%d." % (pfx, i)
-        xn = ln_fwd(c, lt + ".ln1", lp + "layer_norm_mha_dec", x)
+        xn = xn1
         a = self_attn_fwd(c, lt + ".sa", lp + "multi_head_attention_dec.", xn, x, ids, B, T, True)
         xn = ln_fwd(c, lt + ".ln2", lp + "layer_norm_mha_enc", a)
         if side is not None and i == 0:
             torch.cuda.current_stream().wait_stream(side)
         b = cross_attn_fwd(c, lt + ".ca", lp + "multi_head_attention_enc_dec.", xn, a, enc_out, enc_ids, B, T, S, kv=kvs[i])
         xn = ln_fwd(c, lt + ".ln3", lp + "layer_norm_ffn", b)
-        x = ffn_fwd(c, lt + ".ff", lp + "positionwise_feed_forward.", xn, b)
+        nxt = ("%s.%d.ln1" % (tag, i + 1), "%sdec.%d.layer_norm_mha_dec" % (pfx, i + 1)) if i + 1 < NL else (tag + ".lnf", pfx + "layer_norm")
+        x, xn1 = ffn_fwd(c, lt + ".ff", lp + "positionwise_feed_forward.", xn, b, next_ln=nxt)
     c.ws.meta[tag + ".last"] = x
-    return ln_fwd(c, tag + ".lnf", pfx + "layer_norm", x)
+    return xn1
 
 
 def decoder_bwd(c, tag, pfx, dy, ids, enc_out, d_enc_out, enc_ids, B, T, S, NL):

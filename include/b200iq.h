@@ -100,6 +100,11 @@ int b200iq_tok0_scatter_add(const float* src, float* dst, int B, int n, int H, i
  * replaces: models/transformer_layers.py:134,151,202,220,256-257,320-322 */
 int b200iq_layernorm_fwd(const float* x, const float* gamma, const float* beta, float* y, float* mean, float* rstd,
                          int M, int H, float eps, void* stream);
+/* sum = x + add (rounded like b200iq_axpby), y = LayerNorm(sum): the residual add in front of a LayerNorm and the LayerNorm in
+ * one pass (H in {128, 256, 512, 1024}, 16-byte aligned pointers; other shapes: b200iq_axpby + b200iq_layernorm_fwd).
+ * replaces: `x + y` at models/transformer_layers.py:282,364 followed by the next layer's layer_norm (:271,338) / the final one */
+int b200iq_add_layernorm_fwd(const float* x, const float* add, float* sum, const float* gamma, const float* beta, float* y,
+                             float* mean, float* rstd, int M, int H, float eps, void* stream);
 int b200iq_layernorm_bwd(const float* dy, const float* x, const float* gamma, const float* mean, const float* rstd,
                          float* dx, float* dgamma, float* dbeta, int M, int H, int accumulate_dx, void* stream);
 /* out[c] += sum_m x[m,c]  (bias gradients) */

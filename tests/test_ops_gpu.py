@@ -112,6 +112,24 @@ def test_layernorm_fwd_bwd(ops):
         assert rel(dg, g.grad) < 1e-4 and rel(db, b.grad) < 1e-4
 
 
+def test_add_layernorm_is_axpby_then_layernorm_bit_for_bit(ops):
+    """the fused residual-add + LayerNorm (one pass) writes exactly what b200iq_axpby followed by b200iq_layernorm_fwd write"""
+    for M, H in ((1000, 512), (10240, 512), (5, 128), (3001, 1024), (100, 256)):
+        assert ops.add_layernorm_supported(torch.empty(M, H))
+        x, f = torch.randn(M, H, device="cuda"), torch.randn(M, H, device="cuda").relu_()
+        g, b = torch.randn(H, device="cuda"), torch.randn(H, device="cuda")
+        s0, y0 = torch.empty(M, H, device="cuda"), torch.empty(M, H, device="cuda")
+        m0, r0 = torch.empty(M, device="cuda"), torch.empty(M, device="cuda")
+        ops.axpby(x, f, s0)
+        ops.layernorm_fwd(s0, g, b, y0, m0, r0)
+        s1, y1 = torch.empty(M, H, device="cuda"), torch.empty(M, H, device="cuda")
+        m1, r1 = torch.empty(M, device="cuda"), torch.empty(M, device="cuda")
+        ops.add_layernorm_fwd(x, f, s1, g, b, y1, m1, r1)
+        assert torch.equal(s1, s0) and torch.equal(y1, y0) and torch.equal(m1, m0) and torch.equal(r1, r0)
+        assert rel(y1, torch.nn.functional.layer_norm(x + f, (H,), g, b, 1e-5)) < 2e-3   # TF32-rounded sum and output
+    assert not ops.add_layernorm_supported(torch.empty(8, 300))
+
+
 def test_small_elementwise(ops):
     B, n, H = 9, 5, 64
     x = torch.randn(B * n, H, device="cuda")
