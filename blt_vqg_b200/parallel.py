@@ -15,12 +15,22 @@ import torch.distributed as dist
 
 
 class GradReducer:
-    def __init__(self, group=None, bucket_bytes=int(os.environ.get("B200IQ_BUCKET_MB", "48")) << 20):
+    def __init__(self, group=None, bucket_bytes=None, tail_bucket_bytes=None, tail_fraction=0.5):
+        """bucket_bytes: all-reduce granularity while most of the backward is still ahead (default B200IQ_BUCKET_MB = 48);
+        tail_bucket_bytes: granularity once the unsent part is the lower `tail_fraction` of the arena (the encoders and the
+        embedding, the end of the backward) — whatever is still pending when the backward ends cannot overlap anything, so
+        the pieces get smaller there (default B200IQ_TAIL_BUCKET_MB = 16; 0 or an explicit bucket_bytes without it: off)."""
+        if bucket_bytes is None:
+            bucket_bytes = int(os.environ.get("B200IQ_BUCKET_MB", "48")) << 20
+            if tail_bucket_bytes is None:
+                tail_bucket_bytes = int(os.environ.get("B200IQ_TAIL_BUCKET_MB", "16")) << 20
         assert dist.is_initialized()
         self.group = group
         self.world_size = dist.get_world_size(group)
         self.rank = dist.get_rank(group)
         self.bucket_elems = bucket_bytes // 4
+        self.tail_elems = (tail_bucket_bytes // 4) if tail_bucket_bytes else None
+        self.tail_fraction = tail_fraction
         self.comm_stream = None
         self.hi = None           # everything in grad[hi:] has been handed to NCCL
         self.pending_lo = None   # lowest offset reported ready and not yet sent
@@ -59,6 +69,11 @@ class GradReducer:
             dist.all_reduce(g[lo:hi], group=self.group)
         self.collectives += 1
 
+    def _bucket(self, top):
+        if self.tail_elems is not None and top <= self.tail_fraction * self._grad.numel():
+            return min(self.tail_elems, self.bucket_elems)
+        return self.bucket_elems
+
     def _send_unsent(self, lo, hi):
         """[lo, hi) minus the pieces mark_range already reduced"""
         for a, b in sorted(self.sent):
@@ -87,7 +102,7 @@ class GradReducer:
         else:
             self._flush_range()
             self.range_pending = (lo, hi)
-        if self.range_pending[1] - self.range_pending[0] >= self.bucket_elems:
+        if self.range_pending[1] - self.range_pending[0] >= self._bucket(self.range_pending[1]):
             self._flush_range()
 
     def mark_ready(self, lo, force=False):
@@ -95,8 +110,8 @@ class GradReducer:
         lo = max(0, min(lo, self.hi))
         if lo < self.pending_lo:
             self.pending_lo = lo
-        while self.hi - self.pending_lo >= self.bucket_elems or (force and self.hi > self.pending_lo):
-            lo_b = max(self.pending_lo, self.hi - self.bucket_elems)
+        while self.hi - self.pending_lo >= self._bucket(self.hi) or (force and self.hi > self.pending_lo):
+            lo_b = max(self.pending_lo, self.hi - self._bucket(self.hi))
             if self.range_pending is not None and self.range_pending[1] > lo_b:
                 self._flush_range()   # the sweep has reached an out-of-order piece that is still waiting for neighbours
             self._send_unsent(lo_b, self.hi)

@@ -21,14 +21,14 @@ class _FakeModel:
         self.on_grad_ready = None
 
 
-def _worker(rank, world, port, n, bucket_bytes, marks, out):
+def _worker(rank, world, port, n, bucket_bytes, marks, out, tail_bytes=None):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
         from blt_vqg_b200.parallel import GradReducer, shard_batch
         m = _FakeModel(n, rank)
         local = m.grad_arena.clone()
-        red = GradReducer(bucket_bytes=bucket_bytes)
+        red = GradReducer(bucket_bytes=bucket_bytes, tail_bucket_bytes=tail_bytes)
         red.begin_step(m)
         assert m.on_grad_ready is not None
         sent_before_finish = []
@@ -83,3 +83,17 @@ def test_grad_reducer_out_of_order_ranges_are_reduced_exactly_once(tmp_path, mar
     res = torch.load(out)
     assert res["ok"]                                    # a piece sent twice would be summed twice: caught by the sum check
     assert res["sent"][-1] >= 2
+
+
+def test_grad_reducer_smaller_buckets_at_the_end_of_the_backward(tmp_path):
+    """below half of the arena the pieces shrink to tail_bucket_bytes: less is left pending when the backward ends"""
+    out = str(tmp_path / "res.pt")
+    port = _free_port()
+    marks = [9000, 6000, 4500, 4000, 3000, (1000, 2000), 2000, 500]
+    mp.spawn(_worker, args=(2, port, 10000, 4 * 3000, marks, out, 4 * 800), nprocs=2, join=True)
+    res = torch.load(out)
+    assert res["ok"]
+    # 9000: nothing yet (1000 < 3000); 6000: one 3000 bucket; 4500: top is 7000 > 5000 -> still large buckets, 2500 pending;
+    # 4000: 3000 sent, top 4000 is in the tail; 3000: one 800 piece; the range (1000, 2000) is a piece of its own
+    assert res["sent"][:5] == [0, 1, 1, 2, 3] and res["sent"][5] == 4
+    assert res["collectives"] > -(-10000 // 3000)
