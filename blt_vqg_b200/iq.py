@@ -28,9 +28,9 @@ PAD = 0
 # run the 5-token context encoder on a side stream next to the 21-token response encoder (forward and backward): its GEMMs
 # have 2560 rows = 20-40 tiles for 148 SMs, so on its own it leaves three quarters of the GPU idle
 # B200IQ_PDL=2: programmatic dependent launch for the forward chain and the vocabulary loop only (=1: the whole step, see
-# train.py).  Off by default: measured on cfg3 it costs 0.5 ms (=2) / 1.2 ms (=1) per step, because a dependent kernel's
+# train.py; the default =3 covers the decoder's forward only, transformer.py).  Measured on cfg3 the wider scopes cost 0.5 ms (=2) / 1.2 ms (=1) per step, because a dependent kernel's
 # CTAs hold their SMs while they wait, and those are the SMs the side-stream kernels would otherwise fill.
-PDL_FORWARD = os.environ.get("B200IQ_PDL", "0") == "2"
+PDL_FORWARD = os.environ.get("B200IQ_PDL", "3") == "2"
 CONCURRENT_ENCODERS = os.environ.get("B200IQ_CONCURRENT", "1") == "1"
 CE_CHUNK_MB = int(os.environ.get("B200IQ_CE_CHUNK_MB", "80"))  # size of one logits chunk of the fused vocabulary projection + CE
 TERMS = ("rec", "img", "kld", "aux", "count", "gnorm_sq", "unused0", "unused1")

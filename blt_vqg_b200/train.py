@@ -15,7 +15,7 @@ from . import _lib, ops
 HIGH_PRIORITY_STEP = os.environ.get("B200IQ_HP_STREAM", "1") == "1"
 # B200IQ_PDL=1: programmatic dependent launch for the whole step (the next kernel's prologue runs under the previous
 # kernel's tail).  Off by default: with the side streams filling the tails it is a net loss (see iq.py PDL_FORWARD).
-PDL = os.environ.get("B200IQ_PDL", "0") == "1"
+PDL = os.environ.get("B200IQ_PDL", "3") == "1"
 
 
 def noam_lr(step, hidden_dim, warmup=4000):

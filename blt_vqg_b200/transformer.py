@@ -18,6 +18,10 @@ FUSE_DROPOUT = os.environ.get("B200IQ_FUSE_DROPOUT", "1") == "1"
 CONCURRENT = os.environ.get("B200IQ_CONCURRENT", "1") == "1"
 # weight-gradient GEMMs of a block on the side stream, under the block's dX chain: the persistent GEMM grids leave SMs idle in
 # their last wave (80 pair tiles on 74 SM pairs for every M=10240, N=512 product) and the side kernels' CTAs fill them
+# B200IQ_PDL=3 (default): programmatic dependent launch for the decoder's forward only — the one phase with a single active
+# stream, where a dependent kernel's waiting CTAs take SMs nobody else wants (12.47 -> 12.41 ms; =1 / =2 widen it to the whole
+# step / the whole forward and lose 1.2 / 0.5 ms to the starved side streams, see iq.py; =0 off)
+PDL_DECODER = os.environ.get("B200IQ_PDL", "3") == "3"
 CONCURRENT_DW = CONCURRENT and os.environ.get("B200IQ_CONCURRENT_DW", "1") == "1"
 
 
@@ -377,11 +381,15 @@ def decoder_fwd(c, tag, pfx, x, ids, enc_out, enc_ids, B, T, S, NL):
         xn = ln_fwd(c, lt + ".ln2", lp + "layer_norm_mha_enc", a)
         if side is not None and i == 0:
             torch.cuda.current_stream().wait_stream(side)
+        if PDL_DECODER and i == 0:
+            pdl_prev = ops.set_pdl(True)   # from here to the end of the stack nothing runs beside the main stream
         b = cross_attn_fwd(c, lt + ".ca", lp + "multi_head_attention_enc_dec.", xn, a, enc_out, enc_ids, B, T, S, kv=kvs[i])
         xn = ln_fwd(c, lt + ".ln3", lp + "layer_norm_ffn", b)
         nxt = ("%s.%d.ln1" % (tag, i + 1), "%sdec.%d.layer_norm_mha_dec" % (pfx, i + 1)) if i + 1 < NL else (tag + ".lnf", pfx + "layer_norm")
         x, xn1 = ffn_fwd(c, lt + ".ff", lp + "positionwise_feed_forward.", xn, b, next_ln=nxt)
     c.ws.meta[tag + ".last"] = x
+    if PDL_DECODER:
+        ops.set_pdl(pdl_prev)
     return xn1
 
 
