@@ -25,12 +25,13 @@ from . import transformer as tf
 from .params import Arena, TRANSFORMER_ALIASES, export_state_dict, import_state_dict, transformer_iq_specs
 
 PAD = 0
+# B200IQ_PDL=2: programmatic dependent launch for the whole forward and the vocabulary loop (=1: the whole step, train.py;
+# the default =3 covers the decoder's forward only, transformer.py).  Measured on cfg3 the wider scopes cost 0.5 ms (=2) /
+# 1.2 ms (=1) per step, because a dependent kernel's CTAs hold their SMs while they wait, and those are the SMs the side-stream
+# kernels would otherwise fill.
+PDL_FORWARD = os.environ.get("B200IQ_PDL", "3") == "2"
 # run the 5-token context encoder on a side stream next to the 21-token response encoder (forward and backward): its GEMMs
 # have 2560 rows = 20-40 tiles for 148 SMs, so on its own it leaves three quarters of the GPU idle
-# B200IQ_PDL=2: programmatic dependent launch for the forward chain and the vocabulary loop only (=1: the whole step, see
-# train.py; the default =3 covers the decoder's forward only, transformer.py).  Measured on cfg3 the wider scopes cost 0.5 ms (=2) / 1.2 ms (=1) per step, because a dependent kernel's
-# CTAs hold their SMs while they wait, and those are the SMs the side-stream kernels would otherwise fill.
-PDL_FORWARD = os.environ.get("B200IQ_PDL", "3") == "2"
 CONCURRENT_ENCODERS = os.environ.get("B200IQ_CONCURRENT", "1") == "1"
 CE_CHUNK_MB = int(os.environ.get("B200IQ_CE_CHUNK_MB", "80"))  # size of one logits chunk of the fused vocabulary projection + CE
 TERMS = ("rec", "img", "kld", "aux", "count", "gnorm_sq", "unused0", "unused1")
