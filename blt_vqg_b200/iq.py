@@ -96,6 +96,7 @@ class IQ(nn.Module):
         self.register_buffer("bn_num_batches_tracked", torch.zeros((), dtype=torch.long), persistent=False)
         self.register_buffer("timing_enc", gen_timing_signal(1000, self.H), persistent=False)  # :96,118
         self.register_buffer("timing_dec", gen_timing_signal(200, self.H), persistent=False)   # :163,184
+        self.feature_cache = None  # set by attach_feature_cache(): `images` may then be (B,) rows of batch.FeatureCache
         self.trunk = None  # set by attach_trunk(); reference: torchvision resnet18 (encoder_cnn.py:17)
         self.seed = 1234
         self.step_idx = 0
@@ -141,6 +142,10 @@ class IQ(nn.Module):
         for p in trunk.parameters():
             p.requires_grad = False
 
+    def attach_feature_cache(self, cache):
+        """batch.FeatureCache of pooled trunk features: `images` may then be a (B,) integer tensor of cache rows"""
+        self.feature_cache = cache
+
     # ------------------------------------------------------------------ internals
     @property
     def grad_arena(self):
@@ -162,6 +167,12 @@ class IQ(nn.Module):
         return ws
 
     def _features(self, images):
+        if images.dim() == 1 and not images.is_floating_point():
+            if self.feature_cache is None:
+                raise _lib.B200iqError("image rows given but no feature cache attached (call attach_feature_cache)")
+            rows = _ids(images, self.flat.device)
+            ws = self._workspace("feats")
+            return self.feature_cache.gather(rows, ws.buf("feats", rows.numel(), self.feature_cache.rows.shape[1]))
         if images.dim() == 2:
             f = images.to(self.flat.device, torch.float32, non_blocking=True).contiguous()
             if ops.exact_mode():

@@ -168,6 +168,12 @@ class LSTMIQ(nn.Module):
         return c
 
     def _feats(self, c, images):
+        if images.dim() == 1 and not images.is_floating_point():
+            cache = getattr(self, "feature_cache", None)
+            if cache is None:
+                raise _lib.B200iqError("image rows given but no feature cache attached (set .feature_cache = batch.FeatureCache)")
+            rows = self._ids(images, self.flat.device)
+            return cache.gather(rows, c.ws.buf("feats", rows.numel(), cache.rows.shape[1]))
         f = images.to(self.flat.device, torch.float32, non_blocking=True).contiguous()
         if f.dim() != 2:
             raise _lib.B200iqError("LSTMIQ takes pooled trunk features (B, FEAT); run the frozen CNN trunk first")

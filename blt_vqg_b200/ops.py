@@ -342,3 +342,25 @@ def log_softmax_rows_(x):
 def topk_softmax_rows(x, k, idx_out, val_out=None):
     rows, V = x.shape
     _call("b200iq_topk_softmax_rows", _p(x), x.stride(0), rows, V, int(k), _p(idx_out), _p(val_out))
+
+
+def feature_gather(cache, idx, out, bad_rows=None):
+    """out[b,:] = fp32(cache[idx[b],:]) — cache is [num_images, F] bf16 or fp32 (b200iq_feature_gather)"""
+    assert cache.dtype in (torch.bfloat16, torch.float32) and idx.dtype == torch.int32 and out.dtype == torch.float32
+    _call("b200iq_feature_gather", _p(cache), C.c_int(int(cache.dtype == torch.bfloat16)), _p(idx), _p(out), idx.numel(),
+          cache.shape[1], cache.shape[0], _p(bad_rows))
+    return out
+
+
+def feature_store(feats, idx, cache, bad_rows=None):
+    """cache[idx[b],:] = feats[b,:] (b200iq_feature_store)"""
+    assert cache.dtype in (torch.bfloat16, torch.float32) and idx.dtype == torch.int32 and feats.dtype == torch.float32
+    _call("b200iq_feature_store", _p(feats), _p(idx), _p(cache), C.c_int(int(cache.dtype == torch.bfloat16)), idx.numel(),
+          cache.shape[1], cache.shape[0], _p(bad_rows))
+
+
+def ids_narrow(src, dst):
+    """dst (int32) = src (int64), elementwise (b200iq_ids_narrow)"""
+    assert src.dtype == torch.int64 and dst.dtype == torch.int32 and src.numel() == dst.numel()
+    _call("b200iq_ids_narrow", _p(src), _p(dst), C.c_size_t(src.numel()))
+    return dst

@@ -206,6 +206,23 @@ int b200iq_lstm_seq_bwd(const float* gates, const float* cbuf, const float* whh,
 /* out[t*B+b] = in[b*T_in + col0 + t], t < T_out: batch-major token ids -> time-major (inputs[:, :-1] of decoder_rnn.py:141) */
 int b200iq_transpose_ids(const int* in, int* out, int B, int T_in, int T_out, int col0, void* stream);
 
+/* ---------------------------------------------------------- input side: feature cache + token block */
+/* The trunk is frozen (models/encoder_cnn.py:18-19) and an image repeats across its questions (utils/store_dataset.py:107-121), so
+ * its pooled features are computed once and kept in HBM: `cache` is [num_images, F], bf16 (cache_bf16 = 1, F % 8 == 0) or fp32
+ * (cache_bf16 = 0, F % 4 == 0) rows, 16-byte aligned.  A batch then names its images by row index (int32 idx[B]).
+ * gather: out[b,:] = cache[idx[b],:] widened to fp32 (fp32 rows are rounded to TF32 like every GEMM operand unless
+ * b200iq_set_tf32_rounding(0)); store: cache[idx[b],:] = feats[b,:] (round-to-nearest-even to bf16).  Rows whose index is outside
+ * [0, num_images) read as zeros / are not written, and are counted into *bad_rows (device int, may be NULL).
+ * replaces: the per-step `self.encoder_cnn.cnn(images)` trunk pass + avgpool of models/encoder_cnn.py:32-33 and the (B,3,224,224)
+ * fp32 host->device copy of the batch dict (utils/data_loader.py:160,168) */
+int b200iq_feature_gather(const void* cache, int cache_bf16, const int* idx, float* out, int B, int F, int num_images,
+                          int* bad_rows, void* stream);
+int b200iq_feature_store(const float* feats, const int* idx, void* cache, int cache_bf16, int B, int F, int num_images,
+                         int* bad_rows, void* stream);
+/* dst[i] = (int32) src[i]: the reference's collate_fn builds int64 token tensors (`.long()`, utils/data_loader.py:162-166);
+ * the kernels read int32 */
+int b200iq_ids_narrow(const int64_t* src, int* dst, size_t n, void* stream);
+
 /* ---------------------------------------------------------- optimizer */
 /* hyper[0..3] = {lr, 1-beta1^t, 1-beta2^t, grad_scale}, written by a kernel whose ARGUMENTS carry the host scalars (no pinned
  * staging buffer to race with).   replaces: the param_groups[0]["lr"] write of train_iq.py:257 */

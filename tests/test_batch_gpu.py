@@ -1,0 +1,134 @@
+"""GPU: the input side of the boundary — feature cache kernels, int64 -> int32 narrowing, the staged
+token block, and that a training step fed through them is bit-identical to one fed the tensors directly."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def env(built_lib):
+    from blt_vqg_b200 import _lib
+    _lib.require_device()
+    return True
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+@pytest.mark.parametrize("B,F,N", [(7, 64, 33), (512, 2048, 4096)])
+def test_feature_cache_round_trip(env, dtype, B, F, N):
+    from blt_vqg_b200 import ops
+    from blt_vqg_b200.batch import FeatureCache
+    g = torch.Generator().manual_seed(B + F)
+    feats = torch.randn(B, F, generator=g).abs().cuda()
+    rows = torch.randperm(N, generator=g)[:B].int().cuda()
+    cache = FeatureCache(N, F, dtype=dtype)
+    cache.store(rows, feats)
+    out = cache.gather(rows)
+    if dtype == torch.bfloat16:
+        want = feats.bfloat16().float()           # a bf16 value is a TF32 value: no second rounding
+        assert torch.equal(cache.rows[rows.long()], feats.bfloat16())
+    else:
+        want = ops.round_tf32(feats, torch.empty_like(feats))
+        assert torch.equal(cache.rows[rows.long()], feats)
+    assert torch.equal(out, want)
+    # rows repeat inside a batch (an image has several questions) and come in any order
+    rep = rows[torch.randint(0, B, (3 * B,), generator=g).cuda()]
+    assert torch.equal(cache.gather(rep), want[(rep[:, None] == rows[None, :]).float().argmax(1)])
+    assert cache.bad_rows() == 0
+
+
+def test_feature_cache_out_of_range_rows_are_zero_and_counted(env):
+    from blt_vqg_b200.batch import FeatureCache
+    cache = FeatureCache(10, 32)
+    cache.rows.fill_(1.0)
+    rows = torch.tensor([0, -1, 9, 10], dtype=torch.int32).cuda()
+    out = cache.gather(rows)
+    assert out[0].eq(1).all() and out[2].eq(1).all() and out[1].eq(0).all() and out[3].eq(0).all()
+    assert cache.bad_rows() == 2
+    cache.store(rows, torch.full((4, 32), 2.0).cuda())
+    assert cache.bad_rows() == 4 and cache.rows[0].eq(2).all() and cache.rows[9].eq(2).all() and cache.rows[1:9].eq(1).all()
+
+
+def test_feature_cache_argument_errors(env):
+    from blt_vqg_b200 import _lib
+    from blt_vqg_b200.batch import FeatureCache
+    with pytest.raises(_lib.B200iqError):
+        FeatureCache(4, 12)                       # bf16 rows need a multiple of 8
+    with pytest.raises(_lib.B200iqError):
+        FeatureCache(4, 16, dtype=torch.float16)
+    c = FeatureCache(2, 16)
+    c.assign_rows([11, 12])
+    with pytest.raises(_lib.B200iqError):
+        c.assign_rows([13])
+    assert c.lookup([12, 11, 12]).tolist() == [1, 0, 1]
+
+
+def test_ids_narrow(env):
+    from blt_vqg_b200 import ops
+    src = torch.randint(0, 32000, (1024, 65), dtype=torch.int64).cuda()
+    dst = torch.empty(src.shape, dtype=torch.int32, device="cuda")
+    assert torch.equal(ops.ids_narrow(src, dst), src.int())
+
+
+def test_stager_views_match_the_batch_dict(env):
+    from blt_vqg_b200 import synth
+    from blt_vqg_b200.batch import BatchStager, TOKEN_KEYS
+    cfg = synth.CONFIGS["tiny"]
+    st = BatchStager()
+    staged, batches = [], []
+    for i in range(5):                                   # 5 steps through 2 slots
+        b = synth.make_batch(cfg, seed=100 + i, B=13)    # int64, like the reference's collate_fn
+        s = st.stage(b, feats=b["feats"], image_rows=torch.arange(13)).wait()
+        for k in TOKEN_KEYS:
+            assert s.tokens[k].dtype == torch.int32 and torch.equal(s.tokens[k].cpu(), b[k].int()), (i, k)
+            assert s.tokens[k].data_ptr() % 16 == 0
+        assert torch.equal(s.feats.cpu(), b["feats"]) and s.image_rows.cpu().tolist() == list(range(13))
+        assert s.h2d_bytes >= 13 * (cfg["S"] + 3 + 2 * cfg["T"] + 1 + 1) * 4 + b["feats"].numel() * 4
+        s.done()
+    with pytest.raises(Exception):
+        st.stage({"questions": torch.zeros(3, dtype=torch.int64)})
+
+
+def test_training_step_through_stager_and_cache_is_bit_identical(env, golden_dir):
+    import os
+    from blt_vqg_b200 import synth
+    from blt_vqg_b200.batch import BatchStager, FeatureCache
+    from blt_vqg_b200.iq import IQ
+    from blt_vqg_b200.train import TrainStep
+    gold = torch.load(os.path.join(golden_dir, "iq_transformer_tiny_latent.pt"), weights_only=False)
+    cfg = gold["cfg"]
+
+    def run(mode):
+        m = IQ(True, synth.SynthVocab(cfg["V"]), synth.args_for(cfg)).cuda()
+        m.load_state_dict(gold["state_dict"])
+        m.attn_dropout = m.relu_dropout = 0.0
+        m.train()
+        ts = TrainStep(m, lr_fn=lambda s: 1e-3)
+        st = BatchStager()
+        cache = FeatureCache(64, cfg["FEAT"], dtype=torch.float32)
+        m.attach_feature_cache(cache)
+        out = []
+        for i in range(3):
+            b = synth.make_batch(cfg, seed=7 + i, B=8)
+            eps = torch.randn(8, cfg["L"], generator=torch.Generator().manual_seed(i)).cuda()
+            if mode == "direct":
+                t = ts.step(b["feats"], b["answers"], b["posteriors"], b["questions"], eps=eps)
+            elif mode == "staged":
+                s = st.stage(b, feats=b["feats"]).wait()
+                t = ts.step(s.feats, s.answers, s.posteriors, s.questions, eps=eps)
+                s.done()
+            else:
+                ids = [1000 * i + j for j in range(8)]
+                rows = cache.assign_rows(ids)
+                cache.store(rows.cuda(), b["feats"].cuda())          # what fill_from_trunk does after the trunk pass
+                s = st.stage(b, image_rows=cache.lookup(ids)).wait()
+                t = ts.step(s.image_rows, s.answers, s.posteriors, s.questions, eps=eps)
+                s.done()
+            out.append(t.clone())
+        return torch.stack(out).cpu(), m.flat.data.clone().cpu()
+
+    t0, p0 = run("direct")
+    for mode in ("staged", "cached"):
+        t1, p1 = run(mode)
+        assert torch.equal(t0, t1), mode
+        assert torch.equal(p0, p1), mode
