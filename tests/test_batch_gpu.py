@@ -1,5 +1,6 @@
 """GPU: the input side of the boundary — feature cache kernels, int64 -> int32 narrowing, the staged
-token block, and that a training step fed through them is bit-identical to one fed the tensors directly."""
+token block, and that a training step fed through them matches one fed the tensors directly (same inputs bit for bit;
+the step's own float atomics set the comparison band)."""
 import pytest
 import torch
 
@@ -89,7 +90,7 @@ def test_stager_views_match_the_batch_dict(env):
         st.stage({"questions": torch.zeros(3, dtype=torch.int64)})
 
 
-def test_training_step_through_stager_and_cache_is_bit_identical(env, golden_dir):
+def test_training_step_through_stager_and_cache_matches_the_direct_step(env, golden_dir):
     import os
     from blt_vqg_b200 import synth
     from blt_vqg_b200.batch import BatchStager, FeatureCache
@@ -128,7 +129,12 @@ def test_training_step_through_stager_and_cache_is_bit_identical(env, golden_dir
         return torch.stack(out).cpu(), m.flat.data.clone().cpu()
 
     t0, p0 = run("direct")
+    ta, pa = run("direct")
+    # the step itself is reproducible only up to the order of its float atomics (embedding scatter-add, LayerNorm
+    # dgamma/dbeta, split-K reduce-add, loss sums): the staged runs must sit inside that same run-to-run band
+    band_t = max(float((t0 - ta).abs().max()), 1e-6) * 4 + 1e-6
+    band_p = max(float((p0 - pa).abs().max()), 1e-8) * 4 + 1e-7
     for mode in ("staged", "cached"):
         t1, p1 = run(mode)
-        assert torch.equal(t0, t1), mode
-        assert torch.equal(p0, p1), mode
+        assert float((t0 - t1).abs().max()) <= band_t, (mode, float((t0 - t1).abs().max()), band_t)
+        assert float((p0 - p1).abs().max()) <= band_p, (mode, float((p0 - p1).abs().max()), band_p)
