@@ -31,8 +31,10 @@ PAD = 0
 TERMS = ("gen", "kl", "rec_i", "rec_a", "count", "unused0", "unused1", "unused2")
 
 
-def lstm_iq_specs(a, V, H, Z, A, FEAT):
-    """parameter inventory in forward order (reverse = gradient-ready order)"""
+def lstm_iq_specs(a, V, H, Z, A, FEAT, num_categories=0):
+    """parameter inventory in forward order (reverse = gradient-ready order); num_categories > 0 appends the category space
+    (encode_categories / encode_into_t / predict_from_category, old_train_iq.py:134-142,194-213) AFTER everything else, so
+    the offsets of the answer space do not depend on it"""
     k = 1.0 / math.sqrt(H)
     a.add("encoder_cnn.cnn.fc.weight", (H, FEAT), ("normal", 0.02))      # encoder_cnn.py:27-28
     a.add("encoder_cnn.cnn.fc.bias", (H,), ("zeros", 0))
@@ -55,6 +57,14 @@ def lstm_iq_specs(a, V, H, Z, A, FEAT):
     a.add("decoder.out.bias", (V,), ("zeros", 0))
     mlp_specs(a, "image_reconstructor", Z, A, H)
     mlp_specs(a, "answer_reconstructor", Z, A, H)
+    if num_categories > 0:
+        a.add("category_encoder.weight", (num_categories, H), ("normal", 1.0))   # nn.Embedding default init
+        mlp_specs(a, "category_attention", 2 * H, A, H)
+        a.add("mu_category_encoder.weight#pack", (Z, H), ("linear", H))       # mu | logvar: one [2Z, H] GEMM operand
+        a.add("logvar_category_encoder.weight", (Z, H), ("linear", H))
+        a.add("mu_category_encoder.bias#pack", (Z,), ("linear_bias", H))
+        a.add("logvar_category_encoder.bias", (Z,), ("linear_bias", H))
+        a.linear("t_decoder", H, Z)
 
 
 def mlp_specs(a, name, i, hdim, o):
@@ -79,8 +89,9 @@ class LSTMIQ(nn.Module):
         super().__init__()
         if rnn_cell.upper() != "LSTM" or num_layers != 1 or num_att_layers != 2:
             raise NotImplementedError("LSTMIQ implements the default upstream configuration: 1-layer LSTM, 2-layer MLPs")
-        if not no_category_space:
-            raise NotImplementedError("category space (encode_categories / encode_into_t) is SURVEY.md §8(f) rank 4: not built yet")
+        # category space: forward / inference only — the in-tree training loop never puts a t-term into the
+        # loss it backpropagates (old_train_iq.py:399-444), only `evaluate` and the samplers use it (:134-142,194-213)
+        self.no_category_space, self.num_categories = no_category_space, num_categories
         self.V, self.H, self.Z, self.A, self.FEAT = vocab_size, hidden_size, z_size, att_ff_size, feat_dim
         self.max_len, self.sos_id, self.eos_id = max_len, sos_id, eos_id
         assert self.H % 4 == 0 and self.Z % 4 == 0 and self.A % 4 == 0 and self.FEAT % 4 == 0 and self.V % 4 == 0, \
@@ -89,7 +100,7 @@ class LSTMIQ(nn.Module):
         self.no_answer_recon, self.no_image_recon = no_answer_recon, no_image_recon
         self.lambdas = dict(lambda_gen=lambda_gen, lambda_z=lambda_z, lambda_i=lambda_i, lambda_a=lambda_a)
         self.arena = Arena()
-        lstm_iq_specs(self.arena, self.V, self.H, self.Z, self.A, self.FEAT)
+        lstm_iq_specs(self.arena, self.V, self.H, self.Z, self.A, self.FEAT, 0 if no_category_space else num_categories)
         self.flat = nn.Parameter(self.arena.finalize())
         self.arena.bind(self.flat.data)
         if embedding is not None:  # GloVe (V, H) tensor: old_train_iq.py:38-40 (copied, see SURVEY §8c on decoder_rnn.py:87-88)
@@ -268,22 +279,22 @@ class LSTMIQ(nn.Module):
         hbuf = self._lstm_fwd(c, "enc", "answer_encoder.rnn.", "answer_encoder.embedding.weight", ids_tm, S, B, None, None, alens)
         return hbuf[S]  # final hidden of every row (state stops updating at its length)
 
-    def _z_params_fwd(self, c, img, ans, B):
-        """encode_into_z: MLP(cat(img, ans)) -> [mu | logvar] in one GEMM"""
+    def _z_params_fwd(self, c, img, ans, B, space="answer"):
+        """encode_into_z (space="answer") / encode_into_t (space="category"): MLP(cat(img, other)) -> [mu | logvar] in one GEMM"""
         H = self.H
         cat = c.ws.buf("cat", B, 2 * H)
         ops.tok0_gather(img, cat[:, :H], B, 1, H)
         ops.tok0_gather(ans, cat[:, H:], B, 1, H)
-        att = self._mlp_fwd(c, "att", "answer_attention", cat)
-        wml = c.pspan("mu_answer_encoder.weight", "logvar_answer_encoder.weight", H)
-        o0, o1 = self.arena.span("mu_answer_encoder.bias", "logvar_answer_encoder.bias")
+        att = self._mlp_fwd(c, "att", space + "_attention", cat)
+        wml = c.pspan("mu_%s_encoder.weight" % space, "logvar_%s_encoder.weight" % space, H)
+        o0, o1 = self.arena.span("mu_%s_encoder.bias" % space, "logvar_%s_encoder.bias" % space)
         mulv = c.ws.buf("mulv", B, 2 * self.Z)
         ops.gemm(att, wml, mulv, bias=self.flat.data[o0:o1], fp32_out=True)
         return cat, att, mulv
 
-    def _init_hidden_fwd(self, c, img, z, B):
-        """decode_questions prologue: h0 = c0 = gen_decoder(img + z_decoder(z))"""
-        zh = tf.linear_fwd(c, "zh", "z_decoder", z)
+    def _init_hidden_fwd(self, c, img, z, B, proj="z_decoder"):
+        """decode_questions prologue: h0 = c0 = gen_decoder(img + z_decoder(z)) (t_decoder for a sample of the category space)"""
+        zh = tf.linear_fwd(c, "zh", proj, z)
         s = ops.axpby(img, zh, c.ws.buf("s", B, self.H))
         return s, self._mlp_fwd(c, "gd", "gen_decoder", s)
 
@@ -464,8 +475,76 @@ class LSTMIQ(nn.Module):
         ra = None if self.no_answer_recon else self._mlp_fwd(c, "ra", "answer_reconstructor", zs.contiguous(), fp32_out=True).clone()
         return ri, ra
 
+    # ---- category space (call sites old_train_iq.py:134-142,194-213, evaluate_iq.py:51-54) -- forward only
+    def _need_category_space(self):
+        if self.no_category_space:
+            raise _lib.B200iqError("this LSTMIQ was built with no_category_space=True")
+
     @torch.no_grad()
-    def decode_questions(self, image_features, zs, questions=None, teacher_forcing_ratio=0, decode_function=None):
+    def encode_categories(self, categories):
+        """nn.Embedding(num_categories, H) lookup: categories (B,) int -> (B, H)"""
+        self._need_category_space()
+        ids = self._ids(categories.reshape(-1), self.flat.device)
+        c = self._stage_ctx("cat", ids.numel())
+        out = c.ws.buf("catf", ids.numel(), self.H)
+        return ops.embed_gather(ids, c.P["category_encoder.weight"], out).clone()
+
+    @torch.no_grad()
+    def encode_into_t(self, image_features, category_features):
+        """(t_mus, t_logvars) = the category space's Gaussian, same shape of computation as encode_into_z"""
+        self._need_category_space()
+        B = image_features.shape[0]
+        c = self._stage_ctx("t", B)
+        _, _, mulv = self._z_params_fwd(c, image_features.contiguous(), category_features.contiguous(), B, "category")
+        return mulv[:, :self.Z].clone(), mulv[:, self.Z:].clone()
+
+    @torch.no_grad()
+    def _kl(self, prior, post):
+        """mean_b KL(N(post) || N(prior)) through b200iq_latent_fwd; prior / post are (mu, logvar) pairs, prior None = unit normal"""
+        B = post[0].shape[0]
+        c = self._stage_ctx("kl", B)
+        q, p = c.ws.buf("kl.q", B, 2 * self.Z), c.ws.buf("kl.p", B, 2 * self.Z)
+        q[:, :self.Z].copy_(post[0]); q[:, self.Z:].copy_(post[1])
+        if prior is None:
+            p.zero_()
+        else:
+            p[:, :self.Z].copy_(prior[0]); p[:, self.Z:].copy_(prior[1])
+        e = c.ws.buf("kl.e", B, self.Z)
+        e.zero_()
+        out = torch.zeros(1, device=q.device)
+        ops.latent_fwd(p, q, e, c.ws.buf("kl.z", B, self.Z), out)
+        return out[0]
+
+    def gaussian_KL_loss(self, mus, logvars):
+        """utils/train_utils.py:148-159: KL to the unit normal, summed over elements, / B"""
+        return self._kl(None, (mus, logvars))
+
+    def compute_two_gaussian_loss(self, mu1, logvar1, mu2, logvar2):
+        """old_train_iq.py:262-278: KL(N(mu1, e^logvar1) || N(mu2, e^logvar2)) summed over elements, / B (the reference adds 1e-8
+        to e^logvar2 and to B)"""
+        return self._kl((mu2, logvar2), (mu1, logvar1))
+
+    @torch.no_grad()
+    def _predict(self, image_features, zs, from_t):
+        _, _, ret = self.decode_questions(image_features, zs, questions=None, teacher_forcing_ratio=0, from_t=from_t)
+        return torch.cat(ret[self.KEY_SEQUENCE], dim=1)
+
+    @torch.no_grad()
+    def predict_from_answer(self, images, answers, alengths, eps=None):
+        """evaluate_iq.py:51-52: (B, max_len) greedy token ids from the answer space (eval mode decodes from the mean)"""
+        img = self.encode_images(images)
+        mus, logvars = self.encode_into_z(img, self.encode_answers(answers, alengths))
+        return self._predict(img, self.reparameterize(mus, logvars, eps), False)
+
+    @torch.no_grad()
+    def predict_from_category(self, images, categories, eps=None):
+        """evaluate_iq.py:53-54, old_train_iq.py:194-213: (B, max_len) greedy token ids from the category space"""
+        img = self.encode_images(images)
+        t_mus, t_logvars = self.encode_into_t(img, self.encode_categories(categories))
+        return self._predict(img, self.reparameterize(t_mus, t_logvars, eps), True)
+
+    @torch.no_grad()
+    def decode_questions(self, image_features, zs, questions=None, teacher_forcing_ratio=0, decode_function=None, from_t=False):
         """models/decoder_rnn.py:110-162 behind the glue: returns (outputs, hidden, ret_dict) with `outputs` a list of (B, V)
         log-probability tensors and ret_dict = {sequence: list of (B,1) argmax ids, length: list of ints}.
         teacher_forcing_ratio >= 1 with `questions`: one pass over questions[:, :-1]; otherwise free-running greedy decoding for
@@ -474,7 +553,9 @@ class LSTMIQ(nn.Module):
         B, H, V = zs.shape[0], self.H, self.V
         c = self._stage_ctx("dec", B)
         ws = c.ws
-        _, hid = self._init_hidden_fwd(c, image_features.contiguous(), zs.contiguous(), B)
+        if from_t:
+            self._need_category_space()
+        _, hid = self._init_hidden_fwd(c, image_features.contiguous(), zs.contiguous(), B, "t_decoder" if from_t else "z_decoder")
         outputs, symbols = [], []
         if questions is not None and teacher_forcing_ratio >= 1:
             qids = self._ids(questions, dev)

@@ -95,6 +95,52 @@ def gaussian_kl_loss(mus, logvars, eps=1e-8):
     return -0.5 * torch.sum(1 + logvars - mus.pow(2) - logvars.exp()) / (mus.size(0) + eps)
 
 
+# ---- category space (old_train_iq.py:134-142,194-213; evaluate_iq.py:51-54).  Composition from the call sites: categories ->
+# nn.Embedding(num_categories, H); encode_into_t mirrors encode_into_z with its own MLP + two Linear(H, Z); a sample of the
+# category space reaches the decoder through its own Linear(Z, H) (t_decoder).
+def encode_categories(P, categories):
+    return F.embedding(categories, P["category_encoder.weight"])
+
+
+def encode_into_t(P, img, catf):
+    att = mlp2(P, "category_attention.", torch.cat((img, catf), dim=1))
+    return (F.linear(att, P["mu_category_encoder.weight"], P["mu_category_encoder.bias"]),
+            F.linear(att, P["logvar_category_encoder.weight"], P["logvar_category_encoder.bias"]))
+
+
+def compute_two_gaussian_loss(mu1, logvar1, mu2, logvar2):
+    """old_train_iq.py:262-278 (statement by statement)"""
+    numerator = logvar1.exp() + torch.pow(mu1 - mu2, 2)
+    fraction = torch.div(numerator, (logvar2.exp() + 1e-8))
+    kl = 0.5 * torch.sum(logvar2 - logvar1 + fraction - 1)
+    return kl / (mu1.size(0) + 1e-8)
+
+
+def greedy_decode_from_t(P, img, ts, sos_id, max_len):
+    Q = dict(P)
+    Q["z_decoder.weight"], Q["z_decoder.bias"] = P["t_decoder.weight"], P["t_decoder.bias"]
+    return greedy_decode(Q, img, ts, sos_id, max_len)
+
+
+def add_category_space(P, cfg, num_categories=16, seed=1):
+    """reference-style initialisation of the category-space blocks, appended to an init_state_dict() result"""
+    g = torch.Generator().manual_seed(seed)
+    H, Z, A = cfg["H"], cfg["Z"], cfg["A"]
+
+    def uni(shape, b):
+        return (torch.rand(shape, generator=g) * 2 - 1) * b
+
+    P["category_encoder.weight"] = torch.randn(num_categories, H, generator=g)
+    P["category_attention.layers.fc0.weight"] = torch.randn(A, 2 * H, generator=g) * math.sqrt(2.0 / (2 * H))
+    P["category_attention.layers.fc0.bias"] = torch.zeros(A)
+    P["category_attention.layers.fc1.weight"] = torch.randn(H, A, generator=g) * math.sqrt(2.0 / A)
+    P["category_attention.layers.fc1.bias"] = torch.zeros(H)
+    for nm in ("mu_category_encoder", "logvar_category_encoder"):
+        P[nm + ".weight"], P[nm + ".bias"] = uni((Z, H), 1 / math.sqrt(H)), uni((Z,), 1 / math.sqrt(H))
+    P["t_decoder.weight"], P["t_decoder.bias"] = uni((H, Z), 1 / math.sqrt(Z)), uni((H,), 1 / math.sqrt(Z))
+    return P
+
+
 def lstm_iq_losses(P, feats, answers, alengths, questions, eps, eps2, lambdas=LAMBDAS, training=True, bn_state=None):
     """one combined training loss: lambda_gen*CE + lambda_z*KL + lambda_i*MSE_img + lambda_a*MSE_ans
     (old_train_iq.py:100-155: CE over non-pad targets of questions[:,1:], KL to the unit normal, reconstructions from the

@@ -179,3 +179,63 @@ def test_persistent_recurrence_matches_the_per_step_kernels(env, T, B, H, ragged
             assert rel(dgp, dgs) < 3e-3 and rel(dh0p, dh_run) < 3e-3 and rel(dc0p, dc) < 3e-3
     finally:
         _lib.lib().b200iq_set_tf32_rounding(prev)
+
+
+def test_category_space_matches_oracle_and_bit_exact_ids(env, golden_dir):
+    """SURVEY §8f rank 4 — the evaluate() / sampler call sequence of old_train_iq.py:134-142,194-213 and evaluate_iq.py:51-54:
+    encode_categories, encode_into_t, the two KL terms, predict_from_category / predict_from_answer (greedy ids bit-exact vs
+    the fp32 oracle in exact mode); the answer space's parameters and offsets are untouched by the extra blocks."""
+    from blt_vqg_b200 import _lib, ops
+    from blt_vqg_b200.lstm_iq import LSTMIQ
+    from oracle import lstm_oracle
+    gold = torch.load(os.path.join(golden_dir, "iq_lstm_tiny.pt"), weights_only=False)
+    b, cfg = gold["batch"], gold["cfg"]
+    sd = dict(gold["state_dict"])
+    sd["encoder_cnn.bn.running_mean"], sd["encoder_cnn.bn.running_var"] = gold["bn_running_mean_after"], gold["bn_running_var_after"]
+    lstm_oracle.add_category_space(sd, cfg, num_categories=16, seed=3)
+    m = LSTMIQ.from_config(cfg, no_category_space=False, num_categories=16).cuda()
+    missing, unexpected = m.load_state_dict(sd)
+    assert not missing and not unexpected
+    m.eval()
+    plain = _build(cfg, {k: v for k, v in sd.items() if "category" not in k and not k.startswith("t_decoder")})
+    for k, off in plain.arena.offsets.items():
+        assert m.arena.offsets[k] == off, k
+    with pytest.raises(_lib.B200iqError):
+        plain.encode_categories(torch.zeros(2, dtype=torch.long))
+    B = cfg["B"]
+    cats = torch.randint(0, 16, (B,), generator=torch.Generator().manual_seed(5))
+    P = sd
+    with torch.no_grad():
+        img_r = lstm_oracle.encode_images(P, b["feats"], training=False)
+        ans_r = lstm_oracle.encode_answers(P, b["answers"], b["alengths"])
+        mu_r, lv_r = lstm_oracle.encode_into_z(P, img_r, ans_r)
+        catf_r = lstm_oracle.encode_categories(P, cats)
+        tmu_r, tlv_r = lstm_oracle.encode_into_t(P, img_r, catf_r)
+        tkl_r = lstm_oracle.gaussian_kl_loss(tmu_r, tlv_r)
+        ztkl_r = lstm_oracle.compute_two_gaussian_loss(mu_r, lv_r, tmu_r, tlv_r)
+        ids_t_r = lstm_oracle.greedy_decode_from_t(P, img_r, tmu_r, 1, cfg["T"])
+        ids_z_r = lstm_oracle.greedy_decode(P, img_r, mu_r, 1, cfg["T"])
+    with ops.gemm_mode(simt=True):
+        img = m.encode_images(b["feats"])
+        ans = m.encode_answers(b["answers"], b["alengths"])
+        mus, logvars = m.encode_into_z(img, ans)
+        catf = m.encode_categories(cats)
+        t_mus, t_logvars = m.encode_into_t(img, catf)
+        t_kl = m.gaussian_KL_loss(t_mus, t_logvars)
+        z_t_kl = m.compute_two_gaussian_loss(mus, logvars, t_mus, t_logvars)
+        ids_t = m.predict_from_category(b["feats"], cats)
+        ids_z = m.predict_from_answer(b["feats"], b["answers"], b["alengths"])
+    assert torch.equal(catf.cpu(), catf_r)
+    assert rel(t_mus, tmu_r) < 1e-5 and rel(t_logvars, tlv_r) < 1e-5
+    assert float(t_kl) == pytest.approx(float(tkl_r), rel=1e-4)
+    assert float(z_t_kl) == pytest.approx(float(ztkl_r), rel=1e-4)
+    assert ids_t.shape == (B, cfg["T"]) and torch.equal(ids_t.cpu(), ids_t_r)
+    assert torch.equal(ids_z.cpu(), ids_z_r) and torch.equal(ids_z.cpu(), gold["greedy_ids"])
+    # tensor-core path: same quantities within the stated TF32 tolerance (losses 1e-3)
+    m.train()   # reparameterize samples in train mode: injected eps
+    eps = torch.randn(B, cfg["Z"], generator=torch.Generator().manual_seed(9))
+    t_mus2, t_logvars2 = m.encode_into_t(img, catf)
+    assert rel(t_mus2, tmu_r) < 5e-3 and rel(t_logvars2, tlv_r) < 5e-3
+    assert float(m.compute_two_gaussian_loss(mus, logvars, t_mus2, t_logvars2)) == pytest.approx(float(ztkl_r), rel=5e-3)
+    ts = m.reparameterize(t_mus, t_logvars, eps.cuda())
+    assert rel(ts, lstm_oracle.reparameterize(tmu_r, tlv_r, eps)) < 1e-3

@@ -62,3 +62,18 @@ def test_lstm_golden_regenerates_from_reference(golden_dir):
     for k in ("loss", "gen", "kl", "rec_i", "rec_a"):
         assert fresh["losses"][k] == pytest.approx(gold["losses"][k], rel=1e-6)
     assert torch.equal(fresh["greedy_ids"], gold["greedy_ids"])
+
+
+def test_category_space_oracle_kl_identities():
+    """compute_two_gaussian_loss against torch.distributions; KL(q || N(0,1)) equals gaussian_kl_loss"""
+    import torch.distributions as D
+    from oracle import lstm_oracle
+    g = torch.Generator().manual_seed(0)
+    mu1, lv1, mu2, lv2 = (torch.randn(6, 10, generator=g) for _ in range(4))
+    want = D.kl_divergence(D.Normal(mu1, (0.5 * lv1).exp()), D.Normal(mu2, (0.5 * lv2).exp())).sum() / 6
+    assert float(lstm_oracle.compute_two_gaussian_loss(mu1, lv1, mu2, lv2)) == pytest.approx(float(want), rel=1e-5)
+    z = torch.zeros_like(mu1)
+    assert float(lstm_oracle.compute_two_gaussian_loss(mu1, lv1, z, z)) == pytest.approx(float(lstm_oracle.gaussian_kl_loss(mu1, lv1)), rel=1e-5)
+    P = lstm_oracle.add_category_space({}, dict(H=32, Z=8, A=16), num_categories=16)
+    t_mu, t_lv = lstm_oracle.encode_into_t(P, torch.randn(3, 32, generator=g), lstm_oracle.encode_categories(P, torch.tensor([0, 15, 7])))
+    assert t_mu.shape == t_lv.shape == (3, 8)
