@@ -9,45 +9,33 @@ namespace b200iq {
 
 __device__ __forceinline__ float bf16_bits_to_float(uint32_t b) { return __uint_as_float(b << 16); }
 
-// out[b, :] = rn_tf32(float(cache[idx[b], :])); rows whose index is outside [0, num_images) become zeros and are counted.
-// Each thread moves UNR 16-byte pieces per trip: all row indices first, then all cache loads, then the stores — the
-// idx -> row dependent chain would otherwise leave one load in flight per thread (bf16 gather at 70 % of the store's rate).
+// out[b, :] = rn_tf32(float(cache[idx[b], :])); rows whose index is outside [0, num_images) become zeros and are counted
 template <bool BF16>
 __global__ void feature_gather_kernel(const void* __restrict__ cache, const int* __restrict__ idx, float* __restrict__ out,
                                       int B, int F, int num_images, int* __restrict__ bad, int rn) {
   constexpr int VEC = BF16 ? 8 : 4;                      // elements per 16-byte load
-  constexpr int UNR = 4;
   const int per_row = F / VEC;
-  const size_t total = (size_t)B * per_row, stride = (size_t)gridDim.x * blockDim.x;
-  for (size_t i0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < total; i0 += UNR * stride) {
-    int row[UNR], b[UNR], c[UNR];
-    uint4 q[UNR];
+  const size_t total = (size_t)B * per_row;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int b = (int)(i / per_row), c = (int)(i % per_row) * VEC;
+    const int row = __ldg(idx + b);
+    float v[VEC];
+    if (row < 0 || row >= num_images) {
 #pragma unroll
-    for (int u = 0; u < UNR; ++u) {
-      const size_t i = i0 + u * stride;
-      b[u] = i < total ? (int)(i / per_row) : -1;
-      c[u] = i < total ? (int)(i % per_row) * VEC : 0;
-      row[u] = b[u] >= 0 ? __ldg(idx + b[u]) : 0;
-    }
+      for (int u = 0; u < VEC; ++u) v[u] = 0.f;
+      if (c == 0 && bad) atomicAdd(bad, 1);
+    } else if (BF16) {
+      const uint4 q = __ldg(reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(cache) + (size_t)row * F + c));
+      const uint32_t w[4] = {q.x, q.y, q.z, q.w};
 #pragma unroll
-    for (int u = 0; u < UNR; ++u) {
-      const bool ok = b[u] >= 0 && row[u] >= 0 && row[u] < num_images;
-      q[u] = make_uint4(0u, 0u, 0u, 0u);
-      if (ok) q[u] = __ldg(reinterpret_cast<const uint4*>(static_cast<const char*>(cache) + ((size_t)row[u] * F + c[u]) * (BF16 ? 2 : 4)));
-      else if (b[u] >= 0 && c[u] == 0 && bad) atomicAdd(bad, 1);
+      for (int u = 0; u < 4; ++u) { v[2 * u] = bf16_bits_to_float(w[u] & 0xFFFFu); v[2 * u + 1] = bf16_bits_to_float(w[u] >> 16); }
+    } else {
+      const float4 q = __ldg(reinterpret_cast<const float4*>(static_cast<const float*>(cache) + (size_t)row * F + c));
+      v[0] = rnd(q.x, rn); v[1] = rnd(q.y, rn); v[2] = rnd(q.z, rn); v[3] = rnd(q.w, rn);   // a bf16 value is a TF32 value already
     }
+    float4* dst = reinterpret_cast<float4*>(out + (size_t)b * F + c);
 #pragma unroll
-    for (int u = 0; u < UNR; ++u) {
-      if (b[u] < 0) continue;
-      float4* dst = reinterpret_cast<float4*>(out + (size_t)b[u] * F + c[u]);
-      const uint32_t w[4] = {q[u].x, q[u].y, q[u].z, q[u].w};
-      if (BF16) {   // a bf16 value is a TF32 value already
-        dst[0] = make_float4(bf16_bits_to_float(w[0] & 0xFFFFu), bf16_bits_to_float(w[0] >> 16), bf16_bits_to_float(w[1] & 0xFFFFu), bf16_bits_to_float(w[1] >> 16));
-        dst[1] = make_float4(bf16_bits_to_float(w[2] & 0xFFFFu), bf16_bits_to_float(w[2] >> 16), bf16_bits_to_float(w[3] & 0xFFFFu), bf16_bits_to_float(w[3] >> 16));
-      } else {
-        dst[0] = make_float4(rnd(__uint_as_float(w[0]), rn), rnd(__uint_as_float(w[1]), rn), rnd(__uint_as_float(w[2]), rn), rnd(__uint_as_float(w[3]), rn));
-      }
-    }
+    for (int u = 0; u < VEC / 4; ++u) dst[u] = make_float4(v[4 * u], v[4 * u + 1], v[4 * u + 2], v[4 * u + 3]);
   }
 }
 
