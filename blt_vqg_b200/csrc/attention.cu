@@ -4,6 +4,7 @@
 //           dropout, PV, merge heads) and its autograd backward.
 // Semantics kept from the reference: the mask fill is the FINITE value -1e18, so a fully masked row
 // softmaxes to a uniform distribution, and masked positions receive no gradient.
+#include <type_traits>
 #include "common.cuh"
 
 namespace b200iq {
@@ -247,8 +248,9 @@ __device__ __forceinline__ void mma_pY_store(const float (&P)[MT][NT][4], const 
 }
 
 // softmax over j of the masked, scaled scores in C-fragment layout; S becomes P (pre-dropout). msk bit (nt*4+e) per mt.
-template <int MT, int NT>
-__device__ __forceinline__ void softmax_frag(const AttnArgs& a, float (&S)[MT][NT][4], uint32_t (&msk)[MT], int b, int g, int t) {
+// i0 = absolute index of the fragment's first query row (a warp of the row-block kernels owns rows i0 .. i0+15).
+template <int MT, int NT, class MaskT = uint32_t>
+__device__ __forceinline__ void softmax_frag(const AttnArgs& a, float (&S)[MT][NT][4], MaskT (&msk)[MT], int b, int g, int t, int i0 = 0) {
   bool padj[NT][2];
 #pragma unroll
   for (int nt = 0; nt < NT; ++nt)
@@ -262,7 +264,7 @@ __device__ __forceinline__ void softmax_frag(const AttnArgs& a, float (&S)[MT][N
     msk[mt] = 0;
 #pragma unroll
     for (int hh = 0; hh < 2; ++hh) {
-      const int i = 16 * mt + g + 8 * hh;
+      const int i = i0 + 16 * mt + g + 8 * hh;
       float mx = -3.0e38f;
 #pragma unroll
       for (int nt = 0; nt < NT; ++nt)
@@ -270,7 +272,7 @@ __device__ __forceinline__ void softmax_frag(const AttnArgs& a, float (&S)[MT][N
         for (int e = 0; e < 2; ++e) {
           const int j = 8 * nt + 2 * t + e;
           const bool m = (a.causal && j > i) || padj[nt][e];
-          if (m) msk[mt] |= 1u << (nt * 4 + 2 * hh + e);
+          if (m) msk[mt] |= (MaskT)1 << (nt * 4 + 2 * hh + e);
           float s = m ? -1e18f : S[mt][nt][2 * hh + e] * a.scale;
           if (j >= a.nk) s = -3.0e38f;
           S[mt][nt][2 * hh + e] = s;
@@ -447,6 +449,147 @@ attention_bwd_tc_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, flo
   mma_TtX_store<MT, NT>(Ws, dO, a.nq, ldo, dv + (size_t)b * a.nk * lddv + h * 64, a.nk, lddv, g, t, a.rn);   // dV = W^T . dO
 }
 
+// ---------------------------------------------------------------- row-block kernels: 32 < n <= 80 (cfg5: T = 64, R = 65)
+// One CTA per (sample, head), one WARP per 16 query rows; the warp keeps its 16 x nk slab of scores in registers
+// (NT <= 10 key tiles of 8).  Forward: warps are independent, no shared memory.  Backward: every warp writes its rows of
+// dS and of the post-dropout weights W into two CTA-wide shared tiles ([16*MT][ATT_LD]); after one barrier warp w owns the
+// 16 keys 16w .. 16w+15 and reduces dK = dS^T Q and dV = W^T dO over ALL query rows.  ATT_LD = 84: the transposed-operand
+// reads (rows 8s + 2t (+1), columns g / g + 8) then fall into 32 distinct banks (2 * 84 mod 32 = 8).
+static constexpr int ATT_LD = 84;
+static constexpr int ATT_ROWBLOCK_MAX = 80;
+
+template <int NT>
+__global__ void __launch_bounds__(160)
+attention_fwd_rows_kernel(AttnArgs a, float* __restrict__ out, int ldo) {
+  using MaskT = typename std::conditional<(NT > 8), unsigned long long, uint32_t>::type;
+  pdl_trigger();
+  pdl_wait();
+  const int bh = blockIdx.x, w = threadIdx.x >> 5, i0 = 16 * w;
+  if (i0 >= a.nq) return;
+  const int b = bh / a.nh, h = bh - b * a.nh, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  const float* Q = a.q + ((size_t)b * a.nq + i0) * a.ldq + h * 64;
+  const float* K = a.k + (size_t)b * a.bsk + h * 64;
+  const float* V = a.v + (size_t)b * a.bsv + h * 64;
+  float S[1][NT][4];
+#pragma unroll
+  for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+    for (int e = 0; e < 4; ++e) S[0][nt][e] = 0.f;
+  mma_xyT<1, NT>(S, Q, a.nq - i0, a.ldq, K, a.nk, a.ldk, g, t);
+  MaskT msk[1];
+  softmax_frag<1, NT, MaskT>(a, S, msk, b, g, t, i0);
+#pragma unroll
+  for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const int i = i0 + g + 8 * (e >> 1), j = 8 * nt + 2 * t + (e & 1);
+      float wgt = S[0][nt][e];
+      if (a.drop_p > 0.f && i < a.nq && j < a.nk) wgt *= keep_scale(a, ((size_t)bh * a.nq + i) * a.nk + j);
+      S[0][nt][e] = tf32_rn(wgt);
+    }
+  mma_pY_store<1, NT>(S, V, a.nk, a.ldv, out + ((size_t)b * a.nq + i0) * ldo + h * 64, a.nq - i0, ldo, g, t, a.rn);
+}
+
+// out[16mj + .., :64] = sum_{i < ni} T[i][j] * X[i, :64] for the 16 keys of block mj (rows j < nj are stored); T is a shared
+// tile [ni][ATT_LD] (ni a multiple of 8, columns up to 16*ceil(NT/2) readable).  Reduction slot t of k-step s is row 8s + 2t,
+// slot t + 4 is row 8s + 2t + 1, on both operands.
+__device__ __forceinline__ void mma_TtX_block_store(const float* T, int ni, int ncols, const float* X, int nx, int ldx, float* out,
+                                                    int mj, int nj, int ldo, int g, int t, int rn) {
+  const int j0 = 16 * mj + g, j1 = j0 + 8;
+#pragma unroll
+  for (int cq = 0; cq < 2; ++cq) {
+    float acc[4][4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) acc[u][e] = 0.f;
+    for (int s = 0; s < ni / 8; ++s) {
+      const int i = 8 * s + 2 * t;
+      const float4 x0 = ld4(X, i, nx, ldx, 32 * cq + 4 * g), x1 = ld4(X, i + 1, nx, ldx, 32 * cq + 4 * g);
+      const float* x0a = &x0.x; const float* x1a = &x1.x;
+      const float a0 = T[i * ATT_LD + j0], a2 = T[(i + 1) * ATT_LD + j0];
+      const float a1 = (j1 < ncols) ? T[i * ATT_LD + j1] : 0.f, a3 = (j1 < ncols) ? T[(i + 1) * ATT_LD + j1] : 0.f;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) mma_tf32(acc[u], a0, a1, a2, a3, x0a[u], x1a[u]);
+    }
+#pragma unroll
+    for (int hh = 0; hh < 2; ++hh) {
+      const int row = 16 * mj + g + 8 * hh;
+      if (row < nj) {
+        float4* dst = reinterpret_cast<float4*>(out + (size_t)row * ldo + 32 * cq + 8 * t);
+        dst[0] = make_float4(rnd(acc[0][2 * hh], rn), rnd(acc[1][2 * hh], rn), rnd(acc[2][2 * hh], rn), rnd(acc[3][2 * hh], rn));
+        dst[1] = make_float4(rnd(acc[0][2 * hh + 1], rn), rnd(acc[1][2 * hh + 1], rn), rnd(acc[2][2 * hh + 1], rn), rnd(acc[3][2 * hh + 1], rn));
+      }
+    }
+  }
+}
+
+template <int NT>
+__global__ void __launch_bounds__(160)
+attention_bwd_rows_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, float* __restrict__ dq, float* __restrict__ dk,
+                          float* __restrict__ dv, int lddq, int lddk, int lddv) {
+  using MaskT = typename std::conditional<(NT > 8), unsigned long long, uint32_t>::type;
+  extern __shared__ float rows_sm[];
+  pdl_trigger();
+  pdl_wait();
+  const int mtiles = (a.nq + 15) / 16, ni = 16 * mtiles;
+  float* Ws = rows_sm;
+  float* Ds = rows_sm + (size_t)ni * ATT_LD;
+  const int bh = blockIdx.x, w = threadIdx.x >> 5, i0 = 16 * w;
+  const int b = bh / a.nh, h = bh - b * a.nh, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  const float* Qh = a.q + (size_t)b * a.nq * a.ldq + h * 64;
+  const float* K = a.k + (size_t)b * a.bsk + h * 64;
+  const float* V = a.v + (size_t)b * a.bsv + h * 64;
+  const float* dOh = dout + (size_t)b * a.nq * ldo + h * 64;
+  if (w < mtiles) {
+    float S[1][NT][4], dW[1][NT][4];
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) { S[0][nt][e] = 0.f; dW[0][nt][e] = 0.f; }
+    mma_xyT<1, NT>(S, Qh + (size_t)i0 * a.ldq, a.nq - i0, a.ldq, K, a.nk, a.ldk, g, t);     // scores
+    mma_xyT<1, NT>(dW, dOh + (size_t)i0 * ldo, a.nq - i0, ldo, V, a.nk, a.ldv, g, t);       // d(post-dropout weights) = dO . V^T
+    MaskT msk[1];
+    softmax_frag<1, NT, MaskT>(a, S, msk, b, g, t, i0);
+#pragma unroll
+    for (int hh = 0; hh < 2; ++hh) {
+      const int i = i0 + g + 8 * hh;
+      float ks[NT][2], dot = 0.f;
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const int j = 8 * nt + 2 * t + e;
+          ks[nt][e] = (a.drop_p > 0.f && i < a.nq && j < a.nk) ? keep_scale(a, ((size_t)bh * a.nq + i) * a.nk + j) : 1.f;
+          const float dP = dW[0][nt][2 * hh + e] * ks[nt][e];
+          dW[0][nt][2 * hh + e] = dP;
+          dot += dP * S[0][nt][2 * hh + e];
+        }
+      dot += __shfl_xor_sync(0xffffffffu, dot, 1);
+      dot += __shfl_xor_sync(0xffffffffu, dot, 2);
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const int j = 8 * nt + 2 * t + e, idx = 2 * hh + e;
+          const float p = S[0][nt][idx];
+          const bool m = (msk[0] >> (nt * 4 + idx)) & 1u;
+          const float ds = (m || i >= a.nq) ? 0.f : tf32_rn(p * (dW[0][nt][idx] - dot) * a.scale);
+          const float wgt = (i >= a.nq) ? 0.f : tf32_rn(p * ks[nt][e]);
+          S[0][nt][idx] = ds;
+          Ws[i * ATT_LD + j] = wgt;
+          Ds[i * ATT_LD + j] = ds;
+        }
+    }
+    mma_pY_store<1, NT>(S, K, a.nk, a.ldk, dq + ((size_t)b * a.nq + i0) * lddq + h * 64, a.nq - i0, lddq, g, t, a.rn);   // dQ = dS . K
+  }
+  __syncthreads();
+  if (16 * w < a.nk) {
+    mma_TtX_block_store(Ds, ni, 8 * NT, Qh, a.nq, a.ldq, dk + (size_t)b * a.nk * lddk + h * 64, w, a.nk, lddk, g, t, a.rn);  // dK = dS^T . Q
+    mma_TtX_block_store(Ws, ni, 8 * NT, dOh, a.nq, ldo, dv + (size_t)b * a.nk * lddv + h * 64, w, a.nk, lddv, g, t, a.rn);   // dV = W^T . dO
+  }
+}
+
 static int check_attn(const B200iqAttention* p) {
   B200IQ_CHECK_ARG(p && p->q && p->k && p->v, "attention: null pointer");
   B200IQ_CHECK_ARG(p->B > 0 && p->num_heads > 0 && p->nq > 0 && p->nk > 0 && p->head_dim > 0, "attention: bad shape");
@@ -472,6 +615,20 @@ static bool tc_ok(const B200iqAttention* p, const void* const* ptrs, int nptr, c
   for (int i = 0; i < nld; ++i) if (lds[i] & 3) return false;
   return true;
 }
+// the row-block kernels: anything the register-resident kernels above do not take, up to 80 x 80
+static bool rows_ok(const B200iqAttention* p, const void* const* ptrs, int nptr, const int* lds, int nld) {
+  if (!round_mode() || p->head_dim != 64 || p->nq > ATT_ROWBLOCK_MAX || p->nk > ATT_ROWBLOCK_MAX) return false;
+  for (int i = 0; i < nptr; ++i) if (((uintptr_t)ptrs[i]) & 15) return false;
+  for (int i = 0; i < nld; ++i) if (lds[i] & 3) return false;
+  return true;
+}
+#define B200IQ_ATT_ROWS_DISPATCH(NT_, CALL) \
+  do { \
+    switch (NT_) { \
+      case 1: CALL(1); break; case 2: CALL(2); break; case 3: CALL(3); break; case 4: CALL(4); break; case 5: CALL(5); break; \
+      case 6: CALL(6); break; case 7: CALL(7); break; case 8: CALL(8); break; case 9: CALL(9); break; default: CALL(10); break; \
+    } \
+  } while (0)
 #define B200IQ_ATT_DISPATCH(MT_, NT_, CALL) \
   do { \
     if (MT_ == 1) { if (NT_ == 1) { CALL(1, 1); } else if (NT_ == 2) { CALL(1, 2); } else if (NT_ == 3) { CALL(1, 3); } else { CALL(1, 4); } } \
@@ -493,6 +650,13 @@ extern "C" int b200iq_attention_fwd(const B200iqAttention* p, void* stream) {
       B200IQ_ATT_DISPATCH(mt, nt, CALL);
 #undef CALL
       return launch_status("attention_fwd_tc");
+    }
+    if (rows_ok(p, ptrs, 4, lds, 4)) {
+      const int nt = (a.nk + 7) / 8, warps = (a.nq + 15) / 16;
+#define CALL(N_) launch_dep(attention_fwd_rows_kernel<N_>, dim3(a.B * a.nh), dim3(32 * warps), 0, (cudaStream_t)stream, a, p->out, p->ldo)
+      B200IQ_ATT_ROWS_DISPATCH(nt, CALL);
+#undef CALL
+      return launch_status("attention_fwd_rows");
     }
   }
   size_t smem = sizeof(float) * ((size_t)(a.nq + 2 * a.nk) * (a.d + 1) + (ATT_THREADS / 32) * a.nk);
@@ -517,6 +681,18 @@ extern "C" int b200iq_attention_bwd(const B200iqAttention* p, const float* dout,
       B200IQ_ATT_DISPATCH(mt, nt, CALL);
 #undef CALL
       return launch_status("attention_bwd_tc");
+    }
+    if (rows_ok(p, ptrs, 7, lds, 7)) {
+      const int nt = (a.nk + 7) / 8, mtiles = (a.nq + 15) / 16, jtiles = (a.nk + 15) / 16, warps = mtiles > jtiles ? mtiles : jtiles;
+      const size_t smem = sizeof(float) * 2 * (size_t)(16 * mtiles) * ATT_LD;
+#define CALL(N_) \
+  do { \
+    if (smem > 48 * 1024) cudaFuncSetAttribute(attention_bwd_rows_kernel<N_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+    launch_dep(attention_bwd_rows_kernel<N_>, dim3(a.B * a.nh), dim3(32 * warps), smem, (cudaStream_t)stream, a, dout, p->ldo, dq, dk, dv, lddq, lddk, lddv); \
+  } while (0)
+      B200IQ_ATT_ROWS_DISPATCH(nt, CALL);
+#undef CALL
+      return launch_status("attention_bwd_rows");
     }
   }
   size_t smem = sizeof(float) * ((size_t)(2 * a.nq + 2 * a.nk) * (a.d + 1) + 2 * (size_t)a.nq * (a.nk + 1));

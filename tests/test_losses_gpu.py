@@ -85,7 +85,10 @@ def test_attention_dropout_is_consistent_between_fwd_and_bwd(ops):
             assert fd == pytest.approx(float(g[idx]), rel=2e-2, abs=2e-3)
 
 
-@pytest.mark.parametrize("nq,nk,causal", [(5, 5, False), (21, 21, False), (20, 20, True), (20, 5, False), (32, 32, True), (1, 1, True), (17, 9, False)])
+@pytest.mark.parametrize("nq,nk,causal", [(5, 5, False), (21, 21, False), (20, 20, True), (20, 5, False), (32, 32, True), (1, 1, True), (17, 9, False),
+                                             # 32 < n <= 80: the row-block kernels (cfg5: T = 64, R = 65, S = 5)
+                                             (64, 64, True), (65, 65, False), (64, 5, False), (5, 64, False), (80, 80, True), (33, 40, False),
+                                             (48, 33, True), (72, 80, False)])
 @pytest.mark.parametrize("drop", [0.0, 0.3])
 def test_attention_tensor_core_path(ops, nq, nk, causal, drop):
     """head_dim 64 with TF32 rounding on -> the warp-per-head mma.sync kernels; checked against torch autograd (drop=0) and
@@ -114,7 +117,7 @@ def test_attention_tensor_core_path(ops, nq, nk, causal, drop):
     exact = run()                                   # rounding off: SIMT kernels
     prev = _lib.lib().b200iq_set_tf32_rounding(1)
     try:
-        tc = run()                                  # rounding on + d=64 + n<=32: tensor-core kernels
+        tc = run()                                  # rounding on + d=64: tensor-core kernels (n <= 32 in registers, n <= 80 row blocks)
     finally:
         _lib.lib().b200iq_set_tf32_rounding(prev)
     for a, b in zip(tc, exact):
