@@ -48,6 +48,8 @@ CONFIGS = {
     # cfg3's widths (head_dim 64, H=512, F=2048, V=15000, T=20) at 2 layers and a small batch: the production kernel variants
     # (CTA-pair GEMM, tensor-core attention, warp-per-row LayerNorm, chunked vocabulary CE) against the host oracle in seconds
     "wide": dict(B=24, V=15000, E=300, H=512, L=100, F=2048, NL=2, NH=8, T=20, S=5, FEAT=2048),
+    # cfg5's widths (V = 32000, T = 64, R = 65: the row-block attention kernels, 20 logits chunks) at 2 layers and a small batch
+    "long": dict(B=8, V=32000, E=300, H=512, L=100, F=2048, NL=2, NH=8, T=64, S=5, FEAT=2048),
     # BASELINE.json configs[0] sizes on the transformer variant
     "cfg1": dict(B=32, V=5000, E=300, H=512, L=100, F=2048, NL=6, NH=8, T=20, S=5, FEAT=2048),
     # BASELINE.json configs[2]: the single-GPU transformer workload the metric is quoted on
