@@ -4,6 +4,7 @@
 //           dropout, PV, merge heads) and its autograd backward.
 // Semantics kept from the reference: the mask fill is the FINITE value -1e18, so a fully masked row
 // softmaxes to a uniform distribution, and masked positions receive no gradient.
+#include <stdlib.h>
 #include <type_traits>
 #include "common.cuh"
 
@@ -212,9 +213,10 @@ __device__ __forceinline__ void mma_xyT(float (&acc)[MT][NT][4], const float* X,
 
 // out[16mt.., :64] = P . Y with P[mt][nt] in C-fragment layout (rows i, cols j) and Y[j, :64] in global memory (rows >= ny zero).
 // Lane (g,t) ends up with 8 contiguous output floats per row and 32-column block: cols 32cq + 8t .. +7.
+// With PLO != nullptr the left operand is P + PLO (two TF32 terms: see the dQ product of the backward kernels).
 template <int MT, int NT>
 __device__ __forceinline__ void mma_pY_store(const float (&P)[MT][NT][4], const float* Y, int ny, int ldy, float* out, int nrows,
-                                             int ldo, int g, int t, int rn) {
+                                             int ldo, int g, int t, int rn, const float (*PLO)[NT][4] = nullptr) {
 #pragma unroll
   for (int cq = 0; cq < 2; ++cq) {
     float acc[MT][4][4];
@@ -231,7 +233,10 @@ __device__ __forceinline__ void mma_pY_store(const float (&P)[MT][NT][4], const 
 #pragma unroll
       for (int mt = 0; mt < MT; ++mt)
 #pragma unroll
-        for (int u = 0; u < 4; ++u) mma_tf32(acc[mt][u], P[mt][nt][0], P[mt][nt][2], P[mt][nt][1], P[mt][nt][3], y0a[u], y1a[u]);
+        for (int u = 0; u < 4; ++u) {
+          mma_tf32(acc[mt][u], P[mt][nt][0], P[mt][nt][2], P[mt][nt][1], P[mt][nt][3], y0a[u], y1a[u]);
+          if (PLO != nullptr) mma_tf32(acc[mt][u], PLO[mt][nt][0], PLO[mt][nt][2], PLO[mt][nt][1], PLO[mt][nt][3], y0a[u], y1a[u]);
+        }
     }
 #pragma unroll
     for (int mt = 0; mt < MT; ++mt)
@@ -436,15 +441,20 @@ attention_bwd_tc_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, flo
           const int j = 8 * nt + 2 * t + e, idx = 2 * hh + e;
           const float p = S[mt][nt][idx];
           const bool m = (msk[mt] >> (nt * 4 + idx)) & 1u;
-          const float ds = (m || i >= a.nq) ? 0.f : tf32_rn(p * (dW[mt][nt][idx] - dot) * a.scale);
+          const float dsf = (m || i >= a.nq) ? 0.f : p * (dW[mt][nt][idx] - dot) * a.scale;
+          const float ds = tf32_rn(dsf);
           const float w = (i >= a.nq) ? 0.f : tf32_rn(p * ks[nt][e]);
           S[mt][nt][idx] = ds;
+          dW[mt][nt][idx] = tf32_rn(dsf - ds);   // low-order term of dS, used by the dQ product only
           Ws[i * 33 + j] = w;
           Ds[i * 33 + j] = ds;
         }
     }
   __syncwarp();
-  mma_pY_store<MT, NT>(S, K, a.nk, a.ldk, dq + (size_t)b * a.nq * lddq + h * 64, a.nq, lddq, g, t, a.rn);   // dQ = dS . K
+  // dQ = dS . K with dS as TWO TF32 terms: every row of dS sums to zero, so when the keys share a large common component (LayerNorm
+  // + a bias-free projection at initialisation) the product cancels it and the 2^-11 rounding of a single-term dS is what is left
+  // (measured 7e-3 of |dQ|, scripts/gpu_attention_err.py; 3e-4 with the second term)
+  mma_pY_store<MT, NT>(S, K, a.nk, a.ldk, dq + (size_t)b * a.nq * lddq + h * 64, a.nq, lddq, g, t, a.rn, dW);
   mma_TtX_store<MT, NT>(Ds, Q, a.nq, a.ldq, dk + (size_t)b * a.nk * lddk + h * 64, a.nk, lddk, g, t, a.rn);  // dK = dS^T . Q
   mma_TtX_store<MT, NT>(Ws, dO, a.nq, ldo, dv + (size_t)b * a.nk * lddv + h * 64, a.nk, lddv, g, t, a.rn);   // dV = W^T . dO
 }
@@ -574,14 +584,16 @@ attention_bwd_rows_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, f
           const int j = 8 * nt + 2 * t + e, idx = 2 * hh + e;
           const float p = S[0][nt][idx];
           const bool m = (msk[0] >> (nt * 4 + idx)) & 1u;
-          const float ds = (m || i >= a.nq) ? 0.f : tf32_rn(p * (dW[0][nt][idx] - dot) * a.scale);
+          const float dsf = (m || i >= a.nq) ? 0.f : p * (dW[0][nt][idx] - dot) * a.scale;
+          const float ds = tf32_rn(dsf);
           const float wgt = (i >= a.nq) ? 0.f : tf32_rn(p * ks[nt][e]);
           S[0][nt][idx] = ds;
+          dW[0][nt][idx] = tf32_rn(dsf - ds);    // low-order term of dS for the dQ product (see attention_bwd_tc_kernel)
           Ws[i * ATT_LD + j] = wgt;
           Ds[i * ATT_LD + j] = ds;
         }
     }
-    mma_pY_store<1, NT>(S, K, a.nk, a.ldk, dq + ((size_t)b * a.nq + i0) * lddq + h * 64, a.nq - i0, lddq, g, t, a.rn);   // dQ = dS . K
+    mma_pY_store<1, NT>(S, K, a.nk, a.ldk, dq + ((size_t)b * a.nq + i0) * lddq + h * 64, a.nq - i0, lddq, g, t, a.rn, dW);   // dQ = (dS + dS_lo) . K
   }
   __syncthreads();
   if (16 * w < a.nk) {
@@ -609,7 +621,13 @@ static AttnArgs to_args(const B200iqAttention* p) {
   return a;
 }
 
+// B200IQ_ATT_SIMT=1: every attention call takes the exact SIMT kernels (A/B switch for numerics / timing experiments)
+static bool att_force_simt() {
+  static const int v = [] { const char* e = getenv("B200IQ_ATT_SIMT"); return (e && e[0] == '1') ? 1 : 0; }();
+  return v != 0;
+}
 static bool tc_ok(const B200iqAttention* p, const void* const* ptrs, int nptr, const int* lds, int nld) {
+  if (att_force_simt()) return false;
   if (!round_mode() || p->head_dim != 64 || p->nq > 32 || p->nk > 32) return false;
   for (int i = 0; i < nptr; ++i) if (((uintptr_t)ptrs[i]) & 15) return false;
   for (int i = 0; i < nld; ++i) if (lds[i] & 3) return false;
@@ -617,6 +635,7 @@ static bool tc_ok(const B200iqAttention* p, const void* const* ptrs, int nptr, c
 }
 // the row-block kernels: anything the register-resident kernels above do not take, up to 80 x 80
 static bool rows_ok(const B200iqAttention* p, const void* const* ptrs, int nptr, const int* lds, int nld) {
+  if (att_force_simt()) return false;
   if (!round_mode() || p->head_dim != 64 || p->nq > ATT_ROWBLOCK_MAX || p->nk > ATT_ROWBLOCK_MAX) return false;
   for (int i = 0; i < nptr; ++i) if (((uintptr_t)ptrs[i]) & 15) return false;
   for (int i = 0; i < nld; ++i) if (lds[i] & 3) return false;
