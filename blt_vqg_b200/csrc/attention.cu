@@ -513,14 +513,29 @@ __device__ __forceinline__ void mma_TtX_block_store(const float* T, int ni, int 
     for (int u = 0; u < 4; ++u)
 #pragma unroll
       for (int e = 0; e < 4; ++e) acc[u][e] = 0.f;
-    for (int s = 0; s < ni / 8; ++s) {
-      const int i = 8 * s + 2 * t;
-      const float4 x0 = ld4(X, i, nx, ldx, 32 * cq + 4 * g), x1 = ld4(X, i + 1, nx, ldx, 32 * cq + 4 * g);
-      const float* x0a = &x0.x; const float* x1a = &x1.x;
-      const float a0 = T[i * ATT_LD + j0], a2 = T[(i + 1) * ATT_LD + j0];
-      const float a1 = (j1 < ncols) ? T[i * ATT_LD + j1] : 0.f, a3 = (j1 < ncols) ? T[(i + 1) * ATT_LD + j1] : 0.f;
+    // the rows of X come straight from global memory: 5 k-steps of loads are issued before the first MMA needs one (a warp that
+    // waits for every pair of loads in turn spends the kernel in L2 latency: 10 trips x 2 products x 2 column halves)
+    constexpr int PF = 5;
+    const int ns = ni / 8;
+    for (int s0 = 0; s0 < ns; s0 += PF) {
+      float4 x0[PF], x1[PF];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) mma_tf32(acc[u], a0, a1, a2, a3, x0a[u], x1a[u]);
+      for (int p = 0; p < PF; ++p) {
+        const int i = 8 * (s0 + p) + 2 * t;      // rows >= nx (and every row of a k-step >= ns) read as zero
+        x0[p] = ld4(X, i, nx, ldx, 32 * cq + 4 * g);
+        x1[p] = ld4(X, i + 1, nx, ldx, 32 * cq + 4 * g);
+      }
+#pragma unroll
+      for (int p = 0; p < PF; ++p) {
+        if (s0 + p < ns) {
+          const int i = 8 * (s0 + p) + 2 * t;
+          const float* x0a = &x0[p].x; const float* x1a = &x1[p].x;
+          const float a0 = T[i * ATT_LD + j0], a2 = T[(i + 1) * ATT_LD + j0];
+          const float a1 = (j1 < ncols) ? T[i * ATT_LD + j1] : 0.f, a3 = (j1 < ncols) ? T[(i + 1) * ATT_LD + j1] : 0.f;
+#pragma unroll
+          for (int u = 0; u < 4; ++u) mma_tf32(acc[u], a0, a1, a2, a3, x0a[u], x1a[u]);
+        }
+      }
     }
 #pragma unroll
     for (int hh = 0; hh < 2; ++hh) {
@@ -535,7 +550,7 @@ __device__ __forceinline__ void mma_TtX_block_store(const float* T, int ni, int 
 }
 
 template <int NT>
-__global__ void __launch_bounds__(160)
+__global__ void __launch_bounds__(160, 2)
 attention_bwd_rows_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, float* __restrict__ dq, float* __restrict__ dk,
                           float* __restrict__ dv, int lddq, int lddk, int lddv) {
   using MaskT = typename std::conditional<(NT > 8), unsigned long long, uint32_t>::type;
