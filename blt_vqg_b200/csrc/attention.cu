@@ -22,6 +22,7 @@ struct AttnArgs {
   float scale, drop_p;
   uint64_t seed, offset;
   int rn;  // round outputs to TF32
+  int dq2; // backward: dQ = (dS + dS_lo) . K, dS as two TF32 terms (B200IQ_ATT_DQ2, default 1)
   size_t bsk, bsv;  // elements between consecutive samples' K / V blocks (nk*ldk, nk*ldv unless reading a KV cache)
 };
 
@@ -454,7 +455,7 @@ attention_bwd_tc_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, flo
   // dQ = dS . K with dS as TWO TF32 terms: every row of dS sums to zero, so when the keys share a large common component (LayerNorm
   // + a bias-free projection at initialisation) the product cancels it and the 2^-11 rounding of a single-term dS is what is left
   // (measured 7e-3 of |dQ|, scripts/gpu_attention_err.py; 3e-4 with the second term)
-  mma_pY_store<MT, NT>(S, K, a.nk, a.ldk, dq + (size_t)b * a.nq * lddq + h * 64, a.nq, lddq, g, t, a.rn, dW);
+  mma_pY_store<MT, NT>(S, K, a.nk, a.ldk, dq + (size_t)b * a.nq * lddq + h * 64, a.nq, lddq, g, t, a.rn, a.dq2 ? dW : nullptr);
   mma_TtX_store<MT, NT>(Ds, Q, a.nq, a.ldq, dk + (size_t)b * a.nk * lddk + h * 64, a.nk, lddk, g, t, a.rn);  // dK = dS^T . Q
   mma_TtX_store<MT, NT>(Ws, dO, a.nq, ldo, dv + (size_t)b * a.nk * lddv + h * 64, a.nk, lddv, g, t, a.rn);   // dV = W^T . dO
 }
@@ -608,7 +609,7 @@ attention_bwd_rows_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, f
           Ds[i * ATT_LD + j] = ds;
         }
     }
-    mma_pY_store<1, NT>(S, K, a.nk, a.ldk, dq + ((size_t)b * a.nq + i0) * lddq + h * 64, a.nq - i0, lddq, g, t, a.rn, dW);   // dQ = (dS + dS_lo) . K
+    mma_pY_store<1, NT>(S, K, a.nk, a.ldk, dq + ((size_t)b * a.nq + i0) * lddq + h * 64, a.nq - i0, lddq, g, t, a.rn, a.dq2 ? dW : nullptr);   // dQ = (dS + dS_lo) . K
   }
   __syncthreads();
   if (16 * w < a.nk) {
@@ -631,6 +632,8 @@ static AttnArgs to_args(const B200iqAttention* p) {
   a.B = p->B; a.nh = p->num_heads; a.nq = p->nq; a.nk = p->nk; a.d = p->head_dim;
   a.scale = p->scale; a.drop_p = p->drop_p; a.seed = p->seed; a.offset = p->offset;
   a.rn = round_mode();
+  static const int dq2 = [] { const char* e = getenv("B200IQ_ATT_DQ2"); return (e && e[0] == '0') ? 0 : 1; }();
+  a.dq2 = dq2;
   a.bsk = p->kv_batch_stride > 0 ? (size_t)p->kv_batch_stride : (size_t)p->nk * p->ldk;
   a.bsv = p->kv_batch_stride > 0 ? (size_t)p->kv_batch_stride : (size_t)p->nk * p->ldv;
   return a;
