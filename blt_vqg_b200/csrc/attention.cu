@@ -26,13 +26,23 @@ struct AttnArgs {
   size_t bsk, bsv;  // elements between consecutive samples' K / V blocks (nk*ldk, nk*ldv unless reading a KV cache)
 };
 
-__device__ __forceinline__ float keep_scale(const AttnArgs& a, size_t elem) {
+// The attention-dropout mask: the 8 keys j = 8c .. 8c+7 of score row `row` (= (sample*heads + head)*nq + i) share ONE call of
+// Philox4x32-7(seed; counter = offset + row*ceil(nk/8) + c, 1): key j takes 16 bits — word (j >> 1) & 3, upper half when j & 1 —
+// and is kept when they are >= round(65536 p) (the feed-forward mask's recipe, common.cuh).  A lane of the tensor-core kernels
+// owns keys 2t, 2t+1 of every 8-key tile of its rows: one call per (row, tile) instead of a 10-round call per element, which
+// was most of the instruction stream of these kernels (5.5 k instructions per warp, ncu profiles/r01k_attention_fwd_rows.txt).
+__device__ __forceinline__ void att_drop_words(const AttnArgs& a, size_t row, int tile, uint32_t (&w)[4]) {
+  const uint64_t ctr = a.offset + row * (uint64_t)((a.nk + 7) >> 3) + (uint64_t)tile;
+  Philox(a.seed).rounds<7>((uint32_t)ctr, (uint32_t)(ctr >> 32), 1u, 0u, w);
+}
+__device__ __forceinline__ float att_keep(const uint32_t (&w)[4], int j, uint32_t thr, float inv) {
+  return (((w[(j >> 1) & 3] >> ((j & 1) << 4)) & 0xFFFFu) >= thr) ? inv : 0.f;
+}
+__device__ __forceinline__ float keep_scale(const AttnArgs& a, size_t row, int j) {
   if (a.drop_p <= 0.f) return 1.f;
-  Philox ph(a.seed);
-  uint32_t r[4];
-  uint64_t ctr = a.offset + (elem >> 2);
-  ph((uint32_t)ctr, (uint32_t)(ctr >> 32), 1u, 0u, r);
-  return (u32_to_unit(r[elem & 3]) > a.drop_p) ? 1.f / (1.f - a.drop_p) : 0.f;
+  uint32_t w[4];
+  att_drop_words(a, row, j >> 3, w);
+  return att_keep(w, j, dropout_threshold(a.drop_p), 1.f / (1.f - a.drop_p));
 }
 
 // softmax row for query i; lane owns keys j = lane + 32*jj.  Returns p[] (pre-dropout) and the mask bits.
@@ -97,7 +107,7 @@ attention_fwd_kernel(AttnArgs a, float* __restrict__ out, int ldo) {
 #pragma unroll
     for (int jj = 0; jj < ATT_MAXJ; ++jj) {
       int j = lane + 32 * jj;
-      if (j < a.nk) Pw[j] = p[jj] * keep_scale(a, ((size_t)blockIdx.x * a.nq + i) * a.nk + j);
+      if (j < a.nk) Pw[j] = p[jj] * keep_scale(a, (size_t)blockIdx.x * a.nq + i, j);
     }
     __syncwarp();
     float* orow = out + ((size_t)b * a.nq + i) * ldo + h * a.d;
@@ -136,7 +146,7 @@ attention_bwd_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, float*
       int j = lane + 32 * jj;
       dP[jj] = 0.f;
       if (j < a.nk) {
-        float ks = keep_scale(a, ((size_t)blockIdx.x * a.nq + i) * a.nk + j);
+        float ks = keep_scale(a, (size_t)blockIdx.x * a.nq + i, j);
         float g = 0.f;
         const float* dor = dOs + i * dp;
         const float* vr = Vs + j * dp;
@@ -335,11 +345,17 @@ attention_fwd_tc_kernel(AttnArgs a, float* __restrict__ out, int ldo) {
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt)
 #pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        const int i = 16 * mt + g + 8 * (e >> 1), j = 8 * nt + 2 * t + (e & 1);
-        float w = S[mt][nt][e];
-        if (a.drop_p > 0.f && i < a.nq && j < a.nk) w *= keep_scale(a, ((size_t)bh * a.nq + i) * a.nk + j);
-        S[mt][nt][e] = tf32_rn(w);
+      for (int hh = 0; hh < 2; ++hh) {
+        const int i = 16 * mt + g + 8 * hh;
+        uint32_t dw[4];
+        if (a.drop_p > 0.f) att_drop_words(a, (size_t)bh * a.nq + i, nt, dw);
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const int j = 8 * nt + 2 * t + e;
+          float w = S[mt][nt][2 * hh + e];
+          if (a.drop_p > 0.f && i < a.nq && j < a.nk) w *= att_keep(dw, j, dropout_threshold(a.drop_p), 1.f / (1.f - a.drop_p));
+          S[mt][nt][2 * hh + e] = tf32_rn(w);
+        }
       }
   mma_pY_store<MT, NT>(S, V, a.nk, a.ldv, out + (size_t)b * a.nq * ldo + h * 64, a.nq, ldo, g, t, a.rn);
 }
@@ -424,15 +440,18 @@ attention_bwd_tc_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, flo
       const int i = 16 * mt + g + 8 * hh;
       float ks[NT][2], dot = 0.f;
 #pragma unroll
-      for (int nt = 0; nt < NT; ++nt)
+      for (int nt = 0; nt < NT; ++nt) {
+        uint32_t dw[4];
+        if (a.drop_p > 0.f) att_drop_words(a, (size_t)bh * a.nq + i, nt, dw);
 #pragma unroll
         for (int e = 0; e < 2; ++e) {
           const int j = 8 * nt + 2 * t + e;
-          ks[nt][e] = (a.drop_p > 0.f && i < a.nq && j < a.nk) ? keep_scale(a, ((size_t)bh * a.nq + i) * a.nk + j) : 1.f;
+          ks[nt][e] = (a.drop_p > 0.f && i < a.nq && j < a.nk) ? att_keep(dw, j, dropout_threshold(a.drop_p), 1.f / (1.f - a.drop_p)) : 1.f;
           const float dP = dW[mt][nt][2 * hh + e] * ks[nt][e];
           dW[mt][nt][2 * hh + e] = dP;
           dot += dP * S[mt][nt][2 * hh + e];
         }
+      }
       dot += __shfl_xor_sync(0xffffffffu, dot, 1);
       dot += __shfl_xor_sync(0xffffffffu, dot, 2);
 #pragma unroll
@@ -492,11 +511,17 @@ attention_fwd_rows_kernel(AttnArgs a, float* __restrict__ out, int ldo) {
 #pragma unroll
   for (int nt = 0; nt < NT; ++nt)
 #pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      const int i = i0 + g + 8 * (e >> 1), j = 8 * nt + 2 * t + (e & 1);
-      float wgt = S[0][nt][e];
-      if (a.drop_p > 0.f && i < a.nq && j < a.nk) wgt *= keep_scale(a, ((size_t)bh * a.nq + i) * a.nk + j);
-      S[0][nt][e] = tf32_rn(wgt);
+    for (int hh = 0; hh < 2; ++hh) {
+      const int i = i0 + g + 8 * hh;
+      uint32_t dw[4];
+      if (a.drop_p > 0.f) att_drop_words(a, (size_t)bh * a.nq + i, nt, dw);
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        const int j = 8 * nt + 2 * t + e;
+        float wgt = S[0][nt][2 * hh + e];
+        if (a.drop_p > 0.f && i < a.nq && j < a.nk) wgt *= att_keep(dw, j, dropout_threshold(a.drop_p), 1.f / (1.f - a.drop_p));
+        S[0][nt][2 * hh + e] = tf32_rn(wgt);
+      }
     }
   mma_pY_store<1, NT>(S, V, a.nk, a.ldv, out + ((size_t)b * a.nq + i0) * ldo + h * 64, a.nq - i0, ldo, g, t, a.rn);
 }
@@ -582,15 +607,18 @@ attention_bwd_rows_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, f
       const int i = i0 + g + 8 * hh;
       float ks[NT][2], dot = 0.f;
 #pragma unroll
-      for (int nt = 0; nt < NT; ++nt)
+      for (int nt = 0; nt < NT; ++nt) {
+        uint32_t dw[4];
+        if (a.drop_p > 0.f) att_drop_words(a, (size_t)bh * a.nq + i, nt, dw);
 #pragma unroll
         for (int e = 0; e < 2; ++e) {
           const int j = 8 * nt + 2 * t + e;
-          ks[nt][e] = (a.drop_p > 0.f && i < a.nq && j < a.nk) ? keep_scale(a, ((size_t)bh * a.nq + i) * a.nk + j) : 1.f;
+          ks[nt][e] = (a.drop_p > 0.f && i < a.nq && j < a.nk) ? att_keep(dw, j, dropout_threshold(a.drop_p), 1.f / (1.f - a.drop_p)) : 1.f;
           const float dP = dW[0][nt][2 * hh + e] * ks[nt][e];
           dW[0][nt][2 * hh + e] = dP;
           dot += dP * S[0][nt][2 * hh + e];
         }
+      }
       dot += __shfl_xor_sync(0xffffffffu, dot, 1);
       dot += __shfl_xor_sync(0xffffffffu, dot, 2);
 #pragma unroll

@@ -134,7 +134,9 @@ typedef struct B200iqAttention {
   int causal;            /* 1: key j > query i is masked (transformer_layers.py:207) */
   int B, num_heads, nq, nk, head_dim;
   float scale;           /* head_dim^-0.5 (transformer_layers.py:449,499) */
-  float drop_p;          /* attention dropout (transformer_layers.py:520); mask = Philox(seed, offset) */
+  float drop_p;          /* attention dropout (transformer_layers.py:520); key j of score row r = (b*heads + h)*nq + i is kept when 16 bits
+                            of Philox4x32-7(seed; counter = offset + r*ceil(nk/8) + j/8, 1) — word (j >> 1) & 3, upper half when
+                            j & 1 — are >= round(65536 p) */
   uint64_t seed, offset;
   long long kv_batch_stride; /* elements between consecutive samples' K (and V) blocks; 0 = nk*ldk / nk*ldv (dense [B*nk, ld]).
                                 A KV cache [B, max_len, H] read at length nk passes max_len*H here (forward only). */
