@@ -77,3 +77,34 @@ def test_category_space_oracle_kl_identities():
     P = lstm_oracle.add_category_space({}, dict(H=32, Z=8, A=16), num_categories=16)
     t_mu, t_lv = lstm_oracle.encode_into_t(P, torch.randn(3, 32, generator=g), lstm_oracle.encode_categories(P, torch.tensor([0, 15, 7])))
     assert t_mu.shape == t_lv.shape == (3, 8)
+
+
+def test_category_space_arena_is_appended_behind_the_answer_space(golden_dir):
+    """host logic (no device): the category-space parameters carry the upstream key names, sit behind the answer space in the flat
+    arena (answer-space offsets and checkpoints do not move), and round-trip through state_dict / load_state_dict"""
+    from blt_vqg_b200.lstm_iq import LSTMIQ
+    gold = torch.load(os.path.join(golden_dir, "iq_lstm_tiny.pt"), weights_only=False)
+    cfg = gold["cfg"]
+    plain = LSTMIQ.from_config(cfg)
+    full = LSTMIQ.from_config(cfg, no_category_space=False, num_categories=16)
+    for k, off in plain.arena.offsets.items():
+        assert full.arena.offsets[k] == off, k
+    extra = [k for k in full.state_dict() if k not in plain.state_dict()]
+    assert sorted(extra) == sorted([
+        "category_encoder.weight", "category_attention.layers.fc0.weight", "category_attention.layers.fc0.bias",
+        "category_attention.layers.fc1.weight", "category_attention.layers.fc1.bias", "mu_category_encoder.weight",
+        "mu_category_encoder.bias", "logvar_category_encoder.weight", "logvar_category_encoder.bias", "t_decoder.weight", "t_decoder.bias"])
+    off_of = lambda k: full.arena.offsets.get(k + "#pack", full.arena.offsets.get(k))   # packed [mu | logvar] operands carry a #pack mark
+    assert min(off_of(k) for k in extra) >= plain.flat.numel() - 64
+    sd = lstm_oracle.add_category_space(dict(gold["state_dict"]), cfg, num_categories=16, seed=3)
+    missing, unexpected = full.load_state_dict(sd)
+    assert not missing and not unexpected
+    out = full.state_dict()
+    for k in extra:
+        assert torch.equal(out[k], sd[k]), k
+    # the answer-space golden weights load into the plain model unchanged
+    missing, unexpected = plain.load_state_dict(gold["state_dict"])
+    assert not missing and not unexpected
+    from blt_vqg_b200 import _lib
+    with pytest.raises(_lib.B200iqError):
+        plain.encode_categories(torch.zeros(2, dtype=torch.long))
