@@ -328,7 +328,7 @@ def measure(args, cfg, config, dp, rank, world, local_rank, roofline=True, cpu_a
         b = rb[i % len(rb)]
         sb = stager.stage(b, image_rows=b["rows"]).wait()
         x = step_inputs(args.workload, {"feats": sb.image_rows, "answers": sb.answers, "posteriors": sb.posteriors,
-                                        "questions": sb.questions, "alengths": hb[i % len(hb)]["alengths"]})
+                                        "questions": sb.questions, "alengths": sb.alengths})
         terms = ts.step(*x)
         sb.done()
         staged_bytes.append(sb.h2d_bytes)

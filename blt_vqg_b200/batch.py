@@ -23,6 +23,9 @@ from . import _lib, ops
 
 # the order the token tensors take inside the block (context first: the encoder starts with it)
 TOKEN_KEYS = ("answers", "answer_types_for_input", "posteriors", "questions")
+# per-sample integers that ride in the same block: answer lengths (utils/train_utils.py:127-141 process_lengths, the LSTM variant's
+# `alengths`) and the category label (`answer_types`, utils/data_loader.py:165)
+VECTOR_KEYS = ("alengths", "answer_types")
 
 
 class StagedBatch:
@@ -67,13 +70,15 @@ def _grow(buf, n, **kw):
 
 
 def token_layout(shapes):
-    """offsets (in int32 elements, each tensor 16-byte aligned) of the token tensors inside one block: {key: (offset, B, n)}"""
+    """offsets (in int32 elements, each tensor 16-byte aligned) of the token tensors inside one block: {key: (offset, B, n)};
+    the (B,) vectors of VECTOR_KEYS follow the (B, n) tensors of TOKEN_KEYS and are listed with n = 0"""
     off, out = 0, {}
-    for k in TOKEN_KEYS:
+    for k in TOKEN_KEYS + VECTOR_KEYS:
         if k in shapes:
-            B, n = shapes[k]
+            shp = tuple(shapes[k])
+            B, n = (shp[0], 0) if len(shp) == 1 else shp
             out[k] = (off, B, n)
-            off += (B * n + 3) // 4 * 4
+            off += (B * max(n, 1) + 3) // 4 * 4
     return out, off
 
 
@@ -88,16 +93,16 @@ class BatchStager:
         self.n = 0
 
     def stage(self, batch, feats=None, image_rows=None):
-        """batch: dict with any of TOKEN_KEYS (int64 or int32 CPU tensors, as utils/data_loader.py:162-166 builds them).
+        """batch: dict with any of TOKEN_KEYS / VECTOR_KEYS (int64 or int32 CPU tensors, as utils/data_loader.py:162-166 builds them).
         feats: optional (B, FEAT) float CPU tensor of pooled features; image_rows: optional (B,) integer CPU tensor of
         FeatureCache rows.  Returns a StagedBatch; call `.wait()` before the first kernel and `.done()` after the last."""
         s = self.slots[self.n % len(self.slots)]
         self.n += 1
-        toks = {k: batch[k] for k in TOKEN_KEYS if k in batch and batch[k] is not None}
+        toks = {k: batch[k] for k in TOKEN_KEYS + VECTOR_KEYS if k in batch and batch[k] is not None}
         for k, t in toks.items():
-            if t.is_cuda or t.dim() != 2 or t.dtype not in (torch.int64, torch.int32):
-                raise _lib.B200iqError("BatchStager: %s must be a (B, n) int64/int32 CPU tensor, got %s %s on %s"
-                                       % (k, tuple(t.shape), t.dtype, t.device))
+            if t.is_cuda or t.dim() != (1 if k in VECTOR_KEYS else 2) or t.dtype not in (torch.int64, torch.int32):
+                raise _lib.B200iqError("BatchStager: %s must be a %s int64/int32 CPU tensor, got %s %s on %s"
+                                       % (k, "(B,)" if k in VECTOR_KEYS else "(B, n)", tuple(t.shape), t.dtype, t.device))
         layout, n_ids = token_layout({k: tuple(t.shape) for k, t in toks.items()})
         n_rows = 0 if image_rows is None else int(image_rows.numel())
         total = n_ids + (n_rows + 3) // 4 * 4
@@ -106,7 +111,7 @@ class BatchStager:
         s.pinned_ids = _grow(s.pinned_ids, total, dtype=torch.int32, pin_memory=True)
         s.dev_ids = _grow(s.dev_ids, total, dtype=torch.int32, device=self.device)
         for k, (off, B, n) in layout.items():
-            s.pinned_ids[off:off + B * n].view(B, n).copy_(toks[k])     # narrows int64 -> int32 on the way in
+            s.pinned_ids[off:off + B * max(n, 1)].view(toks[k].shape).copy_(toks[k])     # narrows int64 -> int32 on the way in
         if n_rows:
             s.pinned_ids[n_ids:n_ids + n_rows].copy_(image_rows.reshape(-1))
         h2d = total * 4
@@ -127,7 +132,7 @@ class BatchStager:
                 s.dev_f[:nf].copy_(s.pinned_f[:nf], non_blocking=True)
             s.copied.record(self.stream)
         s.used, s.has_consumed = True, False
-        views = {k: s.dev_ids[off:off + B * n].view(B, n) for k, (off, B, n) in layout.items()}
+        views = {k: s.dev_ids[off:off + B * max(n, 1)].view((B, n) if n else (B,)) for k, (off, B, n) in layout.items()}
         rows = s.dev_ids[n_ids:n_ids + n_rows] if n_rows else None
         f = s.dev_f[:feats.numel()].view(feats.shape) if feats is not None else None
         return StagedBatch(s, views, f, rows, h2d)

@@ -15,6 +15,10 @@ def test_token_layout_is_packed_in_key_order_and_16_byte_aligned():
     assert total % 4 == 0 and total >= end
     lay2, total2 = token_layout({"questions": (7, 20)})
     assert lay2 == {"questions": (0, 7, 20)} and total2 == 140
+    # per-sample vectors (answer lengths, category labels) follow the token tensors
+    lay3, total3 = token_layout({"alengths": (7,), "questions": (7, 20), "answer_types": (7,)})
+    assert list(lay3) == ["questions", "alengths", "answer_types"]
+    assert lay3["alengths"] == (140, 7, 0) and lay3["answer_types"] == (148, 7, 0) and total3 == 156
 
 
 def test_input_pipeline_has_no_cpu_fallback():

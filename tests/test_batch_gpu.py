@@ -79,7 +79,10 @@ def test_stager_views_match_the_batch_dict(env):
     staged, batches = [], []
     for i in range(5):                                   # 5 steps through 2 slots
         b = synth.make_batch(cfg, seed=100 + i, B=13)    # int64, like the reference's collate_fn
+        b["answer_types"] = b["answer_types_for_input"][:, 1].contiguous()       # (B,) category labels, data_loader.py:165
         s = st.stage(b, feats=b["feats"], image_rows=torch.arange(13)).wait()
+        assert torch.equal(s.alengths.cpu(), b["alengths"].int()) and s.alengths.shape == (13,)
+        assert torch.equal(s.answer_types.cpu(), b["answer_types"].int())
         for k in TOKEN_KEYS:
             assert s.tokens[k].dtype == torch.int32 and torch.equal(s.tokens[k].cpu(), b[k].int()), (i, k)
             assert s.tokens[k].data_ptr() % 16 == 0
