@@ -6,9 +6,49 @@
 // softmaxes to a uniform distribution, and masked positions receive no gradient.
 #include <stdlib.h>
 #include <type_traits>
+#include <cuda_fp16.h>
 #include "common.cuh"
 
 namespace b200iq {
+
+// where a kernel's result rows go: fp32 (f32 != NULL) or fp16 planes hi (+ lo) for the next GEMM (gemm_f16.cu); ld in elements
+struct AttOut { float* f32; __half* hi; __half* lo; int ld; };
+__device__ __forceinline__ AttOut att_out_at(const AttOut& o, size_t off) {
+  AttOut r = o;
+  if (r.f32) r.f32 += off;
+  if (r.hi) r.hi += off;
+  if (r.lo) r.lo += off;
+  return r;
+}
+__device__ __forceinline__ void att_store1(const AttOut& o, size_t idx, float v, int rn) {
+  if (o.hi) {
+    const __half h = __float2half_rn(v);
+    o.hi[idx] = h;
+    if (o.lo) o.lo[idx] = __float2half_rn(v - __half2float(h));
+  } else {
+    o.f32[idx] = rnd(v, rn);
+  }
+}
+// 8 consecutive elements of one row (idx a multiple of 8 for planes / of 4 for fp32)
+__device__ __forceinline__ void att_store8(const AttOut& o, size_t idx, const float (&v)[8], int rn) {
+  if (o.hi) {
+    uint32_t hb[4], lb[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const __half2 h = __floats2half2_rn(v[2 * j], v[2 * j + 1]);
+      hb[j] = *reinterpret_cast<const uint32_t*>(&h);
+      const float2 f = __half22float2(h);
+      const __half2 l = __floats2half2_rn(v[2 * j] - f.x, v[2 * j + 1] - f.y);
+      lb[j] = *reinterpret_cast<const uint32_t*>(&l);
+    }
+    *reinterpret_cast<uint4*>(o.hi + idx) = make_uint4(hb[0], hb[1], hb[2], hb[3]);
+    if (o.lo) *reinterpret_cast<uint4*>(o.lo + idx) = make_uint4(lb[0], lb[1], lb[2], lb[3]);
+  } else {
+    float4* dst = reinterpret_cast<float4*>(o.f32 + idx);
+    dst[0] = make_float4(rnd(v[0], rn), rnd(v[1], rn), rnd(v[2], rn), rnd(v[3], rn));
+    dst[1] = make_float4(rnd(v[4], rn), rnd(v[5], rn), rnd(v[6], rn), rnd(v[7], rn));
+  }
+}
 
 static constexpr int ATT_THREADS = 128;
 static constexpr int ATT_MAXJ = 4;  // keys per lane -> nk <= 128
@@ -88,7 +128,8 @@ __device__ __forceinline__ void load_tile(float* dst, const float* src, int rows
 }
 
 __global__ void __launch_bounds__(ATT_THREADS)
-attention_fwd_kernel(AttnArgs a, float* __restrict__ out, int ldo) {
+attention_fwd_kernel(AttnArgs a, AttOut out) {
+  const int ldo = out.ld;
   extern __shared__ float sm[];
   const int b = blockIdx.x / a.nh, h = blockIdx.x % a.nh, dp = a.d + 1;
   float* Qs = sm;
@@ -110,19 +151,19 @@ attention_fwd_kernel(AttnArgs a, float* __restrict__ out, int ldo) {
       if (j < a.nk) Pw[j] = p[jj] * keep_scale(a, (size_t)blockIdx.x * a.nq + i, j);
     }
     __syncwarp();
-    float* orow = out + ((size_t)b * a.nq + i) * ldo + h * a.d;
+    const size_t orow = ((size_t)b * a.nq + i) * ldo + h * a.d;
     for (int c = lane; c < a.d; c += 32) {
       float o = 0.f;
       for (int j = 0; j < a.nk; ++j) o = fmaf(Pw[j], Vs[j * dp + c], o);
-      orow[c] = rnd(o, a.rn);
+      att_store1(out, orow + c, o, a.rn);
     }
     __syncwarp();
   }
 }
 
 __global__ void __launch_bounds__(ATT_THREADS)
-attention_bwd_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, float* __restrict__ dq, float* __restrict__ dk,
-                     float* __restrict__ dv, int lddq, int lddk, int lddv) {
+attention_bwd_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, AttOut dq, AttOut dk, AttOut dv) {
+  const int lddq = dq.ld, lddk = dk.ld, lddv = dv.ld;
   extern __shared__ float sm[];
   const int b = blockIdx.x / a.nh, h = blockIdx.x % a.nh, dp = a.d + 1, np = a.nk + 1;
   float* Qs = sm;
@@ -168,7 +209,7 @@ attention_bwd_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, float*
     int i = idx / a.d, c = idx - i * a.d;
     float s = 0.f;
     for (int j = 0; j < a.nk; ++j) s = fmaf(dSs[i * np + j], Ks[j * dp + c], s);
-    dq[((size_t)b * a.nq + i) * lddq + h * a.d + c] = rnd(s, a.rn);
+    att_store1(dq, ((size_t)b * a.nq + i) * lddq + h * a.d + c, s, a.rn);
   }
   for (int idx = threadIdx.x; idx < a.nk * a.d; idx += blockDim.x) {
     int j = idx / a.d, c = idx - j * a.d;
@@ -177,8 +218,8 @@ attention_bwd_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, float*
       sk = fmaf(dSs[i * np + j], Qs[i * dp + c], sk);
       sv = fmaf(Ws[i * np + j], dOs[i * dp + c], sv);
     }
-    dk[((size_t)b * a.nk + j) * lddk + h * a.d + c] = rnd(sk, a.rn);
-    dv[((size_t)b * a.nk + j) * lddv + h * a.d + c] = rnd(sv, a.rn);
+    att_store1(dk, ((size_t)b * a.nk + j) * lddk + h * a.d + c, sk, a.rn);
+    att_store1(dv, ((size_t)b * a.nk + j) * lddv + h * a.d + c, sv, a.rn);
   }
 }
 
@@ -201,8 +242,14 @@ __device__ __forceinline__ float4 ld4(const float* base, int row, int nrows, int
   return make_float4(0.f, 0.f, 0.f, 0.f);
 }
 
+// The operands arrive as unrounded fp32 and mma.sync TRUNCATES to TF32, so every operand is split in registers:
+// hi = round-to-nearest TF32, lo = x - hi (exact; its own truncation is a 2^-22 effect).
+__device__ __forceinline__ float4 hi4(float4 v) { return make_float4(tf32_rn(v.x), tf32_rn(v.y), tf32_rn(v.z), tf32_rn(v.w)); }
+__device__ __forceinline__ float4 sub4(float4 a, float4 b) { return make_float4(a.x - b.x, a.y - b.y, a.z - b.z, a.w - b.w); }
+
 // acc[mt][nt] += X[16mt.., :64] . Y[8nt.., :64]^T   (both K-major in global memory; rows beyond nx / ny read as zero)
-template <int MT, int NT>
+// TERMS = 1: hi.hi (operands rounded to nearest);  TERMS = 3: hi.hi + lo.hi + hi.lo (~2^-21: the forward products)
+template <int MT, int NT, int TERMS>
 __device__ __forceinline__ void mma_xyT(float (&acc)[MT][NT][4], const float* X, int nx, int ldx, const float* Y, int ny, int ldy,
                                         int g, int t) {
 #pragma unroll
@@ -212,10 +259,29 @@ __device__ __forceinline__ void mma_xyT(float (&acc)[MT][NT][4], const float* X,
     for (int mt = 0; mt < MT; ++mt) { xa[mt] = ld4(X, 16 * mt + g, nx, ldx, 16 * kk + 4 * t); xb[mt] = ld4(X, 16 * mt + g + 8, nx, ldx, 16 * kk + 4 * t); }
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt) yf[nt] = ld4(Y, 8 * nt + g, ny, ldy, 16 * kk + 4 * t);
+    float4 xal[MT], xbl[MT], yl[NT];
+#pragma unroll
+    for (int mt = 0; mt < MT; ++mt) {
+      const float4 ah = hi4(xa[mt]), bh = hi4(xb[mt]);
+      if (TERMS == 3) { xal[mt] = sub4(xa[mt], ah); xbl[mt] = sub4(xb[mt], bh); }
+      xa[mt] = ah; xb[mt] = bh;
+    }
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) {
+      const float4 yh = hi4(yf[nt]);
+      if (TERMS == 3) yl[nt] = sub4(yf[nt], yh);
+      yf[nt] = yh;
+    }
 #pragma unroll
     for (int mt = 0; mt < MT; ++mt)
 #pragma unroll
       for (int nt = 0; nt < NT; ++nt) {
+        if (TERMS == 3) {
+          mma_tf32(acc[mt][nt], xal[mt].x, xbl[mt].x, xal[mt].y, xbl[mt].y, yf[nt].x, yf[nt].y);
+          mma_tf32(acc[mt][nt], xal[mt].z, xbl[mt].z, xal[mt].w, xbl[mt].w, yf[nt].z, yf[nt].w);
+          mma_tf32(acc[mt][nt], xa[mt].x, xb[mt].x, xa[mt].y, xb[mt].y, yl[nt].x, yl[nt].y);
+          mma_tf32(acc[mt][nt], xa[mt].z, xb[mt].z, xa[mt].w, xb[mt].w, yl[nt].z, yl[nt].w);
+        }
         mma_tf32(acc[mt][nt], xa[mt].x, xb[mt].x, xa[mt].y, xb[mt].y, yf[nt].x, yf[nt].y);
         mma_tf32(acc[mt][nt], xa[mt].z, xb[mt].z, xa[mt].w, xb[mt].w, yf[nt].z, yf[nt].w);
       }
@@ -225,9 +291,12 @@ __device__ __forceinline__ void mma_xyT(float (&acc)[MT][NT][4], const float* X,
 // out[16mt.., :64] = P . Y with P[mt][nt] in C-fragment layout (rows i, cols j) and Y[j, :64] in global memory (rows >= ny zero).
 // Lane (g,t) ends up with 8 contiguous output floats per row and 32-column block: cols 32cq + 8t .. +7.
 // With PLO != nullptr the left operand is P + PLO (two TF32 terms: see the dQ product of the backward kernels).
-template <int MT, int NT>
-__device__ __forceinline__ void mma_pY_store(const float (&P)[MT][NT][4], const float* Y, int ny, int ldy, float* out, int nrows,
-                                             int ldo, int g, int t, int rn, const float (*PLO)[NT][4] = nullptr) {
+// Y is rounded to nearest here; P (and PLO) must hold TF32 values.  TERMS = 3 adds the P.Y_lo term (with P = hi, PLO = lo of the
+// attention weights this is the forward's 3-term P.V).
+template <int MT, int NT, int TERMS>
+__device__ __forceinline__ void mma_pY_store(const float (&P)[MT][NT][4], const float* Y, int ny, int ldy, const AttOut& out, int nrows,
+                                             int g, int t, int rn, const float (*PLO)[NT][4] = nullptr) {
+  const int ldo = out.ld;
 #pragma unroll
   for (int cq = 0; cq < 2; ++cq) {
     float acc[MT][4][4];
@@ -239,14 +308,18 @@ __device__ __forceinline__ void mma_pY_store(const float (&P)[MT][NT][4], const 
         for (int e = 0; e < 4; ++e) acc[mt][u][e] = 0.f;
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt) {
-      const float4 y0 = ld4(Y, 8 * nt + 2 * t, ny, ldy, 32 * cq + 4 * g), y1 = ld4(Y, 8 * nt + 2 * t + 1, ny, ldy, 32 * cq + 4 * g);
+      const float4 y0f = ld4(Y, 8 * nt + 2 * t, ny, ldy, 32 * cq + 4 * g), y1f = ld4(Y, 8 * nt + 2 * t + 1, ny, ldy, 32 * cq + 4 * g);
+      const float4 y0 = hi4(y0f), y1 = hi4(y1f);
+      const float4 y0l = sub4(y0f, y0), y1l = sub4(y1f, y1);
       const float* y0a = &y0.x; const float* y1a = &y1.x;
+      const float* y0b = &y0l.x; const float* y1b = &y1l.x;
 #pragma unroll
       for (int mt = 0; mt < MT; ++mt)
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
-          mma_tf32(acc[mt][u], P[mt][nt][0], P[mt][nt][2], P[mt][nt][1], P[mt][nt][3], y0a[u], y1a[u]);
+          if (TERMS == 3) mma_tf32(acc[mt][u], P[mt][nt][0], P[mt][nt][2], P[mt][nt][1], P[mt][nt][3], y0b[u], y1b[u]);
           if (PLO != nullptr) mma_tf32(acc[mt][u], PLO[mt][nt][0], PLO[mt][nt][2], PLO[mt][nt][1], PLO[mt][nt][3], y0a[u], y1a[u]);
+          mma_tf32(acc[mt][u], P[mt][nt][0], P[mt][nt][2], P[mt][nt][1], P[mt][nt][3], y0a[u], y1a[u]);
         }
     }
 #pragma unroll
@@ -255,9 +328,9 @@ __device__ __forceinline__ void mma_pY_store(const float (&P)[MT][NT][4], const 
       for (int hh = 0; hh < 2; ++hh) {
         const int row = 16 * mt + g + 8 * hh;
         if (row < nrows) {
-          float4* dst = reinterpret_cast<float4*>(out + (size_t)row * ldo + 32 * cq + 8 * t);
-          dst[0] = make_float4(rnd(acc[mt][0][2 * hh], rn), rnd(acc[mt][1][2 * hh], rn), rnd(acc[mt][2][2 * hh], rn), rnd(acc[mt][3][2 * hh], rn));
-          dst[1] = make_float4(rnd(acc[mt][0][2 * hh + 1], rn), rnd(acc[mt][1][2 * hh + 1], rn), rnd(acc[mt][2][2 * hh + 1], rn), rnd(acc[mt][3][2 * hh + 1], rn));
+          const float v[8] = {acc[mt][0][2 * hh], acc[mt][1][2 * hh], acc[mt][2][2 * hh], acc[mt][3][2 * hh],
+                              acc[mt][0][2 * hh + 1], acc[mt][1][2 * hh + 1], acc[mt][2][2 * hh + 1], acc[mt][3][2 * hh + 1]};
+          att_store8(out, (size_t)row * ldo + 32 * cq + 8 * t, v, rn);
         }
       }
   }
@@ -321,7 +394,8 @@ static constexpr int ATT_TC_WARPS = 4;
 
 template <int MT, int NT>
 __global__ void __launch_bounds__(ATT_TC_WARPS * 32)
-attention_fwd_tc_kernel(AttnArgs a, float* __restrict__ out, int ldo) {
+attention_fwd_tc_kernel(AttnArgs a, AttOut out) {
+  const int ldo = out.ld;
   pdl_trigger();
   pdl_wait();
   const int bh = blockIdx.x * ATT_TC_WARPS + (threadIdx.x >> 5);
@@ -337,9 +411,10 @@ attention_fwd_tc_kernel(AttnArgs a, float* __restrict__ out, int ldo) {
     for (int nt = 0; nt < NT; ++nt)
 #pragma unroll
       for (int e = 0; e < 4; ++e) S[mt][nt][e] = 0.f;
-  mma_xyT<MT, NT>(S, Q, a.nq, a.ldq, K, a.nk, a.ldk, g, t);
+  mma_xyT<MT, NT, 3>(S, Q, a.nq, a.ldq, K, a.nk, a.ldk, g, t);
   uint32_t msk[MT];
   softmax_frag<MT, NT>(a, S, msk, b, g, t);
+  float SL[MT][NT][4];   // low-order TF32 term of the attention weights (3-term P.V)
 #pragma unroll
   for (int mt = 0; mt < MT; ++mt)
 #pragma unroll
@@ -354,18 +429,21 @@ attention_fwd_tc_kernel(AttnArgs a, float* __restrict__ out, int ldo) {
           const int j = 8 * nt + 2 * t + e;
           float w = S[mt][nt][2 * hh + e];
           if (a.drop_p > 0.f && i < a.nq && j < a.nk) w *= att_keep(dw, j, dropout_threshold(a.drop_p), 1.f / (1.f - a.drop_p));
-          S[mt][nt][2 * hh + e] = tf32_rn(w);
+          const float wh = tf32_rn(w);
+          S[mt][nt][2 * hh + e] = wh;
+          SL[mt][nt][2 * hh + e] = w - wh;
         }
       }
-  mma_pY_store<MT, NT>(S, V, a.nk, a.ldv, out + (size_t)b * a.nq * ldo + h * 64, a.nq, ldo, g, t, a.rn);
+  mma_pY_store<MT, NT, 3>(S, V, a.nk, a.ldv, att_out_at(out, (size_t)b * a.nq * ldo + h * 64), a.nq, g, t, a.rn, SL);
 }
 
 // out[j, :64] = sum_i T[i][j] * X[i, :64] for j < nj, with T ([32][33] floats, rows i, written by this warp in C layout)
 // used as the TRANSPOSED A operand.  Reduction slot t of k-step s is i = 4*MT*t + 2s (slot t+4: i+1), which makes the
 // shared-memory reads of a fragment hit 32 distinct banks for MT = 2.
 template <int MT, int NT>
-__device__ __forceinline__ void mma_TtX_store(const float* T, const float* X, int nx, int ldx, float* out, int nj, int ldo,
+__device__ __forceinline__ void mma_TtX_store(const float* T, const float* X, int nx, int ldx, const AttOut& out, int nj,
                                               int g, int t, int rn) {
+  const int ldo = out.ld;
   constexpr int MTJ = (NT + 1) / 2;
 #pragma unroll
   for (int cq = 0; cq < 2; ++cq) {
@@ -379,7 +457,7 @@ __device__ __forceinline__ void mma_TtX_store(const float* T, const float* X, in
 #pragma unroll
     for (int s = 0; s < 2 * MT; ++s) {
       const int i = 4 * MT * t + 2 * s;
-      const float4 x0 = ld4(X, i, nx, ldx, 32 * cq + 4 * g), x1 = ld4(X, i + 1, nx, ldx, 32 * cq + 4 * g);
+      const float4 x0 = hi4(ld4(X, i, nx, ldx, 32 * cq + 4 * g)), x1 = hi4(ld4(X, i + 1, nx, ldx, 32 * cq + 4 * g));
       const float* x0a = &x0.x; const float* x1a = &x1.x;
 #pragma unroll
       for (int mj = 0; mj < MTJ; ++mj) {
@@ -396,9 +474,9 @@ __device__ __forceinline__ void mma_TtX_store(const float* T, const float* X, in
       for (int hh = 0; hh < 2; ++hh) {
         const int row = 16 * mj + g + 8 * hh;
         if (row < nj) {
-          float4* dst = reinterpret_cast<float4*>(out + (size_t)row * ldo + 32 * cq + 8 * t);
-          dst[0] = make_float4(rnd(acc[mj][0][2 * hh], rn), rnd(acc[mj][1][2 * hh], rn), rnd(acc[mj][2][2 * hh], rn), rnd(acc[mj][3][2 * hh], rn));
-          dst[1] = make_float4(rnd(acc[mj][0][2 * hh + 1], rn), rnd(acc[mj][1][2 * hh + 1], rn), rnd(acc[mj][2][2 * hh + 1], rn), rnd(acc[mj][3][2 * hh + 1], rn));
+          const float v[8] = {acc[mj][0][2 * hh], acc[mj][1][2 * hh], acc[mj][2][2 * hh], acc[mj][3][2 * hh],
+                              acc[mj][0][2 * hh + 1], acc[mj][1][2 * hh + 1], acc[mj][2][2 * hh + 1], acc[mj][3][2 * hh + 1]};
+          att_store8(out, (size_t)row * ldo + 32 * cq + 8 * t, v, rn);
         }
       }
   }
@@ -406,8 +484,8 @@ __device__ __forceinline__ void mma_TtX_store(const float* T, const float* X, in
 
 template <int MT, int NT>
 __global__ void __launch_bounds__(ATT_TC_WARPS * 32)
-attention_bwd_tc_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, float* __restrict__ dq, float* __restrict__ dk,
-                        float* __restrict__ dv, int lddq, int lddk, int lddv) {
+attention_bwd_tc_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, AttOut dq, AttOut dk, AttOut dv) {
+  const int lddq = dq.ld, lddk = dk.ld, lddv = dv.ld;
   __shared__ float tsm[ATT_TC_WARPS][2][32 * 33];
   pdl_trigger();
   pdl_wait();
@@ -426,8 +504,8 @@ attention_bwd_tc_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, flo
     for (int nt = 0; nt < NT; ++nt)
 #pragma unroll
       for (int e = 0; e < 4; ++e) { S[mt][nt][e] = 0.f; dW[mt][nt][e] = 0.f; }
-  mma_xyT<MT, NT>(S, Q, a.nq, a.ldq, K, a.nk, a.ldk, g, t);      // scores
-  mma_xyT<MT, NT>(dW, dO, a.nq, ldo, V, a.nk, a.ldv, g, t);      // d(post-dropout weights) = dO . V^T
+  mma_xyT<MT, NT, 3>(S, Q, a.nq, a.ldq, K, a.nk, a.ldk, g, t);   // scores: the forward's 3-term product, so P is the forward's P
+  mma_xyT<MT, NT, 1>(dW, dO, a.nq, ldo, V, a.nk, a.ldv, g, t);   // d(post-dropout weights) = dO . V^T
   uint32_t msk[MT];
   softmax_frag<MT, NT>(a, S, msk, b, g, t);
   float* Ws = tsm[wid][0];
@@ -474,9 +552,9 @@ attention_bwd_tc_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, flo
   // dQ = dS . K with dS as TWO TF32 terms: every row of dS sums to zero, so when the keys share a large common component (LayerNorm
   // + a bias-free projection at initialisation) the product cancels it and the 2^-11 rounding of a single-term dS is what is left
   // (measured 7e-3 of |dQ|, scripts/gpu_attention_err.py; 3e-4 with the second term)
-  mma_pY_store<MT, NT>(S, K, a.nk, a.ldk, dq + (size_t)b * a.nq * lddq + h * 64, a.nq, lddq, g, t, a.rn, a.dq2 ? dW : nullptr);
-  mma_TtX_store<MT, NT>(Ds, Q, a.nq, a.ldq, dk + (size_t)b * a.nk * lddk + h * 64, a.nk, lddk, g, t, a.rn);  // dK = dS^T . Q
-  mma_TtX_store<MT, NT>(Ws, dO, a.nq, ldo, dv + (size_t)b * a.nk * lddv + h * 64, a.nk, lddv, g, t, a.rn);   // dV = W^T . dO
+  mma_pY_store<MT, NT, 1>(S, K, a.nk, a.ldk, att_out_at(dq, (size_t)b * a.nq * lddq + h * 64), a.nq, g, t, a.rn, a.dq2 ? dW : nullptr);
+  mma_TtX_store<MT, NT>(Ds, Q, a.nq, a.ldq, att_out_at(dk, (size_t)b * a.nk * lddk + h * 64), a.nk, g, t, a.rn);  // dK = dS^T . Q
+  mma_TtX_store<MT, NT>(Ws, dO, a.nq, ldo, att_out_at(dv, (size_t)b * a.nk * lddv + h * 64), a.nk, g, t, a.rn);   // dV = W^T . dO
 }
 
 // ---------------------------------------------------------------- row-block kernels: 32 < n <= 80 (cfg5: T = 64, R = 65)
@@ -490,7 +568,8 @@ static constexpr int ATT_ROWBLOCK_MAX = 80;
 
 template <int NT>
 __global__ void __launch_bounds__(160)
-attention_fwd_rows_kernel(AttnArgs a, float* __restrict__ out, int ldo) {
+attention_fwd_rows_kernel(AttnArgs a, AttOut out) {
+  const int ldo = out.ld;
   using MaskT = typename std::conditional<(NT > 8), unsigned long long, uint32_t>::type;
   pdl_trigger();
   pdl_wait();
@@ -505,9 +584,10 @@ attention_fwd_rows_kernel(AttnArgs a, float* __restrict__ out, int ldo) {
   for (int nt = 0; nt < NT; ++nt)
 #pragma unroll
     for (int e = 0; e < 4; ++e) S[0][nt][e] = 0.f;
-  mma_xyT<1, NT>(S, Q, a.nq - i0, a.ldq, K, a.nk, a.ldk, g, t);
+  mma_xyT<1, NT, 3>(S, Q, a.nq - i0, a.ldq, K, a.nk, a.ldk, g, t);
   MaskT msk[1];
   softmax_frag<1, NT, MaskT>(a, S, msk, b, g, t, i0);
+  float SL[1][NT][4];
 #pragma unroll
   for (int nt = 0; nt < NT; ++nt)
 #pragma unroll
@@ -520,17 +600,20 @@ attention_fwd_rows_kernel(AttnArgs a, float* __restrict__ out, int ldo) {
         const int j = 8 * nt + 2 * t + e;
         float wgt = S[0][nt][2 * hh + e];
         if (a.drop_p > 0.f && i < a.nq && j < a.nk) wgt *= att_keep(dw, j, dropout_threshold(a.drop_p), 1.f / (1.f - a.drop_p));
-        S[0][nt][2 * hh + e] = tf32_rn(wgt);
+        const float wh = tf32_rn(wgt);
+        S[0][nt][2 * hh + e] = wh;
+        SL[0][nt][2 * hh + e] = wgt - wh;
       }
     }
-  mma_pY_store<1, NT>(S, V, a.nk, a.ldv, out + ((size_t)b * a.nq + i0) * ldo + h * 64, a.nq - i0, ldo, g, t, a.rn);
+  mma_pY_store<1, NT, 3>(S, V, a.nk, a.ldv, att_out_at(out, ((size_t)b * a.nq + i0) * ldo + h * 64), a.nq - i0, g, t, a.rn, SL);
 }
 
 // out[16mj + .., :64] = sum_{i < ni} T[i][j] * X[i, :64] for the 16 keys of block mj (rows j < nj are stored); T is a shared
 // tile [ni][ATT_LD] (ni a multiple of 8, columns up to 16*ceil(NT/2) readable).  Reduction slot t of k-step s is row 8s + 2t,
 // slot t + 4 is row 8s + 2t + 1, on both operands.
-__device__ __forceinline__ void mma_TtX_block_store(const float* T, int ni, int ncols, const float* X, int nx, int ldx, float* out,
-                                                    int mj, int nj, int ldo, int g, int t, int rn) {
+__device__ __forceinline__ void mma_TtX_block_store(const float* T, int ni, int ncols, const float* X, int nx, int ldx, const AttOut& out,
+                                                    int mj, int nj, int g, int t, int rn) {
+  const int ldo = out.ld;
   const int j0 = 16 * mj + g, j1 = j0 + 8;
 #pragma unroll
   for (int cq = 0; cq < 2; ++cq) {
@@ -548,8 +631,8 @@ __device__ __forceinline__ void mma_TtX_block_store(const float* T, int ni, int 
 #pragma unroll
       for (int p = 0; p < PF; ++p) {
         const int i = 8 * (s0 + p) + 2 * t;      // rows >= nx (and every row of a k-step >= ns) read as zero
-        x0[p] = ld4(X, i, nx, ldx, 32 * cq + 4 * g);
-        x1[p] = ld4(X, i + 1, nx, ldx, 32 * cq + 4 * g);
+        x0[p] = hi4(ld4(X, i, nx, ldx, 32 * cq + 4 * g));
+        x1[p] = hi4(ld4(X, i + 1, nx, ldx, 32 * cq + 4 * g));
       }
 #pragma unroll
       for (int p = 0; p < PF; ++p) {
@@ -567,9 +650,9 @@ __device__ __forceinline__ void mma_TtX_block_store(const float* T, int ni, int 
     for (int hh = 0; hh < 2; ++hh) {
       const int row = 16 * mj + g + 8 * hh;
       if (row < nj) {
-        float4* dst = reinterpret_cast<float4*>(out + (size_t)row * ldo + 32 * cq + 8 * t);
-        dst[0] = make_float4(rnd(acc[0][2 * hh], rn), rnd(acc[1][2 * hh], rn), rnd(acc[2][2 * hh], rn), rnd(acc[3][2 * hh], rn));
-        dst[1] = make_float4(rnd(acc[0][2 * hh + 1], rn), rnd(acc[1][2 * hh + 1], rn), rnd(acc[2][2 * hh + 1], rn), rnd(acc[3][2 * hh + 1], rn));
+        const float v[8] = {acc[0][2 * hh], acc[1][2 * hh], acc[2][2 * hh], acc[3][2 * hh],
+                            acc[0][2 * hh + 1], acc[1][2 * hh + 1], acc[2][2 * hh + 1], acc[3][2 * hh + 1]};
+        att_store8(out, (size_t)row * ldo + 32 * cq + 8 * t, v, rn);
       }
     }
   }
@@ -577,8 +660,8 @@ __device__ __forceinline__ void mma_TtX_block_store(const float* T, int ni, int 
 
 template <int NT>
 __global__ void __launch_bounds__(160, 2)
-attention_bwd_rows_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, float* __restrict__ dq, float* __restrict__ dk,
-                          float* __restrict__ dv, int lddq, int lddk, int lddv) {
+attention_bwd_rows_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, AttOut dq, AttOut dk, AttOut dv) {
+  const int lddq = dq.ld, lddk = dk.ld, lddv = dv.ld;
   using MaskT = typename std::conditional<(NT > 8), unsigned long long, uint32_t>::type;
   extern __shared__ float rows_sm[];
   pdl_trigger();
@@ -598,8 +681,8 @@ attention_bwd_rows_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, f
     for (int nt = 0; nt < NT; ++nt)
 #pragma unroll
       for (int e = 0; e < 4; ++e) { S[0][nt][e] = 0.f; dW[0][nt][e] = 0.f; }
-    mma_xyT<1, NT>(S, Qh + (size_t)i0 * a.ldq, a.nq - i0, a.ldq, K, a.nk, a.ldk, g, t);     // scores
-    mma_xyT<1, NT>(dW, dOh + (size_t)i0 * ldo, a.nq - i0, ldo, V, a.nk, a.ldv, g, t);       // d(post-dropout weights) = dO . V^T
+    mma_xyT<1, NT, 3>(S, Qh + (size_t)i0 * a.ldq, a.nq - i0, a.ldq, K, a.nk, a.ldk, g, t);  // scores (the forward's 3-term product)
+    mma_xyT<1, NT, 1>(dW, dOh + (size_t)i0 * ldo, a.nq - i0, ldo, V, a.nk, a.ldv, g, t);    // d(post-dropout weights) = dO . V^T
     MaskT msk[1];
     softmax_frag<1, NT, MaskT>(a, S, msk, b, g, t, i0);
 #pragma unroll
@@ -637,12 +720,12 @@ attention_bwd_rows_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, f
           Ds[i * ATT_LD + j] = ds;
         }
     }
-    mma_pY_store<1, NT>(S, K, a.nk, a.ldk, dq + ((size_t)b * a.nq + i0) * lddq + h * 64, a.nq - i0, lddq, g, t, a.rn, a.dq2 ? dW : nullptr);   // dQ = (dS + dS_lo) . K
+    mma_pY_store<1, NT, 1>(S, K, a.nk, a.ldk, att_out_at(dq, ((size_t)b * a.nq + i0) * lddq + h * 64), a.nq - i0, g, t, a.rn, a.dq2 ? dW : nullptr);   // dQ = (dS + dS_lo) . K
   }
   __syncthreads();
   if (16 * w < a.nk) {
-    mma_TtX_block_store(Ds, ni, 8 * NT, Qh, a.nq, a.ldq, dk + (size_t)b * a.nk * lddk + h * 64, w, a.nk, lddk, g, t, a.rn);  // dK = dS^T . Q
-    mma_TtX_block_store(Ws, ni, 8 * NT, dOh, a.nq, ldo, dv + (size_t)b * a.nk * lddv + h * 64, w, a.nk, lddv, g, t, a.rn);   // dV = W^T . dO
+    mma_TtX_block_store(Ds, ni, 8 * NT, Qh, a.nq, a.ldq, att_out_at(dk, (size_t)b * a.nk * lddk + h * 64), w, a.nk, g, t, a.rn);  // dK = dS^T . Q
+    mma_TtX_block_store(Ws, ni, 8 * NT, dOh, a.nq, ldo, att_out_at(dv, (size_t)b * a.nk * lddv + h * 64), w, a.nk, g, t, a.rn);   // dV = W^T . dO
   }
 }
 
@@ -672,20 +755,34 @@ static bool att_force_simt() {
   static const int v = [] { const char* e = getenv("B200IQ_ATT_SIMT"); return (e && e[0] == '1') ? 1 : 0; }();
   return v != 0;
 }
-static bool tc_ok(const B200iqAttention* p, const void* const* ptrs, int nptr, const int* lds, int nld) {
-  if (att_force_simt()) return false;
-  if (!round_mode() || p->head_dim != 64 || p->nq > 32 || p->nk > 32) return false;
-  for (int i = 0; i < nptr; ++i) if (((uintptr_t)ptrs[i]) & 15) return false;
-  for (int i = 0; i < nld; ++i) if (lds[i] & 3) return false;
+// the tensor-core kernels take fp32 rows with 16-byte alignment and plane rows with 16-byte alignment (ld % 8 halves)
+static bool outs_ok(const AttOut* outs, int n) {
+  for (int i = 0; i < n; ++i) {
+    if (outs[i].hi) {
+      if ((((uintptr_t)outs[i].hi) | ((uintptr_t)outs[i].lo)) & 15) return false;
+      if (outs[i].ld & 7) return false;
+    } else {
+      if (((uintptr_t)outs[i].f32) & 15) return false;
+      if (outs[i].ld & 3) return false;
+    }
+  }
   return true;
 }
-// the row-block kernels: anything the register-resident kernels above do not take, up to 80 x 80
-static bool rows_ok(const B200iqAttention* p, const void* const* ptrs, int nptr, const int* lds, int nld) {
+static bool tc_common_ok(const B200iqAttention* p, const void* const* ptrs, int nptr, const int* lds, int nld, const AttOut* outs, int nout) {
   if (att_force_simt()) return false;
-  if (!round_mode() || p->head_dim != 64 || p->nq > ATT_ROWBLOCK_MAX || p->nk > ATT_ROWBLOCK_MAX) return false;
+  // legacy callers (TF32 rounding mode on) or the precise mode of the fp16-plane path; the exact mode (rounding off, precise 0)
+  // keeps the CUDA-core kernels
+  if (!(round_mode() || p->precise) || p->head_dim != 64) return false;
   for (int i = 0; i < nptr; ++i) if (((uintptr_t)ptrs[i]) & 15) return false;
   for (int i = 0; i < nld; ++i) if (lds[i] & 3) return false;
-  return true;
+  return outs_ok(outs, nout);
+}
+static bool tc_ok(const B200iqAttention* p, const void* const* ptrs, int nptr, const int* lds, int nld, const AttOut* outs, int nout) {
+  return p->nq <= 32 && p->nk <= 32 && tc_common_ok(p, ptrs, nptr, lds, nld, outs, nout);
+}
+// the row-block kernels: anything the register-resident kernels above do not take, up to 80 x 80
+static bool rows_ok(const B200iqAttention* p, const void* const* ptrs, int nptr, const int* lds, int nld, const AttOut* outs, int nout) {
+  return p->nq <= ATT_ROWBLOCK_MAX && p->nk <= ATT_ROWBLOCK_MAX && tc_common_ok(p, ptrs, nptr, lds, nld, outs, nout);
 }
 #define B200IQ_ATT_ROWS_DISPATCH(NT_, CALL) \
   do { \
@@ -699,26 +796,22 @@ static bool rows_ok(const B200iqAttention* p, const void* const* ptrs, int nptr,
     if (MT_ == 1) { if (NT_ == 1) { CALL(1, 1); } else if (NT_ == 2) { CALL(1, 2); } else if (NT_ == 3) { CALL(1, 3); } else { CALL(1, 4); } } \
     else          { if (NT_ == 1) { CALL(2, 1); } else if (NT_ == 2) { CALL(2, 2); } else if (NT_ == 3) { CALL(2, 3); } else { CALL(2, 4); } } \
   } while (0)
-}  // namespace b200iq
-using namespace b200iq;
 
-extern "C" int b200iq_attention_fwd(const B200iqAttention* p, void* stream) {
-  if (int rc = check_attn(p)) return rc;
-  B200IQ_CHECK_ARG(p->out, "attention_fwd: null out");
+static int attention_fwd_impl(const B200iqAttention* p, const AttOut& out, void* stream) {
   AttnArgs a = to_args(p);
   {
-    const void* ptrs[] = {p->q, p->k, p->v, p->out};
-    const int lds[] = {p->ldq, p->ldk, p->ldv, p->ldo};
-    if (tc_ok(p, ptrs, 4, lds, 4)) {
+    const void* ptrs[] = {p->q, p->k, p->v};
+    const int lds[] = {p->ldq, p->ldk, p->ldv};
+    if (tc_ok(p, ptrs, 3, lds, 3, &out, 1)) {
       const int mt = a.nq > 16 ? 2 : 1, nt = (a.nk + 7) / 8, grid = (a.B * a.nh + ATT_TC_WARPS - 1) / ATT_TC_WARPS;
-#define CALL(M_, N_) launch_dep(attention_fwd_tc_kernel<M_, N_>, dim3(grid), dim3(ATT_TC_WARPS * 32), 0, (cudaStream_t)stream, a, p->out, p->ldo)
+#define CALL(M_, N_) launch_dep(attention_fwd_tc_kernel<M_, N_>, dim3(grid), dim3(ATT_TC_WARPS * 32), 0, (cudaStream_t)stream, a, out)
       B200IQ_ATT_DISPATCH(mt, nt, CALL);
 #undef CALL
       return launch_status("attention_fwd_tc");
     }
-    if (rows_ok(p, ptrs, 4, lds, 4)) {
+    if (rows_ok(p, ptrs, 3, lds, 3, &out, 1)) {
       const int nt = (a.nk + 7) / 8, warps = (a.nq + 15) / 16;
-#define CALL(N_) launch_dep(attention_fwd_rows_kernel<N_>, dim3(a.B * a.nh), dim3(32 * warps), 0, (cudaStream_t)stream, a, p->out, p->ldo)
+#define CALL(N_) launch_dep(attention_fwd_rows_kernel<N_>, dim3(a.B * a.nh), dim3(32 * warps), 0, (cudaStream_t)stream, a, out)
       B200IQ_ATT_ROWS_DISPATCH(nt, CALL);
 #undef CALL
       return launch_status("attention_fwd_rows");
@@ -727,33 +820,30 @@ extern "C" int b200iq_attention_fwd(const B200iqAttention* p, void* stream) {
   size_t smem = sizeof(float) * ((size_t)(a.nq + 2 * a.nk) * (a.d + 1) + (ATT_THREADS / 32) * a.nk);
   B200IQ_CHECK_ARG(smem <= 227 * 1024, "attention_fwd: tile does not fit shared memory (%zu B)", smem);
   if (smem > 48 * 1024) cudaFuncSetAttribute(attention_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  attention_fwd_kernel<<<a.B * a.nh, ATT_THREADS, smem, (cudaStream_t)stream>>>(a, p->out, p->ldo);
+  attention_fwd_kernel<<<a.B * a.nh, ATT_THREADS, smem, (cudaStream_t)stream>>>(a, out);
   return launch_status("attention_fwd");
 }
 
-extern "C" int b200iq_attention_bwd(const B200iqAttention* p, const float* dout, float* dq, float* dk, float* dv,
-                                    int lddq, int lddk, int lddv, void* stream) {
-  if (int rc = check_attn(p)) return rc;
-  B200IQ_CHECK_ARG(dout && dq && dk && dv, "attention_bwd: null pointer");
-  B200IQ_CHECK_ARG(p->kv_batch_stride == 0, "attention_bwd: kv_batch_stride is a forward-only (KV cache) option");
+static int attention_bwd_impl(const B200iqAttention* p, const float* dout, const AttOut& dq, const AttOut& dk, const AttOut& dv, void* stream) {
   AttnArgs a = to_args(p);
   {
-    const void* ptrs[] = {p->q, p->k, p->v, dout, dq, dk, dv};
-    const int lds[] = {p->ldq, p->ldk, p->ldv, p->ldo, lddq, lddk, lddv};
-    if (tc_ok(p, ptrs, 7, lds, 7)) {
+    const void* ptrs[] = {p->q, p->k, p->v, dout};
+    const int lds[] = {p->ldq, p->ldk, p->ldv, p->ldo};
+    const AttOut outs[] = {dq, dk, dv};
+    if (tc_ok(p, ptrs, 4, lds, 4, outs, 3)) {
       const int mt = a.nq > 16 ? 2 : 1, nt = (a.nk + 7) / 8, grid = (a.B * a.nh + ATT_TC_WARPS - 1) / ATT_TC_WARPS;
-#define CALL(M_, N_) launch_dep(attention_bwd_tc_kernel<M_, N_>, dim3(grid), dim3(ATT_TC_WARPS * 32), 0, (cudaStream_t)stream, a, dout, p->ldo, dq, dk, dv, lddq, lddk, lddv)
+#define CALL(M_, N_) launch_dep(attention_bwd_tc_kernel<M_, N_>, dim3(grid), dim3(ATT_TC_WARPS * 32), 0, (cudaStream_t)stream, a, dout, p->ldo, dq, dk, dv)
       B200IQ_ATT_DISPATCH(mt, nt, CALL);
 #undef CALL
       return launch_status("attention_bwd_tc");
     }
-    if (rows_ok(p, ptrs, 7, lds, 7)) {
+    if (rows_ok(p, ptrs, 4, lds, 4, outs, 3)) {
       const int nt = (a.nk + 7) / 8, mtiles = (a.nq + 15) / 16, jtiles = (a.nk + 15) / 16, warps = mtiles > jtiles ? mtiles : jtiles;
       const size_t smem = sizeof(float) * 2 * (size_t)(16 * mtiles) * ATT_LD;
 #define CALL(N_) \
   do { \
     if (smem > 48 * 1024) cudaFuncSetAttribute(attention_bwd_rows_kernel<N_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
-    launch_dep(attention_bwd_rows_kernel<N_>, dim3(a.B * a.nh), dim3(32 * warps), smem, (cudaStream_t)stream, a, dout, p->ldo, dq, dk, dv, lddq, lddk, lddv); \
+    launch_dep(attention_bwd_rows_kernel<N_>, dim3(a.B * a.nh), dim3(32 * warps), smem, (cudaStream_t)stream, a, dout, p->ldo, dq, dk, dv); \
   } while (0)
       B200IQ_ATT_ROWS_DISPATCH(nt, CALL);
 #undef CALL
@@ -763,6 +853,33 @@ extern "C" int b200iq_attention_bwd(const B200iqAttention* p, const float* dout,
   size_t smem = sizeof(float) * ((size_t)(2 * a.nq + 2 * a.nk) * (a.d + 1) + 2 * (size_t)a.nq * (a.nk + 1));
   B200IQ_CHECK_ARG(smem <= 227 * 1024, "attention_bwd: tile does not fit shared memory (%zu B)", smem);
   if (smem > 48 * 1024) cudaFuncSetAttribute(attention_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  attention_bwd_kernel<<<a.B * a.nh, ATT_THREADS, smem, (cudaStream_t)stream>>>(a, dout, p->ldo, dq, dk, dv, lddq, lddk, lddv);
+  attention_bwd_kernel<<<a.B * a.nh, ATT_THREADS, smem, (cudaStream_t)stream>>>(a, dout, p->ldo, dq, dk, dv);
   return launch_status("attention_bwd");
+}
+}  // namespace b200iq
+using namespace b200iq;
+
+extern "C" int b200iq_attention_fwd(const B200iqAttention* p, void* stream) {
+  if (int rc = check_attn(p)) return rc;
+  B200IQ_CHECK_ARG(p->out || p->out_hi, "attention_fwd: null out");
+  B200IQ_CHECK_ARG(!p->out_lo || p->out_hi, "attention_fwd: out_lo without out_hi");
+  const AttOut out{p->out_hi ? nullptr : p->out, (__half*)p->out_hi, (__half*)p->out_lo, p->ldo};
+  return attention_fwd_impl(p, out, stream);
+}
+
+extern "C" int b200iq_attention_bwd(const B200iqAttention* p, const float* dout, float* dq, float* dk, float* dv,
+                                    int lddq, int lddk, int lddv, void* stream) {
+  if (int rc = check_attn(p)) return rc;
+  B200IQ_CHECK_ARG(dout && dq && dk && dv, "attention_bwd: null pointer");
+  B200IQ_CHECK_ARG(p->kv_batch_stride == 0, "attention_bwd: kv_batch_stride is a forward-only (KV cache) option");
+  return attention_bwd_impl(p, dout, AttOut{dq, nullptr, nullptr, lddq}, AttOut{dk, nullptr, nullptr, lddk}, AttOut{dv, nullptr, nullptr, lddv}, stream);
+}
+
+extern "C" int b200iq_attention_bwd_f16(const B200iqAttention* p, const float* dout, void* dq_hi, void* dk_hi, void* dv_hi,
+                                        int lddq, int lddk, int lddv, void* stream) {
+  if (int rc = check_attn(p)) return rc;
+  B200IQ_CHECK_ARG(dout && dq_hi && dk_hi && dv_hi, "attention_bwd_f16: null pointer");
+  B200IQ_CHECK_ARG(p->kv_batch_stride == 0, "attention_bwd_f16: kv_batch_stride is a forward-only (KV cache) option");
+  return attention_bwd_impl(p, dout, AttOut{nullptr, (__half*)dq_hi, nullptr, lddq}, AttOut{nullptr, (__half*)dk_hi, nullptr, lddk},
+                            AttOut{nullptr, (__half*)dv_hi, nullptr, lddv}, stream);
 }

@@ -293,10 +293,10 @@ extern "C" int b200iq_layernorm_fwd(const float* x, const float* gamma, const fl
   B200IQ_CHECK_ARG(x && gamma && beta && y && M > 0 && H > 0, "layernorm_fwd: bad args");
   if ((H == 128 || H == 256 || H == 512 || H == 1024) && (((uintptr_t)x | (uintptr_t)y | (uintptr_t)gamma | (uintptr_t)beta) & 15) == 0) {
     const int grid = min(ceil_div(M, 8), sm_count() * 8), rn = round_mode();
-    if (H == 128) launch_dep(ln_fwd_warp_kernel<1, false>, dim3(grid), dim3(256), 0, ST, x, nullptr, nullptr, gamma, beta, y, mean, rstd, M, eps, rn);
-    else if (H == 256) launch_dep(ln_fwd_warp_kernel<2, false>, dim3(grid), dim3(256), 0, ST, x, nullptr, nullptr, gamma, beta, y, mean, rstd, M, eps, rn);
-    else if (H == 512) launch_dep(ln_fwd_warp_kernel<4, false>, dim3(grid), dim3(256), 0, ST, x, nullptr, nullptr, gamma, beta, y, mean, rstd, M, eps, rn);
-    else launch_dep(ln_fwd_warp_kernel<8, false>, dim3(grid), dim3(256), 0, ST, x, nullptr, nullptr, gamma, beta, y, mean, rstd, M, eps, rn);
+    if (H == 128) launch_dep(ln_fwd_warp_kernel<1, false>, dim3(grid), dim3(256), 0, ST, x, nullptr, nullptr, gamma, beta, y, mean, rstd, M, eps, rn, (__half*)nullptr, (__half*)nullptr, 0);
+    else if (H == 256) launch_dep(ln_fwd_warp_kernel<2, false>, dim3(grid), dim3(256), 0, ST, x, nullptr, nullptr, gamma, beta, y, mean, rstd, M, eps, rn, (__half*)nullptr, (__half*)nullptr, 0);
+    else if (H == 512) launch_dep(ln_fwd_warp_kernel<4, false>, dim3(grid), dim3(256), 0, ST, x, nullptr, nullptr, gamma, beta, y, mean, rstd, M, eps, rn, (__half*)nullptr, (__half*)nullptr, 0);
+    else launch_dep(ln_fwd_warp_kernel<8, false>, dim3(grid), dim3(256), 0, ST, x, nullptr, nullptr, gamma, beta, y, mean, rstd, M, eps, rn, (__half*)nullptr, (__half*)nullptr, 0);
     return launch_status("layernorm_fwd");
   }
   layernorm_fwd_kernel<<<ceil_div(M, 8), 256, 0, ST>>>(x, gamma, beta, y, mean, rstd, M, H, eps, round_mode());
@@ -310,10 +310,10 @@ extern "C" int b200iq_add_layernorm_fwd(const float* x, const float* add, float*
   B200IQ_CHECK_ARG((((uintptr_t)x | (uintptr_t)add | (uintptr_t)sum | (uintptr_t)y | (uintptr_t)gamma | (uintptr_t)beta) & 15) == 0,
                    "add_layernorm_fwd: pointers must be 16-byte aligned");
   const int grid = min(ceil_div(M, 8), sm_count() * 8), rn = round_mode();
-  if (H == 128) launch_dep(ln_fwd_warp_kernel<1, true>, dim3(grid), dim3(256), 0, ST, x, add, sum, gamma, beta, y, mean, rstd, M, eps, rn);
-  else if (H == 256) launch_dep(ln_fwd_warp_kernel<2, true>, dim3(grid), dim3(256), 0, ST, x, add, sum, gamma, beta, y, mean, rstd, M, eps, rn);
-  else if (H == 512) launch_dep(ln_fwd_warp_kernel<4, true>, dim3(grid), dim3(256), 0, ST, x, add, sum, gamma, beta, y, mean, rstd, M, eps, rn);
-  else launch_dep(ln_fwd_warp_kernel<8, true>, dim3(grid), dim3(256), 0, ST, x, add, sum, gamma, beta, y, mean, rstd, M, eps, rn);
+  if (H == 128) launch_dep(ln_fwd_warp_kernel<1, true>, dim3(grid), dim3(256), 0, ST, x, add, sum, gamma, beta, y, mean, rstd, M, eps, rn, (__half*)nullptr, (__half*)nullptr, 0);
+  else if (H == 256) launch_dep(ln_fwd_warp_kernel<2, true>, dim3(grid), dim3(256), 0, ST, x, add, sum, gamma, beta, y, mean, rstd, M, eps, rn, (__half*)nullptr, (__half*)nullptr, 0);
+  else if (H == 512) launch_dep(ln_fwd_warp_kernel<4, true>, dim3(grid), dim3(256), 0, ST, x, add, sum, gamma, beta, y, mean, rstd, M, eps, rn, (__half*)nullptr, (__half*)nullptr, 0);
+  else launch_dep(ln_fwd_warp_kernel<8, true>, dim3(grid), dim3(256), 0, ST, x, add, sum, gamma, beta, y, mean, rstd, M, eps, rn, (__half*)nullptr, (__half*)nullptr, 0);
   return launch_status("add_layernorm_fwd");
 }
 
@@ -323,10 +323,10 @@ extern "C" int b200iq_layernorm_bwd(const float* dy, const float* x, const float
   B200IQ_CHECK_ARG(H <= 2048, "layernorm_bwd: H=%d > 2048 unsupported", H);
   if ((H == 128 || H == 256 || H == 512 || H == 1024) && (((uintptr_t)x | (uintptr_t)dy | (uintptr_t)dx | (uintptr_t)gamma) & 15) == 0) {
     const int grid = min(ceil_div(M, 8), sm_count() * 2), rn = round_mode();
-    if (H == 128) launch_dep(ln_bwd_warp_kernel<1>, dim3(grid), dim3(256), 0, ST, dy, x, gamma, mean, rstd, dx, dgamma, dbeta, M, accumulate_dx, rn);
-    else if (H == 256) launch_dep(ln_bwd_warp_kernel<2>, dim3(grid), dim3(256), 0, ST, dy, x, gamma, mean, rstd, dx, dgamma, dbeta, M, accumulate_dx, rn);
-    else if (H == 512) launch_dep(ln_bwd_warp_kernel<4>, dim3(grid), dim3(256), 0, ST, dy, x, gamma, mean, rstd, dx, dgamma, dbeta, M, accumulate_dx, rn);
-    else launch_dep(ln_bwd_warp_kernel<8>, dim3(grid), dim3(256), 0, ST, dy, x, gamma, mean, rstd, dx, dgamma, dbeta, M, accumulate_dx, rn);
+    if (H == 128) launch_dep(ln_bwd_warp_kernel<1>, dim3(grid), dim3(256), 0, ST, dy, x, gamma, mean, rstd, dx, dgamma, dbeta, M, accumulate_dx, rn, (__half*)nullptr);
+    else if (H == 256) launch_dep(ln_bwd_warp_kernel<2>, dim3(grid), dim3(256), 0, ST, dy, x, gamma, mean, rstd, dx, dgamma, dbeta, M, accumulate_dx, rn, (__half*)nullptr);
+    else if (H == 512) launch_dep(ln_bwd_warp_kernel<4>, dim3(grid), dim3(256), 0, ST, dy, x, gamma, mean, rstd, dx, dgamma, dbeta, M, accumulate_dx, rn, (__half*)nullptr);
+    else launch_dep(ln_bwd_warp_kernel<8>, dim3(grid), dim3(256), 0, ST, dy, x, gamma, mean, rstd, dx, dgamma, dbeta, M, accumulate_dx, rn, (__half*)nullptr);
     return launch_status("layernorm_bwd");
   }
   int ctas = min(M, sm_count() * 4);
@@ -343,7 +343,7 @@ extern "C" int b200iq_colsum_add(const float* x, float* out, int M, int N, int l
   B200IQ_CHECK_ARG(x && out && M > 0 && N > 0 && ld >= N, "colsum_add: bad args");
   if ((N & 3) == 0 && (ld & 3) == 0 && (((uintptr_t)x) & 15) == 0) {
     const int cx = ceil_div(N, 128), rpc = max(32, ceil_div(M, max(1, sm_count() * 4 / cx)));
-    launch_dep(colsum4_kernel<false>, dim3(cx, ceil_div(M, rpc)), dim3(32, 8), 0, ST, x, nullptr, nullptr, out, M, N, ld, rpc, 1.f, 0);
+    launch_dep(colsum4_kernel<false>, dim3(cx, ceil_div(M, rpc)), dim3(32, 8), 0, ST, x, nullptr, nullptr, out, M, N, ld, rpc, 1.f, 0, (__half*)nullptr);
     return launch_status("colsum_add");
   }
   int rows = max(8, ceil_div(M, max(1, sm_count() * 4 / ceil_div(N, 128))));
@@ -356,7 +356,7 @@ extern "C" int b200iq_relu_bwd_colsum(const float* dy, const float* y, float* dp
   B200IQ_CHECK_ARG(dy && y && dpre && M > 0 && N > 0, "relu_bwd_colsum: bad args");
   if ((N & 3) == 0 && (((uintptr_t)dy | (uintptr_t)y | (uintptr_t)dpre) & 15) == 0) {
     const int cx = ceil_div(N, 128), rpc = max(32, ceil_div(M, max(1, sm_count() * 4 / cx)));
-    launch_dep(colsum4_kernel<true>, dim3(cx, ceil_div(M, rpc)), dim3(32, 8), 0, ST, dy, y, dpre, dbias, M, N, N, rpc, scale, round_mode());
+    launch_dep(colsum4_kernel<true>, dim3(cx, ceil_div(M, rpc)), dim3(32, 8), 0, ST, dy, y, dpre, dbias, M, N, N, rpc, scale, round_mode(), (__half*)nullptr);
     return launch_status("relu_bwd_colsum");
   }
   int rows = max(8, ceil_div(M, max(1, sm_count() * 4 / ceil_div(N, 128))));

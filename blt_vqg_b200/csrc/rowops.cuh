@@ -5,11 +5,31 @@
 // reductions = 4 __syncthreads per row) and the scalar column sums at 8 %.
 #pragma once
 #include "common.cuh"
+#include <cuda_fp16.h>
 
 namespace b200iq {
 
 __device__ __forceinline__ float4 ldg4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
 __device__ __forceinline__ void st4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
+// fp16 planes of a GEMM operand (gemm_f16.cu): hi = fp16(x), lo = fp16(x - hi); four consecutive elements = one 8-byte store
+__device__ __forceinline__ void st4_planes(__half* hi, __half* lo, size_t off, float4 v) {
+  const __half2 h0 = __floats2half2_rn(v.x, v.y), h1 = __floats2half2_rn(v.z, v.w);
+  uint2 hb;
+  hb.x = *reinterpret_cast<const uint32_t*>(&h0); hb.y = *reinterpret_cast<const uint32_t*>(&h1);
+  *reinterpret_cast<uint2*>(hi + off) = hb;
+  if (lo) {
+    const float2 f0 = __half22float2(h0), f1 = __half22float2(h1);
+    const __half2 l0 = __floats2half2_rn(v.x - f0.x, v.y - f0.y), l1 = __floats2half2_rn(v.z - f1.x, v.w - f1.y);
+    uint2 lb;
+    lb.x = *reinterpret_cast<const uint32_t*>(&l0); lb.y = *reinterpret_cast<const uint32_t*>(&l1);
+    *reinterpret_cast<uint2*>(lo + off) = lb;
+  }
+}
+__device__ __forceinline__ void st1_planes(__half* hi, __half* lo, size_t off, float v) {
+  const __half h = __float2half_rn(v);
+  hi[off] = h;
+  if (lo) lo[off] = __float2half_rn(v - __half2float(h));
+}
 
 // ---------------------------------------------------------------- LayerNorm forward: one warp per row, one HBM read
 // ADD: the residual add in front of the LayerNorm rides along — s = rnd(x + add) is written to `sum` (the next block's
@@ -19,7 +39,7 @@ template <int NV, bool ADD>  // float4s per lane; H = 128 * NV
 __global__ void __launch_bounds__(256)
 ln_fwd_warp_kernel(const float* __restrict__ x, const float* __restrict__ add, float* __restrict__ sum, const float* __restrict__ g,
                    const float* __restrict__ b, float* __restrict__ y, float* __restrict__ mean, float* __restrict__ rstd, int M,
-                   float eps, int rn) {
+                   float eps, int rn, __half* __restrict__ y_hi, __half* __restrict__ y_lo, int ldy) {
   constexpr int H = 128 * NV;
   const int lane = threadIdx.x & 31, nw = gridDim.x * (blockDim.x >> 5);
   pdl_trigger();
@@ -55,7 +75,8 @@ ln_fwd_warp_kernel(const float* __restrict__ x, const float* __restrict__ add, f
       o.y = rnd((xv[i].y - mu) * rs * gv[i].y + bv[i].y, rn);
       o.z = rnd((xv[i].z - mu) * rs * gv[i].z + bv[i].z, rn);
       o.w = rnd((xv[i].w - mu) * rs * gv[i].w + bv[i].w, rn);
-      st4(y + (size_t)row * H + (i * 32 + lane) * 4, o);
+      if (y) st4(y + (size_t)row * H + (i * 32 + lane) * 4, o);
+      if (y_hi) st4_planes(y_hi, y_lo, (size_t)row * ldy + (i * 32 + lane) * 4, o);
     }
     if (lane == 0) { if (mean) mean[row] = mu; if (rstd) rstd[row] = rs; }
   }
@@ -69,7 +90,7 @@ template <int NV>
 __global__ void __launch_bounds__(256)
 ln_bwd_warp_kernel(const float* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ g,
                    const float* __restrict__ mean, const float* __restrict__ rstd, float* __restrict__ dx,
-                   float* __restrict__ dg, float* __restrict__ db, int M, int accumulate, int rn) {
+                   float* __restrict__ dg, float* __restrict__ db, int M, int accumulate, int rn, __half* __restrict__ dx_hi) {
   constexpr int H = 128 * NV;
   __shared__ float red[8][H];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = gridDim.x * 8;
@@ -109,6 +130,7 @@ ln_bwd_warp_kernel(const float* __restrict__ dy, const float* __restrict__ x, co
       o.w = rs * (dv[i].w * gv[i].w - s1 - xh[i].w * s2);
       if (accumulate) { const float4 p = *reinterpret_cast<const float4*>(dst); o.x += p.x; o.y += p.y; o.z += p.z; o.w += p.w; }
       st4(dst, make_float4(rnd(o.x, rn), rnd(o.y, rn), rnd(o.z, rn), rnd(o.w, rn)));
+      if (dx_hi) st4_planes(dx_hi, nullptr, (size_t)row * H + (i * 32 + lane) * 4, o);
     }
   }
 #pragma unroll 1
@@ -133,7 +155,7 @@ ln_bwd_warp_kernel(const float* __restrict__ dy, const float* __restrict__ x, co
 template <bool RELU_BWD>
 __global__ void __launch_bounds__(256)
 colsum4_kernel(const float* dy, const float* __restrict__ y, float* dpre, float* __restrict__ out, int M, int N, int ld,
-               int rows_per_cta, float scale, int rn) {
+               int rows_per_cta, float scale, int rn, __half* __restrict__ dpre_hi) {
   __shared__ float4 red[8][32];
   const int tx = threadIdx.x, ty = threadIdx.y, c = (blockIdx.x * 32 + tx) * 4;
   const int r0 = blockIdx.y * rows_per_cta, r1 = min(M, r0 + rows_per_cta);
@@ -151,7 +173,8 @@ colsum4_kernel(const float* dy, const float* __restrict__ y, float* dpre, float*
         v.y = yv.y > 0.f ? rnd(v.y * scale, sc) : 0.f;
         v.z = yv.z > 0.f ? rnd(v.z * scale, sc) : 0.f;
         v.w = yv.w > 0.f ? rnd(v.w * scale, sc) : 0.f;
-        st4(dpre + (size_t)r * ld + c, v);
+        if (dpre) st4(dpre + (size_t)r * ld + c, v);
+        if (dpre_hi) st4_planes(dpre_hi, nullptr, (size_t)r * ld + c, v);
       }
       s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
     }

@@ -12,6 +12,8 @@ from . import _lib as L
 
 # global switch: exact-fp32 CUDA-core GEMMs instead of tcgen05 TF32 (parity debugging, greedy decode)
 _FORCE_SIMT = os.environ.get("B200IQ_GEMM", "") == "simt"
+# fp32-in / fp32-out attention calls: 1 = precise mode (3-term forward products on unrounded inputs) — set by the transformer path
+PRECISE_ATTENTION = 0
 # number of kernel launches issued through the C ABI (bench.py reports it as gpu_launches)
 LAUNCHES = 0
 # when a list: gemm() brackets every launch with CUDA events on the launching stream and appends
@@ -27,6 +29,143 @@ def exact_mode():
 def set_pdl(on):
     """programmatic dependent launch for the hot kernels (b200iq_set_pdl); returns the previous setting"""
     return bool(L.lib().b200iq_set_pdl(1 if on else 0))
+
+
+class no_rounding:
+    """context manager for the fp16-plane path (the transformer IQ): fp32 tensors stay unrounded — precision is decided per GEMM
+    operand by its planes — so the library's TF32 write-rounding (the legacy kind::tf32 scheme the LSTM variant still uses) is off"""
+
+    def __enter__(self):
+        self.prev = L.lib().b200iq_set_tf32_rounding(0)
+
+    def __exit__(self, *a):
+        L.lib().b200iq_set_tf32_rounding(self.prev)
+
+
+class Act:
+    """a GEMM operand: exact mode -> `f32` tensor [M, K]; fp16-plane mode -> `hi` (+ `lo`) fp16 views [M, K] (row pitch a
+    multiple of 8 halves) written by the producing kernel.  hi = fp16(x), lo = fp16(x - hi)."""
+    __slots__ = ("f32", "hi", "lo")
+
+    def __init__(self, f32=None, hi=None, lo=None):
+        self.f32, self.hi, self.lo = f32, hi, lo
+
+    @property
+    def shape(self):
+        return (self.f32 if self.f32 is not None else self.hi).shape
+
+    def rows(self, r0, r1):
+        return Act(*(None if t is None else t[r0:r1] for t in (self.f32, self.hi, self.lo)))
+
+    def cols(self, c0, c1):
+        return Act(*(None if t is None else t[:, c0:c1] for t in (self.f32, self.hi, self.lo)))
+
+
+def pad8(n):
+    return (n + 7) // 8 * 8
+
+
+def new_act(ws, name, M, K, lo=True):
+    """workspace-backed operand for the current mode (Workspace.buf keeps addresses stable)"""
+    if _FORCE_SIMT:
+        return Act(f32=ws.buf(name, M, K))
+    ld = pad8(K)
+    hi = ws.buf(name + ".hi", M, ld, dtype=torch.float16)[:, :K]
+    return Act(hi=hi, lo=ws.buf(name + ".lo", M, ld, dtype=torch.float16)[:, :K] if lo else None)
+
+
+def to_act(ws, name, x, lo=True, scale=1.0):
+    """planes of an fp32 tensor [M, K] (b200iq_split_f16); exact mode: the tensor itself"""
+    if _FORCE_SIMT:
+        assert scale == 1.0
+        return Act(f32=x)
+    a = new_act(ws, name, x.shape[0], x.shape[1], lo=lo)
+    split_f16(x, a.hi, a.lo, scale)
+    return a
+
+
+def split_f16(src, hi, lo=None, scale=1.0):
+    """hi = fp16(scale*src), lo = fp16(scale*src - hi); src [rows, cols] (or flat), any row pitches"""
+    if src.dim() == 1:
+        rows, cols, lds, ldd = 1, src.numel(), src.numel(), hi.numel()
+    else:
+        rows, cols = src.shape
+        lds, ldd = _ld(src), _ld(hi)
+        assert lo is None or _ld(lo) == ldd
+    _call("b200iq_split_f16", _p(src), _p(hi), _p(lo), rows, C.c_longlong(cols), C.c_longlong(lds), C.c_longlong(ldd), _f(scale))
+
+
+class GemmF16Params(C.Structure):
+    _fields_ = [
+        ("A_hi", C.c_void_p), ("A_lo", C.c_void_p), ("B_hi", C.c_void_p), ("B_lo", C.c_void_p),
+        ("C", C.c_void_p), ("C_hi", C.c_void_p), ("C_lo", C.c_void_p),
+        ("bias", C.c_void_p), ("residual", C.c_void_p), ("gate", C.c_void_p),
+        ("M", C.c_int), ("N", C.c_int), ("K", C.c_int),
+        ("lda", C.c_int), ("ldb", C.c_int), ("ldc", C.c_int), ("ldh", C.c_int), ("ldr", C.c_int), ("ldg", C.c_int),
+        ("flags", C.c_int), ("split_k", C.c_int), ("alpha", C.c_float),
+        ("drop_p", C.c_float), ("drop_seed", C.c_uint64), ("drop_offset", C.c_uint64),
+    ]
+
+
+def _dp(t):
+    return t.data_ptr() if t is not None else None
+
+
+def gemm2(a, b, out=None, *, planes=None, a_t=False, b_t=False, bias=None, residual=None, relu=False, relu_mask=None,
+          accumulate=False, split_k=1, alpha=1.0, dropout=None, auto_split=False, terms=3):
+    """epi(alpha * A @ B^T) over operands `a`, `b` (Act).  out: fp32 tensor [M, N] and / or planes: Act receiving the result as
+    operand planes for the next GEMM (exact mode: its fp32 tensor).  terms=3: the accurate 3-term product when both operands
+    carry lo planes (forward products); terms=1: single pass (backward products, vocabulary projection).
+    relu_mask: Act whose hi plane (> 0) gates the result."""
+    if _FORCE_SIMT:
+        dest = out if out is not None else planes.f32
+        assert out is None or planes is None
+        return gemm(a.f32, b.f32, dest, a_t=a_t, b_t=b_t, bias=bias, residual=residual, relu=relu,
+                    relu_mask=relu_mask.f32 if relu_mask is not None else None, accumulate=accumulate, split_k=split_k,
+                    alpha=alpha, fp32_out=True, dropout=dropout)
+    ah, bh = a.hi, b.hi
+    M, K = (ah.shape[1], ah.shape[0]) if a_t else ah.shape
+    N, Kb = (bh.shape[1], bh.shape[0]) if b_t else bh.shape
+    assert K == Kb, (ah.shape, bh.shape, a_t, b_t)
+    three = terms == 3 and a.lo is not None and b.lo is not None and not a_t and not b_t
+    if auto_split and not accumulate and residual is None and relu_mask is None and not relu and planes is None:
+        tiles = ((M + 127) // 128) * ((N + 127) // 128)
+        sk = min(148 // tiles, K // 512) if tiles <= 74 else 1
+        if sk > 1:
+            out.zero_()
+            accumulate, split_k = True, sk
+    flags = 0
+    if a_t: flags |= L.GEMM_A_MN
+    if b_t: flags |= L.GEMM_B_MN
+    if bias is not None: flags |= L.GEMM_BIAS
+    if relu: flags |= L.GEMM_RELU
+    if residual is not None: flags |= L.GEMM_RESIDUAL
+    if relu_mask is not None: flags |= L.GEMM_RELU_MASK
+    if accumulate: flags |= L.GEMM_ACCUM
+    dp, dseed, doff = dropout if dropout is not None and dropout[0] > 0 else (0.0, 0, 0)
+    if dp > 0: flags |= L.GEMM_DROPOUT
+    ph = planes.hi if planes is not None else None
+    pl = planes.lo if planes is not None else None
+    assert out is not None or ph is not None
+    gate = relu_mask.hi if relu_mask is not None else None
+    p = GemmF16Params(ah.data_ptr(), a.lo.data_ptr() if three else None, bh.data_ptr(), b.lo.data_ptr() if three else None,
+                      _dp(out), _dp(ph), _dp(pl), _dp(bias), _dp(residual), _dp(gate), M, N, K,
+                      _ld(ah), _ld(bh), _ld(out) if out is not None else 0, _ld(ph) if ph is not None else 0,
+                      _ld(residual) if residual is not None else 0, _ld(gate) if gate is not None else 0,
+                      flags, split_k, float(alpha), float(dp), dseed, doff)
+    global LAUNCHES
+    LAUNCHES += 1
+    if GEMM_TRACE is not None:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        L.check(L.lib().b200iq_gemm_f16(C.byref(p), L.stream_ptr()), "b200iq_gemm_f16")
+        e1.record()
+        nt = 3 if three else 1
+        by = 2.0 * nt * (M * K + N * K) + (4.0 * M * N if out is not None else 0.0) + (2.0 * M * N * (2 if pl is not None else 1) if ph is not None else 0.0)
+        GEMM_TRACE.append((e0, e1, 2.0 * M * N * K, by, (M, N, K, flags, split_k, nt)))
+    else:
+        L.check(L.lib().b200iq_gemm_f16(C.byref(p), L.stream_ptr()), "b200iq_gemm_f16")
+    return out if out is not None else planes
 
 
 class gemm_mode:
@@ -126,6 +265,7 @@ class AttnParams(C.Structure):
         ("B", C.c_int), ("num_heads", C.c_int), ("nq", C.c_int), ("nk", C.c_int), ("head_dim", C.c_int),
         ("scale", C.c_float), ("drop_p", C.c_float), ("seed", C.c_uint64), ("offset", C.c_uint64),
         ("kv_batch_stride", C.c_longlong),
+        ("precise", C.c_int), ("out_hi", C.c_void_p), ("out_lo", C.c_void_p),
     ]
 
 
@@ -168,6 +308,69 @@ def add_layernorm_fwd(x, add, out, g, b, y, mean, rstd, eps=1e-5):
     M, H = x.shape
     _call("b200iq_add_layernorm_fwd", _p(x), _p(add), _p(out), _p(g), _p(b), _p(y), _p(mean), _p(rstd), M, H, _f(eps))
     return y
+
+
+def embed_gather_act(ids, table, out):
+    """out: Act [M, E] (planes in fp16-plane mode)"""
+    if out.f32 is not None:
+        return embed_gather(ids, table, out.f32)
+    _call("b200iq_embed_gather_f16", _p(ids), _p(table), _p(out.hi), _p(out.lo), ids.numel(), table.shape[1], table.shape[0], _ld(out.hi))
+    return out
+
+
+def layernorm_fwd_act(x, g, b, mean, rstd, y=None, act=None, add=None, sum_out=None, eps=1e-5):
+    """LayerNorm(x [+ add]) with any of: fp32 y, operand planes `act`; with add the sum is written to sum_out.
+    Exact mode (act.f32): the fp32 kernels."""
+    M, H = x.shape
+    if act is not None and act.f32 is not None:
+        assert y is None
+        y, act = act.f32, None
+    if act is None:
+        if add is not None:
+            if add_layernorm_supported(x):
+                return add_layernorm_fwd(x, add, sum_out, g, b, y, mean, rstd, eps)
+            axpby(x, add, sum_out)
+            return layernorm_fwd(sum_out, g, b, y, mean, rstd, eps)
+        return layernorm_fwd(x, g, b, y, mean, rstd, eps)
+    _call("b200iq_layernorm_fwd_f16", _p(x), _p(add), _p(sum_out), _p(g), _p(b), _p(y), _p(act.hi), _p(act.lo), _ld(act.hi),
+          _p(mean), _p(rstd), M, H, _f(eps))
+    return y
+
+
+def layernorm_bwd_act(dy, x, g, mean, rstd, dx, dg, db, accumulate_dx, dx_hi=None):
+    """layernorm_bwd that also leaves fp16(dx) in dx_hi (fp16 [M, H]) for the GEMMs that read the residual-stream gradient"""
+    if dx_hi is None:
+        return layernorm_bwd(dy, x, g, mean, rstd, dx, dg, db, accumulate_dx)
+    M, H = x.shape
+    assert dx_hi.stride(0) == H
+    _call("b200iq_layernorm_bwd_f16", _p(dy), _p(x), _p(g), _p(mean), _p(rstd), _p(dx), _p(dx_hi), _p(dg), _p(db), M, H, int(accumulate_dx))
+
+
+def relu_bwd_colsum_act(dy, y, dpre, dbias, scale=1.0):
+    """dpre: Act; planes mode: hi = fp16(scale * dy * (y > 0))"""
+    if dpre.f32 is not None:
+        return relu_bwd_colsum(dy, y, dpre.f32, dbias, scale)
+    M, N = y.shape
+    assert _ld(dpre.hi) == N
+    _call("b200iq_relu_bwd_colsum_f16", _p(dy), _p(y), _p(dpre.hi), _p(dbias), M, N, _f(scale))
+
+
+def colsum_add_act(x, out):
+    """out[c] += column sums of an operand (its hi plane in fp16-plane mode)"""
+    if x.f32 is not None:
+        return colsum_add(x.f32, out)
+    M, N = x.hi.shape
+    _call("b200iq_colsum_add_f16", _p(x.hi), _p(out), M, N, _ld(x.hi))
+
+
+def ce_rows_act(logits, targets, pad_id, count, coef, loss_sum, grad):
+    """cross-entropy of a logits chunk; grad: Act receiving coef * (softmax - onehot) / count (planes mode: hi plane; exact mode:
+    grad.f32 must be the logits tensor itself — in place)"""
+    if grad is None or grad.f32 is not None:
+        return ce_rows(logits, targets, pad_id, count, coef, loss_sum, write_grad=grad is not None)
+    rows, V = logits.shape
+    _call("b200iq_ce_rows_f16", _p(logits), logits.stride(0), _p(targets), rows, V, int(pad_id), _p(count), _f(coef), _p(loss_sum),
+          _p(grad.hi), _ld(grad.hi))
 
 
 def layernorm_bwd(dy, x, g, mean, rstd, dx, dg, db, accumulate_dx):
@@ -213,19 +416,35 @@ def _attn_params(q, k, v, out, key_ids, pad_id, causal, B, nh, nq, nk, d, drop_p
     return AttnParams(q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr() if out is not None else 0,
                       q.stride(0), k.stride(0), v.stride(0), out.stride(0) if out is not None else 0,
                       key_ids.data_ptr() if key_ids is not None else 0, pad_id, int(causal),
-                      B, nh, nq, nk, d, d ** -0.5, drop_p, seed, offset, kv_batch_stride)
+                      B, nh, nq, nk, d, d ** -0.5, drop_p, seed, offset, kv_batch_stride, 0, None, None)
 
 
 def attention_fwd(q, k, v, out, key_ids, pad_id, causal, B, nh, nq, nk, d, drop_p=0.0, seed=0, offset=0, kv_batch_stride=0):
-    """kv_batch_stride (elements) lets k / v be the first nk positions of a [B, max_len, H] KV cache"""
+    """kv_batch_stride (elements) lets k / v be the first nk positions of a [B, max_len, H] KV cache.
+    out: fp32 tensor, or an Act — in fp16-plane mode the merged heads then go out as planes and the products run in the
+    precise (3-term) mode on unrounded fp32 q / k / v"""
+    if isinstance(out, Act):
+        if out.f32 is not None:
+            return attention_fwd(q, k, v, out.f32, key_ids, pad_id, causal, B, nh, nq, nk, d, drop_p, seed, offset, kv_batch_stride)
+        p = _attn_params(q, k, v, None, key_ids, pad_id, causal, B, nh, nq, nk, d, drop_p, seed, offset, kv_batch_stride)
+        p.precise, p.out_hi, p.out_lo, p.ldo = 1, out.hi.data_ptr(), _dp(out.lo), _ld(out.hi)
+        _call("b200iq_attention_fwd", C.byref(p))
+        return out
     p = _attn_params(q, k, v, out, key_ids, pad_id, causal, B, nh, nq, nk, d, drop_p, seed, offset, kv_batch_stride)
+    p.precise = 0 if _FORCE_SIMT else PRECISE_ATTENTION
     _call("b200iq_attention_fwd", C.byref(p))
     return out
 
 
 def attention_bwd(q, k, v, dout, dq, dk, dv, key_ids, pad_id, causal, B, nh, nq, nk, d, drop_p=0.0, seed=0, offset=0):
+    """dq / dk / dv: fp32 tensors, or fp16 tensors (the hi planes of the gradients: operands of the projections' backward GEMMs)"""
     p = _attn_params(q, k, v, None, key_ids, pad_id, causal, B, nh, nq, nk, d, drop_p, seed, offset)
     p.ldo = dout.stride(0)
+    if dq.dtype == torch.float16:
+        p.precise = 1
+        _call("b200iq_attention_bwd_f16", C.byref(p), _p(dout), _p(dq), _p(dk), _p(dv), dq.stride(0), dk.stride(0), dv.stride(0))
+        return
+    p.precise = 0 if _FORCE_SIMT else PRECISE_ATTENTION
     _call("b200iq_attention_bwd", C.byref(p), _p(dout), _p(dq), _p(dk), _p(dv), dq.stride(0), dk.stride(0), dv.stride(0))
 
 

@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define B200IQ_ABI_VERSION 1
+#define B200IQ_ABI_VERSION 2
 
 int b200iq_abi_version(void);
 /* 1 when the current device is compute capability 10.0, else 0 */
@@ -84,6 +84,54 @@ int b200iq_gemm(const B200iqGemm* p, void* stream);
  * Environment default: B200IQ_GEMM_TILE. */
 int b200iq_set_gemm_tile(int tile);
 
+/* ------------------------------------------------------------------ fp16-plane GEMM (the transformer path's precision scheme)
+ * A GEMM operand x is stored as fp16 PLANES written by the kernel that produces x: hi = fp16(x) and, for operands of forward
+ * products, lo = fp16(x - hi) (together ~22 significand bits).  With both lo planes given the product is the 3-term
+ * A_hi.B_hi + A_lo.B_hi + A_hi.B_lo (K-major operands only); without them it is the single pass A_hi.B_hi.  Why: the forward
+ * products feed ReLU gates, and 11-bit operands there flip enough gates to put ~1e-2 of error on the gradients, while the
+ * backward products (dX = dY.W, dW = dY^T.X) tolerate 11 bits (profiles/r02a_cpu_precision_study.txt).  Backward operands carry
+ * the loss scale of the caller (fp16 range).  Output: fp32 C (TMA store; ACCUM / split-K as in b200iq_gemm) and / or fp16 planes
+ * C_hi (+ C_lo) for the next GEMM.  flags: A_MN, B_MN, BIAS, RELU, RESIDUAL (fp32 tile, needs C), ACCUM, RELU_MASK (gate = fp16
+ * plane, > 0 passes), DROPOUT.  Planes: 16-byte aligned, leading dimensions multiples of 8 halves.
+ * replaces: the same nn.Linear call sites as b200iq_gemm (models/transformer_layers.py:489-491,530,403; models/iq.py:76;
+ * models/decoder_transformer.py:35,40; models/mlp.py:37; models/encoder_cnn.py:20) and their autograd backward. */
+typedef struct B200iqGemmF16 {
+  const void* A_hi; const void* A_lo;   /* [M,K] ld=lda halves ([K,M] when A_MN); A_lo NULL = single pass */
+  const void* B_hi; const void* B_lo;   /* [N,K] ld=ldb halves ([K,N] when B_MN) */
+  float* C;                             /* [M,N] ld=ldc floats, or NULL */
+  void* C_hi; void* C_lo;               /* fp16 planes [M,N] ld=ldh halves, or NULL */
+  const float* bias;                    /* [N] or NULL */
+  const float* residual;                /* [M,N] ld=ldr floats (RESIDUAL) */
+  const void* gate;                     /* fp16 plane [M,N] ld=ldg halves (RELU_MASK) */
+  int M, N, K;
+  int lda, ldb, ldc, ldh, ldr, ldg;
+  int flags;
+  int split_k;
+  float alpha;
+  float drop_p;
+  unsigned long long drop_seed, drop_offset;
+} B200iqGemmF16;
+int b200iq_gemm_f16(const B200iqGemmF16* p, void* stream);
+/* hi[r,c] = fp16(scale * src[r,c]), lo[r,c] = fp16(scale * src[r,c] - hi[r,c]) (lo may be NULL): the plane copy of the fp32
+ * master weights (rows = 1, cols = arena size) and of small fp32 tensors that feed a GEMM.  lds / ldd: row pitches (floats / halves). */
+int b200iq_split_f16(const float* src, void* hi, void* lo, int rows, long long cols, long long lds, long long ldd, float scale, void* stream);
+/* b200iq_embed_gather writing planes (ldo halves).   replaces: nn.Embedding forward, models/iq.py:71-78 */
+int b200iq_embed_gather_f16(const int* ids, const float* table, void* out_hi, void* out_lo, int M, int E, int V, int ldo, void* stream);
+/* LayerNorm forward with plane outputs: sum = x + add when add != NULL (sum may be NULL otherwise); y (fp32), y_hi, y_lo are
+ * each optional outputs of the same normalised row (ldy halves for the planes). */
+int b200iq_layernorm_fwd_f16(const float* x, const float* add, float* sum, const float* gamma, const float* beta, float* y,
+                             void* y_hi, void* y_lo, int ldy, float* mean, float* rstd, int M, int H, float eps, void* stream);
+/* b200iq_layernorm_bwd that also writes fp16(dx) (the accumulated result) to dx_hi (ld H halves) when dx_hi != NULL */
+int b200iq_layernorm_bwd_f16(const float* dy, const float* x, const float* gamma, const float* mean, const float* rstd,
+                             float* dx, void* dx_hi, float* dgamma, float* dbeta, int M, int H, int accumulate_dx, void* stream);
+/* dpre_hi = fp16(scale * dy * (y > 0)); dbias[c] += colsum (dbias may be NULL) */
+int b200iq_relu_bwd_colsum_f16(const float* dy, const float* y, void* dpre_hi, float* dbias, int M, int N, float scale, void* stream);
+/* out[c] += sum_m x_hi[m,c] over an fp16 plane (bias gradients of tensors that only exist as planes) */
+int b200iq_colsum_add_f16(const void* x_hi, float* out, int M, int N, int ld, void* stream);
+/* b200iq_ce_rows that leaves the logits untouched and writes the gradient rows as an fp16 plane (ldg halves) */
+int b200iq_ce_rows_f16(const float* logits, int ld, const int* targets, int rows, int V, int pad_id, const float* count,
+                       float coef, float* loss_sum, void* grad_hi, int ldg, void* stream);
+
 /* ---------------------------------------------------------- row / elementwise ops */
 /* out[m,:] = table[ids[m],:]   replaces: nn.Embedding fwd, models/iq.py:71-78 (also decoder_rnn.py:102, encoder_rnn.py:78) */
 int b200iq_embed_gather(const int* ids, const float* table, float* out, int M, int E, int V, void* stream);
@@ -140,12 +188,20 @@ typedef struct B200iqAttention {
   uint64_t seed, offset;
   long long kv_batch_stride; /* elements between consecutive samples' K (and V) blocks; 0 = nk*ldk / nk*ldv (dense [B*nk, ld]).
                                 A KV cache [B, max_len, H] read at length nk passes max_len*H here (forward only). */
+  int precise;           /* 1 (head_dim 64, n <= 80): q / k / v are unrounded fp32; the forward's QK^T and PV run as 3-term TF32
+                            products (hi.hi + lo.hi + hi.lo, ~2^-21), the backward recomputes the scores the same way and rounds
+                            (instead of truncating) the operands of its single-pass products.  0: legacy TF32 single pass. */
+  void* out_hi;          /* precise forward: fp16 planes of the merged-head output (ldo halves) written instead of `out` when */
+  void* out_lo;          /*   out_hi != NULL (out_lo optional) */
 } B200iqAttention;
 /* replaces: models/transformer_layers.py:494-526; mask fill is the finite -1e18 of :506 */
 int b200iq_attention_fwd(const B200iqAttention* p, void* stream);
 /* recomputes the probabilities from q/k (nothing is stashed by fwd); writes dq/dk/dv (not accumulated) */
 int b200iq_attention_bwd(const B200iqAttention* p, const float* dout, float* dq, float* dk, float* dv,
                          int lddq, int lddk, int lddv, void* stream);
+/* same, gradients written as fp16 planes (ld in halves): the operands of the projections' backward GEMMs */
+int b200iq_attention_bwd_f16(const B200iqAttention* p, const float* dout, void* dq_hi, void* dk_hi, void* dv_hi,
+                             int lddq, int lddk, int lddv, void* stream);
 
 /* ---------------------------------------------------------- losses */
 /* count[0] = #(targets != pad_id)  (the CE "mean over non-pad" denominator, train_iq.py:82-83) */
