@@ -12,8 +12,6 @@ import torch
 from . import _lib, ops
 
 PAD = 0
-# forward FFN dropout inside the GEMM epilogue (1) or as the standalone HBM-bound kernel (0); same mask either way
-FUSE_DROPOUT = os.environ.get("B200IQ_FUSE_DROPOUT", "1") == "1"
 # small context-side GEMMs of the decoder (cross-attention K|V projections, their gradients) on a side stream
 CONCURRENT = os.environ.get("B200IQ_CONCURRENT", "1") == "1"
 # weight-gradient GEMMs of a block on the side stream, under the block's dX chain: the persistent GEMM grids leave SMs idle in
@@ -43,19 +41,61 @@ class Workspace:
     def __getitem__(self, name):
         return self.bufs[name]
 
+    def act(self, name):
+        """the operand made by ops.new_act(ws, name, ...) in the current mode"""
+        if name in self.bufs:
+            return ops.Act(f32=self.bufs[name])
+        hi, lo = self.bufs[name + ".hi"], self.bufs.get(name + ".lo")
+        K = self.meta[("actK", name)]
+        return ops.Act(hi=hi[:, :K], lo=lo[:, :K] if lo is not None else None)
+
     def nbytes(self):
         return sum(t.numel() * t.element_size() for t in self.bufs.values())
+
+
+class WeightOperands:
+    """name -> ops.Act of a weight matrix: the fp32 master view in exact mode, else views of the fp16 plane arenas (hi, lo) that
+    mirror the parameter arena element for element; matrices whose row pitch is not a multiple of 8 halves (E = 300, L = 100)
+    live in their own padded plane buffers (`odd`)"""
+
+    def __init__(self, arena, whi=None, wlo=None, odd=None):
+        self.arena, self.whi, self.wlo, self.odd = arena, whi, wlo, odd or {}
+        self.vh = arena.views_over(whi) if whi is not None else None
+        self.vl = arena.views_over(wlo) if wlo is not None else None
+        self.cache = {}
+
+    def __getitem__(self, name):
+        a = self.cache.get(name)
+        if a is None:
+            if self.whi is None:
+                a = ops.Act(f32=self.arena.views[name])
+            elif name in self.odd:
+                a = self.odd[name]
+            else:
+                a = ops.Act(hi=self.vh[name], lo=self.vl[name])
+            self.cache[name] = a
+        return a
+
+    def span(self, first, last, cols):
+        key = (first, last)
+        a = self.cache.get(key)
+        if a is None:
+            o0, o1 = self.arena.span(first, last)
+            if self.whi is None:
+                a = ops.Act(f32=self.arena.flat.detach()[o0:o1].view(-1, cols))
+            else:
+                a = ops.Act(hi=self.whi[o0:o1].view(-1, cols), lo=self.wlo[o0:o1].view(-1, cols))
+            self.cache[key] = a
+        return a
 
 
 class Ctx:
     """everything a block schedule needs: parameter / gradient views, workspace, sizes, dropout keys"""
 
-    def __init__(self, arena, gflat, ws, H, nh, F, E, attn_drop, relu_drop, training, seed, wflat=None):
+    def __init__(self, arena, gflat, ws, H, nh, F, E, attn_drop, relu_drop, training, seed, weights):
         self.arena, self.ws = arena, ws
         self.P = arena.views      # fp32 masters: biases, LayerNorm / BatchNorm affine, embedding table
-        # GEMM weight operands: the TF32-rounded copy of the arena (the masters themselves in exact mode)
-        self.wflat = wflat if wflat is not None else arena.flat.detach()
-        self.W = arena.views_over(wflat) if wflat is not None else arena.views
+        self.W = weights          # GEMM weight operands (WeightOperands)
         self.gflat = gflat
         self.G = arena.views_over(gflat) if gflat is not None else None
         self.H, self.nh, self.F, self.E, self.d = H, nh, F, E, H // nh
@@ -127,12 +167,20 @@ class Ctx:
             self.on_ready(self.arena.offsets.get(name + "#pack", self.arena.offsets.get(name)))
 
     def pspan(self, first, last, cols):
-        o0, o1 = self.arena.span(first, last)
-        return self.wflat[o0:o1].view(-1, cols)
+        return self.W.span(first, last, cols)
 
     def gspan(self, first, last, cols):
         o0, o1 = self.arena.span(first, last)
         return self.gflat[o0:o1].view(-1, cols)
+
+    def act(self, name, M, K, lo=True):
+        """a forward operand buffer (planes hi + lo, or fp32 in exact mode)"""
+        self.ws.meta[("actK", name)] = K
+        return ops.new_act(self.ws, name, M, K, lo=lo)
+
+    def gact(self, name, M, K):
+        """a backward operand buffer: single fp16 plane (the gradients carry the loss scale), or fp32 in exact mode"""
+        return self.act(name, M, K, lo=False)
 
     def key(self, tag):
         """(seed, offset) of a dropout site; remembered under `tag` so the backward re-creates the mask"""
@@ -150,43 +198,61 @@ class Ctx:
 
 
 def grad_w(c, dy, x, gw, gb=None):
-    """dW[N,K] += dy[M,N]^T @ x[M,K];  db[N] += colsum(dy)"""
+    """dW[N,K] += dy[M,N]^T @ x[M,K];  db[N] += colsum(dy)   (dy, x: operands; single-pass product)"""
     M = dy.shape[0]
-    ops.gemm(dy, x, gw, a_t=True, b_t=True, accumulate=True, split_k=c.split_k(gw.shape[0], gw.shape[1], M))
+    ops.gemm2(dy, x, gw, a_t=True, b_t=True, accumulate=True, split_k=c.split_k(gw.shape[0], gw.shape[1], M), terms=1)
     if gb is not None:
-        ops.colsum_add(dy, gb)
+        ops.colsum_add_act(dy, gb)
 
 
-def ln_fwd(c, tag, pfx, x):
+def ln_fwd(c, tag, pfx, x, kind="act"):
+    """LayerNorm(x) as a GEMM operand (kind "act": planes hi + lo, "act_hi": hi only) or as an fp32 tensor (kind "f32")"""
     M, H = x.shape
-    y = c.ws.buf(tag + ".y", M, H)
     mean, rstd = c.ws.buf(tag + ".mean", M), c.ws.buf(tag + ".rstd", M)
-    ops.layernorm_fwd(x, c.P[pfx + ".weight"], c.P[pfx + ".bias"], y, mean, rstd)
+    g, b = c.P[pfx + ".weight"], c.P[pfx + ".bias"]
+    if kind == "f32":
+        y = c.ws.buf(tag + ".y", M, H)
+        ops.layernorm_fwd_act(x, g, b, mean, rstd, y=y)
+        return y
+    y = c.act(tag + ".y", M, H, lo=kind == "act")
+    ops.layernorm_fwd_act(x, g, b, mean, rstd, act=y)
     return y
 
 
-def ln_bwd(c, tag, pfx, dy, x, dx, accumulate):
-    ops.layernorm_bwd(dy, x, c.P[pfx + ".weight"], c.ws[tag + ".mean"], c.ws[tag + ".rstd"], dx,
-                      c.G[pfx + ".weight"], c.G[pfx + ".bias"], accumulate)
+def ln_bwd(c, tag, pfx, dy, x, dx, accumulate, dx_act=None):
+    """dx (+)= LayerNorm-backward(dy); dx_act (fp16-plane mode): also leave fp16(dx) in its hi plane for the GEMMs that read dx"""
+    ops.layernorm_bwd_act(dy, x, c.P[pfx + ".weight"], c.ws[tag + ".mean"], c.ws[tag + ".rstd"], dx,
+                          c.G[pfx + ".weight"], c.G[pfx + ".bias"], accumulate,
+                          dx_hi=dx_act.hi if (dx_act is not None and dx_act.hi is not None) else None)
+
+
+def dx_operand(c, name, dx):
+    """the residual-stream gradient as a GEMM operand: the fp32 tensor itself in exact mode, else a single fp16 plane that the
+    LayerNorm backward fills next to dx"""
+    if ops.exact_mode():
+        return ops.Act(f32=dx)
+    return ops.Act(hi=c.ws.buf(name, dx.shape[0], dx.shape[1], dtype=torch.float16))
 
 
 # ------------------------------------------------------------------ embedder (models/iq.py:57-79)
 def embed_fwd(c, tag, ids, B, n, timing, add0=None, add1=None):
     M = B * n
-    e = c.ws.buf(tag + ".e", M, c.E)
-    ops.embed_gather(ids, c.P["embedding.0.weight"], e)
+    e = c.act(tag + ".e", M, c.E)
+    ops.embed_gather_act(ids, c.P["embedding.0.weight"], e)
     x = c.ws.buf(tag + ".x0", M, c.H)
-    ops.gemm(e, c.W["embedding.1.weight"], x, bias=c.P["embedding.1.bias"])
+    ops.gemm2(e, c.W["embedding.1.weight"], x, bias=c.P["embedding.1.bias"])
     ops.add_timing(x, timing, add0, add1, B, n, c.H)
     return x
 
 
-def embed_bwd(c, tag, ids, dx):
-    e = c.ws[tag + ".e"]
+def embed_bwd(c, tag, ids, dxa):
+    """dxa: the gradient wrt the embedder output as an operand (dx_operand)"""
+    e = c.ws.act(tag + ".e")
+    M = dxa.shape[0]
     ev = c.mark()
-    de = c.ws.buf("tmp.de.%d" % dx.shape[0], dx.shape[0], c.E)
-    ops.gemm(dx, c.W["embedding.1.weight"], de, b_t=True)
-    c.on_side(lambda: grad_w(c, dx, e, c.G["embedding.1.weight"], c.G["embedding.1.bias"]), ev)
+    de = c.ws.buf("tmp.de.%d" % M, M, c.E)
+    ops.gemm2(dxa, c.W["embedding.1.weight"], de, b_t=True, terms=1)
+    c.on_side(lambda: grad_w(c, dxa, e, c.G["embedding.1.weight"], c.G["embedding.1.bias"]), ev)
     ops.embed_scatter_add(ids, de, c.G["embedding.0.weight"], PAD)
     c.join_side()
 
@@ -196,31 +262,39 @@ def self_attn_fwd(c, tag, pfx, xn, x_res, ids, B, n, causal):
     M, H = xn.shape
     wqkv = c.pspan(pfx + "query_linear.weight", pfx + "value_linear.weight", H)
     qkv = c.ws.buf(tag + ".qkv", M, 3 * H)
-    ops.gemm(xn, wqkv, qkv)
-    ctx = c.ws.buf(tag + ".ctx", M, H)
+    ops.gemm2(xn, wqkv, qkv)
+    ctx = c.act(tag + ".ctx", M, H)
     seed, off = c.key(tag + ".adrop")
     ops.attention_fwd(qkv[:, :H], qkv[:, H:2 * H], qkv[:, 2 * H:], ctx, ids, PAD, causal, B, c.nh, n, n, c.d,
                       c.attn_drop, seed, off)
     out = c.ws.buf(tag + ".out", M, H)
-    ops.gemm(ctx, c.W[pfx + "output_linear.weight"], out, residual=x_res)
+    ops.gemm2(ctx, c.W[pfx + "output_linear.weight"], out, residual=x_res)
     return out
 
 
+def _grad_parts(a, *col_ranges):
+    """column slices of a gradient operand as the tensors attention_bwd writes (fp16 hi plane or fp32)"""
+    t = a.f32 if a.f32 is not None else a.hi
+    return [t[:, c0:c1] for c0, c1 in col_ranges]
+
+
 def self_attn_bwd(c, tag, pfx, dout, xn, ids, B, n, causal):
+    """dout: the block-output gradient as an operand; xn: the block's LayerNorm-ed input operand.  Returns fp32 grad wrt xn."""
     M, H = xn.shape
-    qkv, ctx = c.ws[tag + ".qkv"], c.ws[tag + ".ctx"]
+    qkv, ctx = c.ws[tag + ".qkv"], c.ws.act(tag + ".ctx")
     ev = c.mark()
     dctx = c.ws.buf("tmp.dctx.%d" % M, M, H)
-    ops.gemm(dout, c.W[pfx + "output_linear.weight"], dctx, b_t=True)
+    ops.gemm2(dout, c.W[pfx + "output_linear.weight"], dctx, b_t=True, terms=1)
     c.on_side(lambda: grad_w(c, dout, ctx, c.G[pfx + "output_linear.weight"]), ev)
     dout_read = c.side_mark()
-    dqkv = c.ws.buf("tmp.dqkv.%d" % M, M, 3 * H)
+    dqkv = c.gact("tmp.dqkv.%d" % M, M, 3 * H)
+    dq, dk, dv = _grad_parts(dqkv, (0, H), (H, 2 * H), (2 * H, 3 * H))
     seed, off = c.key(tag + ".adrop")
-    ops.attention_bwd(qkv[:, :H], qkv[:, H:2 * H], qkv[:, 2 * H:], dctx, dqkv[:, :H], dqkv[:, H:2 * H], dqkv[:, 2 * H:],
+    ops.attention_bwd(qkv[:, :H], qkv[:, H:2 * H], qkv[:, 2 * H:], dctx, dq, dk, dv,
                       ids, PAD, causal, B, c.nh, n, n, c.d, c.attn_drop, seed, off)
     ev = c.mark()
     dxn = c.ws.buf("tmp.dxn.%d" % M, M, H)
-    ops.gemm(dqkv, c.pspan(pfx + "query_linear.weight", pfx + "value_linear.weight", H), dxn, b_t=True)
+    ops.gemm2(dqkv, c.pspan(pfx + "query_linear.weight", pfx + "value_linear.weight", H), dxn, b_t=True, terms=1)
     c.on_side(lambda: grad_w(c, dqkv, xn, c.gspan(pfx + "query_linear.weight", pfx + "value_linear.weight", H)), ev)
     c.wait_side_mark(dout_read)   # the caller's LayerNorm backward accumulates into dout's buffer next; the stack joins
     return dxn                    # the rest of the side work at the end of the layer
@@ -229,47 +303,48 @@ def self_attn_bwd(c, tag, pfx, dout, xn, ids, B, n, causal):
 def cross_kv_fwd(c, tag, pfx, enc_out):
     """K | V of the context for one decoder layer: depends only on enc_out, so decoder_fwd computes all layers' up front"""
     kv = c.ws.buf(tag + ".kv", enc_out.shape[0], 2 * c.H)
-    ops.gemm(enc_out, c.pspan(pfx + "key_linear.weight", pfx + "value_linear.weight", c.H), kv)
+    ops.gemm2(enc_out, c.pspan(pfx + "key_linear.weight", pfx + "value_linear.weight", c.H), kv)
     return kv
 
 
 def cross_attn_fwd(c, tag, pfx, xn, x_res, enc_out, enc_ids, B, nq, nk, kv=None):
     M, H = xn.shape
     q = c.ws.buf(tag + ".q", M, H)
-    ops.gemm(xn, c.W[pfx + "query_linear.weight"], q)
+    ops.gemm2(xn, c.W[pfx + "query_linear.weight"], q)
     if kv is None:
         kv = cross_kv_fwd(c, tag, pfx, enc_out)
-    ctx = c.ws.buf(tag + ".ctx", M, H)
+    ctx = c.act(tag + ".ctx", M, H)
     seed, off = c.key(tag + ".adrop")
     ops.attention_fwd(q, kv[:, :H], kv[:, H:], ctx, enc_ids, PAD, False, B, c.nh, nq, nk, c.d, c.attn_drop, seed, off)
     out = c.ws.buf(tag + ".out", M, H)
-    ops.gemm(ctx, c.W[pfx + "output_linear.weight"], out, residual=x_res)
+    ops.gemm2(ctx, c.W[pfx + "output_linear.weight"], out, residual=x_res)
     return out
 
 
 def cross_attn_bwd(c, tag, pfx, dout, xn, enc_out, d_enc_out, first, enc_ids, B, nq, nk):
     M, H = xn.shape
     Me = enc_out.shape[0]
-    q, kv, ctx = c.ws[tag + ".q"], c.ws[tag + ".kv"], c.ws[tag + ".ctx"]
+    q, kv, ctx = c.ws[tag + ".q"], c.ws[tag + ".kv"], c.ws.act(tag + ".ctx")
     ev = c.mark()
     dctx = c.ws.buf("tmp.dctx.%d" % M, M, H)
-    ops.gemm(dout, c.W[pfx + "output_linear.weight"], dctx, b_t=True)
+    ops.gemm2(dout, c.W[pfx + "output_linear.weight"], dctx, b_t=True, terms=1)
     c.on_side(lambda: grad_w(c, dout, ctx, c.G[pfx + "output_linear.weight"]), ev)
     dout_read = c.side_mark()
-    dq = c.ws.buf("tmp.dq.%d" % M, M, H)
-    dkv = c.ws.buf("tmp.dkv.%d" % Me, Me, 2 * H)
+    dqa = c.gact("tmp.dq.%d" % M, M, H)
+    dkva = c.gact("tmp.dkv.%d" % Me, Me, 2 * H)
+    (dq,), (dk, dv) = _grad_parts(dqa, (0, H)), _grad_parts(dkva, (0, H), (H, 2 * H))
     seed, off = c.key(tag + ".adrop")
-    ops.attention_bwd(q, kv[:, :H], kv[:, H:], dctx, dq, dkv[:, :H], dkv[:, H:], enc_ids, PAD, False, B, c.nh, nq, nk,
+    ops.attention_bwd(q, kv[:, :H], kv[:, H:], dctx, dq, dk, dv, enc_ids, PAD, False, B, c.nh, nq, nk,
                       c.d, c.attn_drop, seed, off)
     def off_path():
         # the context-side 2560-row GEMMs (20-40 tiles) and the query weight gradient: none feeds the decoder's dX chain
-        grad_w(c, dkv, enc_out, c.gspan(pfx + "key_linear.weight", pfx + "value_linear.weight", H))
+        grad_w(c, dkva, enc_out, c.gspan(pfx + "key_linear.weight", pfx + "value_linear.weight", H))
         wkv = c.pspan(pfx + "key_linear.weight", pfx + "value_linear.weight", H)
-        ops.gemm(dkv, wkv, d_enc_out, b_t=True, residual=None if first else d_enc_out)
-        grad_w(c, dq, xn, c.G[pfx + "query_linear.weight"])
+        ops.gemm2(dkva, wkv, d_enc_out, b_t=True, residual=None if first else d_enc_out, terms=1)
+        grad_w(c, dqa, xn, c.G[pfx + "query_linear.weight"])
     ev = c.mark()
     dxn = c.ws.buf("tmp.dxn.%d" % M, M, H)
-    ops.gemm(dq, c.W[pfx + "query_linear.weight"], dxn, b_t=True)
+    ops.gemm2(dqa, c.W[pfx + "query_linear.weight"], dxn, b_t=True, terms=1)
     c.on_side(off_path, ev)
     c.wait_side_mark(dout_read)
     return dxn
@@ -277,59 +352,54 @@ def cross_attn_bwd(c, tag, pfx, dout, xn, enc_out, d_enc_out, first, enc_ids, B,
 
 # ------------------------------------------------------------------ position-wise FFN (ReLU after BOTH linears, N1)
 def ffn_fwd(c, tag, pfx, xn, x_res, next_ln=None):
-    """relu + dropout after BOTH linears (N1) ride in the GEMM epilogues: h and f2 are written once, post-dropout.
-    next_ln = (tag, prefix) of the LayerNorm that reads this block's output (the next layer's first one, or the stack's final
-    one): the residual add and that LayerNorm then run as one kernel and (out, LN(out)) is returned instead of out."""
+    """relu + dropout after BOTH linears (N1) ride in the GEMM epilogues: h (operand planes) and f2 (fp32) are written once,
+    post-dropout.  next_ln = (tag, prefix, kind) of the LayerNorm that reads this block's output (the next layer's first one, or
+    the stack's final one): the residual add and that LayerNorm then run as one kernel and (out, LN(out)) is returned."""
     M, H = xn.shape
-    h = c.ws.buf(tag + ".h", M, c.F)
+    h = c.act(tag + ".h", M, c.F)
     f2 = c.ws.buf(tag + ".f2", M, H)
-    if FUSE_DROPOUT:
-        ops.gemm(xn, c.W[pfx + "layers.0.weight"], h, bias=c.P[pfx + "layers.0.bias"], relu=True,
-                 dropout=(c.relu_drop, *c.key(tag + ".d1")))
-        ops.gemm(h, c.W[pfx + "layers.1.weight"], f2, bias=c.P[pfx + "layers.1.bias"], relu=True,
-                 dropout=(c.relu_drop, *c.key(tag + ".d2")))
-    else:
-        ops.gemm(xn, c.W[pfx + "layers.0.weight"], h, bias=c.P[pfx + "layers.0.bias"], relu=True)
-        ops.dropout_(h, c.relu_drop, *c.key(tag + ".d1"))
-        ops.gemm(h, c.W[pfx + "layers.1.weight"], f2, bias=c.P[pfx + "layers.1.bias"], relu=True)
-        ops.dropout_(f2, c.relu_drop, *c.key(tag + ".d2"))
+    ops.gemm2(xn, c.W[pfx + "layers.0.weight"], planes=h, bias=c.P[pfx + "layers.0.bias"], relu=True,
+              dropout=(c.relu_drop, *c.key(tag + ".d1")))
+    ops.gemm2(h, c.W[pfx + "layers.1.weight"], f2, bias=c.P[pfx + "layers.1.bias"], relu=True,
+              dropout=(c.relu_drop, *c.key(tag + ".d2")))
     out = c.ws.buf(tag + ".out", M, H)
     if next_ln is None:
         ops.axpby(x_res, f2, out)
         return out
-    ln_tag, ln_pfx = next_ln
-    y = c.ws.buf(ln_tag + ".y", M, H)
+    ln_tag, ln_pfx, kind = next_ln
     mean, rstd = c.ws.buf(ln_tag + ".mean", M), c.ws.buf(ln_tag + ".rstd", M)
-    if ops.add_layernorm_supported(out):
-        ops.add_layernorm_fwd(x_res, f2, out, c.P[ln_pfx + ".weight"], c.P[ln_pfx + ".bias"], y, mean, rstd)
+    g, b = c.P[ln_pfx + ".weight"], c.P[ln_pfx + ".bias"]
+    if kind == "f32":
+        y = c.ws.buf(ln_tag + ".y", M, H)
+        ops.layernorm_fwd_act(x_res, g, b, mean, rstd, y=y, add=f2, sum_out=out)
     else:
-        ops.axpby(x_res, f2, out)
-        ops.layernorm_fwd(out, c.P[ln_pfx + ".weight"], c.P[ln_pfx + ".bias"], y, mean, rstd)
+        y = c.act(ln_tag + ".y", M, H, lo=kind == "act")
+        ops.layernorm_fwd_act(x_res, g, b, mean, rstd, act=y, add=f2, sum_out=out)
     return out, y
 
 
 def ffn_bwd(c, tag, pfx, dout, xn):
-    """dout: grad wrt (x_res + f2); returns grad wrt xn.  h and f2 are post-dropout, so (y > 0) is the relu mask AND the
-    keep mask; the dropout backward is just the 1/(1-p) factor (no Philox in the backward)"""
+    """dout: fp32 grad wrt (x_res + f2); returns fp32 grad wrt xn.  h and f2 are post-dropout, so (y > 0) is the relu mask AND
+    the keep mask; the dropout backward is just the 1/(1-p) factor (no Philox in the backward)"""
     M, H = xn.shape
-    h, f2 = c.ws[tag + ".h"], c.ws[tag + ".f2"]
+    h, f2 = c.ws.act(tag + ".h"), c.ws[tag + ".f2"]
     inv_keep = 1.0 / (1.0 - c.relu_drop)
-    dpre2 = c.ws.buf("tmp.dpre2.%d" % M, M, H)
-    ops.relu_bwd_colsum(dout, f2, dpre2, c.G[pfx + "layers.1.bias"], scale=inv_keep)
+    dpre2 = c.gact("tmp.dpre2.%d" % M, M, H)
+    ops.relu_bwd_colsum_act(dout, f2, dpre2, c.G[pfx + "layers.1.bias"], scale=inv_keep)
     ev = c.mark()
-    dh = c.ws.buf("tmp.dh.%d" % M, M, c.F)
-    ops.gemm(dpre2, c.W[pfx + "layers.1.weight"], dh, b_t=True, relu_mask=h, alpha=inv_keep)
+    dh = c.gact("tmp.dh.%d" % M, M, c.F)
+    ops.gemm2(dpre2, c.W[pfx + "layers.1.weight"], planes=dh, b_t=True, relu_mask=h, alpha=inv_keep, terms=1)
     c.on_side(lambda: grad_w(c, dpre2, h, c.G[pfx + "layers.1.weight"]), ev)
     ev = c.mark()
     dxn = c.ws.buf("tmp.dxn.%d" % M, M, H)
-    ops.gemm(dh, c.W[pfx + "layers.0.weight"], dxn, b_t=True)
+    ops.gemm2(dh, c.W[pfx + "layers.0.weight"], dxn, b_t=True, terms=1)
     c.on_side(lambda: grad_w(c, dh, xn, c.G[pfx + "layers.0.weight"], c.G[pfx + "layers.0.bias"]), ev)
     return dxn   # side work reads dpre2 / dh / saved activations only: joined by the stack at the end of the layer
 
 
 # ------------------------------------------------------------------ stacks
-def encoder_fwd(c, tag, pfx, x, ids, B, n, NL):
-    """models/transformer_layers.py:138-152 (timing already added by embed_fwd). Returns LN(x_NL)."""
+def encoder_fwd(c, tag, pfx, x, ids, B, n, NL, out_kind="f32"):
+    """models/transformer_layers.py:138-152 (timing already added by embed_fwd). Returns LN(x_NL) as `out_kind`."""
     c.ws.meta[tag + ".in"] = x
     xn = ln_fwd(c, tag + ".0.ln1", pfx + "enc.0.layer_norm_mha", x)
     for i in range(NL):
@@ -337,32 +407,34 @@ def encoder_fwd(c, tag, pfx, x, ids, B, n, NL):
         a = self_attn_fwd(c, lt + ".sa", lp + "multi_head_attention.", xn, x, ids, B, n, False)
         xn2 = ln_fwd(c, lt + ".ln2", lp + "layer_norm_ffn", a)
         # the block's residual add and the LayerNorm that reads it (next layer's first, or the final one) are one kernel
-        nxt = ("%s.%d.ln1" % (tag, i + 1), "%senc.%d.layer_norm_mha" % (pfx, i + 1)) if i + 1 < NL else (tag + ".lnf", pfx + "layer_norm")
+        nxt = ("%s.%d.ln1" % (tag, i + 1), "%senc.%d.layer_norm_mha" % (pfx, i + 1), "act") if i + 1 < NL else (tag + ".lnf", pfx + "layer_norm", out_kind)
         x, xn = ffn_fwd(c, lt + ".ff", lp + "positionwise_feed_forward.", xn2, a, next_ln=nxt)
     c.ws.meta[tag + ".last"] = x
     return xn
 
 
 def encoder_bwd(c, tag, pfx, dy, ids, B, n, NL):
-    """dy: grad wrt the final LayerNorm output [M,H]. Returns grad wrt the stack input (in a workspace buffer)."""
+    """dy: fp32 grad wrt the final LayerNorm output [M,H]. Returns the grad wrt the stack input as an operand (dx_operand)."""
     M, H = dy.shape
     dx = c.ws.buf(tag + ".dx", M, H)
+    dxa = dx_operand(c, tag + ".dx.hi", dx)
     ln_bwd(c, tag + ".lnf", pfx + "layer_norm", dy, c.ws.meta[tag + ".last"], dx, False)
     for i in reversed(range(NL)):
         lt, lp = "%s.%d" % (tag, i), "%senc.%d." % (pfx, i)
         x_in = c.ws.meta[tag + ".in"] if i == 0 else c.ws["%s.%d.ff.out" % (tag, i - 1)]
         a = c.ws[lt + ".sa.out"]
-        dxn2 = ffn_bwd(c, lt + ".ff", lp + "positionwise_feed_forward.", dx, c.ws[lt + ".ln2.y"])
-        ln_bwd(c, lt + ".ln2", lp + "layer_norm_ffn", dxn2, a, dx, True)
-        dxn = self_attn_bwd(c, lt + ".sa", lp + "multi_head_attention.", dx, c.ws[lt + ".ln1.y"], ids, B, n, False)
-        ln_bwd(c, lt + ".ln1", lp + "layer_norm_mha", dxn, x_in, dx, True)
+        dxn2 = ffn_bwd(c, lt + ".ff", lp + "positionwise_feed_forward.", dx, c.ws.act(lt + ".ln2.y"))
+        ln_bwd(c, lt + ".ln2", lp + "layer_norm_ffn", dxn2, a, dx, True, dx_act=dxa)
+        dxn = self_attn_bwd(c, lt + ".sa", lp + "multi_head_attention.", dxa, c.ws.act(lt + ".ln1.y"), ids, B, n, False)
+        ln_bwd(c, lt + ".ln1", lp + "layer_norm_mha", dxn, x_in, dx, True, dx_act=dxa if i == 0 else None)
         c.join_side()   # the layer's weight gradients are final, and the tmp.* buffers the side work read are free again
         c.ready(lp + "layer_norm_mha.weight")
-    return dx
+    return dxa
 
 
-def decoder_fwd(c, tag, pfx, x, ids, enc_out, enc_ids, B, T, S, NL):
-    """models/transformer_layers.py:205-221; causal|pad mask of :207 is built inside the attention kernel."""
+def decoder_fwd(c, tag, pfx, x, ids, enc_out, enc_ids, B, T, S, NL, out_kind="act_hi"):
+    """models/transformer_layers.py:205-221; causal|pad mask of :207 is built inside the attention kernel.
+    enc_out: the context as a GEMM operand."""
     c.ws.meta[tag + ".in"] = x
     # every layer's cross-attention K | V depends only on enc_out: six 2560-row GEMMs on the side stream, under layer 0's
     # self-attention block
@@ -374,6 +446,7 @@ def decoder_fwd(c, tag, pfx, x, ids, enc_out, enc_ids, B, T, S, NL):
             for i in range(NL):
                 kvs[i] = cross_kv_fwd(c, "%s.%d.ca" % (tag, i), "%sdec.%d.multi_head_attention_enc_dec." % (pfx, i), enc_out)
     xn1 = ln_fwd(c, tag + ".0.ln1", pfx + "dec.0.layer_norm_mha_dec", x)
+    pdl_prev = None
     for i in range(NL):
         lt, lp = "%s.%d" % (tag, i), "%sdec.%d." % (pfx, i)
         xn = xn1
@@ -385,50 +458,64 @@ def decoder_fwd(c, tag, pfx, x, ids, enc_out, enc_ids, B, T, S, NL):
             pdl_prev = ops.set_pdl(True)   # from here to the end of the stack nothing runs beside the main stream
         b = cross_attn_fwd(c, lt + ".ca", lp + "multi_head_attention_enc_dec.", xn, a, enc_out, enc_ids, B, T, S, kv=kvs[i])
         xn = ln_fwd(c, lt + ".ln3", lp + "layer_norm_ffn", b)
-        nxt = ("%s.%d.ln1" % (tag, i + 1), "%sdec.%d.layer_norm_mha_dec" % (pfx, i + 1)) if i + 1 < NL else (tag + ".lnf", pfx + "layer_norm")
+        nxt = ("%s.%d.ln1" % (tag, i + 1), "%sdec.%d.layer_norm_mha_dec" % (pfx, i + 1), "act") if i + 1 < NL else (tag + ".lnf", pfx + "layer_norm", out_kind)
         x, xn1 = ffn_fwd(c, lt + ".ff", lp + "positionwise_feed_forward.", xn, b, next_ln=nxt)
     c.ws.meta[tag + ".last"] = x
-    if PDL_DECODER:
+    if pdl_prev is not None:
         ops.set_pdl(pdl_prev)
     return xn1
 
 
 def decoder_bwd(c, tag, pfx, dy, ids, enc_out, d_enc_out, enc_ids, B, T, S, NL):
-    """returns grad wrt decoder input; writes (not accumulates) the sum of cross-attention grads into d_enc_out"""
+    """returns the grad wrt the decoder input as an operand; writes (not accumulates) the sum of cross-attention grads into d_enc_out"""
     M, H = dy.shape
     dx = c.ws.buf(tag + ".dx", M, H)
+    dxa = dx_operand(c, tag + ".dx.hi", dx)
     ln_bwd(c, tag + ".lnf", pfx + "layer_norm", dy, c.ws.meta[tag + ".last"], dx, False)
     for i in reversed(range(NL)):
         lt, lp = "%s.%d" % (tag, i), "%sdec.%d." % (pfx, i)
         x_in = c.ws.meta[tag + ".in"] if i == 0 else c.ws["%s.%d.ff.out" % (tag, i - 1)]
         a, b = c.ws[lt + ".sa.out"], c.ws[lt + ".ca.out"]
-        dxn = ffn_bwd(c, lt + ".ff", lp + "positionwise_feed_forward.", dx, c.ws[lt + ".ln3.y"])
-        ln_bwd(c, lt + ".ln3", lp + "layer_norm_ffn", dxn, b, dx, True)
-        dxn = cross_attn_bwd(c, lt + ".ca", lp + "multi_head_attention_enc_dec.", dx, c.ws[lt + ".ln2.y"], enc_out,
+        dxn = ffn_bwd(c, lt + ".ff", lp + "positionwise_feed_forward.", dx, c.ws.act(lt + ".ln3.y"))
+        ln_bwd(c, lt + ".ln3", lp + "layer_norm_ffn", dxn, b, dx, True, dx_act=dxa)
+        dxn = cross_attn_bwd(c, lt + ".ca", lp + "multi_head_attention_enc_dec.", dxa, c.ws.act(lt + ".ln2.y"), enc_out,
                              d_enc_out, i == NL - 1, enc_ids, B, T, S)
-        ln_bwd(c, lt + ".ln2", lp + "layer_norm_mha_enc", dxn, a, dx, True)
-        dxn = self_attn_bwd(c, lt + ".sa", lp + "multi_head_attention_dec.", dx, c.ws[lt + ".ln1.y"], ids, B, T, True)
-        ln_bwd(c, lt + ".ln1", lp + "layer_norm_mha_dec", dxn, x_in, dx, True)
+        ln_bwd(c, lt + ".ln2", lp + "layer_norm_mha_enc", dxn, a, dx, True, dx_act=dxa)
+        dxn = self_attn_bwd(c, lt + ".sa", lp + "multi_head_attention_dec.", dxa, c.ws.act(lt + ".ln1.y"), ids, B, T, True)
+        ln_bwd(c, lt + ".ln1", lp + "layer_norm_mha_dec", dxn, x_in, dx, True, dx_act=dxa if i == 0 else None)
         c.join_side()
         c.ready(lp + "layer_norm_mha_dec.weight")
-    return dx
+    return dx, dxa
 
 
 # ------------------------------------------------------------------ small MLPs
-def linear_fwd(c, tag, pfx, x, relu=False, out=None, fp32_out=False):
-    y = out if out is not None else c.ws.buf(tag, x.shape[0], c.W[pfx + ".weight"].shape[0])
-    ops.gemm(x, c.W[pfx + ".weight"], y, bias=c.P[pfx + ".bias"], relu=relu, fp32_out=fp32_out)
+def linear_fwd(c, tag, pfx, x, relu=False, out=None, planes=False, terms=3):
+    """x: operand.  Returns the fp32 output tensor, or (planes=True) the output as an operand for the next GEMM"""
+    N = c.P[pfx + ".weight"].shape[0]
+    if planes:
+        y = c.act(tag, x.shape[0], N)
+        ops.gemm2(x, c.W[pfx + ".weight"], planes=y, bias=c.P[pfx + ".bias"], relu=relu, terms=terms)
+        return y
+    y = out if out is not None else c.ws.buf(tag, x.shape[0], N)
+    ops.gemm2(x, c.W[pfx + ".weight"], y, bias=c.P[pfx + ".bias"], relu=relu, terms=terms)
     return y
 
 
-def linear_bwd(c, tag, pfx, dy, x, relu_mask=None, need_dx=True, dx=None, accumulate_dx=False):
-    """dy is the grad wrt the (pre-activation) output; relu_mask = post-relu INPUT x when x came out of a relu"""
+def linear_bwd(c, tag, pfx, dy, x, relu_mask=None, need_dx=True, dx=None, accumulate_dx=False, planes=False):
+    """dy: the grad wrt the (pre-activation) output as an operand; x: the layer's input operand; relu_mask = the post-relu INPUT
+    operand when x came out of a relu.  Returns dx as an fp32 tensor, or (planes=True) as an operand for the next backward GEMM."""
     grad_w(c, dy, x, c.G[pfx + ".weight"], c.G[pfx + ".bias"])
     if not need_dx:
         return None
+    K = c.P[pfx + ".weight"].shape[1]
+    if planes:
+        assert dx is None and not accumulate_dx
+        dxa = c.gact(tag, dy.shape[0], K)
+        ops.gemm2(dy, c.W[pfx + ".weight"], planes=dxa, b_t=True, relu_mask=relu_mask, terms=1)
+        return dxa
     if dx is None:
-        dx = c.ws.buf(tag, dy.shape[0], c.W[pfx + ".weight"].shape[1])
+        dx = c.ws.buf(tag, dy.shape[0], K)
     assert not (accumulate_dx and relu_mask is not None)
-    ops.gemm(dy, c.W[pfx + ".weight"], dx, b_t=True, relu_mask=relu_mask, residual=dx if accumulate_dx else None,
-             auto_split=True)   # e.g. z_classifier: 512 x 512 output over K = 15000 -> 4 tiles without split-K
+    ops.gemm2(dy, c.W[pfx + ".weight"], dx, b_t=True, relu_mask=relu_mask, residual=dx if accumulate_dx else None,
+              auto_split=True, terms=1)   # e.g. z_classifier: 512 x 512 output over K = 15000 -> 4 tiles without split-K
     return dx

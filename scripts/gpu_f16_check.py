@@ -83,7 +83,8 @@ def gemm_case(layout, terms):
         e = relerr(out, want)
         ms = time_call(lambda: ops.gemm2(a, b, out, a_t=a_t, b_t=b_t, terms=terms))
         tf = 2.0 * M * N * K / ms * 1e-9
-        good = e < 2e-6
+        tol = 1e-6 + 1.5e-9 * K * terms   # fp32 accumulation in TMEM truncates: the error grows linearly with the number of MMAs
+        good = e < tol
         ok = ok and good
         print("  %-5s terms=%d M=%-6d N=%-6d K=%-6d err %.2e  %.1f us  %.0f TFLOP/s algorithmic (%.0f hw)  %s" % (
             layout, terms, M, N, K, e, ms * 1e3, tf, tf * terms, "ok" if good else "FAIL"), flush=True)
@@ -94,7 +95,7 @@ def gemm_case(layout, terms):
                 ops.gemm2(a, b, acc, a_t=True, b_t=True, accumulate=True, split_k=sk, terms=1)
                 e = relerr(acc, want + 1.0)
                 ms = time_call(lambda: ops.gemm2(a, b, acc, a_t=True, b_t=True, accumulate=True, split_k=sk, terms=1))
-                good = e < 2e-6
+                good = e < tol
                 ok = ok and good
                 print("        split_k=%d accumulate err %.2e  %.1f us  %.0f TFLOP/s %s" % (sk, e, ms * 1e3, 2.0 * M * N * K / ms * 1e-9, "ok" if good else "FAIL"), flush=True)
     return ok
@@ -102,10 +103,11 @@ def gemm_case(layout, terms):
 
 def epilogue_case():
     import torch
-    from blt_vqg_b200 import ops
+    from blt_vqg_b200 import _lib, ops
     torch.manual_seed(1)
     dev = "cuda"
     ok = True
+    _lib.lib().b200iq_set_tf32_rounding(0)   # the standalone dropout kernel used as the mask reference must not round
     for (M, N, K) in [(10240, 2048, 512), (640, 512, 2048), (300, 200, 304), (100, 64, 64)]:
         A, B = torch.randn(M, K, device=dev), torch.randn(N, K, device=dev) * 0.05
         bias = torch.randn(N, device=dev)
@@ -148,7 +150,8 @@ def epilogue_case():
                 o6 = torch.zeros(M, N, device=dev)
                 ops.gemm2(a, b, o6, bias=bias, relu=True, dropout=(0.1, 77, 5 << 40), terms=terms)
                 e5 = max(e5, relerr(o6, ref.double()))
-            good = e1 < 3e-6 and ehi < 6e-4 and e2 < 3e-6 and e3 < 3e-6 and e4 < 6e-4 and e5 < 3e-6
+            tol = 2e-6 + 1.5e-9 * K * terms
+            good = e1 < tol and ehi < 6e-4 and e2 < tol and e3 < tol and e4 < 6e-4 and e5 < tol
             ok = ok and good
             print("  epi M=%d N=%d K=%d terms=%d: planes %.1e (hi only %.1e) f32+planes %.1e residual %.1e gate %.1e dropout %.1e %s" % (
                 M, N, K, terms, e1, ehi, e2, e3, e4, e5, "ok" if good else "FAIL"), flush=True)
