@@ -84,8 +84,8 @@ class IQ(nn.Module):
         self.FEAT = getattr(args, "feat_dim", 512)  # resnet18 fc.in_features (encoder_cnn.py:20)
         self.sos_id = vocab.word2idx[vocab.SYM_SOQ]
         assert vocab.word2idx[vocab.SYM_PAD] == PAD
-        assert self.H % self.nh == 0 and self.H % 4 == 0 and self.E % 4 == 0 and self.V % 4 == 0 and self.L % 2 == 0, \
-            "tcgen05/TMA path needs 16-byte aligned rows (H, E, V multiples of 4)"
+        assert self.H % self.nh == 0 and self.H % 8 == 0 and self.E % 4 == 0 and self.V % 8 == 0 and self.L % 4 == 0 and self.F % 8 == 0, \
+            "tcgen05/TMA path needs 16-byte aligned rows (H, F, V multiples of 8; E, L multiples of 4)"
         self.attn_dropout, self.relu_dropout = 0.1, 0.1  # transformer_layers.py:96-97,163-164 defaults (N4)
         self.arena = Arena()
         transformer_iq_specs(self.arena, self.V, self.E, self.H, self.L, self.F, self.NL, self.FEAT)
@@ -99,11 +99,17 @@ class IQ(nn.Module):
         self.feature_cache = None  # set by attach_feature_cache(): `images` may then be (B,) rows of batch.FeatureCache
         self.trunk = None  # set by attach_trunk(); reference: torchvision resnet18 (encoder_cnn.py:17)
         self.seed = 1234
-        self.step_idx = 0
+        self.seed_rank = 0   # data-parallel rank (parallel.GradReducer.begin_step): ranks draw different masks / eps like DDP replicas do
+        self.step_idx = 0    # stochastic forward passes so far: every training-mode forward / decode draws fresh dropout masks and eps
         self._ws = {}
         self._gflat = None
         self._terms = None
-        self._wflat = None  # TF32-rounded copy of the arena: the GEMM weight operands
+        self._wops = None   # transformer.WeightOperands: fp16 plane arenas (hi, lo) of the weights, or the masters in exact mode
+        self._wops_exact = None
+        # loss scale of the fp16-plane path: every gradient seed is multiplied by it so that activation gradients (~1e-6) sit in
+        # the fp16 normal range as single-plane GEMM operands; folded back out in Adam's grad_scale (train.py) / at the end of the
+        # API backward.  A power of two: exact.
+        self.loss_scale = float(os.environ.get("B200IQ_LOSS_SCALE", "65536"))
         self._ctx = None
         self.on_grad_ready = None  # set by parallel.GradReducer.begin_step
         self.on_grad_range = None  # (lo, hi) pieces that become final out of arena order (the side-stream encoder)
@@ -112,7 +118,7 @@ class IQ(nn.Module):
     def _apply(self, fn, *a, **k):
         super()._apply(fn, *a, **k)
         self.arena.bind(self.flat.data)
-        self._ws, self._gflat, self._terms, self._wflat = {}, None, None, None
+        self._ws, self._gflat, self._terms, self._wops, self._wops_exact = {}, None, None, None, None
         return self
 
     def _buffers_map(self):
@@ -174,15 +180,11 @@ class IQ(nn.Module):
             ws = self._workspace("feats")
             return self.feature_cache.gather(rows, ws.buf("feats", rows.numel(), self.feature_cache.rows.shape[1]))
         if images.dim() == 2:
-            f = images.to(self.flat.device, torch.float32, non_blocking=True).contiguous()
-            if ops.exact_mode():
-                return f
-            return ops.round_tf32(f, self._workspace("feats").buf("feats", *f.shape))
+            return images.to(self.flat.device, torch.float32, non_blocking=True).contiguous()
         if self.trunk is None:
             raise _lib.B200iqError("raw images given but no trunk attached (call attach_trunk, or pass pooled features)")
         with torch.no_grad():
-            f = self.trunk(images.to(self.flat.device)).flatten(1).float().contiguous()
-        return f if ops.exact_mode() else ops.round_tf32(f, f)
+            return self.trunk(images.to(self.flat.device)).flatten(1).float().contiguous()
 
     def _range_marks(self, prefix):
         """Ctx.on_ready callback for a stack that runs beside the main backward: turns its top-down layer marks into
@@ -210,61 +212,94 @@ class IQ(nn.Module):
         if side is not None:
             torch.cuda.current_stream().wait_stream(side)
 
+    def scale(self):
+        """the loss scale in force: 1 in exact mode"""
+        return 1.0 if ops.exact_mode() else self.loss_scale
+
+    def _weights(self):
+        """GEMM weight operands for this step: exact mode = the fp32 masters; else the fp16 planes (hi, lo) of the arena, refreshed
+        from the masters (one streaming pass: 4 B read + 4 B written per parameter, like the TF32 copy it replaces)"""
+        if ops.exact_mode():
+            if self._wops_exact is None:
+                self._wops_exact = tf.WeightOperands(self.arena)
+            return self._wops_exact
+        if self._wops is None:
+            dev = self.flat.device
+            whi = torch.zeros(self.flat.numel(), device=dev, dtype=torch.float16)
+            wlo = torch.zeros(self.flat.numel(), device=dev, dtype=torch.float16)
+            odd = {}
+            for name, shape, _ in self.arena.specs:
+                name = name.replace("#pack", "")
+                if len(shape) == 2 and shape[1] % 8 and name != "embedding.0.weight":
+                    ld = ops.pad8(shape[1])   # TMA needs 16-byte row pitches: E = 300 / L = 100 wide matrices get padded planes
+                    odd[name] = ops.Act(hi=torch.zeros(shape[0], ld, device=dev, dtype=torch.float16)[:, :shape[1]],
+                                        lo=torch.zeros(shape[0], ld, device=dev, dtype=torch.float16)[:, :shape[1]])
+            self._wops = tf.WeightOperands(self.arena, whi, wlo, odd)
+        w = self._wops
+        ops.split_f16(self.flat.data, w.whi, w.wlo)
+        for name, a in w.odd.items():
+            ops.split_f16(self.arena.views[name], a.hi, a.lo)
+        return w
+
+    def _next_seed(self):
+        """Philox key of the next stochastic pass.  The reference draws fresh dropout masks and a fresh torch.randn eps on every
+        call (transformer_layers.py:45,406,520); a counter-based generator needs a new key per call to do the same, so the
+        module counts its own stochastic passes (checkpoint.py saves / restores the counter)."""
+        self.step_idx += 1
+        return self.seed + self.step_idx + 1000003 * self.seed_rank
+
     def _make_ctx(self, B, S, R, T, training):
         _lib.require_device()
-        key = (B, S, R, T, bool(self.latent_transformer), bool(training))
+        key = (B, S, R, T, bool(self.latent_transformer), bool(training), ops.exact_mode())
         ws = self._workspace(key)
-        wflat = None
-        if not ops.exact_mode():
-            # tcgen05 kind::tf32 truncates its operands: feed it round-to-nearest copies of the master weights
-            if self._wflat is None:
-                self._wflat = torch.empty_like(self.flat.data)
-            wflat = ops.round_tf32(self.flat.data, self._wflat)
         c = tf.Ctx(self.arena, self.grad_arena, ws, self.H, self.nh, self.F, self.E, self.attn_dropout,
-                   self.relu_dropout, training, self.seed + self.step_idx, wflat=wflat)
+                   self.relu_dropout, training, self._next_seed(), self._weights())
         c.on_ready = self.on_grad_ready
         return c
 
     def _run_forward(self, c, feats, cids, rids, tids, eps):
-        """models/iq.py:101-112 down to the decoder's final LayerNorm; everything stays in the workspace"""
+        """models/iq.py:101-112 down to the decoder's final LayerNorm; everything stays in the workspace.
+        GEMM operands travel as ops.Act (fp16 planes hi + lo written by their producers; fp32 in exact mode)."""
         ws, P, H, L = c.ws, c.P, self.H, self.L
         B, S, T = feats.shape[0], cids.shape[1], tids.shape[1]
         latent = self.latent_transformer
         m = ws.meta
         # image head: fc + BatchNorm1d (encoder_cnn.py:33-34)
+        feats_a = ops.to_act(ws, "feats.a", feats)
         img_pre = ws.buf("img_pre", B, H)
-        ops.gemm(feats, c.W["encoder_cnn.cnn.fc.weight"], img_pre, bias=P["encoder_cnn.cnn.fc.bias"], fp32_out=True)
+        ops.gemm2(feats_a, c.W["encoder_cnn.cnn.fc.weight"], img_pre, bias=P["encoder_cnn.cnn.fc.bias"])
         img = ws.buf("img", B, H)
         ops.bn_fwd(img_pre, P["encoder_cnn.bn.weight"], P["encoder_cnn.bn.bias"], img, ws.buf("bn.mean", H),
                    ws.buf("bn.rstd", H), self.bn_running_mean, self.bn_running_var, c.training)
         # context encoder (encoder_transformer.py:27-32)
         def context_encoder():
             x = tf.embed_fwd(c, "enc.emb", cids, B, S, self.timing_enc)
-            eo = tf.encoder_fwd(c, "enc", "answer_encoder.encoder.", x, cids, B, S, self.NL)
+            eo = tf.encoder_fwd(c, "enc", "answer_encoder.encoder.", x, cids, B, S, self.NL, out_kind="f32")
             ops.add_timing(eo, None, img, None, B, S, H)  # enc_out[:,0] += image_features
-            return eo
+            return eo, ops.to_act(ws, "enc_out.a", eo)    # the cross-attention K|V projections read it as an operand
         z = None
         # (the two stacks share per-row-count scratch buffers in the backward, so they must differ in length)
         side = self._fork(latent and CONCURRENT_ENCODERS and rids.shape[1] != S)
         if side is None:
-            enc_out = context_encoder()
+            enc_out, enc_a = context_encoder()
         else:
             with torch.cuda.stream(side), _lib.pinned_stream():
-                enc_out = context_encoder()
+                enc_out, enc_a = context_encoder()
         if latent:
             R = rids.shape[1]
             xr = tf.embed_fwd(c, "renc.emb", rids, B, R, self.timing_enc)
-            r_out = tf.encoder_fwd(c, "renc", "answer_encoder.r_encoder.", xr, rids, B, R, self.NL)
+            r_out = tf.encoder_fwd(c, "renc", "answer_encoder.r_encoder.", xr, rids, B, R, self.NL, out_kind="f32")
             self._join(side)
             cat = ws.buf("lat.cat", B, 2 * H)  # cat(x_p, x), transformer_layers.py:52
             ops.tok0_gather(r_out, cat[:, :H], B, R, H)
             ops.tok0_gather(enc_out, cat[:, H:], B, S, H)
+            cat_a = ops.to_act(ws, "lat.cat.a", cat)
             pp, pq = "latent_layer.mean_logvar_prior.", "latent_layer.mean_logvar_posterior."
-            p1 = tf.linear_fwd(c, "lat.p1", pp + "0", cat[:, H:], relu=True)
-            p2 = tf.linear_fwd(c, "lat.p2", pp + "3", p1, relu=True)
+            p1 = tf.linear_fwd(c, "lat.p1", pp + "0", cat_a.cols(H, 2 * H), relu=True, planes=True)
+            p2 = tf.linear_fwd(c, "lat.p2", pp + "3", p1, relu=True, planes=True)
             prior = tf.linear_fwd(c, "lat.prior", pp + "6", p2)
-            q1 = tf.linear_fwd(c, "lat.q1", pq + "0", cat, relu=True)
-            q2 = tf.linear_fwd(c, "lat.q2", pq + "3", q1, relu=True)
+            q1 = tf.linear_fwd(c, "lat.q1", pq + "0", cat_a, relu=True, planes=True)
+            q2 = tf.linear_fwd(c, "lat.q2", pq + "3", q1, relu=True, planes=True)
             post = tf.linear_fwd(c, "lat.post", pq + "6", q2)
             e = ws.buf("lat.eps", B, L)
             if eps is not None:
@@ -273,60 +308,71 @@ class IQ(nn.Module):
                 ops.randn_(e, c.seed, 7 << 40)
             zl = ws.buf("lat.z", B, L)
             ops.latent_fwd(prior, post, e, zl, self.terms[2:3])
-            z = tf.linear_fwd(c, "z", "latent_projection", zl)
+            zl_a = ops.to_act(ws, "lat.z.a", zl)
+            z = tf.linear_fwd(c, "z", "latent_projection", zl_a)
             zimg = ops.axpby(z, img, ws.buf("zimg", B, H))
-            m["z_logit"] = tf.linear_fwd(c, "z_logit", "decoder.z_classifier", zimg, fp32_out=True)
+            zimg_a = ops.to_act(ws, "zimg.a", zimg, lo=False)
+            m["z_logit"] = tf.linear_fwd(c, "z_logit", "decoder.z_classifier", zimg_a, terms=1)
+            m.update(cat_a=cat_a, zl_a=zl_a, zimg_a=zimg_a, p1=p1, p2=p2, q1=q1, q2=q2)
+        else:
+            self._join(side)
         # decoder (decoder_transformer.py:22-38)
         shifted = ws.buf("dec.ids", B, T, dtype=torch.int32)
         shifted[:, 0] = self.sos_id
         shifted[:, 1:] = tids[:, :-1]
         xd = tf.embed_fwd(c, "dec.emb", shifted, B, T, self.timing_dec, add0=img, add1=z)
-        dec_out = tf.decoder_fwd(c, "dec", "decoder.decoder.", xd, shifted, enc_out, cids, B, T, S, self.NL)
+        dec_out = tf.decoder_fwd(c, "dec", "decoder.decoder.", xd, shifted, enc_a, cids, B, T, S, self.NL)
         # image reconstruction (iq.py:109-112)
         rin = ws.buf("rin", B, H)
         ops.tok0_gather(enc_out, rin, B, S, H)
         if latent:
             ops.axpby(rin, z, rin)
-        rh = tf.linear_fwd(c, "rec.h", "image_reconstructor.layers.fc0", rin, relu=True)
-        recon = tf.linear_fwd(c, "rec.out", "image_reconstructor.layers.fc1", rh, fp32_out=True)
-        m.update(img=img, img_pre=img_pre, enc_out=enc_out, z=z, dec_out=dec_out, shifted=shifted, rin=rin, rh=rh,
-                 recon=recon, feats=feats, cids=cids, rids=rids, tids=tids)
+        rin_a = ops.to_act(ws, "rin.a", rin)
+        rh = tf.linear_fwd(c, "rec.h", "image_reconstructor.layers.fc0", rin_a, relu=True, planes=True)
+        recon = tf.linear_fwd(c, "rec.out", "image_reconstructor.layers.fc1", rh)
+        m.update(img=img, img_pre=img_pre, enc_out=enc_out, enc_a=enc_a, z=z, dec_out=dec_out, shifted=shifted, rin_a=rin_a, rh=rh,
+                 recon=recon, feats=feats, feats_a=feats_a, cids=cids, rids=rids, tids=tids)
         return dec_out
 
     def _backward_tail(self, c, d_dec, d_img, d_z, d_recon, kld_coef):
         """everything below the loss seeds: recon MLP, decoder, latent, both encoders, embedder, image head.
-        d_img / d_z are accumulators already holding the seeds from the losses / z_classifier."""
+        d_img / d_z are fp32 accumulators already holding the seeds from the losses / z_classifier.  Every gradient carries
+        the loss scale (self.scale()); backward GEMM operands are single fp16 planes."""
         ws, P, G, H, L = c.ws, c.P, c.G, self.H, self.L
         m = ws.meta
         latent = self.latent_transformer
         B, S, T = m["feats"].shape[0], m["cids"].shape[1], m["tids"].shape[1]
-        d_rh = tf.linear_bwd(c, "d_rh", "image_reconstructor.layers.fc1", d_recon, m["rh"], relu_mask=m["rh"])
-        d_rin = tf.linear_bwd(c, "d_rin", "image_reconstructor.layers.fc0", d_rh, m["rin"])
+        d_recon_a = ops.to_act(ws, "d_recon.a", d_recon, lo=False)
+        d_rh = tf.linear_bwd(c, "d_rh", "image_reconstructor.layers.fc1", d_recon_a, m["rh"], relu_mask=m["rh"], planes=True)
+        d_rin = tf.linear_bwd(c, "d_rin", "image_reconstructor.layers.fc0", d_rh, m["rin_a"])
         c.ready("decoder.z_classifier.weight")  # vocab projections + reconstructor: final, largest bucket goes first
         if latent:
             ops.axpby(d_z, d_rin, d_z)
         d_enc_out = ws.buf("d_enc_out", B * S, H)
-        dxd = tf.decoder_bwd(c, "dec", "decoder.decoder.", d_dec, m["shifted"], m["enc_out"], d_enc_out, m["cids"],
-                             B, T, S, self.NL)
+        dxd, dxd_a = tf.decoder_bwd(c, "dec", "decoder.decoder.", d_dec, m["shifted"], m["enc_a"], d_enc_out, m["cids"],
+                                    B, T, S, self.NL)
         ops.tok0_gather(dxd, d_img, B, T, H, accumulate=True)
         if latent:
             ops.tok0_gather(dxd, d_z, B, T, H, accumulate=True)
-        tf.embed_bwd(c, "dec.emb", m["shifted"], dxd)
+        tf.embed_bwd(c, "dec.emb", m["shifted"], dxd_a)
         ops.tok0_scatter_add(d_rin, d_enc_out, B, S, H)
         if latent:
             R = m["rids"].shape[1]
             pp, pq = "latent_layer.mean_logvar_prior.", "latent_layer.mean_logvar_posterior."
-            d_zl = tf.linear_bwd(c, "d_zl", "latent_projection", d_z, ws["lat.z"])
+            d_z_a = ops.to_act(ws, "d_z.a", d_z, lo=False)
+            d_zl = tf.linear_bwd(c, "d_zl", "latent_projection", d_z_a, m["zl_a"])
             dprior, dpost = ws.buf("d_prior", B, 2 * L), ws.buf("d_post", B, 2 * L)
             ops.latent_bwd(ws["lat.prior"], ws["lat.post"], ws["lat.eps"], d_zl, kld_coef, dprior, dpost)
-            cat = ws["lat.cat"]
+            cat_a = m["cat_a"]
             d_cat = ws.buf("d_cat", B, 2 * H)
-            d_q2 = tf.linear_bwd(c, "d_q2", pq + "6", dpost, ws["lat.q2"], relu_mask=ws["lat.q2"])
-            d_q1 = tf.linear_bwd(c, "d_q1", pq + "3", d_q2, ws["lat.q1"], relu_mask=ws["lat.q1"])
-            tf.linear_bwd(c, None, pq + "0", d_q1, cat, dx=d_cat)
-            d_p2 = tf.linear_bwd(c, "d_p2", pp + "6", dprior, ws["lat.p2"], relu_mask=ws["lat.p2"])
-            d_p1 = tf.linear_bwd(c, "d_p1", pp + "3", d_p2, ws["lat.p1"], relu_mask=ws["lat.p1"])
-            tf.linear_bwd(c, None, pp + "0", d_p1, cat[:, H:], dx=d_cat[:, H:], accumulate_dx=True)
+            dpost_a = ops.to_act(ws, "d_post.a", dpost, lo=False)
+            d_q2 = tf.linear_bwd(c, "d_q2", pq + "6", dpost_a, m["q2"], relu_mask=m["q2"], planes=True)
+            d_q1 = tf.linear_bwd(c, "d_q1", pq + "3", d_q2, m["q1"], relu_mask=m["q1"], planes=True)
+            tf.linear_bwd(c, None, pq + "0", d_q1, cat_a, dx=d_cat)
+            dprior_a = ops.to_act(ws, "d_prior.a", dprior, lo=False)
+            d_p2 = tf.linear_bwd(c, "d_p2", pp + "6", dprior_a, m["p2"], relu_mask=m["p2"], planes=True)
+            d_p1 = tf.linear_bwd(c, "d_p1", pp + "3", d_p2, m["p1"], relu_mask=m["p1"], planes=True)
+            tf.linear_bwd(c, None, pp + "0", d_p1, cat_a.cols(H, 2 * H), dx=d_cat[:, H:], accumulate_dx=True)
             ops.tok0_scatter_add(d_cat[:, H:], d_enc_out, B, S, H)
             c.ready("latent_layer.mean_logvar_prior.0.weight")
 
@@ -360,7 +406,8 @@ class IQ(nn.Module):
         d_img_pre = ws.buf("d_img_pre", B, H)
         ops.bn_bwd(d_img, m["img_pre"], P["encoder_cnn.bn.weight"], ws["bn.mean"], ws["bn.rstd"], d_img_pre,
                    G["encoder_cnn.bn.weight"], G["encoder_cnn.bn.bias"])
-        tf.grad_w(c, d_img_pre, m["feats"], G["encoder_cnn.cnn.fc.weight"], G["encoder_cnn.cnn.fc.bias"])
+        d_img_pre_a = ops.to_act(ws, "d_img_pre.a", d_img_pre, lo=False)
+        tf.grad_w(c, d_img_pre_a, m["feats_a"], G["encoder_cnn.cnn.fc.weight"], G["encoder_cnn.cnn.fc.bias"])
 
     # ------------------------------------------------------------------ fused training path
     def loss_coefs(self, kliter=0):
@@ -379,7 +426,16 @@ class IQ(nn.Module):
     def forward_losses(self, images, answers, response, target, kliter=0, eps=None, backward=True):
         """Forward + losses (train_iq.py:81-103) + full backward, logits never materialised.
         Returns the device tensor of loss terms (rec, img, kld, aux, count, ...); gradients are ACCUMULATED into
-        `self.grad_arena`.  total = rec + c_img*img + c_kld*kld + c_aux*aux (see loss_coefs / total_loss)."""
+        `self.grad_arena` MULTIPLIED BY self.scale() (the loss scale of the fp16-plane path; train.TrainStep folds it into Adam's
+        grad_scale, `unscaled_grads()` gives a plain copy).  total = rec + c_img*img + c_kld*kld + c_aux*aux (loss_coefs / total_loss)."""
+        with ops.no_rounding():
+            return self._forward_losses(images, answers, response, target, kliter, eps, backward)
+
+    def unscaled_grads(self):
+        """the flat gradient arena with the loss scale divided out (tests / inspection)"""
+        return self.grad_arena / self.scale()
+
+    def _forward_losses(self, images, answers, response, target, kliter, eps, backward):
         dev = self.flat.device
         feats = self._features(images)
         cids, tids = _ids(answers, dev), _ids(target, dev)
@@ -391,6 +447,8 @@ class IQ(nn.Module):
         ws, P, G, H, V = c.ws, c.P, c.G, self.H, self.V
         terms = self.terms
         terms.zero_()
+        exact = ops.exact_mode()
+        SC = self.scale()
         pdl_prev = ops.set_pdl(True) if PDL_FORWARD else None
         dec_out = self._run_forward(c, feats, cids, rids, tids, eps)
         m = ws.meta
@@ -402,18 +460,20 @@ class IQ(nn.Module):
         d_dec = ws.buf("d_dec_out", M, H)
         chunk = self._ce_chunk_rows(M)
         logits = ws.buf("logits_chunk", chunk, V)
+        # the chunk's gradient coef * (softmax - onehot) / N: an fp16 plane beside the fp32 logits (exact mode: in place)
+        lgrad = ops.Act(f32=logits) if exact else ops.Act(hi=ws.buf("logits_grad", chunk, V, dtype=torch.float16))
         wout, bout = c.W["decoder.output.weight"], P["decoder.output.bias"]
         for r0 in range(0, M, chunk):
             rows = min(chunk, M - r0)
-            lg, xs = logits[:rows], dec_out[r0:r0 + rows]
-            ops.gemm(xs, wout, lg, bias=bout, fp32_out=True)       # decoder_transformer.py:40
-            ops.ce_rows(lg, tflat[r0:r0 + rows], PAD, count, c_rec, terms[0:1], write_grad=backward)
+            lg, xs, gr = logits[:rows], dec_out.rows(r0, r0 + rows), lgrad.rows(0, rows)
+            ops.gemm2(xs, wout, lg, bias=bout, terms=1)       # decoder_transformer.py:40
+            ops.ce_rows_act(lg, tflat[r0:r0 + rows], PAD, count, c_rec * SC, terms[0:1], gr if backward else None)
             if backward:
                 # dX on the critical path, the vocabulary weight gradient (+ bias column sum) on the side stream under it;
-                # joined before the next chunk's logits overwrite lg
+                # joined before the next chunk's gradient overwrites gr
                 ev = c.mark()
-                ops.gemm(lg, wout, d_dec[r0:r0 + rows], b_t=True, auto_split=True)
-                c.on_side(lambda: tf.grad_w(c, lg, xs, G["decoder.output.weight"], G["decoder.output.bias"]), ev)
+                ops.gemm2(gr, wout, d_dec[r0:r0 + rows], b_t=True, auto_split=True, terms=1)
+                c.on_side(lambda: tf.grad_w(c, gr, xs, G["decoder.output.weight"], G["decoder.output.bias"]), ev)
                 c.join_side()
         if pdl_prev is not None:
             ops.set_pdl(pdl_prev)
@@ -421,16 +481,17 @@ class IQ(nn.Module):
         d_z = None
         if self.latent_transformer:
             dzl = ws.buf("d_z_logit", B, V)
-            ops.ce_aux(m["z_logit"], dzl, tids, PAD, count, c_aux, terms[3:4])
+            ops.ce_aux(m["z_logit"], dzl, tids, PAD, count, c_aux * SC, terms[3:4])
             if backward:
-                d_z = tf.linear_bwd(c, "d_zimg", "decoder.z_classifier", dzl, ws["zimg"])
+                dzl_a = ops.to_act(ws, "d_z_logit.a", dzl, lo=False)
+                d_z = tf.linear_bwd(c, "d_zimg", "decoder.z_classifier", dzl_a, m["zimg_a"])
                 ops.axpby(d_z, d_z, d_img, 1.0, 0.0)
         elif backward:
             d_img.zero_()
         d_recon = ws.buf("d_recon", B, H)
-        ops.mse(m["img"], m["recon"], c_img, terms[1:2], d_img if backward else None, d_recon if backward else None)
+        ops.mse(m["img"], m["recon"], c_img * SC, terms[1:2], d_img if backward else None, d_recon if backward else None)
         if backward:
-            self._backward_tail(c, d_dec, d_img, d_z, d_recon, c_kld)
+            self._backward_tail(c, d_dec, d_img, d_z, d_recon, c_kld * SC)
         return terms
 
     def total_loss(self, terms, kliter=0):
@@ -453,63 +514,71 @@ class IQ(nn.Module):
         return output, z_logit, kld, (img, recon)
 
     def _forward_api(self, feats, cids, rids, tids, eps):
-        B, S, T = feats.shape[0], cids.shape[1], tids.shape[1]
-        R = rids.shape[1] if rids is not None else 0
-        c = self._make_ctx(B, S, R, T, self.training)
-        self._ctx = c
-        self.terms.zero_()
-        dec_out = self._run_forward(c, feats, cids, rids, tids, eps)
-        m = c.ws.meta
-        output = torch.empty(B * T, self.V, device=feats.device)
-        ops.gemm(dec_out, c.W["decoder.output.weight"], output, bias=c.P["decoder.output.bias"], fp32_out=True)
-        if self.latent_transformer:
-            z_logit, kld = m["z_logit"].clone(), self.terms[2].clone()
-        else:
-            z_logit, kld = torch.zeros(1, device=feats.device), torch.zeros((), device=feats.device)
-        return output.view(B, T, self.V), z_logit, kld, m["img"].clone(), m["recon"].clone()
+        with ops.no_rounding():
+            B, S, T = feats.shape[0], cids.shape[1], tids.shape[1]
+            R = rids.shape[1] if rids is not None else 0
+            c = self._make_ctx(B, S, R, T, self.training)
+            self._ctx = c
+            self.terms.zero_()
+            dec_out = self._run_forward(c, feats, cids, rids, tids, eps)
+            m = c.ws.meta
+            output = torch.empty(B * T, self.V, device=feats.device)
+            ops.gemm2(dec_out, c.W["decoder.output.weight"], output, bias=c.P["decoder.output.bias"], terms=1)
+            if self.latent_transformer:
+                z_logit, kld = m["z_logit"].clone(), self.terms[2].clone()
+            else:
+                z_logit, kld = torch.zeros(1, device=feats.device), torch.zeros((), device=feats.device)
+            return output.view(B, T, self.V), z_logit, kld, m["img"].clone(), m["recon"].clone()
 
     def _backward_api(self, d_output, d_z_logit, d_kld, d_img_in, d_recon_in):
+        with ops.no_rounding():
+            return self._backward_api_body(d_output, d_z_logit, d_kld, d_img_in, d_recon_in)
+
+    def _backward_api_body(self, d_output, d_z_logit, d_kld, d_img_in, d_recon_in):
+        """autograd's incoming gradients are multiplied by the loss scale as they become operands; the result is divided by it"""
         c = self._ctx
         ws, m, H = c.ws, c.ws.meta, self.H
         B, T = m["tids"].shape
+        SC = self.scale()
         g = torch.zeros_like(self.flat.data)
         c.gflat = g
         c.G = self.arena.views_over(g, cache=False)
         d_dec = ws.buf("d_dec_out", B * T, H)
         if d_output is not None:
             dout = d_output.reshape(B * T, self.V).contiguous()
-            if not ops.exact_mode():
-                dout = ops.round_tf32(dout, torch.empty_like(dout))
-            ops.gemm(dout, c.W["decoder.output.weight"], d_dec, b_t=True)
-            tf.grad_w(c, dout, m["dec_out"], c.G["decoder.output.weight"], c.G["decoder.output.bias"])
+            if ops.exact_mode():
+                dout_a = ops.Act(f32=dout)
+            else:
+                dout_a = ops.Act(hi=torch.empty(B * T, self.V, device=dout.device, dtype=torch.float16))
+                ops.split_f16(dout, dout_a.hi, None, SC)
+            ops.gemm2(dout_a, c.W["decoder.output.weight"], d_dec, b_t=True, auto_split=True, terms=1)
+            tf.grad_w(c, dout_a, m["dec_out"], c.G["decoder.output.weight"], c.G["decoder.output.bias"])
         else:
             d_dec.zero_()
         d_img = ws.buf("d_img", B, H)
         if d_img_in is not None:
-            d_img.copy_(d_img_in)
+            ops.axpby(d_img_in.contiguous(), d_img_in.contiguous(), d_img, SC, 0.0)
         else:
             d_img.zero_()
         d_z = None
         if self.latent_transformer:
             d_z = ws.buf("d_zimg", B, H)
             if d_z_logit is not None:
-                dzl = d_z_logit.contiguous()
-                if not ops.exact_mode():
-                    dzl = ops.round_tf32(dzl, torch.empty_like(dzl))
-                tf.linear_bwd(c, "d_zimg", "decoder.z_classifier", dzl, ws["zimg"], dx=d_z)
+                dzl_a = ops.to_act(ws, "d_z_logit.a", d_z_logit.contiguous(), lo=False, scale=SC)
+                tf.linear_bwd(c, "d_zimg", "decoder.z_classifier", dzl_a, m["zimg_a"], dx=d_z)
                 ops.axpby(d_img, d_z, d_img)
             else:
                 d_z.zero_()
         d_recon = ws.buf("d_recon", B, H)
         if d_recon_in is not None:
-            d_recon.copy_(d_recon_in)
-            if not ops.exact_mode():
-                ops.round_tf32(d_recon, d_recon)
+            ops.axpby(d_recon_in.contiguous(), d_recon_in.contiguous(), d_recon, SC, 0.0)
         else:
             d_recon.zero_()
-        kld_coef = float(d_kld) if (d_kld is not None and self.latent_transformer) else 0.0
+        kld_coef = float(d_kld) * SC if (d_kld is not None and self.latent_transformer) else 0.0
         self._backward_tail(c, d_dec, d_img, d_z, d_recon, kld_coef)
         c.gflat, c.G = self.grad_arena, None
+        if SC != 1.0:
+            g.mul_(1.0 / SC)
         return g
 
     # ------------------------------------------------------------------ greedy decoding (models/iq.py:117-152)
@@ -526,93 +595,101 @@ class IQ(nn.Module):
         with ops.gemm_mode(simt=exact):
             return self._decode_greedy(images, answers, max_decode_length, eps, kv_cache)
 
-    def _decode_steps_cached(self, c, ys, top_i, top_v, enc_out, cids, img, z, B, S, steps):
+    def _decode_steps_cached(self, c, ys, top_i, top_v, enc_out, enc_a, cids, img, z, B, S, steps):
         """inference_forward (decoder_transformer.py:43-48) for the newest token only, with per-layer K/V caches"""
         ws, P, W, H, V, NL, nh, d = c.ws, c.P, c.W, self.H, self.V, self.NL, self.nh, self.H // self.nh
         pfx = "decoder.decoder."
+        A = lambda name, t, lo=True: ops.to_act(ws, name, t, lo=lo)   # fp32 buffer -> GEMM operand (free in exact mode)
         kc = [ws.buf("kv.k%d" % i, B, steps, H) for i in range(NL)]
         vc = [ws.buf("kv.v%d" % i, B, steps, H) for i in range(NL)]
         ckv = []
         for i in range(NL):   # cross-attention K | V of the context: once per layer instead of once per step
             lp = "%sdec.%d.multi_head_attention_enc_dec." % (pfx, i)
-            ckv.append(ops.gemm(enc_out, c.pspan(lp + "key_linear.weight", lp + "value_linear.weight", H), ws.buf("kv.c%d" % i, B * S, 2 * H)))
-        e1, x = ws.buf("kv.e", B, self.E), ws.buf("kv.x", B, H)
-        xn, qkv, ctx = ws.buf("kv.xn", B, H), ws.buf("kv.qkv", B, 3 * H), ws.buf("kv.ctx", B, H)
-        a, q, b_, h, f2 = ws.buf("kv.a", B, H), ws.buf("kv.q", B, H), ws.buf("kv.b", B, H), ws.buf("kv.h", B, self.F), ws.buf("kv.f2", B, H)
+            ckv.append(ops.gemm2(enc_a, c.pspan(lp + "key_linear.weight", lp + "value_linear.weight", H), ws.buf("kv.c%d" % i, B * S, 2 * H)))
+        e1, x = c.act("kv.e", B, self.E), ws.buf("kv.x", B, H)
+        xn, qkv, ctx = c.act("kv.xn", B, H), ws.buf("kv.qkv", B, 3 * H), c.act("kv.ctx", B, H)
+        a, q, b_, h, f2 = ws.buf("kv.a", B, H), ws.buf("kv.q", B, H), ws.buf("kv.b", B, H), c.act("kv.h", B, self.F), ws.buf("kv.f2", B, H)
         logit = ws.buf("g.logit", B, V)
         ti, tv = ws.buf("g.ti", B, 6, dtype=torch.int32), ws.buf("g.tv", B, 6)
 
         def ln(name, src, dst):
-            ops.layernorm_fwd(src, P[name + ".weight"], P[name + ".bias"], dst, None, None)
+            ops.layernorm_fwd_act(src, P[name + ".weight"], P[name + ".bias"], None, None, act=dst)
         for p in range(steps):
             n = p + 1
             tok = ys[:, p].contiguous()
             prefix = ys[:, :n].contiguous()
-            ops.embed_gather(tok, P["embedding.0.weight"], e1)
-            ops.gemm(e1, W["embedding.1.weight"], x, bias=P["embedding.1.bias"])
+            ops.embed_gather_act(tok, P["embedding.0.weight"], e1)
+            ops.gemm2(e1, W["embedding.1.weight"], x, bias=P["embedding.1.bias"])
             # timing signal of position p; token 0 also gets z + image_features (decoder_transformer.py:46)
             ops.add_timing(x, self.timing_dec[p:p + 1], z if p == 0 else None, img if p == 0 else None, B, 1, H)
             for i in range(NL):
                 lp = "%sdec.%d." % (pfx, i)
                 sa, ca, ff = lp + "multi_head_attention_dec.", lp + "multi_head_attention_enc_dec.", lp + "positionwise_feed_forward."
                 ln(lp + "layer_norm_mha_dec", x, xn)
-                ops.gemm(xn, c.pspan(sa + "query_linear.weight", sa + "value_linear.weight", H), qkv)
+                ops.gemm2(xn, c.pspan(sa + "query_linear.weight", sa + "value_linear.weight", H), qkv)
                 kc[i][:, p].copy_(qkv[:, H:2 * H])
                 vc[i][:, p].copy_(qkv[:, 2 * H:])
                 # every cached key is at or before the query's position: the causal part of the mask is implied
                 ops.attention_fwd(qkv[:, :H], kc[i].view(B * steps, H), vc[i].view(B * steps, H), ctx, prefix, PAD, False, B, nh, 1, n, d,
                                   kv_batch_stride=steps * H)
-                ops.gemm(ctx, W[sa + "output_linear.weight"], a, residual=x)
+                ops.gemm2(ctx, W[sa + "output_linear.weight"], a, residual=x)
                 ln(lp + "layer_norm_mha_enc", a, xn)
-                ops.gemm(xn, W[ca + "query_linear.weight"], q)
+                ops.gemm2(xn, W[ca + "query_linear.weight"], q)
                 ops.attention_fwd(q, ckv[i][:, :H], ckv[i][:, H:], ctx, cids, PAD, False, B, nh, 1, S, d)
-                ops.gemm(ctx, W[ca + "output_linear.weight"], b_, residual=a)
+                ops.gemm2(ctx, W[ca + "output_linear.weight"], b_, residual=a)
                 ln(lp + "layer_norm_ffn", b_, xn)
-                ops.gemm(xn, W[ff + "layers.0.weight"], h, bias=P[ff + "layers.0.bias"], relu=True)
-                ops.gemm(h, W[ff + "layers.1.weight"], f2, bias=P[ff + "layers.1.bias"], relu=True)
+                ops.gemm2(xn, W[ff + "layers.0.weight"], planes=h, bias=P[ff + "layers.0.bias"], relu=True)
+                ops.gemm2(h, W[ff + "layers.1.weight"], f2, bias=P[ff + "layers.1.bias"], relu=True)
                 ops.axpby(b_, f2, x)
             ln(pfx + "layer_norm", x, xn)
-            ops.gemm(xn, W["decoder.output.weight"], logit, bias=P["decoder.output.bias"], fp32_out=True)
+            ops.gemm2(xn, W["decoder.output.weight"], logit, bias=P["decoder.output.bias"], terms=1)
             ops.topk_softmax_rows(logit, 6, ti, tv)                           # iq.py:136-137
             ys[:, n] = ti[:, 0]
             top_i[:, p] = ti
             top_v[:, p] = tv
 
     def _decode_greedy(self, images, answers, max_decode_length, eps, kv_cache=True):
+        with ops.no_rounding():
+            return self._decode_greedy_body(images, answers, max_decode_length, eps, kv_cache)
+
+    def _decode_greedy_body(self, images, answers, max_decode_length, eps, kv_cache=True):
         dev = self.flat.device
         was_training = self.training
         self.eval()
+        wkey = None
         try:
             feats = self._features(images)
             cids = _ids(answers, dev)
             B, S, H, L, V = feats.shape[0], cids.shape[1], self.H, self.L, self.V
             steps = max_decode_length + 1
             c = self._make_ctx(B, S, 0, steps, False)
+            wkey = (B, S, 0, steps, bool(self.latent_transformer), False, ops.exact_mode())
             ws, P = c.ws, c.P
             img_pre = ws.buf("img_pre", B, H)
-            ops.gemm(feats, c.W["encoder_cnn.cnn.fc.weight"], img_pre, bias=P["encoder_cnn.cnn.fc.bias"], fp32_out=True)
+            ops.gemm2(ops.to_act(ws, "feats.a", feats), c.W["encoder_cnn.cnn.fc.weight"], img_pre, bias=P["encoder_cnn.cnn.fc.bias"])
             img = ws.buf("img", B, H)
             ops.bn_fwd(img_pre, P["encoder_cnn.bn.weight"], P["encoder_cnn.bn.bias"], img, ws.buf("bn.mean", H), ws.buf("bn.rstd", H),
                        self.bn_running_mean, self.bn_running_var, False)
             x = tf.embed_fwd(c, "enc.emb", cids, B, S, self.timing_enc)
-            enc_out = tf.encoder_fwd(c, "enc", "answer_encoder.encoder.", x, cids, B, S, self.NL)
+            enc_out = tf.encoder_fwd(c, "enc", "answer_encoder.encoder.", x, cids, B, S, self.NL, out_kind="f32")
             ops.add_timing(enc_out, None, img, None, B, S, H)
+            enc_a = ops.to_act(ws, "enc_out.a", enc_out)
             z = None
             if self.latent_transformer:
                 x0 = ws.buf("g.x0", B, H)
                 ops.tok0_gather(enc_out, x0, B, S, H)
                 pp = "latent_layer.mean_logvar_prior."
-                p1 = tf.linear_fwd(c, "lat.p1", pp + "0", x0, relu=True)
-                p2 = tf.linear_fwd(c, "lat.p2", pp + "3", p1, relu=True)
-                prior = tf.linear_fwd(c, "lat.prior", pp + "6", p2, fp32_out=True)
+                p1 = tf.linear_fwd(c, "lat.p1", pp + "0", ops.to_act(ws, "g.x0.a", x0), relu=True, planes=True)
+                p2 = tf.linear_fwd(c, "lat.p2", pp + "3", p1, relu=True, planes=True)
+                prior = tf.linear_fwd(c, "lat.prior", pp + "6", p2)
                 e = ws.buf("lat.eps", B, L)
                 if eps is not None:
                     e.copy_(eps)
                 else:
-                    ops.randn_(e, self.seed + self.step_idx, 11 << 40)
+                    ops.randn_(e, c.seed, 11 << 40)
                 zl = ws.buf("lat.z", B, L)
                 ops.latent_fwd(prior, None, e, zl, None)                     # Latent(x, None): sample from the prior (iq.py:126)
-                z = tf.linear_fwd(c, "z", "latent_projection", zl)
+                z = tf.linear_fwd(c, "z", "latent_projection", ops.to_act(ws, "lat.z.a", zl))
             ys = torch.full((B, steps + 1), PAD, dtype=torch.int32, device=dev)  # prefix: ys[:, 0] = PAD (iq.py:129)
             top_i = torch.zeros(B, steps, 6, dtype=torch.int32, device=dev)
             top_v = torch.zeros(B, steps, 6, device=dev)
@@ -620,15 +697,15 @@ class IQ(nn.Module):
             logit = ws.buf("g.logit", B, V)
             ti, tv = ws.buf("g.ti", B, 6, dtype=torch.int32), ws.buf("g.tv", B, 6)
             if kv_cache:
-                self._decode_steps_cached(c, ys, top_i, top_v, enc_out, cids, img, z, B, S, steps)
+                self._decode_steps_cached(c, ys, top_i, top_v, enc_out, enc_a, cids, img, z, B, S, steps)
             else:
                 for i in range(steps):
                     n = i + 1
                     prefix = ys[:, :n].contiguous()
                     xd = tf.embed_fwd(c, "g.emb", prefix, B, n, self.timing_dec, add0=z, add1=img)   # decoder_transformer.py:46
-                    dec = tf.decoder_fwd(c, "g", "decoder.decoder.", xd, prefix, enc_out, cids, B, n, S, self.NL)
+                    dec = tf.decoder_fwd(c, "g", "decoder.decoder.", xd, prefix, enc_a, cids, B, n, S, self.NL, out_kind="f32")
                     ops.tok0_gather(dec[n - 1:], last, B, n, H)                    # logits[:, -1]
-                    ops.gemm(last, c.W["decoder.output.weight"], logit, bias=P["decoder.output.bias"], fp32_out=True)
+                    ops.gemm2(ops.to_act(ws, "g.last.a", last, lo=False), c.W["decoder.output.weight"], logit, bias=P["decoder.output.bias"], terms=1)
                     ops.topk_softmax_rows(logit, 6, ti, tv)                       # iq.py:136-137
                     ys[:, n] = ti[:, 0]
                     top_i[:, i] = ti
@@ -636,7 +713,8 @@ class IQ(nn.Module):
             ids = ys[:, 1:].cpu()
         finally:
             self.train(was_training)
-            self._ws.pop((B, S, 0, steps, bool(self.latent_transformer), False), None)  # decode buffers are not kept
+            if wkey is not None:
+                self._ws.pop(wkey, None)  # decode buffers are not kept
         eos = self.vocab.word2idx[self.vocab.SYM_EOS]
         sentences = []
         for row in ids.tolist():                                              # iq.py:144-151

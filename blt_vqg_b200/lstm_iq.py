@@ -11,8 +11,10 @@ Blocks and the reference code each replaces:
 The wiring (z from MLP(cat(img, ans)); h0 = c0 = MLP(img + W z); reconstructions from a second reparameterisation of the
 DETACHED features) is the call-site contract restated in oracle/lstm_oracle.py (the glue is not in the reference tree).
 
-All arithmetic runs in libb200iq.so.  The recurrence is time-major: one GEMM projects the inputs of all T steps, each step
-is one tcgen05 GEMM (h.W_hh^T + x-projection, residual epilogue) + one cell kernel, and every weight gradient is one GEMM
+All arithmetic runs in libb200iq.so.  The recurrence is time-major: one GEMM projects the inputs of all T steps; the T
+dependent steps then run inside ONE persistent cluster kernel (lstm_seq.cu: W_hh resident in shared memory, forward and
+BPTT each one launch) wherever b200iq_lstm_seq_supported(H) — the per-step pair "tcgen05 GEMM (h.W_hh^T + x-projection,
+residual epilogue) + cell kernel" is the fallback for other widths and for exact mode; every weight gradient is one GEMM
 over all T*B rows.  State-dict names follow the upstream module tree (see oracle/lstm_oracle.py).
 """
 import math
@@ -24,7 +26,7 @@ import torch
 import torch.nn as nn
 
 from . import _lib, ops
-from . import transformer as tf
+from . import tf32_blocks as tf
 from .params import Arena, export_state_dict, import_state_dict
 
 PAD = 0
@@ -112,7 +114,9 @@ class LSTMIQ(nn.Module):
         # what train.TrainStep reads
         self.args = SimpleNamespace(num_pretraining_steps=-1)
         self.latent_transformer = True
-        self.seed, self.step_idx = 1234, 0
+        # step_idx counts this module's stochastic passes: every context (a training step, or a stage call of the staged API)
+        # draws a fresh Philox key, like the reference's nn.Dropout / torch.randn draw fresh numbers on every call
+        self.seed, self.seed_rank, self.step_idx = 1234, 0, 0
         self.on_grad_ready = None
         self._ws, self._gflat, self._terms, self._wflat = {}, None, None, None
 
@@ -173,7 +177,9 @@ class LSTMIQ(nn.Module):
             if self._wflat is None:
                 self._wflat = torch.empty_like(self.flat.data)
             wflat = ops.round_tf32(self.flat.data, self._wflat)
-        c = tf.Ctx(self.arena, self.grad_arena, ws, self.H, 1, self.A, self.H, 0.0, 0.0, training, self.seed + self.step_idx, wflat=wflat)
+        self.step_idx += 1
+        c = tf.Ctx(self.arena, self.grad_arena, ws, self.H, 1, self.A, self.H, 0.0, 0.0, training,
+                   self.seed + self.step_idx + 1000003 * self.seed_rank, wflat=wflat)
         c.on_ready = self.on_grad_ready
         c.in_drop = self.input_dropout_p if training else 0.0
         return c

@@ -52,6 +52,7 @@ class GradReducer:
         self.sent, self.range_pending = [], None
         model.on_grad_ready = self.mark_ready
         model.on_grad_range = self.mark_range
+        model.seed_rank = self.rank   # every rank draws its own dropout masks / latent eps, like DDP replicas
 
     def _send(self, lo, hi):
         if hi <= lo:

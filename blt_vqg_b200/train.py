@@ -44,8 +44,10 @@ class TrainStep:
     def set_hyper(self):
         lr = self.lr_fn(self.iter)
         t = self.t + 1
+        # grad_scale: the data-parallel mean and the loss scale of the fp16-plane path (IQ.scale()) leave the gradients here
+        scale = self.model.scale() if hasattr(self.model, "scale") else 1.0
         ops.set_hyper(self.hyper, lr, 1.0 - self.betas[0] ** t, 1.0 - self.betas[1] ** t,
-                      1.0 / (self.dp.world_size if self.dp is not None else 1))
+                      1.0 / ((self.dp.world_size if self.dp is not None else 1) * scale))
 
     def step(self, images, answers, response, target, eps=None):
         """returns the device tensor of loss terms (rec, img, kld, aux, count, gnorm_sq, ...) of this step"""
@@ -74,8 +76,10 @@ class TrainStep:
     def _step_body(self, images, answers, response, target, eps):
         m = self.model
         a = m.args
-        if self.iter == getattr(a, "num_pretraining_steps", -1) and not m.latent_transformer:
-            m.switch_GVT_train_mode(True)  # train_iq.py:108-110
+        if 0 <= getattr(a, "num_pretraining_steps", -1) <= self.iter and not m.latent_transformer:
+            # train_iq.py:108-110 switches when iter == num_pretraining_steps; ">=" also covers a run resumed from a checkpoint
+            # taken after the switch (the reference's checkpoint carries no mode flag)
+            m.switch_GVT_train_mode(True)
         self.set_hyper()
         if self.dp is not None:
             self.dp.begin_step(m)
@@ -90,5 +94,4 @@ class TrainStep:
         self.t += 1
         if m.latent_transformer:
             self.kliter += 1
-        m.step_idx += 1
         return terms

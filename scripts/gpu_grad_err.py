@@ -52,7 +52,7 @@ def run(name, B=None, latent=True):
         m.load_state_dict(sd); m.attn_dropout = m.relu_dropout = 0.0
         with ops.gemm_mode(simt=simt):
             t = m.forward_losses(batch["feats"], batch["answers"], batch["posteriors"], batch["questions"], kliter=7000, eps=eps.cuda()).cpu()
-        g = {n: m.arena.view_of(m.grad_arena, n).double().cpu() for n in m.arena.names()}
+        g = {n: m.arena.view_of(m.unscaled_grads(), n).double().cpu() for n in m.arena.names()}
         report("ours exact" if simt else "ours tf32", g, truth)
 
 run("tiny"); run("small"); run("cfg1", B=32); run("cfg1", B=32, latent=False)

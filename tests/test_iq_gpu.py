@@ -4,11 +4,12 @@ reference and (b) the oracle restatement on seeded synthetic batches.
 Tolerances, stated per path (BASELINE.json north_star: losses 1e-3 rel, gradients 2e-3 rel, "bf16/TF32 tolerance stated
 per kernel"):
   exact path (CUDA-core fp32 GEMMs, no rounding):  losses 1e-4, every gradient tensor 2e-4 (north_star bar: 2e-3).
-  tensor-core path (tcgen05 kind::tf32, operands rounded to nearest TF32): losses 1e-3; gradients carry the 10-bit
-  mantissa noise of ~50-180 chained GEMMs, measured (scripts/gpu_grad_err.py, vs an fp64 oracle) at 1.6e-3..1.3e-2 of
-  the global gradient norm and up to 5.5e-2 on single small tensors -- the same as the reference itself run with
-  torch's TF32 matmuls (cuBLAS) on the same B200 (1.3e-3..1.25e-2 / 4.4e-2).  The test bars: global 2e-2, per tensor
-  8e-2, and never worse than 1.5x torch-TF32's own error on the same inputs."""
+  tensor-core path (the timed one: tcgen05 kind::f16 on fp16 operand planes): forward products are 3-term (hi.hi + lo.hi +
+  hi.lo, ~2^-21 per operand), backward products single-pass (11 bits) under a 2^16 loss scale, attention forward 3-term TF32.
+  Why that split: 11-bit FORWARD operands flip ReLU gates and that alone puts ~1e-2 of error on the gradients, 11-bit backward
+  operands cost ~3e-4 (profiles/r02a_cpu_precision_study.txt).  Bars: losses 1e-3, global gradient error 2e-3 (north_star),
+  every tensor 2e-3 except a justified allowance of 4e-3 for tensors directly below a ReLU gate at full depth (gate flips
+  give sqrt(eps) errors: even an fp32 run differs from fp64 by ~1e-3 there); full-size tests print the measured values."""
 import math
 import os
 
@@ -51,14 +52,15 @@ def _build(cfg, latent, sd, dropout=False):
     return m
 
 
-TOL = {True: dict(loss=1e-4, tensor=2e-4, glob=2e-4), False: dict(loss=1e-3, tensor=8e-2, glob=2e-2)}  # keyed by simt
+TOL = {True: dict(loss=1e-4, tensor=2e-4, glob=2e-4), False: dict(loss=1e-3, tensor=4e-3, glob=2e-3)}  # keyed by simt
 
 
 def _check_grads(m, ref_grads, tol_tensor, tol_global, gflat=None):
     """per-tensor and global relative error of the flat gradient arena vs reference gradients; returns the global error"""
-    gflat = m.grad_arena if gflat is None else gflat
+    gflat = m.unscaled_grads() if gflat is None else gflat
     seen = set()
     num = den = 0.0
+    worst = (0.0, "")
     for k, gref in ref_grads.items():
         name = _canon(k)
         if name in seen:
@@ -75,8 +77,11 @@ def _check_grads(m, ref_grads, tol_tensor, tol_global, gflat=None):
             continue
         num += d * d
         den += float(gref.double().norm()) ** 2
-        assert d / (float(gref.double().norm()) + 1e-30) < tol_tensor or float((g.cpu() - gref.cpu()).abs().max()) < 1e-6, (name, d)
+        r = d / (float(gref.double().norm()) + 1e-30)
+        worst = max(worst, (r, name))
+        assert r < tol_tensor or float((g.cpu() - gref.cpu()).abs().max()) < 1e-6, (name, r)
     glob = (num / den) ** 0.5
+    print("gradient error: global %.3e, worst tensor %.3e (%s)" % (glob, worst[0], worst[1]))
     assert glob < tol_global, glob
     return glob
 
@@ -159,12 +164,59 @@ def test_training_step_matches_oracle_small(env, latent, size):
         num += float((Pg[k].grad.double().cpu() - g.double()).norm()) ** 2
         den += float(g.double().norm()) ** 2
     torch_tf32 = (num / den) ** 0.5
-    print("global gradient error: ours %.3e, torch TF32 %.3e" % (ours, torch_tf32))
-    # T = 64: cuBLAS runs torch's 64 x 64 x 64 attention matmuls without rounding their operands, ours rounds P / dS to TF32 for the
-    # tensor-core products; measured 1.32e-2 (9.2e-3 with B200IQ_ATT_SIMT=1) against torch's 8.1e-3 — a wider yardstick for
-    # that one configuration, the absolute bars above (global 2e-2, per tensor 8e-2, losses 1e-3) are the same for all
-    factor = 1.75 if size == "long" else 1.5
-    assert ours <= factor * torch_tf32 + 1e-3, (ours, torch_tf32)
+    print("global gradient error: ours %.3e, torch TF32 (cuBLAS, the stock Blackwell path) %.3e" % (ours, torch_tf32))
+    assert ours <= torch_tf32, (ours, torch_tf32)
+
+
+def _oracle_step_on_gpu(cfg, latent, sd, batch, eps, kliter, dtype=torch.float64):
+    """the oracle restatement of the reference step executed on this GPU in fp64 (SURVEY 8c pin (ii)/(iii): full-size dumps are
+    regenerated on the fly): returns (loss terms, {name: gradient})"""
+    from oracle import iq_oracle
+    ocfg = dict(num_layers=cfg["NL"], num_heads=cfg["NH"], latent_dim=cfg["L"], image_recon_lambda=0.1, kl_ceiling=0.5,
+                aux_ceiling=1.0, full_kl_step=15000)
+    P = {k: (v.to("cuda", dtype) if v.dtype.is_floating_point else v.cuda()).clone() for k, v in sd.items()}
+    for k, v in P.items():
+        if v.dtype.is_floating_point and "running" not in k:
+            v.requires_grad_(True)
+    bn = (P["encoder_cnn.bn.running_mean"].detach().clone(), P["encoder_cnn.bn.running_var"].detach().clone())
+    b = {k: v.cuda() for k, v in batch.items()}
+    out, zl, kld, img, recon = iq_oracle.iq_forward(P, ocfg, b["feats"].to(dtype), b["answers"], b["posteriors"], b["questions"],
+                                                    eps=eps.to("cuda", dtype), latent_mode=latent, training=True, bn_state=bn)
+    loss, tr = iq_oracle.iq_losses(ocfg, out, zl, kld, img, recon, b["questions"], kliter, latent)
+    loss.backward()
+    grads = {k: v.grad.detach() for k, v in P.items() if v.requires_grad and v.grad is not None}
+    terms = {k: float(v) for k, v in tr.items()}
+    del out, zl, loss
+    torch.cuda.empty_cache()
+    return terms, grads
+
+
+@pytest.mark.parametrize("name", ["cfg1", "cfg3", "cfg5"])
+def test_full_size_training_step_matches_fp64_oracle(env, name):
+    """BASELINE.json configs at their OWN size on the timed (tensor-core) path: cfg1's sizes on the transformer variant (B=32),
+    cfg3 (configs[2]: B=512, 6 layers, V=15000 — the bench workload) and cfg5's per-GPU shard (configs[4]: V=32000, T=64, B=128),
+    every loss term and every gradient tensor against the oracle run in fp64 on this GPU.  north_star bars: losses 1e-3,
+    gradients 2e-3."""
+    from blt_vqg_b200 import synth
+    from blt_vqg_b200.iq import IQ
+    cfg = synth.CONFIGS[name]
+    batch = synth.make_batch(cfg, seed=11)
+    torch.manual_seed(3)
+    m0 = IQ(True, synth.SynthVocab(cfg["V"]), synth.args_for(cfg))
+    sd = {k: v.clone() for k, v in m0.state_dict().items()}
+    names = set(m0.arena.names())
+    del m0
+    eps = torch.randn(cfg["B"], cfg["L"])
+    want, grads = _oracle_step_on_gpu(cfg, True, sd, batch, eps, 7000)
+    grads = {k: g for k, g in grads.items() if k in names}
+    m = _build(cfg, True, sd)
+    terms = m.forward_losses(batch["feats"], batch["answers"], batch["posteriors"], batch["questions"], kliter=7000, eps=eps.cuda())
+    t = terms.cpu()
+    errs = {k: abs(float(t[i]) - want[k]) / abs(want[k]) for i, k in enumerate(("rec", "img", "kld", "aux"))}
+    print("%s loss-term errors vs fp64: %s" % (name, {k: "%.1e" % v for k, v in errs.items()}))
+    assert max(errs.values()) < 1e-3, errs
+    assert float(m.total_loss(t, 7000)) == pytest.approx(want["loss"], rel=1e-3)
+    _check_grads(m, grads, TOL[False]["tensor"], TOL[False]["glob"])
 
 
 def test_api_forward_returns_reference_tuple_and_autograd_works(env, golden_dir):
@@ -247,17 +299,23 @@ def test_dropout_training_mode_runs_and_is_reproducible(env):
     torch.manual_seed(7)
     m = IQ(True, synth.SynthVocab(cfg["V"]), synth.args_for(cfg)).cuda().train()
     b = synth.make_batch(cfg)
+    m.step_idx = 40
     t1 = m.forward_losses(b["feats"], b["answers"], b["posteriors"], b["questions"]).clone()
     g1 = m.grad_arena.clone()
     m.grad_arena.zero_()
+    m.step_idx = 40   # the counter of stochastic passes is the Philox key: restoring it (checkpoint.py does) replays the pass
     t2 = m.forward_losses(b["feats"], b["answers"], b["posteriors"], b["questions"]).clone()
     assert torch.isfinite(t1).all() and torch.isfinite(g1).all()
-    assert torch.allclose(t1[:4], t2[:4], rtol=1e-5)  # same (seed, step) -> same Philox masks and eps
+    assert torch.allclose(t1[:4], t2[:4], rtol=1e-5)  # same (seed, counter) -> same Philox masks and eps
     assert rel(m.grad_arena, g1) < 1e-4
-    m.step_idx += 1
+    # two consecutive calls draw fresh dropout masks and a fresh eps, like nn.Dropout / torch.randn in the reference
     m.grad_arena.zero_()
     t3 = m.forward_losses(b["feats"], b["answers"], b["posteriors"], b["questions"])
-    assert not torch.allclose(t1[:4], t3[:4], rtol=1e-7)
+    assert m.step_idx == 42 and not torch.allclose(t2[:4], t3[:4], rtol=1e-7)
+    # ... and so does the module-level drop-in path (IQ.forward under autograd), with no TrainStep involved
+    o1 = m(b["feats"], b["answers"], b["posteriors"], b["questions"])[0].detach().clone()
+    o2 = m(b["feats"], b["answers"], b["posteriors"], b["questions"])[0].detach()
+    assert m.step_idx == 44 and not torch.allclose(o1, o2, rtol=1e-6)
 
 
 @pytest.mark.parametrize("mode", ["latent", "pretrain"])
@@ -323,7 +381,7 @@ def test_full_size_fused_path_equals_api_path_and_trains(env):
     B, T, V = cfg["B"], cfg["T"], cfg["V"]
     m.grad_arena.zero_()
     terms = m.forward_losses(b["feats"], b["answers"], b["posteriors"], b["questions"], kliter=7000, eps=eps).clone()
-    g_fused = m.grad_arena.clone()
+    g_fused = m.unscaled_grads()
     m.grad_arena.zero_()
     output, z_logit, kld, (img, recon) = m(b["feats"], b["answers"], b["posteriors"], b["questions"], eps=eps)
     tgt = b["questions"].long()
@@ -364,6 +422,7 @@ def test_programmatic_dependent_launch_changes_nothing(env):
         prev = ops.set_pdl(on)
         try:
             m.grad_arena.zero_()
+            m.step_idx = 7   # same Philox key for the three passes (dropout is on)
             t = m.forward_losses(b["feats"], b["answers"], b["posteriors"], b["questions"], kliter=7000, eps=eps).clone()
             torch.cuda.synchronize()
         finally:
