@@ -246,7 +246,7 @@ def gemm_roofline(ts, model, args, dev_batches, peaks):
         d[2] += fl
         d[3] += by
     top = sorted(by_shape.items(), key=lambda kv: -kv[1][1])[:int(os.environ.get("B200IQ_GEMM_ROWS", "12"))]
-    detail = [{"M": k[0], "N": k[1], "K": k[2], "flags": k[3], "split_k": k[4], "launches": v[0], "ms": round(v[1], 4),
+    detail = [{"M": k[0], "N": k[1], "K": k[2], "flags": k[3], "split_k": k[4], "terms": k[5] if len(k) > 5 else "tf32", "launches": v[0], "ms": round(v[1], 4),
                "tflops": round(v[2] / v[1] * 1e-9, 1) if v[1] > 0 else None,
                "operand_gbs": round(v[3] / v[1] * 1e-6, 1) if v[1] > 0 else None} for k, v in top]
     peak = peaks.get("bf16_tflops_sustained") or 1400.0

@@ -109,7 +109,9 @@ class IQ(nn.Module):
         # loss scale of the fp16-plane path: every gradient seed is multiplied by it so that activation gradients (~1e-6) sit in
         # the fp16 normal range as single-plane GEMM operands; folded back out in Adam's grad_scale (train.py) / at the end of the
         # API backward.  A power of two: exact.
-        self.loss_scale = float(os.environ.get("B200IQ_LOSS_SCALE", "65536"))
+        # Default (loss_scale = 0): 16 x 2^floor(log2(B*T/2)) — the largest seed, (softmax - onehot) / N_tokens, then sits near 2^4
+        # whatever the batch (cfg3: 65536), with 2^12 of headroom below the fp16 maximum.
+        self.loss_scale = float(os.environ.get("B200IQ_LOSS_SCALE", "0"))
         self._ctx = None
         self.on_grad_ready = None  # set by parallel.GradReducer.begin_step
         self.on_grad_range = None  # (lo, hi) pieces that become final out of arena order (the side-stream encoder)
@@ -212,9 +214,16 @@ class IQ(nn.Module):
         if side is not None:
             torch.cuda.current_stream().wait_stream(side)
 
-    def scale(self):
-        """the loss scale in force: 1 in exact mode"""
-        return 1.0 if ops.exact_mode() else self.loss_scale
+    def scale(self, tokens=None):
+        """the loss scale in force: 1 in exact mode; else self.loss_scale, or (loss_scale = 0) the power of two chosen from the
+        number of target tokens of the batch.  Without `tokens`: the scale of the last pass."""
+        if ops.exact_mode():
+            return 1.0
+        if self.loss_scale > 0:
+            return self.loss_scale
+        if tokens is None:
+            return getattr(self, "_grad_scale", 1.0)
+        return 16.0 * 2.0 ** math.floor(math.log2(max(1.0, tokens / 2.0)))
 
     def _weights(self):
         """GEMM weight operands for this step: exact mode = the fp32 masters; else the fp16 planes (hi, lo) of the arena, refreshed
@@ -432,8 +441,8 @@ class IQ(nn.Module):
             return self._forward_losses(images, answers, response, target, kliter, eps, backward)
 
     def unscaled_grads(self):
-        """the flat gradient arena with the loss scale divided out (tests / inspection)"""
-        return self.grad_arena / self.scale()
+        """the flat gradient arena with the loss scale of the pass that filled it divided out (tests / inspection)"""
+        return self.grad_arena / getattr(self, "_grad_scale", 1.0)
 
     def _forward_losses(self, images, answers, response, target, kliter, eps, backward):
         dev = self.flat.device
@@ -448,7 +457,7 @@ class IQ(nn.Module):
         terms = self.terms
         terms.zero_()
         exact = ops.exact_mode()
-        SC = self.scale()
+        SC = self._grad_scale = self.scale(B * T)
         pdl_prev = ops.set_pdl(True) if PDL_FORWARD else None
         dec_out = self._run_forward(c, feats, cids, rids, tids, eps)
         m = ws.meta
@@ -539,7 +548,7 @@ class IQ(nn.Module):
         c = self._ctx
         ws, m, H = c.ws, c.ws.meta, self.H
         B, T = m["tids"].shape
-        SC = self.scale()
+        SC = self.scale(B * T)
         g = torch.zeros_like(self.flat.data)
         c.gflat = g
         c.G = self.arena.views_over(g, cache=False)

@@ -52,6 +52,8 @@ class GradReducer:
         self.sent, self.range_pending = [], None
         model.on_grad_ready = self.mark_ready
         model.on_grad_range = self.mark_range
+        if hasattr(model, "seed_rank"):
+            model.seed_rank = self.rank   # replicas draw different dropout masks / eps, like DDP processes do
         model.seed_rank = self.rank   # every rank draws its own dropout masks / latent eps, like DDP replicas
 
     def _send(self, lo, hi):

@@ -44,8 +44,9 @@ class TrainStep:
     def set_hyper(self):
         lr = self.lr_fn(self.iter)
         t = self.t + 1
-        # grad_scale: the data-parallel mean and the loss scale of the fp16-plane path (IQ.scale()) leave the gradients here
-        scale = self.model.scale() if hasattr(self.model, "scale") else 1.0
+        # grad_scale: the data-parallel mean and the loss scale of the pass that just filled the gradient arena (fp16-plane path,
+        # IQ.scale()) leave the gradients here
+        scale = getattr(self.model, "_grad_scale", 1.0)
         ops.set_hyper(self.hyper, lr, 1.0 - self.betas[0] ** t, 1.0 - self.betas[1] ** t,
                       1.0 / ((self.dp.world_size if self.dp is not None else 1) * scale))
 
@@ -80,10 +81,10 @@ class TrainStep:
             # train_iq.py:108-110 switches when iter == num_pretraining_steps; ">=" also covers a run resumed from a checkpoint
             # taken after the switch (the reference's checkpoint carries no mode flag)
             m.switch_GVT_train_mode(True)
-        self.set_hyper()
         if self.dp is not None:
             self.dp.begin_step(m)
         terms = m.forward_losses(images, answers, response, target, kliter=self.kliter, eps=eps, backward=True)
+        self.set_hyper()   # after the pass: its loss scale is part of grad_scale; only the Adam kernel below reads `hyper`
         g = m.grad_arena
         if self.dp is not None:
             self.dp.finish_step(m)
