@@ -24,6 +24,8 @@ sys.path.insert(0, ROOT)
 
 import torch  # noqa: E402
 
+DTYPES = {"transformer": "f16 (fp16 operand planes: 3-term hi/lo forward products, single-pass backward under a loss scale; fp32 accumulate, fp32 master weights)",
+          "lstm": "tf32 (fp32 storage, fp32 accumulate)"}
 METRIC = "iq_train_samples_per_sec"
 UNIT = "samples/s"
 
@@ -41,7 +43,8 @@ def parse():
     ap.add_argument("--no-roofline", action="store_true")
     ap.add_argument("--no-eager-baseline", action="store_true", help="skip the stock-PyTorch-eager-on-B200 timing of the oracle port")
     ap.add_argument("--no-secondary", action="store_true", help="skip the LSTM (configs[1]) measurement beside the transformer headline")
-    ap.add_argument("--cpu-batch", type=int, default=64, help="bounded CPU sample: batch size of the oracle step")
+    ap.add_argument("--cpu-batch", type=int, default=64, help="bounded CPU sample of the cpu_baseline leg: batch size of the reference step")
+    ap.add_argument("--ref-batch", type=int, default=0, help="--impl reference: batch (default: the workload's own, cut only if the time budget demands)")
     return ap.parse_args()
 
 
@@ -107,11 +110,97 @@ class ClockSampler(threading.Thread):
                 "samples": len(s)}
 
 
-# ------------------------------------------------------------------ the CPU arm (oracle port of the reference step)
-def cpu_reference_steps(args, cfg, steps, warmup, batch, device="cpu", mode="fp32"):
-    """the reference training step (fp32, PyTorch CPU, all host threads) via oracle/; returns (samples/s, cores, ms/step).
-    device="cuda" runs the same port as stock PyTorch eager on the B200 (the reference ships no kernels of
-    its own, so eager PyTorch is its Blackwell path): mode "fp32" (TF32 off) | "tf32" | "bf16" (autocast).  Transformer only."""
+# ------------------------------------------------------------------ the reference arm (the reference's OWN modules)
+def _median(xs):
+    xs = sorted(xs)
+    return xs[len(xs) // 2] if len(xs) % 2 else 0.5 * (xs[len(xs) // 2 - 1] + xs[len(xs) // 2])
+
+
+def reference_available():
+    from oracle import refload
+    return refload.available()
+
+
+def build_reference_step(workload, cfg, device):
+    """(params, step_fn(batch dict, step index) -> loss) over the UNMODIFIED reference modules from baseline/_ref (or
+    /root/reference): transformer = models.IQ (trunk cut at pooled features, its own initialisers, dropout ON, eps from the CPU
+    generator: stock behaviour) + TrainIQ.calculate_losses verbatim (train_iq.py:81-103); LSTM = the upstream glue over the
+    reference's DecoderRNN / EncoderRNN / MLP classes (oracle/gen_golden_lstm.py RefLSTMIQ; the glue itself is absent from the
+    tree).  Nothing of blt_vqg_b200's model code is on this path (synth only makes the synthetic batch)."""
+    import torch.nn as nn
+    import torch.nn.functional as F
+    from types import SimpleNamespace
+    from blt_vqg_b200 import synth
+    from oracle import refload
+    if workload == "transformer":
+        rargs = synth.args_for(cfg, device=device)
+        m = refload.build_reference_iq(synth.SynthVocab(cfg["V"]), rargs, True, seed=0, dropout=True).to(device).train()
+        calc = refload.import_calculate_losses()
+        self_ = SimpleNamespace(criterion=nn.CrossEntropyLoss(ignore_index=synth.PAD), image_recon_criterion=nn.MSELoss(),
+                                latent_transformer=True, kliter=7000, args=rargs)
+
+        def step_fn(b, step):
+            output, z_logit, kld, (img, recon) = m(b["feats"], b["answers"], b["posteriors"], b["questions"])
+            return calc(self_, output, (img, recon), kld, z_logit, b["questions"])[0]
+    else:
+        from oracle import lstm_oracle
+        from oracle.gen_golden_lstm import RefLSTMIQ
+        torch.manual_seed(0)
+        m = RefLSTMIQ(cfg, synth.SOQ, synth.EOS)
+        m.decoder.input_dropout.p = 0.3   # old_train_iq.py:539-564 defaults (dropout 0.3 / 0.3)
+        m.answer_encoder.input_dropout.p = 0.3
+        m = m.to(device).train()
+        lam = lstm_oracle.LAMBDAS
+
+        def step_fn(b, step):
+            order = torch.argsort(b["alengths"], descending=True, stable=True)   # pack_padded_sequence wants sorted lengths
+            b = {k: v[order].contiguous() for k, v in b.items()}
+            img = m.encoder_cnn(b["feats"])
+            ans = m.encode_answers(b["answers"], b["alengths"].tolist())
+            mus, logvars = m.encode_into_z(img, ans)
+            zs = torch.randn(mus.shape).to(mus.device) * torch.exp(0.5 * logvars) + mus
+            outputs, _, _ = m.decode_questions(img, zs, questions=b["questions"], teacher_forcing_ratio=1.0)
+            logp = torch.cat([o.unsqueeze(1) for o in outputs], dim=1)
+            gen = F.nll_loss(logp.reshape(-1, cfg["V"]), b["questions"][:, 1:].reshape(-1), ignore_index=synth.PAD)
+            kl = lstm_oracle.gaussian_kl_loss(mus, logvars)
+            mus2, logvars2 = m.encode_into_z(img.detach(), ans.detach())
+            z2 = torch.randn(mus2.shape).to(mus2.device) * torch.exp(0.5 * logvars2) + mus2
+            rec_i = F.mse_loss(m.image_reconstructor(z2), img.detach())
+            rec_a = F.mse_loss(m.answer_reconstructor(z2), ans.detach())
+            return lam["lambda_gen"] * gen + lam["lambda_z"] * kl + lam["lambda_i"] * rec_i + lam["lambda_a"] * rec_a
+    return [p for p in m.parameters() if p.requires_grad], step_fn
+
+
+def build_port_step(workload, cfg, device):
+    """fallback when no reference tree is reachable: the oracle restatement (kind "port")"""
+    from blt_vqg_b200 import synth
+    if workload == "transformer":
+        from oracle import iq_oracle
+        from blt_vqg_b200.iq import IQ
+        torch.manual_seed(0)
+        m0 = IQ(True, synth.SynthVocab(cfg["V"]), synth.args_for(cfg))
+        P = {k: v.clone().to(device) for k, v in m0.state_dict().items()}
+        params = [P[n].requires_grad_(True) for n in m0.arena.names()]
+        ocfg = dict(num_layers=cfg["NL"], num_heads=cfg["NH"], latent_dim=cfg["L"], image_recon_lambda=0.1, kl_ceiling=0.5,
+                    aux_ceiling=1.0, full_kl_step=15000)
+        bn = (P["encoder_cnn.bn.running_mean"], P["encoder_cnn.bn.running_var"])
+
+        def step_fn(b, step):
+            eps = torch.randn(b["feats"].shape[0], cfg["L"]).to(device)
+            out, zl, kld, img, recon = iq_oracle.iq_forward(P, ocfg, b["feats"], b["answers"], b["posteriors"], b["questions"],
+                                                            eps=eps, latent_mode=True, training=True, drop=(0.1, 0.1), bn_state=bn)
+            return iq_oracle.iq_losses(ocfg, out, zl, kld, img, recon, b["questions"], step, True)[0]
+        return params, step_fn
+    from oracle import lstm_oracle
+    return lstm_oracle.make_training_closure(cfg)
+
+
+def reference_steps(workload, cfg, steps, warmup, batch, device="cpu", mode="fp32", budget_s=None):
+    """the reference training step — forward + losses + backward + clip_grad_norm_(5) + Adam (train_iq.py:259-261,372), fp32,
+    stock PyTorch — on `device`.  device="cpu": all host threads.  device="cuda": the same modules as stock PyTorch eager on the
+    B200 (the reference ships no kernels of its own, eager PyTorch IS its Blackwell path), mode "fp32" (TF32
+    off) | "tf32" | "bf16" (autocast).  budget_s: if the first step predicts that warmup + steps would not fit, the batch is cut
+    (multiples of 32) — the batch actually run is returned.  Returns a dict (value samples/s from the median step, min, cores, ...)."""
     from blt_vqg_b200 import synth
     torch.set_num_threads(os.cpu_count())
     cores = torch.get_num_threads()
@@ -119,50 +208,44 @@ def cpu_reference_steps(args, cfg, steps, warmup, batch, device="cpu", mode="fp3
     if on_gpu:
         torch.backends.cuda.matmul.allow_tf32 = mode != "fp32"
         torch.backends.cudnn.allow_tf32 = mode != "fp32"
-    if args.workload == "transformer":
-        from oracle import iq_oracle
-        from blt_vqg_b200.iq import IQ
-        torch.manual_seed(0)
-        m0 = IQ(True, synth.SynthVocab(cfg["V"]), synth.args_for(cfg))
-        names = m0.arena.names()
-        P = {k: v.clone().to(device) for k, v in m0.state_dict().items()}
-        params = [P[n].requires_grad_(True) for n in names]
-        ocfg = dict(num_layers=cfg["NL"], num_heads=cfg["NH"], latent_dim=cfg["L"], image_recon_lambda=0.1, kl_ceiling=0.5,
-                    aux_ceiling=1.0, full_kl_step=15000)
-        bn = (P["encoder_cnn.bn.running_mean"], P["encoder_cnn.bn.running_var"])
-
-        def loss_fn(b, step):
-            eps = torch.randn(b["feats"].shape[0], cfg["L"]).to(device)  # CPU generator like transformer_layers.py:45
-            out, zl, kld, img, recon = iq_oracle.iq_forward(P, ocfg, b["feats"], b["answers"], b["posteriors"], b["questions"],
-                                                            eps=eps, latent_mode=True, training=True, drop=(0.1, 0.1), bn_state=bn)
-            return iq_oracle.iq_losses(ocfg, out, zl, kld, img, recon, b["questions"], step, True)[0]
-    else:
-        from oracle import lstm_oracle
-        params, loss_fn = lstm_oracle.make_training_closure(cfg)
+    kind = "reference" if reference_available() else "port"
+    params, step_fn = (build_reference_step if kind == "reference" else build_port_step)(workload, cfg, device)
     opt = torch.optim.Adam(params, lr=1e-4)
-    times = []
-    for s in range(warmup + steps):
-        b = synth.make_batch(cfg, seed=1234 + s, B=batch)
+
+    def one(s, B):
+        b = synth.make_batch(cfg, seed=1234 + s, B=B)
         if on_gpu:
             b = {k: v.to(device) for k, v in b.items()}
             torch.cuda.synchronize()
         t0 = time.perf_counter()
         if mode == "bf16":
             with torch.autocast(device_type="cuda", dtype=torch.bfloat16):
-                loss = loss_fn(b, s)
+                loss = step_fn(b, s)
         else:
-            loss = loss_fn(b, s)
+            loss = step_fn(b, s)
         opt.zero_grad()
         loss.backward()
         torch.nn.utils.clip_grad_norm_(params, 5.0)
         opt.step()
         if on_gpu:
             torch.cuda.synchronize()
-        dt = time.perf_counter() - t0
-        if s >= warmup:
-            times.append(dt)
-    total = sum(times)
-    return batch * len(times) / total, cores, 1e3 * total / len(times)
+        return time.perf_counter() - t0
+
+    times, s = [], 0
+    if warmup > 0:
+        t_first = one(s, batch)
+        s += 1
+        if budget_s is not None and t_first * (warmup + steps) > budget_s and batch > 32:
+            batch = max(32, int(batch * budget_s / (t_first * (warmup + steps))) // 32 * 32)
+        for _ in range(warmup - 1):
+            one(s, batch)
+            s += 1
+    for _ in range(steps):
+        times.append(one(s, batch))
+        s += 1
+    med = _median(times)
+    return {"value": batch / med, "min_step_value": batch / max(times), "max_step_value": batch / min(times), "ms_per_step": 1e3 * med,
+            "ms_per_step_min": 1e3 * min(times), "cores": cores, "kind": kind, "batch": batch, "steps": len(times), "warmup": warmup}
 
 
 # ------------------------------------------------------------------ our arm
@@ -368,28 +451,30 @@ def measure(args, cfg, config, dp, rank, world, local_rank, roofline=True, cpu_a
         ts.dp = saved_dp
     cpu = None
     if cpu_arm and world == 1:
-        v, cores, cms = cpu_reference_steps(args, cfg, 3, 1, args.cpu_batch)
-        cpu = {"value": round(v, 2), "unit": UNIT, "cores": cores, "kind": "port", "ms_per_step": round(cms, 1),
-               "sample": "3 timed steps (after 1 warm-up) of fwd+losses+bwd+clip+Adam at batch %d of the same shapes, fp32 PyTorch CPU oracle port" % args.cpu_batch}
-        if args.workload == "transformer" and not args.no_eager_baseline:
-            # the same port as stock PyTorch eager on this B200 at the FULL batch (device-resident inputs)
+        r = reference_steps(args.workload, cfg, 3, 1, args.cpu_batch)
+        cpu = {"value": round(r["value"], 2), "unit": UNIT, "cores": r["cores"], "kind": r["kind"], "ms_per_step": round(r["ms_per_step"], 1),
+               "sample": "median of 3 timed steps (after 1 warm-up) of fwd+losses+bwd+clip+Adam at batch %d of the same shapes, fp32 PyTorch on the host "
+                         "cores, %s" % (r["batch"], "the reference's own modules from baseline/_ref" if r["kind"] == "reference" else "oracle port (no reference tree reachable)")}
+        if not args.no_eager_baseline:
+            # the same reference modules as stock PyTorch eager on this B200 at the FULL batch (device-resident inputs)
             eager = {}
             for mode in ("fp32", "tf32", "bf16"):
                 try:
-                    ev, _, ems = cpu_reference_steps(args, cfg, 5, 3, cfg["B"], device="cuda", mode=mode)
-                    eager[mode] = {"value": round(ev, 1), "ms_per_step": round(ems, 2)}
-                except Exception as e:  # informational leg: never fail the bench line over it
-                    eager[mode] = {"error": "%s: %s" % (type(e).__name__, str(e)[:120])}
+                    e = reference_steps(args.workload, cfg, 5, 3, cfg["B"], device="cuda", mode=mode)
+                    eager[mode] = {"value": round(e["value"], 1), "ms_per_step": round(e["ms_per_step"], 2), "ms_per_step_min": round(e["ms_per_step_min"], 2)}
+                except Exception as ex:  # informational leg: never fail the bench line over it
+                    eager[mode] = {"error": "%s: %s" % (type(ex).__name__, str(ex)[:120])}
                 torch.cuda.empty_cache()
             torch.backends.cuda.matmul.allow_tf32 = False
             torch.backends.cudnn.allow_tf32 = False
-            cpu["eager_b200"] = dict(eager, unit=UNIT, sample="oracle port of the reference step run by stock PyTorch eager on cuda:0, batch %d, "
-                                     "5 timed steps after 3 warm-up; fp32 = TF32 off, tf32 = allow_tf32, bf16 = autocast" % cfg["B"])
+            cpu["eager_b200"] = dict(eager, unit=UNIT, kind=r["kind"],
+                                     sample="the reference's modules run by stock PyTorch eager on cuda:0 (cuBLAS / cuDNN / ATen), batch %d, median of 5 timed steps "
+                                            "after 3 warm-up; fp32 = TF32 off, tf32 = allow_tf32, bf16 = autocast" % cfg["B"])
     B = cfg["B"]
     h2d = sum(v.numel() * v.element_size() for k, v in hb[0].items() if k in ("feats", "answers", "posteriors", "questions", "alengths"))
     line = {"metric": METRIC, "value": round(B * world * args.steps / (ms * 1e-3), 1), "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(3, args.warmup), "ms_per_step": round(ms / args.steps, 3), "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "tf32 (fp32 storage, fp32 accumulate)", "data": "synthetic", "config": config,
+            "vs_baseline": None, "dtype": DTYPES[args.workload], "data": "synthetic", "config": config,
             "e2e": {"value": round(B * world * args.steps / (ms_e2e * 1e-3), 1), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 32,
                     "ms_per_step": round(ms_e2e / args.steps, 3), "loss_read": "every step, double-buffered pinned sink, consumed one step later",
                     "blocking_read_value": round(B * world * args.steps / (ms_e2e_blk * 1e-3), 1),
@@ -431,17 +516,23 @@ def main():
               "l2_policy": "inputs larger than L2: the per-step working set (weights, gradients, Adam moments, activations: > 2 GB) far exceeds the 126 MB L2; 4 rotating input batches"}
 
     if args.impl == "reference":
-        # the reference's CPU implementation of the path: rank 0 alone, all host threads, bounded sample per step
+        # the reference's own CPU implementation of the path: rank 0 alone, all host threads, the workload's own batch unless the
+        # first step predicts that --warmup + --steps would run past the budget (then the batch is cut and reported as run)
         if rank != 0:
             return 0
-        steps, warm = min(args.steps, 3), min(args.warmup, 1)
-        v, cores, ms = cpu_reference_steps(args, cfg, steps, warm, args.cpu_batch)
-        sample = "fwd+losses+bwd+clip+Adam, fp32 PyTorch CPU oracle port of the reference step, batch %d of the workload's shapes, %d timed steps" % (args.cpu_batch, steps)
-        line = {"impl": "reference", "metric": METRIC, "value": round(v, 2), "unit": UNIT, "n_gpus": args.gpus, "steps": steps, "warmup": warm,
-                "ms_per_step": round(ms, 2), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-                "data": "synthetic", "config": config,
-                "cpu_baseline": {"value": round(v, 2), "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
-                "e2e": {"value": round(v, 2), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        steps, warm = max(1, args.steps), max(1, args.warmup)
+        r = reference_steps(args.workload, cfg, steps, warm, args.ref_batch or cfg["B"], budget_s=float(os.environ.get("B200IQ_REF_BUDGET_S", "240")))
+        config = dict(config, per_gpu_batch=r["batch"], global_batch=r["batch"], parallelism="cpu (rank 0 only)")
+        sample = ("fwd+losses+bwd+clip_grad_norm_(5)+Adam, fp32 stock PyTorch on the host cores, %s, batch %d of the workload's shapes, "
+                  "%d warm-up + %d timed steps, value from the median step" % (
+                      "the reference's own modules (baseline/_ref: models.IQ + TrainIQ.calculate_losses)" if r["kind"] == "reference"
+                      else "oracle port (no reference tree reachable)", r["batch"], r["warmup"], r["steps"]))
+        line = {"impl": "reference", "metric": METRIC, "value": round(r["value"], 2), "unit": UNIT, "n_gpus": args.gpus, "steps": r["steps"], "warmup": r["warmup"],
+                "ms_per_step": round(r["ms_per_step"], 2), "ms_per_step_min": round(r["ms_per_step_min"], 2), "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config,
+                "cpu_baseline": {"value": round(r["value"], 2), "unit": UNIT, "cores": r["cores"], "kind": r["kind"], "sample": sample,
+                                 "min_step_value": round(r["min_step_value"], 2), "max_step_value": round(r["max_step_value"], 2)},
+                "e2e": {"value": round(r["value"], 2), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
         emit(line)
         return 0
 

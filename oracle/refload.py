@@ -1,6 +1,7 @@
 """ORACLE support (test infrastructure only): import the REAL reference modules from /root/reference.
 
-Only usable where the reference tree exists (this container, not the GPU box).  Used by
+Usable where the reference tree exists: /root/reference in this container, or its copy under baseline/_ref on the GPU box
+(baseline/install_ref.py; bench.py's reference arm runs there).  Used by
 oracle/gen_golden.py to pin oracle/iq_oracle.py and to write tests/golden/*.pt.  Shims
 (nothing under /root/reference is edited):
   1. numpy.float = float            (models/transformer_layers.py:551 uses the removed alias)
@@ -17,7 +18,19 @@ import numpy as np
 import torch
 import torch.nn as nn
 
-REF_ROOT = os.environ.get("B200IQ_REFERENCE", "/root/reference")
+_HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def _find_root():
+    """the reference tree: $B200IQ_REFERENCE, /root/reference (this container), else the copy baseline/install_ref.py made under
+    baseline/_ref (what the GPU box has)"""
+    for p in (os.environ.get("B200IQ_REFERENCE"), "/root/reference", os.path.join(os.path.dirname(_HERE), "baseline", "_ref")):
+        if p and os.path.isdir(os.path.join(p, "models")):
+            return p
+    return "/root/reference"
+
+
+REF_ROOT = _find_root()
 
 
 def available():

@@ -45,7 +45,7 @@ def step(path, label="cfg3, B=512"):
         agg[k][0] += 1
         agg[k][1] += v
     tot = sum(v[1] for v in agg.values())
-    gemm = sum(v[1] for k, v in agg.items() if "gemm_tf32_kernel" in k)
+    gemm = sum(v[1] for k, v in agg.items() if "gemm_tf32_kernel" in k or "gemm_f16_kernel" in k)
     print("# one training step (%s) out of %s: %d launches, %.1f us total, GEMMs %.1f us = %.1f%% (ncu per-launch times are "
           "cold-cache and serialised, and the step's side streams run one kernel at a time under ncu: compare SHARES)" % (label, path, len(data), tot, gemm, 100 * gemm / tot))
     for k, v in sorted(agg.items(), key=lambda kv: -kv[1][1]):
