@@ -61,6 +61,7 @@ struct AttnArgs {
   int B, nh, nq, nk, d;
   float scale, drop_p;
   uint64_t seed, offset;
+  const unsigned long long* seed_dev;  // device word added to seed at run time (CUDA-graph replays), or NULL
   int rn;  // round outputs to TF32
   int dq2; // backward: dQ = (dS + dS_lo) . K, dS as two TF32 terms (B200IQ_ATT_DQ2, default 1)
   size_t bsk, bsv;  // elements between consecutive samples' K / V blocks (nk*ldk, nk*ldv unless reading a KV cache)
@@ -73,7 +74,7 @@ struct AttnArgs {
 // was most of the instruction stream of these kernels (5.5 k instructions per warp, ncu profiles/r01k_attention_fwd_rows.txt).
 __device__ __forceinline__ void att_drop_words(const AttnArgs& a, size_t row, int tile, uint32_t (&w)[4]) {
   const uint64_t ctr = a.offset + row * (uint64_t)((a.nk + 7) >> 3) + (uint64_t)tile;
-  Philox(a.seed).rounds<7>((uint32_t)ctr, (uint32_t)(ctr >> 32), 1u, 0u, w);
+  Philox(a.seed + ((a.drop_p > 0.f && a.seed_dev) ? __ldg(a.seed_dev) : 0ull)).rounds<7>((uint32_t)ctr, (uint32_t)(ctr >> 32), 1u, 0u, w);
 }
 __device__ __forceinline__ float att_keep(const uint32_t (&w)[4], int j, uint32_t thr, float inv) {
   return (((w[(j >> 1) & 3] >> ((j & 1) << 4)) & 0xFFFFu) >= thr) ? inv : 0.f;
@@ -741,7 +742,7 @@ static AttnArgs to_args(const B200iqAttention* p) {
   a.q = p->q; a.k = p->k; a.v = p->v; a.ldq = p->ldq; a.ldk = p->ldk; a.ldv = p->ldv;
   a.key_ids = p->key_ids; a.pad_id = p->pad_id; a.causal = p->causal;
   a.B = p->B; a.nh = p->num_heads; a.nq = p->nq; a.nk = p->nk; a.d = p->head_dim;
-  a.scale = p->scale; a.drop_p = p->drop_p; a.seed = p->seed; a.offset = p->offset;
+  a.scale = p->scale; a.drop_p = p->drop_p; a.seed = p->seed; a.offset = p->offset; a.seed_dev = p->seed_dev;
   a.rn = round_mode();
   static const int dq2 = [] { const char* e = getenv("B200IQ_ATT_DQ2"); return (e && e[0] == '0') ? 0 : 1; }();
   a.dq2 = dq2;

@@ -192,8 +192,8 @@ __global__ void dropout_kernel(float* __restrict__ x, size_t n, float p, uint64_
 }
 
 // out[i] ~ N(0,1): Philox4x32-10(seed; counter = offset + i/4) + Box-Muller (pairs -> cos/sin)
-__global__ void randn_kernel(float* __restrict__ out, size_t n, uint64_t seed, uint64_t offset) {
-  Philox ph(seed);
+__global__ void randn_kernel(float* __restrict__ out, size_t n, uint64_t seed, uint64_t offset, const unsigned long long* seed_dev) {
+  Philox ph(seed + (seed_dev ? __ldg(seed_dev) : 0ull));
   size_t n4 = (n + 3) / 4;
   for (size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x; q < n4; q += (size_t)gridDim.x * blockDim.x) {
     uint32_t r[4];
@@ -374,8 +374,14 @@ extern "C" int b200iq_dropout(float* x, size_t n, float p, uint64_t seed, uint64
 
 extern "C" int b200iq_randn(float* out, size_t n, uint64_t seed, uint64_t offset, void* stream) {
   B200IQ_CHECK_ARG(out && n > 0, "randn: bad args");
-  randn_kernel<<<grid_for((n + 3) / 4, 256), 256, 0, ST>>>(out, n, seed, offset);
+  randn_kernel<<<grid_for((n + 3) / 4, 256), 256, 0, ST>>>(out, n, seed, offset, nullptr);
   return launch_status("randn");
+}
+
+extern "C" int b200iq_randn_dev(float* out, size_t n, uint64_t seed, uint64_t offset, const unsigned long long* seed_dev, void* stream) {
+  B200IQ_CHECK_ARG(out && n > 0, "randn_dev: bad args");
+  randn_kernel<<<grid_for((n + 3) / 4, 256), 256, 0, ST>>>(out, n, seed, offset, seed_dev);
+  return launch_status("randn_dev");
 }
 
 extern "C" int b200iq_axpby(const float* x, const float* y, float* out, size_t n, float a, float b, void* stream) {

@@ -25,7 +25,7 @@ static constexpr int F16_STG_BYTES = 4096;  // one 32 x 32 fp32 tile = two 32 x 
 struct F16Epi {
   float* C; __half* Chi; __half* Clo; const float* bias; const float* residual; const __half* gate;
   int M, N, ldc, ldh, ldr, ldg, flags; float alpha;
-  float drop_p, drop_scale; uint64_t drop_seed, drop_offset;
+  float drop_p, drop_scale; uint64_t drop_seed, drop_offset; const unsigned long long* drop_seed_dev;
 };
 
 __device__ __forceinline__ void umma_f16(uint32_t tmem_c, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
@@ -53,7 +53,7 @@ __device__ __forceinline__ float f16_epi_value(float acc, const F16Epi& e, int r
   if (e.flags & B200IQ_GEMM_DROPOUT) {
     const size_t i = (size_t)row * e.N + col;
     uint32_t w[4];
-    dropout_words(e.drop_seed, e.drop_offset, i, w);
+    dropout_words(e.drop_seed + (e.drop_seed_dev ? __ldg(e.drop_seed_dev) : 0ull), e.drop_offset, i, w);
     v = dropout_keep(w, i, dropout_threshold(e.drop_p)) ? v * e.drop_scale : 0.f;
   }
   return v;
@@ -191,6 +191,7 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant_
     const bool drop = EPI == 2;
     const bool drop_pairs = (epi.N & 7) == 0;
     const uint32_t drop_thr = dropout_threshold(epi.drop_p);
+    const uint64_t drop_seed = epi.drop_seed + ((drop && epi.drop_seed_dev) ? __ldg(epi.drop_seed_dev) : 0ull);
     uint32_t ti = 0, chunk = 0;
     // EPI 1 + RESIDUAL: the 32 x 32 fp32 residual tile of a chunk is pulled by TMA straight into the chunk's staging buffer
     // (same 128B swizzle as the output tile), one chunk ahead of the math when there are two buffers
@@ -263,7 +264,7 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant_
             float4 gg = make_float4(0.f, 0.f, 0.f, 0.f);
             if (has_r) gg = *reinterpret_cast<const float4*>(buf + lane * 128 + (((j >> 2) ^ (lane & 7)) << 4));
             const size_t ei = (size_t)row * epi.N + col0 + j;
-            if (drop && (!drop_pairs || !(j & 4))) dropout_words(epi.drop_seed, epi.drop_offset, ei, keep);
+            if (drop && (!drop_pairs || !(j & 4))) dropout_words(drop_seed, epi.drop_offset, ei, keep);
             const float* ga = &gg.x; const float* ba = &bb.x;
 #pragma unroll
             for (int t = 0; t < 4; ++t) {
@@ -466,12 +467,13 @@ extern "C" int b200iq_gemm_f16(const B200iqGemmF16* p, void* stream) {
   B200IQ_CHECK_ARG((((uintptr_t)p->A_hi | (uintptr_t)p->B_hi | (uintptr_t)p->A_lo | (uintptr_t)p->B_lo) & 15) == 0, "gemm_f16: operand planes must be 16-byte aligned");
   B200IQ_CHECK_ARG(terms == 1 || (!amn && !bmn), "gemm_f16: the 3-term product takes K-major A and B");
   F16Epi e{p->C, (__half*)p->C_hi, (__half*)p->C_lo, p->bias, p->residual, (const __half*)p->gate,
-           p->M, p->N, p->ldc, p->ldh, p->ldr, p->ldg, f, p->alpha, 0.f, 1.f, 0ull, 0ull};
+           p->M, p->N, p->ldc, p->ldh, p->ldr, p->ldg, f, p->alpha, 0.f, 1.f, 0ull, 0ull, nullptr};
   if (f & B200IQ_GEMM_DROPOUT) {
     B200IQ_CHECK_ARG(p->drop_p > 0.f && p->drop_p < 1.f, "gemm_f16: DROPOUT needs 0 < drop_p < 1");
     B200IQ_CHECK_ARG((p->N & 3) == 0 && split == 1 && !(f & B200IQ_GEMM_ACCUM) && !amn && !bmn && !(f & (B200IQ_GEMM_RESIDUAL | B200IQ_GEMM_RELU_MASK)),
                      "gemm_f16: DROPOUT needs N %% 4 == 0, K-major operands, no split-K / ACCUM / residual / gate");
     e.drop_p = p->drop_p; e.drop_scale = 1.f / (1.f - p->drop_p); e.drop_seed = p->drop_seed; e.drop_offset = p->drop_offset;
+    e.drop_seed_dev = p->drop_seed_dev;
   }
   // the fast epilogue needs TMA-storable fp32 tiles and 16-byte plane rows; anything else takes the generic per-lane path
   bool fast = true;

@@ -164,10 +164,10 @@ __global__ void latent_fwd_kernel(const float* __restrict__ prior, const float* 
 }
 
 __global__ void latent_bwd_kernel(const float* __restrict__ prior, const float* __restrict__ post, const float* __restrict__ eps,
-                                  const float* __restrict__ dz, float kld_coef, float* __restrict__ dprior, float* __restrict__ dpost,
-                                  int B, int L, int rn) {
+                                  const float* __restrict__ dz, float kld_coef, const float* __restrict__ kld_coef_dev,
+                                  float* __restrict__ dprior, float* __restrict__ dpost, int B, int L, int rn) {
   int n = B * L;
-  float kc = kld_coef / B;
+  float kc = (kld_coef_dev ? __ldg(kld_coef_dev) : kld_coef) / B;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     int b = i / L, c = i - b * L;
     float mp = prior[b * 2 * L + c], lp = prior[b * 2 * L + L + c];
@@ -386,8 +386,15 @@ extern "C" int b200iq_latent_fwd(const float* prior, const float* post, const fl
 extern "C" int b200iq_latent_bwd(const float* prior, const float* post, const float* eps, const float* dz, float kld_coef,
                                  float* dprior, float* dpost, int B, int L, void* stream) {
   B200IQ_CHECK_ARG(prior && post && eps && dprior && dpost && B > 0 && L > 0, "latent_bwd: bad args");
-  latent_bwd_kernel<<<min(ceil_div(B * L, 256), 148), 256, 0, ST>>>(prior, post, eps, dz, kld_coef, dprior, dpost, B, L, round_mode());
+  latent_bwd_kernel<<<min(ceil_div(B * L, 256), 148), 256, 0, ST>>>(prior, post, eps, dz, kld_coef, nullptr, dprior, dpost, B, L, round_mode());
   return launch_status("latent_bwd");
+}
+
+extern "C" int b200iq_latent_bwd_dev(const float* prior, const float* post, const float* eps, const float* dz, const float* kld_coef_dev,
+                                     float* dprior, float* dpost, int B, int L, void* stream) {
+  B200IQ_CHECK_ARG(prior && post && eps && dprior && dpost && kld_coef_dev && B > 0 && L > 0, "latent_bwd_dev: bad args");
+  latent_bwd_kernel<<<min(ceil_div(B * L, 256), 148), 256, 0, ST>>>(prior, post, eps, dz, 0.f, kld_coef_dev, dprior, dpost, B, L, round_mode());
+  return launch_status("latent_bwd_dev");
 }
 
 extern "C" int b200iq_bn_fwd(const float* x, const float* gamma, const float* beta, float* y, float* save_mean, float* save_rstd,

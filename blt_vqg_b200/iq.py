@@ -101,6 +101,11 @@ class IQ(nn.Module):
         self.seed = 1234
         self.seed_rank = 0   # data-parallel rank (parallel.GradReducer.begin_step): ranks draw different masks / eps like DDP replicas do
         self.step_idx = 0    # stochastic forward passes so far: every training-mode forward / decode draws fresh dropout masks and eps
+        # device-resident per-step scalars (train.TrainStep sets them when it captures the step in a CUDA graph: a captured launch
+        # keeps its arguments, so what changes every step must be read from memory): seed_dev = int64 word added to every Philox
+        # seed (then it, not step_idx, counts the passes), kld_coef_dev = float holding kl_ceiling * kl_weight * loss_scale
+        self.seed_dev = None
+        self.kld_coef_dev = None
         self._ws = {}
         self._gflat = None
         self._terms = None
@@ -254,6 +259,8 @@ class IQ(nn.Module):
         """Philox key of the next stochastic pass.  The reference draws fresh dropout masks and a fresh torch.randn eps on every
         call (transformer_layers.py:45,406,520); a counter-based generator needs a new key per call to do the same, so the
         module counts its own stochastic passes (checkpoint.py saves / restores the counter)."""
+        if self.seed_dev is not None:
+            return self.seed + 1000003 * self.seed_rank   # + *seed_dev, added by the kernels
         self.step_idx += 1
         return self.seed + self.step_idx + 1000003 * self.seed_rank
 
@@ -437,8 +444,12 @@ class IQ(nn.Module):
         Returns the device tensor of loss terms (rec, img, kld, aux, count, ...); gradients are ACCUMULATED into
         `self.grad_arena` MULTIPLIED BY self.scale() (the loss scale of the fp16-plane path; train.TrainStep folds it into Adam's
         grad_scale, `unscaled_grads()` gives a plain copy).  total = rec + c_img*img + c_kld*kld + c_aux*aux (loss_coefs / total_loss)."""
-        with ops.no_rounding():
-            return self._forward_losses(images, answers, response, target, kliter, eps, backward)
+        prev, ops.SEED_DEV = ops.SEED_DEV, self.seed_dev
+        try:
+            with ops.no_rounding():
+                return self._forward_losses(images, answers, response, target, kliter, eps, backward)
+        finally:
+            ops.SEED_DEV = prev
 
     def unscaled_grads(self):
         """the flat gradient arena with the loss scale of the pass that filled it divided out (tests / inspection)"""
@@ -500,7 +511,7 @@ class IQ(nn.Module):
         d_recon = ws.buf("d_recon", B, H)
         ops.mse(m["img"], m["recon"], c_img * SC, terms[1:2], d_img if backward else None, d_recon if backward else None)
         if backward:
-            self._backward_tail(c, d_dec, d_img, d_z, d_recon, c_kld * SC)
+            self._backward_tail(c, d_dec, d_img, d_z, d_recon, self.kld_coef_dev if self.kld_coef_dev is not None else c_kld * SC)
         return terms
 
     def total_loss(self, terms, kliter=0):

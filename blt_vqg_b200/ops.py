@@ -14,6 +14,9 @@ from . import _lib as L
 _FORCE_SIMT = os.environ.get("B200IQ_GEMM", "") == "simt"
 # fp32-in / fp32-out attention calls: 1 = precise mode (3-term forward products on unrounded inputs) — set by the transformer path
 PRECISE_ATTENTION = 0
+# device int64 word added to every Philox seed at run time (None: off).  A step captured in a CUDA graph keeps its launch
+# arguments, so the per-step part of the dropout / eps keys lives here and the captured step increments it itself (train.py).
+SEED_DEV = None
 # number of kernel launches issued through the C ABI (bench.py reports it as gpu_launches)
 LAUNCHES = 0
 # when a list: gemm() brackets every launch with CUDA events on the launching stream and appends
@@ -26,9 +29,13 @@ def exact_mode():
     return _FORCE_SIMT
 
 
+# False: set_pdl(True) requests are ignored (train.TrainStep while it runs / captures a step for a CUDA graph)
+PDL_ALLOWED = True
+
+
 def set_pdl(on):
     """programmatic dependent launch for the hot kernels (b200iq_set_pdl); returns the previous setting"""
-    return bool(L.lib().b200iq_set_pdl(1 if on else 0))
+    return bool(L.lib().b200iq_set_pdl(1 if (on and PDL_ALLOWED) else 0))
 
 
 class no_rounding:
@@ -103,7 +110,7 @@ class GemmF16Params(C.Structure):
         ("M", C.c_int), ("N", C.c_int), ("K", C.c_int),
         ("lda", C.c_int), ("ldb", C.c_int), ("ldc", C.c_int), ("ldh", C.c_int), ("ldr", C.c_int), ("ldg", C.c_int),
         ("flags", C.c_int), ("split_k", C.c_int), ("alpha", C.c_float),
-        ("drop_p", C.c_float), ("drop_seed", C.c_uint64), ("drop_offset", C.c_uint64),
+        ("drop_p", C.c_float), ("drop_seed", C.c_uint64), ("drop_offset", C.c_uint64), ("drop_seed_dev", C.c_void_p),
     ]
 
 
@@ -152,7 +159,7 @@ def gemm2(a, b, out=None, *, planes=None, a_t=False, b_t=False, bias=None, resid
                       _dp(out), _dp(ph), _dp(pl), _dp(bias), _dp(residual), _dp(gate), M, N, K,
                       _ld(ah), _ld(bh), _ld(out) if out is not None else 0, _ld(ph) if ph is not None else 0,
                       _ld(residual) if residual is not None else 0, _ld(gate) if gate is not None else 0,
-                      flags, split_k, float(alpha), float(dp), dseed, doff)
+                      flags, split_k, float(alpha), float(dp), dseed, doff, _dp(SEED_DEV) if dp > 0 else None)
     global LAUNCHES
     LAUNCHES += 1
     if GEMM_TRACE is not None:
@@ -265,7 +272,7 @@ class AttnParams(C.Structure):
         ("B", C.c_int), ("num_heads", C.c_int), ("nq", C.c_int), ("nk", C.c_int), ("head_dim", C.c_int),
         ("scale", C.c_float), ("drop_p", C.c_float), ("seed", C.c_uint64), ("offset", C.c_uint64),
         ("kv_batch_stride", C.c_longlong),
-        ("precise", C.c_int), ("out_hi", C.c_void_p), ("out_lo", C.c_void_p),
+        ("precise", C.c_int), ("out_hi", C.c_void_p), ("out_lo", C.c_void_p), ("seed_dev", C.c_void_p),
     ]
 
 
@@ -395,7 +402,10 @@ def dropout_(x, p, seed, offset):
 
 
 def randn_(out, seed, offset=0):
-    _call("b200iq_randn", _p(out), C.c_size_t(out.numel()), C.c_uint64(seed), C.c_uint64(offset))
+    if SEED_DEV is not None:
+        _call("b200iq_randn_dev", _p(out), C.c_size_t(out.numel()), C.c_uint64(seed), C.c_uint64(offset), _p(SEED_DEV))
+    else:
+        _call("b200iq_randn", _p(out), C.c_size_t(out.numel()), C.c_uint64(seed), C.c_uint64(offset))
     return out
 
 
@@ -416,7 +426,8 @@ def _attn_params(q, k, v, out, key_ids, pad_id, causal, B, nh, nq, nk, d, drop_p
     return AttnParams(q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr() if out is not None else 0,
                       q.stride(0), k.stride(0), v.stride(0), out.stride(0) if out is not None else 0,
                       key_ids.data_ptr() if key_ids is not None else 0, pad_id, int(causal),
-                      B, nh, nq, nk, d, d ** -0.5, drop_p, seed, offset, kv_batch_stride, 0, None, None)
+                      B, nh, nq, nk, d, d ** -0.5, drop_p, seed, offset, kv_batch_stride, 0, None, None,
+                      _dp(SEED_DEV) if drop_p > 0 else None)
 
 
 def attention_fwd(q, k, v, out, key_ids, pad_id, causal, B, nh, nq, nk, d, drop_p=0.0, seed=0, offset=0, kv_batch_stride=0):
@@ -469,8 +480,12 @@ def latent_fwd(prior, post, eps, z, kld_sum):
 
 
 def latent_bwd(prior, post, eps, dz, kld_coef, dprior, dpost):
+    """kld_coef: a float, or a device tensor whose first element holds it (steps captured in a CUDA graph)"""
     B, L = eps.shape
-    _call("b200iq_latent_bwd", _p(prior), _p(post), _p(eps), _p(dz), _f(kld_coef), _p(dprior), _p(dpost), B, L)
+    if isinstance(kld_coef, torch.Tensor):
+        _call("b200iq_latent_bwd_dev", _p(prior), _p(post), _p(eps), _p(dz), _p(kld_coef), _p(dprior), _p(dpost), B, L)
+    else:
+        _call("b200iq_latent_bwd", _p(prior), _p(post), _p(eps), _p(dz), _f(kld_coef), _p(dprior), _p(dpost), B, L)
 
 
 def bn_fwd(x, g, b, y, save_mean, save_rstd, run_mean, run_var, training, eps=1e-5, momentum=0.01):

@@ -110,6 +110,9 @@ typedef struct B200iqGemmF16 {
   float alpha;
   float drop_p;
   unsigned long long drop_seed, drop_offset;
+  const unsigned long long* drop_seed_dev; /* NULL, or a DEVICE word added to drop_seed when the kernel runs: a step captured in a
+                                              CUDA graph keeps its launch arguments, so the per-step part of the Philox key lives
+                                              in device memory and is bumped by the graph itself */
 } B200iqGemmF16;
 int b200iq_gemm_f16(const B200iqGemmF16* p, void* stream);
 /* hi[r,c] = fp16(scale * src[r,c]), lo[r,c] = fp16(scale * src[r,c] - hi[r,c]) (lo may be NULL): the plane copy of the fp32
@@ -165,6 +168,8 @@ int b200iq_dropout(float* x, size_t n, float p, uint64_t seed, uint64_t offset, 
 /* out ~ N(0,1), Philox4x32-10(seed; counter = offset + i/4) + Box-Muller (moments checked in tests/test_ops_gpu.py)
  * replaces: torch.randn on the CPU + H2D copy, models/transformer_layers.py:45 */
 int b200iq_randn(float* out, size_t n, uint64_t seed, uint64_t offset, void* stream);
+/* same with the device word *seed_dev (may be NULL) added to the seed at run time (CUDA-graph replays draw fresh numbers) */
+int b200iq_randn_dev(float* out, size_t n, uint64_t seed, uint64_t offset, const unsigned long long* seed_dev, void* stream);
 /* out = a*x + b*y (out may alias x or y): residual adds that cannot ride a GEMM epilogue */
 int b200iq_axpby(const float* x, const float* y, float* out, size_t n, float a, float b, void* stream);
 /* dst = round_to_nearest_tf32(src): the GEMM-operand copy of the fp32 master weights / of user inputs */
@@ -193,6 +198,7 @@ typedef struct B200iqAttention {
                             (instead of truncating) the operands of its single-pass products.  0: legacy TF32 single pass. */
   void* out_hi;          /* precise forward: fp16 planes of the merged-head output (ldo halves) written instead of `out` when */
   void* out_lo;          /*   out_hi != NULL (out_lo optional) */
+  const unsigned long long* seed_dev; /* NULL, or a device word added to `seed` at run time (see B200iqGemmF16.drop_seed_dev) */
 } B200iqAttention;
 /* replaces: models/transformer_layers.py:494-526; mask fill is the finite -1e18 of :506 */
 int b200iq_attention_fwd(const B200iqAttention* p, void* stream);
@@ -220,6 +226,10 @@ int b200iq_ce_aux(const float* z_logit, float* dz_logit, const int* targets, int
 int b200iq_latent_fwd(const float* prior, const float* post, const float* eps, float* z, float* kld_sum, int B, int L, void* stream);
 int b200iq_latent_bwd(const float* prior, const float* post, const float* eps, const float* dz, float kld_coef,
                       float* dprior, float* dpost, int B, int L, void* stream);
+/* same with the coefficient read from device memory (kld_coef_dev[0]): the KL weight anneals every step (train_iq.py:96), a
+ * captured step cannot carry it as a launch argument */
+int b200iq_latent_bwd_dev(const float* prior, const float* post, const float* eps, const float* dz, const float* kld_coef_dev,
+                          float* dprior, float* dpost, int B, int L, void* stream);
 /* nn.BatchNorm1d(H, momentum) on [B,H]; training: batch statistics + running-stat update.   replaces: models/encoder_cnn.py:21,34 */
 int b200iq_bn_fwd(const float* x, const float* gamma, const float* beta, float* y, float* save_mean, float* save_rstd,
                   float* running_mean, float* running_var, int B, int H, float eps, float momentum, int training, void* stream);

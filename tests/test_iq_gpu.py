@@ -434,3 +434,44 @@ def test_programmatic_dependent_launch_changes_nothing(env):
     noise = max(rel(g2, g0), 1e-7)          # split-K atomics reorder between two identical plain runs
     assert torch.allclose(t1[:4], t0[:4], rtol=1e-5, atol=1e-6), (t1, t0)
     assert rel(g1, g0) <= 4 * noise + 1e-6, (rel(g1, g0), noise)
+
+
+def test_cuda_graph_step_matches_the_eager_schedule(env):
+    """train.TrainStep captures the whole step (~600 launches, side streams included) in a CUDA graph after two eager warm-up
+    steps: six steps on rotating batches must leave the same parameters as the eager schedule (dropout off, eps injected; the
+    split-K reductions reorder, so equal to rounding), the loss terms of every step must agree, and with dropout ON two replays
+    of the same batch must draw different masks (the Philox key lives in device memory and the graph bumps it)."""
+    from blt_vqg_b200 import synth
+    from blt_vqg_b200.iq import IQ
+    from blt_vqg_b200.train import TrainStep
+    cfg = synth.CONFIGS["wide"]
+    torch.manual_seed(11)
+    m0 = IQ(True, synth.SynthVocab(cfg["V"]), synth.args_for(cfg))
+    sd = {k: v.clone() for k, v in m0.state_dict().items()}
+    batches = [{k: v.cuda() for k, v in synth.make_batch(cfg, seed=50 + i).items()} for i in range(3)]
+    eps = [torch.randn(cfg["B"], cfg["L"], device="cuda") for _ in range(3)]
+    res = {}
+    for graph in (False, True):
+        m = _build(cfg, True, sd)
+        ts = TrainStep(m, lr_fn=lambda s: 1e-4, graph=graph)
+        ts.kliter = 5000
+        losses = []
+        for i in range(6):
+            b = batches[i % 3]
+            t = ts.step(b["feats"], b["answers"], b["posteriors"], b["questions"], eps=eps[i % 3])
+            losses.append(t[:4].clone())
+        torch.cuda.synchronize()
+        assert ts.graph_replays == (4 if graph else 0)
+        res[graph] = (torch.stack(losses).cpu(), m.flat.data.clone())
+    assert torch.allclose(res[True][0], res[False][0], rtol=2e-5, atol=1e-6), (res[True][0], res[False][0])
+    upd_e, upd_g = res[False][1] - m0.flat.data.cuda(), res[True][1] - m0.flat.data.cuda()
+    assert rel(upd_g, upd_e) < 1e-3
+    # dropout on: replays of the same inputs differ, and everything stays finite
+    m = _build(cfg, True, sd, dropout=True)
+    ts = TrainStep(m, lr_fn=lambda s: 0.0, graph=True)
+    b = batches[0]
+    out = [ts.step(b["feats"], b["answers"], b["posteriors"], b["questions"])[:4].clone() for _ in range(5)]
+    torch.cuda.synchronize()
+    assert ts.graph_replays == 3
+    assert all(torch.isfinite(o).all() for o in out)
+    assert not torch.allclose(out[3], out[4], rtol=1e-7) and not torch.allclose(out[2], out[3], rtol=1e-7)
