@@ -69,7 +69,7 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant_
   constexpr int BNL = BN / CTAS;  // rows of B this CTA stages (the pair's MMA reads N/2 from each CTA)
   constexpr int NPL = TERMS == 3 ? 2 : 1;
   constexpr int A_BYTES = FBM * 128, B_BYTES = BNL * 128, STAGE_BYTES = NPL * (A_BYTES + B_BYTES);
-  constexpr int NBUF = TERMS == 3 ? 1 : 2;  // staging buffers per epilogue warp (the 3-term stages leave room for one)
+  constexpr int NBUF = (TERMS == 3 && STAGE_BYTES > 49152) ? 1 : 2;  // staging buffers per epilogue warp (64 KB stages leave room for one)
   extern __shared__ uint8_t smem_raw[];
   pdl_trigger();
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -400,8 +400,10 @@ template <int BN, bool A_MN, bool B_MN, int TERMS, int EPI, int CTAS>
 static int launch_f16(const F16Maps& m, int fast_epi, const F16Epi& e, int K, int split, cudaStream_t st) {
   constexpr int NPL = TERMS == 3 ? 2 : 1;
   constexpr int STAGE = NPL * (FBM * 128 + (BN / CTAS) * 128);
-  constexpr int STAGES = TERMS == 3 ? 3 : (STAGE <= 32768 ? 5 : 3);
-  constexpr int NBUF = TERMS == 3 ? 1 : 2;
+  constexpr int NBUF = (TERMS == 3 && STAGE > 49152) ? 1 : 2;
+  constexpr int ROOM = 232448 - 512 - 1024 - F16_EPI_WARPS * NBUF * F16_STG_BYTES;
+  constexpr int STAGES = ROOM / STAGE > 6 ? 6 : ROOM / STAGE;
+  static_assert(STAGES >= 3, "pipeline depth");
   constexpr int SMEM = STAGES * STAGE + F16_EPI_WARPS * NBUF * F16_STG_BYTES + 1024;
   static_assert(SMEM + 512 <= 232448, "shared memory budget");
   auto kern = gemm_f16_kernel<BN, A_MN, B_MN, TERMS, STAGES, EPI, CTAS>;
@@ -484,8 +486,21 @@ extern "C" int b200iq_gemm_f16(const B200iqGemmF16* p, void* stream) {
   if ((f & B200IQ_GEMM_DROPOUT) && !fast) { set_error("gemm_f16: DROPOUT needs the aligned fast epilogue"); return -1; }
   B200IQ_CHECK_ARG(fast || !p->C || p->ldc >= p->N, "gemm_f16: ldc too small");
 
-  const bool pair = p->M > 128 && p->N > 128;
-  const int BNL = 128;
+  // tile policy.  CTA pairs (cta_group::2, 256 rows per pair) wherever M > 128; the pair's N is 256, or 128 when that fills the
+  // 74 pairs better: a persistent grid finishes in ceil(tiles / pairs) rounds, and e.g. M = 10240, N = 512 is 80 tiles of
+  // 256 x 256 (2 rounds, the second with 6 pairs busy) but 160 tiles of 256 x 128 (3 rounds of half the work each)
+  static const int force_bn = [] { const char* v = getenv("B200IQ_F16_TILE_N"); return v ? atoi(v) : 0; }();
+  const bool pair = p->M > 128 && p->N > 64;
+  int pair_bn = 256;
+  if (pair) {
+    const int slots = sm_count() / 2 > 0 ? sm_count() / 2 : 1, mt = ceil_div(p->M, 256);
+    int kb = ceil_div(p->K, FBK), sp = split > kb ? kb : split;
+    const long t256 = (long)mt * ceil_div(p->N, 256) * sp, t128 = (long)mt * ceil_div(p->N, 128) * sp;
+    const double c256 = (double)((t256 + slots - 1) / slots) * 2.0, c128 = (double)((t128 + slots - 1) / slots) * 1.08;
+    if (p->N <= 128 || c128 < 0.95 * c256) pair_bn = 128;
+    if (force_bn == 128 || force_bn == 256) pair_bn = (p->N <= 128) ? 128 : force_bn;
+  }
+  const int BNL = pair ? pair_bn / 2 : 128;
   F16Maps m;
   memset(&m, 0, sizeof(m));
   int rc;
@@ -503,7 +518,7 @@ extern "C" int b200iq_gemm_f16(const B200iqGemmF16* p, void* stream) {
   const int fe = fast ? 1 : 0;
   const int epi_mode = (f & B200IQ_GEMM_DROPOUT) ? 2 : (f & (B200IQ_GEMM_RESIDUAL | B200IQ_GEMM_RELU_MASK)) ? 1 : 0;
 #define F16_GO(BN_, AM_, BM_, T_, E_, C_) return launch_f16<BN_, AM_, BM_, T_, E_, C_>(m, fe, e, p->K, split, st)
-#define F16_TILE(AM_, BM_, T_, E_) do { if (pair) F16_GO(256, AM_, BM_, T_, E_, 2); else F16_GO(128, AM_, BM_, T_, E_, 1); } while (0)
+#define F16_TILE(AM_, BM_, T_, E_) do { if (pair && pair_bn == 256) F16_GO(256, AM_, BM_, T_, E_, 2); else if (pair) F16_GO(128, AM_, BM_, T_, E_, 2); else F16_GO(128, AM_, BM_, T_, E_, 1); } while (0)
   if (terms == 3) {
     if (epi_mode == 2) F16_TILE(false, false, 3, 2);
     if (epi_mode == 1) F16_TILE(false, false, 3, 1);

@@ -205,17 +205,18 @@ def grad_w(c, dy, x, gw, gb=None):
         ops.colsum_add_act(dy, gb)
 
 
-def ln_fwd(c, tag, pfx, x, kind="act"):
-    """LayerNorm(x) as a GEMM operand (kind "act": planes hi + lo, "act_hi": hi only) or as an fp32 tensor (kind "f32")"""
+def ln_fwd(c, tag, pfx, x, kind="act", add=None, sum_out=None):
+    """LayerNorm(x [+ add]) as a GEMM operand (kind "act": planes hi + lo, "act_hi": hi only) or as an fp32 tensor (kind "f32").
+    With add, x + add is written to sum_out in the same pass (the residual add of the block in front of this LayerNorm)."""
     M, H = x.shape
     mean, rstd = c.ws.buf(tag + ".mean", M), c.ws.buf(tag + ".rstd", M)
     g, b = c.P[pfx + ".weight"], c.P[pfx + ".bias"]
     if kind == "f32":
         y = c.ws.buf(tag + ".y", M, H)
-        ops.layernorm_fwd_act(x, g, b, mean, rstd, y=y)
+        ops.layernorm_fwd_act(x, g, b, mean, rstd, y=y, add=add, sum_out=sum_out)
         return y
     y = c.act(tag + ".y", M, H, lo=kind == "act")
-    ops.layernorm_fwd_act(x, g, b, mean, rstd, act=y)
+    ops.layernorm_fwd_act(x, g, b, mean, rstd, act=y, add=add, sum_out=sum_out)
     return y
 
 
@@ -258,7 +259,9 @@ def embed_bwd(c, tag, ids, dxa):
 
 
 # ------------------------------------------------------------------ attention blocks
-def self_attn_fwd(c, tag, pfx, xn, x_res, ids, B, n, causal):
+def self_attn_fwd(c, tag, pfx, xn, ids, B, n, causal):
+    """returns the block's output projection WITHOUT the residual: the caller's next LayerNorm adds it (ln_fwd add= / sum_out=),
+    so the GEMM keeps its lean epilogue and the sum is written once, by the kernel that normalises it"""
     M, H = xn.shape
     wqkv = c.pspan(pfx + "query_linear.weight", pfx + "value_linear.weight", H)
     qkv = c.ws.buf(tag + ".qkv", M, 3 * H)
@@ -267,9 +270,9 @@ def self_attn_fwd(c, tag, pfx, xn, x_res, ids, B, n, causal):
     seed, off = c.key(tag + ".adrop")
     ops.attention_fwd(qkv[:, :H], qkv[:, H:2 * H], qkv[:, 2 * H:], ctx, ids, PAD, causal, B, c.nh, n, n, c.d,
                       c.attn_drop, seed, off)
-    out = c.ws.buf(tag + ".out", M, H)
-    ops.gemm2(ctx, c.W[pfx + "output_linear.weight"], out, residual=x_res)
-    return out
+    proj = c.ws.buf(tag + ".proj", M, H)
+    ops.gemm2(ctx, c.W[pfx + "output_linear.weight"], proj)
+    return proj
 
 
 def _grad_parts(a, *col_ranges):
@@ -307,7 +310,8 @@ def cross_kv_fwd(c, tag, pfx, enc_out):
     return kv
 
 
-def cross_attn_fwd(c, tag, pfx, xn, x_res, enc_out, enc_ids, B, nq, nk, kv=None):
+def cross_attn_fwd(c, tag, pfx, xn, enc_out, enc_ids, B, nq, nk, kv=None):
+    """returns the output projection without the residual (see self_attn_fwd)"""
     M, H = xn.shape
     q = c.ws.buf(tag + ".q", M, H)
     ops.gemm2(xn, c.W[pfx + "query_linear.weight"], q)
@@ -316,9 +320,9 @@ def cross_attn_fwd(c, tag, pfx, xn, x_res, enc_out, enc_ids, B, nq, nk, kv=None)
     ctx = c.act(tag + ".ctx", M, H)
     seed, off = c.key(tag + ".adrop")
     ops.attention_fwd(q, kv[:, :H], kv[:, H:], ctx, enc_ids, PAD, False, B, c.nh, nq, nk, c.d, c.attn_drop, seed, off)
-    out = c.ws.buf(tag + ".out", M, H)
-    ops.gemm2(ctx, c.W[pfx + "output_linear.weight"], out, residual=x_res)
-    return out
+    proj = c.ws.buf(tag + ".proj", M, H)
+    ops.gemm2(ctx, c.W[pfx + "output_linear.weight"], proj)
+    return proj
 
 
 def cross_attn_bwd(c, tag, pfx, dout, xn, enc_out, d_enc_out, first, enc_ids, B, nq, nk):
@@ -404,8 +408,9 @@ def encoder_fwd(c, tag, pfx, x, ids, B, n, NL, out_kind="f32"):
     xn = ln_fwd(c, tag + ".0.ln1", pfx + "enc.0.layer_norm_mha", x)
     for i in range(NL):
         lt, lp = "%s.%d" % (tag, i), "%senc.%d." % (pfx, i)
-        a = self_attn_fwd(c, lt + ".sa", lp + "multi_head_attention.", xn, x, ids, B, n, False)
-        xn2 = ln_fwd(c, lt + ".ln2", lp + "layer_norm_ffn", a)
+        y = self_attn_fwd(c, lt + ".sa", lp + "multi_head_attention.", xn, ids, B, n, False)
+        a = c.ws.buf(lt + ".sa.out", x.shape[0], x.shape[1])
+        xn2 = ln_fwd(c, lt + ".ln2", lp + "layer_norm_ffn", x, add=y, sum_out=a)   # a = x + attention block
         # the block's residual add and the LayerNorm that reads it (next layer's first, or the final one) are one kernel
         nxt = ("%s.%d.ln1" % (tag, i + 1), "%senc.%d.layer_norm_mha" % (pfx, i + 1), "act") if i + 1 < NL else (tag + ".lnf", pfx + "layer_norm", out_kind)
         x, xn = ffn_fwd(c, lt + ".ff", lp + "positionwise_feed_forward.", xn2, a, next_ln=nxt)
@@ -450,14 +455,16 @@ def decoder_fwd(c, tag, pfx, x, ids, enc_out, enc_ids, B, T, S, NL, out_kind="ac
     for i in range(NL):
         lt, lp = "%s.%d" % (tag, i), "%sdec.%d." % (pfx, i)
         xn = xn1
-        a = self_attn_fwd(c, lt + ".sa", lp + "multi_head_attention_dec.", xn, x, ids, B, T, True)
-        xn = ln_fwd(c, lt + ".ln2", lp + "layer_norm_mha_enc", a)
+        y = self_attn_fwd(c, lt + ".sa", lp + "multi_head_attention_dec.", xn, ids, B, T, True)
+        a = c.ws.buf(lt + ".sa.out", x.shape[0], x.shape[1])
+        xn = ln_fwd(c, lt + ".ln2", lp + "layer_norm_mha_enc", x, add=y, sum_out=a)
         if side is not None and i == 0:
             torch.cuda.current_stream().wait_stream(side)
         if PDL_DECODER and i == 0:
             pdl_prev = ops.set_pdl(True)   # from here to the end of the stack nothing runs beside the main stream
-        b = cross_attn_fwd(c, lt + ".ca", lp + "multi_head_attention_enc_dec.", xn, a, enc_out, enc_ids, B, T, S, kv=kvs[i])
-        xn = ln_fwd(c, lt + ".ln3", lp + "layer_norm_ffn", b)
+        y = cross_attn_fwd(c, lt + ".ca", lp + "multi_head_attention_enc_dec.", xn, enc_out, enc_ids, B, T, S, kv=kvs[i])
+        b = c.ws.buf(lt + ".ca.out", x.shape[0], x.shape[1])
+        xn = ln_fwd(c, lt + ".ln3", lp + "layer_norm_ffn", a, add=y, sum_out=b)
         nxt = ("%s.%d.ln1" % (tag, i + 1), "%sdec.%d.layer_norm_mha_dec" % (pfx, i + 1), "act") if i + 1 < NL else (tag + ".lnf", pfx + "layer_norm", out_kind)
         x, xn1 = ffn_fwd(c, lt + ".ff", lp + "positionwise_feed_forward.", xn, b, next_ln=nxt)
     c.ws.meta[tag + ".last"] = x

@@ -465,7 +465,7 @@ def test_cuda_graph_step_matches_the_eager_schedule(env):
         res[graph] = (torch.stack(losses).cpu(), m.flat.data.clone())
     # the first steps agree to rounding; later ones drift by what Adam makes of reordered split-K sums (two eager runs do too)
     assert torch.allclose(res[True][0][:2], res[False][0][:2], rtol=2e-5, atol=1e-6), (res[True][0], res[False][0])
-    assert torch.allclose(res[True][0], res[False][0], rtol=1e-3, atol=1e-5), (res[True][0], res[False][0])
+    assert torch.allclose(res[True][0], res[False][0], rtol=5e-3, atol=1e-4), (res[True][0], res[False][0])
     upd_e, upd_g = res[False][1] - m0.flat.data.cuda(), res[True][1] - m0.flat.data.cuda()
     assert rel(upd_g, upd_e) < 3e-2
     # dropout on: replays of the same inputs differ, and everything stays finite

@@ -7,6 +7,7 @@ import pytest
 import torch
 
 pytestmark = pytest.mark.gpu
+FULL_TOL = (1e-3, 8e-2, 2e-2)   # (loss, per tensor, global) of the full-size tensor-core runs
 
 
 def rel(a, b):
@@ -27,9 +28,10 @@ def _build(cfg, sd):
     return m
 
 
-def _check(m, terms, want, grads, simt):
-    ltol, ttol, gtol = (1e-4, 2e-4, 2e-4) if simt else (1e-3, 8e-2, 2e-2)
+def _check(m, terms, want, grads, simt, tols=None):
+    ltol, ttol, gtol = tols or ((1e-4, 2e-4, 2e-4) if simt else (1e-3, 8e-2, 2e-2))
     t = terms.cpu()
+    worst = (0.0, "")
     for i, k in enumerate(("gen", "kl", "rec_i", "rec_a")):
         assert float(t[i]) == pytest.approx(float(want[k]), rel=ltol), k
     assert float(m.total_loss(t)) == pytest.approx(float(want["loss"]), rel=ltol)
@@ -42,7 +44,10 @@ def _check(m, terms, want, grads, simt):
         d = float((g.double().cpu() - gref.double()).norm())
         num += d * d
         den += float(gref.double().norm()) ** 2
-        assert d / (float(gref.double().norm()) + 1e-30) < ttol or float((g.cpu() - gref).abs().max()) < 1e-6, (k, d)
+        r = d / (float(gref.double().norm()) + 1e-30)
+        worst = max(worst, (r, k))
+        assert r < ttol or float((g.cpu() - gref.cpu()).abs().max()) < 1e-6, (k, r)
+    print("gradient error: global %.3e, worst tensor %.3e (%s)" % ((num / den) ** 0.5, worst[0], worst[1]))
     assert (num / den) ** 0.5 < gtol
 
 
@@ -76,6 +81,34 @@ def test_lstm_training_step_matches_oracle_small(env, simt):
     with ops.gemm_mode(simt=simt):
         terms = m.forward_losses(b["feats"], b["answers"], b["alengths"], b["questions"], eps=eps.cuda(), eps2=eps2.cuda())
     _check(m, terms, {k: v.detach() for k, v in want.items()}, {k: v.grad for k, v in P.items() if v.requires_grad}, simt)
+
+
+@pytest.mark.parametrize("name", ["cfg1", "cfg2", "cfg4"])
+def test_lstm_full_size_training_step_matches_fp64_oracle(env, name):
+    """BASELINE.json configs[0] (cfg1: H=512, V=5000, B=32), configs[1] (cfg2: GloVe H=300, V=15000, B=256 — the persistent
+    recurrence's production shape) and configs[3]'s per-GPU shard (cfg4: H=512, B=512) at their own sizes on the timed path,
+    against the oracle executed in fp64 on this GPU.  (The glue's wiring is the builder's restatement of the call-site contract —
+    the reference tree pins the blocks, not the wiring: SURVEY 8c.)"""
+    from blt_vqg_b200 import synth
+    from oracle import lstm_oracle
+    cfg = synth.LSTM_CONFIGS[name]
+    b = synth.make_batch(cfg, seed=21)
+    sd = lstm_oracle.init_state_dict(cfg, seed=4)
+    g = torch.Generator().manual_seed(5)
+    eps, eps2 = torch.randn(cfg["B"], cfg["Z"], generator=g), torch.randn(cfg["B"], cfg["Z"], generator=g)
+    P = {k: v.double().cuda().requires_grad_("running" not in k) for k, v in sd.items()}
+    bn = (P["encoder_cnn.bn.running_mean"].detach().clone(), P["encoder_cnn.bn.running_var"].detach().clone())
+    bg = {k: v.cuda() for k, v in b.items()}
+    loss, want = lstm_oracle.lstm_iq_losses(P, bg["feats"].double(), bg["answers"], bg["alengths"], bg["questions"],
+                                            eps.double().cuda(), eps2.double().cuda(), bn_state=bn)
+    loss.backward()
+    grads = {k: v.grad.detach().cpu() for k, v in P.items() if v.requires_grad}
+    want = {k: v.detach().cpu() for k, v in want.items()}
+    del loss
+    torch.cuda.empty_cache()
+    m = _build(cfg, sd)
+    terms = m.forward_losses(b["feats"], b["answers"], b["alengths"], b["questions"], eps=eps.cuda(), eps2=eps2.cuda())
+    _check(m, terms, want, grads, False, tols=FULL_TOL)
 
 
 def test_staged_api_and_bit_exact_greedy_ids(env, golden_dir):
