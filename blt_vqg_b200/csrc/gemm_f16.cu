@@ -497,7 +497,11 @@ extern "C" int b200iq_gemm_f16(const B200iqGemmF16* p, void* stream) {
     int kb = ceil_div(p->K, FBK), sp = split > kb ? kb : split;
     const long t256 = (long)mt * ceil_div(p->N, 256) * sp, t128 = (long)mt * ceil_div(p->N, 128) * sp;
     const double c256 = (double)((t256 + slots - 1) / slots) * 2.0, c128 = (double)((t128 + slots - 1) / slots) * 1.08;
-    if (p->N <= 128 || c128 < 0.95 * c256) pair_bn = 128;
+    // measured (profiles/r02f_tile_policy.txt): the narrower tile re-reads A twice as often and only pays off on paper — K = 2048 and
+    // N = 1536 shapes lose 10-25 %, N = K = 512 gains 8 % in isolation and nothing in the step; it stays the choice for N <= 128
+    // and behind B200IQ_F16_TILE_N=128
+    (void)c128; (void)c256;
+    if (p->N <= 128) pair_bn = 128;
     if (force_bn == 128 || force_bn == 256) pair_bn = (p->N <= 128) ? 128 : force_bn;
   }
   const int BNL = pair ? pair_bn / 2 : 128;

