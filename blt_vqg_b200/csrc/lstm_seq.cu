@@ -40,17 +40,25 @@ __device__ __forceinline__ float ls_sigmoid(float x) { return 1.f / (1.f + __exp
 struct LstmSeqDims { int T, B, H, U, Hp, LD; };  // U units per CTA, Hp = H rounded up to 8, LD = shared-memory pitch
 
 // W_slice[4*ul + gate][k] = W_hh[gate*H + (rank*U + ul)][k]   (zero for units / k beyond H)
-__device__ __forceinline__ void ls_load_wslice(float* Ws, const float* __restrict__ whh, const LstmSeqDims& d, int rank) {
+// round: store round-to-nearest TF32 values (the single-pass products of the BPTT when the caller's tensors are unrounded fp32)
+__device__ __forceinline__ void ls_load_wslice(float* Ws, const float* __restrict__ whh, const LstmSeqDims& d, int rank, bool round = false) {
   // one warp per slice row, lanes along k: coalesced 128-byte reads, 8 rows in flight per warp
   const int rows = 4 * d.U, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   for (int n = warp; n < rows; n += LS_THREADS / 32) {
     const int ul = n >> 2, gate = n & 3, u = rank * d.U + ul;
     const float* src = whh + (size_t)(gate * d.H + u) * d.H;
 #pragma unroll 4
-    for (int k = lane; k < d.LD; k += 32) Ws[n * d.LD + k] = (u < d.H && k < d.H) ? __ldg(src + k) : 0.f;
+    for (int k = lane; k < d.LD; k += 32) {
+      const float w = (u < d.H && k < d.H) ? __ldg(src + k) : 0.f;
+      Ws[n * d.LD + k] = round ? tf32_rn(w) : w;
+    }
   }
 }
 
+// PRECISE (the fp16-plane / no-rounding mode of the library): h and W_hh are unrounded fp32 and every product h.W_hh^T is the 3-term
+// TF32 split hi.hi + lo.hi + hi.lo (hi = round-to-nearest TF32, lo = x - hi), ~2^-21 per operand: the encoder's final state
+// feeds ReLU MLPs, where 11-bit forward products flip gates (profiles/r02a_cpu_precision_study.txt).
+template <bool PRECISE>
 __global__ void __cluster_dims__(LS_CL, 1, 1) __launch_bounds__(LS_THREADS, 1)
 lstm_seq_fwd_kernel(float* gates, const float* __restrict__ whh, float* hbuf, float* cbuf,
                     const int* __restrict__ lengths, LstmSeqDims d, int rn) {
@@ -112,13 +120,26 @@ lstm_seq_fwd_kernel(float* gates, const float* __restrict__ whh, float* hbuf, fl
 #pragma unroll 2
     for (int ks = 0; ks < KS; ++ks) {
       const float* hp = hs + 8 * ks + t4;
-      const float a0 = hp[g * d.LD], a1 = hp[(g + 8) * d.LD], a2 = hp[g * d.LD + 4], a3 = hp[(g + 8) * d.LD + 4];
+      float a0 = hp[g * d.LD], a1 = hp[(g + 8) * d.LD], a2 = hp[g * d.LD + 4], a3 = hp[(g + 8) * d.LD + 4];
+      float l0 = 0.f, l1 = 0.f, l2 = 0.f, l3 = 0.f;
+      if (PRECISE) {
+        const float h0 = tf32_rn(a0), h1 = tf32_rn(a1), h2 = tf32_rn(a2), h3 = tf32_rn(a3);
+        l0 = a0 - h0; l1 = a1 - h1; l2 = a2 - h2; l3 = a3 - h3;
+        a0 = h0; a1 = h1; a2 = h2; a3 = h3;
+      }
 #pragma unroll
       for (int i = 0; i < LS_MAXT; ++i) {
         const int nt = warp + 8 * i;
         if (nt < NT) {
           const float* wp = Ws + (8 * nt + g) * d.LD + 8 * ks + t4;
-          ls_mma(acc[i], a0, a1, a2, a3, wp[0], wp[4]);
+          if (PRECISE) {
+            const float w0 = wp[0], w1 = wp[4], wh0 = tf32_rn(w0), wh1 = tf32_rn(w1);
+            ls_mma(acc[i], l0, l1, l2, l3, wh0, wh1);
+            ls_mma(acc[i], a0, a1, a2, a3, w0 - wh0, w1 - wh1);
+            ls_mma(acc[i], a0, a1, a2, a3, wh0, wh1);
+          } else {
+            ls_mma(acc[i], a0, a1, a2, a3, wp[0], wp[4]);
+          }
         }
       }
     }
@@ -174,7 +195,9 @@ __global__ void __cluster_dims__(LS_CL, 1, 1) __launch_bounds__(LS_THREADS, 1)
 lstm_seq_bwd_kernel(const float* __restrict__ gates, const float* __restrict__ cbuf, const float* __restrict__ whh,
                     const float* __restrict__ dh_last, const float* __restrict__ d_out, float* __restrict__ dgates,
                     float* __restrict__ dh0, float* __restrict__ dc0, float* part, const int* __restrict__ lengths,
-                    LstmSeqDims d, int LDG, int rn) {
+                    LstmSeqDims d, int LDG, int rn, int rnd_ops) {
+  // rnd_ops: the caller's tensors are unrounded fp32 -> round the operands of the (single-pass) products to TF32 here: the W_hh
+  // slice once at load, the gate-gradient tile as it is written to shared memory (mma.sync would truncate instead)
   extern __shared__ float ls_smem[];
   float* Ws = ls_smem;                    // [4U][LD]
   float* dgs = Ws + 4 * d.U * d.LD;       // [16][LDG]  (unit-major / gate-minor columns, like the rows of Ws)
@@ -182,7 +205,7 @@ lstm_seq_bwd_kernel(const float* __restrict__ gates, const float* __restrict__ c
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t4 = lane & 3;
   const int NT = d.U / 2, NTB = d.Hp / 8, KS = d.U / 2;
   const size_t BH = (size_t)d.B * d.H, B4H = 4 * BH;
-  ls_load_wslice(Ws, whh, d, rank);
+  ls_load_wslice(Ws, whh, d, rank, rnd_ops != 0);
   for (int idx = threadIdx.x; idx < LS_ROWS * LDG; idx += LS_THREADS) dgs[idx] = 0.f;
   const int my_row = g + 8 * (t4 & 1), b = b0 + my_row;
   const bool row_ok = b < d.B;
@@ -235,7 +258,8 @@ lstm_seq_bwd_kernel(const float* __restrict__ gates, const float* __restrict__ c
         } else {
           dh_run[i] = dh;  // the state was copied at this step: the gradient passes straight through, dc unchanged
         }
-        *reinterpret_cast<float4*>(dgs + my_row * LDG + 4 * ul[i]) = make_float4(dg4[0], dg4[1], dg4[2], dg4[3]);
+        *reinterpret_cast<float4*>(dgs + my_row * LDG + 4 * ul[i]) =
+            rnd_ops ? make_float4(tf32_rn(dg4[0]), tf32_rn(dg4[1]), tf32_rn(dg4[2]), tf32_rn(dg4[3])) : make_float4(dg4[0], dg4[1], dg4[2], dg4[3]);
         ct[i] = cprev[i];  // c_{t-1} is the next step's c_t
       }
     }
@@ -322,9 +346,15 @@ extern "C" int b200iq_lstm_seq_fwd(float* gates, const float* whh, float* hbuf, 
   LstmSeqDims d; size_t smem;
   ls_dims(T, B, H, &d, &smem);
   static bool attr_done = false;
-  if (!attr_done) { cudaFuncSetAttribute(lstm_seq_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); attr_done = true; }
+  if (!attr_done) {
+    cudaFuncSetAttribute(lstm_seq_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaFuncSetAttribute(lstm_seq_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    attr_done = true;
+  }
   const int clusters = (B + LS_ROWS - 1) / LS_ROWS;
-  lstm_seq_fwd_kernel<<<clusters * LS_CL, LS_THREADS, smem, (cudaStream_t)stream>>>(gates, whh, hbuf, cbuf, lengths, d, round_mode());
+  // rounding mode off = the caller keeps unrounded fp32 tensors (fp16-plane scheme): 3-term products
+  if (round_mode()) lstm_seq_fwd_kernel<false><<<clusters * LS_CL, LS_THREADS, smem, (cudaStream_t)stream>>>(gates, whh, hbuf, cbuf, lengths, d, 1);
+  else lstm_seq_fwd_kernel<true><<<clusters * LS_CL, LS_THREADS, smem, (cudaStream_t)stream>>>(gates, whh, hbuf, cbuf, lengths, d, 0);
   return launch_status("lstm_seq_fwd");
 }
 
@@ -352,6 +382,6 @@ extern "C" int b200iq_lstm_seq_bwd(const float* gates, const float* cbuf, const 
   if (!attr_done) { cudaFuncSetAttribute(lstm_seq_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); attr_done = true; }
   const int clusters = (B + LS_ROWS - 1) / LS_ROWS;
   lstm_seq_bwd_kernel<<<clusters * LS_CL, LS_THREADS, smem, (cudaStream_t)stream>>>(gates, cbuf, whh, dh_last, d_out, dgates, dh0, dc0,
-                                                                                    workspace, lengths, d, LDG, round_mode());
+                                                                                    workspace, lengths, d, LDG, round_mode(), round_mode() ? 0 : 1);
   return launch_status("lstm_seq_bwd");
 }

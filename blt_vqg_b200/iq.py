@@ -238,31 +238,9 @@ class IQ(nn.Module):
                 self._wops_exact = tf.WeightOperands(self.arena)
             return self._wops_exact
         if self._wops is None:
-            dev = self.flat.device
-            whi = torch.zeros(self.flat.numel(), device=dev, dtype=torch.float16)
-            wlo = torch.zeros(self.flat.numel(), device=dev, dtype=torch.float16)
-            odd = {}
-            for name, shape, _ in self.arena.specs:
-                name = name.replace("#pack", "")
-                if len(shape) == 2 and shape[1] % 8 and name != "embedding.0.weight":
-                    ld = ops.pad8(shape[1])   # TMA needs 16-byte row pitches: E = 300 / L = 100 wide matrices get padded planes
-                    odd[name] = ops.Act(hi=torch.zeros(shape[0], ld, device=dev, dtype=torch.float16)[:, :shape[1]],
-                                        lo=torch.zeros(shape[0], ld, device=dev, dtype=torch.float16)[:, :shape[1]])
-            self._wops = tf.WeightOperands(self.arena, whi, wlo, odd)
-        w = self._wops
-        ops.split_f16(self.flat.data, w.whi, w.wlo)
-        for name, a in w.odd.items():
-            ops.split_f16(self.arena.views[name], a.hi, a.lo)
-        return w
-
-    def _next_seed(self):
-        """Philox key of the next stochastic pass.  The reference draws fresh dropout masks and a fresh torch.randn eps on every
-        call (transformer_layers.py:45,406,520); a counter-based generator needs a new key per call to do the same, so the
-        module counts its own stochastic passes (checkpoint.py saves / restores the counter)."""
-        if self.seed_dev is not None:
-            return self.seed + 1000003 * self.seed_rank   # + *seed_dev, added by the kernels
-        self.step_idx += 1
-        return self.seed + self.step_idx + 1000003 * self.seed_rank
+            self._wops = tf.build_weight_operands(self.arena, self.flat.device, skip=("embedding.0.weight",))
+        tf.refresh_weight_operands(self._wops, self.arena, self.flat.data)
+        return self._wops
 
     def _make_ctx(self, B, S, R, T, training):
         _lib.require_device()

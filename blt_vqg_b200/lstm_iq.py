@@ -26,10 +26,24 @@ import torch
 import torch.nn as nn
 
 from . import _lib, ops
-from . import tf32_blocks as tf
+from . import blocks as tf
 from .params import Arena, export_state_dict, import_state_dict
 
 PAD = 0
+
+
+def _planes_mode(fn):
+    """public entry points run with the library's TF32 write-rounding off (fp32 tensors stay exact; precision is decided per GEMM
+    operand by its fp16 planes, and the persistent recurrence takes its 3-term form)"""
+    import functools
+
+    @functools.wraps(fn)
+    def wrapped(*a, **k):
+        with ops.no_rounding():
+            return fn(*a, **k)
+    return wrapped
+
+
 TERMS = ("gen", "kl", "rec_i", "rec_a", "count", "unused0", "unused1", "unused2")
 
 
@@ -118,7 +132,7 @@ class LSTMIQ(nn.Module):
         # draws a fresh Philox key, like the reference's nn.Dropout / torch.randn draw fresh numbers on every call
         self.seed, self.seed_rank, self.step_idx = 1234, 0, 0
         self.on_grad_ready = None
-        self._ws, self._gflat, self._terms, self._wflat = {}, None, None, None
+        self._ws, self._gflat, self._terms, self._wops, self._wops_exact = {}, None, None, None, None
 
     @classmethod
     def from_config(cls, cfg, **kw):
@@ -128,7 +142,7 @@ class LSTMIQ(nn.Module):
     def _apply(self, fn, *a, **k):
         super()._apply(fn, *a, **k)
         self.arena.bind(self.flat.data)
-        self._ws, self._gflat, self._terms, self._wflat = {}, None, None, None
+        self._ws, self._gflat, self._terms, self._wops, self._wops_exact = {}, None, None, None, None
         return self
 
     def _buffers_map(self):
@@ -171,15 +185,19 @@ class LSTMIQ(nn.Module):
 
     def _make_ctx(self, key, training):
         _lib.require_device()
-        ws = self._workspace(key)
-        wflat = None
-        if not ops.exact_mode():
-            if self._wflat is None:
-                self._wflat = torch.empty_like(self.flat.data)
-            wflat = ops.round_tf32(self.flat.data, self._wflat)
+        ws = self._workspace(key + (ops.exact_mode(),))
+        if ops.exact_mode():
+            if self._wops_exact is None:
+                self._wops_exact = tf.WeightOperands(self.arena)
+            weights = self._wops_exact
+        else:
+            if self._wops is None:   # fp16 planes (hi, lo) of the weights; the embedding tables are gathered, never multiplied
+                self._wops = tf.build_weight_operands(self.arena, self.flat.device, skip=tuple(n for n in self.arena.views if n.endswith("embedding.weight") or n == "category_encoder.weight"))
+            tf.refresh_weight_operands(self._wops, self.arena, self.flat.data)
+            weights = self._wops
         self.step_idx += 1
         c = tf.Ctx(self.arena, self.grad_arena, ws, self.H, 1, self.A, self.H, 0.0, 0.0, training,
-                   self.seed + self.step_idx + 1000003 * self.seed_rank, wflat=wflat)
+                   self.seed + self.step_idx + 1000003 * self.seed_rank, weights)
         c.on_ready = self.on_grad_ready
         c.in_drop = self.input_dropout_p if training else 0.0
         return c
@@ -194,7 +212,7 @@ class LSTMIQ(nn.Module):
         f = images.to(self.flat.device, torch.float32, non_blocking=True).contiguous()
         if f.dim() != 2:
             raise _lib.B200iqError("LSTMIQ takes pooled trunk features (B, FEAT); run the frozen CNN trunk first")
-        return f if ops.exact_mode() else ops.round_tf32(f, c.ws.buf("feats", *f.shape))
+        return f
 
     @staticmethod
     def _ids(t, device):
@@ -206,7 +224,7 @@ class LSTMIQ(nn.Module):
         """models/encoder_cnn.py:33-34"""
         ws, P, B, H = c.ws, c.P, feats.shape[0], self.H
         img_pre = ws.buf("img_pre", B, H)
-        ops.gemm(feats, c.W["encoder_cnn.cnn.fc.weight"], img_pre, bias=P["encoder_cnn.cnn.fc.bias"], fp32_out=True)
+        tf.mm(c, feats, "encoder_cnn.cnn.fc.weight", img_pre, bias=P["encoder_cnn.cnn.fc.bias"])
         img = ws.buf("img", B, H)
         ops.bn_fwd(img_pre, P["encoder_cnn.bn.weight"], P["encoder_cnn.bn.bias"], img, ws.buf("bn.mean", H), ws.buf("bn.rstd", H),
                    self.bn_running_mean, self.bn_running_var, c.training)
@@ -221,7 +239,7 @@ class LSTMIQ(nn.Module):
         bsum = ws.buf(tag + ".bsum", 4 * H)
         ops.axpby(P[pfx + "bias_ih_l0"], P[pfx + "bias_hh_l0"], bsum)
         gates = ws.buf(tag + ".gates", T, B, 4 * H)
-        ops.gemm(e, c.W[pfx + "weight_ih_l0"], gates.view(T * B, 4 * H), bias=bsum, fp32_out=True)  # x-projection of all steps
+        tf.mm(c, e, pfx + "weight_ih_l0", gates.view(T * B, 4 * H), bias=bsum)  # x-projection of all steps
         hbuf, cbuf = ws.buf(tag + ".h", T + 1, B, H), ws.buf(tag + ".c", T + 1, B, H)
         if h0 is None:
             hbuf[0].zero_()
@@ -229,19 +247,19 @@ class LSTMIQ(nn.Module):
         else:
             hbuf[0].copy_(h0)
             cbuf[0].copy_(c0)
-        whh = c.W[pfx + "weight_hh_l0"]
         if PERSISTENT and ops.lstm_seq_supported(H):
-            ops.lstm_seq_fwd(gates, whh, hbuf, cbuf, lengths)   # the whole recurrence in one launch
+            # the whole recurrence in one launch; the kernel splits h and the fp32 master W_hh into TF32 hi / lo itself (3-term)
+            ops.lstm_seq_fwd(gates, P[pfx + "weight_hh_l0"], hbuf, cbuf, lengths)
             return hbuf
         for t in range(T):
-            ops.gemm(hbuf[t], whh, gates[t], residual=gates[t], fp32_out=True)
+            tf.mm(c, hbuf[t], pfx + "weight_hh_l0", gates[t], residual=gates[t])
             ops.lstm_cell_fwd(gates[t], cbuf[t], hbuf[t], cbuf[t + 1], hbuf[t + 1], lengths, t)
         return hbuf
 
     def _lstm_bwd(self, c, tag, pfx, emb_name, ids_tm, T, B, dh_last, d_out, lengths):
         """BPTT.  dh_last: gradient wrt the final hidden state (or None); d_out: [T*B,H] gradient wrt every output (or None).
         Returns (d h0, d c0) in workspace buffers; accumulates weight / embedding gradients."""
-        ws, G, H = c.ws, c.G, self.H
+        ws, G, H, P = c.ws, c.G, self.H, c.P
         gates, hbuf, cbuf, e = ws[tag + ".gates"], ws[tag + ".h"], ws[tag + ".c"], ws[tag + ".e"]
         dgates = ws.buf(tag + ".dgates", T, B, 4 * H)
         dh_run, dc = ws.buf(tag + ".dh_run", B, H), ws.buf(tag + ".dc", B, H)
@@ -250,21 +268,20 @@ class LSTMIQ(nn.Module):
         else:
             dh_run.copy_(dh_last)
         dc.zero_()
-        whh = c.W[pfx + "weight_hh_l0"]
         dov = d_out.view(T, B, H) if d_out is not None else None
         if PERSISTENT and ops.lstm_seq_supported(H):
-            ops.lstm_seq_bwd(gates, cbuf, whh, dh_run, dov, dgates, dh_run, dc, lengths)   # BPTT in one launch
+            ops.lstm_seq_bwd(gates, cbuf, P[pfx + "weight_hh_l0"], dh_run, dov, dgates, dh_run, dc, lengths)   # BPTT in one launch
         else:
             for t in reversed(range(T)):
                 ops.lstm_cell_bwd(gates[t], cbuf[t], cbuf[t + 1], dh_run, dov[t] if dov is not None else None, dc, dgates[t], lengths, t)
-                ops.gemm(dgates[t], whh, dh_run, b_t=True, residual=dh_run)
+                tf.mm(c, dgates[t], pfx + "weight_hh_l0", dh_run, b_t=True, residual=dh_run)
         dg = dgates.view(T * B, 4 * H)
         def weight_grads():   # off the dX chain: side stream, under the input-gradient GEMM and the embedding scatter
             tf.grad_w(c, dg, hbuf[:T].view(T * B, H), G[pfx + "weight_hh_l0"], G[pfx + "bias_hh_l0"])
             tf.grad_w(c, dg, e, G[pfx + "weight_ih_l0"], G[pfx + "bias_ih_l0"])
         ev = c.mark()
         de = ws.buf(tag + ".de", T * B, H)
-        ops.gemm(dg, c.W[pfx + "weight_ih_l0"], de, b_t=True)
+        tf.mm(c, dg, pfx + "weight_ih_l0", de, b_t=True)
         c.on_side(weight_grads, ev)
         ops.dropout_(de, c.in_drop, *c.key(tag + ".indrop"))
         ops.embed_scatter_add(ids_tm, de, G[emb_name], -1)
@@ -295,7 +312,7 @@ class LSTMIQ(nn.Module):
         wml = c.pspan("mu_%s_encoder.weight" % space, "logvar_%s_encoder.weight" % space, H)
         o0, o1 = self.arena.span("mu_%s_encoder.bias" % space, "logvar_%s_encoder.bias" % space)
         mulv = c.ws.buf("mulv", B, 2 * self.Z)
-        ops.gemm(att, wml, mulv, bias=self.flat.data[o0:o1], fp32_out=True)
+        tf.mm(c, att, wml, mulv, bias=self.flat.data[o0:o1])
         return cat, att, mulv
 
     def _init_hidden_fwd(self, c, img, z, B, proj="z_decoder"):
@@ -309,6 +326,21 @@ class LSTMIQ(nn.Module):
         """forward + losses (old_train_iq.py:100-155 contract) + complete backward; returns the device vector
         (gen, kl, rec_i, rec_a, n_tokens, ...); gradients are ACCUMULATED into `grad_arena`.  `kliter` is unused (signature
         shared with IQ.forward_losses so train.TrainStep drives both)."""
+        with ops.no_rounding():
+            return self._forward_losses(images, answers, alengths, questions, eps, backward, eps2)
+
+    def scale(self, tokens=None):
+        """loss scale of the fp16-plane path (see IQ.scale): every gradient seed is multiplied by it, train.TrainStep divides it out"""
+        if ops.exact_mode():
+            return 1.0
+        if tokens is None:
+            return getattr(self, "_grad_scale", 1.0)
+        return 16.0 * 2.0 ** math.floor(math.log2(max(1.0, tokens / 2.0)))
+
+    def unscaled_grads(self):
+        return self.grad_arena / getattr(self, "_grad_scale", 1.0)
+
+    def _forward_losses(self, images, answers, alengths, questions, eps, backward, eps2):
         dev = self.flat.device
         aids, qids = self._ids(answers, dev), self._ids(questions, dev)
         alens = self._ids(alengths, dev)
@@ -316,7 +348,8 @@ class LSTMIQ(nn.Module):
         Td = T - 1
         c = self._make_ctx(("train", B, S, T, bool(self.training)), self.training)
         ws, P, G, H, Z, V = c.ws, c.P, c.G, self.H, self.Z, self.V
-        lam = self.lambdas
+        SC = self._grad_scale = self.scale(B * Td)
+        lam = {k: v * SC for k, v in self.lambdas.items()}   # every gradient seed carries the loss scale (the loss TERMS do not)
         terms = self.terms
         terms.zero_()
         feats = self._feats(c, images)
@@ -350,17 +383,21 @@ class LSTMIQ(nn.Module):
         rows = max(128, ((48 << 20) // (4 * V)) // 128 * 128)
         chunk = min(M, rows)
         logits = ws.buf("logits_chunk", chunk, V)
+        # the chunk's gradient goes out as an fp16 plane beside the fp32 logits (exact mode: in place); the vocabulary products are
+        # smooth (no ReLU behind them): single pass
+        lgrad = ops.Act(f32=logits) if ops.exact_mode() else ops.Act(hi=ws.buf("logits_grad", chunk, V, dtype=torch.float16))
+        outs_a = tf.act(c, outs, lo=False)
         wout, bout = c.W["decoder.out.weight"], P["decoder.out.bias"]
         for r0 in range(0, M, chunk):
             n = min(chunk, M - r0)
-            lg, xs = logits[:n], outs[r0:r0 + n]
-            ops.gemm(xs, wout, lg, bias=bout, fp32_out=True)                          # decoder_rnn.py:107
-            ops.ce_rows(lg, tgt[r0:r0 + n], PAD, count, lam["lambda_gen"], terms[0:1], write_grad=backward)
+            lg, xs, gr = logits[:n], outs_a.rows(r0, r0 + n), lgrad.rows(0, n)
+            ops.gemm2(xs, wout, lg, bias=bout, terms=1)                                # decoder_rnn.py:107
+            ops.ce_rows_act(lg, tgt[r0:r0 + n], PAD, count, lam["lambda_gen"], terms[0:1], gr if backward else None)
             if backward:
                 ev = c.mark()
-                ops.gemm(lg, wout, d_out[r0:r0 + n], b_t=True, auto_split=True)
-                c.on_side(lambda: tf.grad_w(c, lg, xs, G["decoder.out.weight"], G["decoder.out.bias"]), ev)
-                c.join_side()   # before the next chunk's logits overwrite lg
+                ops.gemm2(gr, wout, d_out[r0:r0 + n], b_t=True, auto_split=True, terms=1)
+                c.on_side(lambda: tf.grad_w(c, gr, xs, G["decoder.out.weight"], G["decoder.out.bias"]), ev)
+                c.join_side()   # before the next chunk's gradient overwrites gr
         # ---- reconstructions from the detached features through a second reparameterisation (old_train_iq.py:145-155)
         z2 = ws.buf("z2", B, Z)
         ops.latent_fwd(zeros2z, mulv, e2, z2, None)
@@ -405,7 +442,7 @@ class LSTMIQ(nn.Module):
             ops.latent_bwd(zeros2z, mulv, ee, dzz, kc, dprior, dpost)
             tf.grad_w(c, dpost, att, gml, gmlb)
             d_att = ws.buf("d_att." + tag, B, H)
-            ops.gemm(dpost, wml, d_att, b_t=True)
+            tf.mm(c, dpost, wml, d_att, b_t=True)
             if flows:
                 d_cat = self._mlp_bwd(c, "att", "answer_attention", d_att, cat)
             else:
@@ -431,11 +468,13 @@ class LSTMIQ(nn.Module):
         return self._make_ctx(("stage", tag, B, bool(self.training)), self.training)
 
     @torch.no_grad()
+    @_planes_mode
     def encode_images(self, images):
         c = self._stage_ctx("img", images.shape[0])
         return self._head_fwd(c, self._feats(c, images)).clone()
 
     @torch.no_grad()
+    @_planes_mode
     def encode_answers(self, answers, alengths):
         dev = self.flat.device
         aids = self._ids(answers, dev)
@@ -445,6 +484,7 @@ class LSTMIQ(nn.Module):
         return self._encode_answers_fwd(c, aids, alens, B, S).clone()
 
     @torch.no_grad()
+    @_planes_mode
     def encode_into_z(self, image_features, answer_features):
         B = image_features.shape[0]
         c = self._stage_ctx("z", B)
@@ -452,6 +492,7 @@ class LSTMIQ(nn.Module):
         return mulv[:, :self.Z].clone(), mulv[:, self.Z:].clone()
 
     @torch.no_grad()
+    @_planes_mode
     def reparameterize(self, mus, logvars, eps=None):
         """train: mu + eps*exp(.5*logvar) with Philox eps (or the injected one); eval: mu"""
         if not self.training:
@@ -473,6 +514,7 @@ class LSTMIQ(nn.Module):
         return z.clone()
 
     @torch.no_grad()
+    @_planes_mode
     def reconstruct_inputs(self, image_features, answer_features, eps=None):
         mus, logvars = self.encode_into_z(image_features, answer_features)
         zs = self.reparameterize(mus, logvars, eps)
@@ -487,6 +529,7 @@ class LSTMIQ(nn.Module):
             raise _lib.B200iqError("this LSTMIQ was built with no_category_space=True")
 
     @torch.no_grad()
+    @_planes_mode
     def encode_categories(self, categories):
         """nn.Embedding(num_categories, H) lookup: categories (B,) int -> (B, H)"""
         self._need_category_space()
@@ -496,6 +539,7 @@ class LSTMIQ(nn.Module):
         return ops.embed_gather(ids, c.P["category_encoder.weight"], out).clone()
 
     @torch.no_grad()
+    @_planes_mode
     def encode_into_t(self, image_features, category_features):
         """(t_mus, t_logvars) = the category space's Gaussian, same shape of computation as encode_into_z"""
         self._need_category_space()
@@ -505,6 +549,7 @@ class LSTMIQ(nn.Module):
         return mulv[:, :self.Z].clone(), mulv[:, self.Z:].clone()
 
     @torch.no_grad()
+    @_planes_mode
     def _kl(self, prior, post):
         """mean_b KL(N(post) || N(prior)) through b200iq_latent_fwd; prior / post are (mu, logvar) pairs, prior None = unit normal"""
         B = post[0].shape[0]
@@ -550,6 +595,7 @@ class LSTMIQ(nn.Module):
         return self._predict(img, self.reparameterize(t_mus, t_logvars, eps), True)
 
     @torch.no_grad()
+    @_planes_mode
     def decode_questions(self, image_features, zs, questions=None, teacher_forcing_ratio=0, decode_function=None, from_t=False):
         """models/decoder_rnn.py:110-162 behind the glue: returns (outputs, hidden, ret_dict) with `outputs` a list of (B, V)
         log-probability tensors and ret_dict = {sequence: list of (B,1) argmax ids, length: list of ints}.
@@ -569,7 +615,7 @@ class LSTMIQ(nn.Module):
             ids_q = ops.transpose_ids(qids, ws.buf("dec.ids", Td * B, dtype=torch.int32), 0, Td)
             hbuf = self._lstm_fwd(c, "dec", "decoder.rnn.", "decoder.embedding.weight", ids_q, Td, B, hid, hid, None)
             logp = ws.buf("logp", Td * B, V)
-            ops.gemm(hbuf[1:].view(Td * B, H), c.W["decoder.out.weight"], logp, bias=c.P["decoder.out.bias"], fp32_out=True)
+            tf.mm(c, hbuf[1:].view(Td * B, H), "decoder.out.weight", logp, bias=c.P["decoder.out.bias"], terms=1)
             ops.log_softmax_rows_(logp)
             top = ws.buf("top", Td * B, dtype=torch.int32)
             ops.topk_softmax_rows(logp, 1, top)
@@ -586,7 +632,7 @@ class LSTMIQ(nn.Module):
                 hb = self._lstm_fwd(c, "dec1", "decoder.rnn.", "decoder.embedding.weight", tok, 1, B, h, cc, None)
                 h, cc = hb[1].clone(), ws["dec1.c"][1].clone()
                 logp = ws.buf("logp1", B, V)
-                ops.gemm(h, c.W["decoder.out.weight"], logp, bias=c.P["decoder.out.bias"], fp32_out=True)
+                tf.mm(c, h, "decoder.out.weight", logp, bias=c.P["decoder.out.bias"], terms=1)
                 ops.log_softmax_rows_(logp)
                 ops.topk_softmax_rows(logp, 1, tok)
                 outputs.append(logp.clone())

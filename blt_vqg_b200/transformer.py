@@ -63,6 +63,7 @@ class WeightOperands:
         self.vh = arena.views_over(whi) if whi is not None else None
         self.vl = arena.views_over(wlo) if wlo is not None else None
         self.cache = {}
+        self.odd_spans = {}   # (o0, o1, cols) -> padded planes of a packed span whose pitch is not a multiple of 8 halves
 
     def __getitem__(self, name):
         a = self.cache.get(name)
@@ -83,10 +84,41 @@ class WeightOperands:
             o0, o1 = self.arena.span(first, last)
             if self.whi is None:
                 a = ops.Act(f32=self.arena.flat.detach()[o0:o1].view(-1, cols))
+            elif cols % 8:
+                rows, ld = (o1 - o0) // cols, ops.pad8(cols)
+                a = ops.Act(hi=torch.zeros(rows, ld, device=self.whi.device, dtype=torch.float16)[:, :cols],
+                            lo=torch.zeros(rows, ld, device=self.whi.device, dtype=torch.float16)[:, :cols])
+                self.odd_spans[(o0, o1, cols)] = a
+                ops.split_f16(self.arena.flat.detach()[o0:o1].view(-1, cols), a.hi, a.lo)   # later steps: refresh_weight_operands
             else:
                 a = ops.Act(hi=self.whi[o0:o1].view(-1, cols), lo=self.wlo[o0:o1].view(-1, cols))
             self.cache[key] = a
         return a
+
+
+def build_weight_operands(arena, device, skip=()):
+    """the fp16 plane arenas (hi, lo) mirroring a parameter arena, plus padded planes for 2-D weights whose row pitch is not a
+    multiple of 8 halves (TMA wants 16-byte pitches); `skip`: 2-D tensors that never are GEMM operands (embedding tables)"""
+    n = arena.flat.numel()
+    whi = torch.zeros(n, device=device, dtype=torch.float16)
+    wlo = torch.zeros(n, device=device, dtype=torch.float16)
+    odd = {}
+    for name, shape, _ in arena.specs:
+        name = name.replace("#pack", "")
+        if len(shape) == 2 and shape[1] % 8 and name not in skip:
+            ld = ops.pad8(shape[1])
+            odd[name] = ops.Act(hi=torch.zeros(shape[0], ld, device=device, dtype=torch.float16)[:, :shape[1]],
+                                lo=torch.zeros(shape[0], ld, device=device, dtype=torch.float16)[:, :shape[1]])
+    return WeightOperands(arena, whi, wlo, odd)
+
+
+def refresh_weight_operands(w, arena, flat):
+    """re-split the fp32 masters into the planes (once per step: 4 B read + 4 B written per parameter)"""
+    ops.split_f16(flat, w.whi, w.wlo)
+    for name, a in w.odd.items():
+        ops.split_f16(arena.views[name], a.hi, a.lo)
+    for (o0, o1, cols), a in w.odd_spans.items():
+        ops.split_f16(flat[o0:o1].view(-1, cols), a.hi, a.lo)
 
 
 class Ctx:

@@ -1,6 +1,7 @@
 """GPU parity of the LSTM variant (through the C ABI): training step vs the golden fixture built from the reference's own
 DecoderRNN / EncoderRNN / MLP classes and vs the oracle on a larger ragged batch; staged API; bit-exact greedy ids.
-Tolerances as in test_iq_gpu.py: exact path 1e-4 / 2e-4; tensor-core (TF32) path losses 1e-3, gradients global 2e-2."""
+Tolerances as in test_iq_gpu.py: exact path 1e-4 / 2e-4; tensor-core path (fp16 operand planes: 3-term forward products and
+3-term TF32 recurrence, single-pass backward) losses 1e-3, gradients: see FULL_TOL / _check."""
 import os
 
 import pytest
@@ -37,7 +38,7 @@ def _check(m, terms, want, grads, simt, tols=None):
     assert float(m.total_loss(t)) == pytest.approx(float(want["loss"]), rel=ltol)
     num = den = 0.0
     for k, gref in grads.items():
-        g = m.arena.view_of(m.grad_arena, k)
+        g = m.arena.view_of(m.unscaled_grads(), k)
         if k == "encoder_cnn.cnn.fc.bias":  # exactly-zero gradient (bias in front of BatchNorm)
             assert float(g.abs().max()) < 1e-3
             continue
