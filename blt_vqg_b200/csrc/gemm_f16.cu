@@ -466,7 +466,7 @@ extern "C" int b200iq_gemm_f16(const B200iqGemmF16* p, void* stream) {
   B200IQ_CHECK_ARG(!(f & B200IQ_GEMM_ACCUM) || (p->C && !p->C_hi), "gemm_f16: ACCUM writes fp32 C only");
   B200IQ_CHECK_ARG(p->lda >= (amn ? p->M : p->K) && p->ldb >= (bmn ? p->N : p->K), "gemm_f16: leading dimension too small");
   B200IQ_CHECK_ARG((p->lda & 7) == 0 && (p->ldb & 7) == 0, "gemm_f16: lda/ldb must be multiples of 8 halves (lda=%d ldb=%d)", p->lda, p->ldb);
-  B200IQ_CHECK_ARG((((uintptr_t)p->A_hi | (uintptr_t)p->B_hi | (uintptr_t)p->A_lo | (uintptr_t)p->B_lo) & 15) == 0, "gemm_f16: operand planes must be 16-byte aligned");
+  B200IQ_CHECK_ARG((((uintptr_t)p->A_hi | (uintptr_t)p->B_hi | (uintptr_t)p->A_lo | (uintptr_t)p->B_lo) & 15) == 0, "gemm_f16: operand planes must be 16-byte aligned (A_hi %p A_lo %p B_hi %p B_lo %p; M=%d N=%d K=%d)", p->A_hi, p->A_lo, p->B_hi, p->B_lo, p->M, p->N, p->K);
   B200IQ_CHECK_ARG(terms == 1 || (!amn && !bmn), "gemm_f16: the 3-term product takes K-major A and B");
   F16Epi e{p->C, (__half*)p->C_hi, (__half*)p->C_lo, p->bias, p->residual, (const __half*)p->gate,
            p->M, p->N, p->ldc, p->ldh, p->ldr, p->ldg, f, p->alpha, 0.f, 1.f, 0ull, 0ull, nullptr};

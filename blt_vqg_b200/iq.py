@@ -242,6 +242,15 @@ class IQ(nn.Module):
         tf.refresh_weight_operands(self._wops, self.arena, self.flat.data)
         return self._wops
 
+    def _next_seed(self):
+        """Philox key of the next stochastic pass.  The reference draws fresh dropout masks and a fresh torch.randn eps on every
+        call (transformer_layers.py:45,406,520); a counter-based generator needs a new key per call to do the same, so the
+        module counts its own stochastic passes (checkpoint.py saves / restores the counter)."""
+        if self.seed_dev is not None:
+            return self.seed + 1000003 * self.seed_rank   # + *seed_dev, added by the kernels
+        self.step_idx += 1
+        return self.seed + self.step_idx + 1000003 * self.seed_rank
+
     def _make_ctx(self, B, S, R, T, training):
         _lib.require_device()
         key = (B, S, R, T, bool(self.latent_transformer), bool(training), ops.exact_mode())

@@ -51,7 +51,9 @@ class Arena:
                 n *= s
             # tensors that must stay contiguous for fused GEMMs (q|k|v) are sized in multiples of 4 and
             # registered back-to-back by the caller via `pack=True` names (no padding between them)
-            off += n if name.endswith("#pack") else (n + ALIGN - 1) // ALIGN * ALIGN
+            # "#pack": the next tensor follows without padding; otherwise the next OFFSET is rounded up to ALIGN (so that a short
+            # packed tensor, e.g. a [Z] bias, cannot shift everything behind it off the 16-byte grid of the fp16 plane arenas)
+            off = off + n if name.endswith("#pack") else (off + n + ALIGN - 1) // ALIGN * ALIGN
         self.numel = off
         flat = torch.zeros(off, dtype=torch.float32)
         self.bind(flat)
