@@ -176,7 +176,9 @@ __global__ void relu_bwd_colsum_kernel(const float* dy, const float* __restrict_
 // ---------------------------------------------------------------- Philox dropout / randn / axpy
 // x *= mask / (1-p), mask = dropout_keep (common.cuh: 16 bits of Philox4x32-7(seed; offset + i/8) per element).  Calling
 // it again with the same (seed, offset) on the gradient reproduces the mask, so no mask tensor is stored.
-__global__ void dropout_kernel(float* __restrict__ x, size_t n, float p, uint64_t seed, uint64_t offset, int rn) {
+__global__ void dropout_kernel(float* __restrict__ x, size_t n, float p, uint64_t seed, uint64_t offset, int rn,
+                               const unsigned long long* __restrict__ seed_dev) {
+  if (seed_dev) seed += __ldg(seed_dev);
   const float scale = 1.f / (1.f - p);
   const uint32_t thr = dropout_threshold(p);
   size_t n8 = (n + 7) / 8;
@@ -368,8 +370,15 @@ extern "C" int b200iq_relu_bwd_colsum(const float* dy, const float* y, float* dp
 extern "C" int b200iq_dropout(float* x, size_t n, float p, uint64_t seed, uint64_t offset, void* stream) {
   B200IQ_CHECK_ARG(x && n > 0 && p >= 0.f && p < 1.f, "dropout: bad args");
   if (p == 0.f) return 0;
-  dropout_kernel<<<grid_for((n + 7) / 8, 256), 256, 0, ST>>>(x, n, p, seed, offset, round_mode());
+  dropout_kernel<<<grid_for((n + 7) / 8, 256), 256, 0, ST>>>(x, n, p, seed, offset, round_mode(), nullptr);
   return launch_status("dropout");
+}
+
+extern "C" int b200iq_dropout_dev(float* x, size_t n, float p, uint64_t seed, uint64_t offset, const unsigned long long* seed_dev, void* stream) {
+  B200IQ_CHECK_ARG(x && n > 0 && p >= 0.f && p < 1.f, "dropout_dev: bad args");
+  if (p == 0.f) return 0;
+  dropout_kernel<<<grid_for((n + 7) / 8, 256), 256, 0, ST>>>(x, n, p, seed, offset, round_mode(), seed_dev);
+  return launch_status("dropout_dev");
 }
 
 extern "C" int b200iq_randn(float* out, size_t n, uint64_t seed, uint64_t offset, void* stream) {

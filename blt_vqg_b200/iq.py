@@ -270,7 +270,8 @@ class IQ(nn.Module):
         # image head: fc + BatchNorm1d (encoder_cnn.py:33-34)
         feats_a = ops.to_act(ws, "feats.a", feats)
         img_pre = ws.buf("img_pre", B, H)
-        ops.gemm2(feats_a, c.W["encoder_cnn.cnn.fc.weight"], img_pre, bias=P["encoder_cnn.cnn.fc.bias"])
+        # (split-K: K = FEAT = 2048 is the longest forward reduction, and the tensor core's fp32 accumulation error grows with K)
+        ops.gemm2(feats_a, c.W["encoder_cnn.cnn.fc.weight"], img_pre, bias=P["encoder_cnn.cnn.fc.bias"], auto_split=True)
         img = ws.buf("img", B, H)
         ops.bn_fwd(img_pre, P["encoder_cnn.bn.weight"], P["encoder_cnn.bn.bias"], img, ws.buf("bn.mean", H),
                    ws.buf("bn.rstd", H), self.bn_running_mean, self.bn_running_var, c.training)

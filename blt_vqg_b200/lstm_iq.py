@@ -131,6 +131,9 @@ class LSTMIQ(nn.Module):
         # step_idx counts this module's stochastic passes: every context (a training step, or a stage call of the staged API)
         # draws a fresh Philox key, like the reference's nn.Dropout / torch.randn draw fresh numbers on every call
         self.seed, self.seed_rank, self.step_idx = 1234, 0, 0
+        self.seed_dev = None       # device int64 word added to every Philox seed (train.TrainStep's CUDA-graph path, see IQ.seed_dev)
+        self.kld_coef_dev = None   # unused here (the LSTM variant's KL weight is constant); TrainStep sets it on both models
+        self.feature_cache = None
         self.on_grad_ready = None
         self._ws, self._gflat, self._terms, self._wops, self._wops_exact = {}, None, None, None, None
 
@@ -195,9 +198,10 @@ class LSTMIQ(nn.Module):
                 self._wops = tf.build_weight_operands(self.arena, self.flat.device, skip=tuple(n for n in self.arena.views if n.endswith("embedding.weight") or n == "category_encoder.weight"))
             tf.refresh_weight_operands(self._wops, self.arena, self.flat.data)
             weights = self._wops
-        self.step_idx += 1
+        if self.seed_dev is None:
+            self.step_idx += 1
         c = tf.Ctx(self.arena, self.grad_arena, ws, self.H, 1, self.A, self.H, 0.0, 0.0, training,
-                   self.seed + self.step_idx + 1000003 * self.seed_rank, weights)
+                   self.seed + (0 if self.seed_dev is not None else self.step_idx) + 1000003 * self.seed_rank, weights)
         c.on_ready = self.on_grad_ready
         c.in_drop = self.input_dropout_p if training else 0.0
         return c
@@ -224,7 +228,8 @@ class LSTMIQ(nn.Module):
         """models/encoder_cnn.py:33-34"""
         ws, P, B, H = c.ws, c.P, feats.shape[0], self.H
         img_pre = ws.buf("img_pre", B, H)
-        tf.mm(c, feats, "encoder_cnn.cnn.fc.weight", img_pre, bias=P["encoder_cnn.cnn.fc.bias"])
+        # split-K: K = FEAT = 2048 is the longest forward reduction and the tensor core's fp32 accumulation error grows with it
+        tf.mm(c, feats, "encoder_cnn.cnn.fc.weight", img_pre, bias=P["encoder_cnn.cnn.fc.bias"], auto_split=True)
         img = ws.buf("img", B, H)
         ops.bn_fwd(img_pre, P["encoder_cnn.bn.weight"], P["encoder_cnn.bn.bias"], img, ws.buf("bn.mean", H), ws.buf("bn.rstd", H),
                    self.bn_running_mean, self.bn_running_var, c.training)
@@ -326,8 +331,12 @@ class LSTMIQ(nn.Module):
         """forward + losses (old_train_iq.py:100-155 contract) + complete backward; returns the device vector
         (gen, kl, rec_i, rec_a, n_tokens, ...); gradients are ACCUMULATED into `grad_arena`.  `kliter` is unused (signature
         shared with IQ.forward_losses so train.TrainStep drives both)."""
-        with ops.no_rounding():
-            return self._forward_losses(images, answers, alengths, questions, eps, backward, eps2)
+        prev, ops.SEED_DEV = ops.SEED_DEV, self.seed_dev
+        try:
+            with ops.no_rounding():
+                return self._forward_losses(images, answers, alengths, questions, eps, backward, eps2)
+        finally:
+            ops.SEED_DEV = prev
 
     def scale(self, tokens=None):
         """loss scale of the fp16-plane path (see IQ.scale): every gradient seed is multiplied by it, train.TrainStep divides it out"""

@@ -398,7 +398,10 @@ def relu_bwd_colsum(dy, y, dpre, dbias, scale=1.0):
 
 def dropout_(x, p, seed, offset):
     if p > 0:
-        _call("b200iq_dropout", _p(x), C.c_size_t(x.numel()), _f(p), C.c_uint64(seed), C.c_uint64(offset))
+        if SEED_DEV is not None:
+            _call("b200iq_dropout_dev", _p(x), C.c_size_t(x.numel()), _f(p), C.c_uint64(seed), C.c_uint64(offset), _p(SEED_DEV))
+        else:
+            _call("b200iq_dropout", _p(x), C.c_size_t(x.numel()), _f(p), C.c_uint64(seed), C.c_uint64(offset))
 
 
 def randn_(out, seed, offset=0):

@@ -57,7 +57,7 @@ class TrainStep:
         self.t = 0         # Adam step count (never reset: train_iq.py:111 is a no-op)
         self.lr_fn = lr_fn or (lambda s: noam_lr(s, model.H))
         self.dp = dp       # parallel.GradReducer or None
-        # graphs need the device-resident scalars of the transformer IQ (IQ.seed_dev / kld_coef_dev); the LSTM variant stays eager
+        # graphs need the models' device-resident per-step scalars (seed_dev / kld_coef_dev)
         self.graph = (GRAPH if graph is None else graph) and hasattr(model, "seed_dev") and flat.is_cuda
         self._captured = {}
         self._seed_ctr = None
@@ -145,7 +145,8 @@ class TrainStep:
         m = self.model
         xs = (images, answers, response if m.latent_transformer else None, target, eps)
         key = tuple((tuple(x.shape), x.is_floating_point()) if x is not None else None for x in xs) + (
-            bool(m.latent_transformer), bool(m.training), id(m.feature_cache), m.attn_dropout, m.relu_dropout)
+            bool(m.latent_transformer), bool(m.training), id(getattr(m, "feature_cache", None)), getattr(m, "attn_dropout", 0.0),
+            getattr(m, "relu_dropout", 0.0), getattr(m, "input_dropout_p", 0.0))
         st = self._captured.get(key)
         if st is None:
             st = self._captured[key] = _Captured()
@@ -163,7 +164,7 @@ class TrainStep:
                     if x is not None and s.data_ptr() != x.data_ptr():
                         s.copy_(x, non_blocking=True)
                 # the two per-step scalars that come from the host: Adam's hyper-parameters and the annealed KL coefficient
-                c_kld = m.loss_coefs(self.kliter)[2]
+                c_kld = m.loss_coefs(self.kliter)[2] if hasattr(m, "loss_coefs") else 0.0
                 if st.warm > 0:
                     self.set_hyper()
                     ops.set_hyper(self.coefs, c_kld * m._grad_scale, 0.0, 0.0, 0.0)

@@ -165,6 +165,8 @@ int b200iq_relu_bwd_colsum(const float* dy, const float* y, float* dpre, float* 
 /* inverted dropout in place; element i is kept when 16 bits of Philox4x32-7(seed; counter = offset + i/8) — word i & 3,
  * upper half when (i >> 2) & 1 — are >= round(65536 p).  Re-applying it to the gradient with the same key is the backward.   replaces: nn.Dropout at transformer_layers.py:406,520; base_rnn.py:41 */
 int b200iq_dropout(float* x, size_t n, float p, uint64_t seed, uint64_t offset, void* stream);
+/* same with the device word *seed_dev (may be NULL) added to the seed at run time (steps replayed from a CUDA graph) */
+int b200iq_dropout_dev(float* x, size_t n, float p, uint64_t seed, uint64_t offset, const unsigned long long* seed_dev, void* stream);
 /* out ~ N(0,1), Philox4x32-10(seed; counter = offset + i/4) + Box-Muller (moments checked in tests/test_ops_gpu.py)
  * replaces: torch.randn on the CPU + H2D copy, models/transformer_layers.py:45 */
 int b200iq_randn(float* out, size_t n, uint64_t seed, uint64_t offset, void* stream);
