@@ -239,7 +239,7 @@ __device__ __forceinline__ void mma_tf32(float (&c)[4], float a0, float a1, floa
                  "r"(__float_as_uint(b0)), "r"(__float_as_uint(b1)));
 }
 __device__ __forceinline__ float4 ld4(const float* base, int row, int nrows, int ld, int col) {
-  if (row < nrows) return __ldg(reinterpret_cast<const float4*>(base + (size_t)row * ld + col));
+  if (row < nrows) return *reinterpret_cast<const float4*>(base + (size_t)row * ld + col);   // global or shared (generic load)
   return make_float4(0.f, 0.f, 0.f, 0.f);
 }
 
@@ -391,7 +391,24 @@ __device__ __forceinline__ void softmax_frag(const AttnArgs& a, float (&S)[MT][N
   }
 }
 
-static constexpr int ATT_TC_WARPS = 4;
+static constexpr int ATT_TC_WARPS = 2;
+// The register-resident kernels first pull the (sample, head) tiles they multiply — Q, K, V (and dO) — into shared memory with
+// cp.async (16-byte chunks, every chunk of a warp's tiles in flight at once) and read the MMA fragments from there: with the
+// fragments loaded straight from global memory every k-step waited for its own L2 round trip (ncu: long-scoreboard stalls, 8 warps
+// per SM, 49 % / 36 % of the HBM roof on the cfg3 shapes).  Row pitch 76 floats: the P.V-style fragment reads (rows 2t, columns 4g)
+// are bank-conflict-free, the Q.K^T-style reads (rows g, columns 4t) 2-way on 4 of 16 banks.
+static constexpr int ATT_SP = 76;
+__device__ __forceinline__ void att_stage(float* dst, const float* __restrict__ src, int rows, int ld, int lane) {
+  for (int idx = lane; idx < rows * 16; idx += 32) {
+    const int r = idx >> 4, c4 = idx & 15;
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;"
+                 ::"r"((uint32_t)__cvta_generic_to_shared(dst + r * ATT_SP + 4 * c4)), "l"(src + (size_t)r * ld + 4 * c4) : "memory");
+  }
+}
+__device__ __forceinline__ void att_stage_wait() {
+  asm volatile("cp.async.wait_all;" ::: "memory");
+  __syncwarp();
+}
 
 template <int MT, int NT>
 __global__ void __launch_bounds__(ATT_TC_WARPS * 32)
@@ -402,9 +419,13 @@ attention_fwd_tc_kernel(AttnArgs a, AttOut out) {
   const int bh = blockIdx.x * ATT_TC_WARPS + (threadIdx.x >> 5);
   if (bh >= a.B * a.nh) return;
   const int b = bh / a.nh, h = bh - b * a.nh, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
-  const float* Q = a.q + (size_t)b * a.nq * a.ldq + h * 64;
-  const float* K = a.k + (size_t)b * a.bsk + h * 64;
-  const float* V = a.v + (size_t)b * a.bsv + h * 64;
+  extern __shared__ __align__(16) float att_dyn[];
+  float* Q = att_dyn + (size_t)(threadIdx.x >> 5) * (a.nq + 2 * a.nk) * ATT_SP;
+  float* K = Q + a.nq * ATT_SP;
+  float* V = K + a.nk * ATT_SP;
+  att_stage(Q, a.q + (size_t)b * a.nq * a.ldq + h * 64, a.nq, a.ldq, lane);
+  att_stage(K, a.k + (size_t)b * a.bsk + h * 64, a.nk, a.ldk, lane);
+  att_stage(V, a.v + (size_t)b * a.bsv + h * 64, a.nk, a.ldv, lane);
   float S[MT][NT][4];
 #pragma unroll
   for (int mt = 0; mt < MT; ++mt)
@@ -412,7 +433,8 @@ attention_fwd_tc_kernel(AttnArgs a, AttOut out) {
     for (int nt = 0; nt < NT; ++nt)
 #pragma unroll
       for (int e = 0; e < 4; ++e) S[mt][nt][e] = 0.f;
-  mma_xyT<MT, NT, 3>(S, Q, a.nq, a.ldq, K, a.nk, a.ldk, g, t);
+  att_stage_wait();
+  mma_xyT<MT, NT, 3>(S, Q, a.nq, ATT_SP, K, a.nk, ATT_SP, g, t);
   uint32_t msk[MT];
   softmax_frag<MT, NT>(a, S, msk, b, g, t);
   float SL[MT][NT][4];   // low-order TF32 term of the attention weights (3-term P.V)
@@ -435,7 +457,7 @@ attention_fwd_tc_kernel(AttnArgs a, AttOut out) {
           SL[mt][nt][2 * hh + e] = w - wh;
         }
       }
-  mma_pY_store<MT, NT, 3>(S, V, a.nk, a.ldv, att_out_at(out, (size_t)b * a.nq * ldo + h * 64), a.nq, g, t, a.rn, SL);
+  mma_pY_store<MT, NT, 3>(S, V, a.nk, ATT_SP, att_out_at(out, (size_t)b * a.nq * ldo + h * 64), a.nq, g, t, a.rn, SL);
 }
 
 // out[j, :64] = sum_i T[i][j] * X[i, :64] for j < nj, with T ([32][33] floats, rows i, written by this warp in C layout)
@@ -494,10 +516,15 @@ attention_bwd_tc_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, Att
   const int bh = blockIdx.x * ATT_TC_WARPS + wid;
   if (bh >= a.B * a.nh) return;
   const int b = bh / a.nh, h = bh - b * a.nh, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
-  const float* Q = a.q + (size_t)b * a.nq * a.ldq + h * 64;
-  const float* K = a.k + (size_t)b * a.bsk + h * 64;
-  const float* V = a.v + (size_t)b * a.bsv + h * 64;
-  const float* dO = dout + (size_t)b * a.nq * ldo + h * 64;
+  extern __shared__ __align__(16) float att_dyn[];
+  float* Q = att_dyn + (size_t)wid * (2 * a.nq + 2 * a.nk) * ATT_SP;
+  float* K = Q + a.nq * ATT_SP;
+  float* V = K + a.nk * ATT_SP;
+  float* dO = V + a.nk * ATT_SP;
+  att_stage(Q, a.q + (size_t)b * a.nq * a.ldq + h * 64, a.nq, a.ldq, lane);
+  att_stage(K, a.k + (size_t)b * a.bsk + h * 64, a.nk, a.ldk, lane);
+  att_stage(V, a.v + (size_t)b * a.bsv + h * 64, a.nk, a.ldv, lane);
+  att_stage(dO, dout + (size_t)b * a.nq * ldo + h * 64, a.nq, ldo, lane);
   float S[MT][NT][4], dW[MT][NT][4];
 #pragma unroll
   for (int mt = 0; mt < MT; ++mt)
@@ -505,8 +532,9 @@ attention_bwd_tc_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, Att
     for (int nt = 0; nt < NT; ++nt)
 #pragma unroll
       for (int e = 0; e < 4; ++e) { S[mt][nt][e] = 0.f; dW[mt][nt][e] = 0.f; }
-  mma_xyT<MT, NT, 3>(S, Q, a.nq, a.ldq, K, a.nk, a.ldk, g, t);   // scores: the forward's 3-term product, so P is the forward's P
-  mma_xyT<MT, NT, 1>(dW, dO, a.nq, ldo, V, a.nk, a.ldv, g, t);   // d(post-dropout weights) = dO . V^T
+  att_stage_wait();
+  mma_xyT<MT, NT, 3>(S, Q, a.nq, ATT_SP, K, a.nk, ATT_SP, g, t);   // scores: the forward's 3-term product, so P is the forward's P
+  mma_xyT<MT, NT, 1>(dW, dO, a.nq, ATT_SP, V, a.nk, ATT_SP, g, t);   // d(post-dropout weights) = dO . V^T
   uint32_t msk[MT];
   softmax_frag<MT, NT>(a, S, msk, b, g, t);
   float* Ws = tsm[wid][0];
@@ -553,9 +581,9 @@ attention_bwd_tc_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, Att
   // dQ = dS . K with dS as TWO TF32 terms: every row of dS sums to zero, so when the keys share a large common component (LayerNorm
   // + a bias-free projection at initialisation) the product cancels it and the 2^-11 rounding of a single-term dS is what is left
   // (measured 7e-3 of |dQ|, scripts/gpu_attention_err.py; 3e-4 with the second term)
-  mma_pY_store<MT, NT, 1>(S, K, a.nk, a.ldk, att_out_at(dq, (size_t)b * a.nq * lddq + h * 64), a.nq, g, t, a.rn, a.dq2 ? dW : nullptr);
-  mma_TtX_store<MT, NT>(Ds, Q, a.nq, a.ldq, att_out_at(dk, (size_t)b * a.nk * lddk + h * 64), a.nk, g, t, a.rn);  // dK = dS^T . Q
-  mma_TtX_store<MT, NT>(Ws, dO, a.nq, ldo, att_out_at(dv, (size_t)b * a.nk * lddv + h * 64), a.nk, g, t, a.rn);   // dV = W^T . dO
+  mma_pY_store<MT, NT, 1>(S, K, a.nk, ATT_SP, att_out_at(dq, (size_t)b * a.nq * lddq + h * 64), a.nq, g, t, a.rn, a.dq2 ? dW : nullptr);
+  mma_TtX_store<MT, NT>(Ds, Q, a.nq, ATT_SP, att_out_at(dk, (size_t)b * a.nk * lddk + h * 64), a.nk, g, t, a.rn);  // dK = dS^T . Q
+  mma_TtX_store<MT, NT>(Ws, dO, a.nq, ATT_SP, att_out_at(dv, (size_t)b * a.nk * lddv + h * 64), a.nk, g, t, a.rn);   // dV = W^T . dO
 }
 
 // ---------------------------------------------------------------- row-block kernels: 32 < n <= 80 (cfg5: T = 64, R = 65)
@@ -805,7 +833,12 @@ static int attention_fwd_impl(const B200iqAttention* p, const AttOut& out, void*
     const int lds[] = {p->ldq, p->ldk, p->ldv};
     if (tc_ok(p, ptrs, 3, lds, 3, &out, 1)) {
       const int mt = a.nq > 16 ? 2 : 1, nt = (a.nk + 7) / 8, grid = (a.B * a.nh + ATT_TC_WARPS - 1) / ATT_TC_WARPS;
-#define CALL(M_, N_) launch_dep(attention_fwd_tc_kernel<M_, N_>, dim3(grid), dim3(ATT_TC_WARPS * 32), 0, (cudaStream_t)stream, a, out)
+      const size_t tsm = sizeof(float) * ATT_TC_WARPS * (size_t)(a.nq + 2 * a.nk) * ATT_SP;
+#define CALL(M_, N_) \
+  do { \
+    if (tsm > 48 * 1024) cudaFuncSetAttribute(attention_fwd_tc_kernel<M_, N_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm); \
+    launch_dep(attention_fwd_tc_kernel<M_, N_>, dim3(grid), dim3(ATT_TC_WARPS * 32), tsm, (cudaStream_t)stream, a, out); \
+  } while (0)
       B200IQ_ATT_DISPATCH(mt, nt, CALL);
 #undef CALL
       return launch_status("attention_fwd_tc");
@@ -833,7 +866,14 @@ static int attention_bwd_impl(const B200iqAttention* p, const float* dout, const
     const AttOut outs[] = {dq, dk, dv};
     if (tc_ok(p, ptrs, 4, lds, 4, outs, 3)) {
       const int mt = a.nq > 16 ? 2 : 1, nt = (a.nk + 7) / 8, grid = (a.B * a.nh + ATT_TC_WARPS - 1) / ATT_TC_WARPS;
-#define CALL(M_, N_) launch_dep(attention_bwd_tc_kernel<M_, N_>, dim3(grid), dim3(ATT_TC_WARPS * 32), 0, (cudaStream_t)stream, a, dout, p->ldo, dq, dk, dv)
+      const size_t tsm = sizeof(float) * ATT_TC_WARPS * (size_t)(2 * a.nq + 2 * a.nk) * ATT_SP;
+#define CALL(M_, N_) \
+  do { \
+    /* static (the two transposed tiles per warp) + dynamic may pass the 48 KB a kernel gets without opting in */ \
+    if (tsm + sizeof(float) * ATT_TC_WARPS * 2 * 32 * 33 > 48 * 1024) \
+      cudaFuncSetAttribute(attention_bwd_tc_kernel<M_, N_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm); \
+    launch_dep(attention_bwd_tc_kernel<M_, N_>, dim3(grid), dim3(ATT_TC_WARPS * 32), tsm, (cudaStream_t)stream, a, dout, p->ldo, dq, dk, dv); \
+  } while (0)
       B200IQ_ATT_DISPATCH(mt, nt, CALL);
 #undef CALL
       return launch_status("attention_bwd_tc");

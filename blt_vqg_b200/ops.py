@@ -99,7 +99,7 @@ def split_f16(src, hi, lo=None, scale=1.0):
         rows, cols = src.shape
         lds, ldd = _ld(src), _ld(hi)
         assert lo is None or _ld(lo) == ldd
-    _call("b200iq_split_f16", _p(src), _p(hi), _p(lo), rows, C.c_longlong(cols), C.c_longlong(lds), C.c_longlong(ldd), _f(scale))
+    _call("b200iq_split_f16", _p(src), _p(hi), _p(lo), rows, C.c_longlong(cols), C.c_longlong(lds), C.c_longlong(ldd), _f(scale), nbytes=_nb(src) + (2 if lo is not None else 1) * 2 * src.numel())
 
 
 class GemmF16Params(C.Structure):
@@ -258,9 +258,26 @@ def _f(x):
     return C.c_float(float(x))
 
 
-def _call(name, *args):
+# when a list: every non-GEMM launch that states its algorithmic bytes is bracketed with CUDA events on the launching stream and
+# appended as (start_event, end_event, kernel name, bytes) — bench.py's per-kernel roofline pass (HBM-bound kernels)
+KERNEL_TRACE = None
+
+
+def _nb(*ts):
+    """bytes of the given tensors (None skipped): the algorithmic traffic of a streaming kernel = what it must read + write"""
+    return sum(t.numel() * t.element_size() for t in ts if t is not None)
+
+
+def _call(name, *args, nbytes=None):
     global LAUNCHES
     LAUNCHES += 1
+    if KERNEL_TRACE is not None and nbytes is not None:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        L.check(getattr(L.lib(), name)(*args, L.stream_ptr()), name)
+        e1.record()
+        KERNEL_TRACE.append((e0, e1, name, float(nbytes)))
+        return
     L.check(getattr(L.lib(), name)(*args, L.stream_ptr()), name)
 
 
@@ -302,7 +319,7 @@ def tok0_scatter_add(src, dst, B, n, H):
 
 def layernorm_fwd(x, g, b, y, mean, rstd, eps=1e-5):
     M, H = x.shape
-    _call("b200iq_layernorm_fwd", _p(x), _p(g), _p(b), _p(y), _p(mean), _p(rstd), M, H, _f(eps))
+    _call("b200iq_layernorm_fwd", _p(x), _p(g), _p(b), _p(y), _p(mean), _p(rstd), M, H, _f(eps), nbytes=_nb(x, y))
     return y
 
 
@@ -313,7 +330,7 @@ def add_layernorm_supported(x):
 def add_layernorm_fwd(x, add, out, g, b, y, mean, rstd, eps=1e-5):
     """out = x + add (rounded like axpby), y = LayerNorm(out) in one pass"""
     M, H = x.shape
-    _call("b200iq_add_layernorm_fwd", _p(x), _p(add), _p(out), _p(g), _p(b), _p(y), _p(mean), _p(rstd), M, H, _f(eps))
+    _call("b200iq_add_layernorm_fwd", _p(x), _p(add), _p(out), _p(g), _p(b), _p(y), _p(mean), _p(rstd), M, H, _f(eps), nbytes=_nb(x, add, out, y))
     return y
 
 
@@ -340,7 +357,7 @@ def layernorm_fwd_act(x, g, b, mean, rstd, y=None, act=None, add=None, sum_out=N
             return layernorm_fwd(sum_out, g, b, y, mean, rstd, eps)
         return layernorm_fwd(x, g, b, y, mean, rstd, eps)
     _call("b200iq_layernorm_fwd_f16", _p(x), _p(add), _p(sum_out), _p(g), _p(b), _p(y), _p(act.hi), _p(act.lo), _ld(act.hi),
-          _p(mean), _p(rstd), M, H, _f(eps))
+          _p(mean), _p(rstd), M, H, _f(eps), nbytes=_nb(x, add, sum_out if add is not None else None, y, act.hi, act.lo))
     return y
 
 
@@ -350,7 +367,7 @@ def layernorm_bwd_act(dy, x, g, mean, rstd, dx, dg, db, accumulate_dx, dx_hi=Non
         return layernorm_bwd(dy, x, g, mean, rstd, dx, dg, db, accumulate_dx)
     M, H = x.shape
     assert dx_hi.stride(0) == H
-    _call("b200iq_layernorm_bwd_f16", _p(dy), _p(x), _p(g), _p(mean), _p(rstd), _p(dx), _p(dx_hi), _p(dg), _p(db), M, H, int(accumulate_dx))
+    _call("b200iq_layernorm_bwd_f16", _p(dy), _p(x), _p(g), _p(mean), _p(rstd), _p(dx), _p(dx_hi), _p(dg), _p(db), M, H, int(accumulate_dx), nbytes=_nb(dy, x, dx, dx if accumulate_dx else None, dx_hi))
 
 
 def relu_bwd_colsum_act(dy, y, dpre, dbias, scale=1.0):
@@ -359,7 +376,7 @@ def relu_bwd_colsum_act(dy, y, dpre, dbias, scale=1.0):
         return relu_bwd_colsum(dy, y, dpre.f32, dbias, scale)
     M, N = y.shape
     assert _ld(dpre.hi) == N
-    _call("b200iq_relu_bwd_colsum_f16", _p(dy), _p(y), _p(dpre.hi), _p(dbias), M, N, _f(scale))
+    _call("b200iq_relu_bwd_colsum_f16", _p(dy), _p(y), _p(dpre.hi), _p(dbias), M, N, _f(scale), nbytes=_nb(dy, y, dpre.hi))
 
 
 def colsum_add_act(x, out):
@@ -367,7 +384,7 @@ def colsum_add_act(x, out):
     if x.f32 is not None:
         return colsum_add(x.f32, out)
     M, N = x.hi.shape
-    _call("b200iq_colsum_add_f16", _p(x.hi), _p(out), M, N, _ld(x.hi))
+    _call("b200iq_colsum_add_f16", _p(x.hi), _p(out), M, N, _ld(x.hi), nbytes=_nb(x.hi))
 
 
 def ce_rows_act(logits, targets, pad_id, count, coef, loss_sum, grad):
@@ -377,23 +394,23 @@ def ce_rows_act(logits, targets, pad_id, count, coef, loss_sum, grad):
         return ce_rows(logits, targets, pad_id, count, coef, loss_sum, write_grad=grad is not None)
     rows, V = logits.shape
     _call("b200iq_ce_rows_f16", _p(logits), logits.stride(0), _p(targets), rows, V, int(pad_id), _p(count), _f(coef), _p(loss_sum),
-          _p(grad.hi), _ld(grad.hi))
+          _p(grad.hi), _ld(grad.hi), nbytes=_nb(logits, grad.hi))
 
 
 def layernorm_bwd(dy, x, g, mean, rstd, dx, dg, db, accumulate_dx):
     M, H = x.shape
-    _call("b200iq_layernorm_bwd", _p(dy), _p(x), _p(g), _p(mean), _p(rstd), _p(dx), _p(dg), _p(db), M, H, int(accumulate_dx))
+    _call("b200iq_layernorm_bwd", _p(dy), _p(x), _p(g), _p(mean), _p(rstd), _p(dx), _p(dg), _p(db), M, H, int(accumulate_dx), nbytes=_nb(dy, x, dx, dx if accumulate_dx else None))
 
 
 def colsum_add(x, out):
     M, N = x.shape
-    _call("b200iq_colsum_add", _p(x), _p(out), M, N, x.stride(0))
+    _call("b200iq_colsum_add", _p(x), _p(out), M, N, x.stride(0), nbytes=_nb(x))
 
 
 def relu_bwd_colsum(dy, y, dpre, dbias, scale=1.0):
     """dpre = scale * dy * (y > 0); dbias += colsum(dpre)"""
     M, N = y.shape
-    _call("b200iq_relu_bwd_colsum", _p(dy), _p(y), _p(dpre), _p(dbias), M, N, _f(scale))
+    _call("b200iq_relu_bwd_colsum", _p(dy), _p(y), _p(dpre), _p(dbias), M, N, _f(scale), nbytes=_nb(dy, y, dpre))
 
 
 def dropout_(x, p, seed, offset):
@@ -442,11 +459,12 @@ def attention_fwd(q, k, v, out, key_ids, pad_id, causal, B, nh, nq, nk, d, drop_
             return attention_fwd(q, k, v, out.f32, key_ids, pad_id, causal, B, nh, nq, nk, d, drop_p, seed, offset, kv_batch_stride)
         p = _attn_params(q, k, v, None, key_ids, pad_id, causal, B, nh, nq, nk, d, drop_p, seed, offset, kv_batch_stride)
         p.precise, p.out_hi, p.out_lo, p.ldo = 1, out.hi.data_ptr(), _dp(out.lo), _ld(out.hi)
-        _call("b200iq_attention_fwd", C.byref(p))
+        # algorithmic bytes: q, k, v rows of every head once (fp32) + the output planes
+        _call("b200iq_attention_fwd", C.byref(p), nbytes=4 * B * nh * d * (nq + 2 * nk) + 2 * B * nq * nh * d * (2 if out.lo is not None else 1))
         return out
     p = _attn_params(q, k, v, out, key_ids, pad_id, causal, B, nh, nq, nk, d, drop_p, seed, offset, kv_batch_stride)
     p.precise = 0 if _FORCE_SIMT else PRECISE_ATTENTION
-    _call("b200iq_attention_fwd", C.byref(p))
+    _call("b200iq_attention_fwd", C.byref(p), nbytes=4 * B * nh * d * (2 * nq + 2 * nk))
     return out
 
 
@@ -456,10 +474,12 @@ def attention_bwd(q, k, v, dout, dq, dk, dv, key_ids, pad_id, causal, B, nh, nq,
     p.ldo = dout.stride(0)
     if dq.dtype == torch.float16:
         p.precise = 1
-        _call("b200iq_attention_bwd_f16", C.byref(p), _p(dout), _p(dq), _p(dk), _p(dv), dq.stride(0), dk.stride(0), dv.stride(0))
+        _call("b200iq_attention_bwd_f16", C.byref(p), _p(dout), _p(dq), _p(dk), _p(dv), dq.stride(0), dk.stride(0), dv.stride(0),
+              nbytes=4 * B * nh * d * (2 * nq + 2 * nk) + 2 * B * nh * d * (nq + 2 * nk))
         return
     p.precise = 0 if _FORCE_SIMT else PRECISE_ATTENTION
-    _call("b200iq_attention_bwd", C.byref(p), _p(dout), _p(dq), _p(dk), _p(dv), dq.stride(0), dk.stride(0), dv.stride(0))
+    _call("b200iq_attention_bwd", C.byref(p), _p(dout), _p(dq), _p(dk), _p(dv), dq.stride(0), dk.stride(0), dv.stride(0),
+          nbytes=4 * B * nh * d * (3 * nq + 4 * nk))
 
 
 # ------------------------------------------------------------------ losses / heads / optimizer
@@ -469,12 +489,12 @@ def count_nonpad(targets, pad_id, count):
 
 def ce_rows(logits, targets, pad_id, count, coef, loss_sum, write_grad=True):
     rows, V = logits.shape
-    _call("b200iq_ce_rows", _p(logits), logits.stride(0), _p(targets), rows, V, int(pad_id), _p(count), _f(coef), _p(loss_sum), int(write_grad))
+    _call("b200iq_ce_rows", _p(logits), logits.stride(0), _p(targets), rows, V, int(pad_id), _p(count), _f(coef), _p(loss_sum), int(write_grad), nbytes=_nb(logits) * (2 if write_grad else 1))
 
 
 def ce_aux(z_logit, dz_logit, targets, pad_id, count, coef, loss_sum):
     B, V = z_logit.shape
-    _call("b200iq_ce_aux", _p(z_logit), _p(dz_logit), _p(targets), B, targets.numel() // B, V, int(pad_id), _p(count), _f(coef), _p(loss_sum))
+    _call("b200iq_ce_aux", _p(z_logit), _p(dz_logit), _p(targets), B, targets.numel() // B, V, int(pad_id), _p(count), _f(coef), _p(loss_sum), nbytes=_nb(z_logit, dz_logit))
 
 
 def latent_fwd(prior, post, eps, z, kld_sum):
@@ -518,12 +538,12 @@ def grad_sumsq(grad, out):
     scratch = _SUMSQ_SCRATCH.get(key)
     if scratch is None:
         scratch = _SUMSQ_SCRATCH[key] = torch.zeros(2048, device=grad.device)
-    _call("b200iq_grad_sumsq", _p(grad), C.c_size_t(grad.numel()), _p(out), _p(scratch), scratch.numel())
+    _call("b200iq_grad_sumsq", _p(grad), C.c_size_t(grad.numel()), _p(out), _p(scratch), scratch.numel(), nbytes=_nb(grad))
 
 
 def adam_step(param, grad, m, v, hyper, normsq, beta1=0.9, beta2=0.999, eps=1e-8, max_norm=5.0, zero_grad=True):
     _call("b200iq_adam_step", _p(param), _p(grad), _p(m), _p(v), C.c_size_t(param.numel()), _p(hyper), _p(normsq),
-          _f(beta1), _f(beta2), _f(eps), _f(max_norm), int(zero_grad))
+          _f(beta1), _f(beta2), _f(eps), _f(max_norm), int(zero_grad), nbytes=_nb(param, grad, m, v) + _nb(param, m, v) + (_nb(grad) if zero_grad else 0))
 
 
 # ------------------------------------------------------------------ LSTM recurrence
@@ -534,7 +554,7 @@ def lstm_seq_supported(H):
 def lstm_seq_fwd(gates, whh, hbuf, cbuf, lengths):
     """all T steps in one launch; gates [T,B,4H] in: x-projection + biases, out: activated gates"""
     T, B, H4 = gates.shape
-    _call("b200iq_lstm_seq_fwd", _p(gates), _p(whh), _p(hbuf), _p(cbuf), _p(lengths), T, B, H4 // 4)
+    _call("b200iq_lstm_seq_fwd", _p(gates), _p(whh), _p(hbuf), _p(cbuf), _p(lengths), T, B, H4 // 4, nbytes=2 * _nb(gates) + _nb(hbuf, cbuf))
 
 
 _LSTM_WS = {}
@@ -550,7 +570,7 @@ def lstm_seq_bwd(gates, cbuf, whh, dh_last, d_out, dgates, dh0, dc0, lengths):
         L.lib().b200iq_lstm_seq_bwd_workspace_bytes.restype = C.c_size_t
         ws = _LSTM_WS[key] = torch.empty(L.lib().b200iq_lstm_seq_bwd_workspace_bytes(B, H) // 4, device=gates.device)
     _call("b200iq_lstm_seq_bwd", _p(gates), _p(cbuf), _p(whh), _p(dh_last), _p(d_out), _p(dgates), _p(dh0), _p(dc0), _p(ws),
-          _p(lengths), T, B, H)
+          _p(lengths), T, B, H, nbytes=_nb(gates, cbuf, d_out, dgates))
 
 
 def lstm_cell_fwd(gates, c_prev, h_prev, c_next, h_next, lengths, t):
