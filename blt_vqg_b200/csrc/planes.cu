@@ -4,6 +4,7 @@
 // itself, so an operand is never re-read just to be converted.
 #include "common.cuh"
 #include "rowops.cuh"
+#include <stdlib.h>
 
 namespace b200iq {
 
@@ -330,7 +331,8 @@ extern "C" int b200iq_layernorm_bwd_f16(const float* dy, const float* x, const f
   __half* hi = (__half*)dx_hi;
   if ((H == 128 || H == 256 || H == 512 || H == 1024) && (((uintptr_t)x | (uintptr_t)dy | (uintptr_t)dx | (uintptr_t)gamma) & 15) == 0 &&
       (((uintptr_t)dx_hi) & 7) == 0) {
-    const int grid = min(ceil_div(M, 8), sm_count() * 2);
+    static const int per_sm = [] { const char* v = getenv("B200IQ_LNB_CTAS"); return v ? atoi(v) : 2; }();
+    const int grid = min(ceil_div(M, 8), sm_count() * per_sm);
     if (H == 128) launch_dep(ln_bwd_warp_kernel<1>, dim3(grid), dim3(256), 0, ST, dy, x, gamma, mean, rstd, dx, dgamma, dbeta, M, accumulate_dx, 0, hi);
     else if (H == 256) launch_dep(ln_bwd_warp_kernel<2>, dim3(grid), dim3(256), 0, ST, dy, x, gamma, mean, rstd, dx, dgamma, dbeta, M, accumulate_dx, 0, hi);
     else if (H == 512) launch_dep(ln_bwd_warp_kernel<4>, dim3(grid), dim3(256), 0, ST, dy, x, gamma, mean, rstd, dx, dgamma, dbeta, M, accumulate_dx, 0, hi);

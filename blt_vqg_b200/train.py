@@ -24,6 +24,10 @@ HIGH_PRIORITY_STEP = os.environ.get("B200IQ_HP_STREAM", "1") == "1"
 # kernel's tail).  Off by default: with the side streams filling the tails it is a net loss (see iq.py PDL_FORWARD).
 PDL = os.environ.get("B200IQ_PDL", "3") == "1"
 GRAPH = os.environ.get("B200IQ_GRAPH", "1") == "1"
+# B200IQ_GRAPH_PDL=1: programmatic dependent launch for every kernel of the captured step (programmatic edges in the graph: a kernel's
+# prologue — barrier init, TMEM allocation, tensor-map fetch — runs under the tail of its predecessor); =2: only where the eager
+# schedule uses it (the decoder's forward)
+GRAPH_PDL = int(os.environ.get("B200IQ_GRAPH_PDL", "0"))
 GRAPH_WARMUP = 2   # eager steps per input shape before the capture (workspaces, kernel attributes, NCCL channels are set up by then)
 
 
@@ -190,8 +194,8 @@ class TrainStep:
         return terms
 
     def _device_step(self, st, hyper_set):
-        prev = ops.set_pdl(False)
-        allowed, ops.PDL_ALLOWED = ops.PDL_ALLOWED, False   # no programmatic edges inside the captured step
+        allowed, ops.PDL_ALLOWED = ops.PDL_ALLOWED, GRAPH_PDL > 0   # default: no programmatic edges inside the captured step
+        prev = ops.set_pdl(GRAPH_PDL == 1)
         try:
             terms = self._step_body(st.inputs[0], st.inputs[1], st.inputs[2], st.inputs[3], st.inputs[4], hyper_set=hyper_set)
             self._seed_ctr.add_(1)
