@@ -84,8 +84,10 @@ class IQ(nn.Module):
         self.FEAT = getattr(args, "feat_dim", 512)  # resnet18 fc.in_features (encoder_cnn.py:20)
         self.sos_id = vocab.word2idx[vocab.SYM_SOQ]
         assert vocab.word2idx[vocab.SYM_PAD] == PAD
-        assert self.H % self.nh == 0 and self.H % 8 == 0 and self.E % 4 == 0 and self.V % 8 == 0 and self.L % 4 == 0 and self.F % 8 == 0, \
-            "tcgen05/TMA path needs 16-byte aligned rows (H, F, V multiples of 8; E, L multiples of 4)"
+        # widths the kernels' 16-byte row accesses fix: the model dimensions.  The VOCABULARY size (len(vocab.word2idx): whatever the
+        # frequency threshold left), the embedding width and the feature width are arbitrary: their buffers get padded row pitches
+        assert self.H % self.nh == 0 and self.H % 8 == 0 and self.L % 4 == 0 and self.F % 8 == 0, \
+            "hidden_dim and pwffn_dim must be multiples of 8, latent_dim a multiple of 4 (16-byte rows for TMA)"
         self.attn_dropout, self.relu_dropout = 0.1, 0.1  # transformer_layers.py:96-97,163-164 defaults (N4)
         self.arena = Arena()
         transformer_iq_specs(self.arena, self.V, self.E, self.H, self.L, self.F, self.NL, self.FEAT)
@@ -467,9 +469,10 @@ class IQ(nn.Module):
         tflat = tids.view(-1)
         d_dec = ws.buf("d_dec_out", M, H)
         chunk = self._ce_chunk_rows(M)
-        logits = ws.buf("logits_chunk", chunk, V)
+        Vp = ops.pad8(V)   # row pitch of the chunk buffers: any vocabulary size keeps 16-byte rows
+        logits = ws.buf("logits_chunk", chunk, Vp)[:, :V]
         # the chunk's gradient coef * (softmax - onehot) / N: an fp16 plane beside the fp32 logits (exact mode: in place)
-        lgrad = ops.Act(f32=logits) if exact else ops.Act(hi=ws.buf("logits_grad", chunk, V, dtype=torch.float16))
+        lgrad = ops.Act(f32=logits) if exact else ops.Act(hi=ws.buf("logits_grad", chunk, Vp, dtype=torch.float16)[:, :V])
         wout, bout = c.W["decoder.output.weight"], P["decoder.output.bias"]
         for r0 in range(0, M, chunk):
             rows = min(chunk, M - r0)
@@ -530,13 +533,14 @@ class IQ(nn.Module):
             self.terms.zero_()
             dec_out = self._run_forward(c, feats, cids, rids, tids, eps)
             m = c.ws.meta
-            output = torch.empty(B * T, self.V, device=feats.device)
+            Vp = ops.pad8(self.V)
+            output = torch.empty(B * T, Vp, device=feats.device)[:, :self.V]   # padded pitch (a view when V % 8 != 0)
             ops.gemm2(dec_out, c.W["decoder.output.weight"], output, bias=c.P["decoder.output.bias"], terms=1)
             if self.latent_transformer:
                 z_logit, kld = m["z_logit"].clone(), self.terms[2].clone()
             else:
                 z_logit, kld = torch.zeros(1, device=feats.device), torch.zeros((), device=feats.device)
-            return output.view(B, T, self.V), z_logit, kld, m["img"].clone(), m["recon"].clone()
+            return output.unflatten(0, (B, T)), z_logit, kld, m["img"].clone(), m["recon"].clone()
 
     def _backward_api(self, d_output, d_z_logit, d_kld, d_img_in, d_recon_in):
         with ops.no_rounding():
@@ -557,7 +561,7 @@ class IQ(nn.Module):
             if ops.exact_mode():
                 dout_a = ops.Act(f32=dout)
             else:
-                dout_a = ops.Act(hi=torch.empty(B * T, self.V, device=dout.device, dtype=torch.float16))
+                dout_a = ops.Act(hi=torch.empty(B * T, ops.pad8(self.V), device=dout.device, dtype=torch.float16)[:, :self.V])
                 ops.split_f16(dout, dout_a.hi, None, SC)
             ops.gemm2(dout_a, c.W["decoder.output.weight"], d_dec, b_t=True, auto_split=True, terms=1)
             tf.grad_w(c, dout_a, m["dec_out"], c.G["decoder.output.weight"], c.G["decoder.output.bias"])

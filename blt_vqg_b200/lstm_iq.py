@@ -110,8 +110,8 @@ class LSTMIQ(nn.Module):
         self.no_category_space, self.num_categories = no_category_space, num_categories
         self.V, self.H, self.Z, self.A, self.FEAT = vocab_size, hidden_size, z_size, att_ff_size, feat_dim
         self.max_len, self.sos_id, self.eos_id = max_len, sos_id, eos_id
-        assert self.H % 4 == 0 and self.Z % 4 == 0 and self.A % 4 == 0 and self.FEAT % 4 == 0 and self.V % 4 == 0, \
-            "TMA needs 16-byte aligned rows"
+        # model widths with 16-byte rows; the vocabulary size and the feature width are arbitrary (padded row pitches)
+        assert self.H % 4 == 0 and self.Z % 4 == 0 and self.A % 4 == 0, "hidden_size, z_size and att_ff_size must be multiples of 4"
         self.input_dropout_p = input_dropout_p
         self.no_answer_recon, self.no_image_recon = no_answer_recon, no_image_recon
         self.lambdas = dict(lambda_gen=lambda_gen, lambda_z=lambda_z, lambda_i=lambda_i, lambda_a=lambda_a)
@@ -391,10 +391,11 @@ class LSTMIQ(nn.Module):
         d_out = ws.buf("d_out", M, H)
         rows = max(128, ((48 << 20) // (4 * V)) // 128 * 128)
         chunk = min(M, rows)
-        logits = ws.buf("logits_chunk", chunk, V)
+        Vp = ops.pad8(V)   # row pitch of the chunk buffers: any vocabulary size keeps 16-byte rows
+        logits = ws.buf("logits_chunk", chunk, Vp)[:, :V]
         # the chunk's gradient goes out as an fp16 plane beside the fp32 logits (exact mode: in place); the vocabulary products are
         # smooth (no ReLU behind them): single pass
-        lgrad = ops.Act(f32=logits) if ops.exact_mode() else ops.Act(hi=ws.buf("logits_grad", chunk, V, dtype=torch.float16))
+        lgrad = ops.Act(f32=logits) if ops.exact_mode() else ops.Act(hi=ws.buf("logits_grad", chunk, Vp, dtype=torch.float16)[:, :V])
         outs_a = tf.act(c, outs, lo=False)
         wout, bout = c.W["decoder.out.weight"], P["decoder.out.bias"]
         for r0 in range(0, M, chunk):

@@ -45,6 +45,9 @@ CONFIGS = {
     # tiny: checked-in golden fixtures
     "tiny": dict(B=4, V=200, E=32, H=64, L=16, F=128, NL=2, NH=4, T=8, S=5, FEAT=48),
     "small": dict(B=16, V=1000, E=60, H=128, L=32, F=256, NL=2, NH=4, T=12, S=5, FEAT=256),
+    # sizes a real run produces: len(vocab.word2idx) is whatever the frequency threshold left (not a multiple of anything), odd
+    # embedding / feature widths — the buffers get padded row pitches, the unaligned GEMM epilogues their generic path
+    "odd": dict(B=6, V=203, E=30, H=64, L=16, F=128, NL=2, NH=4, T=9, S=5, FEAT=50),
     # cfg3's widths (head_dim 64, H=512, F=2048, V=15000, T=20) at 2 layers and a small batch: the production kernel variants
     # (CTA-pair GEMM, tensor-core attention, warp-per-row LayerNorm, chunked vocabulary CE) against the host oracle in seconds
     "wide": dict(B=24, V=15000, E=300, H=512, L=100, F=2048, NL=2, NH=8, T=20, S=5, FEAT=2048),
@@ -62,6 +65,7 @@ CONFIGS = {
 LSTM_CONFIGS = {
     "tiny": dict(B=6, V=120, H=32, Z=12, A=40, T=8, S=5, FEAT=48),
     "small": dict(B=24, V=1000, H=128, Z=32, A=96, T=12, S=5, FEAT=256),
+    "odd": dict(B=10, V=203, H=32, Z=12, A=40, T=9, S=5, FEAT=50),
     "cfg1": dict(B=32, V=5000, H=512, Z=100, A=512, T=20, S=5, FEAT=2048),     # BASELINE.json configs[0]
     "cfg2": dict(B=256, V=15000, H=300, Z=100, A=512, T=20, S=5, FEAT=2048),   # configs[1]: GloVe-300 => H=300
     "cfg4": dict(B=512, V=15000, H=512, Z=100, A=512, T=20, S=5, FEAT=2048),   # configs[3] per-GPU shard

@@ -108,12 +108,12 @@ def epilogue_case():
     dev = "cuda"
     ok = True
     _lib.lib().b200iq_set_tf32_rounding(0)   # the standalone dropout kernel used as the mask reference must not round
-    for (M, N, K) in [(10240, 2048, 512), (640, 512, 2048), (300, 200, 304), (100, 64, 64)]:
+    for (M, N, K) in [(10240, 2048, 512), (640, 512, 2048), (300, 200, 304), (100, 64, 64), (77, 203, 72), (300, 100, 64)]:   # the last two: generic epilogue
         A, B = torch.randn(M, K, device=dev), torch.randn(N, K, device=dev) * 0.05
         bias = torch.randn(N, device=dev)
         res = torch.randn(M, N, device=dev)
         gate_src = torch.relu(torch.randn(M, N, device=dev))
-        gh, _ = planes_of(gate_src, lo=False)
+        gh, _ = planes_of(gate_src, lo=False, ld=N if N % 8 else None)
         for terms in (1, 3):
             a, b = ops.Act(*(None,) + planes_of(A, lo=terms == 3)), ops.Act(*(None,) + planes_of(B, lo=terms == 3))
             base = val(a) @ val(b).t()

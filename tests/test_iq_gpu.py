@@ -112,7 +112,7 @@ def test_training_step_matches_reference_golden(env, golden_dir, mode, simt):
     assert rel(m.bn_running_var, gold["bn_running_var_after"]) < 1e-3
 
 
-@pytest.mark.parametrize("latent,size", [(True, "small"), (False, "small"), (True, "wide"), (True, "long")])
+@pytest.mark.parametrize("latent,size", [(True, "small"), (False, "small"), (True, "wide"), (True, "long"), (True, "odd")])
 def test_training_step_matches_oracle_small(env, latent, size):
     """seeded synthetic batch at a mid size (ragged lengths, 12 tokens), at cfg3's full widths (2 layers, 20 tokens) and at
     cfg5's (2 layers, 64 tokens, V = 32000): oracle computed here on the host"""

@@ -65,11 +65,12 @@ def test_lstm_training_step_matches_reference_blocks_golden(env, golden_dir, sim
     assert rel(m.bn_running_mean, gold["bn_running_mean_after"]) < 1e-3
 
 
+@pytest.mark.parametrize("size", ["small", "odd"])
 @pytest.mark.parametrize("simt", [True, False])
-def test_lstm_training_step_matches_oracle_small(env, simt):
+def test_lstm_training_step_matches_oracle_small(env, simt, size):
     from blt_vqg_b200 import ops, synth
     from oracle import lstm_oracle
-    cfg = synth.LSTM_CONFIGS["small"]
+    cfg = synth.LSTM_CONFIGS[size]
     b = synth.make_batch(cfg)  # unsorted, ragged answer lengths: length masking instead of packing
     sd = lstm_oracle.init_state_dict(cfg, seed=4)
     g = torch.Generator().manual_seed(5)
