@@ -55,14 +55,40 @@ def load_checkpoint(ckpt, model, train_step=None, strict=True, map_location="cpu
             train_step.t, train_step.iter, train_step.kliter = int(extra["t"]), int(extra["iter"]), int(extra["kliter"])
             model.step_idx = int(extra.get("step_idx", train_step.iter))
         elif isinstance(ckpt, dict) and "global_step" in ckpt:
-            train_step.iter = int(ckpt["global_step"])   # TrainIQ.iter restarts at 0 in the reference; the LR schedule needs it
+            # a checkpoint written by the reference: only the global step is known (TrainIQ.iter / kliter are not saved and the
+            # file carries no mode flag).  The LR schedule needs iter; the KL annealing and the latent switch follow from it
+            # (train_iq.py:108-111: the switch happens at iter == num_pretraining_steps, kliter counts from there)
+            train_step.iter = int(ckpt["global_step"])
+            pre = getattr(getattr(model, "args", None), "num_pretraining_steps", -1)
+            if pre is not None and pre >= 0 and train_step.iter >= pre:
+                train_step.kliter = train_step.iter - pre
+                if hasattr(model, "switch_GVT_train_mode"):
+                    model.switch_GVT_train_mode(True)
+            train_step._seed_ctr = None
+            model.step_idx = train_step.iter
+        if getattr(train_step, "_seed_ctr", None) is not None:
+            train_step._seed_ctr.fill_(int(model.step_idx))   # the device-resident pass counter of the CUDA-graph step
     if isinstance(ckpt, dict) and "b200iq_latent_transformer" in ckpt:
         model.switch_GVT_train_mode(bool(ckpt["b200iq_latent_transformer"]))
     return missing, unexpected
 
 
+def sync_batchnorm_stats(model, group=None):
+    """average the BatchNorm running statistics over the data-parallel ranks (they are per-rank, like DDP's — where
+    broadcast_buffers=True then makes rank 0's win; the mean is the better estimate): call before rank 0 writes a checkpoint"""
+    import torch.distributed as dist
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        for name in ("bn_running_mean", "bn_running_var"):
+            t = getattr(model, name, None)
+            if t is not None:
+                dist.all_reduce(t, group=group)
+                t.div_(dist.get_world_size(group))
+
+
 def make_checkpoint(model, train_step=None, epoch=0, hyper_parameters=None):
-    """a Lightning-shaped checkpoint dict of `model` (the keys `TrainIQ.load_from_checkpoint` / `IQ.load_state_dict` read)"""
+    """a Lightning-shaped checkpoint dict of `model` (the keys `TrainIQ.load_from_checkpoint` / `IQ.load_state_dict` read).
+    Under data parallelism every rank calls it (the BatchNorm statistics are averaged over the ranks first)."""
+    sync_batchnorm_stats(model)
     sd = {PREFIX + k: v.detach().cpu().clone() for k, v in model.state_dict().items()}
     t = getattr(model, "trunk", None)
     if t is not None and hasattr(t, "state_dict"):

@@ -33,6 +33,8 @@ PDL_FORWARD = os.environ.get("B200IQ_PDL", "3") == "2"
 # run the 5-token context encoder on a side stream next to the 21-token response encoder (forward and backward): its GEMMs
 # have 2560 rows = 20-40 tiles for 148 SMs, so on its own it leaves three quarters of the GPU idle
 CONCURRENT_ENCODERS = os.environ.get("B200IQ_CONCURRENT", "1") == "1"
+# B200IQ_NVTX=1: NVTX ranges around the phases of a step (forward / vocabulary CE / backward, and one per stack), for timelines
+NVTX = os.environ.get("B200IQ_NVTX", "0") == "1"
 CE_CHUNK_MB = int(os.environ.get("B200IQ_CE_CHUNK_MB", "80"))  # size of one logits chunk of the fused vocabulary projection + CE
 TERMS = ("rec", "img", "kld", "aux", "count", "gnorm_sq", "unused0", "unused1")
 
@@ -47,6 +49,21 @@ def gen_timing_signal(length, channels, min_timescale=1.0, max_timescale=1.0e4):
     signal = np.concatenate([np.sin(scaled), np.cos(scaled)], axis=1)
     signal = np.pad(signal, [[0, 0], [0, channels % 2]], "constant")
     return torch.from_numpy(signal).float()
+
+
+class _nvtx:
+    """`with _nvtx("name"):` — an NVTX range when B200IQ_NVTX=1, else nothing"""
+
+    def __init__(self, name):
+        self.name = name
+
+    def __enter__(self):
+        if NVTX:
+            torch.cuda.nvtx.range_push(self.name)
+
+    def __exit__(self, *a):
+        if NVTX:
+            torch.cuda.nvtx.range_pop()
 
 
 def _ids(t, device):
@@ -460,7 +477,8 @@ class IQ(nn.Module):
         exact = ops.exact_mode()
         SC = self._grad_scale = self.scale(B * T)
         pdl_prev = ops.set_pdl(True) if PDL_FORWARD else None
-        dec_out = self._run_forward(c, feats, cids, rids, tids, eps)
+        with _nvtx("iq.forward"):
+            dec_out = self._run_forward(c, feats, cids, rids, tids, eps)
         m = ws.meta
         c_rec, c_img, c_kld, c_aux = self.loss_coefs(kliter)
         M = B * T
@@ -474,6 +492,8 @@ class IQ(nn.Module):
         # the chunk's gradient coef * (softmax - onehot) / N: an fp16 plane beside the fp32 logits (exact mode: in place)
         lgrad = ops.Act(f32=logits) if exact else ops.Act(hi=ws.buf("logits_grad", chunk, Vp, dtype=torch.float16)[:, :V])
         wout, bout = c.W["decoder.output.weight"], P["decoder.output.bias"]
+        if NVTX:
+            torch.cuda.nvtx.range_push("iq.vocab_ce")
         for r0 in range(0, M, chunk):
             rows = min(chunk, M - r0)
             lg, xs, gr = logits[:rows], dec_out.rows(r0, r0 + rows), lgrad.rows(0, rows)
@@ -486,6 +506,8 @@ class IQ(nn.Module):
                 ops.gemm2(gr, wout, d_dec[r0:r0 + rows], b_t=True, auto_split=True, terms=1)
                 c.on_side(lambda: tf.grad_w(c, gr, xs, G["decoder.output.weight"], G["decoder.output.bias"]), ev)
                 c.join_side()
+        if NVTX:
+            torch.cuda.nvtx.range_pop()
         if pdl_prev is not None:
             ops.set_pdl(pdl_prev)
         d_img = ws.buf("d_img", B, H)
@@ -502,7 +524,8 @@ class IQ(nn.Module):
         d_recon = ws.buf("d_recon", B, H)
         ops.mse(m["img"], m["recon"], c_img * SC, terms[1:2], d_img if backward else None, d_recon if backward else None)
         if backward:
-            self._backward_tail(c, d_dec, d_img, d_z, d_recon, self.kld_coef_dev if self.kld_coef_dev is not None else c_kld * SC)
+            with _nvtx("iq.backward"):
+                self._backward_tail(c, d_dec, d_img, d_z, d_recon, self.kld_coef_dev if self.kld_coef_dev is not None else c_kld * SC)
         return terms
 
     def total_loss(self, terms, kliter=0):
