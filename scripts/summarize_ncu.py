@@ -58,8 +58,13 @@ def kernel(path):
     for r in rows[2:]:
         print("# kernel:", r[h.index("Kernel Name")][:100])
         for i, c in enumerate(h):
-            if c in KEYS:
+            if c in KEYS or c == "smsp__issue_active.avg.pct_of_peak_sustained_active":
                 print("%-72s %14s %s" % (c, r[i], units[i]))
+        # warp stall reasons (warps stalled per issue-active cycle), largest first
+        st = [(float(r[i].replace(",", "")), c) for i, c in enumerate(h) if c.startswith("smsp__average_warps_issue_stalled_") and c.endswith("_per_issue_active.ratio") and r[i]]
+        print("# stall reasons (warps per issue-active cycle):")
+        for v, c in sorted(st, reverse=True)[:8]:
+            print("%-72s %14.3f" % (c.replace("smsp__average_warps_issue_stalled_", "stall_").replace("_per_issue_active.ratio", ""), v))
 
 if __name__ == "__main__":
     {"launches": launches, "kernel": kernel, "step": step}[sys.argv[1]](*sys.argv[2:])
