@@ -253,7 +253,9 @@ __device__ __forceinline__ float4 sub4(float4 a, float4 b) { return make_float4(
 template <int MT, int NT, int TERMS>
 __device__ __forceinline__ void mma_xyT(float (&acc)[MT][NT][4], const float* X, int nx, int ldx, const float* Y, int ny, int ldy,
                                         int g, int t) {
-#pragma unroll
+  // rolled: the body (all tiles, three terms) is large and these kernels were instruction-fetch bound when every k-step was
+  // unrolled (ncu r02i: stall_no_instruction the top stall of the backward kernel)
+#pragma unroll 1
   for (int kk = 0; kk < 4; ++kk) {
     float4 xa[MT], xb[MT], yf[NT];
 #pragma unroll
@@ -298,7 +300,7 @@ template <int MT, int NT, int TERMS>
 __device__ __forceinline__ void mma_pY_store(const float (&P)[MT][NT][4], const float* Y, int ny, int ldy, const AttOut& out, int nrows,
                                              int g, int t, int rn, const float (*PLO)[NT][4] = nullptr) {
   const int ldo = out.ld;
-#pragma unroll
+#pragma unroll 1
   for (int cq = 0; cq < 2; ++cq) {
     float acc[MT][4][4];
 #pragma unroll
@@ -468,7 +470,7 @@ __device__ __forceinline__ void mma_TtX_store(const float* T, const float* X, in
                                               int g, int t, int rn) {
   const int ldo = out.ld;
   constexpr int MTJ = (NT + 1) / 2;
-#pragma unroll
+#pragma unroll 1
   for (int cq = 0; cq < 2; ++cq) {
     float acc[MTJ][4][4];
 #pragma unroll
@@ -644,7 +646,7 @@ __device__ __forceinline__ void mma_TtX_block_store(const float* T, int ni, int 
                                                     int mj, int nj, int g, int t, int rn) {
   const int ldo = out.ld;
   const int j0 = 16 * mj + g, j1 = j0 + 8;
-#pragma unroll
+#pragma unroll 1
   for (int cq = 0; cq < 2; ++cq) {
     float acc[4][4];
 #pragma unroll
