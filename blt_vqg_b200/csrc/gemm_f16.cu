@@ -83,6 +83,16 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant_
   const int rank = (CTAS == 2) ? (int)cluster_ctarank() : 0;
   const int w_first = blockIdx.x / CTAS, w_step = gridDim.x / CTAS;
 
+  if (warp == 0 && lane == 0) {
+    // the descriptors are fetched while the barriers / TMEM are being set up (the first TMA of each map otherwise waits for them)
+    asm volatile("prefetch.tensormap [%0];" ::"l"((uint64_t)&tmAh) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"((uint64_t)&tmBh) : "memory");
+    if (TERMS == 3) {
+      asm volatile("prefetch.tensormap [%0];" ::"l"((uint64_t)&tmAl) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"((uint64_t)&tmBl) : "memory");
+    }
+    if (epi.C && fast_epi) asm volatile("prefetch.tensormap [%0];" ::"l"((uint64_t)&tmC) : "memory");
+  }
   if (threadIdx.x == 0) {
     for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
     for (int a = 0; a < 2; ++a) { mbar_init(&tfull_bar[a], 1); mbar_init(&tempty_bar[a], F16_EPI_WARPS * CTAS); }
@@ -355,7 +365,9 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant_
       __syncwarp();
       if (lane == 0) { if (CTAS == 2) mbar_arrive_leader(&tempty_bar[acc]); else mbar_arrive(&tempty_bar[acc]); }
     }
-    if (lane == 0) bulk_wait_all();
+    // the staging buffers must outlive the TMA engine's READ of them; the writes themselves complete with the grid (what CUTLASS's
+    // tma_store_wait does too) — waiting for full completion added the global write latency to every CTA's tail
+    if (lane == 0) bulk_wait_read<0>();
   }
   tc_fence_before();
   __syncthreads();
