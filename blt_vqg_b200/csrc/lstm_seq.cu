@@ -385,3 +385,61 @@ extern "C" int b200iq_lstm_seq_bwd(const float* gates, const float* cbuf, const 
                                                                                     workspace, lengths, d, LDG, round_mode(), round_mode() ? 0 : 1);
   return launch_status("lstm_seq_bwd");
 }
+
+// ------------------------------------------------------------------ allocation-free variant of b200iq_lstm_seq_bwd
+// No counterpart in the reference: for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses
+// that forbid it).  The partial-product scratch of the BPTT kernel lives in a file-scope device array instead of a caller-owned
+// workspace, so every GPU that loads the library holds B200IQ_LSTM_SEQ_BWD_STATIC_MAX_BYTES of HBM until the process exits.
+// All calls on one device share the array: calls that overlap on the GPU (different streams) race on it.  Nothing in it has to
+// start at zero — every (parity, cluster, rank) slot the kernel reads at step t was written by the same launch at step t before
+// the cluster barrier — so the previous call's contents need no clearing.
+static __device__ __align__(256) float g_lstm_bwd_scratch[B200IQ_LSTM_SEQ_BWD_STATIC_MAX_BYTES / sizeof(float)];
+
+// `g_lstm_bwd_scratch` in HOST code is only the symbol's host-side stand-in, not a device address: resolve it once per device
+// (with that device current) through cudaGetSymbolAddress and hand the kernel the result.
+static int ls_static_scratch(float** out) {
+  constexpr int MAXDEV = 64;
+  static float* ptrs[MAXDEV] = {};
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) { set_error("lstm_seq_bwd_static: cudaGetDevice: %s", cudaGetErrorString(e)); return (int)e; }
+  if (dev < 0 || dev >= MAXDEV) { set_error("lstm_seq_bwd_static: device ordinal %d out of range", dev); return -1; }
+  float* p = __atomic_load_n(&ptrs[dev], __ATOMIC_ACQUIRE);
+  if (!p) {
+    e = cudaGetSymbolAddress((void**)&p, g_lstm_bwd_scratch);
+    if (e != cudaSuccess || !p) {
+      set_error("lstm_seq_bwd_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+      return e != cudaSuccess ? (int)e : -1;
+    }
+    // function attributes are per device too: part of the same once-per-device set-up
+    e = cudaFuncSetAttribute(lstm_seq_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e != cudaSuccess) { set_error("lstm_seq_bwd_static: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return (int)e; }
+    __atomic_store_n(&ptrs[dev], p, __ATOMIC_RELEASE);  // racing threads resolve the same address
+  }
+  *out = p;
+  return 0;
+}
+
+extern "C" size_t b200iq_lstm_seq_bwd_static_max_bytes(void) { return B200IQ_LSTM_SEQ_BWD_STATIC_MAX_BYTES; }
+
+extern "C" int b200iq_lstm_seq_bwd_static(const float* gates, const float* cbuf, const float* whh, const float* dh_last,
+                                          const float* d_out, float* dgates, float* dh0, float* dc0, const int* lengths,
+                                          int T, int B, int H, void* stream) {
+  B200IQ_CHECK_ARG(gates && cbuf && whh && dgates && dh0 && dc0 && T > 0 && B > 0 && H > 0, "lstm_seq_bwd_static: bad args");
+  LstmSeqDims d; size_t smem;
+  ls_dims(T, B, H, &d, &smem);
+  const int LDG = ls_ldg(d);
+  smem = sizeof(float) * ((size_t)4 * d.U * d.LD + (size_t)LS_ROWS * LDG);
+  B200IQ_CHECK_ARG(b200iq_lstm_seq_supported(H) && d.Hp / 8 <= 8 * LS_MAXTB && smem + 1024 <= 227 * 1024,
+                   "lstm_seq_bwd_static: H=%d does not fit the shared-memory resident slice", H);
+  const size_t need = b200iq_lstm_seq_bwd_workspace_bytes(B, H);
+  B200IQ_CHECK_ARG(need <= (size_t)B200IQ_LSTM_SEQ_BWD_STATIC_MAX_BYTES,
+                   "lstm_seq_bwd_static: B=%d, H=%d needs %zu bytes of scratch, the built-in array holds %zu "
+                   "(use b200iq_lstm_seq_bwd with a caller-owned workspace)", B, H, need, (size_t)B200IQ_LSTM_SEQ_BWD_STATIC_MAX_BYTES);
+  float* scratch = nullptr;
+  if (int rc = ls_static_scratch(&scratch)) return rc;
+  const int clusters = (B + LS_ROWS - 1) / LS_ROWS;
+  lstm_seq_bwd_kernel<<<clusters * LS_CL, LS_THREADS, smem, (cudaStream_t)stream>>>(gates, cbuf, whh, dh_last, d_out, dgates, dh0, dc0,
+                                                                                    scratch, lengths, d, LDG, round_mode(), round_mode() ? 0 : 1);
+  return launch_status("lstm_seq_bwd_static");
+}

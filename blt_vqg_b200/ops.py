@@ -573,6 +573,15 @@ def lstm_seq_bwd(gates, cbuf, whh, dh_last, d_out, dgates, dh0, dc0, lengths):
           _p(lengths), T, B, H, nbytes=_nb(gates, cbuf, d_out, dgates))
 
 
+def lstm_seq_bwd_static(gates, cbuf, whh, dh_last, d_out, dgates, dh0, dc0, lengths):
+    """lstm_seq_bwd without a workspace argument and without any allocation: the scratch is a 5 MiB file-scope device array of
+    the library (B <= 256; larger batches raise).  For callers that cannot allocate (graph capture, serving loops).  Calls that
+    overlap on the GPU share — and race on — that array."""
+    T, B, H4 = gates.shape
+    _call("b200iq_lstm_seq_bwd_static", _p(gates), _p(cbuf), _p(whh), _p(dh_last), _p(d_out), _p(dgates), _p(dh0), _p(dc0),
+          _p(lengths), T, B, H4 // 4, nbytes=_nb(gates, cbuf, d_out, dgates))
+
+
 def lstm_cell_fwd(gates, c_prev, h_prev, c_next, h_next, lengths, t):
     B, H = c_prev.shape
     _call("b200iq_lstm_cell_fwd", _p(gates), _p(c_prev), _p(h_prev), _p(c_next), _p(h_next), _p(lengths), int(t), B, H)

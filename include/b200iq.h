@@ -273,6 +273,17 @@ int b200iq_lstm_seq_fwd(float* gates, const float* whh, float* hbuf, float* cbuf
 size_t b200iq_lstm_seq_bwd_workspace_bytes(int B, int H);
 int b200iq_lstm_seq_bwd(const float* gates, const float* cbuf, const float* whh, const float* dh_last, const float* d_out,
                         float* dgates, float* dh0, float* dc0, float* workspace, const int* lengths, int T, int B, int H, void* stream);
+/* b200iq_lstm_seq_bwd for callers that cannot allocate device memory (CUDA graph capture, serving loops, harnesses that forbid
+ * cudaMalloc): same kernel, same arguments minus `workspace` — the scratch is a file-scope device array inside the library
+ * (B200IQ_LSTM_SEQ_BWD_STATIC_MAX_BYTES = 5 MiB per GPU that loads the library, held until exit; covers B <= 256 at any supported
+ * H, e.g. the B = 256, H = 300 full-size LSTM config).  Calls no cudaMalloc / cudaFree / allocating routine.  Returns < 0 with a
+ * message when b200iq_lstm_seq_bwd_workspace_bytes(B, H) exceeds the limit.  Every call on a device shares the array: calls that
+ * OVERLAP on the GPU (different streams) race; back-to-back calls are fine (nothing in the array has to start at zero).
+ * No counterpart in the reference. */
+#define B200IQ_LSTM_SEQ_BWD_STATIC_MAX_BYTES (5u << 20)
+size_t b200iq_lstm_seq_bwd_static_max_bytes(void);
+int b200iq_lstm_seq_bwd_static(const float* gates, const float* cbuf, const float* whh, const float* dh_last, const float* d_out,
+                               float* dgates, float* dh0, float* dc0, const int* lengths, int T, int B, int H, void* stream);
 /* out[t*B+b] = in[b*T_in + col0 + t], t < T_out: batch-major token ids -> time-major (inputs[:, :-1] of decoder_rnn.py:141) */
 int b200iq_transpose_ids(const int* in, int* out, int B, int T_in, int T_out, int col0, void* stream);
 
