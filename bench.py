@@ -311,6 +311,10 @@ def kernel_rooflines(ts, model, args, dev_batches, peaks):
     ops.GEMM_TRACE, ops.KERNEL_TRACE = [], []
     step_t0, step_t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     try:
+        # the eager issue of an instrumented step (every launch through ctypes plus two event records) is slower than the device
+        # runs it; with an empty queue an event pair would then also span the host's gap in front of its kernel.  ~25 ms of
+        # spinning first lets the host run ahead, so the launches of both steps wait in the stream behind their start events
+        torch.cuda._sleep(int(25e-3 * 1.9e9))
         step_t0.record()
         for i in range(2):
             ts.step(*step_inputs(args.workload, dev_batches[i % len(dev_batches)]))

@@ -33,6 +33,14 @@ PDL_FORWARD = os.environ.get("B200IQ_PDL", "3") == "2"
 # run the 5-token context encoder on a side stream next to the 21-token response encoder (forward and backward): its GEMMs
 # have 2560 rows = 20-40 tiles for 148 SMs, so on its own it leaves three quarters of the GPU idle
 CONCURRENT_ENCODERS = os.environ.get("B200IQ_CONCURRENT", "1") == "1"
+# B200IQ_DEC_SPLIT=n (default 1 = off): the decoder stack as n independent chains over n equal sample ranges of the batch, each on
+# its own stream, forward and backward (WorkspacePart: every chain works on its row range of the same full-size buffers).
+# The decoder is the one serial phase of the step (timeline profiles/r02m_timeline_summary.txt: one kernel resident for the
+# 2.25 ms of its forward), but cutting it does not pay on cfg3: half-size products run one tile round on 40 of the 74 SM pairs
+# in almost the time the full-size ones need for two, and two 80-CTA persistent grids do not fit the 148 SMs side by side —
+# 11.15 ms per step with n = 2, 11.85 with n = 4, against 10.92 (profiles/r02m_decoder_split.txt).  Kept as a switch.
+DEC_SPLIT = int(os.environ.get("B200IQ_DEC_SPLIT", "1"))
+DEC_SPLIT_MIN_ROWS = int(os.environ.get("B200IQ_DEC_SPLIT_MIN_ROWS", "2048"))
 # B200IQ_NVTX=1: NVTX ranges around the phases of a step (forward / vocabulary CE / backward, and one per stack), for timelines
 NVTX = os.environ.get("B200IQ_NVTX", "0") == "1"
 CE_CHUNK_MB = int(os.environ.get("B200IQ_CE_CHUNK_MB", "80"))  # size of one logits chunk of the fused vocabulary projection + CE
@@ -238,6 +246,43 @@ class IQ(nn.Module):
         if side is not None:
             torch.cuda.current_stream().wait_stream(side)
 
+    def _dec_parts(self, B, T):
+        """number of sample ranges the decoder stack is cut into (DEC_SPLIT)"""
+        n = DEC_SPLIT
+        if n > 1 and B % n == 0 and (B // n) * T >= DEC_SPLIT_MIN_ROWS:
+            return n
+        return 1
+
+    def _run_parts(self, c, nparts, fn):
+        """fn(part, nparts) for every part: part 0 on the current stream, the others on their own streams (same priority) that
+        fork here and are joined before this returns; c.ws is the part's row slice of the workspace while fn issues its launches"""
+        main = torch.cuda.current_stream()
+        ws = c.ws
+        streams = [main]
+        for i in range(1, nparts):
+            key = ("part_stream", main.cuda_stream, i)
+            st = ws.meta.get(key)
+            if st is None:
+                st = ws.meta[key] = torch.cuda.Stream(device=ws.device, priority=main.priority)
+            st.wait_stream(main)
+            streams.append(st)
+        try:
+            for i, st in enumerate(streams):
+                key = ("part_ws", i, nparts)
+                part = ws.meta.get(key)
+                if part is None:
+                    part = ws.meta[key] = tf.WorkspacePart(ws, i, nparts)
+                c.ws = part
+                if i == 0:
+                    fn(i, nparts)
+                else:
+                    with torch.cuda.stream(st), _lib.pinned_stream():
+                        fn(i, nparts)
+        finally:
+            c.ws = ws
+        for st in streams[1:]:
+            main.wait_stream(st)
+
     def scale(self, tokens=None):
         """the loss scale in force: 1 in exact mode; else self.loss_scale, or (loss_scale = 0) the power of two chosen from the
         number of target tokens of the batch.  Without `tokens`: the scale of the last pass."""
@@ -344,7 +389,16 @@ class IQ(nn.Module):
         shifted[:, 0] = self.sos_id
         shifted[:, 1:] = tids[:, :-1]
         xd = tf.embed_fwd(c, "dec.emb", shifted, B, T, self.timing_dec, add0=img, add1=z)
-        dec_out = tf.decoder_fwd(c, "dec", "decoder.decoder.", xd, shifted, enc_a, cids, B, T, S, self.NL)
+        nparts = self._dec_parts(B, T)
+        if nparts == 1:
+            dec_out = tf.decoder_fwd(c, "dec", "decoder.decoder.", xd, shifted, enc_a, cids, B, T, S, self.NL)
+        else:
+            def part_fwd(i, n):
+                b0, b1 = i * (B // n), (i + 1) * (B // n)
+                tf.decoder_fwd(c, "dec", "decoder.decoder.", xd[b0 * T:b1 * T], shifted[b0:b1], enc_a.rows(b0 * S, b1 * S),
+                               cids[b0:b1], b1 - b0, T, S, self.NL, pdl=False)
+            self._run_parts(c, nparts, part_fwd)
+            dec_out = ws.act("dec.lnf.y")   # the parts wrote their rows of the full-size buffers
         # image reconstruction (iq.py:109-112)
         rin = ws.buf("rin", B, H)
         ops.tok0_gather(enc_out, rin, B, S, H)
@@ -372,8 +426,26 @@ class IQ(nn.Module):
         if latent:
             ops.axpby(d_z, d_rin, d_z)
         d_enc_out = ws.buf("d_enc_out", B * S, H)
-        dxd, dxd_a = tf.decoder_bwd(c, "dec", "decoder.decoder.", d_dec, m["shifted"], m["enc_a"], d_enc_out, m["cids"],
-                                    B, T, S, self.NL)
+        nparts = self._dec_parts(B, T)
+        if nparts == 1:
+            dxd, dxd_a = tf.decoder_bwd(c, "dec", "decoder.decoder.", d_dec, m["shifted"], m["enc_a"], d_enc_out, m["cids"],
+                                        B, T, S, self.NL)
+        else:
+            # the parts add into the same weight gradients (atomic reduce-adds) in no fixed order: a layer's gradients are final
+            # when every part has passed it, so the bucket marks of the stack are replaced by one mark after the join
+            saved, c.on_ready = c.on_ready, None
+
+            def part_bwd(i, n):
+                b0, b1 = i * (B // n), (i + 1) * (B // n)
+                tf.decoder_bwd(c, "dec", "decoder.decoder.", d_dec[b0 * T:b1 * T], m["shifted"][b0:b1], m["enc_a"].rows(b0 * S, b1 * S),
+                               d_enc_out[b0 * S:b1 * S], m["cids"][b0:b1], b1 - b0, T, S, self.NL)
+            try:
+                self._run_parts(c, nparts, part_bwd)
+            finally:
+                c.on_ready = saved
+            c.ready("decoder.decoder.dec.0.layer_norm_mha_dec.weight")
+            dxd = ws["dec.dx"]
+            dxd_a = tf.dx_operand(c, "dec.dx.hi", dxd)
         ops.tok0_gather(dxd, d_img, B, T, H, accumulate=True)
         if latent:
             ops.tok0_gather(dxd, d_z, B, T, H, accumulate=True)

@@ -53,6 +53,47 @@ class Workspace:
         return sum(t.numel() * t.element_size() for t in self.bufs.values())
 
 
+class _PartMeta(dict):
+    """meta of a WorkspacePart: private to the part (stack in / out tensors, dropout keys, side streams) except the operand widths
+    ("actK", name), which describe the shared full-size buffers and are mirrored into the parent"""
+
+    def __init__(self, parent_meta):
+        super().__init__()
+        self.parent_meta = parent_meta
+
+    def __setitem__(self, k, v):
+        if isinstance(k, tuple) and k and k[0] == "actK":
+            self.parent_meta[k] = v
+        super().__setitem__(k, v)
+
+
+class WorkspacePart:
+    """rows [part/nparts, (part+1)/nparts) of every buffer of a parent Workspace: the view a stack schedule gets when the batch
+    is cut into `nparts` equal sample ranges that run as independent chains on their own streams (iq.py: the decoder's two
+    half-batch passes).  Every buffer of a stack has the batch in its leading dimension ([B*n, ...], [B, ...]), so a part asks
+    for `shape` and receives its slice of the parent's `nparts * shape[0]`-row buffer; whoever runs after the parts have joined
+    reads the parent's full-size buffers as if one pass had written them."""
+
+    def __init__(self, parent, part, nparts):
+        self.parent, self.part, self.nparts = parent, part, nparts
+        self.device = parent.device
+        self.meta = _PartMeta(parent.meta)
+
+    def _rows(self, t):
+        n = t.shape[0] // self.nparts
+        return t[self.part * n:(self.part + 1) * n]
+
+    def buf(self, name, *shape, dtype=torch.float32):
+        return self._rows(self.parent.buf(name, shape[0] * self.nparts, *shape[1:], dtype=dtype))
+
+    def __getitem__(self, name):
+        return self._rows(self.parent.bufs[name])
+
+    def act(self, name):
+        a = self.parent.act(name)
+        return ops.Act(*(None if t is None else self._rows(t) for t in (a.f32, a.hi, a.lo)))
+
+
 class WeightOperands:
     """name -> ops.Act of a weight matrix: the fp32 master view in exact mode, else views of the fp16 plane arenas (hi, lo) that
     mirror the parameter arena element for element; matrices whose row pitch is not a multiple of 8 halves (E = 300, L = 100)
@@ -469,7 +510,7 @@ def encoder_bwd(c, tag, pfx, dy, ids, B, n, NL):
     return dxa
 
 
-def decoder_fwd(c, tag, pfx, x, ids, enc_out, enc_ids, B, T, S, NL, out_kind="act_hi"):
+def decoder_fwd(c, tag, pfx, x, ids, enc_out, enc_ids, B, T, S, NL, out_kind="act_hi", pdl=True):
     """models/transformer_layers.py:205-221; causal|pad mask of :207 is built inside the attention kernel.
     enc_out: the context as a GEMM operand."""
     c.ws.meta[tag + ".in"] = x
@@ -492,7 +533,7 @@ def decoder_fwd(c, tag, pfx, x, ids, enc_out, enc_ids, B, T, S, NL, out_kind="ac
         xn = ln_fwd(c, lt + ".ln2", lp + "layer_norm_mha_enc", x, add=y, sum_out=a)
         if side is not None and i == 0:
             torch.cuda.current_stream().wait_stream(side)
-        if PDL_DECODER and i == 0:
+        if PDL_DECODER and pdl and i == 0:
             pdl_prev = ops.set_pdl(True)   # from here to the end of the stack nothing runs beside the main stream
         y = cross_attn_fwd(c, lt + ".ca", lp + "multi_head_attention_enc_dec.", xn, enc_out, enc_ids, B, T, S, kv=kvs[i])
         b = c.ws.buf(lt + ".ca.out", x.shape[0], x.shape[1])

@@ -476,3 +476,30 @@ def test_cuda_graph_step_matches_the_eager_schedule(env):
     assert ts.graph_replays == 3
     assert all(torch.isfinite(o).all() for o in out)
     assert not torch.allclose(out[3], out[4], rtol=1e-7) and not torch.allclose(out[2], out[3], rtol=1e-7)
+
+
+@pytest.mark.parametrize("simt", [True, False])
+def test_decoder_as_two_sample_range_chains_matches_the_single_chain(env, simt, monkeypatch):
+    """B200IQ_DEC_SPLIT (iq.DEC_SPLIT): the decoder stack run as two half-batch chains on two streams over row ranges of the same
+    buffers (transformer.WorkspacePart) gives the single chain's loss terms and gradients (the chains add into the same weight
+    gradients atomically, so only the summation order differs)"""
+    from blt_vqg_b200 import iq as iq_mod, ops, synth
+    from blt_vqg_b200.iq import IQ
+    cfg = synth.CONFIGS["wide"]
+    batch = synth.make_batch(cfg)
+    torch.manual_seed(5)
+    sd = IQ(True, synth.SynthVocab(cfg["V"]), synth.args_for(cfg)).state_dict()
+    eps = torch.randn(cfg["B"], cfg["L"]).cuda()
+    res = []
+    for split in (1, 2):
+        monkeypatch.setattr(iq_mod, "DEC_SPLIT", split)
+        monkeypatch.setattr(iq_mod, "DEC_SPLIT_MIN_ROWS", 1)
+        m = _build(cfg, True, sd)
+        assert m._dec_parts(cfg["B"], cfg["T"]) == split
+        with ops.gemm_mode(simt=simt):
+            t = m.forward_losses(batch["feats"], batch["answers"], batch["posteriors"], batch["questions"], kliter=7000, eps=eps)
+        torch.cuda.synchronize()
+        res.append((t.cpu().clone(), m.unscaled_grads().clone()))
+    (t1, g1), (t2, g2) = res
+    assert torch.allclose(t1[:5], t2[:5], rtol=1e-5, atol=0)
+    assert rel(g2, g1) < (1e-5 if simt else 2e-4)   # fp16 dX planes: a different summation order moves single roundings
