@@ -588,6 +588,404 @@ attention_bwd_tc_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, Att
   mma_TtX_store<MT, NT>(Ws, dO, a.nq, ATT_SP, att_out_at(dv, (size_t)b * a.nk * lddv + h * 64), a.nk, g, t, a.rn);   // dV = W^T . dO
 }
 
+// ---------------------------------------------------------------- fp16 mma.sync backward (precise mode, fp16-plane gradients)
+// attention_bwd_tc_kernel above executes ~5 k SASS instructions per (sample, head) — m16n8k8 TF32 MMAs whose fragments are
+// assembled from scalar / 16-byte shared loads and split into TF32 terms at every use, 12 Philox calls per lane — at 6 warps per
+// SM, and sits at 12-20 % of the HBM roof although its DRAM traffic is the algorithmic minimum (ncu profiles/r02i_attention_bwd.txt).
+// This kernel does the same five products with mma.sync.m16n8k16 on fp16 tiles: Q, K (hi + lo planes, for the 3-term score
+// product that reproduces the forward's probabilities), V and dO (hi) are converted ONCE while they are staged, fragments come
+// from ldmatrix (.trans for the operands that are read transposed: dS^T, W^T, and K / Q / dO as row-major B operands), dS goes
+// from the accumulator layout of the score product straight into the A operand of dQ = dS . K (two fp16 terms: rows of dS sum
+// to zero, see attention_bwd_tc_kernel), and the 4 lanes that share a score row compute each Philox call once between them.
+// Every operand of a backward product carries 11 significant bits either way (fp16 here, TF32 there); gradients are under the
+// caller's loss scale, as the fp16 planes they are written to require anyway.  Tiles hold exactly nq / nk rows: fragment rows
+// beyond them read one shared row of zeros.
+// Staging: a row arrives as 64 fp32 (256 B, cp.async: every 16-byte piece of all four tensors in flight at once, no registers
+// held) and is converted IN PLACE into its fp16 hi half-row (bytes 0..127) and lo half-row (bytes 128..255); row pitch 272 B.
+static constexpr int ATT_HP = 136;  // halves per row of a 64-column tile (272 B: the 8 rows of an ldmatrix hit 8 distinct 16-byte slots)
+static constexpr int ATT_HL = 64;   // the lo half-row starts 64 halves into the row
+static constexpr int ATT_HS = 40;   // halves per row of a score tile (<= 32 keys; 80 B: likewise conflict-free)
+static constexpr int ATT_HZ = 72;   // halves of the shared row of zeros
+static size_t att_h_bytes(int nq, int nk) { return (size_t)2 * ((size_t)ATT_HP * (2 * nq + 2 * nk) + ATT_HZ + (size_t)ATT_HS * 2 * nq); }
+
+__device__ __forceinline__ void ldsm4(uint32_t (&r)[4], const __half* p) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"((uint32_t)__cvta_generic_to_shared(p)));
+}
+__device__ __forceinline__ void ldsm4t(uint32_t (&r)[4], const __half* p) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"((uint32_t)__cvta_generic_to_shared(p)));
+}
+__device__ __forceinline__ void mma_f16(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint32_t pack_h2(float a, float b) {
+  const __half2 h = __floats2half2_rn(a, b);
+  return *reinterpret_cast<const uint32_t*>(&h);
+}
+// rows x 64 fp32 (global, 16-byte aligned rows) -> the tile's rows, still fp32: one cp.async per 16-byte piece.  Lane l owns
+// piece l & 15 of rows (l >> 4), (l >> 4) + 2, ...: both addresses advance by constants
+__device__ __forceinline__ void att_stage_h(__half* tile, const float* __restrict__ src, int rows, int ld, int lane) {
+  const int r0 = lane >> 4, c4 = lane & 15;
+  uint32_t d = (uint32_t)__cvta_generic_to_shared(tile + r0 * ATT_HP + 8 * c4);
+  const float* sp = src + (size_t)r0 * ld + 4 * c4;
+  const size_t step = (size_t)2 * ld;
+  for (int r = r0; r < rows; r += 2, d += 4 * ATT_HP, sp += step)
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(sp) : "memory");
+  asm volatile("cp.async.commit_group;" ::: "memory");
+}
+// fp32 rows -> fp16 hi (+ lo = fp16(x - hi)) in place.  The 16 lanes that own the pieces of one row read them in the same
+// instruction and write that row's half-rows after a warp sync; other rows are untouched, so rows go through in batches of 8
+template <bool LO>
+__device__ __forceinline__ void att_convert_h(__half* tile, int rows, int lane) {
+  const int r0 = lane >> 4, c4 = lane & 15;
+  for (int rb = 0; rb < rows; rb += 8) {
+    float4 v[4];
+    __half* base = tile + (rb + r0) * ATT_HP;
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (rb + r0 + 2 * u < rows) v[u] = *reinterpret_cast<const float4*>(base + 2 * u * ATT_HP + 8 * c4);
+    __syncwarp();
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (rb + r0 + 2 * u < rows) {
+        __half* o = base + 2 * u * ATT_HP + 4 * c4;
+        const __half2 h0 = __floats2half2_rn(v[u].x, v[u].y), h1 = __floats2half2_rn(v[u].z, v[u].w);
+        *reinterpret_cast<uint2*>(o) = make_uint2(*reinterpret_cast<const uint32_t*>(&h0), *reinterpret_cast<const uint32_t*>(&h1));
+        if (LO) {
+          const float2 f0 = __half22float2(h0), f1 = __half22float2(h1);
+          *reinterpret_cast<uint2*>(o + ATT_HL) = make_uint2(pack_h2(v[u].x - f0.x, v[u].y - f0.y), pack_h2(v[u].z - f1.x, v[u].w - f1.y));
+        }
+      }
+  }
+}
+
+// out[16mj + .., :64] (rows < nj) = T^T . X: T = score tile [ni][ATT_HS] (rows = queries, read transposed through ldmatrix.trans),
+// X = [ni][ATT_HP] tile (queries x 64); Z = the row of zeros.  MT = 16-query steps, NP = 16-key output blocks.
+template <int MT, int NP>
+__device__ __forceinline__ void att_h_TtX_store(const __half* T, const __half* X, const __half* Z, int ni, const AttOut& out, int nj, int lane) {
+  const int g = lane >> 2, t = lane & 3, r8 = lane & 7, mi = lane >> 3;
+  // per-lane fragment rows (query index = the reduction index of both operands)
+  const __half* xrow[MT];
+  const __half* trow[MT];
+#pragma unroll
+  for (int ks = 0; ks < MT; ++ks) {
+    const int xr = 16 * ks + r8 + 8 * (mi & 1), tr = 16 * ks + r8 + 8 * (mi >> 1);
+    xrow[ks] = (xr < ni ? X + xr * ATT_HP : Z) + 8 * (mi >> 1);
+    trow[ks] = (tr < ni ? T + tr * ATT_HS : Z) + 8 * (mi & 1);
+  }
+  __half* orow[NP][2];
+#pragma unroll
+  for (int mj = 0; mj < NP; ++mj)
+#pragma unroll
+    for (int hh = 0; hh < 2; ++hh) orow[mj][hh] = out.hi + (size_t)(16 * mj + g + 8 * hh) * out.ld + 2 * t;
+#pragma unroll 1
+  for (int cq = 0; cq < 2; ++cq) {
+    float acc[NP][4][4];
+#pragma unroll
+    for (int mj = 0; mj < NP; ++mj)
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) acc[mj][u][e] = 0.f;
+#pragma unroll
+    for (int ks = 0; ks < MT; ++ks) {
+      // B = X rows (k = query) as a row-major operand: .trans; two loads cover the four 8-column tiles of this 32-column half
+      uint32_t xb[2][4];
+#pragma unroll
+      for (int x = 0; x < 2; ++x) ldsm4t(xb[x], xrow[ks] + 32 * cq + 16 * x);
+#pragma unroll
+      for (int mj = 0; mj < NP; ++mj) {
+        uint32_t af[4];
+        ldsm4t(af, trow[ks] + 16 * mj);
+#pragma unroll
+        for (int x = 0; x < 2; ++x) {
+          mma_f16(acc[mj][2 * x], af[0], af[1], af[2], af[3], xb[x][0], xb[x][1]);
+          mma_f16(acc[mj][2 * x + 1], af[0], af[1], af[2], af[3], xb[x][2], xb[x][3]);
+        }
+      }
+    }
+#pragma unroll
+    for (int mj = 0; mj < NP; ++mj)
+#pragma unroll
+      for (int hh = 0; hh < 2; ++hh)
+        if (16 * mj + g + 8 * hh < nj) {
+#pragma unroll
+          for (int u = 0; u < 4; ++u)
+            *reinterpret_cast<uint32_t*>(orow[mj][hh] + 32 * cq + 8 * u) = pack_h2(acc[mj][u][2 * hh], acc[mj][u][2 * hh + 1]);
+        }
+  }
+}
+
+template <int MT, int NT>
+__global__ void __launch_bounds__(ATT_TC_WARPS * 32)
+attention_bwd_h_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, AttOut dq, AttOut dk, AttOut dv, int warp_bytes) {
+  constexpr int NP = (NT + 1) / 2;   // 16-key steps
+  pdl_trigger();
+  pdl_wait();
+  const int wid = threadIdx.x >> 5;
+  const int bh = blockIdx.x * ATT_TC_WARPS + wid;
+  if (bh >= a.B * a.nh) return;
+  const int b = bh / a.nh, h = bh - b * a.nh, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3, r8 = lane & 7, mi = lane >> 3;
+  const int nq = a.nq, nk = a.nk;
+  extern __shared__ __align__(16) float att_dyn[];
+  __half* Qh = reinterpret_cast<__half*>(reinterpret_cast<uint8_t*>(att_dyn) + (size_t)wid * warp_bytes);
+  __half* Kh = Qh + nq * ATT_HP;
+  __half* Vh = Kh + nk * ATT_HP;
+  __half* Oh = Vh + nk * ATT_HP;
+  __half* Z = Oh + nq * ATT_HP;      // one row of zeros
+  __half* Ds = Z + ATT_HZ;           // [nq][ATT_HS] dS (hi)
+  __half* Ws = Ds + nq * ATT_HS;     // [nq][ATT_HS] post-dropout weights
+  att_stage_h(Qh, a.q + (size_t)b * nq * a.ldq + h * 64, nq, a.ldq, lane);
+  att_stage_h(Kh, a.k + (size_t)b * a.bsk + h * 64, nk, a.ldk, lane);
+  att_stage_h(Vh, a.v + (size_t)b * a.bsv + h * 64, nk, a.ldv, lane);
+  att_stage_h(Oh, dout + (size_t)b * nq * ldo + h * 64, nq, ldo, lane);
+  for (int i = lane; i < ATT_HZ / 2; i += 32) reinterpret_cast<uint32_t*>(Z)[i] = 0u;
+  // the dropout words of this (sample, head): call (row i, key tile c) is made once, by lane (i * NT + c) % 32, and left in the
+  // score-tile region (free until dS / W are written) as four words; every lane then picks word t of the calls of its rows
+  const bool drop = a.drop_p > 0.f;
+  uint4* dwords = reinterpret_cast<uint4*>(Ds);
+  if (drop) {
+    for (int c = lane; c < nq * NT; c += 32) {
+      uint32_t w[4];
+      att_drop_words(a, (size_t)bh * nq + c / NT, c % NT, w);
+      dwords[c] = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+  }
+  // masks of this lane's keys j = 8 nt + 2 t + e (bit 2 nt + e): inside the sequence, and padding
+  uint32_t jvalid = 0u, jpad = 0u;
+#pragma unroll
+  for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+      const int j = 8 * nt + 2 * t + e;
+      if (j < nk) {
+        jvalid |= 1u << (2 * nt + e);
+        if (a.key_ids != nullptr && __ldg(a.key_ids + b * nk + j) == a.pad_id) jpad |= 1u << (2 * nt + e);
+      }
+    }
+  // the tensors land in issue order: convert each as soon as its group is complete, under the loads of the later ones
+  asm volatile("cp.async.wait_group 3;" ::: "memory");
+  __syncwarp();
+  att_convert_h<true>(Qh, nq, lane);
+  asm volatile("cp.async.wait_group 2;" ::: "memory");
+  __syncwarp();
+  att_convert_h<true>(Kh, nk, lane);
+  asm volatile("cp.async.wait_group 1;" ::: "memory");
+  __syncwarp();
+  att_convert_h<false>(Vh, nk, lane);
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  __syncwarp();
+  att_convert_h<false>(Oh, nq, lane);
+  __syncwarp();
+
+  float S[MT][NT][4], dW[MT][NT][4];
+#pragma unroll
+  for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) { S[mt][nt][e] = 0.f; dW[mt][nt][e] = 0.f; }
+  // scores = Q . K^T (3-term) and d(post-dropout weights) = dO . V^T (single pass); K / V rows are the B operand as stored
+  {
+    const __half* kp[NT]; const __half* klp[NT]; const __half* vp[NT];
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) {
+      const int r = 8 * nt + r8;
+      const bool ok = r < nk;
+      kp[nt] = (ok ? Kh + r * ATT_HP : Z) + 8 * mi;
+      klp[nt] = (ok ? Kh + r * ATT_HP + ATT_HL : Z) + 8 * mi;
+      vp[nt] = (ok ? Vh + r * ATT_HP : Z) + 8 * mi;
+    }
+    const __half* qp[MT]; const __half* qlp[MT]; const __half* op[MT];
+#pragma unroll
+    for (int mt = 0; mt < MT; ++mt) {
+      const int r = 16 * mt + r8 + 8 * (mi & 1);
+      const bool ok = r < nq;
+      qp[mt] = (ok ? Qh + r * ATT_HP : Z) + 8 * (mi >> 1);
+      qlp[mt] = (ok ? Qh + r * ATT_HP + ATT_HL : Z) + 8 * (mi >> 1);
+      op[mt] = (ok ? Oh + r * ATT_HP : Z) + 8 * (mi >> 1);
+    }
+#pragma unroll 1
+    for (int k2 = 0; k2 < 2; ++k2) {   // 32 head columns per pass
+      uint32_t kh[NT][4], kl[NT][4], vh[NT][4];
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt) {
+        ldsm4(kh[nt], kp[nt] + 32 * k2);
+        ldsm4(kl[nt], klp[nt] + 32 * k2);
+        ldsm4(vh[nt], vp[nt] + 32 * k2);
+      }
+#pragma unroll
+      for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+        for (int kq = 0; kq < 2; ++kq) {
+          uint32_t qh[4], ql[4], oh[4];
+          ldsm4(qh, qp[mt] + 32 * k2 + 16 * kq);
+          ldsm4(ql, qlp[mt] + 32 * k2 + 16 * kq);
+          ldsm4(oh, op[mt] + 32 * k2 + 16 * kq);
+          // term-major: consecutive MMAs go to different accumulators (a dependent accumulate waits out the whole MMA latency)
+#pragma unroll
+          for (int nt = 0; nt < NT; ++nt) mma_f16(S[mt][nt], ql[0], ql[1], ql[2], ql[3], kh[nt][2 * kq], kh[nt][2 * kq + 1]);
+#pragma unroll
+          for (int nt = 0; nt < NT; ++nt) mma_f16(dW[mt][nt], oh[0], oh[1], oh[2], oh[3], vh[nt][2 * kq], vh[nt][2 * kq + 1]);
+#pragma unroll
+          for (int nt = 0; nt < NT; ++nt) mma_f16(S[mt][nt], qh[0], qh[1], qh[2], qh[3], kl[nt][2 * kq], kl[nt][2 * kq + 1]);
+#pragma unroll
+          for (int nt = 0; nt < NT; ++nt) mma_f16(S[mt][nt], qh[0], qh[1], qh[2], qh[3], kh[nt][2 * kq], kh[nt][2 * kq + 1]);
+        }
+    }
+  }
+  // softmax over the keys, dP = dW * keep, dS = P (dP - sum_j dP P) scale (0 where masked), W = P * keep — per score row
+  // (16 mt + g + 8 hh; rows >= nq hold finite junk that no stored result depends on).  dS leaves as two fp16 terms in A-fragment
+  // order for dQ and, with W, as the shared tiles whose transposes feed dK / dV.
+  const uint32_t thr = dropout_threshold(a.drop_p);
+  const float inv_keep = 1.f / (1.f - a.drop_p);
+  const int gd = g - 2 * t;   // causal: key j = 8 nt + 2 t + e is masked for row i = 16 mt + 8 hh + g when 8 nt + e - 16 mt - 8 hh > g - 2 t
+  uint32_t dsh[MT][2 * NP][2], dsl[MT][2 * NP][2];
+  __syncwarp();   // (dropout words are read below, the tiles are written after the next sync)
+#pragma unroll
+  for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+    for (int hh = 0; hh < 2; ++hh) {
+      const int i = 16 * mt + g + 8 * hh;
+      const bool row_ok = i < nq;
+      float p[NT][2], kp2[NT][2];
+      uint32_t mbits = 0u;
+      float mx = -3.0e38f;
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const bool m = (a.causal && (8 * nt + e - 16 * mt - 8 * hh) > gd) || ((jpad >> (2 * nt + e)) & 1u);
+          if (m) mbits |= 1u << (2 * nt + e);
+          float sv = m ? -1e18f : S[mt][nt][2 * hh + e] * a.scale;
+          sv = ((jvalid >> (2 * nt + e)) & 1u) ? sv : -3.0e38f;
+          p[nt][e] = sv;
+          mx = fmaxf(mx, sv);
+        }
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+      float sum = 0.f;
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const float pe = ((jvalid >> (2 * nt + e)) & 1u) ? __expf(p[nt][e] - mx) : 0.f;
+          p[nt][e] = pe;
+          sum += pe;
+        }
+      sum += __shfl_xor_sync(0xffffffffu, sum, 1);
+      sum += __shfl_xor_sync(0xffffffffu, sum, 2);
+      const float inv = 1.f / sum;
+      float dot = 0.f;
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt) {
+        uint32_t w = 0xFFFFFFFFu;
+        if (drop && row_ok) w = reinterpret_cast<const uint32_t*>(dwords + (i * NT + nt))[t];
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          p[nt][e] *= inv;
+          kp2[nt][e] = (!drop || (((w >> (16 * e)) & 0xFFFFu) >= thr)) ? (drop ? inv_keep : 1.f) : 0.f;
+          const float dP = dW[mt][nt][2 * hh + e] * kp2[nt][e];
+          dW[mt][nt][2 * hh + e] = dP;
+          dot += dP * p[nt][e];
+        }
+      }
+      dot += __shfl_xor_sync(0xffffffffu, dot, 1);
+      dot += __shfl_xor_sync(0xffffffffu, dot, 2);
+#pragma unroll
+      for (int nt = 0; nt < 2 * NP; ++nt) {
+        float ds0 = 0.f, ds1 = 0.f;
+        if (nt < NT) {
+          ds0 = ((mbits >> (2 * nt)) & 1u) ? 0.f : p[nt][0] * (dW[mt][nt][2 * hh] - dot) * a.scale;
+          ds1 = ((mbits >> (2 * nt + 1)) & 1u) ? 0.f : p[nt][1] * (dW[mt][nt][2 * hh + 1] - dot) * a.scale;
+          S[mt][nt][2 * hh] = p[nt][0] * kp2[nt][0];       // W replaces the scores (written to its tile below)
+          S[mt][nt][2 * hh + 1] = p[nt][1] * kp2[nt][1];
+        }
+        const __half2 dh = __floats2half2_rn(ds0, ds1);
+        const float2 df = __half22float2(dh);
+        dsh[mt][nt][hh] = *reinterpret_cast<const uint32_t*>(&dh);
+        dsl[mt][nt][hh] = pack_h2(ds0 - df.x, ds1 - df.y);
+      }
+    }
+  __syncwarp();   // every lane has read its dropout words: the region becomes the dS / W tiles
+#pragma unroll
+  for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+    for (int hh = 0; hh < 2; ++hh) {
+      const int i = 16 * mt + g + 8 * hh;
+      if (i < nq) {
+        uint32_t* drow = reinterpret_cast<uint32_t*>(Ds + i * ATT_HS + 2 * t);
+        uint32_t* wrow = reinterpret_cast<uint32_t*>(Ws + i * ATT_HS + 2 * t);
+#pragma unroll
+        for (int nt = 0; nt < 2 * NP; ++nt) {
+          drow[4 * nt] = dsh[mt][nt][hh];
+          wrow[4 * nt] = (nt < NT) ? pack_h2(S[mt][nt < NT ? nt : 0][2 * hh], S[mt][nt < NT ? nt : 0][2 * hh + 1]) : 0u;   // (index clamp: compile-time)
+        }
+      }
+    }
+  __syncwarp();
+  // dQ = (dS + dS_lo) . K: dS straight from the accumulator layout (two 8-key tiles = one 16-key A fragment), K rows as a
+  // row-major B operand (.trans)
+  {
+    const __half* kr[NP];
+#pragma unroll
+    for (int j = 0; j < NP; ++j) {
+      const int r = 16 * j + r8 + 8 * (mi & 1);
+      kr[j] = (r < nk ? Kh + r * ATT_HP : Z) + 8 * (mi >> 1);
+    }
+    __half* orow[MT][2];
+#pragma unroll
+    for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+      for (int hh = 0; hh < 2; ++hh) orow[mt][hh] = dq.hi + ((size_t)b * nq + 16 * mt + g + 8 * hh) * dq.ld + h * 64 + 2 * t;
+#pragma unroll 1
+    for (int cq = 0; cq < 2; ++cq) {
+      float acc[MT][4][4];
+#pragma unroll
+      for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+#pragma unroll
+          for (int e = 0; e < 4; ++e) acc[mt][u][e] = 0.f;
+#pragma unroll
+      for (int j = 0; j < NP; ++j) {
+        uint32_t kb[2][4];
+#pragma unroll
+        for (int x = 0; x < 2; ++x) ldsm4t(kb[x], kr[j] + 32 * cq + 16 * x);
+        if (a.dq2) {
+#pragma unroll
+          for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+            for (int x = 0; x < 2; ++x) {
+              mma_f16(acc[mt][2 * x], dsl[mt][2 * j][0], dsl[mt][2 * j][1], dsl[mt][2 * j + 1][0], dsl[mt][2 * j + 1][1], kb[x][0], kb[x][1]);
+              mma_f16(acc[mt][2 * x + 1], dsl[mt][2 * j][0], dsl[mt][2 * j][1], dsl[mt][2 * j + 1][0], dsl[mt][2 * j + 1][1], kb[x][2], kb[x][3]);
+            }
+        }
+#pragma unroll
+        for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+          for (int x = 0; x < 2; ++x) {
+            mma_f16(acc[mt][2 * x], dsh[mt][2 * j][0], dsh[mt][2 * j][1], dsh[mt][2 * j + 1][0], dsh[mt][2 * j + 1][1], kb[x][0], kb[x][1]);
+            mma_f16(acc[mt][2 * x + 1], dsh[mt][2 * j][0], dsh[mt][2 * j][1], dsh[mt][2 * j + 1][0], dsh[mt][2 * j + 1][1], kb[x][2], kb[x][3]);
+          }
+      }
+#pragma unroll
+      for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh)
+          if (16 * mt + g + 8 * hh < nq) {
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+              *reinterpret_cast<uint32_t*>(orow[mt][hh] + 32 * cq + 8 * u) = pack_h2(acc[mt][u][2 * hh], acc[mt][u][2 * hh + 1]);
+          }
+    }
+  }
+  att_h_TtX_store<MT, NP>(Ds, Qh, Z, nq, att_out_at(dk, (size_t)b * nk * dk.ld + h * 64), nk, lane);   // dK = dS^T . Q
+  att_h_TtX_store<MT, NP>(Ws, Oh, Z, nq, att_out_at(dv, (size_t)b * nk * dv.ld + h * 64), nk, lane);   // dV = W^T . dO
+}
+
 // ---------------------------------------------------------------- row-block kernels: 32 < n <= 80 (cfg5: T = 64, R = 65)
 // One CTA per (sample, head), one WARP per 16 query rows; the warp keeps its 16 x nk slab of scores in registers
 // (NT <= 10 key tiles of 8).  Forward: warps are independent, no shared memory.  Backward: every warp writes its rows of
@@ -866,6 +1264,22 @@ static int attention_bwd_impl(const B200iqAttention* p, const float* dout, const
     const void* ptrs[] = {p->q, p->k, p->v, dout};
     const int lds[] = {p->ldq, p->ldk, p->ldv, p->ldo};
     const AttOut outs[] = {dq, dk, dv};
+    // B200IQ_ATT_BWD_H=0: keep the TF32 register kernel for the fp16-plane gradients too (A/B switch)
+    static const bool use_h = [] { const char* e = getenv("B200IQ_ATT_BWD_H"); return !(e && e[0] == '0'); }();
+    const bool planes_hi = dq.hi && dk.hi && dv.hi && !dq.lo && !dk.lo && !dv.lo;
+    if (use_h && p->precise && planes_hi && tc_ok(p, ptrs, 4, lds, 4, outs, 3)) {
+      const int mt = a.nq > 16 ? 2 : 1, nt = (a.nk + 7) / 8, grid = (a.B * a.nh + ATT_TC_WARPS - 1) / ATT_TC_WARPS;
+      const int wbytes = (int)((att_h_bytes(a.nq, a.nk) + 15) & ~(size_t)15);
+      const size_t tsm = (size_t)ATT_TC_WARPS * wbytes;
+#define CALL(M_, N_) \
+  do { \
+    if (tsm > 48 * 1024) cudaFuncSetAttribute(attention_bwd_h_kernel<M_, N_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm); \
+    launch_dep(attention_bwd_h_kernel<M_, N_>, dim3(grid), dim3(ATT_TC_WARPS * 32), tsm, (cudaStream_t)stream, a, dout, p->ldo, dq, dk, dv, wbytes); \
+  } while (0)
+      B200IQ_ATT_DISPATCH(mt, nt, CALL);
+#undef CALL
+      return launch_status("attention_bwd_h");
+    }
     if (tc_ok(p, ptrs, 4, lds, 4, outs, 3)) {
       const int mt = a.nq > 16 ? 2 : 1, nt = (a.nk + 7) / 8, grid = (a.B * a.nh + ATT_TC_WARPS - 1) / ATT_TC_WARPS;
       const size_t tsm = sizeof(float) * ATT_TC_WARPS * (size_t)(2 * a.nq + 2 * a.nk) * ATT_SP;

@@ -130,6 +130,39 @@ def test_attention_tensor_core_path(ops, nq, nk, causal, drop):
         assert rel(tc[0], ref) < 2e-3 and rel(tc[1], qr.grad) < 2e-3 and rel(tc[2], kr.grad) < 2e-3 and rel(tc[3], vr.grad) < 2e-3
 
 
+@pytest.mark.parametrize("nq,nk,causal", [(20, 20, True), (21, 21, False), (20, 5, False), (5, 5, False), (32, 32, True), (1, 1, True),
+                                             (17, 9, False), (9, 30, False), (64, 64, True)])
+@pytest.mark.parametrize("drop", [0.0, 0.3])
+def test_attention_backward_into_fp16_planes(ops, nq, nk, causal, drop):
+    """b200iq_attention_bwd_f16 (precise mode: unrounded fp32 q / k / v / dO in, gradients out as fp16 hi planes — the fp16
+    mma.sync kernel for n <= 32, the row-block kernel above that) against fp64 autograd (drop = 0) and against the exact CUDA-core
+    kernels under the same Philox key (drop > 0: same mask by construction).  Bar 2e-3: 11-bit operands of the single-pass
+    backward products plus the 2^-12 rounding of the fp16 result."""
+    B, nh, d = 9, 3, 64
+    H = nh * d
+    q = torch.randn(B * nq, H, device="cuda")
+    kv = torch.randn(B * nk, 2 * H, device="cuda") + 1.0   # a common component in the keys (LayerNorm + bias-free projection)
+    k, v = kv[:, :H], kv[:, H:]
+    do = torch.randn(B * nq, H, device="cuda") * 0.05
+    ids = torch.randint(1, 50, (B, nk), device="cuda", dtype=torch.int32)
+    for b in range(B):
+        ids[b, max(1, nk - b):] = 0
+    if nk > 1:
+        ids[0, 0] = 0
+    key = (drop, 4321, 11 << 40)
+    dq, dkv = torch.full((B * nq, H), float("nan"), device="cuda", dtype=torch.float16), torch.full((B * nk, 2 * H), float("nan"), device="cuda", dtype=torch.float16)
+    ops.attention_bwd(q, k, v, do, dq, dkv[:, :H], dkv[:, H:], ids, 0, causal, B, nh, nq, nk, d, *key)
+    eq, ekv = torch.empty(B * nq, H, device="cuda"), torch.empty(B * nk, 2 * H, device="cuda")
+    ops.attention_bwd(q, k, v, do, eq, ekv[:, :H], ekv[:, H:], ids, 0, causal, B, nh, nq, nk, d, *key)   # rounding off, fp32 out: exact kernels
+    for got, want in ((dq, eq), (dkv[:, :H], ekv[:, :H]), (dkv[:, H:], ekv[:, H:])):
+        assert torch.isfinite(got).all()
+        assert rel(got, want) < 2e-3
+    if drop == 0.0:
+        qr, kr, vr = (t.double().clone().requires_grad_(True) for t in (q, k.contiguous(), v.contiguous()))
+        _ref_attention(qr, kr, vr, ids, causal, B, nh, nq, nk, d).backward(do.double())
+        assert rel(dq, qr.grad) < 2e-3 and rel(dkv[:, :H], kr.grad) < 2e-3 and rel(dkv[:, H:], vr.grad) < 2e-3
+
+
 def test_ce_rows_and_aux(ops):
     rows, V, T = 300, 1000, 10
     logits = torch.randn(rows, V, device="cuda") * 3
