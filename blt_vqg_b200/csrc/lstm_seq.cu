@@ -13,6 +13,8 @@
 //      c_t / h_t (the backward pass and the vocabulary GEMM read them) and
 //   4. meets its 7 peers at a hardware cluster barrier (release / acquire), after which h_t is visible to them.
 // The algorithmic HBM traffic per token is what SURVEY 8(d) counts: read x-projection 16H B, write gates 16H + h,c 8H B.
+#include <stdlib.h>
+#include <cuda_fp16.h>
 #include "common.cuh"
 
 namespace b200iq {
@@ -183,6 +185,169 @@ lstm_seq_fwd_kernel(float* gates, const float* __restrict__ whh, float* hbuf, fl
 }
 
 
+// ---------------------------------------------------------------- precise forward on fp16 mma.sync
+// lstm_seq_fwd_kernel<true> splits h and W_hh into TF32 hi / lo terms in registers at every k-step of every time step: ~8 k
+// issued instructions per warp and step for 114 MMAs' worth of math (ncu profiles/r02i_lstm_seq_fwd.txt: 30 % issue-active on 8
+// warps, stall_wait on top; 29.6 us per time step).  Here the CTA's W_hh slice is split ONCE, when it is loaded, into fp16 hi / lo
+// half-rows that stay in shared memory (the same bytes as the fp32 slice), h_{t-1} is split once per step as it is staged, and
+// the 3-term product hi.hi + lo.hi + hi.lo runs as mma.sync.m16n8k16 with ldmatrix fragments: one ldmatrix.x4 per A term and
+// k-step, one per n-tile and k-step for all four B registers (hi and lo sit side by side in a row).
+// W is stored scaled by 2^6 (|W_hh| ~ H^-1/2: its lo term would otherwise sit among fp16 subnormals); the accumulators are
+// scaled back, both exactly.
+static constexpr float LS_WSCALE = 64.f;
+struct LstmSeqHDims { int KP, P; };   // KP = H rounded up to 16 (k extent), P = row pitch in halves (hi: [0, KP), lo: [KP, 2 KP))
+
+__device__ __forceinline__ void ls_ldsm4(uint32_t (&r)[4], const __half* p) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"((uint32_t)__cvta_generic_to_shared(p)));
+}
+__device__ __forceinline__ void ls_mma_f16(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+__global__ void __cluster_dims__(LS_CL, 1, 1) __launch_bounds__(LS_THREADS, 1)
+lstm_seq_fwd_h_kernel(float* gates, const float* __restrict__ whh, float* hbuf, float* cbuf,
+                      const int* __restrict__ lengths, LstmSeqDims d, LstmSeqHDims hd) {
+  extern __shared__ float ls_smem[];
+  __half* Ws = reinterpret_cast<__half*>(ls_smem);   // [4U][P]: row n = 4 * unit + gate
+  __half* hs = Ws + (size_t)4 * d.U * hd.P;          // [16][P]
+  const int KP = hd.KP, P = hd.P;
+  const int rank = ls_ctarank(), b0 = ls_clusterid() * LS_ROWS;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t4 = lane & 3, r8 = lane & 7, mi = lane >> 3;
+  const int NT = d.U / 2, KS = KP / 16;
+  const size_t BH = (size_t)d.B * d.H, B4H = 4 * BH;
+  // the slice, split once: one warp per row, lanes along k (coalesced 128-byte reads)
+  for (int n = warp; n < 4 * d.U; n += LS_THREADS / 32) {
+    const int ul = n >> 2, gate = n & 3, u = rank * d.U + ul;
+    const float* src = whh + (size_t)(gate * d.H + u) * d.H;
+    for (int k = lane; k < KP; k += 32) {
+      const float w = (u < d.H && k < d.H) ? __ldg(src + k) * LS_WSCALE : 0.f;
+      const __half hi = __float2half_rn(w);
+      Ws[(size_t)n * P + k] = hi;
+      Ws[(size_t)n * P + KP + k] = __float2half_rn(w - __half2float(hi));
+    }
+  }
+  for (int idx = threadIdx.x; idx < LS_ROWS * P; idx += LS_THREADS) hs[idx] = __float2half_rn(0.f);   // k padding stays zero
+  const int my_row = g + 8 * (t4 & 1), b = b0 + my_row;
+  const bool row_ok = b < d.B;
+  const int len = (lengths && row_ok) ? __ldg(lengths + b) : 0x7fffffff;
+  float creg[LS_MAXT], xg[LS_MAXT][4];
+  int unit[LS_MAXT];
+#pragma unroll
+  for (int i = 0; i < LS_MAXT; ++i) {
+    const int nt = warp + 8 * i;
+    unit[i] = (nt < NT) ? rank * d.U + 2 * nt + (t4 >> 1) : d.H;  // >= H: nothing to do
+    creg[i] = (row_ok && unit[i] < d.H) ? cbuf[(size_t)b * d.H + unit[i]] : 0.f;
+  }
+  auto fetch_x = [&](int t) {
+#pragma unroll
+    for (int i = 0; i < LS_MAXT; ++i)
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+        xg[i][q] = (row_ok && unit[i] < d.H && t < len) ? __ldcg(gates + (size_t)t * B4H + (size_t)b * 4 * d.H + q * d.H + unit[i]) : 0.f;
+  };
+  fetch_x(0);
+  // per-lane fragment addresses: A = h rows (r8 + 8 (mi & 1)), k half (mi >> 1); B = slice rows 8 nt + r8, registers
+  // {hi k 0-7, hi k 8-15, lo k 0-7, lo k 8-15}
+  const __half* ap = hs + (size_t)(r8 + 8 * (mi & 1)) * P + 8 * (mi >> 1);
+  const __half* bp[LS_MAXT];
+#pragma unroll
+  for (int i = 0; i < LS_MAXT; ++i) {
+    const int nt = warp + 8 * i;
+    bp[i] = Ws + (size_t)(8 * (nt < NT ? nt : 0) + r8) * P + 8 * (mi & 1) + (mi >> 1) * KP;
+  }
+  const float wsinv = 1.f / LS_WSCALE;
+  __syncthreads();
+  for (int t = 0; t < d.T; ++t) {
+    // 1. h_{t-1} of the cluster's 16 rows -> fp16 hi / lo half-rows
+    const float* hprev = hbuf + (size_t)t * BH;
+    if ((d.H & 3) == 0) {
+      const int h4 = d.H >> 2;
+      for (int idx = threadIdx.x; idx < LS_ROWS * h4; idx += LS_THREADS) {
+        const int r = idx / h4, c4 = idx - r * h4;
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (b0 + r < d.B) v = __ldcg(reinterpret_cast<const float4*>(hprev + (size_t)(b0 + r) * d.H + 4 * c4));  // L2: written by peer SMs
+        const __half2 h0 = __floats2half2_rn(v.x, v.y), h1 = __floats2half2_rn(v.z, v.w);
+        const float2 f0 = __half22float2(h0), f1 = __half22float2(h1);
+        const __half2 l0 = __floats2half2_rn(v.x - f0.x, v.y - f0.y), l1 = __floats2half2_rn(v.z - f1.x, v.w - f1.y);
+        __half* o = hs + (size_t)r * P + 4 * c4;
+        *reinterpret_cast<uint2*>(o) = make_uint2(*reinterpret_cast<const uint32_t*>(&h0), *reinterpret_cast<const uint32_t*>(&h1));
+        *reinterpret_cast<uint2*>(o + KP) = make_uint2(*reinterpret_cast<const uint32_t*>(&l0), *reinterpret_cast<const uint32_t*>(&l1));
+      }
+    } else {
+      for (int idx = threadIdx.x; idx < LS_ROWS * d.H; idx += LS_THREADS) {
+        const int r = idx / d.H, c = idx - r * d.H;
+        const float v = (b0 + r < d.B) ? __ldcg(hprev + (size_t)(b0 + r) * d.H + c) : 0.f;
+        const __half hi = __float2half_rn(v);
+        hs[(size_t)r * P + c] = hi;
+        hs[(size_t)r * P + KP + c] = __float2half_rn(v - __half2float(hi));
+      }
+    }
+    __syncthreads();
+    // 2. gates[16, 4U] = h . W_slice^T, three terms; consecutive MMAs go to different accumulators
+    float acc[LS_MAXT][4];
+#pragma unroll
+    for (int i = 0; i < LS_MAXT; ++i)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) acc[i][e] = 0.f;
+#pragma unroll 2
+    for (int ks = 0; ks < KS; ++ks) {
+      uint32_t ah[4], al[4], w[LS_MAXT][4];
+      ls_ldsm4(ah, ap + 16 * ks);
+      ls_ldsm4(al, ap + KP + 16 * ks);
+#pragma unroll
+      for (int i = 0; i < LS_MAXT; ++i)
+        if (warp + 8 * i < NT) ls_ldsm4(w[i], bp[i] + 16 * ks);
+#pragma unroll
+      for (int i = 0; i < LS_MAXT; ++i)
+        if (warp + 8 * i < NT) ls_mma_f16(acc[i], al, w[i][0], w[i][1]);
+#pragma unroll
+      for (int i = 0; i < LS_MAXT; ++i)
+        if (warp + 8 * i < NT) ls_mma_f16(acc[i], ah, w[i][2], w[i][3]);
+#pragma unroll
+      for (int i = 0; i < LS_MAXT; ++i)
+        if (warp + 8 * i < NT) ls_mma_f16(acc[i], ah, w[i][0], w[i][1]);
+    }
+    // 3. the four gates of (my_row, unit) meet (see lstm_seq_fwd_kernel)
+    float hnew[LS_MAXT], ga[LS_MAXT][4];
+#pragma unroll
+    for (int i = 0; i < LS_MAXT; ++i) {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) acc[i][e] *= wsinv;
+      const bool odd = t4 & 1;
+      const float s0 = odd ? acc[i][0] : acc[i][2], s1 = odd ? acc[i][1] : acc[i][3];
+      const float r0 = __shfl_xor_sync(0xffffffffu, s0, 1), r1 = __shfl_xor_sync(0xffffffffu, s1, 1);
+      float gi = odd ? r0 : acc[i][0], gf = odd ? r1 : acc[i][1], gg = odd ? acc[i][2] : r0, go = odd ? acc[i][3] : r1;
+      hnew[i] = 0.f;
+      if (row_ok && unit[i] < d.H) {
+        if (t < len) {
+          gi = ls_sigmoid(gi + xg[i][0]); gf = ls_sigmoid(gf + xg[i][1]); gg = tanhf(gg + xg[i][2]); go = ls_sigmoid(go + xg[i][3]);
+          creg[i] = gf * creg[i] + gi * gg;
+          hnew[i] = go * tanhf(creg[i]);
+        } else {
+          hnew[i] = __ldcg(hprev + (size_t)b * d.H + unit[i]);  // packed-sequence semantics: the state stops at the row's length
+        }
+        hbuf[(size_t)(t + 1) * BH + (size_t)b * d.H + unit[i]] = hnew[i];
+      }
+      ga[i][0] = gi; ga[i][1] = gf; ga[i][2] = gg; ga[i][3] = go;
+    }
+    // 4. h_t first, then ARRIVE; what the peers do not need overlaps the barrier latency before the WAIT
+    ls_cluster_arrive();
+#pragma unroll
+    for (int i = 0; i < LS_MAXT; ++i)
+      if (row_ok && unit[i] < d.H) {
+        if (t < len) {
+          float* gout = gates + (size_t)t * B4H + (size_t)b * 4 * d.H + unit[i];
+          gout[0] = ga[i][0]; gout[d.H] = ga[i][1]; gout[2 * d.H] = ga[i][2]; gout[3 * d.H] = ga[i][3];
+        }
+        cbuf[(size_t)(t + 1) * BH + (size_t)b * d.H + unit[i]] = creg[i];
+      }
+    if (t + 1 < d.T) fetch_x(t + 1);
+    ls_cluster_wait();  // h_t of all 8 unit slices is visible; also orders this step's reads of `hs` before the refill
+  }
+}
+
 // ---------------------------------------------------------------- BPTT, same decomposition
 // Per step (t = T-1 .. 0) a CTA turns d h_t, d c_t of ITS units into the four pre-activation gate gradients (registers ->
 // dgates[t] in global memory for the weight-gradient GEMMs, and a [16, 4U] shared-memory tile), multiplies that tile with
@@ -352,7 +517,24 @@ extern "C" int b200iq_lstm_seq_fwd(float* gates, const float* whh, float* hbuf, 
     attr_done = true;
   }
   const int clusters = (B + LS_ROWS - 1) / LS_ROWS;
-  // rounding mode off = the caller keeps unrounded fp32 tensors (fp16-plane scheme): 3-term products
+  // rounding mode off = the caller keeps unrounded fp32 tensors (fp16-plane scheme): 3-term products, on the fp16 mma.sync kernel
+  // when its tiles fit (B200IQ_LSTM_FWD_H=0: the TF32 register-split kernel, the A/B switch)
+  if (!round_mode()) {
+    static const bool use_h = [] { const char* e = getenv("B200IQ_LSTM_FWD_H"); return !(e && e[0] == '0'); }();
+    LstmSeqHDims hd;
+    hd.KP = (H + 15) & ~15;
+    hd.P = 2 * hd.KP;
+    while (((2 * hd.P) % 128) / 16 % 2 == 0) hd.P += 8;   // row pitch = odd multiple of 16 B (mod 128): conflict-free ldmatrix
+    const size_t smem_h = sizeof(__half) * (size_t)(4 * d.U + LS_ROWS) * hd.P;
+    if (use_h && smem_h + 1024 <= 227 * 1024) {
+      static int attr_dev = -1;
+      int dev = 0;
+      cudaGetDevice(&dev);
+      if (attr_dev != dev) { cudaFuncSetAttribute(lstm_seq_fwd_h_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); attr_dev = dev; }
+      lstm_seq_fwd_h_kernel<<<clusters * LS_CL, LS_THREADS, smem_h, (cudaStream_t)stream>>>(gates, whh, hbuf, cbuf, lengths, d, hd);
+      return launch_status("lstm_seq_fwd_h");
+    }
+  }
   if (round_mode()) lstm_seq_fwd_kernel<false><<<clusters * LS_CL, LS_THREADS, smem, (cudaStream_t)stream>>>(gates, whh, hbuf, cbuf, lengths, d, 1);
   else lstm_seq_fwd_kernel<true><<<clusters * LS_CL, LS_THREADS, smem, (cudaStream_t)stream>>>(gates, whh, hbuf, cbuf, lengths, d, 0);
   return launch_status("lstm_seq_fwd");

@@ -216,6 +216,39 @@ def test_persistent_recurrence_matches_the_per_step_kernels(env, T, B, H, ragged
         _lib.lib().b200iq_set_tf32_rounding(prev)
 
 
+@pytest.mark.parametrize("T,B,H,ragged", [(19, 256, 300, False), (5, 256, 300, True), (7, 37, 64, True), (3, 16, 100, False), (4, 50, 304, True),
+                                           (6, 20, 30, True)])
+def test_precise_persistent_forward_matches_an_fp64_recurrence(env, T, B, H, ragged):
+    """b200iq_lstm_seq_fwd in the library's precise mode (TF32 rounding off: unrounded fp32 tensors, 3-term products — the fp16
+    mma.sync kernel with the W_hh slice split once into fp16 hi / lo half-rows) against the same recurrence in fp64: activated
+    gates, h and c sequences.  ~2^-21 per operand of the recurrent product, compounded over T steps."""
+    from blt_vqg_b200 import ops
+    assert ops.lstm_seq_supported(H)
+    torch.manual_seed(4)
+    whh = torch.randn(4 * H, H, device="cuda") * H ** -0.5
+    xproj = torch.randn(T, B, 4 * H, device="cuda")
+    h0, c0 = torch.randn(B, H, device="cuda") * 0.5, torch.randn(B, H, device="cuda") * 0.5
+    lengths = torch.randint(1, T + 1, (B,), device="cuda", dtype=torch.int32) if ragged else None
+    gates = xproj.clone()
+    hbuf, cbuf = torch.zeros(T + 1, B, H, device="cuda"), torch.zeros(T + 1, B, H, device="cuda")
+    hbuf[0].copy_(h0)
+    cbuf[0].copy_(c0)
+    with ops.no_rounding():
+        ops.lstm_seq_fwd(gates, whh, hbuf, cbuf, lengths)
+    torch.cuda.synchronize()
+    h, c, w = h0.double(), c0.double(), whh.double()
+    for t in range(T):
+        pre = xproj[t].double() + h @ w.t()
+        i, f, g, o = pre[:, :H].sigmoid(), pre[:, H:2 * H].sigmoid(), pre[:, 2 * H:3 * H].tanh(), pre[:, 3 * H:].sigmoid()
+        cn = f * c + i * g
+        hn = o * cn.tanh()
+        live = torch.ones(B, 1, device="cuda", dtype=torch.bool) if lengths is None else (lengths > t)[:, None]
+        h, c = torch.where(live, hn, h), torch.where(live, cn, c)
+        act = torch.cat([i, f, g, o], 1)
+        assert rel(hbuf[t + 1], h) < 2e-5 and rel(cbuf[t + 1], c) < 2e-5, t
+        assert rel(gates[t] * live, act * live) < 2e-5, t
+
+
 def test_category_space_matches_oracle_and_bit_exact_ids(env, golden_dir):
     """SURVEY §8f rank 4 — the evaluate() / sampler call sequence of old_train_iq.py:134-142,194-213 and evaluate_iq.py:51-54:
     encode_categories, encode_into_t, the two KL terms, predict_from_category / predict_from_answer (greedy ids bit-exact vs
