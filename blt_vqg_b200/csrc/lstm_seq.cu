@@ -15,6 +15,7 @@
 // The algorithmic HBM traffic per token is what SURVEY 8(d) counts: read x-projection 16H B, write gates 16H + h,c 8H B.
 #include <stdlib.h>
 #include <cuda_fp16.h>
+#include <type_traits>
 #include "common.cuh"
 
 namespace b200iq {
@@ -218,14 +219,46 @@ lstm_seq_fwd_h_kernel(float* gates, const float* __restrict__ whh, float* hbuf, 
   const int NT = d.U / 2, KS = KP / 16;
   const size_t BH = (size_t)d.B * d.H, B4H = 4 * BH;
   // the slice, split once: one warp per row, lanes along k (coalesced 128-byte reads)
-  for (int n = warp; n < 4 * d.U; n += LS_THREADS / 32) {
-    const int ul = n >> 2, gate = n & 3, u = rank * d.U + ul;
-    const float* src = whh + (size_t)(gate * d.H + u) * d.H;
-    for (int k = lane; k < KP; k += 32) {
-      const float w = (u < d.H && k < d.H) ? __ldg(src + k) * LS_WSCALE : 0.f;
-      const __half hi = __float2half_rn(w);
-      Ws[(size_t)n * P + k] = hi;
-      Ws[(size_t)n * P + KP + k] = __float2half_rn(w - __half2float(hi));
+  if ((d.H & 3) == 0) {
+    // 16-byte pieces; a warp covers 4 rows per pass of 8 lanes x 4 pieces each... simply: piece p of the slice = (row p / KP4, k4 = p % KP4)
+    const int KP4 = KP >> 2, H4 = d.H >> 2, pieces = 4 * d.U * KP4;
+    for (int p0 = threadIdx.x; p0 < pieces; p0 += 4 * LS_THREADS) {
+      float4 v[4];
+      int nn[4], kk[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int pidx = p0 + j * LS_THREADS;
+        v[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+        nn[j] = -1;
+        if (pidx < pieces) {
+          nn[j] = pidx / KP4;
+          kk[j] = pidx - nn[j] * KP4;
+          const int u = rank * d.U + (nn[j] >> 2);
+          if (u < d.H && kk[j] < H4) v[j] = __ldg(reinterpret_cast<const float4*>(whh + (size_t)((nn[j] & 3) * d.H + u) * d.H) + kk[j]);
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (nn[j] >= 0) {
+          const float x0 = v[j].x * LS_WSCALE, x1 = v[j].y * LS_WSCALE, x2 = v[j].z * LS_WSCALE, x3 = v[j].w * LS_WSCALE;
+          const __half2 h0 = __floats2half2_rn(x0, x1), h1 = __floats2half2_rn(x2, x3);
+          const float2 f0 = __half22float2(h0), f1 = __half22float2(h1);
+          const __half2 l0 = __floats2half2_rn(x0 - f0.x, x1 - f0.y), l1 = __floats2half2_rn(x2 - f1.x, x3 - f1.y);
+          __half* o = Ws + (size_t)nn[j] * P + 4 * kk[j];
+          *reinterpret_cast<uint2*>(o) = make_uint2(*reinterpret_cast<const uint32_t*>(&h0), *reinterpret_cast<const uint32_t*>(&h1));
+          *reinterpret_cast<uint2*>(o + KP) = make_uint2(*reinterpret_cast<const uint32_t*>(&l0), *reinterpret_cast<const uint32_t*>(&l1));
+        }
+    }
+  } else {
+    for (int n = warp; n < 4 * d.U; n += LS_THREADS / 32) {
+      const int ul = n >> 2, gate = n & 3, u = rank * d.U + ul;
+      const float* src = whh + (size_t)(gate * d.H + u) * d.H;
+      for (int k = lane; k < KP; k += 32) {
+        const float w = (u < d.H && k < d.H) ? __ldg(src + k) * LS_WSCALE : 0.f;
+        const __half hi = __float2half_rn(w);
+        Ws[(size_t)n * P + k] = hi;
+        Ws[(size_t)n * P + KP + k] = __float2half_rn(w - __half2float(hi));
+      }
     }
   }
   for (int idx = threadIdx.x; idx < LS_ROWS * P; idx += LS_THREADS) hs[idx] = __float2half_rn(0.f);   // k padding stays zero
@@ -258,22 +291,36 @@ lstm_seq_fwd_h_kernel(float* gates, const float* __restrict__ whh, float* hbuf, 
     bp[i] = Ws + (size_t)(8 * (nt < NT ? nt : 0) + r8) * P + 8 * (mi & 1) + (mi >> 1) * KP;
   }
   const float wsinv = 1.f / LS_WSCALE;
+  int ntw = 0;   // n-tiles of this warp
+#pragma unroll
+  for (int i = 0; i < LS_MAXT; ++i) ntw += (warp + 8 * i < NT) ? 1 : 0;
   __syncthreads();
   for (int t = 0; t < d.T; ++t) {
     // 1. h_{t-1} of the cluster's 16 rows -> fp16 hi / lo half-rows
     const float* hprev = hbuf + (size_t)t * BH;
     if ((d.H & 3) == 0) {
-      const int h4 = d.H >> 2;
-      for (int idx = threadIdx.x; idx < LS_ROWS * h4; idx += LS_THREADS) {
-        const int r = idx / h4, c4 = idx - r * h4;
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (b0 + r < d.B) v = __ldcg(reinterpret_cast<const float4*>(hprev + (size_t)(b0 + r) * d.H + 4 * c4));  // L2: written by peer SMs
-        const __half2 h0 = __floats2half2_rn(v.x, v.y), h1 = __floats2half2_rn(v.z, v.w);
-        const float2 f0 = __half22float2(h0), f1 = __half22float2(h1);
-        const __half2 l0 = __floats2half2_rn(v.x - f0.x, v.y - f0.y), l1 = __floats2half2_rn(v.z - f1.x, v.w - f1.y);
-        __half* o = hs + (size_t)r * P + 4 * c4;
-        *reinterpret_cast<uint2*>(o) = make_uint2(*reinterpret_cast<const uint32_t*>(&h0), *reinterpret_cast<const uint32_t*>(&h1));
-        *reinterpret_cast<uint2*>(o + KP) = make_uint2(*reinterpret_cast<const uint32_t*>(&l0), *reinterpret_cast<const uint32_t*>(&l1));
+      // thread -> row tid / 16, 16-byte pieces (tid % 16) + 16 j of that row: all of a thread's loads are issued before the first use
+      const int h4 = d.H >> 2, r = threadIdx.x >> 4, c0 = threadIdx.x & 15;
+      const bool live = b0 + r < d.B;
+      const float4* src = reinterpret_cast<const float4*>(hprev + (size_t)(b0 + r) * d.H);
+      __half* orow = hs + (size_t)r * P;
+      for (int cb = c0; cb < h4; cb += 64) {
+        float4 v[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          v[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (live && cb + 16 * j < h4) v[j] = __ldcg(src + cb + 16 * j);   // L2: written by peer SMs
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          if (cb + 16 * j < h4) {
+            const __half2 h0 = __floats2half2_rn(v[j].x, v[j].y), h1 = __floats2half2_rn(v[j].z, v[j].w);
+            const float2 f0 = __half22float2(h0), f1 = __half22float2(h1);
+            const __half2 l0 = __floats2half2_rn(v[j].x - f0.x, v[j].y - f0.y), l1 = __floats2half2_rn(v[j].z - f1.x, v[j].w - f1.y);
+            __half* o = orow + 4 * (cb + 16 * j);
+            *reinterpret_cast<uint2*>(o) = make_uint2(*reinterpret_cast<const uint32_t*>(&h0), *reinterpret_cast<const uint32_t*>(&h1));
+            *reinterpret_cast<uint2*>(o + KP) = make_uint2(*reinterpret_cast<const uint32_t*>(&l0), *reinterpret_cast<const uint32_t*>(&l1));
+          }
       }
     } else {
       for (int idx = threadIdx.x; idx < LS_ROWS * d.H; idx += LS_THREADS) {
@@ -291,24 +338,27 @@ lstm_seq_fwd_h_kernel(float* gates, const float* __restrict__ whh, float* hbuf, 
     for (int i = 0; i < LS_MAXT; ++i)
 #pragma unroll
       for (int e = 0; e < 4; ++e) acc[i][e] = 0.f;
+    // (the warp's tile count is warp-uniform: one branch per step, no predicates around the .sync instructions)
+    auto product = [&](auto ntw_c) {
+      constexpr int NTW = decltype(ntw_c)::value;
 #pragma unroll 2
-    for (int ks = 0; ks < KS; ++ks) {
-      uint32_t ah[4], al[4], w[LS_MAXT][4];
-      ls_ldsm4(ah, ap + 16 * ks);
-      ls_ldsm4(al, ap + KP + 16 * ks);
+      for (int ks = 0; ks < KS; ++ks) {
+        uint32_t ah[4], al[4], w[NTW > 0 ? NTW : 1][4];
+        ls_ldsm4(ah, ap + 16 * ks);
+        ls_ldsm4(al, ap + KP + 16 * ks);
 #pragma unroll
-      for (int i = 0; i < LS_MAXT; ++i)
-        if (warp + 8 * i < NT) ls_ldsm4(w[i], bp[i] + 16 * ks);
+        for (int i = 0; i < NTW; ++i) ls_ldsm4(w[i], bp[i] + 16 * ks);
 #pragma unroll
-      for (int i = 0; i < LS_MAXT; ++i)
-        if (warp + 8 * i < NT) ls_mma_f16(acc[i], al, w[i][0], w[i][1]);
+        for (int i = 0; i < NTW; ++i) ls_mma_f16(acc[i], al, w[i][0], w[i][1]);
 #pragma unroll
-      for (int i = 0; i < LS_MAXT; ++i)
-        if (warp + 8 * i < NT) ls_mma_f16(acc[i], ah, w[i][2], w[i][3]);
+        for (int i = 0; i < NTW; ++i) ls_mma_f16(acc[i], ah, w[i][2], w[i][3]);
 #pragma unroll
-      for (int i = 0; i < LS_MAXT; ++i)
-        if (warp + 8 * i < NT) ls_mma_f16(acc[i], ah, w[i][0], w[i][1]);
-    }
+        for (int i = 0; i < NTW; ++i) ls_mma_f16(acc[i], ah, w[i][0], w[i][1]);
+      }
+    };
+    if (ntw == 3) product(std::integral_constant<int, 3>{});
+    else if (ntw == 2) product(std::integral_constant<int, 2>{});
+    else if (ntw == 1) product(std::integral_constant<int, 1>{});
     // 3. the four gates of (my_row, unit) meet (see lstm_seq_fwd_kernel)
     float hnew[LS_MAXT], ga[LS_MAXT][4];
 #pragma unroll
