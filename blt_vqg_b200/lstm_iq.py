@@ -281,12 +281,13 @@ class LSTMIQ(nn.Module):
                 ops.lstm_cell_bwd(gates[t], cbuf[t], cbuf[t + 1], dh_run, dov[t] if dov is not None else None, dc, dgates[t], lengths, t)
                 tf.mm(c, dgates[t], pfx + "weight_hh_l0", dh_run, b_t=True, residual=dh_run)
         dg = dgates.view(T * B, 4 * H)
+        dga = tf.act(c, dg, lo=False)   # one split of the gate gradients for the three products that read them
         def weight_grads():   # off the dX chain: side stream, under the input-gradient GEMM and the embedding scatter
-            tf.grad_w(c, dg, hbuf[:T].view(T * B, H), G[pfx + "weight_hh_l0"], G[pfx + "bias_hh_l0"])
-            tf.grad_w(c, dg, e, G[pfx + "weight_ih_l0"], G[pfx + "bias_ih_l0"])
+            tf.grad_w(c, dg, hbuf[:T].view(T * B, H), G[pfx + "weight_hh_l0"], G[pfx + "bias_hh_l0"], dya=dga)
+            tf.grad_w(c, dg, e, G[pfx + "weight_ih_l0"], G[pfx + "bias_ih_l0"], dya=dga, x_cached=True)
         ev = c.mark()
         de = ws.buf(tag + ".de", T * B, H)
-        tf.mm(c, dg, pfx + "weight_ih_l0", de, b_t=True)
+        tf.mm(c, dga, pfx + "weight_ih_l0", de, b_t=True)
         c.on_side(weight_grads, ev)
         ops.dropout_(de, c.in_drop, *c.key(tag + ".indrop"))
         ops.embed_scatter_add(ids_tm, de, G[emb_name], -1)
@@ -450,9 +451,10 @@ class LSTMIQ(nn.Module):
         for tag, ee, dzz, kc, flows in paths:
             dpost = ws.buf("d_mulv." + tag, B, 2 * Z)
             ops.latent_bwd(zeros2z, mulv, ee, dzz, kc, dprior, dpost)
-            tf.grad_w(c, dpost, att, gml, gmlb)
+            dpa = tf.act(c, dpost, lo=False)
+            tf.grad_w(c, dpost, att, gml, gmlb, dya=dpa, x_cached=True)
             d_att = ws.buf("d_att." + tag, B, H)
-            tf.mm(c, dpost, wml, d_att, b_t=True)
+            tf.mm(c, dpa, wml, d_att, b_t=True)
             if flows:
                 d_cat = self._mlp_bwd(c, "att", "answer_attention", d_att, cat)
             else:
@@ -467,7 +469,7 @@ class LSTMIQ(nn.Module):
         d_img_pre = ws.buf("d_img_pre", B, H)
         ops.bn_bwd(d_img, ws["img_pre"], P["encoder_cnn.bn.weight"], ws["bn.mean"], ws["bn.rstd"], d_img_pre,
                    G["encoder_cnn.bn.weight"], G["encoder_cnn.bn.bias"])
-        tf.grad_w(c, d_img_pre, feats, G["encoder_cnn.cnn.fc.weight"], G["encoder_cnn.cnn.fc.bias"])
+        tf.grad_w(c, d_img_pre, feats, G["encoder_cnn.cnn.fc.weight"], G["encoder_cnn.cnn.fc.bias"], x_cached=True)
         return terms
 
 

@@ -164,6 +164,7 @@ def refresh_weight_operands(w, arena, flat):
 
 class Ctx:
     """everything a block schedule needs: parameter / gradient views, workspace, sizes, dropout keys"""
+    _count = 0
 
     def __init__(self, arena, gflat, ws, H, nh, F, E, attn_drop, relu_drop, training, seed, weights):
         self.arena, self.ws = arena, ws
@@ -179,6 +180,8 @@ class Ctx:
         self.site = 0
         self.sm = 148
         self.on_ready = None  # callable(flat_offset): gradients at and after this arena offset are final (parallel.py)
+        Ctx._count += 1
+        self.seed_id = Ctx._count   # identity of this pass: blocks.act(cached=True) only reuses planes made under the same Ctx
 
     def side_stream(self):
         """the side stream paired with the CURRENT stream (the two encoders run on different streams, each gets its own)
