@@ -365,7 +365,9 @@ extern "C" int b200iq_relu_bwd_colsum_f16(const float* dy, const float* y, void*
 extern "C" int b200iq_colsum_add_f16(const void* x_hi, float* out, int M, int N, int ld, void* stream) {
   B200IQ_CHECK_ARG(x_hi && out && M > 0 && N > 0 && ld >= N, "colsum_add_f16: bad args");
   if ((N & 7) == 0 && (ld & 7) == 0 && (((uintptr_t)x_hi) & 15) == 0) {
-    const int cx = ceil_div(N, 256), rpc = max(32, ceil_div(M, max(1, sm_count() * 4 / cx)));
+    // >= 64 rows per CTA: narrow planes (N = 512: 2 column blocks) otherwise get ~590 CTAs of 35 rows and the per-CTA reduction +
+    // 256 atomics dominate (24.3 -> 14.5 us at M = 10240, scripts/gpu_colsum_time.py)
+    const int cx = ceil_div(N, 256), rpc = max(64, ceil_div(M, max(1, sm_count() * 4 / cx)));
     colsum_f16_vec_kernel<<<dim3(cx, ceil_div(M, rpc)), dim3(32, 8), 0, ST>>>((const __half*)x_hi, out, M, N, ld, rpc);
     return launch_status("colsum_add_f16");
   }
