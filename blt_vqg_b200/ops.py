@@ -136,8 +136,13 @@ def gemm2(a, b, out=None, *, planes=None, a_t=False, b_t=False, bias=None, resid
     assert K == Kb, (ah.shape, bh.shape, a_t, b_t)
     three = terms == 3 and a.lo is not None and b.lo is not None and not a_t and not b_t
     if auto_split and not accumulate and residual is None and relu_mask is None and not relu and planes is None:
-        tiles = ((M + 127) // 128) * ((N + 127) // 128)
-        sk = min(148 // tiles, K // 512) if tiles <= 74 else 1
+        # work units of the kernel's tile policy: CTA pairs of 256 x 256 wherever M > 128 and N > 64 (74 pairs), else 128 x 128 CTAs
+        # (the vocabulary dX product, M = 1280, N = 512, K = 15000, is 10 pair tiles: 7 K-splits fill the pairs, 3 left 44 idle)
+        if M > 128 and N > 64:
+            tiles, slots = ((M + 255) // 256) * ((N + 255) // 256), 74
+        else:
+            tiles, slots = ((M + 127) // 128) * ((N + 127) // 128), 148
+        sk = min(slots // tiles, K // 512) if tiles <= slots // 2 else 1
         if sk > 1:
             out.zero_()
             accumulate, split_k = True, sk
