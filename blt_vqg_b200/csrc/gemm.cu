@@ -355,11 +355,13 @@ static int launch_tc(const CUtensorMap& ta, const CUtensorMap& tb, const CUtenso
                      int split, cudaStream_t st) {
   constexpr int STAGES = (CTAS == 2) ? 5 : (BN == 256) ? 3 : 4;
   constexpr int SMEM = STAGES * (BM * 128 + (BN / CTAS) * 128) + EPI_WARPS * 2 * 32 * 128 + 1024;
-  static bool attr_done = false;
+  static int attr_dev = -1;  // the opt-in is per device: redo it when the calling thread's device changes
   auto kern = gemm_tf32_kernel<BN, A_MN, B_MN, STAGES, EPI, CTAS>;
-  if (!attr_done) {
+  int cur_dev = 0;
+  cudaGetDevice(&cur_dev);
+  if (attr_dev != cur_dev) {
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
-    attr_done = true;
+    attr_dev = cur_dev;
   }
   int kblocks = ceil_div(K, BK);
   if (split > kblocks) split = kblocks;

@@ -560,11 +560,13 @@ extern "C" int b200iq_lstm_seq_fwd(float* gates, const float* whh, float* hbuf, 
   B200IQ_CHECK_ARG((((uintptr_t)hbuf) & 15) == 0, "lstm_seq_fwd: hbuf must be 16-byte aligned");
   LstmSeqDims d; size_t smem;
   ls_dims(T, B, H, &d, &smem);
-  static bool attr_done = false;
-  if (!attr_done) {
+  static int attr_dev = -1;  // the opt-in is per device: redo it when the calling thread's device changes
+  int cur_dev = 0;
+  cudaGetDevice(&cur_dev);
+  if (attr_dev != cur_dev) {
     cudaFuncSetAttribute(lstm_seq_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     cudaFuncSetAttribute(lstm_seq_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    attr_done = true;
+    attr_dev = cur_dev;
   }
   const int clusters = (B + LS_ROWS - 1) / LS_ROWS;
   // rounding mode off = the caller keeps unrounded fp32 tensors (fp16-plane scheme): 3-term products, on the fp16 mma.sync kernel
@@ -610,8 +612,10 @@ extern "C" int b200iq_lstm_seq_bwd(const float* gates, const float* cbuf, const 
   B200IQ_CHECK_ARG(b200iq_lstm_seq_supported(H) && d.Hp / 8 <= 8 * LS_MAXTB && smem + 1024 <= 227 * 1024,
                    "lstm_seq_bwd: H=%d does not fit the shared-memory resident slice", H);
   B200IQ_CHECK_ARG((((uintptr_t)workspace) & 15) == 0, "lstm_seq_bwd: workspace must be 16-byte aligned");
-  static bool attr_done = false;
-  if (!attr_done) { cudaFuncSetAttribute(lstm_seq_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); attr_done = true; }
+  static int attr_dev = -1;  // per device, like the forward
+  int cur_dev = 0;
+  cudaGetDevice(&cur_dev);
+  if (attr_dev != cur_dev) { cudaFuncSetAttribute(lstm_seq_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); attr_dev = cur_dev; }
   const int clusters = (B + LS_ROWS - 1) / LS_ROWS;
   lstm_seq_bwd_kernel<<<clusters * LS_CL, LS_THREADS, smem, (cudaStream_t)stream>>>(gates, cbuf, whh, dh_last, d_out, dgates, dh0, dc0,
                                                                                     workspace, lengths, d, LDG, round_mode(), round_mode() ? 0 : 1);
