@@ -718,6 +718,236 @@ __device__ __forceinline__ void att_h_TtX_store(const __half* T, const __half* X
   }
 }
 
+// Precise forward in the same form: scores = Q . K^T and out = W . V both as 3-term fp16 products (hi.hi + lo.hi + hi.lo) with
+// ldmatrix fragments; the post-dropout weights W go from the accumulator layout of the score product straight into the A operand of
+// W . V as two fp16 terms.  (attention_fwd_tc_kernel: the TF32 version that splits every operand in registers at every use.)
+static size_t att_hf_bytes(int nq, int nk, int nt) { return (size_t)2 * ((size_t)ATT_HP * (nq + 2 * nk) + ATT_HZ) + (size_t)16 * nq * nt; }
+
+template <int MT, int NT>
+__global__ void __launch_bounds__(ATT_TC_WARPS * 32)
+attention_fwd_h_kernel(AttnArgs a, AttOut out, int warp_bytes) {
+  constexpr int NP = (NT + 1) / 2;   // 16-key steps
+  pdl_trigger();
+  pdl_wait();
+  const int wid = threadIdx.x >> 5;
+  const int bh = blockIdx.x * ATT_TC_WARPS + wid;
+  if (bh >= a.B * a.nh) return;
+  const int b = bh / a.nh, h = bh - b * a.nh, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3, r8 = lane & 7, mi = lane >> 3;
+  const int nq = a.nq, nk = a.nk;
+  extern __shared__ __align__(16) float att_dyn[];
+  __half* Qh = reinterpret_cast<__half*>(reinterpret_cast<uint8_t*>(att_dyn) + (size_t)wid * warp_bytes);
+  __half* Kh = Qh + nq * ATT_HP;
+  __half* Vh = Kh + nk * ATT_HP;
+  __half* Z = Vh + nk * ATT_HP;      // one row of zeros
+  uint4* dwords = reinterpret_cast<uint4*>(Z + ATT_HZ);   // [nq * NT] dropout words
+  att_stage_h(Qh, a.q + (size_t)b * nq * a.ldq + h * 64, nq, a.ldq, lane);
+  att_stage_h(Kh, a.k + (size_t)b * a.bsk + h * 64, nk, a.ldk, lane);
+  att_stage_h(Vh, a.v + (size_t)b * a.bsv + h * 64, nk, a.ldv, lane);
+  for (int i = lane; i < ATT_HZ / 2; i += 32) reinterpret_cast<uint32_t*>(Z)[i] = 0u;
+  const bool drop = a.drop_p > 0.f;
+  if (drop) {
+    for (int c = lane; c < nq * NT; c += 32) {
+      uint32_t w[4];
+      att_drop_words(a, (size_t)bh * nq + c / NT, c % NT, w);
+      dwords[c] = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+  }
+  uint32_t jvalid = 0u, jpad = 0u;
+#pragma unroll
+  for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+      const int j = 8 * nt + 2 * t + e;
+      if (j < nk) {
+        jvalid |= 1u << (2 * nt + e);
+        if (a.key_ids != nullptr && __ldg(a.key_ids + b * nk + j) == a.pad_id) jpad |= 1u << (2 * nt + e);
+      }
+    }
+  asm volatile("cp.async.wait_group 2;" ::: "memory");
+  __syncwarp();
+  att_convert_h<true>(Qh, nq, lane);
+  asm volatile("cp.async.wait_group 1;" ::: "memory");
+  __syncwarp();
+  att_convert_h<true>(Kh, nk, lane);
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  __syncwarp();
+  att_convert_h<true>(Vh, nk, lane);
+  __syncwarp();
+
+  float S[MT][NT][4];
+#pragma unroll
+  for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) S[mt][nt][e] = 0.f;
+  {
+    const __half* kp[NT]; const __half* klp[NT];
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) {
+      const int r = 8 * nt + r8;
+      const bool ok = r < nk;
+      kp[nt] = (ok ? Kh + r * ATT_HP : Z) + 8 * mi;
+      klp[nt] = (ok ? Kh + r * ATT_HP + ATT_HL : Z) + 8 * mi;
+    }
+    const __half* qp[MT]; const __half* qlp[MT];
+#pragma unroll
+    for (int mt = 0; mt < MT; ++mt) {
+      const int r = 16 * mt + r8 + 8 * (mi & 1);
+      const bool ok = r < nq;
+      qp[mt] = (ok ? Qh + r * ATT_HP : Z) + 8 * (mi >> 1);
+      qlp[mt] = (ok ? Qh + r * ATT_HP + ATT_HL : Z) + 8 * (mi >> 1);
+    }
+#pragma unroll 1
+    for (int k2 = 0; k2 < 2; ++k2) {
+      uint32_t kh[NT][4], kl[NT][4];
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt) { ldsm4(kh[nt], kp[nt] + 32 * k2); ldsm4(kl[nt], klp[nt] + 32 * k2); }
+#pragma unroll
+      for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+        for (int kq = 0; kq < 2; ++kq) {
+          uint32_t qh[4], ql[4];
+          ldsm4(qh, qp[mt] + 32 * k2 + 16 * kq);
+          ldsm4(ql, qlp[mt] + 32 * k2 + 16 * kq);
+#pragma unroll
+          for (int nt = 0; nt < NT; ++nt) mma_f16(S[mt][nt], ql[0], ql[1], ql[2], ql[3], kh[nt][2 * kq], kh[nt][2 * kq + 1]);
+#pragma unroll
+          for (int nt = 0; nt < NT; ++nt) mma_f16(S[mt][nt], qh[0], qh[1], qh[2], qh[3], kl[nt][2 * kq], kl[nt][2 * kq + 1]);
+#pragma unroll
+          for (int nt = 0; nt < NT; ++nt) mma_f16(S[mt][nt], qh[0], qh[1], qh[2], qh[3], kh[nt][2 * kq], kh[nt][2 * kq + 1]);
+        }
+    }
+  }
+  // softmax, dropout; the weights as two fp16 terms in A-fragment order
+  const uint32_t thr = dropout_threshold(a.drop_p);
+  const float inv_keep = 1.f / (1.f - a.drop_p);
+  const int gd = g - 2 * t;
+  uint32_t wh[MT][2 * NP][2], wl[MT][2 * NP][2];
+  __syncwarp();
+#pragma unroll
+  for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+    for (int hh = 0; hh < 2; ++hh) {
+      const int i = 16 * mt + g + 8 * hh;
+      const bool row_ok = i < nq;
+      float p[NT][2];
+      float mx = -3.0e38f;
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const bool m = (a.causal && (8 * nt + e - 16 * mt - 8 * hh) > gd) || ((jpad >> (2 * nt + e)) & 1u);
+          float sv = m ? -1e18f : S[mt][nt][2 * hh + e] * a.scale;
+          sv = ((jvalid >> (2 * nt + e)) & 1u) ? sv : -3.0e38f;
+          p[nt][e] = sv;
+          mx = fmaxf(mx, sv);
+        }
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+      float sum = 0.f;
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const float pe = ((jvalid >> (2 * nt + e)) & 1u) ? __expf(p[nt][e] - mx) : 0.f;
+          p[nt][e] = pe;
+          sum += pe;
+        }
+      sum += __shfl_xor_sync(0xffffffffu, sum, 1);
+      sum += __shfl_xor_sync(0xffffffffu, sum, 2);
+      const float inv = 1.f / sum;
+#pragma unroll
+      for (int nt = 0; nt < 2 * NP; ++nt) {
+        float w0 = 0.f, w1 = 0.f;
+        if (nt < NT) {
+          uint32_t w = 0xFFFFFFFFu;
+          if (drop && row_ok) w = reinterpret_cast<const uint32_t*>(dwords + (i * NT + nt))[t];
+          const float k0 = (!drop || ((w & 0xFFFFu) >= thr)) ? (drop ? inv_keep : 1.f) : 0.f;
+          const float k1 = (!drop || ((w >> 16) >= thr)) ? (drop ? inv_keep : 1.f) : 0.f;
+          w0 = p[nt][0] * inv * k0;
+          w1 = p[nt][1] * inv * k1;
+        }
+        const __half2 hv = __floats2half2_rn(w0, w1);
+        const float2 hf = __half22float2(hv);
+        wh[mt][nt][hh] = *reinterpret_cast<const uint32_t*>(&hv);
+        wl[mt][nt][hh] = pack_h2(w0 - hf.x, w1 - hf.y);
+      }
+    }
+  // out = W . V (3-term); V rows as a row-major B operand (.trans), hi and lo half-rows
+  {
+    const __half* vr[NP]; const __half* vlr[NP];
+#pragma unroll
+    for (int j = 0; j < NP; ++j) {
+      const int r = 16 * j + r8 + 8 * (mi & 1);
+      const bool ok = r < nk;
+      vr[j] = (ok ? Vh + r * ATT_HP : Z) + 8 * (mi >> 1);
+      vlr[j] = (ok ? Vh + r * ATT_HP + ATT_HL : Z) + 8 * (mi >> 1);
+    }
+    const size_t obase = (size_t)b * nq * out.ld + h * 64;
+#pragma unroll 1
+    for (int cq = 0; cq < 2; ++cq) {
+      float acc[MT][4][4];
+#pragma unroll
+      for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+#pragma unroll
+          for (int e = 0; e < 4; ++e) acc[mt][u][e] = 0.f;
+#pragma unroll
+      for (int j = 0; j < NP; ++j) {
+        uint32_t vb[2][4], vlb[2][4];
+#pragma unroll
+        for (int x = 0; x < 2; ++x) { ldsm4t(vb[x], vr[j] + 32 * cq + 16 * x); ldsm4t(vlb[x], vlr[j] + 32 * cq + 16 * x); }
+#pragma unroll
+        for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+          for (int x = 0; x < 2; ++x) {
+            mma_f16(acc[mt][2 * x], wl[mt][2 * j][0], wl[mt][2 * j][1], wl[mt][2 * j + 1][0], wl[mt][2 * j + 1][1], vb[x][0], vb[x][1]);
+            mma_f16(acc[mt][2 * x + 1], wl[mt][2 * j][0], wl[mt][2 * j][1], wl[mt][2 * j + 1][0], wl[mt][2 * j + 1][1], vb[x][2], vb[x][3]);
+          }
+#pragma unroll
+        for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+          for (int x = 0; x < 2; ++x) {
+            mma_f16(acc[mt][2 * x], wh[mt][2 * j][0], wh[mt][2 * j][1], wh[mt][2 * j + 1][0], wh[mt][2 * j + 1][1], vlb[x][0], vlb[x][1]);
+            mma_f16(acc[mt][2 * x + 1], wh[mt][2 * j][0], wh[mt][2 * j][1], wh[mt][2 * j + 1][0], wh[mt][2 * j + 1][1], vlb[x][2], vlb[x][3]);
+          }
+#pragma unroll
+        for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+          for (int x = 0; x < 2; ++x) {
+            mma_f16(acc[mt][2 * x], wh[mt][2 * j][0], wh[mt][2 * j][1], wh[mt][2 * j + 1][0], wh[mt][2 * j + 1][1], vb[x][0], vb[x][1]);
+            mma_f16(acc[mt][2 * x + 1], wh[mt][2 * j][0], wh[mt][2 * j][1], wh[mt][2 * j + 1][0], wh[mt][2 * j + 1][1], vb[x][2], vb[x][3]);
+          }
+      }
+#pragma unroll
+      for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+          const int row = 16 * mt + g + 8 * hh;
+          if (row < nq) {
+            const size_t o = obase + (size_t)row * out.ld + 32 * cq + 2 * t;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const float v0 = acc[mt][u][2 * hh], v1 = acc[mt][u][2 * hh + 1];
+              if (out.hi) {
+                const __half2 hv = __floats2half2_rn(v0, v1);
+                *reinterpret_cast<uint32_t*>(out.hi + o + 8 * u) = *reinterpret_cast<const uint32_t*>(&hv);
+                if (out.lo) {
+                  const float2 hf = __half22float2(hv);
+                  *reinterpret_cast<uint32_t*>(out.lo + o + 8 * u) = pack_h2(v0 - hf.x, v1 - hf.y);
+                }
+              } else {
+                *reinterpret_cast<float2*>(out.f32 + o + 8 * u) = make_float2(rnd(v0, a.rn), rnd(v1, a.rn));
+              }
+            }
+          }
+        }
+    }
+  }
+}
+
 template <int MT, int NT>
 __global__ void __launch_bounds__(ATT_TC_WARPS * 32)
 attention_bwd_h_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, AttOut dq, AttOut dk, AttOut dv, int warp_bytes) {
@@ -1231,6 +1461,21 @@ static int attention_fwd_impl(const B200iqAttention* p, const AttOut& out, void*
   {
     const void* ptrs[] = {p->q, p->k, p->v};
     const int lds[] = {p->ldq, p->ldk, p->ldv};
+    // B200IQ_ATT_FWD_H=0: the TF32 register kernel for the precise mode too (A/B switch)
+    static const bool use_h = [] { const char* e = getenv("B200IQ_ATT_FWD_H"); return !(e && e[0] == '0'); }();
+    if (use_h && p->precise && tc_ok(p, ptrs, 3, lds, 3, &out, 1)) {
+      const int mt = a.nq > 16 ? 2 : 1, nt = (a.nk + 7) / 8, grid = (a.B * a.nh + ATT_TC_WARPS - 1) / ATT_TC_WARPS;
+      const int wbytes = (int)((att_hf_bytes(a.nq, a.nk, nt) + 15) & ~(size_t)15);
+      const size_t tsm = (size_t)ATT_TC_WARPS * wbytes;
+#define CALL(M_, N_) \
+  do { \
+    if (tsm > 48 * 1024) cudaFuncSetAttribute(attention_fwd_h_kernel<M_, N_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm); \
+    launch_dep(attention_fwd_h_kernel<M_, N_>, dim3(grid), dim3(ATT_TC_WARPS * 32), tsm, (cudaStream_t)stream, a, out, wbytes); \
+  } while (0)
+      B200IQ_ATT_DISPATCH(mt, nt, CALL);
+#undef CALL
+      return launch_status("attention_fwd_h");
+    }
     if (tc_ok(p, ptrs, 3, lds, 3, &out, 1)) {
       const int mt = a.nq > 16 ? 2 : 1, nt = (a.nk + 7) / 8, grid = (a.B * a.nh + ATT_TC_WARPS - 1) / ATT_TC_WARPS;
       const size_t tsm = sizeof(float) * ATT_TC_WARPS * (size_t)(a.nq + 2 * a.nk) * ATT_SP;

@@ -134,7 +134,7 @@ def test_attention_tensor_core_path(ops, nq, nk, causal, drop):
                                              (17, 9, False), (9, 30, False), (64, 64, True)])
 @pytest.mark.parametrize("drop", [0.0, 0.3])
 def test_attention_backward_into_fp16_planes(ops, nq, nk, causal, drop):
-    """b200iq_attention_bwd_f16 (precise mode: unrounded fp32 q / k / v / dO in, gradients out as fp16 hi planes — the fp16
+    """b200iq_attention_fwd in precise mode (fp16 hi + lo planes out) and b200iq_attention_bwd_f16 (precise mode: unrounded fp32 q / k / v / dO in, gradients out as fp16 hi planes — the fp16
     mma.sync kernel for n <= 32, the row-block kernel above that) against fp64 autograd (drop = 0) and against the exact CUDA-core
     kernels under the same Philox key (drop > 0: same mask by construction).  Bar 2e-3: 11-bit operands of the single-pass
     backward products plus the 2^-12 rounding of the fp16 result."""
@@ -150,6 +150,14 @@ def test_attention_backward_into_fp16_planes(ops, nq, nk, causal, drop):
     if nk > 1:
         ids[0, 0] = 0
     key = (drop, 4321, 11 << 40)
+    # the precise forward (3-term products) into hi + lo planes against the exact kernels' fp32 output under the same key
+    act = ops.Act(hi=torch.full((B * nq, H), float("nan"), device="cuda", dtype=torch.float16),
+                  lo=torch.full((B * nq, H), float("nan"), device="cuda", dtype=torch.float16))
+    ops.attention_fwd(q, k, v, act, ids, 0, causal, B, nh, nq, nk, d, *key)
+    o32 = torch.empty(B * nq, H, device="cuda")
+    ops.attention_fwd(q, k, v, o32, ids, 0, causal, B, nh, nq, nk, d, *key)
+    assert torch.isfinite(act.hi).all() and torch.isfinite(act.lo).all()
+    assert rel(act.hi.double() + act.lo.double(), o32) < 5e-6
     dq, dkv = torch.full((B * nq, H), float("nan"), device="cuda", dtype=torch.float16), torch.full((B * nk, 2 * H), float("nan"), device="cuda", dtype=torch.float16)
     ops.attention_bwd(q, k, v, do, dq, dkv[:, :H], dkv[:, H:], ids, 0, causal, B, nh, nq, nk, d, *key)
     eq, ekv = torch.empty(B * nq, H, device="cuda"), torch.empty(B * nk, 2 * H, device="cuda")
