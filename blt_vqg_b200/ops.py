@@ -174,7 +174,15 @@ def gemm2(a, b, out=None, *, planes=None, a_t=False, b_t=False, bias=None, resid
         e1.record()
         nt = 3 if three else 1
         by = 2.0 * nt * (M * K + N * K) + (4.0 * M * N if out is not None else 0.0) + (2.0 * M * N * (2 if pl is not None else 1) if ph is not None else 0.0)
-        GEMM_TRACE.append((e0, e1, 2.0 * M * N * K, by, (M, N, K, flags, split_k, nt)))
+        # shared-memory fill of the launch (what the TMA producer pulls from L2): a CTA pair stages (256 + 256) x 64 halves per
+        # k-block and plane (single CTAs: (128 + 128) x 64 per 128 x 128 tile), hi and lo planes for the 3-term product
+        if M > 128 and N > 64:
+            bn = 128 if N <= 128 else 256
+            fill = ((M + 255) // 256) * ((N + bn - 1) // bn) * ((K + 63) // 64) * (256 + bn) * 64 * 2.0
+        else:
+            fill = ((M + 127) // 128) * ((N + 127) // 128) * ((K + 63) // 64) * 256 * 64 * 2.0
+        fill *= 2 if three else 1
+        GEMM_TRACE.append((e0, e1, 2.0 * M * N * K, by, (M, N, K, flags, split_k, nt), fill))
     else:
         L.check(L.lib().b200iq_gemm_f16(C.byref(p), L.stream_ptr()), "b200iq_gemm_f16")
     return out if out is not None else planes
