@@ -65,7 +65,7 @@ __global__ void __launch_bounds__(F16_THREADS, 1)
 gemm_f16_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__ CUtensorMap tmAl,
                 const __grid_constant__ CUtensorMap tmBh, const __grid_constant__ CUtensorMap tmBl,
                 const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmR, F16Epi epi,
-                int m_tiles, int n_tiles, int splits, int kblocks_total, int kblocks_per_split, int fast_epi) {
+                int m_tiles, int n_tiles, int splits, int kblocks_total, int kblocks_per_split, int fast_epi, int gate_map) {
   constexpr int BNL = BN / CTAS;  // rows of B this CTA stages (the pair's MMA reads N/2 from each CTA)
   constexpr int NPL = TERMS == 3 ? 2 : 1;
   constexpr int A_BYTES = FBM * 128, B_BYTES = BNL * 128, STAGE_BYTES = NPL * (A_BYTES + B_BYTES);
@@ -75,7 +75,7 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant_
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   uint8_t* stg_base = smem + STAGES * STAGE_BYTES;  // [8 epilogue warps][NBUF][4096 B], 1024-aligned
   __shared__ uint64_t full_bar[STAGES], empty_bar[STAGES], tfull_bar[2], tempty_bar[2];
-  __shared__ uint64_t gbar[EPI == 1 ? F16_EPI_WARPS : 1][2];
+  __shared__ uint64_t gbar[EPI == 1 ? F16_EPI_WARPS : 1][4];
   __shared__ uint32_t tmem_base_s;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -92,11 +92,12 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant_
       asm volatile("prefetch.tensormap [%0];" ::"l"((uint64_t)&tmBl) : "memory");
     }
     if (epi.C && fast_epi) asm volatile("prefetch.tensormap [%0];" ::"l"((uint64_t)&tmC) : "memory");
+    if (gate_map) asm volatile("prefetch.tensormap [%0];" ::"l"((uint64_t)&tmR) : "memory");
   }
   if (threadIdx.x == 0) {
     for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
     for (int a = 0; a < 2; ++a) { mbar_init(&tfull_bar[a], 1); mbar_init(&tempty_bar[a], F16_EPI_WARPS * CTAS); }
-    if (EPI == 1) for (int a = 0; a < F16_EPI_WARPS; ++a) { mbar_init(&gbar[a][0], 1); mbar_init(&gbar[a][1], 1); }
+    if (EPI == 1) for (int a = 0; a < F16_EPI_WARPS; ++a) for (int k = 0; k < 4; ++k) mbar_init(&gbar[a][k], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 2) {
@@ -213,6 +214,19 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant_
         tma_load_2d(stg + (ch % NBUF) * F16_STG_BYTES, &tmR, col0, row0, gb);
       }
     };
+    // EPI 1 + RELU_MASK with a plane-only result (the FFN's dX through its first relu): the 32 x 32-half gate tile of a chunk comes
+    // by TMA (64-byte swizzle) into one of three 2 KB slots behind the hi-plane transpose area, two chunks ahead.  Read
+    // straight from global memory, every lane pulls 64 bytes of a different row: 128 L1 wavefronts per chunk for 2 KB, and with 8
+    // epilogue warps that alone takes as long as the tile's MMAs (51 us against 27 us without a gate at M = 10240, N = 2048, K = 512)
+    const bool gate_tma = gate && fast_epi && gate_map && NBUF == 2 && epi.C == nullptr && epi.Clo == nullptr;
+    auto fetch_g = [&](int row0, int col0, uint32_t ch) {
+      if (lane == 0) {
+        fence_async_smem();   // the generic reads of this half-buffer (two chunks ago) are ordered before the async write
+        uint64_t* gb = &gbar[EPI == 1 ? warp - 2 : 0][ch % 3];
+        mbar_expect_tx(gb, 2048);
+        tma_load_2d(stg + 2048 * (1 + ch % 3), &tmR, col0, row0, gb);
+      }
+    };
     for (int w = w_first; w < total; w += w_step, ++ti) {
       const int z = w / tiles, r = w - z * tiles, mt = r / n_tiles, nt = r - mt * n_tiles;
       const int m0 = (mt * CTAS + rank) * FBM, n0 = nt * BN;
@@ -220,6 +234,11 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant_
       const int row0 = m0 + q * 32, row = row0 + lane;
       const bool add_bias = (z == 0);
       if (has_r && fast_epi && row0 < epi.M && n0 + chalf * CHUNKS * 32 < epi.N) fetch_r(row0, n0 + chalf * CHUNKS * 32, chunk);
+      if (gate_tma && row0 < epi.M) {
+        const int c0 = n0 + chalf * CHUNKS * 32;
+        if (c0 < epi.N) fetch_g(row0, c0, chunk);
+        if (CHUNKS > 1 && c0 + 32 < epi.N) fetch_g(row0, c0 + 32, chunk + 1);
+      }
       mbar_wait(&tfull_bar[acc], aph);
       tc_fence_after();
 #pragma unroll 1
@@ -249,7 +268,7 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant_
         uint4 gq[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) gq[j] = make_uint4(0u, 0u, 0u, 0u);
-        if (gate && fast_epi && row < epi.M) {
+        if (gate && fast_epi && !gate_tma && row < epi.M) {
           const uint4* gp = reinterpret_cast<const uint4*>(epi.gate + (size_t)row * epi.ldg + col0);
 #pragma unroll
           for (int j = 0; j < 4; ++j) if (col0 + 8 * j < epi.N) gq[j] = __ldg(gp + j);
@@ -257,8 +276,17 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant_
         uint32_t rr[32];
         tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN + c * 32, rr);
         if (row0 >= epi.M) continue;  // warp-uniform: nothing of this quadrant is inside the matrix
+        if (gate_tma) {
+          mbar_wait(&gbar[EPI == 1 ? warp - 2 : 0][chunk % 3], (chunk / 3) & 1);   // this chunk's gate tile has landed
+          const uint4* gp = reinterpret_cast<const uint4*>(stg + 2048 * (1 + chunk % 3) + lane * 64);
+          const int sw = (lane >> 1) & 3;   // 64-byte swizzle: 16-byte piece j of row r sits at piece j ^ ((r >> 1) & 3)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) gq[j] = gp[j ^ sw];
+          __syncwarp();
+          if (c + 2 < (chalf + 1) * CHUNKS && col0 + 64 < epi.N) fetch_g(row0, col0 + 64, chunk + 2);   // slot of chunk - 1: read
+        }
         if (fast_epi) {
-          uint8_t* buf = stg + (chunk % NBUF) * F16_STG_BYTES;
+          uint8_t* buf = gate_tma ? stg : stg + (chunk % NBUF) * F16_STG_BYTES;
           if (has_r) {
             mbar_wait(&gbar[EPI == 1 ? warp - 2 : 0][chunk & 1], (chunk >> 1) & 1);  // the residual tile has landed
           } else {
@@ -267,6 +295,7 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant_
           }
           uint32_t keep[4] = {0u, 0u, 0u, 0u};
           const uint32_t* gw = &gq[0].x;
+          const bool gate_packed = gate && epi.C == nullptr && epi.Clo == nullptr;
           // ---- epilogue math, in place in rr[]
 #pragma unroll
           for (int j = 0; j < 32; j += 4) {
@@ -279,7 +308,7 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant_
 #pragma unroll
             for (int t = 0; t < 4; ++t) {
               float x = __uint_as_float(rr[j + t]) * epi.alpha + ba[t] + ga[t];
-              if (gate) {
+              if (gate && !gate_packed) {
                 const uint32_t hw = gw[(j + t) >> 1];
                 x = half_bits_positive((j + t) & 1 ? (hw >> 16) : (hw & 0xFFFFu)) ? x : 0.f;
               }
@@ -297,6 +326,9 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant_
               const float a = __uint_as_float(rr[2 * j]), b = __uint_as_float(rr[2 * j + 1]);
               const __half2 h = __floats2half2_rn(a, b);
               hp[j] = *reinterpret_cast<const uint32_t*>(&h);
+              // hi-plane-only result: the gate is applied to the packed pair (one compare + one AND per two elements instead of
+              // five instructions per element on the fp32 values; these epilogues are instruction-bound)
+              if (gate_packed) hp[j] &= __hgt2_mask(*reinterpret_cast<const __half2*>(&gw[j]), __float2half2_rn(0.f));
               const float2 hf = __half22float2(h);
               const __half2 l = __floats2half2_rn(a - hf.x, b - hf.y);
               lp[j] = *reinterpret_cast<const uint32_t*>(&l);
@@ -406,10 +438,24 @@ static int make_map_f32_tile(CUtensorMap* tm, const float* base, int rows, int c
   return 0;
 }
 
+// 32 rows x 32 halves of an fp16 plane, 64-byte swizzle (the relu gate tile of one epilogue chunk)
+static int make_map_f16_gate(CUtensorMap* tm, const void* base, int rows, int cols, int ld) {
+  EncodeTiledFn enc = get_encode();
+  B200IQ_CHECK_ARG(enc, "cuTensorMapEncodeTiled entry point not available");
+  cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t gstr[1] = {(cuuint64_t)ld * 2};
+  cuuint32_t box[2] = {32, 32};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, (void*)base, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  B200IQ_CHECK_ARG(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled (gate tile) failed (%d) rows=%d cols=%d ld=%d", (int)r, rows, cols, ld);
+  return 0;
+}
+
 struct F16Maps { CUtensorMap ah, al, bh, bl, c, r; };
 
 template <int BN, bool A_MN, bool B_MN, int TERMS, int EPI, int CTAS>
-static int launch_f16(const F16Maps& m, int fast_epi, const F16Epi& e, int K, int split, cudaStream_t st) {
+static int launch_f16(const F16Maps& m, int fast_epi, int gate_map, const F16Epi& e, int K, int split, cudaStream_t st) {
   constexpr int NPL = TERMS == 3 ? 2 : 1;
   constexpr int STAGE = NPL * (FBM * 128 + (BN / CTAS) * 128);
   constexpr int NBUF = (TERMS == 3 && STAGE > 49152) ? 1 : 2;
@@ -449,7 +495,7 @@ static int launch_f16(const F16Maps& m, int fast_epi, const F16Epi& e, int K, in
     ++na;
   }
   cfg.attrs = at; cfg.numAttrs = na;
-  cudaError_t err = cudaLaunchKernelEx(&cfg, kern, m.ah, m.al, m.bh, m.bl, m.c, m.r, e, m_tiles, n_tiles, split, kblocks, per, fast_epi);
+  cudaError_t err = cudaLaunchKernelEx(&cfg, kern, m.ah, m.al, m.bh, m.bl, m.c, m.r, e, m_tiles, n_tiles, split, kblocks, per, fast_epi, gate_map);
   if (err != cudaSuccess) { set_error("gemm_f16_kernel: %s", cudaGetErrorString(err)); return (int)err; }
   return launch_status("gemm_f16_kernel");
 }
@@ -531,9 +577,16 @@ extern "C" int b200iq_gemm_f16(const B200iqGemmF16* p, void* stream) {
   }
   if (fast && p->C) { rc = make_map_f32_tile(&m.c, p->C, p->M, p->N, p->ldc); if (rc) return rc; }
   if (fast && (f & B200IQ_GEMM_RESIDUAL)) { rc = make_map_f32_tile(&m.r, p->residual, p->M, p->N, p->ldr); if (rc) return rc; }
+  // gate tiles by TMA (RESIDUAL and RELU_MASK are exclusive, so the map slot is free): B200IQ_F16_GATE_TMA=0 keeps the per-lane loads
+  static const bool gate_tma_on = [] { const char* v = getenv("B200IQ_F16_GATE_TMA"); return !(v && v[0] == '0'); }();
+  int gm = 0;
+  if (fast && gate_tma_on && (f & B200IQ_GEMM_RELU_MASK) && !p->C && !p->C_lo) {
+    rc = make_map_f16_gate(&m.r, p->gate, p->M, p->N, p->ldg); if (rc) return rc;
+    gm = 1;
+  }
   const int fe = fast ? 1 : 0;
   const int epi_mode = (f & B200IQ_GEMM_DROPOUT) ? 2 : (f & (B200IQ_GEMM_RESIDUAL | B200IQ_GEMM_RELU_MASK)) ? 1 : 0;
-#define F16_GO(BN_, AM_, BM_, T_, E_, C_) return launch_f16<BN_, AM_, BM_, T_, E_, C_>(m, fe, e, p->K, split, st)
+#define F16_GO(BN_, AM_, BM_, T_, E_, C_) return launch_f16<BN_, AM_, BM_, T_, E_, C_>(m, fe, gm, e, p->K, split, st)
 #define F16_TILE(AM_, BM_, T_, E_) do { if (pair && pair_bn == 256) F16_GO(256, AM_, BM_, T_, E_, 2); else if (pair) F16_GO(128, AM_, BM_, T_, E_, 2); else F16_GO(128, AM_, BM_, T_, E_, 1); } while (0)
   if (terms == 3) {
     if (epi_mode == 2) F16_TILE(false, false, 3, 2);
