@@ -297,6 +297,9 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant_
           const uint32_t* gw = &gq[0].x;
           const bool gate_packed = gate && epi.C == nullptr && epi.Clo == nullptr;
           // ---- epilogue math, in place in rr[]
+          // (a plain product — no bias, residual, gate on fp32 values, relu, dropout, alpha — leaves the accumulators as they are)
+          const bool plain = !bias_on && !has_r && !(gate && !gate_packed) && !relu && !drop && epi.alpha == 1.f;
+          if (!plain)
 #pragma unroll
           for (int j = 0; j < 32; j += 4) {
             const float4 bb = bias4[j >> 2];
@@ -329,9 +332,12 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant_
               // hi-plane-only result: the gate is applied to the packed pair (one compare + one AND per two elements instead of
               // five instructions per element on the fp32 values; these epilogues are instruction-bound)
               if (gate_packed) hp[j] &= __hgt2_mask(*reinterpret_cast<const __half2*>(&gw[j]), __float2half2_rn(0.f));
-              const float2 hf = __half22float2(h);
-              const __half2 l = __floats2half2_rn(a - hf.x, b - hf.y);
-              lp[j] = *reinterpret_cast<const uint32_t*>(&l);
+              lp[j] = 0u;
+              if (epi.Clo) {   // warp-uniform: hi-only planes (every backward operand) skip the remainder's five instructions per pair
+                const float2 hf = __half22float2(h);
+                const __half2 l = __floats2half2_rn(a - hf.x, b - hf.y);
+                lp[j] = *reinterpret_cast<const uint32_t*>(&l);
+              }
             }
             const int sw = (lane >> 1) & 3;
 #pragma unroll
