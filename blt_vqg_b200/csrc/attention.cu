@@ -65,6 +65,7 @@ struct AttnArgs {
   int rn;  // round outputs to TF32
   int dq2; // backward: dQ = (dS + dS_lo) . K, dS as two TF32 terms (B200IQ_ATT_DQ2, default 1)
   size_t bsk, bsv;  // elements between consecutive samples' K / V blocks (nk*ldk, nk*ldv unless reading a KV cache)
+  const __half *ql, *kl, *vl;  // planes_in: q / k / v above are fp16 hi planes (cast), these their lo planes; ld* in halves
 };
 
 // The attention-dropout mask: the 8 keys j = 8c .. 8c+7 of score row `row` (= (sample*heads + head)*nq + i) share ONE call of
@@ -606,7 +607,9 @@ static constexpr int ATT_HP = 136;  // halves per row of a 64-column tile (272 B
 static constexpr int ATT_HL = 64;   // the lo half-row starts 64 halves into the row
 static constexpr int ATT_HS = 40;   // halves per row of a score tile (<= 32 keys; 80 B: likewise conflict-free)
 static constexpr int ATT_HZ = 72;   // halves of the shared row of zeros
-static size_t att_h_bytes(int nq, int nk) { return (size_t)2 * ((size_t)ATT_HP * (2 * nq + 2 * nk) + ATT_HZ + (size_t)ATT_HS * 2 * nq); }
+static size_t att_h_bytes(int nq, int nk, bool planes = false) {
+  return (size_t)2 * ((size_t)ATT_HP * (nq + nk) + (size_t)(planes ? ATT_HZ : ATT_HP) * (nq + nk) + ATT_HZ + (size_t)ATT_HS * 2 * nq);
+}
 
 __device__ __forceinline__ void ldsm4(uint32_t (&r)[4], const __half* p) {
   asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
@@ -632,6 +635,20 @@ __device__ __forceinline__ void att_stage_h(__half* tile, const float* __restric
   const float* sp = src + (size_t)r0 * ld + 4 * c4;
   const size_t step = (size_t)2 * ld;
   for (int r = r0; r < rows; r += 2, d += 4 * ATT_HP, sp += step)
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(sp) : "memory");
+  asm volatile("cp.async.commit_group;" ::: "memory");
+}
+// planes_in: rows of an fp16 hi plane (and lo plane) straight into the tile's half-rows — 8 pieces of 16 bytes per half-row
+template <bool LO>
+__device__ __forceinline__ void att_stage_p(__half* tile, int pitch, const __half* __restrict__ hi, const __half* __restrict__ lo,
+                                            int rows, int ld, int lane) {
+  constexpr int PPR = LO ? 16 : 8;   // pieces per row
+  const int r0 = lane / PPR, pc = lane % PPR;
+  const __half* sp = (LO && pc >= 8 ? lo : hi) + (size_t)r0 * ld + 8 * (pc & 7);
+  uint32_t d = (uint32_t)__cvta_generic_to_shared(tile + r0 * pitch + (LO && pc >= 8 ? ATT_HL : 0) + 8 * (pc & 7));
+  constexpr int RS = 32 / PPR;       // rows per warp pass
+  const size_t step = (size_t)RS * ld;
+  for (int r = r0; r < rows; r += RS, d += 2 * RS * pitch, sp += step)
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(sp) : "memory");
   asm volatile("cp.async.commit_group;" ::: "memory");
 }
@@ -662,9 +679,9 @@ __device__ __forceinline__ void att_convert_h(__half* tile, int rows, int lane) 
 }
 
 // out[16mj + .., :64] (rows < nj) = T^T . X: T = score tile [ni][ATT_HS] (rows = queries, read transposed through ldmatrix.trans),
-// X = [ni][ATT_HP] tile (queries x 64); Z = the row of zeros.  MT = 16-query steps, NP = 16-key output blocks.
+// X = [ni][xp] tile (queries x 64, row pitch xp halves); Z = the row of zeros.  MT = 16-query steps, NP = 16-key output blocks.
 template <int MT, int NP>
-__device__ __forceinline__ void att_h_TtX_store(const __half* T, const __half* X, const __half* Z, int ni, const AttOut& out, int nj, int lane) {
+__device__ __forceinline__ void att_h_TtX_store(const __half* T, const __half* X, int xp, const __half* Z, int ni, const AttOut& out, int nj, int lane) {
   const int g = lane >> 2, t = lane & 3, r8 = lane & 7, mi = lane >> 3;
   // per-lane fragment rows (query index = the reduction index of both operands)
   const __half* xrow[MT];
@@ -672,7 +689,7 @@ __device__ __forceinline__ void att_h_TtX_store(const __half* T, const __half* X
 #pragma unroll
   for (int ks = 0; ks < MT; ++ks) {
     const int xr = 16 * ks + r8 + 8 * (mi & 1), tr = 16 * ks + r8 + 8 * (mi >> 1);
-    xrow[ks] = (xr < ni ? X + xr * ATT_HP : Z) + 8 * (mi >> 1);
+    xrow[ks] = (xr < ni ? X + xr * xp : Z) + 8 * (mi >> 1);
     trow[ks] = (tr < ni ? T + tr * ATT_HS : Z) + 8 * (mi & 1);
   }
   __half* orow[NP][2];
@@ -723,7 +740,7 @@ __device__ __forceinline__ void att_h_TtX_store(const __half* T, const __half* X
 // W . V as two fp16 terms.  (attention_fwd_tc_kernel: the TF32 version that splits every operand in registers at every use.)
 static size_t att_hf_bytes(int nq, int nk, int nt) { return (size_t)2 * ((size_t)ATT_HP * (nq + 2 * nk) + ATT_HZ) + (size_t)16 * nq * nt; }
 
-template <int MT, int NT>
+template <int MT, int NT, bool PLANES>
 __global__ void __launch_bounds__(ATT_TC_WARPS * 32)
 attention_fwd_h_kernel(AttnArgs a, AttOut out, int warp_bytes) {
   constexpr int NP = (NT + 1) / 2;   // 16-key steps
@@ -740,9 +757,16 @@ attention_fwd_h_kernel(AttnArgs a, AttOut out, int warp_bytes) {
   __half* Vh = Kh + nk * ATT_HP;
   __half* Z = Vh + nk * ATT_HP;      // one row of zeros
   uint4* dwords = reinterpret_cast<uint4*>(Z + ATT_HZ);   // [nq * NT] dropout words
-  att_stage_h(Qh, a.q + (size_t)b * nq * a.ldq + h * 64, nq, a.ldq, lane);
-  att_stage_h(Kh, a.k + (size_t)b * a.bsk + h * 64, nk, a.ldk, lane);
-  att_stage_h(Vh, a.v + (size_t)b * a.bsv + h * 64, nk, a.ldv, lane);
+  if (PLANES) {   // the projections' fp16 planes: half-rows land where the conversion would have put them
+    const size_t oq = (size_t)b * nq * a.ldq + h * 64, ok = (size_t)b * a.bsk + h * 64, ov = (size_t)b * a.bsv + h * 64;
+    att_stage_p<true>(Qh, ATT_HP, reinterpret_cast<const __half*>(a.q) + oq, a.ql + oq, nq, a.ldq, lane);
+    att_stage_p<true>(Kh, ATT_HP, reinterpret_cast<const __half*>(a.k) + ok, a.kl + ok, nk, a.ldk, lane);
+    att_stage_p<true>(Vh, ATT_HP, reinterpret_cast<const __half*>(a.v) + ov, a.vl + ov, nk, a.ldv, lane);
+  } else {
+    att_stage_h(Qh, a.q + (size_t)b * nq * a.ldq + h * 64, nq, a.ldq, lane);
+    att_stage_h(Kh, a.k + (size_t)b * a.bsk + h * 64, nk, a.ldk, lane);
+    att_stage_h(Vh, a.v + (size_t)b * a.bsv + h * 64, nk, a.ldv, lane);
+  }
   for (int i = lane; i < ATT_HZ / 2; i += 32) reinterpret_cast<uint32_t*>(Z)[i] = 0u;
   const bool drop = a.drop_p > 0.f;
   if (drop) {
@@ -763,15 +787,19 @@ attention_fwd_h_kernel(AttnArgs a, AttOut out, int warp_bytes) {
         if (a.key_ids != nullptr && __ldg(a.key_ids + b * nk + j) == a.pad_id) jpad |= 1u << (2 * nt + e);
       }
     }
-  asm volatile("cp.async.wait_group 2;" ::: "memory");
-  __syncwarp();
-  att_convert_h<true>(Qh, nq, lane);
-  asm volatile("cp.async.wait_group 1;" ::: "memory");
-  __syncwarp();
-  att_convert_h<true>(Kh, nk, lane);
-  asm volatile("cp.async.wait_group 0;" ::: "memory");
-  __syncwarp();
-  att_convert_h<true>(Vh, nk, lane);
+  if (PLANES) {
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+  } else {
+    asm volatile("cp.async.wait_group 2;" ::: "memory");
+    __syncwarp();
+    att_convert_h<true>(Qh, nq, lane);
+    asm volatile("cp.async.wait_group 1;" ::: "memory");
+    __syncwarp();
+    att_convert_h<true>(Kh, nk, lane);
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncwarp();
+    att_convert_h<true>(Vh, nk, lane);
+  }
   __syncwarp();
 
   float S[MT][NT][4];
@@ -948,10 +976,11 @@ attention_fwd_h_kernel(AttnArgs a, AttOut out, int warp_bytes) {
   }
 }
 
-template <int MT, int NT>
+template <int MT, int NT, bool PLANES>
 __global__ void __launch_bounds__(ATT_TC_WARPS * 32)
 attention_bwd_h_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, AttOut dq, AttOut dk, AttOut dv, int warp_bytes) {
   constexpr int NP = (NT + 1) / 2;   // 16-key steps
+  constexpr int PV = PLANES ? ATT_HZ : ATT_HP;   // row pitch of the V and dO tiles: hi half-rows only when they arrive as planes
   pdl_trigger();
   pdl_wait();
   const int wid = threadIdx.x >> 5;
@@ -963,14 +992,22 @@ attention_bwd_h_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, AttO
   __half* Qh = reinterpret_cast<__half*>(reinterpret_cast<uint8_t*>(att_dyn) + (size_t)wid * warp_bytes);
   __half* Kh = Qh + nq * ATT_HP;
   __half* Vh = Kh + nk * ATT_HP;
-  __half* Oh = Vh + nk * ATT_HP;
-  __half* Z = Oh + nq * ATT_HP;      // one row of zeros
+  __half* Oh = Vh + nk * PV;
+  __half* Z = Oh + nq * PV;          // one row of zeros
   __half* Ds = Z + ATT_HZ;           // [nq][ATT_HS] dS (hi)
   __half* Ws = Ds + nq * ATT_HS;     // [nq][ATT_HS] post-dropout weights
-  att_stage_h(Qh, a.q + (size_t)b * nq * a.ldq + h * 64, nq, a.ldq, lane);
-  att_stage_h(Kh, a.k + (size_t)b * a.bsk + h * 64, nk, a.ldk, lane);
-  att_stage_h(Vh, a.v + (size_t)b * a.bsv + h * 64, nk, a.ldv, lane);
-  att_stage_h(Oh, dout + (size_t)b * nq * ldo + h * 64, nq, ldo, lane);
+  if (PLANES) {
+    const size_t oq = (size_t)b * nq * a.ldq + h * 64, ok = (size_t)b * a.bsk + h * 64, ov = (size_t)b * a.bsv + h * 64;
+    att_stage_p<true>(Qh, ATT_HP, reinterpret_cast<const __half*>(a.q) + oq, a.ql + oq, nq, a.ldq, lane);
+    att_stage_p<true>(Kh, ATT_HP, reinterpret_cast<const __half*>(a.k) + ok, a.kl + ok, nk, a.ldk, lane);
+    att_stage_p<false>(Vh, PV, reinterpret_cast<const __half*>(a.v) + ov, nullptr, nk, a.ldv, lane);
+    att_stage_p<false>(Oh, PV, reinterpret_cast<const __half*>(dout) + (size_t)b * nq * ldo + h * 64, nullptr, nq, ldo, lane);
+  } else {
+    att_stage_h(Qh, a.q + (size_t)b * nq * a.ldq + h * 64, nq, a.ldq, lane);
+    att_stage_h(Kh, a.k + (size_t)b * a.bsk + h * 64, nk, a.ldk, lane);
+    att_stage_h(Vh, a.v + (size_t)b * a.bsv + h * 64, nk, a.ldv, lane);
+    att_stage_h(Oh, dout + (size_t)b * nq * ldo + h * 64, nq, ldo, lane);
+  }
   for (int i = lane; i < ATT_HZ / 2; i += 32) reinterpret_cast<uint32_t*>(Z)[i] = 0u;
   // the dropout words of this (sample, head): call (row i, key tile c) is made once, by lane (i * NT + c) % 32, and left in the
   // score-tile region (free until dS / W are written) as four words; every lane then picks word t of the calls of its rows
@@ -996,18 +1033,22 @@ attention_bwd_h_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, AttO
       }
     }
   // the tensors land in issue order: convert each as soon as its group is complete, under the loads of the later ones
-  asm volatile("cp.async.wait_group 3;" ::: "memory");
-  __syncwarp();
-  att_convert_h<true>(Qh, nq, lane);
-  asm volatile("cp.async.wait_group 2;" ::: "memory");
-  __syncwarp();
-  att_convert_h<true>(Kh, nk, lane);
-  asm volatile("cp.async.wait_group 1;" ::: "memory");
-  __syncwarp();
-  att_convert_h<false>(Vh, nk, lane);
-  asm volatile("cp.async.wait_group 0;" ::: "memory");
-  __syncwarp();
-  att_convert_h<false>(Oh, nq, lane);
+  if (PLANES) {
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+  } else {
+    asm volatile("cp.async.wait_group 3;" ::: "memory");
+    __syncwarp();
+    att_convert_h<true>(Qh, nq, lane);
+    asm volatile("cp.async.wait_group 2;" ::: "memory");
+    __syncwarp();
+    att_convert_h<true>(Kh, nk, lane);
+    asm volatile("cp.async.wait_group 1;" ::: "memory");
+    __syncwarp();
+    att_convert_h<false>(Vh, nk, lane);
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncwarp();
+    att_convert_h<false>(Oh, nq, lane);
+  }
   __syncwarp();
 
   float S[MT][NT][4], dW[MT][NT][4];
@@ -1026,7 +1067,7 @@ attention_bwd_h_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, AttO
       const bool ok = r < nk;
       kp[nt] = (ok ? Kh + r * ATT_HP : Z) + 8 * mi;
       klp[nt] = (ok ? Kh + r * ATT_HP + ATT_HL : Z) + 8 * mi;
-      vp[nt] = (ok ? Vh + r * ATT_HP : Z) + 8 * mi;
+      vp[nt] = (ok ? Vh + r * PV : Z) + 8 * mi;
     }
     const __half* qp[MT]; const __half* qlp[MT]; const __half* op[MT];
 #pragma unroll
@@ -1035,7 +1076,7 @@ attention_bwd_h_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, AttO
       const bool ok = r < nq;
       qp[mt] = (ok ? Qh + r * ATT_HP : Z) + 8 * (mi >> 1);
       qlp[mt] = (ok ? Qh + r * ATT_HP + ATT_HL : Z) + 8 * (mi >> 1);
-      op[mt] = (ok ? Oh + r * ATT_HP : Z) + 8 * (mi >> 1);
+      op[mt] = (ok ? Oh + r * PV : Z) + 8 * (mi >> 1);
     }
 #pragma unroll 1
     for (int k2 = 0; k2 < 2; ++k2) {   // 32 head columns per pass
@@ -1212,8 +1253,8 @@ attention_bwd_h_kernel(AttnArgs a, const float* __restrict__ dout, int ldo, AttO
           }
     }
   }
-  att_h_TtX_store<MT, NP>(Ds, Qh, Z, nq, att_out_at(dk, (size_t)b * nk * dk.ld + h * 64), nk, lane);   // dK = dS^T . Q
-  att_h_TtX_store<MT, NP>(Ws, Oh, Z, nq, att_out_at(dv, (size_t)b * nk * dv.ld + h * 64), nk, lane);   // dV = W^T . dO
+  att_h_TtX_store<MT, NP>(Ds, Qh, ATT_HP, Z, nq, att_out_at(dk, (size_t)b * nk * dk.ld + h * 64), nk, lane);   // dK = dS^T . Q
+  att_h_TtX_store<MT, NP>(Ws, Oh, PV, Z, nq, att_out_at(dv, (size_t)b * nk * dv.ld + h * 64), nk, lane);       // dV = W^T . dO
 }
 
 // ---------------------------------------------------------------- row-block kernels: 32 < n <= 80 (cfg5: T = 64, R = 65)
@@ -1402,6 +1443,7 @@ static AttnArgs to_args(const B200iqAttention* p) {
   a.B = p->B; a.nh = p->num_heads; a.nq = p->nq; a.nk = p->nk; a.d = p->head_dim;
   a.scale = p->scale; a.drop_p = p->drop_p; a.seed = p->seed; a.offset = p->offset; a.seed_dev = p->seed_dev;
   a.rn = round_mode();
+  a.ql = (const __half*)p->q_lo; a.kl = (const __half*)p->k_lo; a.vl = (const __half*)p->v_lo;
   static const int dq2 = [] { const char* e = getenv("B200IQ_ATT_DQ2"); return (e && e[0] == '0') ? 0 : 1; }();
   a.dq2 = dq2;
   a.bsk = p->kv_batch_stride > 0 ? (size_t)p->kv_batch_stride : (size_t)p->nk * p->ldk;
@@ -1463,14 +1505,33 @@ static int attention_fwd_impl(const B200iqAttention* p, const AttOut& out, void*
     const int lds[] = {p->ldq, p->ldk, p->ldv};
     // B200IQ_ATT_FWD_H=0: the TF32 register kernel for the precise mode too (A/B switch)
     static const bool use_h = [] { const char* e = getenv("B200IQ_ATT_FWD_H"); return !(e && e[0] == '0'); }();
+    if (p->planes_in) {
+      const int lds8[] = {p->ldq, p->ldk, p->ldv};
+      bool okp = p->precise && p->head_dim == 64 && p->nq <= 32 && p->nk <= 32 && p->q_lo && p->k_lo && p->v_lo && outs_ok(&out, 1);
+      for (int i = 0; i < 3; ++i) okp = okp && (lds8[i] & 7) == 0;
+      const void* pp[] = {p->q, p->k, p->v, p->q_lo, p->k_lo, p->v_lo};
+      for (int i = 0; i < 6; ++i) okp = okp && (((uintptr_t)pp[i]) & 15) == 0;
+      B200IQ_CHECK_ARG(okp, "attention_fwd: planes_in needs precise mode, head_dim 64, nq, nk <= 32, all three lo planes, 16-byte aligned rows");
+      const int mt = a.nq > 16 ? 2 : 1, nt = (a.nk + 7) / 8, grid = (a.B * a.nh + ATT_TC_WARPS - 1) / ATT_TC_WARPS;
+      const int wbytes = (int)((att_hf_bytes(a.nq, a.nk, nt) + 15) & ~(size_t)15);
+      const size_t tsm = (size_t)ATT_TC_WARPS * wbytes;
+#define CALL(M_, N_) \
+  do { \
+    if (tsm > 48 * 1024) cudaFuncSetAttribute(attention_fwd_h_kernel<M_, N_, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm); \
+    launch_dep(attention_fwd_h_kernel<M_, N_, true>, dim3(grid), dim3(ATT_TC_WARPS * 32), tsm, (cudaStream_t)stream, a, out, wbytes); \
+  } while (0)
+      B200IQ_ATT_DISPATCH(mt, nt, CALL);
+#undef CALL
+      return launch_status("attention_fwd_h (planes)");
+    }
     if (use_h && p->precise && tc_ok(p, ptrs, 3, lds, 3, &out, 1)) {
       const int mt = a.nq > 16 ? 2 : 1, nt = (a.nk + 7) / 8, grid = (a.B * a.nh + ATT_TC_WARPS - 1) / ATT_TC_WARPS;
       const int wbytes = (int)((att_hf_bytes(a.nq, a.nk, nt) + 15) & ~(size_t)15);
       const size_t tsm = (size_t)ATT_TC_WARPS * wbytes;
 #define CALL(M_, N_) \
   do { \
-    if (tsm > 48 * 1024) cudaFuncSetAttribute(attention_fwd_h_kernel<M_, N_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm); \
-    launch_dep(attention_fwd_h_kernel<M_, N_>, dim3(grid), dim3(ATT_TC_WARPS * 32), tsm, (cudaStream_t)stream, a, out, wbytes); \
+    if (tsm > 48 * 1024) cudaFuncSetAttribute(attention_fwd_h_kernel<M_, N_, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm); \
+    launch_dep(attention_fwd_h_kernel<M_, N_, false>, dim3(grid), dim3(ATT_TC_WARPS * 32), tsm, (cudaStream_t)stream, a, out, wbytes); \
   } while (0)
       B200IQ_ATT_DISPATCH(mt, nt, CALL);
 #undef CALL
@@ -1512,14 +1573,33 @@ static int attention_bwd_impl(const B200iqAttention* p, const float* dout, const
     // B200IQ_ATT_BWD_H=0: keep the TF32 register kernel for the fp16-plane gradients too (A/B switch)
     static const bool use_h = [] { const char* e = getenv("B200IQ_ATT_BWD_H"); return !(e && e[0] == '0'); }();
     const bool planes_hi = dq.hi && dk.hi && dv.hi && !dq.lo && !dk.lo && !dv.lo;
+    if (p->planes_in) {
+      const int lds8[] = {p->ldq, p->ldk, p->ldv, p->ldo};
+      bool okp = p->precise && planes_hi && p->head_dim == 64 && p->nq <= 32 && p->nk <= 32 && p->q_lo && p->k_lo && outs_ok(outs, 3);
+      for (int i = 0; i < 4; ++i) okp = okp && (lds8[i] & 7) == 0;
+      const void* pp[] = {p->q, p->k, p->v, p->q_lo, p->k_lo, dout};
+      for (int i = 0; i < 6; ++i) okp = okp && (((uintptr_t)pp[i]) & 15) == 0;
+      B200IQ_CHECK_ARG(okp, "attention_bwd: planes_in needs precise mode, fp16-plane gradients, head_dim 64, nq, nk <= 32, q_lo / k_lo, 16-byte aligned rows");
+      const int mt = a.nq > 16 ? 2 : 1, nt = (a.nk + 7) / 8, grid = (a.B * a.nh + ATT_TC_WARPS - 1) / ATT_TC_WARPS;
+      const int wbytes = (int)((att_h_bytes(a.nq, a.nk, true) + 15) & ~(size_t)15);
+      const size_t tsm = (size_t)ATT_TC_WARPS * wbytes;
+#define CALL(M_, N_) \
+  do { \
+    if (tsm > 48 * 1024) cudaFuncSetAttribute(attention_bwd_h_kernel<M_, N_, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm); \
+    launch_dep(attention_bwd_h_kernel<M_, N_, true>, dim3(grid), dim3(ATT_TC_WARPS * 32), tsm, (cudaStream_t)stream, a, dout, p->ldo, dq, dk, dv, wbytes); \
+  } while (0)
+      B200IQ_ATT_DISPATCH(mt, nt, CALL);
+#undef CALL
+      return launch_status("attention_bwd_h (planes)");
+    }
     if (use_h && p->precise && planes_hi && tc_ok(p, ptrs, 4, lds, 4, outs, 3)) {
       const int mt = a.nq > 16 ? 2 : 1, nt = (a.nk + 7) / 8, grid = (a.B * a.nh + ATT_TC_WARPS - 1) / ATT_TC_WARPS;
       const int wbytes = (int)((att_h_bytes(a.nq, a.nk) + 15) & ~(size_t)15);
       const size_t tsm = (size_t)ATT_TC_WARPS * wbytes;
 #define CALL(M_, N_) \
   do { \
-    if (tsm > 48 * 1024) cudaFuncSetAttribute(attention_bwd_h_kernel<M_, N_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm); \
-    launch_dep(attention_bwd_h_kernel<M_, N_>, dim3(grid), dim3(ATT_TC_WARPS * 32), tsm, (cudaStream_t)stream, a, dout, p->ldo, dq, dk, dv, wbytes); \
+    if (tsm > 48 * 1024) cudaFuncSetAttribute(attention_bwd_h_kernel<M_, N_, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm); \
+    launch_dep(attention_bwd_h_kernel<M_, N_, false>, dim3(grid), dim3(ATT_TC_WARPS * 32), tsm, (cudaStream_t)stream, a, dout, p->ldo, dq, dk, dv, wbytes); \
   } while (0)
       B200IQ_ATT_DISPATCH(mt, nt, CALL);
 #undef CALL

@@ -303,6 +303,7 @@ class AttnParams(C.Structure):
         ("scale", C.c_float), ("drop_p", C.c_float), ("seed", C.c_uint64), ("offset", C.c_uint64),
         ("kv_batch_stride", C.c_longlong),
         ("precise", C.c_int), ("out_hi", C.c_void_p), ("out_lo", C.c_void_p), ("seed_dev", C.c_void_p),
+        ("planes_in", C.c_int), ("q_lo", C.c_void_p), ("k_lo", C.c_void_p), ("v_lo", C.c_void_p),
     ]
 
 
@@ -456,11 +457,24 @@ def axpby(x, y, out, a=1.0, b=1.0):
 
 # ------------------------------------------------------------------ attention
 def _attn_params(q, k, v, out, key_ids, pad_id, causal, B, nh, nq, nk, d, drop_p, seed, offset, kv_batch_stride=0):
+    """q / k / v: fp32 tensors, or Acts whose fp16 planes the projection GEMM wrote (planes_in: the hi planes go in as q / k / v,
+    row pitches in halves)"""
+    planes = isinstance(q, Act) and q.hi is not None
+    if planes:
+        qh, kh, vh = q.hi, k.hi, v.hi
+        p = AttnParams(qh.data_ptr(), kh.data_ptr(), vh.data_ptr(), out.data_ptr() if out is not None else 0,
+                       qh.stride(0), kh.stride(0), vh.stride(0), out.stride(0) if out is not None else 0,
+                       key_ids.data_ptr() if key_ids is not None else 0, pad_id, int(causal),
+                       B, nh, nq, nk, d, d ** -0.5, drop_p, seed, offset, kv_batch_stride, 0, None, None,
+                       _dp(SEED_DEV) if drop_p > 0 else None, 1, _dp(q.lo), _dp(k.lo), _dp(v.lo))
+        return p
+    if isinstance(q, Act):
+        q, k, v = q.f32, k.f32, v.f32
     return AttnParams(q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr() if out is not None else 0,
                       q.stride(0), k.stride(0), v.stride(0), out.stride(0) if out is not None else 0,
                       key_ids.data_ptr() if key_ids is not None else 0, pad_id, int(causal),
                       B, nh, nq, nk, d, d ** -0.5, drop_p, seed, offset, kv_batch_stride, 0, None, None,
-                      _dp(SEED_DEV) if drop_p > 0 else None)
+                      _dp(SEED_DEV) if drop_p > 0 else None, 0, None, None, None)
 
 
 def attention_fwd(q, k, v, out, key_ids, pad_id, causal, B, nh, nq, nk, d, drop_p=0.0, seed=0, offset=0, kv_batch_stride=0):
@@ -472,7 +486,7 @@ def attention_fwd(q, k, v, out, key_ids, pad_id, causal, B, nh, nq, nk, d, drop_
             return attention_fwd(q, k, v, out.f32, key_ids, pad_id, causal, B, nh, nq, nk, d, drop_p, seed, offset, kv_batch_stride)
         p = _attn_params(q, k, v, None, key_ids, pad_id, causal, B, nh, nq, nk, d, drop_p, seed, offset, kv_batch_stride)
         p.precise, p.out_hi, p.out_lo, p.ldo = 1, out.hi.data_ptr(), _dp(out.lo), _ld(out.hi)
-        # algorithmic bytes: q, k, v rows of every head once (fp32) + the output planes
+        # algorithmic bytes: q, k, v rows of every head once (fp32, or hi + lo planes: the same 4 bytes) + the output planes
         _call("b200iq_attention_fwd", C.byref(p), nbytes=4 * B * nh * d * (nq + 2 * nk) + 2 * B * nq * nh * d * (2 if out.lo is not None else 1))
         return out
     p = _attn_params(q, k, v, out, key_ids, pad_id, causal, B, nh, nq, nk, d, drop_p, seed, offset, kv_batch_stride)
@@ -482,8 +496,17 @@ def attention_fwd(q, k, v, out, key_ids, pad_id, causal, B, nh, nq, nk, d, drop_
 
 
 def attention_bwd(q, k, v, dout, dq, dk, dv, key_ids, pad_id, causal, B, nh, nq, nk, d, drop_p=0.0, seed=0, offset=0):
-    """dq / dk / dv: fp32 tensors, or fp16 tensors (the hi planes of the gradients: operands of the projections' backward GEMMs)"""
+    """dq / dk / dv: fp32 tensors, or fp16 tensors (the hi planes of the gradients: operands of the projections' backward GEMMs).
+    q / k / v / dout may be Acts with fp16 planes (planes_in: all four, dout as its hi plane)"""
     p = _attn_params(q, k, v, None, key_ids, pad_id, causal, B, nh, nq, nk, d, drop_p, seed, offset)
+    if p.planes_in:
+        assert isinstance(dout, Act) and dout.hi is not None and dq.dtype == torch.float16
+        p.ldo, p.precise = dout.hi.stride(0), 1
+        _call("b200iq_attention_bwd_f16", C.byref(p), _p(dout.hi), _p(dq), _p(dk), _p(dv), dq.stride(0), dk.stride(0), dv.stride(0),
+              nbytes=2 * B * nh * d * (2 * nq + 2 * nk + nk + nq) + 2 * B * nh * d * (nq + 2 * nk))
+        return
+    if isinstance(dout, Act):
+        dout = dout.f32
     p.ldo = dout.stride(0)
     if dq.dtype == torch.float16:
         p.precise = 1

@@ -21,6 +21,14 @@ CONCURRENT = os.environ.get("B200IQ_CONCURRENT", "1") == "1"
 # step / the whole forward and lose 1.2 / 0.5 ms to the starved side streams, see iq.py; =0 off)
 PDL_DECODER = os.environ.get("B200IQ_PDL", "3") == "3"
 CONCURRENT_DW = CONCURRENT and os.environ.get("B200IQ_CONCURRENT_DW", "1") == "1"
+# q | k | v (and the attention output's gradient) travel from the projection GEMMs to the attention kernels as fp16 planes
+# (hi + lo: the same bytes as fp32; hi only where the backward reads them) whenever the fp16 mma.sync attention kernels take the
+# shape (head_dim 64, n <= 32): those kernels then stage their operands without a conversion pass.  B200IQ_ATT_PLANES=0: fp32.
+ATT_PLANES = os.environ.get("B200IQ_ATT_PLANES", "1") == "1"
+
+
+def att_planes(c, nq, nk):
+    return ATT_PLANES and not ops.exact_mode() and c.d == 64 and nq <= 32 and nk <= 32
 
 
 class Workspace:
@@ -340,15 +348,30 @@ def self_attn_fwd(c, tag, pfx, xn, ids, B, n, causal):
     so the GEMM keeps its lean epilogue and the sum is written once, by the kernel that normalises it"""
     M, H = xn.shape
     wqkv = c.pspan(pfx + "query_linear.weight", pfx + "value_linear.weight", H)
-    qkv = c.ws.buf(tag + ".qkv", M, 3 * H)
-    ops.gemm2(xn, wqkv, qkv)
+    if att_planes(c, n, n):
+        qkv = c.act(tag + ".qkv", M, 3 * H)
+        ops.gemm2(xn, wqkv, planes=qkv)
+    else:
+        qkv = ops.Act(f32=c.ws.buf(tag + ".qkv", M, 3 * H))
+        ops.gemm2(xn, wqkv, qkv.f32)
     ctx = c.act(tag + ".ctx", M, H)
     seed, off = c.key(tag + ".adrop")
-    ops.attention_fwd(qkv[:, :H], qkv[:, H:2 * H], qkv[:, 2 * H:], ctx, ids, PAD, causal, B, c.nh, n, n, c.d,
+    ops.attention_fwd(qkv.cols(0, H), qkv.cols(H, 2 * H), qkv.cols(2 * H, 3 * H), ctx, ids, PAD, causal, B, c.nh, n, n, c.d,
                       c.attn_drop, seed, off)
     proj = c.ws.buf(tag + ".proj", M, H)
     ops.gemm2(ctx, c.W[pfx + "output_linear.weight"], proj)
     return proj
+
+
+def _dctx(c, dout, wo, M, H, planes):
+    """gradient wrt the merged heads = dout . W_o: an fp16 hi plane when the attention backward takes planes, else fp32"""
+    if planes:
+        d = c.gact("tmp.dctx.%d" % M, M, H)
+        ops.gemm2(dout, wo, planes=d, b_t=True, terms=1)
+        return d
+    d = c.ws.buf("tmp.dctx32.%d" % M, M, H)
+    ops.gemm2(dout, wo, d, b_t=True, terms=1)
+    return ops.Act(f32=d)
 
 
 def _grad_parts(a, *col_ranges):
@@ -360,16 +383,15 @@ def _grad_parts(a, *col_ranges):
 def self_attn_bwd(c, tag, pfx, dout, xn, ids, B, n, causal):
     """dout: the block-output gradient as an operand; xn: the block's LayerNorm-ed input operand.  Returns fp32 grad wrt xn."""
     M, H = xn.shape
-    qkv, ctx = c.ws[tag + ".qkv"], c.ws.act(tag + ".ctx")
+    qkv, ctx = c.ws.act(tag + ".qkv"), c.ws.act(tag + ".ctx")
     ev = c.mark()
-    dctx = c.ws.buf("tmp.dctx.%d" % M, M, H)
-    ops.gemm2(dout, c.W[pfx + "output_linear.weight"], dctx, b_t=True, terms=1)
+    dctx = _dctx(c, dout, c.W[pfx + "output_linear.weight"], M, H, att_planes(c, n, n))
     c.on_side(lambda: grad_w(c, dout, ctx, c.G[pfx + "output_linear.weight"]), ev)
     dout_read = c.side_mark()
     dqkv = c.gact("tmp.dqkv.%d" % M, M, 3 * H)
     dq, dk, dv = _grad_parts(dqkv, (0, H), (H, 2 * H), (2 * H, 3 * H))
     seed, off = c.key(tag + ".adrop")
-    ops.attention_bwd(qkv[:, :H], qkv[:, H:2 * H], qkv[:, 2 * H:], dctx, dq, dk, dv,
+    ops.attention_bwd(qkv.cols(0, H), qkv.cols(H, 2 * H), qkv.cols(2 * H, 3 * H), dctx, dq, dk, dv,
                       ids, PAD, causal, B, c.nh, n, n, c.d, c.attn_drop, seed, off)
     ev = c.mark()
     dxn = c.ws.buf("tmp.dxn.%d" % M, M, H)
@@ -379,23 +401,33 @@ def self_attn_bwd(c, tag, pfx, dout, xn, ids, B, n, causal):
     return dxn                    # the rest of the side work at the end of the layer
 
 
-def cross_kv_fwd(c, tag, pfx, enc_out):
+def cross_kv_fwd(c, tag, pfx, enc_out, planes=False):
     """K | V of the context for one decoder layer: depends only on enc_out, so decoder_fwd computes all layers' up front"""
-    kv = c.ws.buf(tag + ".kv", enc_out.shape[0], 2 * c.H)
-    ops.gemm2(enc_out, c.pspan(pfx + "key_linear.weight", pfx + "value_linear.weight", c.H), kv)
+    wkv = c.pspan(pfx + "key_linear.weight", pfx + "value_linear.weight", c.H)
+    if planes:
+        kv = c.act(tag + ".kv", enc_out.shape[0], 2 * c.H)
+        ops.gemm2(enc_out, wkv, planes=kv)
+    else:
+        kv = ops.Act(f32=c.ws.buf(tag + ".kv", enc_out.shape[0], 2 * c.H))
+        ops.gemm2(enc_out, wkv, kv.f32)
     return kv
 
 
 def cross_attn_fwd(c, tag, pfx, xn, enc_out, enc_ids, B, nq, nk, kv=None):
     """returns the output projection without the residual (see self_attn_fwd)"""
     M, H = xn.shape
-    q = c.ws.buf(tag + ".q", M, H)
-    ops.gemm2(xn, c.W[pfx + "query_linear.weight"], q)
+    planes = att_planes(c, nq, nk)
+    if planes:
+        q = c.act(tag + ".q", M, H)
+        ops.gemm2(xn, c.W[pfx + "query_linear.weight"], planes=q)
+    else:
+        q = ops.Act(f32=c.ws.buf(tag + ".q", M, H))
+        ops.gemm2(xn, c.W[pfx + "query_linear.weight"], q.f32)
     if kv is None:
-        kv = cross_kv_fwd(c, tag, pfx, enc_out)
+        kv = cross_kv_fwd(c, tag, pfx, enc_out, planes)
     ctx = c.act(tag + ".ctx", M, H)
     seed, off = c.key(tag + ".adrop")
-    ops.attention_fwd(q, kv[:, :H], kv[:, H:], ctx, enc_ids, PAD, False, B, c.nh, nq, nk, c.d, c.attn_drop, seed, off)
+    ops.attention_fwd(q, kv.cols(0, H), kv.cols(H, 2 * H), ctx, enc_ids, PAD, False, B, c.nh, nq, nk, c.d, c.attn_drop, seed, off)
     proj = c.ws.buf(tag + ".proj", M, H)
     ops.gemm2(ctx, c.W[pfx + "output_linear.weight"], proj)
     return proj
@@ -404,17 +436,16 @@ def cross_attn_fwd(c, tag, pfx, xn, enc_out, enc_ids, B, nq, nk, kv=None):
 def cross_attn_bwd(c, tag, pfx, dout, xn, enc_out, d_enc_out, first, enc_ids, B, nq, nk):
     M, H = xn.shape
     Me = enc_out.shape[0]
-    q, kv, ctx = c.ws[tag + ".q"], c.ws[tag + ".kv"], c.ws.act(tag + ".ctx")
+    q, kv, ctx = c.ws.act(tag + ".q"), c.ws.act(tag + ".kv"), c.ws.act(tag + ".ctx")
     ev = c.mark()
-    dctx = c.ws.buf("tmp.dctx.%d" % M, M, H)
-    ops.gemm2(dout, c.W[pfx + "output_linear.weight"], dctx, b_t=True, terms=1)
+    dctx = _dctx(c, dout, c.W[pfx + "output_linear.weight"], M, H, att_planes(c, nq, nk))
     c.on_side(lambda: grad_w(c, dout, ctx, c.G[pfx + "output_linear.weight"]), ev)
     dout_read = c.side_mark()
     dqa = c.gact("tmp.dq.%d" % M, M, H)
     dkva = c.gact("tmp.dkv.%d" % Me, Me, 2 * H)
     (dq,), (dk, dv) = _grad_parts(dqa, (0, H)), _grad_parts(dkva, (0, H), (H, 2 * H))
     seed, off = c.key(tag + ".adrop")
-    ops.attention_bwd(q, kv[:, :H], kv[:, H:], dctx, dq, dk, dv, enc_ids, PAD, False, B, c.nh, nq, nk,
+    ops.attention_bwd(q, kv.cols(0, H), kv.cols(H, 2 * H), dctx, dq, dk, dv, enc_ids, PAD, False, B, c.nh, nq, nk,
                       c.d, c.attn_drop, seed, off)
     def off_path():
         # the context-side 2560-row GEMMs (20-40 tiles) and the query weight gradient: none feeds the decoder's dX chain
@@ -525,7 +556,7 @@ def decoder_fwd(c, tag, pfx, x, ids, enc_out, enc_ids, B, T, S, NL, out_kind="ac
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side), _lib.pinned_stream():
             for i in range(NL):
-                kvs[i] = cross_kv_fwd(c, "%s.%d.ca" % (tag, i), "%sdec.%d.multi_head_attention_enc_dec." % (pfx, i), enc_out)
+                kvs[i] = cross_kv_fwd(c, "%s.%d.ca" % (tag, i), "%sdec.%d.multi_head_attention_enc_dec." % (pfx, i), enc_out, att_planes(c, T, S))
     xn1 = ln_fwd(c, tag + ".0.ln1", pfx + "dec.0.layer_norm_mha_dec", x)
     pdl_prev = None
     for i in range(NL):

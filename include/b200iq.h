@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define B200IQ_ABI_VERSION 2
+#define B200IQ_ABI_VERSION 3
 
 int b200iq_abi_version(void);
 /* 1 when the current device is compute capability 10.0, else 0 */
@@ -201,6 +201,12 @@ typedef struct B200iqAttention {
   void* out_hi;          /* precise forward: fp16 planes of the merged-head output (ldo halves) written instead of `out` when */
   void* out_lo;          /*   out_hi != NULL (out_lo optional) */
   const unsigned long long* seed_dev; /* NULL, or a device word added to `seed` at run time (see B200iqGemmF16.drop_seed_dev) */
+  /* planes_in = 1 (precise mode, head_dim 64, nq, nk <= 32): q / k / v are the fp16 HI planes of the projections (what
+   * b200iq_gemm_f16 writes through C_hi / C_lo), q_lo / k_lo / v_lo their lo planes, ldq / ldk / ldv row pitches in halves
+   * (multiples of 8, 16-byte aligned bases).  The kernels then stage the operands without a conversion pass; the backward reads
+   * v as hi only (v_lo may be NULL there) and takes `dout` of b200iq_attention_bwd_f16 as an fp16 hi plane with pitch ldo halves. */
+  int planes_in;
+  const void* q_lo; const void* k_lo; const void* v_lo;
 } B200iqAttention;
 /* replaces: models/transformer_layers.py:494-526; mask fill is the finite -1e18 of :506 */
 int b200iq_attention_fwd(const B200iqAttention* p, void* stream);

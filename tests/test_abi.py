@@ -22,7 +22,7 @@ def test_library_exports_every_declared_symbol(built_lib):
     assert len(names) >= 28
     for n in names:
         assert hasattr(lib, n), "libb200iq.so does not export %s" % n
-    assert lib.b200iq_abi_version() == 2
+    assert lib.b200iq_abi_version() == 3
 
 
 def test_argument_errors_are_reported_without_a_launch(built_lib):

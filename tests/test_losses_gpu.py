@@ -169,6 +169,20 @@ def test_attention_backward_into_fp16_planes(ops, nq, nk, causal, drop):
         qr, kr, vr = (t.double().clone().requires_grad_(True) for t in (q, k.contiguous(), v.contiguous()))
         _ref_attention(qr, kr, vr, ids, causal, B, nh, nq, nk, d).backward(do.double())
         assert rel(dq, qr.grad) < 2e-3 and rel(dkv[:, :H], kr.grad) < 2e-3 and rel(dkv[:, H:], vr.grad) < 2e-3
+    if nq <= 32 and nk <= 32:
+        # planes_in: the same operands handed over as the fp16 planes a projection GEMM would have written (hi = fp16(x),
+        # lo = fp16(x - hi)) — the kernels stage them without converting and must produce the same bits
+        def planes(x, lo=True):
+            hi = x.half()
+            return ops.Act(hi=hi, lo=(x - hi.float()).half() if lo else None)
+        qa, kva, doa = planes(q), planes(kv), planes(do, lo=False)
+        ka, va = kva.cols(0, H), kva.cols(H, 2 * H)
+        act2 = ops.Act(hi=torch.zeros_like(act.hi), lo=torch.zeros_like(act.lo))
+        ops.attention_fwd(qa, ka, va, act2, ids, 0, causal, B, nh, nq, nk, d, *key)
+        assert torch.equal(act2.hi, act.hi) and torch.equal(act2.lo, act.lo)
+        dq2, dkv2 = torch.zeros_like(dq), torch.zeros_like(dkv)
+        ops.attention_bwd(qa, ka, va, doa, dq2, dkv2[:, :H], dkv2[:, H:], ids, 0, causal, B, nh, nq, nk, d, *key)
+        assert torch.equal(dq2, dq) and torch.equal(dkv2, dkv)
 
 
 def test_ce_rows_and_aux(ops):
