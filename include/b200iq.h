@@ -195,9 +195,10 @@ typedef struct B200iqAttention {
   uint64_t seed, offset;
   long long kv_batch_stride; /* elements between consecutive samples' K (and V) blocks; 0 = nk*ldk / nk*ldv (dense [B*nk, ld]).
                                 A KV cache [B, max_len, H] read at length nk passes max_len*H here (forward only). */
-  int precise;           /* 1 (head_dim 64, n <= 80): q / k / v are unrounded fp32; the forward's QK^T and PV run as 3-term TF32
-                            products (hi.hi + lo.hi + hi.lo, ~2^-21), the backward recomputes the scores the same way and rounds
-                            (instead of truncating) the operands of its single-pass products.  0: legacy TF32 single pass. */
+  int precise;           /* 1 (head_dim 64, n <= 80): q / k / v are unrounded fp32; the forward's QK^T and PV run as 3-term
+                            products (hi.hi + lo.hi + hi.lo, ~2^-21: fp16 mma.sync with ldmatrix fragments for n <= 32, TF32 terms
+                            split in registers above that), the backward recomputes the scores the same way and rounds (instead of
+                            truncating) the operands of its single-pass products.  0: legacy TF32 single pass. */
   void* out_hi;          /* precise forward: fp16 planes of the merged-head output (ldo halves) written instead of `out` when */
   void* out_lo;          /*   out_hi != NULL (out_lo optional) */
   const unsigned long long* seed_dev; /* NULL, or a device word added to `seed` at run time (see B200iqGemmF16.drop_seed_dev) */
