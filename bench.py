@@ -25,7 +25,7 @@ sys.path.insert(0, ROOT)
 import torch  # noqa: E402
 
 DTYPES = {"transformer": "f16 (fp16 operand planes: 3-term hi/lo forward products, single-pass backward under a loss scale; fp32 accumulate, fp32 master weights)",
-          "lstm": "f16 (fp16 operand planes like the transformer; the persistent recurrence is a 3-term TF32 mma.sync product; fp32 accumulate, fp32 master weights)"}
+          "lstm": "f16 (fp16 operand planes like the transformer; the persistent recurrence is a 3-term fp16 mma.sync product over hi / lo halves; fp32 accumulate, fp32 master weights)"}
 METRIC = "iq_train_samples_per_sec"
 UNIT = "samples/s"
 

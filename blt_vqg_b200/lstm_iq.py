@@ -253,7 +253,7 @@ class LSTMIQ(nn.Module):
             hbuf[0].copy_(h0)
             cbuf[0].copy_(c0)
         if PERSISTENT and ops.lstm_seq_supported(H):
-            # the whole recurrence in one launch; the kernel splits h and the fp32 master W_hh into TF32 hi / lo itself (3-term)
+            # the whole recurrence in one launch; the kernel splits its slice of the fp32 master W_hh (once) and h (per step) into fp16 hi / lo itself (3-term)
             ops.lstm_seq_fwd(gates, P[pfx + "weight_hh_l0"], hbuf, cbuf, lengths)
             return hbuf
         for t in range(T):
